@@ -1,0 +1,132 @@
+/* libtvi — C ABI of the B200-native (sm_100a) hot path for SVD keyframe interpolation.
+ *
+ * This is the drop-in boundary: every symbol below is what the reference's
+ * Python code would bind through ctypes in place of a torch/xformers/numpy call.  Citations are
+ * path:line inside the reference tree (dreamyou070/Timelapse_Video_Interpolation).
+ *
+ * Conventions
+ *   - every pointer is a DEVICE pointer unless the parameter name ends in `_host`;
+ *   - bf16 tensors are passed as `const tvi_bf16*` (raw 16-bit storage, torch.bfloat16 layout);
+ *   - all leading dimensions / strides are in ELEMENTS, rows are tokens, heads are packed along
+ *     the row (head h occupies columns [h*d, (h+1)*d)), so a fused [tokens, 3C] QKV buffer is
+ *     consumed in place with ldq = ldk = ldv = 3C and three base pointers;
+ *   - `stream` is a cudaStream_t (0 = legacy default stream); nothing synchronises the host;
+ *   - nothing allocates: outputs and workspaces are caller-provided;
+ *   - return value: 0 on success, a negative TVI_ERR_* otherwise; the message is available from
+ *     tvi_last_error() (thread-local).  There is NO CPU fallback anywhere behind this ABI.
+ */
+#ifndef TVI_H_
+#define TVI_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef uint16_t tvi_bf16;
+
+#define TVI_OK 0
+#define TVI_ERR_INVALID (-1)     /* bad argument (shape, alignment, null pointer)          */
+#define TVI_ERR_CUDA (-2)        /* a CUDA runtime/driver call or a kernel launch failed    */
+#define TVI_ERR_UNSUPPORTED (-3) /* valid request this build has no kernel for (e.g. d=96)  */
+
+/* Library identity / diagnostics. */
+const char* tvi_version(void);
+const char* tvi_last_error(void);
+/* Fills SM count and compute capability of the current device. */
+int tvi_device_info(int* sm_count, int* cc_major, int* cc_minor);
+
+/* ---------------------------------------------------------------------------------------------
+ * A1  first/last-frame latent slerp.
+ * Replaces: frame_slerp_interp.py (0 bytes in the reference; unused flags at
+ * src/train_decouples.py:1566-1567, src/test.py:648-649).  Spec: SURVEY.md §8.1 row A1.
+ *   v0, v1 : [nclips, n] fp32      out : [nclips, T, n] fp32
+ *   c = <v0,v1>/(|v0||v1|) per clip (fp64 accumulation); |c| > dot_threshold -> lerp, else slerp
+ *   with t_i = i/(T-1).  T >= 2, n % 4 == 0, pointers 16-byte aligned.
+ */
+int tvi_slerp_f32(const float* v0, const float* v1, float* out, int64_t nclips, int64_t n, int T,
+                  float dot_threshold, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * A6  mean per-pixel cosine similarity of two optical-flow fields.
+ * Replaces: cosine_similarity(flow_a, flow_b), dataset_construction/step4_flow_check.py:25-34.
+ *   fa, fb : [npairs, H, W, 2] fp32 if hwc_layout != 0 (OpenCV layout, step4_flow_check.py:22),
+ *            [npairs, 2, H, W] otherwise.     out : [npairs] fp32.
+ *   workspace : tvi_flow_cosine_workspace_bytes(npairs, H, W) bytes, 8-byte aligned.
+ */
+size_t tvi_flow_cosine_workspace_bytes(int64_t npairs, int H, int W);
+int tvi_flow_cosine_f32(const float* fa, const float* fb, float* out, void* workspace, int64_t npairs, int H,
+                        int W, int hwc_layout, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * A7  backward warp + forward/backward consistency check (north-star extension; the reference
+ * file dataset_construction/step4_flow_check.py has no warp — spec in SURVEY.md §8.1 row A7,
+ * oracle = torch.nn.functional.grid_sample(bilinear, zeros, align_corners=True)).
+ *   img2 : [B, C, H, W] fp32   f_fwd, f_bwd : [B, 2, H, W] fp32 (x then y displacement, pixels)
+ *   warped : [B, C, H, W] fp32  = bilinear sample of img2 at p + f_fwd(p), zero outside
+ *   mask   : [B, H, W] u8, bit0 = occluded: |f_fwd + b~|^2 > alpha(|f_fwd|^2 + |b~|^2) + beta with
+ *            b~ = f_bwd sampled at p + f_fwd(p); bit1 = sample point inside the image.
+ */
+int tvi_backward_warp_f32(const float* img2, const float* f_fwd, const float* f_bwd, float* warped,
+                          uint8_t* mask, int64_t B, int C, int H, int W, float alpha, float beta,
+                          void* stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * A2/A3  projections: Y[M,N] = X[M,K] . W[N,K]^T (+ bias[N]), bf16 in/out, fp32 accumulation
+ * (tcgen05.mma, TMEM accumulators, TMA-fed).
+ * Replaces: attn.to_q / to_k / to_v / to_out[0] (nn.Linear -> cuBLAS),
+ * src/models/attention_processor.py:729,736-737,754 and :1223,1230-1231,1251.
+ *   ldx, ldw, ldy: row strides in elements (multiples of 8); K % 8 == 0; N % 8 == 0;
+ *   X, W, Y 16-byte aligned; bias nullable.
+ */
+int tvi_gemm_bf16_tn(const tvi_bf16* X, const tvi_bf16* W, const tvi_bf16* bias, tvi_bf16* Y, int64_t M, int N,
+                     int K, int64_t ldx, int64_t ldw, int64_t ldy, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * A3c  short-sequence (temporal) attention core: nseq independent sequences, every head,
+ * O = softmax(scale . Q K^T) V with fp32 softmax.  Sequence s owns query rows [s*Tq, (s+1)*Tq)
+ * and key/value rows [s*Tk, (s+1)*Tk).  1 <= Tq, Tk <= 64, d == 64.
+ * Replaces: F.scaled_dot_product_attention / xformers / baddbmm+softmax+bmm on the
+ * [B*S, T, C] operands, src/models/attention_processor.py:1243, :1156, :598-615+:750, called from
+ * src/models/attention.py:451-453.
+ *   lse (nullable): [nseq*Tq, heads] fp32 natural-log-sum-exp of the scaled logits (for backward).
+ */
+int tvi_attn_temporal_fwd(const tvi_bf16* q, const tvi_bf16* k, const tvi_bf16* v, tvi_bf16* o, float* lse,
+                          int64_t nseq, int heads, int Tq, int Tk, int d, int64_t ldq, int64_t ldk,
+                          int64_t ldv, int64_t ldo, float scale, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * A3b/A3d  few-key cross-attention core (image-embedding context, 1..8 keys): query row r attends
+ * to the L key/value rows of context group (r / rows_per_group).
+ * Replaces the same call sites as above for attn2 (src/models/attention.py:311-316, :457-459) and
+ * the patched temporal forward src/train_decouples.py:377-495 (additive ramp bias :437-457 and
+ * per-frame mean-logit statistics :460-471).
+ *   q : [nrows, heads*d] (ldq)   k, v : [ngroups*L, heads*d] (ldk, ldv)   o : [nrows, heads*d] (ldo)
+ *   bias  (nullable): [Tq, L] fp32 added to the scaled logits of query row r at index r % Tq
+ *   stats (nullable): [Tq, L] fp32, receives the mean over (rows with r % Tq == t, heads) of the
+ *                     pre-softmax logits (after bias).  stats_ws: Tq*L doubles (zeroed by the call).
+ *   Tq is only used to index bias/stats (pass 1 if both are null).  d in {64, 128}, L <= 8.
+ */
+int tvi_attn_fewkeys_fwd(const tvi_bf16* q, const tvi_bf16* k, const tvi_bf16* v, tvi_bf16* o, int64_t nrows,
+                         int64_t rows_per_group, int heads, int L, int d, int64_t ldq, int64_t ldk,
+                         int64_t ldv, int64_t ldo, float scale, int Tq, const float* bias, float* stats,
+                         void* stats_ws, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * A3a  spatial self-attention core (flash-style, tcgen05 QK^T and PV, online fp32 softmax):
+ * batch independent sequences of S query rows and Skv key rows, no mask, non-causal.
+ * Replaces: F.scaled_dot_product_attention / xformers.ops.memory_efficient_attention on
+ * [BF, h, S, 64], src/models/attention_processor.py:1243, :1156 (called from
+ * src/models/attention.py:276-281).  d == 64.
+ *   lse (nullable): [batch*S, heads] fp32.
+ */
+int tvi_attn_spatial_fwd(const tvi_bf16* q, const tvi_bf16* k, const tvi_bf16* v, tvi_bf16* o, float* lse,
+                         int batch, int heads, int S, int Skv, int d, int64_t ldq, int64_t ldk, int64_t ldv,
+                         int64_t ldo, float scale, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* TVI_H_ */

@@ -1,0 +1,476 @@
+// A3c / A3b / A3d — the two HBM-bound attention cores.
+//
+// tvi_attn_temporal_fwd : nseq x heads independent problems of T<=64 tokens, d=64.  One warp
+//   per (sequence, head): the three T x 64 bf16 tiles are staged in shared memory with 128-bit
+//   cp.async copies (each tile row is one full 128-byte line; rows live in XOR-swizzled 16-byte
+//   chunks so ldmatrix is conflict-free), double-buffered per warp so the next problem's loads
+//   are in flight while this one computes.  QK^T and PV run on mma.sync m16n8k16 (a 14x14
+//   problem cannot fill a 128-row tcgen05 tile; CUDA-core FMAs would be 1.4x short of the HBM
+//   roofline), softmax is fp32 in registers with quad shuffles, and O goes back through shared
+//   memory so every global store is a coalesced 128-bit write.
+//   Algorithmic HBM bytes: 4 * rows * heads*d * 2 (Q, K, V read once, O written once).
+//
+// tvi_attn_fewkeys_fwd : cross-attention against 1..8 context tokens that are shared by
+//   rows_per_group query rows.  K/V of the group stay in registers; each thread owns one 16-byte
+//   channel chunk and walks down the rows, the 64-wide dot products are reduced across the 8
+//   (d=64) or 16 (d=128) lanes of a head with shuffles.  With one key the softmax is exactly 1,
+//   so Q is never read.  Optional additive [Tq,L] bias and fused [Tq,L] mean-logit statistics
+//   replace the reference's 2*T .item() syncs (src/train_decouples.py:437-471).
+//   Algorithmic HBM bytes: 2 * rows * heads*d * 2 (Q read, O written); L == 1: rows*heads*d*2.
+#include "tvi_common.cuh"
+
+namespace tvi {
+namespace {
+
+// ---------------------------------------------------------------------------------------------
+// temporal (short-sequence) attention
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ void ldsm_x4(uint32_t addr, uint32_t& r0, uint32_t& r1, uint32_t& r2, uint32_t& r3) {
+  asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r0), "=r"(r1), "=r"(r2), "=r"(r3)
+               : "r"(addr)
+               : "memory");
+}
+__device__ __forceinline__ void ldsm_x4_t(uint32_t addr, uint32_t& r0, uint32_t& r1, uint32_t& r2, uint32_t& r3) {
+  asm volatile("ldmatrix.sync.aligned.m8n8.x4.trans.shared.b16 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r0), "=r"(r1), "=r"(r2), "=r"(r3)
+               : "r"(addr)
+               : "memory");
+}
+__device__ __forceinline__ void mma_bf16_16816(float* c, const uint32_t* a, uint32_t b0, uint32_t b1) {
+  asm volatile(
+      "mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+      : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+      : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+
+// byte offset of 16-byte chunk `c` (0..7) of row `r` inside a [rows][64] bf16 tile
+__device__ __forceinline__ uint32_t tile_off(int r, int c) { return (uint32_t)(r * 128 + ((c ^ (r & 7)) << 4)); }
+
+template <int MT>
+struct TemporalCfg {
+  static constexpr int kRows = 16 * MT;
+  static constexpr int kTileBytes = kRows * 128;
+  static constexpr int kStageBytes = 3 * kTileBytes;
+  static constexpr int kWarps = (MT == 4) ? 4 : 8;
+  static constexpr int kSmemBytes = kWarps * 2 * kStageBytes;
+};
+
+template <int MT>
+__device__ __forceinline__ void temporal_issue_loads(uint32_t stage_smem, const tvi_bf16* q, const tvi_bf16* k,
+                                                     const tvi_bf16* v, int64_t item, int heads, int Tq, int Tk,
+                                                     int64_t ldq, int64_t ldk, int64_t ldv, int lane) {
+  constexpr int kRows = 16 * MT;
+  const int64_t seq = item / heads;
+  const int head = (int)(item - seq * heads);
+  const tvi_bf16* qb = q + seq * Tq * ldq + head * 64;
+  const tvi_bf16* kb = k + seq * Tk * ldk + head * 64;
+  const tvi_bf16* vb = v + seq * Tk * ldv + head * 64;
+  const int c = lane & 7;
+#pragma unroll
+  for (int i = 0; i < kRows / 4; ++i) {
+    const int r = (lane >> 3) + 4 * i;
+    const uint32_t off = tile_off(r, c);
+    const bool pq = r < Tq, pk = r < Tk;
+    // rows past the sequence are zero-filled (src-size 0): padded K rows are masked in the
+    // softmax, padded V rows must be finite because they are multiplied by P = 0.
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(stage_smem + off),
+                 "l"(pq ? qb + r * ldq + c * 8 : qb), "r"(pq ? 16 : 0)
+                 : "memory");
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(stage_smem + kRows * 128 + off),
+                 "l"(pk ? kb + r * ldk + c * 8 : kb), "r"(pk ? 16 : 0)
+                 : "memory");
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(stage_smem + 2 * kRows * 128 + off),
+                 "l"(pk ? vb + r * ldv + c * 8 : vb), "r"(pk ? 16 : 0)
+                 : "memory");
+  }
+}
+
+template <int MT>
+__global__ void __launch_bounds__(TemporalCfg<MT>::kWarps * 32)
+attn_temporal_kernel(const tvi_bf16* __restrict__ q, const tvi_bf16* __restrict__ k, const tvi_bf16* __restrict__ v,
+                     tvi_bf16* __restrict__ o, float* __restrict__ lse, int64_t nitems, int heads, int Tq, int Tk,
+                     int64_t ldq, int64_t ldk, int64_t ldv, int64_t ldo, float scale) {
+  using Cfg = TemporalCfg<MT>;
+  constexpr int kRows = Cfg::kRows;
+  constexpr int NT = 2 * MT;  // 8-key column tiles of S
+  extern __shared__ __align__(128) uint8_t smem_raw[];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t warp_smem = smem_u32(smem_raw) + warp * 2 * Cfg::kStageBytes;
+  uint8_t* warp_ptr = smem_raw + warp * 2 * Cfg::kStageBytes;
+
+  const int64_t gw = (int64_t)blockIdx.x * Cfg::kWarps + warp;
+  const int64_t stride = (int64_t)gridDim.x * Cfg::kWarps;
+  const float sl2 = scale * 1.4426950408889634f;
+  const int g = lane >> 2, qd = lane & 3;
+
+  int64_t item = gw;
+  int stage = 0;
+  if (item < nitems) temporal_issue_loads<MT>(warp_smem, q, k, v, item, heads, Tq, Tk, ldq, ldk, ldv, lane);
+  cp_async_commit();
+
+  for (; item < nitems; item += stride, stage ^= 1) {
+    const int64_t next = item + stride;
+    if (next < nitems)
+      temporal_issue_loads<MT>(warp_smem + (stage ^ 1) * Cfg::kStageBytes, q, k, v, next, heads, Tq, Tk, ldq, ldk, ldv,
+                               lane);
+    cp_async_commit();
+    cp_async_wait<1>();
+    __syncwarp();
+
+    const uint32_t sQ = warp_smem + stage * Cfg::kStageBytes;
+    const uint32_t sK = sQ + kRows * 128;
+    const uint32_t sV = sK + kRows * 128;
+    uint8_t* pQ = warp_ptr + stage * Cfg::kStageBytes;
+    const int64_t seq = item / heads;
+    const int head = (int)(item - seq * heads);
+
+#pragma unroll
+    for (int mt = 0; mt < MT; ++mt) {
+      if (mt * 16 >= Tq) break;
+      // ---- S = Q K^T ---------------------------------------------------------------
+      float s[NT][4];
+#pragma unroll
+      for (int nt = 0; nt < NT; ++nt) s[nt][0] = s[nt][1] = s[nt][2] = s[nt][3] = 0.f;
+#pragma unroll
+      for (int ks = 0; ks < 4; ++ks) {
+        uint32_t a[4];
+        ldsm_x4(sQ + tile_off(mt * 16 + (lane & 7) + ((lane >> 3) & 1) * 8, 2 * ks + (lane >> 4)), a[0], a[1], a[2], a[3]);
+#pragma unroll
+        for (int np = 0; np < MT; ++np) {
+          uint32_t b0, b1, b2, b3;
+          ldsm_x4(sK + tile_off(np * 16 + (lane & 7) + (lane >> 4) * 8, 2 * ks + ((lane >> 3) & 1)), b0, b1, b2, b3);
+          mma_bf16_16816(s[2 * np], a, b0, b1);
+          mma_bf16_16816(s[2 * np + 1], a, b2, b3);
+        }
+      }
+      // ---- softmax over keys (rows g and g+8 of this m-tile) ---------------------------
+      float m0 = -INFINITY, m1 = -INFINITY;
+#pragma unroll
+      for (int nt = 0; nt < NT; ++nt) {
+        const int col = nt * 8 + qd * 2;
+        if (col >= Tk) s[nt][0] = s[nt][2] = -INFINITY;
+        if (col + 1 >= Tk) s[nt][1] = s[nt][3] = -INFINITY;
+        m0 = fmaxf(m0, fmaxf(s[nt][0], s[nt][1]));
+        m1 = fmaxf(m1, fmaxf(s[nt][2], s[nt][3]));
+      }
+      m0 = fmaxf(m0, __shfl_xor_sync(0xffffffffu, m0, 1));
+      m0 = fmaxf(m0, __shfl_xor_sync(0xffffffffu, m0, 2));
+      m1 = fmaxf(m1, __shfl_xor_sync(0xffffffffu, m1, 1));
+      m1 = fmaxf(m1, __shfl_xor_sync(0xffffffffu, m1, 2));
+      const float ms0 = m0 * sl2, ms1 = m1 * sl2;
+      float l0 = 0.f, l1 = 0.f;
+      uint32_t p[NT][2];
+#pragma unroll
+      for (int nt = 0; nt < NT; ++nt) {
+        const float e0 = fast_exp2(fmaf(s[nt][0], sl2, -ms0)), e1 = fast_exp2(fmaf(s[nt][1], sl2, -ms0));
+        const float e2 = fast_exp2(fmaf(s[nt][2], sl2, -ms1)), e3 = fast_exp2(fmaf(s[nt][3], sl2, -ms1));
+        l0 += e0 + e1;
+        l1 += e2 + e3;
+        p[nt][0] = pack_bf16x2(e0, e1);
+        p[nt][1] = pack_bf16x2(e2, e3);
+      }
+      l0 += __shfl_xor_sync(0xffffffffu, l0, 1);
+      l0 += __shfl_xor_sync(0xffffffffu, l0, 2);
+      l1 += __shfl_xor_sync(0xffffffffu, l1, 1);
+      l1 += __shfl_xor_sync(0xffffffffu, l1, 2);
+      // ---- O = P V ------------------------------------------------------------------
+      float acc[8][4];
+#pragma unroll
+      for (int nt = 0; nt < 8; ++nt) acc[nt][0] = acc[nt][1] = acc[nt][2] = acc[nt][3] = 0.f;
+#pragma unroll
+      for (int kk = 0; kk < MT; ++kk) {
+        if (kk * 16 >= Tk) break;
+        const uint32_t a[4] = {p[2 * kk][0], p[2 * kk][1], p[2 * kk + 1][0], p[2 * kk + 1][1]};
+#pragma unroll
+        for (int nc = 0; nc < 8; nc += 2) {
+          uint32_t b0, b1, b2, b3;
+          ldsm_x4_t(sV + tile_off(kk * 16 + (lane & 7) + ((lane >> 3) & 1) * 8, nc + (lane >> 4)), b0, b1, b2, b3);
+          mma_bf16_16816(acc[nc], a, b0, b1);
+          mma_bf16_16816(acc[nc + 1], a, b2, b3);
+        }
+      }
+      const float inv0 = 1.f / l0, inv1 = 1.f / l1;
+      // every lane of the warp has consumed this m-tile's Q rows (ldmatrix above is warp-wide):
+      // stage O over them.
+      __syncwarp();
+      const int r0 = mt * 16 + g, r1 = r0 + 8;
+#pragma unroll
+      for (int nt = 0; nt < 8; ++nt) {
+        *reinterpret_cast<uint32_t*>(pQ + tile_off(r0, nt) + qd * 4) = pack_bf16x2(acc[nt][0] * inv0, acc[nt][1] * inv0);
+        *reinterpret_cast<uint32_t*>(pQ + tile_off(r1, nt) + qd * 4) = pack_bf16x2(acc[nt][2] * inv1, acc[nt][3] * inv1);
+      }
+      if (lse != nullptr && qd == 0) {
+        // natural-log-sum-exp of the scaled logits
+        if (r0 < Tq) lse[(seq * Tq + r0) * heads + head] = m0 * scale + __logf(l0);
+        if (r1 < Tq) lse[(seq * Tq + r1) * heads + head] = m1 * scale + __logf(l1);
+      }
+    }
+    __syncwarp();
+    // ---- coalesced 128-bit stores of the O tile --------------------------------------
+    tvi_bf16* ob = o + seq * Tq * ldo + head * 64;
+#pragma unroll
+    for (int i = 0; i < kRows / 4; ++i) {
+      const int r = (lane >> 3) + 4 * i;
+      if (r < Tq) {
+        const uint4 val = *reinterpret_cast<const uint4*>(pQ + tile_off(r, lane & 7));
+        *reinterpret_cast<uint4*>(ob + r * ldo + (lane & 7) * 8) = val;
+      }
+    }
+    __syncwarp();  // the stage may be refilled by the next iteration's cp.async
+  }
+  cp_async_wait<0>();
+}
+
+template <int MT>
+int launch_temporal(const tvi_bf16* q, const tvi_bf16* k, const tvi_bf16* v, tvi_bf16* o, float* lse, int64_t nseq,
+                    int heads, int Tq, int Tk, int64_t ldq, int64_t ldk, int64_t ldv, int64_t ldo, float scale,
+                    cudaStream_t st) {
+  using Cfg = TemporalCfg<MT>;
+  static bool configured = false;
+  if (!configured) {
+    TVI_CUDA_OK(cudaFuncSetAttribute(attn_temporal_kernel<MT>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes));
+    configured = true;
+  }
+  const int64_t nitems = nseq * heads;
+  const int per_sm = (MT == 1) ? 2 : 1;
+  int64_t grid = (nitems + Cfg::kWarps - 1) / Cfg::kWarps;
+  const int64_t cap = (int64_t)num_sms() * per_sm;
+  if (grid > cap) grid = cap;
+  attn_temporal_kernel<MT><<<(unsigned)grid, Cfg::kWarps * 32, Cfg::kSmemBytes, st>>>(q, k, v, o, lse, nitems, heads, Tq, Tk,
+                                                                                     ldq, ldk, ldv, ldo, scale);
+  TVI_LAUNCH_OK("attn_temporal_kernel");
+  return TVI_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// few-key cross attention
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ void unpack8(const uint4& u, float* f) {
+  const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&u);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const float2 t = __bfloat1622float2(h[i]);
+    f[2 * i] = t.x;
+    f[2 * i + 1] = t.y;
+  }
+}
+
+constexpr int kFewRowsPerThread = 16;
+
+template <int LT, int LPH, bool STATS>
+__global__ void __launch_bounds__(512)
+attn_fewkeys_kernel(const tvi_bf16* __restrict__ q, const tvi_bf16* __restrict__ k, const tvi_bf16* __restrict__ v,
+                    tvi_bf16* __restrict__ o, int64_t rows_per_group, int tiles_per_group, int L, int64_t ldq,
+                    int64_t ldk, int64_t ldv, int64_t ldo, float scale, int Tq, const float* __restrict__ bias,
+                    double* __restrict__ stats_acc) {
+  const int cx = threadIdx.x;               // 16-byte channel chunk of the row
+  const int ry = threadIdx.y, RY = blockDim.y;
+  const int64_t group = blockIdx.x / tiles_per_group;
+  const int tile = blockIdx.x - (int)(group * tiles_per_group);
+  const int64_t rows_per_tile = (int64_t)RY * kFewRowsPerThread;
+  const int64_t rlo = group * rows_per_group + (int64_t)tile * rows_per_tile;
+  int64_t rhi = rlo + rows_per_tile;
+  const int64_t gend = (group + 1) * rows_per_group;
+  if (rhi > gend) rhi = gend;
+
+  extern __shared__ float s_stats[];  // [Tq * LT] when STATS
+  if (STATS) {
+    for (int i = threadIdx.y * blockDim.x + threadIdx.x; i < Tq * LT; i += blockDim.x * blockDim.y) s_stats[i] = 0.f;
+    __syncthreads();
+  }
+
+  // K / V chunks of this group stay in registers (packed bf16)
+  uint4 kr[LT], vr[LT];
+#pragma unroll
+  for (int l = 0; l < LT; ++l) {
+    if (l < L) {
+      kr[l] = __ldg(reinterpret_cast<const uint4*>(k + (group * L + l) * ldk + cx * 8));
+      vr[l] = __ldg(reinterpret_cast<const uint4*>(v + (group * L + l) * ldv + cx * 8));
+    } else {
+      kr[l] = make_uint4(0, 0, 0, 0);
+      vr[l] = make_uint4(0, 0, 0, 0);
+    }
+  }
+
+  if (LT == 1 && !STATS) {
+    // softmax over one key is exactly 1: O = V broadcast, Q is never read
+    for (int64_t r = rlo + ry; r < rhi; r += RY) *reinterpret_cast<uint4*>(o + r * ldo + cx * 8) = vr[0];
+    return;
+  }
+
+  // A warp can straddle two rows (blockDim.x = 40 at C = 320), so the trip count is made
+  // block-uniform and rows past the tile are predicated: every lane reaches every shuffle.
+#pragma unroll 2
+  for (int it = 0; it < kFewRowsPerThread; ++it) {
+    if (rlo + (int64_t)it * RY >= rhi) break;
+    const int64_t rr = rlo + (int64_t)it * RY + ry;
+    const bool act = rr < rhi;
+    const int64_t r = act ? rr : rlo;
+    float qf[8];
+    unpack8(__ldg(reinterpret_cast<const uint4*>(q + r * ldq + cx * 8)), qf);
+    float logit[LT];
+#pragma unroll
+    for (int l = 0; l < LT; ++l) {
+      float kf[8];
+      unpack8(kr[l], kf);
+      float d = 0.f;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) d = fmaf(qf[j], kf[j], d);
+#pragma unroll
+      for (int off = LPH / 2; off > 0; off >>= 1) d += __shfl_xor_sync(0xffffffffu, d, off);
+      logit[l] = d * scale;
+    }
+    const int t = (int)(r % Tq);
+    if (bias != nullptr) {
+#pragma unroll
+      for (int l = 0; l < LT; ++l)
+        if (l < L) logit[l] += __ldg(bias + t * L + l);
+    }
+    if (STATS) {
+      if (act && (cx & (LPH - 1)) == 0) {
+#pragma unroll
+        for (int l = 0; l < LT; ++l)
+          if (l < L) atomicAdd(&s_stats[t * LT + l], logit[l]);
+      }
+    }
+    float m = -INFINITY;
+#pragma unroll
+    for (int l = 0; l < LT; ++l) {
+      if (l >= L) logit[l] = -INFINITY;
+      m = fmaxf(m, logit[l]);
+    }
+    float sum = 0.f, pr[LT];
+#pragma unroll
+    for (int l = 0; l < LT; ++l) {
+      pr[l] = __expf(logit[l] - m);
+      sum += pr[l];
+    }
+    const float inv = 1.f / sum;
+    float of[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) of[j] = 0.f;
+#pragma unroll
+    for (int l = 0; l < LT; ++l) {
+      float vf[8];
+      unpack8(vr[l], vf);
+      const float w = pr[l] * inv;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) of[j] = fmaf(w, vf[j], of[j]);
+    }
+    uint4 outv;
+    outv.x = pack_bf16x2(of[0], of[1]);
+    outv.y = pack_bf16x2(of[2], of[3]);
+    outv.z = pack_bf16x2(of[4], of[5]);
+    outv.w = pack_bf16x2(of[6], of[7]);
+    if (act) *reinterpret_cast<uint4*>(o + r * ldo + cx * 8) = outv;
+  }
+
+  if (STATS) {
+    __syncthreads();
+    for (int i = threadIdx.y * blockDim.x + threadIdx.x; i < Tq * LT; i += blockDim.x * blockDim.y) {
+      const int t = i / LT, l = i - t * LT;
+      if (l < L) atomicAdd(&stats_acc[t * L + l], (double)s_stats[i]);
+    }
+  }
+}
+
+__global__ void fewkeys_stats_final_kernel(const double* __restrict__ acc, float* __restrict__ stats, int n, double inv_count) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) stats[i] = (float)(acc[i] * inv_count);
+}
+
+template <int LT, int LPH>
+int launch_fewkeys(const tvi_bf16* q, const tvi_bf16* k, const tvi_bf16* v, tvi_bf16* o, int64_t ngroups,
+                   int64_t rows_per_group, int C8, int L, int64_t ldq, int64_t ldk, int64_t ldv, int64_t ldo,
+                   float scale, int Tq, const float* bias, double* stats_acc, cudaStream_t st) {
+  // whole warps only: blockDim.x * blockDim.y must be a multiple of 32 (C8 is a multiple of 8)
+  const int unit = (C8 % 32 == 0) ? 1 : (C8 % 16 == 0) ? 2 : 4;
+  int RY = unit * (256 / (C8 * unit) > 0 ? 256 / (C8 * unit) : 1);
+  TVI_CHECK_ARG(C8 * RY <= 512, "tvi_attn_fewkeys_fwd: heads*d = %d is too wide for this kernel", C8 * 8);
+  const int64_t rows_per_tile = (int64_t)RY * kFewRowsPerThread;
+  const int64_t tiles = (rows_per_group + rows_per_tile - 1) / rows_per_tile;
+  TVI_CHECK_ARG(tiles * ngroups < ((int64_t)1 << 31), "tvi_attn_fewkeys_fwd: grid too large");
+  dim3 block((unsigned)C8, (unsigned)RY);
+  dim3 grid((unsigned)(tiles * ngroups));
+  if (stats_acc != nullptr) {
+    const size_t sm = (size_t)Tq * LT * sizeof(float);
+    TVI_CHECK_ARG(sm <= 48 * 1024, "tvi_attn_fewkeys_fwd: Tq*L too large for the statistics buffer");
+    attn_fewkeys_kernel<LT, LPH, true><<<grid, block, sm, st>>>(q, k, v, o, rows_per_group, (int)tiles, L, ldq, ldk, ldv, ldo,
+                                                                scale, Tq, bias, stats_acc);
+  } else {
+    attn_fewkeys_kernel<LT, LPH, false><<<grid, block, 0, st>>>(q, k, v, o, rows_per_group, (int)tiles, L, ldq, ldk, ldv, ldo,
+                                                                scale, Tq, bias, nullptr);
+  }
+  TVI_LAUNCH_OK("attn_fewkeys_kernel");
+  return TVI_OK;
+}
+
+}  // namespace
+}  // namespace tvi
+
+extern "C" {
+
+int tvi_attn_temporal_fwd(const tvi_bf16* q, const tvi_bf16* k, const tvi_bf16* v, tvi_bf16* o, float* lse, int64_t nseq,
+                          int heads, int Tq, int Tk, int d, int64_t ldq, int64_t ldk, int64_t ldv, int64_t ldo,
+                          float scale, void* stream) {
+  using namespace tvi;
+  TVI_CHECK_ARG(nseq >= 0 && heads >= 0, "tvi_attn_temporal_fwd: negative size");
+  if (nseq == 0 || heads == 0) return TVI_OK;
+  TVI_CHECK_ARG(q && k && v && o, "tvi_attn_temporal_fwd: null pointer");
+  if (d != 64) return fail(TVI_ERR_UNSUPPORTED, "tvi_attn_temporal_fwd: head dim %d (only 64 is built)", d);
+  TVI_CHECK_ARG(Tq >= 1 && Tq <= 64 && Tk >= 1 && Tk <= 64, "tvi_attn_temporal_fwd: Tq=%d Tk=%d outside [1,64]", Tq, Tk);
+  TVI_CHECK_ARG(ldq % 8 == 0 && ldk % 8 == 0 && ldv % 8 == 0 && ldo % 8 == 0, "tvi_attn_temporal_fwd: row strides must be multiples of 8 elements");
+  TVI_CHECK_ARG(ldq >= heads * 64 && ldk >= heads * 64 && ldv >= heads * 64 && ldo >= heads * 64, "tvi_attn_temporal_fwd: row stride smaller than heads*d");
+  TVI_CHECK_ARG(((uintptr_t)q | (uintptr_t)k | (uintptr_t)v | (uintptr_t)o) % 16 == 0, "tvi_attn_temporal_fwd: pointers must be 16-byte aligned");
+  cudaStream_t st = (cudaStream_t)stream;
+  const int T = Tq > Tk ? Tq : Tk;
+  if (T <= 16) return launch_temporal<1>(q, k, v, o, lse, nseq, heads, Tq, Tk, ldq, ldk, ldv, ldo, scale, st);
+  if (T <= 32) return launch_temporal<2>(q, k, v, o, lse, nseq, heads, Tq, Tk, ldq, ldk, ldv, ldo, scale, st);
+  return launch_temporal<4>(q, k, v, o, lse, nseq, heads, Tq, Tk, ldq, ldk, ldv, ldo, scale, st);
+}
+
+int tvi_attn_fewkeys_fwd(const tvi_bf16* q, const tvi_bf16* k, const tvi_bf16* v, tvi_bf16* o, int64_t nrows,
+                         int64_t rows_per_group, int heads, int L, int d, int64_t ldq, int64_t ldk, int64_t ldv,
+                         int64_t ldo, float scale, int Tq, const float* bias, float* stats, void* stats_ws, void* stream) {
+  using namespace tvi;
+  TVI_CHECK_ARG(nrows >= 0 && heads >= 0, "tvi_attn_fewkeys_fwd: negative size");
+  if (nrows == 0 || heads == 0) return TVI_OK;
+  TVI_CHECK_ARG(k && v && o, "tvi_attn_fewkeys_fwd: null pointer");
+  if (d != 64 && d != 128) return fail(TVI_ERR_UNSUPPORTED, "tvi_attn_fewkeys_fwd: head dim %d (64 and 128 are built)", d);
+  TVI_CHECK_ARG(L >= 1 && L <= 8, "tvi_attn_fewkeys_fwd: L=%d outside [1,8]", L);
+  TVI_CHECK_ARG(rows_per_group >= 1 && nrows % rows_per_group == 0, "tvi_attn_fewkeys_fwd: nrows must be a multiple of rows_per_group");
+  TVI_CHECK_ARG(q != nullptr || (L == 1 && stats == nullptr), "tvi_attn_fewkeys_fwd: q may only be null when L == 1 and no statistics are requested");
+  TVI_CHECK_ARG(Tq >= 1, "tvi_attn_fewkeys_fwd: Tq must be >= 1");
+  TVI_CHECK_ARG(stats == nullptr || stats_ws != nullptr, "tvi_attn_fewkeys_fwd: stats requires stats_ws");
+  const int C = heads * d;
+  TVI_CHECK_ARG(C / 8 <= 512, "tvi_attn_fewkeys_fwd: heads*d too large");
+  TVI_CHECK_ARG(ldk % 8 == 0 && ldv % 8 == 0 && ldo % 8 == 0 && (q == nullptr || ldq % 8 == 0), "tvi_attn_fewkeys_fwd: row strides must be multiples of 8 elements");
+  TVI_CHECK_ARG(((uintptr_t)q | (uintptr_t)k | (uintptr_t)v | (uintptr_t)o) % 16 == 0, "tvi_attn_fewkeys_fwd: pointers must be 16-byte aligned");
+  cudaStream_t st = (cudaStream_t)stream;
+  const int64_t ngroups = nrows / rows_per_group;
+  double* acc = nullptr;
+  if (stats != nullptr) {
+    acc = (double*)stats_ws;
+    TVI_CUDA_OK(cudaMemsetAsync(acc, 0, sizeof(double) * Tq * L, st));
+  }
+  int rc;
+#define TVI_FEW(LT)                                                                                              \
+  (d == 64 ? launch_fewkeys<LT, 8>(q, k, v, o, ngroups, rows_per_group, C / 8, L, ldq, ldk, ldv, ldo, scale, Tq, bias, acc, st) \
+           : launch_fewkeys<LT, 16>(q, k, v, o, ngroups, rows_per_group, C / 8, L, ldq, ldk, ldv, ldo, scale, Tq, bias, acc, st))
+  if (L == 1) rc = TVI_FEW(1);
+  else if (L == 2) rc = TVI_FEW(2);
+  else if (L <= 4) rc = TVI_FEW(4);
+  else rc = TVI_FEW(8);
+#undef TVI_FEW
+  if (rc != TVI_OK) return rc;
+  if (stats != nullptr) {
+    const int n = Tq * L;
+    const double count = (double)(nrows / Tq) * heads;
+    fewkeys_stats_final_kernel<<<(n + 127) / 128, 128, 0, st>>>(acc, stats, n, count > 0 ? 1.0 / count : 0.0);
+    TVI_LAUNCH_OK("fewkeys_stats_final_kernel");
+  }
+  return TVI_OK;
+}
+
+}  // extern "C"
