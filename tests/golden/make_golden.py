@@ -1,0 +1,180 @@
+"""Generates the committed golden vectors from the REFERENCE'S OWN CODE.  Runs only in the build
+container (needs /root/reference); the GPU box uses the .npz files.
+
+    python tests/golden/make_golden.py
+
+* flow_cosine.npz      — dataset_construction/step4_flow_check.py:cosine_similarity, imported as is.
+* attn_processor.npz   — src/models/attention_processor.py: the reference's `Attention` module driven
+  through `AttnProcessor` (eager) and `AttnProcessor2_0` (SDPA) in fp32 on CPU.  `diffusers` is not
+  installed, so the four leaf imports at :21-24 are satisfied by a shim (USE_PEFT_BACKEND=True ->
+  `linear_cls = nn.Linear`, reference :176-177; `maybe_allow_in_graph` = identity; logging/deprecate
+  stubs).  No reference arithmetic is replaced.
+* temporal_patched.npz — src/train_decouples.py:377-495 (the monkey-patched temporal forward) cannot be
+  imported (it is a closure inside `main`), so its source lines are extracted with `ast`/text slicing
+  from the reference file at generation time and exec'd against the reference's `Attention`.
+"""
+from __future__ import annotations
+
+import importlib.util
+import logging as pylogging
+import sys
+import textwrap
+import types
+from pathlib import Path
+
+import numpy as np
+import torch
+
+REF = Path("/root/reference")
+OUT = Path(__file__).resolve().parent
+
+
+def _shim_diffusers():
+    d = types.ModuleType("diffusers")
+    utils = types.ModuleType("diffusers.utils")
+    utils.USE_PEFT_BACKEND = True
+    utils.deprecate = lambda *a, **k: None
+    lg = types.SimpleNamespace(get_logger=lambda name: pylogging.getLogger(name))
+    utils.logging = lg
+    iu = types.ModuleType("diffusers.utils.import_utils")
+    iu.is_xformers_available = lambda: False
+    tu = types.ModuleType("diffusers.utils.torch_utils")
+    tu.maybe_allow_in_graph = lambda cls: cls
+    models = types.ModuleType("diffusers.models")
+    lora = types.ModuleType("diffusers.models.lora")
+
+    class LoRACompatibleLinear(torch.nn.Linear):
+        def forward(self, x, scale: float = 1.0):
+            return super().forward(x)
+
+    lora.LoRACompatibleLinear = LoRACompatibleLinear
+    lora.LoRALinearLayer = type("LoRALinearLayer", (torch.nn.Module,), {})
+    for name, mod in {"diffusers": d, "diffusers.utils": utils, "diffusers.utils.import_utils": iu,
+                      "diffusers.utils.torch_utils": tu, "diffusers.models": models, "diffusers.models.lora": lora}.items():
+        sys.modules[name] = mod
+
+
+def _load(path: Path, name: str):
+    spec = importlib.util.spec_from_file_location(name, path)
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    return mod
+
+
+def make_flow():
+    ref = _load(REF / "dataset_construction/step4_flow_check.py", "ref_step4")
+    rng = np.random.default_rng(0)
+    cases = {}
+    for i, (h, w) in enumerate([(4, 6), (33, 47), (120, 160), (135, 240)]):
+        a = rng.normal(0, 3, (h, w, 2)).astype(np.float32)
+        b = (0.7 * a + rng.normal(0, 2, (h, w, 2))).astype(np.float32)
+        if i == 1:  # zero vectors exercise the +1e-6 terms
+            a[::3, ::5] = 0
+            b[1::4, ::2] = 0
+        cases[f"a{i}"], cases[f"b{i}"] = a, b
+        cases[f"out{i}"] = np.asarray(ref.cosine_similarity(a, b), dtype=np.float32)
+    # identical and opposite fields: known answers ~ +1 / -1
+    a = rng.normal(0, 1, (16, 16, 2)).astype(np.float32)
+    cases["a4"], cases["b4"], cases["out4"] = a, a.copy(), np.asarray(ref.cosine_similarity(a, a), dtype=np.float32)
+    cases["a5"], cases["b5"], cases["out5"] = a, -a, np.asarray(ref.cosine_similarity(a, -a), dtype=np.float32)
+    np.savez_compressed(OUT / "flow_cosine.npz", **cases)
+    print("flow_cosine.npz", {k: float(v) for k, v in cases.items() if k.startswith("out")})
+
+
+def _attn_cases():
+    # (name, query_dim, cross_dim, heads, B', S, L)  — small SVD-shaped calls; d = 64 everywhere
+    return [
+        ("spatial_self", 128, None, 2, 2, 80, None),
+        ("temporal_self", 128, None, 2, 6, 14, None),
+        ("temporal_self_t25", 64, None, 1, 3, 25, None),
+        ("cross_l1", 128, 96, 2, 3, 14, 1),
+        ("cross_l2", 128, 96, 2, 3, 14, 2),
+        ("spatial_cross_l2", 128, 96, 2, 2, 40, 2),
+    ]
+
+
+def make_attention():
+    _shim_diffusers()
+    ap = _load(REF / "src/models/attention_processor.py", "ref_attention_processor")
+    out = {}
+    for name, qd, cd, heads, B, S, L in _attn_cases():
+        torch.manual_seed(hash(name) % 1000 + 1)
+        g = torch.Generator().manual_seed(len(name) * 7 + 3)
+        attn = ap.Attention(query_dim=qd, cross_attention_dim=cd, heads=heads, dim_head=64, processor=ap.AttnProcessor())
+        for p in attn.parameters():
+            p.data = torch.randn(p.shape, generator=g) * (p.shape[-1] ** -0.5)
+        x = torch.randn(B, S, qd, generator=g)
+        e = torch.randn(B, L, cd, generator=g) if L else None
+        with torch.no_grad():
+            y_eager = attn(x, encoder_hidden_states=e)
+            attn.set_processor(ap.AttnProcessor2_0())
+            y_sdpa = attn(x, encoder_hidden_states=e)
+        assert torch.allclose(y_eager, y_sdpa, atol=2e-5, rtol=1e-4), name
+        out[f"{name}.x"] = x.numpy()
+        if e is not None:
+            out[f"{name}.e"] = e.numpy()
+        out[f"{name}.wq"] = attn.to_q.weight.detach().numpy()
+        out[f"{name}.wk"] = attn.to_k.weight.detach().numpy()
+        out[f"{name}.wv"] = attn.to_v.weight.detach().numpy()
+        out[f"{name}.wo"] = attn.to_out[0].weight.detach().numpy()
+        out[f"{name}.bo"] = attn.to_out[0].bias.detach().numpy()
+        out[f"{name}.heads"] = np.int64(heads)
+        out[f"{name}.y"] = y_eager.numpy()
+        out[f"{name}.y_sdpa"] = y_sdpa.numpy()
+    np.savez_compressed(OUT / "attn_processor.npz", **out)
+    print("attn_processor.npz", sorted({k.split(".")[0] for k in out}))
+    return ap
+
+
+def make_temporal_patched(ap):
+    src = (REF / "src/train_decouples.py").read_text().splitlines()
+    # lines 377..495 (1-based) hold `def ca_temporal_forward(...)` up to `return forward`
+    start = next(i for i, l in enumerate(src) if "def ca_temporal_forward(self, controller, module_name)" in l)
+    end = next(i for i in range(start, len(src)) if src[i].strip() == "return forward")
+    code = textwrap.dedent("\n".join(src[start:end + 1]))
+    ns = {"torch": torch, "Optional": __import__("typing").Optional, "USE_PEFT_BACKEND": True}
+    exec(code, ns)  # defines ca_temporal_forward exactly as the reference wrote it
+    ca_temporal_forward = ns["ca_temporal_forward"]
+
+    class Controller:  # same recording interface as AttnController, src/train_decouples.py:518-545
+        def __init__(self, use_attentionmask):
+            self.use_attentionmask = use_attentionmask
+            self.temporal_cross_repeat = 0
+            self.start, self.end = {}, {}
+
+        def set_startframe_attention(self, f, v):
+            self.start[f] = v
+
+        def set_endframe_attention(self, f, v):
+            self.end[f] = v
+
+    out = {}
+    for name, use_mask, L in [("self", False, None), ("cross_l2", False, 2), ("cross_l2_mask", True, 2)]:
+        g = torch.Generator().manual_seed(11 + len(name))
+        attn = ap.Attention(query_dim=128, cross_attention_dim=96 if L else None, heads=2, dim_head=64)
+        for p in attn.parameters():
+            p.data = torch.randn(p.shape, generator=g) * (p.shape[-1] ** -0.5)
+        T = 14
+        x = torch.randn(5, T, 128, generator=g)
+        e = torch.randn(5, L, 96, generator=g) if L else None
+        ctl = Controller(use_mask)
+        fwd = ca_temporal_forward(attn, ctl, "temporal")
+        with torch.no_grad():
+            y = fwd(x, encoder_hidden_states=e)
+        out[f"{name}.x"] = x.numpy()
+        if e is not None:
+            out[f"{name}.e"] = e.numpy()
+            out[f"{name}.stats"] = np.array([[ctl.start[f], ctl.end[f]] for f in range(T)], dtype=np.float64)
+        for k, lin in (("wq", attn.to_q), ("wk", attn.to_k), ("wv", attn.to_v), ("wo", attn.to_out[0])):
+            out[f"{name}.{k}"] = lin.weight.detach().numpy()
+        out[f"{name}.bo"] = attn.to_out[0].bias.detach().numpy()
+        out[f"{name}.y"] = y.numpy()
+    np.savez_compressed(OUT / "temporal_patched.npz", **out)
+    print("temporal_patched.npz", sorted({k.split(".")[0] for k in out}))
+
+
+if __name__ == "__main__":
+    torch.set_num_threads(4)
+    make_flow()
+    ap = make_attention()
+    make_temporal_patched(ap)

@@ -1,0 +1,16 @@
+"""tvi — B200-native (sm_100a) kernels for the SVD keyframe-interpolation hot path.
+
+Public surface (mirrors the reference's interfaces for this path):
+  TviAttnProcessor, install, uninstall   diffusers AttentionProcessor plugin
+  slerp                                  first/last-frame latent slerp
+  cosine_similarity, backward_warp_check optical-flow checks
+Everything runs through libtvi.so (include/tvi.h); there is no CPU or torch fallback.
+"""
+from . import _lib, ops  # noqa: F401
+from ._lib import TviError, version  # noqa: F401
+from .flow import backward_warp_check, cosine_similarity, cosine_similarity_chw  # noqa: F401
+from .processor import TviAttnProcessor, install, uninstall  # noqa: F401
+from .slerp import slerp  # noqa: F401
+
+__all__ = ["TviAttnProcessor", "install", "uninstall", "slerp", "cosine_similarity", "cosine_similarity_chw",
+           "backward_warp_check", "TviError", "version", "ops"]

@@ -17,7 +17,7 @@
 //   so Q is never read.  Optional additive [Tq,L] bias and fused [Tq,L] mean-logit statistics
 //   replace the reference's 2*T .item() syncs (src/train_decouples.py:437-471).
 //   Algorithmic HBM bytes: 2 * rows * heads*d * 2 (Q read, O written); L == 1: rows*heads*d*2.
-#include "tvi_common.cuh"
+#include "mma_sync.cuh"
 
 namespace tvi {
 namespace {
@@ -25,28 +25,6 @@ namespace {
 // ---------------------------------------------------------------------------------------------
 // temporal (short-sequence) attention
 // ---------------------------------------------------------------------------------------------
-__device__ __forceinline__ void ldsm_x4(uint32_t addr, uint32_t& r0, uint32_t& r1, uint32_t& r2, uint32_t& r3) {
-  asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];"
-               : "=r"(r0), "=r"(r1), "=r"(r2), "=r"(r3)
-               : "r"(addr)
-               : "memory");
-}
-__device__ __forceinline__ void ldsm_x4_t(uint32_t addr, uint32_t& r0, uint32_t& r1, uint32_t& r2, uint32_t& r3) {
-  asm volatile("ldmatrix.sync.aligned.m8n8.x4.trans.shared.b16 {%0,%1,%2,%3}, [%4];"
-               : "=r"(r0), "=r"(r1), "=r"(r2), "=r"(r3)
-               : "r"(addr)
-               : "memory");
-}
-__device__ __forceinline__ void mma_bf16_16816(float* c, const uint32_t* a, uint32_t b0, uint32_t b1) {
-  asm volatile(
-      "mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
-      : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
-      : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
-}
-
-// byte offset of 16-byte chunk `c` (0..7) of row `r` inside a [rows][64] bf16 tile
-__device__ __forceinline__ uint32_t tile_off(int r, int c) { return (uint32_t)(r * 128 + ((c ^ (r & 7)) << 4)); }
-
 template <int MT>
 struct TemporalCfg {
   static constexpr int kRows = 16 * MT;

@@ -1,0 +1,239 @@
+// A3a — spatial self-attention core, O = softmax(scale . Q K^T) V over `batch` independent
+// sequences (frames) of S query rows / Skv key rows, every head, d = 64, no mask, non-causal.
+// Replaces F.scaled_dot_product_attention / xformers.ops.memory_efficient_attention on
+// [BF, h, S, 64] (src/models/attention_processor.py:1243, :1156; caller src/models/attention.py:276-281).
+//
+// Flash-style single pass with online fp32 softmax; the S x Skv score matrix never leaves the SM.
+// One CTA = 128 query rows of one (frame, head): 8 warps x 16 rows.  Q fragments live in
+// registers for the whole pass; K/V tiles of 64 keys stream through a 3-deep cp.async ring of
+// XOR-swizzled 128-byte rows (conflict-free ldmatrix); QK^T and PV run on mma.sync m16n8k16 with
+// P re-used straight from the accumulator registers; O is staged through shared memory so every
+// global store is a coalesced 128-bit write.  Heads are read in place from the packed
+// [tokens, heads*d] projection output (row stride ld*), so no head-split copy is ever made.
+// FLOPs: 4 * batch * heads * S * Skv * d.
+#include "mma_sync.cuh"
+
+namespace tvi {
+namespace {
+
+constexpr int kSpBr = 128;  // query rows per CTA
+constexpr int kSpBc = 64;   // keys per pipeline stage
+constexpr int kSpStages = 3;
+constexpr int kSpThreads = 256;
+constexpr int kSpQBytes = kSpBr * 128;
+constexpr int kSpKVBytes = kSpBc * 128;
+constexpr int kSpSmem = kSpQBytes + kSpStages * 2 * kSpKVBytes;  // 16 KB + 48 KB
+
+__device__ __forceinline__ void sp_load_kv(uint32_t dstK, uint32_t dstV, const tvi_bf16* kb, const tvi_bf16* vb, int j0,
+                                           int Skv, int64_t ldk, int64_t ldv, int tid) {
+#pragma unroll
+  for (int i = 0; i < (kSpBc * 8) / kSpThreads; ++i) {
+    const int idx = tid + i * kSpThreads;
+    const int r = idx >> 3, c = idx & 7;
+    const bool in = (j0 + r) < Skv;
+    const uint32_t off = tile_off(r, c);
+    const int64_t row = in ? (j0 + r) : 0;
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dstK + off), "l"(kb + row * ldk + c * 8),
+                 "r"(in ? 16 : 0)
+                 : "memory");
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dstV + off), "l"(vb + row * ldv + c * 8),
+                 "r"(in ? 16 : 0)
+                 : "memory");
+  }
+}
+
+__global__ void __launch_bounds__(kSpThreads, 2)
+attn_spatial_kernel(const tvi_bf16* __restrict__ q, const tvi_bf16* __restrict__ k, const tvi_bf16* __restrict__ v,
+                    tvi_bf16* __restrict__ o, float* __restrict__ lse, int heads, int S, int Skv, int64_t ldq, int64_t ldk,
+                    int64_t ldv, int64_t ldo, float scale) {
+  extern __shared__ __align__(128) uint8_t smem_raw[];
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int g = lane >> 2, qd = lane & 3;
+  const int bh = blockIdx.y;
+  const int b = bh / heads, h = bh - b * heads;
+  const int q0 = blockIdx.x * kSpBr;
+
+  const uint32_t sQ = smem_u32(smem_raw);
+  const uint32_t sKV = sQ + kSpQBytes;
+  const tvi_bf16* qb = q + ((int64_t)b * S) * ldq + h * 64;
+  const tvi_bf16* kb = k + ((int64_t)b * Skv) * ldk + h * 64;
+  const tvi_bf16* vb = v + ((int64_t)b * Skv) * ldv + h * 64;
+
+  // ---- prologue: Q tile + first K/V stages ----------------------------------------------
+#pragma unroll
+  for (int i = 0; i < (kSpBr * 8) / kSpThreads; ++i) {
+    const int idx = tid + i * kSpThreads;
+    const int r = idx >> 3, c = idx & 7;
+    const bool in = (q0 + r) < S;
+    const int64_t row = in ? (q0 + r) : 0;
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(sQ + tile_off(r, c)), "l"(qb + row * ldq + c * 8),
+                 "r"(in ? 16 : 0)
+                 : "memory");
+  }
+  const int nblk = (Skv + kSpBc - 1) / kSpBc;
+  sp_load_kv(sKV, sKV + kSpKVBytes, kb, vb, 0, Skv, ldk, ldv, tid);
+  cp_async_commit();  // group 0: Q + stage 0
+  if (nblk > 1) sp_load_kv(sKV + 2 * kSpKVBytes, sKV + 3 * kSpKVBytes, kb, vb, kSpBc, Skv, ldk, ldv, tid);
+  cp_async_commit();  // group 1: stage 1 (possibly empty)
+
+  cp_async_wait<1>();
+  __syncthreads();
+  uint32_t qf[4][4];
+#pragma unroll
+  for (int ks = 0; ks < 4; ++ks)
+    ldsm_x4(sQ + tile_off(warp * 16 + (lane & 7) + ((lane >> 3) & 1) * 8, 2 * ks + (lane >> 4)), qf[ks][0], qf[ks][1],
+            qf[ks][2], qf[ks][3]);
+
+  const float sl2 = scale * 1.4426950408889634f;
+  float m0 = -INFINITY, m1 = -INFINITY, l0 = 0.f, l1 = 0.f;
+  float acc[8][4];
+#pragma unroll
+  for (int nt = 0; nt < 8; ++nt) acc[nt][0] = acc[nt][1] = acc[nt][2] = acc[nt][3] = 0.f;
+
+  for (int j = 0; j < nblk; ++j) {
+    // stage j has landed for this thread (at most the newest group may be pending) ...
+    cp_async_wait<1>();
+    // ... and for everybody; also: everybody is done reading stage j-1, which is refilled next
+    __syncthreads();
+    if (j + 2 < nblk) {
+      const int st = (j + 2) % kSpStages;
+      sp_load_kv(sKV + st * 2 * kSpKVBytes, sKV + st * 2 * kSpKVBytes + kSpKVBytes, kb, vb, (j + 2) * kSpBc, Skv, ldk, ldv,
+                 tid);
+    }
+    cp_async_commit();
+    const uint32_t sK = sKV + (j % kSpStages) * 2 * kSpKVBytes;
+    const uint32_t sV = sK + kSpKVBytes;
+
+    // ---- S = Q K^T (16 x 64 per warp) ---------------------------------------------------
+    float s[8][4];
+#pragma unroll
+    for (int nt = 0; nt < 8; ++nt) s[nt][0] = s[nt][1] = s[nt][2] = s[nt][3] = 0.f;
+#pragma unroll
+    for (int ks = 0; ks < 4; ++ks) {
+#pragma unroll
+      for (int np = 0; np < 4; ++np) {
+        uint32_t b0, b1, b2, b3;
+        ldsm_x4(sK + tile_off(np * 16 + (lane & 7) + (lane >> 4) * 8, 2 * ks + ((lane >> 3) & 1)), b0, b1, b2, b3);
+        mma_bf16_16816(s[2 * np], qf[ks], b0, b1);
+        mma_bf16_16816(s[2 * np + 1], qf[ks], b2, b3);
+      }
+    }
+    if ((j + 1) * kSpBc > Skv) {  // ragged last block: mask keys past the sequence
+      const int j0 = j * kSpBc;
+#pragma unroll
+      for (int nt = 0; nt < 8; ++nt) {
+        const int col = j0 + nt * 8 + qd * 2;
+        if (col >= Skv) s[nt][0] = s[nt][2] = -INFINITY;
+        if (col + 1 >= Skv) s[nt][1] = s[nt][3] = -INFINITY;
+      }
+    }
+    // ---- online softmax ------------------------------------------------------------------
+    float bm0 = -INFINITY, bm1 = -INFINITY;
+#pragma unroll
+    for (int nt = 0; nt < 8; ++nt) {
+      bm0 = fmaxf(bm0, fmaxf(s[nt][0], s[nt][1]));
+      bm1 = fmaxf(bm1, fmaxf(s[nt][2], s[nt][3]));
+    }
+    bm0 = fmaxf(bm0, __shfl_xor_sync(0xffffffffu, bm0, 1));
+    bm0 = fmaxf(bm0, __shfl_xor_sync(0xffffffffu, bm0, 2));
+    bm1 = fmaxf(bm1, __shfl_xor_sync(0xffffffffu, bm1, 1));
+    bm1 = fmaxf(bm1, __shfl_xor_sync(0xffffffffu, bm1, 2));
+    const float mn0 = fmaxf(m0, bm0), mn1 = fmaxf(m1, bm1);  // finite: every block has >= 1 real key
+    const float a0 = fast_exp2((m0 - mn0) * sl2), a1 = fast_exp2((m1 - mn1) * sl2);
+    m0 = mn0;
+    m1 = mn1;
+    const float ms0 = mn0 * sl2, ms1 = mn1 * sl2;
+    float rs0 = 0.f, rs1 = 0.f;
+    uint32_t pfr[8][2];
+#pragma unroll
+    for (int nt = 0; nt < 8; ++nt) {
+      const float e0 = fast_exp2(fmaf(s[nt][0], sl2, -ms0)), e1 = fast_exp2(fmaf(s[nt][1], sl2, -ms0));
+      const float e2 = fast_exp2(fmaf(s[nt][2], sl2, -ms1)), e3 = fast_exp2(fmaf(s[nt][3], sl2, -ms1));
+      rs0 += e0 + e1;
+      rs1 += e2 + e3;
+      pfr[nt][0] = pack_bf16x2(e0, e1);
+      pfr[nt][1] = pack_bf16x2(e2, e3);
+    }
+    l0 = l0 * a0 + rs0;  // per-thread partial row sums; reduced across the quad at the end
+    l1 = l1 * a1 + rs1;
+#pragma unroll
+    for (int nt = 0; nt < 8; ++nt) {
+      acc[nt][0] *= a0;
+      acc[nt][1] *= a0;
+      acc[nt][2] *= a1;
+      acc[nt][3] *= a1;
+    }
+    // ---- O += P V ---------------------------------------------------------------------------
+#pragma unroll
+    for (int kk = 0; kk < 4; ++kk) {
+      const uint32_t a[4] = {pfr[2 * kk][0], pfr[2 * kk][1], pfr[2 * kk + 1][0], pfr[2 * kk + 1][1]};
+#pragma unroll
+      for (int nc = 0; nc < 8; nc += 2) {
+        uint32_t b0, b1, b2, b3;
+        ldsm_x4_t(sV + tile_off(kk * 16 + (lane & 7) + ((lane >> 3) & 1) * 8, nc + (lane >> 4)), b0, b1, b2, b3);
+        mma_bf16_16816(acc[nc], a, b0, b1);
+        mma_bf16_16816(acc[nc + 1], a, b2, b3);
+      }
+    }
+  }
+  cp_async_wait<0>();
+
+  l0 += __shfl_xor_sync(0xffffffffu, l0, 1);
+  l0 += __shfl_xor_sync(0xffffffffu, l0, 2);
+  l1 += __shfl_xor_sync(0xffffffffu, l1, 1);
+  l1 += __shfl_xor_sync(0xffffffffu, l1, 2);
+  const float inv0 = 1.f / l0, inv1 = 1.f / l1;
+
+  // Q tile is dead (fragments are in registers since before the loop): stage O over this warp's 16 rows.
+  uint8_t* pQ = smem_raw;
+  const int r0 = warp * 16 + g, r1 = r0 + 8;
+#pragma unroll
+  for (int nt = 0; nt < 8; ++nt) {
+    *reinterpret_cast<uint32_t*>(pQ + tile_off(r0, nt) + qd * 4) = pack_bf16x2(acc[nt][0] * inv0, acc[nt][1] * inv0);
+    *reinterpret_cast<uint32_t*>(pQ + tile_off(r1, nt) + qd * 4) = pack_bf16x2(acc[nt][2] * inv1, acc[nt][3] * inv1);
+  }
+  if (lse != nullptr && qd == 0) {
+    if (q0 + r0 < S) lse[((int64_t)b * S + q0 + r0) * heads + h] = m0 * scale + __logf(l0);
+    if (q0 + r1 < S) lse[((int64_t)b * S + q0 + r1) * heads + h] = m1 * scale + __logf(l1);
+  }
+  __syncwarp();
+  tvi_bf16* ob = o + ((int64_t)b * S) * ldo + h * 64;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int r = warp * 16 + (lane >> 3) + 4 * i;
+    if (q0 + r < S) {
+      const uint4 val = *reinterpret_cast<const uint4*>(pQ + tile_off(r, lane & 7));
+      *reinterpret_cast<uint4*>(ob + (int64_t)(q0 + r) * ldo + (lane & 7) * 8) = val;
+    }
+  }
+}
+
+}  // namespace
+}  // namespace tvi
+
+extern "C" int tvi_attn_spatial_fwd(const tvi_bf16* q, const tvi_bf16* k, const tvi_bf16* v, tvi_bf16* o, float* lse, int batch,
+                                    int heads, int S, int Skv, int d, int64_t ldq, int64_t ldk, int64_t ldv, int64_t ldo,
+                                    float scale, void* stream) {
+  using namespace tvi;
+  TVI_CHECK_ARG(batch >= 0 && heads >= 0 && S >= 0 && Skv >= 0, "tvi_attn_spatial_fwd: negative size");
+  if (batch == 0 || heads == 0 || S == 0) return TVI_OK;
+  TVI_CHECK_ARG(Skv >= 1, "tvi_attn_spatial_fwd: softmax over zero keys is undefined");
+  TVI_CHECK_ARG(q && k && v && o, "tvi_attn_spatial_fwd: null pointer");
+  if (d != 64) return fail(TVI_ERR_UNSUPPORTED, "tvi_attn_spatial_fwd: head dim %d (only 64 is built)", d);
+  TVI_CHECK_ARG(ldq % 8 == 0 && ldk % 8 == 0 && ldv % 8 == 0 && ldo % 8 == 0, "tvi_attn_spatial_fwd: row strides must be multiples of 8 elements");
+  TVI_CHECK_ARG(ldq >= heads * 64 && ldk >= heads * 64 && ldv >= heads * 64 && ldo >= heads * 64, "tvi_attn_spatial_fwd: row stride smaller than heads*d");
+  TVI_CHECK_ARG(((uintptr_t)q | (uintptr_t)k | (uintptr_t)v | (uintptr_t)o) % 16 == 0, "tvi_attn_spatial_fwd: pointers must be 16-byte aligned");
+  TVI_CHECK_ARG((int64_t)batch * heads <= 65535, "tvi_attn_spatial_fwd: batch*heads exceeds 65535");
+  static bool configured[64] = {false};
+  int dev = 0;
+  TVI_CUDA_OK(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= 64 || !configured[dev]) {
+    TVI_CUDA_OK(cudaFuncSetAttribute(attn_spatial_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSpSmem));
+    if (dev >= 0 && dev < 64) configured[dev] = true;
+  }
+  dim3 grid((unsigned)((S + kSpBr - 1) / kSpBr), (unsigned)(batch * heads));
+  attn_spatial_kernel<<<grid, kSpThreads, kSpSmem, (cudaStream_t)stream>>>(q, k, v, o, lse, heads, S, Skv, ldq, ldk, ldv, ldo,
+                                                                         scale);
+  TVI_LAUNCH_OK("attn_spatial_kernel");
+  return TVI_OK;
+}

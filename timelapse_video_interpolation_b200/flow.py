@@ -1,0 +1,50 @@
+"""Optical-flow checks: drop-in `cosine_similarity` and the backward-warp consistency check.
+
+`cosine_similarity(flow_a, flow_b)` has the name, arity and return type of the reference function
+(dataset_construction/step4_flow_check.py:25-34): two (H, W, 2) float32 numpy arrays in OpenCV's HWC
+layout -> np.float32 scalar.  CUDA tensors (optionally batched) are accepted too and then a CUDA
+tensor is returned without a host sync.
+
+`backward_warp_check` is the north-star extension (the reference file has no warp);
+its spec is F.grid_sample(bilinear, zeros, align_corners=True) + the usual forward/backward
+consistency inequality, see oracle/flow_ref.py.
+"""
+from __future__ import annotations
+
+import numpy as np
+import torch
+
+from . import ops
+
+OCC_ALPHA = 0.01
+OCC_BETA = 0.5
+
+
+def cosine_similarity(flow_a, flow_b):
+    if isinstance(flow_a, np.ndarray):
+        a = torch.from_numpy(np.ascontiguousarray(flow_a, dtype=np.float32))
+        b = torch.from_numpy(np.ascontiguousarray(flow_b, dtype=np.float32))
+        if a.shape != b.shape or a.numel() % 2 != 0:
+            raise ValueError("flow fields must have the same shape and 2 components per pixel")
+        # the reference reshapes to (-1, 2): any shape whose flattening is pixel-major works
+        a = a.reshape(1, 1, -1, 2).cuda(non_blocking=True)
+        b = b.reshape(1, 1, -1, 2).cuda(non_blocking=True)
+        return np.float32(ops.flow_cosine_f32(a, b, hwc=True).cpu().numpy()[0])
+    a, b = flow_a, flow_b
+    single = a.dim() == 3
+    if single:
+        a, b = a.unsqueeze(0), b.unsqueeze(0)
+    out = ops.flow_cosine_f32(a, b, hwc=True)
+    return out[0] if single else out
+
+
+def cosine_similarity_chw(flow_a: torch.Tensor, flow_b: torch.Tensor) -> torch.Tensor:
+    """Same reduction for planar [B, 2, H, W] flows (the layout the warp kernel uses)."""
+    return ops.flow_cosine_f32(flow_a, flow_b, hwc=False)
+
+
+def backward_warp_check(img2: torch.Tensor, f_fwd: torch.Tensor, f_bwd: torch.Tensor, alpha: float = OCC_ALPHA,
+                        beta: float = OCC_BETA):
+    """Returns (warped [B,C,H,W] fp32, occluded [B,H,W] bool, valid [B,H,W] bool)."""
+    warped, mask = ops.backward_warp_f32(img2, f_fwd, f_bwd, alpha, beta)
+    return warped, (mask & 1).bool(), (mask & 2).bool()

@@ -1,0 +1,55 @@
+"""`Attention` — a diffusers-free parameter container with the reference module's interface.
+
+diffusers is not installed on the build or GPU boxes, so tests and benchmarks need an
+object the processor can be installed on.  This mirrors the SVD-relevant subset of
+`Attention.__init__` / `set_processor` / `forward` (reference src/models/attention_processor.py:88-207,
+:371-404, :496-528): same attribute names, same parameter shapes and state_dict keys
+(`to_q.weight`, `to_k.weight`, `to_v.weight`, `to_out.0.weight`, `to_out.0.bias`), same dispatch to
+`self.processor`.  It holds no attention arithmetic of its own.
+"""
+from __future__ import annotations
+
+from typing import Optional
+
+import torch
+from torch import nn
+
+
+class Attention(nn.Module):
+    def __init__(self, query_dim: int, cross_attention_dim: Optional[int] = None, heads: int = 8, dim_head: int = 64,
+                 dropout: float = 0.0, bias: bool = False, out_bias: bool = True, processor=None):
+        super().__init__()
+        self.inner_dim = dim_head * heads
+        self.cross_attention_dim = cross_attention_dim if cross_attention_dim is not None else query_dim
+        self.upcast_attention = False
+        self.upcast_softmax = False
+        self.rescale_output_factor = 1.0
+        self.residual_connection = False
+        self.dropout = dropout
+        self.scale = dim_head ** -0.5            # reference :127
+        self.heads = heads                       # reference :129
+        self.sliceable_head_dim = heads
+        self.added_kv_proj_dim = None
+        self.only_cross_attention = False
+        self.group_norm = None
+        self.spatial_norm = None
+        self.norm_cross = None
+        self.to_q = nn.Linear(query_dim, self.inner_dim, bias=bias)                    # :181
+        self.to_k = nn.Linear(self.cross_attention_dim, self.inner_dim, bias=bias)     # :185
+        self.to_v = nn.Linear(self.cross_attention_dim, self.inner_dim, bias=bias)     # :186
+        self.to_out = nn.ModuleList([nn.Linear(self.inner_dim, query_dim, bias=out_bias), nn.Dropout(dropout)])  # :195-197
+        if processor is None:
+            from .processor import TviAttnProcessor
+            processor = TviAttnProcessor()
+        self.set_processor(processor)
+
+    def set_processor(self, processor, _remove_lora: bool = False) -> None:
+        # reference :371-404: a processor that is not an nn.Module is simply assigned
+        if hasattr(self, "processor") and isinstance(self.processor, nn.Module) and not isinstance(processor, nn.Module):
+            self._modules.pop("processor")
+        self.processor = processor
+
+    def forward(self, hidden_states, encoder_hidden_states=None, attention_mask=None, **cross_attention_kwargs):
+        # reference :522-528
+        return self.processor(self, hidden_states, encoder_hidden_states=encoder_hidden_states,
+                              attention_mask=attention_mask, **cross_attention_kwargs)

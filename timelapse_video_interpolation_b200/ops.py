@@ -1,0 +1,189 @@
+"""Thin tensor-level wrappers over the C ABI: pointer/stride marshalling only, no arithmetic.
+
+Every function takes CUDA tensors, launches on `torch.cuda.current_stream()`, never synchronises
+the host and never falls back to torch math.  `LAUNCHES` counts libtvi kernel launches (bench.py
+reports it as `gpu_launches`).
+"""
+from __future__ import annotations
+
+import torch
+
+from . import _lib
+
+LAUNCHES = 0  # kernels launched through libtvi since import (per process)
+
+
+def _stream() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _need_cuda(*ts):
+    for t in ts:
+        if t is not None and not t.is_cuda:
+            raise _lib.TviError(_lib.TVI_ERR_INVALID, "libtvi operates on CUDA tensors only (there is no CPU fallback)")
+
+
+def _rows2d(t: torch.Tensor, what: str):
+    """Returns (tensor, ld) for a tensor whose last dim is contiguous and whose leading dims
+    collapse to one row stride (e.g. a column slice of a packed QKV buffer)."""
+    if t.dtype != torch.bfloat16:
+        raise _lib.TviError(_lib.TVI_ERR_INVALID, f"{what}: expected bfloat16, got {t.dtype}")
+    if t.dim() < 2 or t.stride(-1) != 1:
+        raise _lib.TviError(_lib.TVI_ERR_INVALID, f"{what}: last dimension must be contiguous")
+    ld = t.stride(-2)
+    exp = ld
+    for i in range(t.dim() - 2, 0, -1):
+        exp *= t.shape[i]
+        if t.shape[i - 1] != 1 and t.stride(i - 1) != exp:
+            raise _lib.TviError(_lib.TVI_ERR_INVALID, f"{what}: leading dimensions do not collapse to one row stride")
+    return t, ld
+
+
+def gemm_bf16_tn(x: torch.Tensor, w: torch.Tensor, bias: torch.Tensor | None = None,
+                 out: torch.Tensor | None = None) -> torch.Tensor:
+    """y[..., N] = x[..., K] @ w[N, K]^T (+ bias) — tcgen05 GEMM (replaces nn.Linear on the path)."""
+    global LAUNCHES
+    _need_cuda(x, w, bias)
+    x, ldx = _rows2d(x, "x")
+    w, ldw = _rows2d(w, "w")
+    K = x.shape[-1]
+    N = w.shape[0]
+    if w.shape[1] != K:
+        raise _lib.TviError(_lib.TVI_ERR_INVALID, f"gemm: x has K={K}, w has K={w.shape[1]}")
+    M = x.numel() // K if K else 0
+    if out is None:
+        out = torch.empty(*x.shape[:-1], N, dtype=torch.bfloat16, device=x.device)
+    out, ldy = _rows2d(out, "out")
+    if bias is not None and (bias.dtype != torch.bfloat16 or not bias.is_contiguous() or bias.numel() != N):
+        raise _lib.TviError(_lib.TVI_ERR_INVALID, "gemm: bias must be a contiguous bf16 vector of length N")
+    _lib.check(_lib.load().tvi_gemm_bf16_tn(x.data_ptr(), w.data_ptr(), bias.data_ptr() if bias is not None else None,
+                                            out.data_ptr(), M, N, K, ldx, ldw, ldy, _stream()))
+    LAUNCHES += 1
+    return out
+
+
+def attn_temporal(q, k, v, nseq: int, heads: int, Tq: int, Tk: int, scale: float, out=None, lse=None):
+    """Short-sequence attention core; q/k/v are [nseq*T, heads*64] row views (may be strided)."""
+    global LAUNCHES
+    _need_cuda(q, k, v)
+    q, ldq = _rows2d(q, "q")
+    k, ldk = _rows2d(k, "k")
+    v, ldv = _rows2d(v, "v")
+    d = q.shape[-1] // heads
+    if out is None:
+        out = torch.empty(nseq * Tq, heads * d, dtype=torch.bfloat16, device=q.device)
+    out, ldo = _rows2d(out, "out")
+    _lib.check(_lib.load().tvi_attn_temporal_fwd(q.data_ptr(), k.data_ptr(), v.data_ptr(), out.data_ptr(),
+                                                 lse.data_ptr() if lse is not None else None, nseq, heads, Tq, Tk, d,
+                                                 ldq, ldk, ldv, ldo, float(scale), _stream()))
+    LAUNCHES += 1
+    return out
+
+
+def attn_fewkeys(q, k, v, nrows: int, rows_per_group: int, heads: int, L: int, scale: float, out=None,
+                 Tq: int = 1, bias=None, stats=None):
+    """Few-key cross-attention core; k/v are [ngroups*L, heads*d]; q may be None when L == 1."""
+    global LAUNCHES
+    _need_cuda(q, k, v, bias, stats)
+    k, ldk = _rows2d(k, "k")
+    v, ldv = _rows2d(v, "v")
+    C_ = k.shape[-1]
+    d = C_ // heads
+    ldq = 0
+    if q is not None:
+        q, ldq = _rows2d(q, "q")
+    if out is None:
+        out = torch.empty(nrows, C_, dtype=torch.bfloat16, device=k.device)
+    out, ldo = _rows2d(out, "out")
+    ws = None
+    if stats is not None:
+        if stats.dtype != torch.float32 or not stats.is_contiguous() or stats.numel() != Tq * L:
+            raise _lib.TviError(_lib.TVI_ERR_INVALID, "stats must be a contiguous fp32 [Tq, L] tensor")
+        ws = torch.empty(Tq * L, dtype=torch.float64, device=k.device)
+    if bias is not None and (bias.dtype != torch.float32 or not bias.is_contiguous() or bias.numel() != Tq * L):
+        raise _lib.TviError(_lib.TVI_ERR_INVALID, "bias must be a contiguous fp32 [Tq, L] tensor")
+    _lib.check(_lib.load().tvi_attn_fewkeys_fwd(q.data_ptr() if q is not None else None, k.data_ptr(), v.data_ptr(),
+                                                out.data_ptr(), nrows, rows_per_group, heads, L, d, ldq, ldk, ldv, ldo,
+                                                float(scale), Tq, bias.data_ptr() if bias is not None else None,
+                                                stats.data_ptr() if stats is not None else None,
+                                                ws.data_ptr() if ws is not None else None, _stream()))
+    LAUNCHES += 1 if stats is None else 2
+    return out
+
+
+def attn_spatial(q, k, v, batch: int, heads: int, S: int, Skv: int, scale: float, out=None, lse=None):
+    """Flash-style spatial attention core; q is [batch*S, heads*64], k/v [batch*Skv, heads*64]."""
+    global LAUNCHES
+    _need_cuda(q, k, v)
+    q, ldq = _rows2d(q, "q")
+    k, ldk = _rows2d(k, "k")
+    v, ldv = _rows2d(v, "v")
+    d = q.shape[-1] // heads
+    if out is None:
+        out = torch.empty(batch * S, heads * d, dtype=torch.bfloat16, device=q.device)
+    out, ldo = _rows2d(out, "out")
+    _lib.check(_lib.load().tvi_attn_spatial_fwd(q.data_ptr(), k.data_ptr(), v.data_ptr(), out.data_ptr(),
+                                                lse.data_ptr() if lse is not None else None, batch, heads, S, Skv, d,
+                                                ldq, ldk, ldv, ldo, float(scale), _stream()))
+    LAUNCHES += 1
+    return out
+
+
+def slerp_f32(v0: torch.Tensor, v1: torch.Tensor, T: int, dot_threshold: float, out=None) -> torch.Tensor:
+    global LAUNCHES
+    _need_cuda(v0, v1)
+    if v0.dtype != torch.float32 or v1.dtype != torch.float32 or v0.shape != v1.shape:
+        raise _lib.TviError(_lib.TVI_ERR_INVALID, "slerp: v0 and v1 must be fp32 tensors of the same shape")
+    v0 = v0.contiguous()
+    v1 = v1.contiguous()
+    nclips = v0.shape[0] if v0.dim() > 0 else 1
+    n = v0.numel() // nclips if nclips else 0
+    if out is None:
+        out = torch.empty((nclips, T) + tuple(v0.shape[1:]), dtype=torch.float32, device=v0.device)
+    _lib.check(_lib.load().tvi_slerp_f32(v0.data_ptr(), v1.data_ptr(), out.data_ptr(), nclips, n, T,
+                                         float(dot_threshold), _stream()))
+    LAUNCHES += 1
+    return out
+
+
+def flow_cosine_f32(fa: torch.Tensor, fb: torch.Tensor, hwc: bool, out=None) -> torch.Tensor:
+    """fa, fb: [npairs, H, W, 2] (hwc) or [npairs, 2, H, W] fp32 -> [npairs] fp32."""
+    global LAUNCHES
+    _need_cuda(fa, fb)
+    if fa.dtype != torch.float32 or fb.dtype != torch.float32 or fa.shape != fb.shape or fa.dim() != 4:
+        raise _lib.TviError(_lib.TVI_ERR_INVALID, "flow_cosine: expected two fp32 4-D tensors of the same shape")
+    fa = fa.contiguous()
+    fb = fb.contiguous()
+    npairs = fa.shape[0]
+    H, W = (fa.shape[1], fa.shape[2]) if hwc else (fa.shape[2], fa.shape[3])
+    if (fa.shape[3] if hwc else fa.shape[1]) != 2:
+        raise _lib.TviError(_lib.TVI_ERR_INVALID, "flow_cosine: a flow field has exactly 2 components")
+    lib = _lib.load()
+    ws = torch.empty(max(1, lib.tvi_flow_cosine_workspace_bytes(npairs, H, W) // 8), dtype=torch.float64, device=fa.device)
+    if out is None:
+        out = torch.empty(npairs, dtype=torch.float32, device=fa.device)
+    _lib.check(lib.tvi_flow_cosine_f32(fa.data_ptr(), fb.data_ptr(), out.data_ptr(), ws.data_ptr(), npairs, H, W,
+                                       1 if hwc else 0, _stream()))
+    LAUNCHES += 2
+    return out
+
+
+def backward_warp_f32(img2, f_fwd, f_bwd, alpha: float, beta: float, warped=None, mask=None):
+    """img2 [B,C,H,W], f_fwd/f_bwd [B,2,H,W] fp32 -> (warped [B,C,H,W] fp32, mask [B,H,W] u8)."""
+    global LAUNCHES
+    _need_cuda(img2, f_fwd, f_bwd)
+    for t in (img2, f_fwd, f_bwd):
+        if t.dtype != torch.float32 or t.dim() != 4:
+            raise _lib.TviError(_lib.TVI_ERR_INVALID, "backward_warp: expected fp32 [B,C,H,W] tensors")
+    B, Cc, H, W = img2.shape
+    if tuple(f_fwd.shape) != (B, 2, H, W) or tuple(f_bwd.shape) != (B, 2, H, W):
+        raise _lib.TviError(_lib.TVI_ERR_INVALID, "backward_warp: flows must be [B,2,H,W] matching img2")
+    img2, f_fwd, f_bwd = img2.contiguous(), f_fwd.contiguous(), f_bwd.contiguous()
+    if warped is None:
+        warped = torch.empty_like(img2)
+    if mask is None:
+        mask = torch.empty(B, H, W, dtype=torch.uint8, device=img2.device)
+    _lib.check(_lib.load().tvi_backward_warp_f32(img2.data_ptr(), f_fwd.data_ptr(), f_bwd.data_ptr(), warped.data_ptr(),
+                                                 mask.data_ptr(), B, Cc, H, W, float(alpha), float(beta), _stream()))
+    LAUNCHES += 1
+    return warped, mask
