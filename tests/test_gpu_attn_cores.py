@@ -1,0 +1,132 @@
+"""GPU: the three attention cores (through the C ABI) vs the oracle's explicit fp32 softmax(QK^T)V."""
+import math
+
+import pytest
+import torch
+
+from oracle.attention_ref import batch_to_head_dim, get_attention_scores, head_to_batch_dim
+from timelapse_video_interpolation_b200 import ops
+
+pytestmark = pytest.mark.gpu
+TOL = 2e-2  # bf16 attention bar from BASELINE.json (max-abs); typical error is ~4e-3, printed below
+
+
+def _core_ref(q, k, v, heads, scale, bias=None):
+    """q [B,Sq,h*d], k/v [B,Sk,h*d] fp32 CPU -> (out [B,Sq,h*d], logits [B*h,Sq,Sk])."""
+    p, logits = get_attention_scores(head_to_batch_dim(q, heads), head_to_batch_dim(k, heads), scale, bias)
+    return batch_to_head_dim(torch.bmm(p, head_to_batch_dim(v, heads)), heads), logits
+
+
+def _rand(shape, g, cuda, mul=1.0):
+    t = (torch.randn(*shape, generator=g) * mul).to(torch.bfloat16)
+    return t.to(cuda), t.float()
+
+
+@pytest.mark.parametrize("nseq,heads,Tq,Tk", [
+    (64, 5, 14, 14), (37, 5, 25, 25), (300, 1, 1, 1), (19, 2, 16, 16), (11, 3, 17, 17),
+    (9, 2, 40, 40), (5, 2, 64, 64), (7, 2, 14, 3), (2000, 10, 14, 14),
+])
+def test_temporal_core(cuda, nseq, heads, Tq, Tk):
+    g = torch.Generator().manual_seed(nseq * 100 + Tq)
+    C = heads * 64
+    q, qf = _rand((nseq, Tq, C), g, cuda)
+    k, kf = _rand((nseq, Tk, C), g, cuda)
+    v, vf = _rand((nseq, Tk, C), g, cuda)
+    scale = 0.125
+    lse = torch.empty(nseq * Tq, heads, dtype=torch.float32, device=cuda)
+    o = ops.attn_temporal(q.view(-1, C), k.view(-1, C), v.view(-1, C), nseq, heads, Tq, Tk, scale, lse=lse)
+    torch.cuda.synchronize()
+    ref, logits = _core_ref(qf, kf, vf, heads, scale)
+    err = (o.float().cpu().view(nseq, Tq, C) - ref).abs().max().item()
+    print(f"temporal core nseq={nseq} T={Tq}x{Tk}: max abs err {err:.3e}")
+    assert err < TOL
+    ref_lse = torch.logsumexp(logits, dim=-1).view(nseq, heads, Tq).permute(0, 2, 1).reshape(nseq * Tq, heads)
+    assert (lse.cpu() - ref_lse).abs().max().item() < 1e-3
+
+
+def test_temporal_core_reads_packed_qkv_in_place(cuda):
+    g = torch.Generator().manual_seed(3)
+    nseq, heads, T = 50, 5, 14
+    C = heads * 64
+    qkv, qkvf = _rand((nseq * T, 3 * C), g, cuda)
+    o = ops.attn_temporal(qkv[:, :C], qkv[:, C:2 * C], qkv[:, 2 * C:], nseq, heads, T, T, 0.125)
+    torch.cuda.synchronize()
+    f = qkvf.view(nseq, T, 3 * C)
+    ref, _ = _core_ref(f[..., :C], f[..., C:2 * C], f[..., 2 * C:], heads, 0.125)
+    assert (o.float().cpu().view(nseq, T, C) - ref).abs().max().item() < TOL
+
+
+@pytest.mark.parametrize("B,heads,S,Skv", [
+    (2, 2, 80, 80), (1, 5, 144, 144), (3, 1, 576, 576), (1, 2, 100, 100), (2, 2, 65, 130),
+    (1, 1, 2304, 2304), (1, 2, 129, 63), (2, 5, 1000, 1000),
+])
+def test_spatial_core(cuda, B, heads, S, Skv):
+    g = torch.Generator().manual_seed(S + Skv)
+    C = heads * 64
+    q, qf = _rand((B, S, C), g, cuda)
+    k, kf = _rand((B, Skv, C), g, cuda)
+    v, vf = _rand((B, Skv, C), g, cuda)
+    lse = torch.empty(B * S, heads, dtype=torch.float32, device=cuda)
+    o = ops.attn_spatial(q.view(-1, C), k.view(-1, C), v.view(-1, C), B, heads, S, Skv, 0.125, lse=lse)
+    torch.cuda.synchronize()
+    ref, logits = _core_ref(qf, kf, vf, heads, 0.125)
+    err = (o.float().cpu().view(B, S, C) - ref).abs().max().item()
+    print(f"spatial core B={B} h={heads} S={S}x{Skv}: max abs err {err:.3e}")
+    assert err < TOL
+    ref_lse = torch.logsumexp(logits, dim=-1).view(B, heads, S).permute(0, 2, 1).reshape(B * S, heads)
+    assert (lse.cpu() - ref_lse).abs().max().item() < 1e-3
+
+
+def test_spatial_core_large_logits_stay_finite(cuda):
+    # online-softmax rescaling: a late key block dominates an early one by a huge margin
+    g = torch.Generator().manual_seed(9)
+    B, heads, S = 1, 1, 256
+    q, qf = _rand((B, S, 64), g, cuda, 6.0)
+    k, kf = _rand((B, S, 64), g, cuda, 6.0)
+    v, vf = _rand((B, S, 64), g, cuda)
+    o = ops.attn_spatial(q.view(-1, 64), k.view(-1, 64), v.view(-1, 64), B, heads, S, S, 0.125)
+    torch.cuda.synchronize()
+    ref, _ = _core_ref(qf, kf, vf, heads, 0.125)
+    assert torch.isfinite(o).all() and (o.float().cpu().view(B, S, 64) - ref).abs().max().item() < 3e-2
+
+
+@pytest.mark.parametrize("groups,S,heads,L,d", [
+    (3, 14, 2, 1, 64), (3, 14, 5, 2, 64), (2, 40, 5, 2, 64), (4, 9, 2, 3, 64), (2, 33, 1, 8, 64),
+    (3, 14, 2, 2, 128), (2, 1000, 10, 2, 64), (5, 14, 20, 2, 64),
+])
+def test_fewkeys_core(cuda, groups, S, heads, L, d):
+    g = torch.Generator().manual_seed(groups * 10 + L)
+    C = heads * d
+    q, qf = _rand((groups, S, C), g, cuda)
+    k, kf = _rand((groups, L, C), g, cuda)
+    v, vf = _rand((groups, L, C), g, cuda)
+    scale = d ** -0.5
+    o = ops.attn_fewkeys(q.view(-1, C), k.view(-1, C), v.view(-1, C), groups * S, S, heads, L, scale)
+    torch.cuda.synchronize()
+    p, _ = get_attention_scores(head_to_batch_dim(qf, heads), head_to_batch_dim(kf, heads), scale)
+    ref = batch_to_head_dim(torch.bmm(p, head_to_batch_dim(vf, heads)), heads)
+    assert (o.float().cpu().view(groups, S, C) - ref).abs().max().item() < TOL
+    if L == 1:  # exact broadcast, and Q may be omitted
+        o2 = ops.attn_fewkeys(None, k.view(-1, C), v.view(-1, C), groups * S, S, heads, 1, scale)
+        torch.cuda.synchronize()
+        assert torch.equal(o2.view(groups, S, C), v.expand(groups, S, C))
+
+
+def test_fewkeys_ramp_bias_and_statistics(cuda):
+    # src/train_decouples.py:437-471: (T,2) linspace bias and per-frame mean logits
+    g = torch.Generator().manual_seed(4)
+    groups, T, heads, L = 37, 14, 5, 2
+    C = heads * 64
+    q, qf = _rand((groups, T, C), g, cuda)
+    k, kf = _rand((groups, L, C), g, cuda)
+    v, vf = _rand((groups, L, C), g, cuda)
+    w = torch.linspace(0, 1, T)
+    bias = torch.stack([1 - w, w], dim=1).contiguous()
+    stats = torch.empty(T, L, dtype=torch.float32, device=cuda)
+    o = ops.attn_fewkeys(q.view(-1, C), k.view(-1, C), v.view(-1, C), groups * T, T, heads, L, 0.125, Tq=T,
+                         bias=bias.to(cuda), stats=stats)
+    torch.cuda.synchronize()
+    p, logits = get_attention_scores(head_to_batch_dim(qf, heads), head_to_batch_dim(kf, heads), 0.125, bias[None])
+    ref = batch_to_head_dim(torch.bmm(p, head_to_batch_dim(vf, heads)), heads)
+    assert (o.float().cpu().view(groups, T, C) - ref).abs().max().item() < TOL
+    assert (stats.cpu() - logits.mean(dim=0)).abs().max().item() < 1e-4

@@ -1,0 +1,142 @@
+"""GPU: the AttentionProcessor plugin end to end (processor -> C ABI -> kernels) against
+(1) golden outputs of the reference's own Attention/AttnProcessor code and (2) the fp32 oracle."""
+import numpy as np
+import pytest
+import torch
+
+import timelapse_video_interpolation_b200 as tvi
+from oracle import attention_ref
+from timelapse_video_interpolation_b200 import ops
+from timelapse_video_interpolation_b200.processor import TviAttnProcessor
+from util import attn_from_golden, bf16_round, make_attn, max_abs
+
+pytestmark = pytest.mark.gpu
+TOL = 2e-2  # BASELINE.json: bf16 attention-block outputs within 2e-2 max-abs
+
+ATTN_CASES = ["spatial_self", "temporal_self", "temporal_self_t25", "cross_l1", "cross_l2", "spatial_cross_l2"]
+
+
+def _oracle_on_bf16_inputs(attn_gpu, x, e):
+    """fp32 oracle fed the same bf16-rounded inputs/weights the kernels see."""
+    return attention_ref.attn_processor_ref(attn_gpu, x.float().cpu(), None if e is None else e.float().cpu())
+
+
+@pytest.mark.parametrize("name", ATTN_CASES)
+def test_processor_matches_reference_golden(cuda, golden_dir, name):
+    z = np.load(golden_dir / "attn_processor.npz")
+    attn = attn_from_golden(z, name, device=cuda, dtype=torch.bfloat16, processor=TviAttnProcessor())
+    x = torch.from_numpy(z[f"{name}.x"]).to(cuda, torch.bfloat16)
+    e = torch.from_numpy(z[f"{name}.e"]).to(cuda, torch.bfloat16) if f"{name}.e" in z else None
+    with torch.no_grad():
+        y = attn(x, encoder_hidden_states=e)
+    torch.cuda.synchronize()
+    assert y.shape == x.shape and y.dtype == torch.bfloat16 and y.is_contiguous()
+    err_ref = max_abs(y.float().cpu(), z[f"{name}.y"])               # vs the reference's fp32 run (unrounded inputs)
+    err_orc = max_abs(y.float().cpu(), _oracle_on_bf16_inputs(attn, x, e))  # vs fp32 oracle on the same bf16 inputs
+    # what a bf16 model rounding after every Linear / core (the reference's own bf16 behaviour) would give
+    err_torch = max_abs(attention_ref.attn_processor_ref(attn, x.float().cpu(), None if e is None else e.float().cpu(),
+                                                         round_to=torch.bfloat16), _oracle_on_bf16_inputs(attn, x, e))
+    print(f"{name}: |tvi - reference fp32 golden| = {err_ref:.3e}; |tvi - fp32 oracle(bf16 inputs)| = {err_orc:.3e}; "
+          f"|bf16-rounding reference - fp32 oracle| = {err_torch:.3e}")
+    assert err_orc < TOL
+    assert err_ref < 2 * TOL  # includes the bf16 rounding of inputs and weights themselves
+
+
+@pytest.mark.parametrize("C,heads,Bp,S,cross,L", [
+    (320, 5, 4, 14, None, None),       # temporal self, L0 width
+    (320, 5, 2, 576, None, None),      # spatial self
+    (640, 10, 2, 144, None, None),
+    (1280, 20, 3, 25, None, None),
+    (320, 5, 3, 14, 1024, 1),          # temporal cross, 1 key
+    (320, 5, 3, 14, 1024, 2),
+    (640, 10, 2, 144, 1024, 2),        # spatial cross
+    (1280, 20, 2, 36, 1024, 1),
+])
+def test_processor_svd_widths(cuda, C, heads, Bp, S, cross, L):
+    attn = make_attn(C, cross, heads, seed=C + S, device=cuda, dtype=torch.bfloat16, processor=TviAttnProcessor())
+    g = torch.Generator().manual_seed(S)
+    x = torch.randn(Bp, S, C, generator=g).to(cuda, torch.bfloat16)
+    e = torch.randn(Bp, L, cross, generator=g).to(cuda, torch.bfloat16) if cross else None
+    x0 = x.clone()
+    with torch.no_grad():
+        y = attn(x, encoder_hidden_states=e)
+    torch.cuda.synchronize()
+    assert torch.equal(x, x0), "inputs are borrowed and must not be modified"
+    err = max_abs(y.float().cpu(), _oracle_on_bf16_inputs(attn, x, e))
+    print(f"C={C} S={S} cross={cross} L={L}: max abs err {err:.3e}")
+    assert err < TOL
+
+
+def test_patched_temporal_forward_semantics(cuda, golden_dir):
+    """install() on a model whose temporal forward was monkey-patched (src/train_decouples.py:375-545):
+    ramp bias + statistics come out of the fused kernel and match the reference-generated golden."""
+    z = np.load(golden_dir / "temporal_patched.npz")
+    got = {}
+    proc = TviAttnProcessor(ramp_bias=True, stats_sink=lambda s, a: got.__setitem__("stats", s))
+    attn = attn_from_golden(z, "cross_l2_mask", device=cuda, dtype=torch.bfloat16, processor=proc)
+    x = torch.from_numpy(z["cross_l2_mask.x"]).to(cuda, torch.bfloat16)
+    e = torch.from_numpy(z["cross_l2_mask.e"]).to(cuda, torch.bfloat16)
+    with torch.no_grad():
+        y = attn(x, encoder_hidden_states=e)
+    torch.cuda.synchronize()
+    y_ref, stats_ref = attention_ref.ca_temporal_forward_ref(attn, x.float().cpu(), e.float().cpu(), use_attentionmask=True)
+    assert max_abs(y.float().cpu(), y_ref) < TOL
+    assert max_abs(y.float().cpu(), z["cross_l2_mask.y"]) < 2 * TOL
+    assert max_abs(got["stats"].cpu(), stats_ref) < 5e-3   # q,k are bf16-rounded before the dot product
+    assert max_abs(got["stats"].cpu(), z["cross_l2_mask.stats"]) < 5e-2
+
+
+def test_non_bf16_requires_opt_in(cuda):
+    attn = make_attn(128, None, 2, seed=1, device=cuda, dtype=torch.float32, processor=TviAttnProcessor())
+    x = torch.randn(2, 14, 128, device=cuda)
+    with pytest.raises(tvi.TviError, match="bf16"):
+        attn(x)
+    attn.set_processor(TviAttnProcessor(cast_inputs=True))
+    with torch.no_grad():
+        y = attn(x)
+    assert y.dtype == torch.float32
+    assert max_abs(y.cpu(), attention_ref.attn_processor_ref(attn, x.cpu())) < 2 * TOL
+
+
+def test_gradients_are_refused_not_dropped(cuda):
+    attn = make_attn(128, None, 2, seed=1, device=cuda, dtype=torch.bfloat16, processor=TviAttnProcessor())
+    x = torch.randn(2, 14, 128, device=cuda, dtype=torch.bfloat16, requires_grad=True)
+    with pytest.raises(NotImplementedError):
+        attn(x)
+
+
+def test_launch_counter_counts_only_libtvi_kernels(cuda):
+    attn = make_attn(128, None, 2, seed=1, device=cuda, dtype=torch.bfloat16, processor=TviAttnProcessor())
+    x = torch.randn(2, 14, 128, device=cuda, dtype=torch.bfloat16)
+    before = ops.LAUNCHES
+    with torch.no_grad():
+        attn(x)
+    assert ops.LAUNCHES - before == 3  # QKV GEMM, temporal core, out GEMM
+
+
+def test_full_size_l0_block_properties(cuda):
+    """BASELINE config 2 size (L0: C=320, 5 heads, B=2 x T=14 frames of 72x128 latents): the spatial pass
+    is permutation-equivariant over tokens and the temporal pass over pixels; sampled rows are checked
+    against the fp32 oracle."""
+    C, heads, BF, S = 320, 5, 28, 9216
+    attn = make_attn(C, None, heads, seed=2, device=cuda, dtype=torch.bfloat16, processor=TviAttnProcessor())
+    g = torch.Generator().manual_seed(0)
+    x = torch.randn(2, S, C, generator=g).to(cuda, torch.bfloat16)  # 2 frames are enough for the property
+    with torch.no_grad():
+        y = attn(x)
+        perm = torch.randperm(S, generator=g).to(cuda)
+        yp = attn(x[:, perm].contiguous())
+    torch.cuda.synchronize()
+    # permuting keys changes the summation order only
+    assert max_abs(yp.float().cpu(), y[:, perm].float().cpu()) < 1e-2
+    # frame 0 against the oracle on a subset of query rows (full K/V): do it with a 1-frame oracle call
+    ref = attention_ref.attn_processor_ref(attn, x[:1].float().cpu())
+    assert max_abs(y[:1].float().cpu(), ref) < TOL
+    # full temporal size: 18 432 sequences of 14 tokens
+    xt = torch.randn(18432, 14, C, generator=g).to(cuda, torch.bfloat16)
+    with torch.no_grad():
+        yt = attn(xt)
+    torch.cuda.synchronize()
+    idx = torch.randint(0, 18432, (256,), generator=g)
+    ref = attention_ref.attn_processor_ref(attn, xt[idx.to(cuda)].float().cpu())
+    assert max_abs(yt[idx.to(cuda)].float().cpu(), ref) < TOL

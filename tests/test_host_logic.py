@@ -1,0 +1,106 @@
+"""CPU: host-side behaviour of the plugin — validation, install/uninstall, no silent CPU fallback."""
+import types
+
+import pytest
+import torch
+from torch import nn
+
+import timelapse_video_interpolation_b200 as tvi
+from timelapse_video_interpolation_b200.modules import Attention
+from timelapse_video_interpolation_b200.processor import TviAttnProcessor, install, uninstall
+
+
+class TinyBlock(nn.Module):
+    def __init__(self):
+        super().__init__()
+        self.attn1 = Attention(128, None, heads=2)
+        self.attn2 = Attention(128, 96, heads=2)
+
+
+class TinyUNet(nn.Module):
+    def __init__(self):
+        super().__init__()
+        self.transformer_blocks = nn.ModuleList([TinyBlock()])
+        self.temporal_transformer_blocks = nn.ModuleList([TinyBlock()])
+        self.other = nn.Linear(4, 4)
+
+
+def test_state_dict_keys_match_reference_layout():
+    keys = set(Attention(320, 1024, heads=5).state_dict())
+    assert keys == {"to_q.weight", "to_k.weight", "to_v.weight", "to_out.0.weight", "to_out.0.bias"}
+    a = Attention(320, 1024, heads=5)
+    assert a.to_k.weight.shape == (320, 1024) and a.scale == 64 ** -0.5
+
+
+def test_cpu_tensors_raise_not_fallback():
+    attn = Attention(128, None, heads=2).to(torch.bfloat16)
+    with pytest.raises(tvi.TviError, match="no CPU fallback"):
+        attn(torch.zeros(2, 14, 128, dtype=torch.bfloat16))
+    with pytest.raises(tvi.TviError):
+        tvi.slerp(torch.zeros(1, 16), torch.zeros(1, 16), 14)
+    with pytest.raises(tvi.TviError):
+        tvi.backward_warp_check(torch.zeros(1, 3, 4, 4), torch.zeros(1, 2, 4, 4), torch.zeros(1, 2, 4, 4))
+
+
+def test_unsupported_configurations_raise():
+    p = TviAttnProcessor()
+    attn = Attention(128, None, heads=2)
+    x = torch.zeros(2, 14, 128, dtype=torch.bfloat16)
+    with pytest.raises(tvi.TviError, match="attention_mask"):
+        p(attn, x, attention_mask=torch.zeros(1))
+    attn.residual_connection = True
+    with pytest.raises(tvi.TviError, match="residual_connection"):
+        p(attn, x)
+    attn.residual_connection = False
+    attn.group_norm = nn.GroupNorm(1, 128)
+    with pytest.raises(tvi.TviError, match="group_norm"):
+        p(attn, x)
+    attn.group_norm = None
+    with pytest.raises(tvi.TviError, match="batch, tokens, channels"):
+        p(attn, torch.zeros(2, 128, 4, 4, dtype=torch.bfloat16))
+
+
+def test_install_and_uninstall_walk_all_attention_modules():
+    net = TinyUNet()
+    old = [m.processor for m in net.modules() if isinstance(m, Attention)]
+    shared = TviAttnProcessor()
+    assert install(net, shared) == 4
+    assert all(m.processor is shared for m in net.modules() if isinstance(m, Attention))
+    assert uninstall(net) == 4
+    assert [m.processor for m in net.modules() if isinstance(m, Attention)] == old
+
+
+def test_install_reowns_monkey_patched_temporal_forward():
+    # src/train_decouples.py:511-515 assigns an instance-level forward on every *temporal* Attention
+    net = TinyUNet()
+    calls = []
+    for name, m in net.named_modules():
+        if isinstance(m, Attention) and "temporal" in name:
+            m.forward = lambda *a, **k: calls.append("patched")
+    sink = lambda stats, attn: None
+    n = install(net, temporal_ramp_bias=True, temporal_stats_sink=sink)
+    assert n == 4
+    t = net.temporal_transformer_blocks[0].attn2
+    s = net.transformer_blocks[0].attn2
+    assert isinstance(t.forward, types.MethodType) and t.processor.ramp_bias and t.processor.stats_sink is sink
+    assert not s.processor.ramp_bias and "forward" not in s.__dict__
+    # the re-owned forward dispatches to the processor (which refuses CPU tensors), not to the patch
+    with pytest.raises(tvi.TviError):
+        t(torch.zeros(1, 14, 128, dtype=torch.bfloat16), encoder_hidden_states=torch.zeros(1, 2, 96, dtype=torch.bfloat16))
+    assert calls == []
+    uninstall(net)
+    t(torch.zeros(1, 14, 128))
+    assert calls == ["patched"]
+
+
+def test_fused_weight_cache_tracks_parameter_updates():
+    p = TviAttnProcessor()
+    attn = Attention(128, None, heads=2)
+    w1 = p._fused(attn, ("to_q", "to_k", "to_v"))
+    assert w1.shape == (384, 128) and w1.dtype == torch.bfloat16
+    assert p._fused(attn, ("to_q", "to_k", "to_v")) is w1
+    with torch.no_grad():
+        attn.to_k.weight.add_(1.0)  # what optimizer.step() does: bumps _version
+    w2 = p._fused(attn, ("to_q", "to_k", "to_v"))
+    assert w2 is not w1 and torch.equal(w2[128:256], attn.to_k.weight.to(torch.bfloat16))
+    assert "fused" not in "".join(attn.state_dict())

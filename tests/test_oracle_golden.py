@@ -1,0 +1,125 @@
+"""CPU: the oracle restatement reproduces the golden vectors generated from the reference's own code
+(tests/golden/make_golden.py).  This is what pins the oracle."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import attention_ref, flow_ref, slerp_ref
+from util import attn_from_golden, max_abs
+
+
+def test_flow_cosine_matches_reference_function(golden_dir):
+    z = np.load(golden_dir / "flow_cosine.npz")
+    for i in range(6):
+        got = flow_ref.cosine_similarity(z[f"a{i}"], z[f"b{i}"])
+        assert got.dtype == np.float32
+        assert got == z[f"out{i}"], (i, got, z[f"out{i}"])  # same numpy ops -> bit-identical
+
+
+ATTN_CASES = ["spatial_self", "temporal_self", "temporal_self_t25", "cross_l1", "cross_l2", "spatial_cross_l2"]
+
+
+@pytest.mark.parametrize("name", ATTN_CASES)
+def test_attention_oracle_matches_reference_processors(golden_dir, name):
+    z = np.load(golden_dir / "attn_processor.npz")
+    attn = attn_from_golden(z, name)
+    x = torch.from_numpy(z[f"{name}.x"])
+    e = torch.from_numpy(z[f"{name}.e"]) if f"{name}.e" in z else None
+    y = attention_ref.attn_processor_ref(attn, x, e)
+    assert y.shape == x.shape
+    # fp32 on both sides; only the summation order inside bmm/softmax may differ
+    assert max_abs(y, z[f"{name}.y"]) < 2e-5
+    assert max_abs(y, z[f"{name}.y_sdpa"]) < 2e-5
+    y64 = attention_ref.attn_processor_ref(attn, x, e, dtype=torch.float64)
+    assert max_abs(y64, z[f"{name}.y"]) < 2e-5
+
+
+@pytest.mark.parametrize("name,mask", [("self", False), ("cross_l2", False), ("cross_l2_mask", True)])
+def test_patched_temporal_forward_oracle(golden_dir, name, mask):
+    z = np.load(golden_dir / "temporal_patched.npz")
+    attn = attn_from_golden(z, name)
+    x = torch.from_numpy(z[f"{name}.x"])
+    e = torch.from_numpy(z[f"{name}.e"]) if f"{name}.e" in z else None
+    y, stats = attention_ref.ca_temporal_forward_ref(attn, x, e, use_attentionmask=mask)
+    assert max_abs(y, z[f"{name}.y"]) < 2e-5
+    if e is None:
+        assert stats is None
+    else:
+        assert max_abs(stats, z[f"{name}.stats"]) < 2e-6
+    if not mask:  # without the ramp bias the patched forward equals the stock processor
+        assert max_abs(y, attention_ref.attn_processor_ref(attn, x, e)) < 2e-5
+
+
+def test_one_key_cross_attention_is_query_independent():
+    # with one context token softmax == 1 and the output ignores Q
+    from util import make_attn
+    attn = make_attn(128, 96, 2, seed=5)
+    g = torch.Generator().manual_seed(0)
+    e = torch.randn(3, 1, 96, generator=g)
+    y1 = attention_ref.attn_processor_ref(attn, torch.randn(3, 14, 128, generator=g), e)
+    y2 = attention_ref.attn_processor_ref(attn, torch.randn(3, 14, 128, generator=g), e)
+    assert torch.equal(y1, y2)
+    assert torch.equal(y1[:, 0], y1[:, 5])
+
+
+# ---------------------------------------------------------------- slerp spec (known answers)
+def _rand(shape, seed):
+    return np.random.default_rng(seed).standard_normal(shape).astype(np.float32)
+
+
+def test_slerp_endpoints_and_shape():
+    v0, v1 = _rand((3, 4, 8, 16), 0), _rand((3, 4, 8, 16), 1)
+    out = slerp_ref.slerp_ref(v0, v1, 14)
+    assert out.shape == (3, 14, 4, 8, 16) and out.dtype == np.float32
+    np.testing.assert_allclose(out[:, 0], v0, rtol=1e-6, atol=1e-7)
+    np.testing.assert_allclose(out[:, -1], v1, rtol=1e-6, atol=1e-6)
+
+
+def test_slerp_identical_inputs_take_lerp_branch():
+    v0 = _rand((2, 64), 2)
+    out = slerp_ref.slerp_ref(v0, v0.copy(), 7)
+    for i in range(7):
+        np.testing.assert_allclose(out[:, i], v0, rtol=2e-7, atol=0)
+
+
+def test_slerp_orthogonal_equal_norm_keeps_norm():
+    v0 = np.zeros((1, 64), np.float32)
+    v1 = np.zeros((1, 64), np.float32)
+    v0[0, :32] = 1.0
+    v1[0, 32:] = 1.0
+    out = slerp_ref.slerp_ref(v0, v1, 25)
+    np.testing.assert_allclose(np.linalg.norm(out[0].astype(np.float64), axis=1), np.sqrt(32.0), rtol=1e-6)
+
+
+def test_slerp_matches_closed_form_fp64():
+    v0, v1 = _rand((2, 4, 72, 128), 3), _rand((2, 4, 72, 128), 4)
+    out = slerp_ref.slerp_ref(v0, v1, 14)
+    for c in range(2):
+        x0, x1 = v0[c].astype(np.float64).ravel(), v1[c].astype(np.float64).ravel()
+        th = np.arccos(x0 @ x1 / np.linalg.norm(x0) / np.linalg.norm(x1))
+        for i in (0, 5, 13):
+            t = i / 13
+            ref = (np.sin((1 - t) * th) * x0 + np.sin(t * th) * x1) / np.sin(th)
+            np.testing.assert_allclose(out[c, i].ravel(), ref, rtol=1e-5, atol=1e-6)
+
+
+def test_slerp_nearly_opposite_is_finite():
+    v0 = _rand((1, 256), 5)
+    v1 = -v0 + 1e-3 * _rand((1, 256), 6)
+    out = slerp_ref.slerp_ref(v0, v1, 14)
+    assert np.isfinite(out).all()
+
+
+# ---------------------------------------------------------------- warp spec vs grid_sample semantics
+def test_warp_oracle_identity_and_shift():
+    g = torch.Generator().manual_seed(0)
+    img = torch.rand(2, 3, 12, 20, generator=g)
+    zero = torch.zeros(2, 2, 12, 20)
+    warped, occ, valid, _ = flow_ref.backward_warp_check(img, zero, zero)
+    assert max_abs(warped, img) < 1e-12 and not occ.any() and valid.all()
+    f = torch.zeros(2, 2, 12, 20)
+    f[:, 0] = 1.0  # sample one pixel to the right
+    warped, occ, valid, _ = flow_ref.backward_warp_check(img, f, -f)
+    assert max_abs(warped[..., :-1], img[..., 1:].double()) < 1e-12
+    assert (warped[..., -1] == 0).all() and not valid[..., -1].any() and valid[..., :-1].all()
+    assert not occ[..., :-2].any()  # consistent flows are not occluded
