@@ -1,0 +1,352 @@
+#!/usr/bin/env python
+"""bench.py — clip-frames/sec of the SVD-XT attention hot path on B200 (BASELINE.json metric).
+
+Workload (BASELINE.json configs[1]): the four attention-processor calls of ONE
+L0 `TransformerSpatioTemporalModel` instance of SVD-XT at 576x1024 (latent 72x128 -> S = 9216 tokens,
+C = 320, 5 heads of 64), T = 14 frames, CFG batch 2 (= 1 clip), bf16, through the AttnProcessor plugin:
+
+    y1 = attn1_spatial(x[28, 9216, 320])                 fused-QKV GEMM -> flash core -> out GEMM
+    y2 = attn2_spatial(y1, ctx_spatial[28, 2, 1024])     KV GEMM, Q GEMM -> 2-key core -> out GEMM
+    y3 = attn1_temporal(y2 viewed as [18432, 14, 320])   fused-QKV GEMM -> short-sequence core -> out GEMM
+    y4 = attn2_temporal(y3, ctx_temporal[18432, 1, 1024]) KV GEMM -> out GEMM on 18432 rows -> broadcast
+
+A "step" is one such pass for `--clips` clips per GPU (default 1); clip-frames = clips x T (CFG duplicates
+are not counted).  Multi-GPU: one process per GPU, clips sharded, no collective on the data path
+(weak scaling); time = max over ranks.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl tvi|reference] [--level L0|L1|L2|mid]
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+from pathlib import Path
+
+ROOT = Path(__file__).resolve().parent
+if str(ROOT) not in sys.path:
+    sys.path.insert(0, str(ROOT))
+
+import torch  # noqa: E402
+
+LEVELS = {  # name: (C, heads, h, w)
+    "L0": (320, 5, 72, 128), "L1": (640, 10, 36, 64), "L2": (1280, 20, 18, 32), "mid": (1280, 20, 9, 16),
+}
+T_FRAMES = 14
+CFG = 2
+L_SPATIAL, L_TEMPORAL, CTX_DIM = 2, 1, 1024
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="tvi", choices=["tvi", "reference"])
+    ap.add_argument("--level", default="L0", choices=list(LEVELS))
+    ap.add_argument("--clips", type=int, default=1, help="clips per GPU per step")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    return ap.parse_args()
+
+
+def peaks():
+    p = ROOT / "MEASURED_PEAKS.json"
+    if p.exists():
+        d = json.loads(p.read_text())
+        return {"hbm": d["hbm_gbs"], "tf_burst": d["bf16_tflops"], "tf_sust": d["bf16_tflops_sustained"], "src": "measured"}
+    return {"hbm": 6650.0, "tf_burst": 1590.0, "tf_sust": 1400.0, "src": "fallback"}
+
+
+def workload_name(level, clips):
+    C, heads, h, w = LEVELS[level]
+    return f"svd_xt_{level}_block_attention_576x1024_T{T_FRAMES}_cfg{CFG}_clips{clips}"
+
+
+def algorithmic_flops(level, clips):
+    """FLOPs of one step (GEMMs 2MNK, cores 4*B*h*Sq*Sk*d), listed per kernel family."""
+    C, heads, h, w = LEVELS[level]
+    S = h * w
+    BF = clips * CFG * T_FRAMES
+    N = BF * S
+    nseq = clips * CFG * S
+    f = {}
+    f["spatial_core"] = 4.0 * BF * heads * S * S * 64
+    f["gemm_spatial_self"] = 2.0 * N * C * (3 * C) + 2.0 * N * C * C
+    f["gemm_spatial_cross"] = 2.0 * N * C * C * 2 + 2.0 * BF * L_SPATIAL * CTX_DIM * 2 * C
+    f["gemm_temporal_self"] = 2.0 * N * C * (3 * C) + 2.0 * N * C * C
+    f["temporal_core"] = 4.0 * nseq * heads * T_FRAMES * T_FRAMES * 64
+    f["gemm_temporal_cross"] = 2.0 * nseq * L_TEMPORAL * CTX_DIM * 2 * C + 2.0 * nseq * C * C
+    f["total"] = sum(f.values())
+    return f
+
+
+class ClockSampler:
+    """Samples nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.index = index
+        self.proc = None
+        self.lines = []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._pump, daemon=True)
+            self.thread.start()
+        except OSError:
+            self.proc = None
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except subprocess.TimeoutExpired:
+            self.proc.kill()
+        sm, smax, reasons, power = [], None, set(), []
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            parts = [p.strip() for p in ln.split(",")]
+            if len(parts) < 7:
+                continue
+            try:
+                sm.append(float(parts[0]))
+                smax = float(parts[1])
+                power.append(float(parts[2]))
+            except ValueError:
+                continue
+            for n, v in zip(names, parts[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": smax, "reasons": sorted(reasons),
+                "samples": len(sm), "power_w_max": max(power) if power else None}
+
+
+class Workload:
+    """The four Attention modules of one block instance + synthetic operands (seeded)."""
+
+    def __init__(self, level: str, clips: int, device, dtype, processor_factory):
+        from timelapse_video_interpolation_b200.modules import Attention
+        C, heads, h, w = LEVELS[level]
+        self.C, self.heads, self.S = C, heads, h * w
+        self.BF = clips * CFG * T_FRAMES
+        self.nseq = clips * CFG * self.S
+        self.clips = clips
+        g = torch.Generator().manual_seed(2)
+        proc = processor_factory()
+
+        def mk(cross):
+            a = Attention(C, cross, heads=heads, dim_head=64, processor=proc)
+            with torch.no_grad():
+                for p in a.parameters():  # nn.Linear default init U(+-1/sqrt(in)), seeded
+                    bound = p.shape[-1] ** -0.5 if p.dim() > 1 else C ** -0.5
+                    p.copy_((torch.rand(p.shape, generator=g) * 2 - 1) * bound)
+            return a.to(device=device, dtype=dtype).eval()
+
+        self.attn1_s, self.attn2_s, self.attn1_t, self.attn2_t = mk(None), mk(CTX_DIM), mk(None), mk(CTX_DIM)
+        g0, g1 = torch.Generator().manual_seed(0), torch.Generator().manual_seed(1)
+        self.x_host = torch.randn(self.BF, self.S, C, generator=g0).to(dtype)
+        self.ctx_s_host = torch.randn(self.BF, L_SPATIAL, CTX_DIM, generator=g1).to(dtype)
+        # time_context is the first frame's tokens broadcast over the h*w pixels of a clip
+        # (reference src/models/transformer_temporal.py:279-297): materialise the broadcast like .reshape does
+        ctx_t = torch.randn(clips * CFG, L_TEMPORAL, CTX_DIM, generator=g1).to(dtype)
+        self.ctx_t_host = ctx_t[:, None].expand(clips * CFG, self.S, L_TEMPORAL, CTX_DIM).reshape(self.nseq, L_TEMPORAL, CTX_DIM).contiguous()
+
+    def step(self, x, ctx_s, ctx_t):
+        y1 = self.attn1_s(x)
+        y2 = self.attn2_s(y1, encoder_hidden_states=ctx_s)
+        v = y2.view(self.nseq, T_FRAMES, self.C)
+        y3 = self.attn1_t(v)
+        return self.attn2_t(y3, encoder_hidden_states=ctx_t)
+
+
+# ---------------------------------------------------------------------------------------------------
+# CPU arm: the oracle port (oracle/attention_ref.py, fp32 eager math of the reference processor) on the
+# host cores.  The reference itself cannot be imported on the GPU box (diffusers is absent).
+# ---------------------------------------------------------------------------------------------------
+def cpu_step_sample(wl_cpu, x, ctx_s, ctx_t):
+    from oracle import attention_ref as ar
+    y1 = ar.attn_processor_ref(wl_cpu.attn1_s, x)
+    y2 = ar.attn_processor_ref(wl_cpu.attn2_s, y1, ctx_s)
+    y3 = ar.attn_processor_ref(wl_cpu.attn1_t, wl_cpu.xt_sample)
+    return y2, ar.attn_processor_ref(wl_cpu.attn2_t, y3, ctx_t)
+
+
+def run_cpu(level, steps, warmup):
+    """Bounded sample = the work of ONE clip-frame: one CFG pair of frames through the spatial calls
+    (2 x S tokens) and 2*S/T temporal sequences through the temporal calls."""
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+
+    class _NoProc:
+        def __call__(self, *a, **k):
+            raise AssertionError("CPU arm must not call a processor")
+
+    wl = Workload(level, 1, "cpu", torch.float32, _NoProc)
+    nseq_sample = max(1, round(CFG * wl.S / T_FRAMES))
+    x = wl.x_host[:CFG].float()
+    ctx_s = wl.ctx_s_host[:CFG].float()
+    ctx_t = wl.ctx_t_host[:nseq_sample].float()
+    wl.xt_sample = torch.randn(nseq_sample, T_FRAMES, wl.C, generator=torch.Generator().manual_seed(5))
+    times = []
+    with torch.no_grad():
+        for i in range(warmup + steps):
+            t0 = time.perf_counter()
+            cpu_step_sample(wl, x, ctx_s, ctx_t)
+            if i >= warmup:
+                times.append(time.perf_counter() - t0)
+    sec = sum(times) / len(times)
+    sample = (f"1 clip-frame of the workload per step: {CFG} frames x {wl.S} tokens through both spatial calls + "
+              f"{nseq_sample} temporal sequences of {T_FRAMES} through both temporal calls, fp32 eager oracle, torch {cores} threads")
+    return 1.0 / sec, sec * 1e3, cores, sample
+
+
+def main():
+    args = parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+
+    if args.impl == "reference":
+        if rank != 0:
+            return 0
+        steps, warmup = max(1, min(args.steps, 5)), max(1, min(args.warmup, 2))
+        value, ms, cores, sample = run_cpu(args.level, steps, warmup)
+        line = {"impl": "reference", "metric": "clip-frames/sec", "value": value, "unit": "clip-frames/s", "n_gpus": args.gpus,
+                "steps": steps, "warmup": warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
+                "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+                "config": {"workload": workload_name(args.level, args.clips), "note": "CPU arm runs a 1-clip-frame sample per step"},
+                "cpu_baseline": {"value": value, "unit": "clip-frames/s", "cores": cores, "kind": "port", "sample": sample},
+                "e2e": {"value": value, "unit": "clip-frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+        print(json.dumps(line))
+        return 0
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py --impl tvi needs a CUDA device (there is no CPU fallback)")
+    import torch.distributed as dist
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+
+    import timelapse_video_interpolation_b200 as tvi
+    from timelapse_video_interpolation_b200 import ops
+    from timelapse_video_interpolation_b200.processor import TviAttnProcessor
+
+    wl = Workload(args.level, args.clips, dev, torch.bfloat16, TviAttnProcessor)
+    x_pin, cs_pin, ct_pin = wl.x_host.pin_memory(), wl.ctx_s_host.pin_memory(), wl.ctx_t_host.pin_memory()
+    x, ctx_s, ctx_t = x_pin.to(dev), cs_pin.to(dev), ct_pin.to(dev)
+    out_pin = torch.empty(wl.nseq, T_FRAMES, wl.C, dtype=torch.bfloat16).pin_memory()
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    dom = "attn_spatial"
+    dom_events = []
+
+    def hook(name, is_start):
+        if name == dom:
+            ev = torch.cuda.Event(enable_timing=True)
+            ev.record()  # torch's current stream == the stream libtvi launches on
+            dom_events.append(ev)
+
+    with torch.no_grad():
+        for _ in range(max(3, args.warmup)):
+            wl.step(x, ctx_s, ctx_t)
+        barrier()
+        # ---------------- timed region 1: device-resident inputs (`value`) ----------------
+        sampler = ClockSampler(local_rank)
+        sampler.start()
+        ops.EVENT_HOOK = hook
+        launches0 = ops.LAUNCHES
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(args.steps):
+            y = wl.step(x, ctx_s, ctx_t)
+        e1.record()
+        barrier()
+        ops.EVENT_HOOK = None
+        launches = ops.LAUNCHES - launches0
+        ms_total = e0.elapsed_time(e1)
+        clocks = sampler.stop()
+        dom_ms = [dom_events[i].elapsed_time(dom_events[i + 1]) for i in range(0, len(dom_events), 2)]
+        # ---------------- timed region 2: host buffers, H2D + D2H inside (`e2e`) ----------------
+        for _ in range(2):
+            wl.step(x_pin.to(dev, non_blocking=True), cs_pin.to(dev, non_blocking=True), ct_pin.to(dev, non_blocking=True))
+        barrier()
+        f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        f0.record()
+        for _ in range(args.steps):
+            xd = x_pin.to(dev, non_blocking=True)
+            csd = cs_pin.to(dev, non_blocking=True)
+            ctd = ct_pin.to(dev, non_blocking=True)
+            y = wl.step(xd, csd, ctd)
+            out_pin.copy_(y, non_blocking=True)
+        f1.record()
+        barrier()
+        ms_e2e = f0.elapsed_time(f1)
+
+    t = torch.tensor([ms_total, ms_e2e], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_total, ms_e2e = float(t[0]), float(t[1])
+    frames_per_step = args.clips * T_FRAMES * world
+    value = frames_per_step * args.steps / (ms_total * 1e-3)
+    e2e_value = frames_per_step * args.steps / (ms_e2e * 1e-3)
+
+    if rank == 0:
+        pk = peaks()
+        fl = algorithmic_flops(args.level, args.clips)
+        dom_avg_ms = sum(dom_ms) / len(dom_ms)
+        achieved = fl["spatial_core"] / (dom_avg_ms * 1e-3) / 1e12
+        h2d = x_pin.numel() * 2 + cs_pin.numel() * 2 + ct_pin.numel() * 2
+        line = {
+            "metric": "clip-frames/sec", "value": value, "unit": "clip-frames/s", "n_gpus": world, "steps": args.steps,
+            "warmup": max(3, args.warmup), "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+            "config": {"workload": workload_name(args.level, args.clips), "level": args.level, "clips_per_gpu": args.clips,
+                       "frames": T_FRAMES, "cfg_batch": CFG, "tokens_per_frame": wl.S, "channels": wl.C, "heads": wl.heads,
+                       "ctx_tokens": [L_SPATIAL, L_TEMPORAL], "parallelism": f"clip-sharded x{world}, no collective",
+                       "l2": "inputs (165 MB activations per call at L0) exceed the 126 MB L2; no explicit flush",
+                       "step_tflop": fl["total"] / 1e12},
+            "e2e": {"value": e2e_value, "unit": "clip-frames/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": out_pin.numel() * 2,
+                    "ms_per_step": ms_e2e / args.steps},
+            "gpu_launches": launches,
+            "clocks": clocks,
+            "roofline": {"kernel": "attn_spatial_kernel", "bound": "tensor", "achieved": achieved, "peak": pk["tf_sust"],
+                         "unit": "TFLOP/s", "frac": achieved / pk["tf_sust"], "traffic": None, "peak_source": pk["src"] + " (sustained)",
+                         "ms_per_launch": dom_avg_ms, "share_of_step": dom_avg_ms / (ms_total / args.steps),
+                         "algorithmic_flops_per_launch": fl["spatial_core"]},
+            "step_tflops": fl["total"] / 1e12 / (ms_total / args.steps * 1e-3),
+        }
+        if world == 1 and not args.no_cpu_baseline:
+            v, ms, cores, sample = run_cpu(args.level, 2, 1)
+            line["cpu_baseline"] = {"value": v, "unit": "clip-frames/s", "cores": cores, "kind": "port", "sample": sample,
+                                    "ms_per_sample": ms}
+        print(json.dumps(line))
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

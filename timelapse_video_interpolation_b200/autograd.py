@@ -47,7 +47,7 @@ def cross_attention(x: torch.Tensor, e: torch.Tensor, w_q: torch.Tensor, w_kv: t
         # softmax over one key == 1: every query row of a group gets to_out(v_group); project the
         # B' value rows once and broadcast them (Q is never needed)
         yv = ops.gemm_bf16_tn(v, w_o, b_o)  # [B', C]
-        y = ops.attn_fewkeys(None, yv, yv, Bp * S, S, 1, 1, 1.0)
+        y = ops.attn_fewkeys(None, yv, yv, Bp * S, S, heads, 1, 1.0)  # L == 1: pure row broadcast
         return y.view(Bp, S, -1)
     q = ops.gemm_bf16_tn(x.view(Bp * S, C), w_q)
     o = ops.attn_fewkeys(q, k, v, Bp * S, S, heads, L, scale, Tq=S if (bias is not None or stats is not None) else 1,

@@ -11,6 +11,9 @@ import torch
 from . import _lib
 
 LAUNCHES = 0  # kernels launched through libtvi since import (per process)
+# Optional profiling hook: callable(kernel_name, is_start) invoked right before / after a launch is
+# enqueued (bench.py uses it to bracket one kernel with CUDA events on the launching stream).
+EVENT_HOOK = None
 
 
 def _stream() -> int:
@@ -56,8 +59,12 @@ def gemm_bf16_tn(x: torch.Tensor, w: torch.Tensor, bias: torch.Tensor | None = N
     out, ldy = _rows2d(out, "out")
     if bias is not None and (bias.dtype != torch.bfloat16 or not bias.is_contiguous() or bias.numel() != N):
         raise _lib.TviError(_lib.TVI_ERR_INVALID, "gemm: bias must be a contiguous bf16 vector of length N")
+    if EVENT_HOOK is not None:
+        EVENT_HOOK("gemm_bf16_tn", True)
     _lib.check(_lib.load().tvi_gemm_bf16_tn(x.data_ptr(), w.data_ptr(), bias.data_ptr() if bias is not None else None,
                                             out.data_ptr(), M, N, K, ldx, ldw, ldy, _stream()))
+    if EVENT_HOOK is not None:
+        EVENT_HOOK("gemm_bf16_tn", False)
     LAUNCHES += 1
     return out
 
@@ -73,9 +80,13 @@ def attn_temporal(q, k, v, nseq: int, heads: int, Tq: int, Tk: int, scale: float
     if out is None:
         out = torch.empty(nseq * Tq, heads * d, dtype=torch.bfloat16, device=q.device)
     out, ldo = _rows2d(out, "out")
+    if EVENT_HOOK is not None:
+        EVENT_HOOK("attn_temporal", True)
     _lib.check(_lib.load().tvi_attn_temporal_fwd(q.data_ptr(), k.data_ptr(), v.data_ptr(), out.data_ptr(),
                                                  lse.data_ptr() if lse is not None else None, nseq, heads, Tq, Tk, d,
                                                  ldq, ldk, ldv, ldo, float(scale), _stream()))
+    if EVENT_HOOK is not None:
+        EVENT_HOOK("attn_temporal", False)
     LAUNCHES += 1
     return out
 
@@ -102,11 +113,15 @@ def attn_fewkeys(q, k, v, nrows: int, rows_per_group: int, heads: int, L: int, s
         ws = torch.empty(Tq * L, dtype=torch.float64, device=k.device)
     if bias is not None and (bias.dtype != torch.float32 or not bias.is_contiguous() or bias.numel() != Tq * L):
         raise _lib.TviError(_lib.TVI_ERR_INVALID, "bias must be a contiguous fp32 [Tq, L] tensor")
+    if EVENT_HOOK is not None:
+        EVENT_HOOK("attn_fewkeys", True)
     _lib.check(_lib.load().tvi_attn_fewkeys_fwd(q.data_ptr() if q is not None else None, k.data_ptr(), v.data_ptr(),
                                                 out.data_ptr(), nrows, rows_per_group, heads, L, d, ldq, ldk, ldv, ldo,
                                                 float(scale), Tq, bias.data_ptr() if bias is not None else None,
                                                 stats.data_ptr() if stats is not None else None,
                                                 ws.data_ptr() if ws is not None else None, _stream()))
+    if EVENT_HOOK is not None:
+        EVENT_HOOK("attn_fewkeys", False)
     LAUNCHES += 1 if stats is None else 2
     return out
 
@@ -122,9 +137,13 @@ def attn_spatial(q, k, v, batch: int, heads: int, S: int, Skv: int, scale: float
     if out is None:
         out = torch.empty(batch * S, heads * d, dtype=torch.bfloat16, device=q.device)
     out, ldo = _rows2d(out, "out")
+    if EVENT_HOOK is not None:
+        EVENT_HOOK("attn_spatial", True)
     _lib.check(_lib.load().tvi_attn_spatial_fwd(q.data_ptr(), k.data_ptr(), v.data_ptr(), out.data_ptr(),
                                                 lse.data_ptr() if lse is not None else None, batch, heads, S, Skv, d,
                                                 ldq, ldk, ldv, ldo, float(scale), _stream()))
+    if EVENT_HOOK is not None:
+        EVENT_HOOK("attn_spatial", False)
     LAUNCHES += 1
     return out
 
@@ -140,8 +159,12 @@ def slerp_f32(v0: torch.Tensor, v1: torch.Tensor, T: int, dot_threshold: float, 
     n = v0.numel() // nclips if nclips else 0
     if out is None:
         out = torch.empty((nclips, T) + tuple(v0.shape[1:]), dtype=torch.float32, device=v0.device)
+    if EVENT_HOOK is not None:
+        EVENT_HOOK("slerp", True)
     _lib.check(_lib.load().tvi_slerp_f32(v0.data_ptr(), v1.data_ptr(), out.data_ptr(), nclips, n, T,
                                          float(dot_threshold), _stream()))
+    if EVENT_HOOK is not None:
+        EVENT_HOOK("slerp", False)
     LAUNCHES += 1
     return out
 
@@ -162,8 +185,12 @@ def flow_cosine_f32(fa: torch.Tensor, fb: torch.Tensor, hwc: bool, out=None) -> 
     ws = torch.empty(max(1, lib.tvi_flow_cosine_workspace_bytes(npairs, H, W) // 8), dtype=torch.float64, device=fa.device)
     if out is None:
         out = torch.empty(npairs, dtype=torch.float32, device=fa.device)
+    if EVENT_HOOK is not None:
+        EVENT_HOOK("flow_cosine", True)
     _lib.check(lib.tvi_flow_cosine_f32(fa.data_ptr(), fb.data_ptr(), out.data_ptr(), ws.data_ptr(), npairs, H, W,
                                        1 if hwc else 0, _stream()))
+    if EVENT_HOOK is not None:
+        EVENT_HOOK("flow_cosine", False)
     LAUNCHES += 2
     return out
 
@@ -183,7 +210,11 @@ def backward_warp_f32(img2, f_fwd, f_bwd, alpha: float, beta: float, warped=None
         warped = torch.empty_like(img2)
     if mask is None:
         mask = torch.empty(B, H, W, dtype=torch.uint8, device=img2.device)
+    if EVENT_HOOK is not None:
+        EVENT_HOOK("backward_warp", True)
     _lib.check(_lib.load().tvi_backward_warp_f32(img2.data_ptr(), f_fwd.data_ptr(), f_bwd.data_ptr(), warped.data_ptr(),
                                                  mask.data_ptr(), B, Cc, H, W, float(alpha), float(beta), _stream()))
+    if EVENT_HOOK is not None:
+        EVENT_HOOK("backward_warp", False)
     LAUNCHES += 1
     return warped, mask
