@@ -126,6 +126,17 @@ int tvi_attn_spatial_fwd(const tvi_bf16* q, const tvi_bf16* k, const tvi_bf16* v
                          int batch, int heads, int S, int Skv, int d, int64_t ldq, int64_t ldk, int64_t ldv,
                          int64_t ldo, float scale, void* stream);
 
+/* Same call with an explicit kernel choice (parity tests exercise both; AUTO is what
+ * tvi_attn_spatial_fwd uses: tcgen05 when S and Skv are >= 1024, mma.sync otherwise).
+ * TVI_SPATIAL_TCGEN05: TMA-fed tcgen05.mma, S/P/O in tensor memory, 256 query rows per CTA.
+ * TVI_SPATIAL_MMA_SYNC: register-resident flash kernel on mma.sync (short sequences). */
+#define TVI_SPATIAL_AUTO 0
+#define TVI_SPATIAL_MMA_SYNC 1
+#define TVI_SPATIAL_TCGEN05 2
+int tvi_attn_spatial_fwd_algo(const tvi_bf16* q, const tvi_bf16* k, const tvi_bf16* v, tvi_bf16* o, float* lse,
+                              int batch, int heads, int S, int Skv, int d, int64_t ldq, int64_t ldk, int64_t ldv,
+                              int64_t ldo, float scale, int algo, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -5,7 +5,7 @@ import pytest
 import torch
 
 from oracle.attention_ref import batch_to_head_dim, get_attention_scores, head_to_batch_dim
-from timelapse_video_interpolation_b200 import ops
+from timelapse_video_interpolation_b200 import _lib, ops
 
 pytestmark = pytest.mark.gpu
 TOL = 2e-2  # bf16 attention bar from BASELINE.json (max-abs); typical error is ~4e-3, printed below
@@ -60,34 +60,52 @@ def test_temporal_core_reads_packed_qkv_in_place(cuda):
     (2, 2, 80, 80), (1, 5, 144, 144), (3, 1, 576, 576), (1, 2, 100, 100), (2, 2, 65, 130),
     (1, 1, 2304, 2304), (1, 2, 129, 63), (2, 5, 1000, 1000),
 ])
-def test_spatial_core(cuda, B, heads, S, Skv):
+@pytest.mark.parametrize("algo", [_lib.SPATIAL_MMA_SYNC, _lib.SPATIAL_TCGEN05], ids=["mma_sync", "tcgen05"])
+def test_spatial_core(cuda, B, heads, S, Skv, algo):
     g = torch.Generator().manual_seed(S + Skv)
     C = heads * 64
     q, qf = _rand((B, S, C), g, cuda)
     k, kf = _rand((B, Skv, C), g, cuda)
     v, vf = _rand((B, Skv, C), g, cuda)
     lse = torch.empty(B * S, heads, dtype=torch.float32, device=cuda)
-    o = ops.attn_spatial(q.view(-1, C), k.view(-1, C), v.view(-1, C), B, heads, S, Skv, 0.125, lse=lse)
+    o = ops.attn_spatial(q.view(-1, C), k.view(-1, C), v.view(-1, C), B, heads, S, Skv, 0.125, lse=lse, algo=algo)
     torch.cuda.synchronize()
     ref, logits = _core_ref(qf, kf, vf, heads, 0.125)
     err = (o.float().cpu().view(B, S, C) - ref).abs().max().item()
-    print(f"spatial core B={B} h={heads} S={S}x{Skv}: max abs err {err:.3e}")
+    print(f"spatial core algo={algo} B={B} h={heads} S={S}x{Skv}: max abs err {err:.3e}")
     assert err < TOL
     ref_lse = torch.logsumexp(logits, dim=-1).view(B, heads, S).permute(0, 2, 1).reshape(B * S, heads)
     assert (lse.cpu() - ref_lse).abs().max().item() < 1e-3
 
 
-def test_spatial_core_large_logits_stay_finite(cuda):
-    # online-softmax rescaling: a late key block dominates an early one by a huge margin
+@pytest.mark.parametrize("algo", [_lib.SPATIAL_MMA_SYNC, _lib.SPATIAL_TCGEN05], ids=["mma_sync", "tcgen05"])
+def test_spatial_core_large_logits_stay_finite(cuda, algo):
+    # online-softmax rescaling: a late key block dominates an early one by a huge margin (the tcgen05
+    # kernel's lazy reference maximum must rescale its TMEM accumulator here)
     g = torch.Generator().manual_seed(9)
-    B, heads, S = 1, 1, 256
+    B, heads, S = 1, 1, 640
     q, qf = _rand((B, S, 64), g, cuda, 6.0)
     k, kf = _rand((B, S, 64), g, cuda, 6.0)
     v, vf = _rand((B, S, 64), g, cuda)
-    o = ops.attn_spatial(q.view(-1, 64), k.view(-1, 64), v.view(-1, 64), B, heads, S, S, 0.125)
+    o = ops.attn_spatial(q.view(-1, 64), k.view(-1, 64), v.view(-1, 64), B, heads, S, S, 0.125, algo=algo)
     torch.cuda.synchronize()
     ref, _ = _core_ref(qf, kf, vf, heads, 0.125)
     assert torch.isfinite(o).all() and (o.float().cpu().view(B, S, 64) - ref).abs().max().item() < 3e-2
+
+
+def test_spatial_core_reads_packed_qkv_in_place_tcgen05(cuda):
+    # the processor hands the kernel three column slices of one [tokens, 3C] buffer (row stride 3C)
+    g = torch.Generator().manual_seed(21)
+    B, heads, S = 2, 5, 1152
+    C = heads * 64
+    qkv, qkvf = _rand((B * S, 3 * C), g, cuda)
+    o = ops.attn_spatial(qkv[:, :C], qkv[:, C:2 * C], qkv[:, 2 * C:], B, heads, S, S, 0.125, algo=_lib.SPATIAL_TCGEN05)
+    o2 = ops.attn_spatial(qkv[:, :C], qkv[:, C:2 * C], qkv[:, 2 * C:], B, heads, S, S, 0.125, algo=_lib.SPATIAL_MMA_SYNC)
+    torch.cuda.synchronize()
+    f = qkvf.view(B, S, 3 * C)
+    ref, _ = _core_ref(f[..., :C], f[..., C:2 * C], f[..., 2 * C:], heads, 0.125)
+    assert (o.float().cpu().view(B, S, C) - ref).abs().max().item() < TOL
+    assert (o.float() - o2.float()).abs().max().item() < TOL
 
 
 @pytest.mark.parametrize("groups,S,heads,L,d", [

@@ -44,7 +44,10 @@ SIGNATURES = {
                                     _i64, _i64, _i64, _i64, _f32, _i32, _ptr, _ptr, _ptr, _ptr]),
     "tvi_attn_spatial_fwd": (_i32, [_ptr, _ptr, _ptr, _ptr, _ptr, _i32, _i32, _i32, _i32, _i32,
                                     _i64, _i64, _i64, _i64, _f32, _ptr]),
+    "tvi_attn_spatial_fwd_algo": (_i32, [_ptr, _ptr, _ptr, _ptr, _ptr, _i32, _i32, _i32, _i32, _i32,
+                                         _i64, _i64, _i64, _i64, _f32, _i32, _ptr]),
 }
+SPATIAL_AUTO, SPATIAL_MMA_SYNC, SPATIAL_TCGEN05 = 0, 1, 2
 
 _lib = None
 

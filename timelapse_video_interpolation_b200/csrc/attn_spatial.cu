@@ -211,9 +211,14 @@ attn_spatial_kernel(const tvi_bf16* __restrict__ q, const tvi_bf16* __restrict__
 }  // namespace
 }  // namespace tvi
 
-extern "C" int tvi_attn_spatial_fwd(const tvi_bf16* q, const tvi_bf16* k, const tvi_bf16* v, tvi_bf16* o, float* lse, int batch,
-                                    int heads, int S, int Skv, int d, int64_t ldq, int64_t ldk, int64_t ldv, int64_t ldo,
-                                    float scale, void* stream) {
+namespace tvi {
+int launch_spatial_tc(const tvi_bf16* q, const tvi_bf16* k, const tvi_bf16* v, tvi_bf16* o, float* lse, int batch, int heads,
+                      int S, int Skv, int64_t ldq, int64_t ldk, int64_t ldv, int64_t ldo, float scale, cudaStream_t st);
+}
+
+extern "C" int tvi_attn_spatial_fwd_algo(const tvi_bf16* q, const tvi_bf16* k, const tvi_bf16* v, tvi_bf16* o, float* lse,
+                                         int batch, int heads, int S, int Skv, int d, int64_t ldq, int64_t ldk, int64_t ldv,
+                                         int64_t ldo, float scale, int algo, void* stream) {
   using namespace tvi;
   TVI_CHECK_ARG(batch >= 0 && heads >= 0 && S >= 0 && Skv >= 0, "tvi_attn_spatial_fwd: negative size");
   if (batch == 0 || heads == 0 || S == 0) return TVI_OK;
@@ -224,6 +229,14 @@ extern "C" int tvi_attn_spatial_fwd(const tvi_bf16* q, const tvi_bf16* k, const 
   TVI_CHECK_ARG(ldq >= heads * 64 && ldk >= heads * 64 && ldv >= heads * 64 && ldo >= heads * 64, "tvi_attn_spatial_fwd: row stride smaller than heads*d");
   TVI_CHECK_ARG(((uintptr_t)q | (uintptr_t)k | (uintptr_t)v | (uintptr_t)o) % 16 == 0, "tvi_attn_spatial_fwd: pointers must be 16-byte aligned");
   TVI_CHECK_ARG((int64_t)batch * heads <= 65535, "tvi_attn_spatial_fwd: batch*heads exceeds 65535");
+  TVI_CHECK_ARG(algo >= TVI_SPATIAL_AUTO && algo <= TVI_SPATIAL_TCGEN05, "tvi_attn_spatial_fwd_algo: unknown algo %d", algo);
+  if (algo == TVI_SPATIAL_AUTO) {
+    // a CTA of the tcgen05 kernel owns 256 query rows and needs a few key tiles to amortise its
+    // prologue; short sequences (L2 / mid level: 576, 144 tokens) stay on the mma.sync kernel
+    algo = (S >= 1024 && Skv >= 1024) ? TVI_SPATIAL_TCGEN05 : TVI_SPATIAL_MMA_SYNC;
+  }
+  if (algo == TVI_SPATIAL_TCGEN05)
+    return launch_spatial_tc(q, k, v, o, lse, batch, heads, S, Skv, ldq, ldk, ldv, ldo, scale, (cudaStream_t)stream);
   static bool configured[64] = {false};
   int dev = 0;
   TVI_CUDA_OK(cudaGetDevice(&dev));
@@ -236,4 +249,10 @@ extern "C" int tvi_attn_spatial_fwd(const tvi_bf16* q, const tvi_bf16* k, const 
                                                                          scale);
   TVI_LAUNCH_OK("attn_spatial_kernel");
   return TVI_OK;
+}
+
+extern "C" int tvi_attn_spatial_fwd(const tvi_bf16* q, const tvi_bf16* k, const tvi_bf16* v, tvi_bf16* o, float* lse, int batch,
+                                    int heads, int S, int Skv, int d, int64_t ldq, int64_t ldk, int64_t ldv, int64_t ldo,
+                                    float scale, void* stream) {
+  return tvi_attn_spatial_fwd_algo(q, k, v, o, lse, batch, heads, S, Skv, d, ldq, ldk, ldv, ldo, scale, TVI_SPATIAL_AUTO, stream);
 }

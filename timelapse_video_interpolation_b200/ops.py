@@ -126,8 +126,10 @@ def attn_fewkeys(q, k, v, nrows: int, rows_per_group: int, heads: int, L: int, s
     return out
 
 
-def attn_spatial(q, k, v, batch: int, heads: int, S: int, Skv: int, scale: float, out=None, lse=None):
-    """Flash-style spatial attention core; q is [batch*S, heads*64], k/v [batch*Skv, heads*64]."""
+def attn_spatial(q, k, v, batch: int, heads: int, S: int, Skv: int, scale: float, out=None, lse=None,
+                 algo: int = _lib.SPATIAL_AUTO):
+    """Flash-style spatial attention core; q is [batch*S, heads*64], k/v [batch*Skv, heads*64].
+    `algo` picks the kernel (_lib.SPATIAL_AUTO / SPATIAL_MMA_SYNC / SPATIAL_TCGEN05)."""
     global LAUNCHES
     _need_cuda(q, k, v)
     q, ldq = _rows2d(q, "q")
@@ -139,9 +141,9 @@ def attn_spatial(q, k, v, batch: int, heads: int, S: int, Skv: int, scale: float
     out, ldo = _rows2d(out, "out")
     if EVENT_HOOK is not None:
         EVENT_HOOK("attn_spatial", True)
-    _lib.check(_lib.load().tvi_attn_spatial_fwd(q.data_ptr(), k.data_ptr(), v.data_ptr(), out.data_ptr(),
-                                                lse.data_ptr() if lse is not None else None, batch, heads, S, Skv, d,
-                                                ldq, ldk, ldv, ldo, float(scale), _stream()))
+    _lib.check(_lib.load().tvi_attn_spatial_fwd_algo(q.data_ptr(), k.data_ptr(), v.data_ptr(), out.data_ptr(),
+                                                     lse.data_ptr() if lse is not None else None, batch, heads, S, Skv,
+                                                     d, ldq, ldk, ldv, ldo, float(scale), int(algo), _stream()))
     if EVENT_HOOK is not None:
         EVENT_HOOK("attn_spatial", False)
     LAUNCHES += 1
