@@ -5,87 +5,95 @@
 // (src/models/attention_processor.py:1243, :1156; caller src/models/attention.py:276-281).
 //
 // One CTA owns 256 query rows (two 128-row tiles) of one (frame, head) and streams the keys in
-// tiles of 128.  320 threads, warp-specialised:
-//   warp 0        TMA producer: the two Q tiles once, then K_j / V_j into a 4-stage smem ring
-//                 (3-D tensor maps [heads*64, S, batch] so sequence tails are zero-filled / clipped).
-//   warp 1        tcgen05.mma issuer (one lane):  S_t = Q_t K_j^T   (SS, M=128 N=128 K=64)
-//                                                O_t += P_t V_j    (TS: P read from TMEM, V_j is the
-//                                                                   MN-major smem operand, N=64)
-//                 ordered  PV0_j, QK0_{j+1}, PV1_j, QK1_{j+1}  so that one tile's MMAs run under the
-//                 other tile's softmax.
+// steps of 64.  320 threads, warp-specialised:
+//   warp 0        TMA producer: K_j / V_j ([64 keys x 64] each) into an 8-stage smem ring
+//                 (3-D tensor maps [heads*64, Skv, batch]: sequence tails are zero-filled).
+//   warp 1        tcgen05.mma issuer (one lane).  Both products take their A operand from tensor
+//                 memory, so shared memory only feeds the 64-wide B operands:
+//                     S_t[j&1] = Q_t K_j^T      (M=128 N=64 K=64, A = Q_t in TMEM, B = K_j K-major)
+//                     O_t     += P_t[j&1] V_j   (M=128 N=64 K=64, A = P in TMEM, B = V_j MN-major)
+//                 issued as  QK0_j QK1_j PV0_{j-1} PV1_{j-1}: the scores of step j are produced while
+//                 the softmax warps are still working on step j-1 (S is double-buffered per tile).
 //   warps 2..5    softmax of tile 0, warps 6..9 softmax of tile 1: one thread per query row
-//                 (TMEM lane), S read with tcgen05.ld, fp32 online softmax with FMNMX3 / FFMA2 /
-//                 ex2, P written back to TMEM as bf16 with tcgen05.st.  The running maximum is only
-//                 advanced when it grows by more than 2^8 (P stays <= 256, exact in the final
-//                 O / l), so the O accumulator in TMEM is rescaled rarely, by the same threads.
-//   epilogue      O_t / l -> bf16 -> swizzled smem (the dead Q tile) -> TMA store, one 32-row box per warp.
-// TMEM columns: S0 [0,128) S1 [128,256) O0 [256,320) O1 [320,384) P0 [384,448) P1 [448,512).
+//                 (TMEM lane).  The thread first parks its Q row in TMEM, then per step reads its 64
+//                 scores with tcgen05.ld, does the fp32 online softmax (FMNMX3 / FFMA2 / ex2 / FADD2)
+//                 and writes P as bf16 over the first half of the same S buffer with tcgen05.st.
+//                 The reference maximum only moves when the row maximum outgrows it by 2^8 (P stays
+//                 <= 256, exact in O / l), so the O accumulator in TMEM is rescaled rarely, by the
+//                 same threads.
+//   epilogue      O_t / l -> bf16 -> swizzled smem -> TMA store, one 32-row box per warp (clips S tails).
+// TMEM columns of tile t (base 256 t): S[0] [0,64) S[1] [64,128) O [128,192) Q [192,224).
 // FLOPs: 4 * batch * heads * S * Skv * 64.  With d = 64 the exp throughput (16 / clk / SM), not the
-// tensor pipe, is the per-SM ceiling: 128x128 exps per 2 x 256 MMA cycles.
+// tensor pipe, is the per-SM ceiling: 2 x 128 x 64 exps against 4 x 128 MMA cycles per step.
 #include "tvi_common.cuh"
 
 namespace tvi {
 namespace {
 
 constexpr int kTcThreads = 320;
-constexpr int kTcBM = 128;       // query rows per tile (UMMA M)
-constexpr int kTcBN = 128;       // keys per stage (UMMA N of QK^T, K of PV)
-constexpr int kTcStages = 4;
-constexpr int kTcTileBytes = 128 * 128;  // 128 rows x 64 bf16
-constexpr int kTcSmem = 1024 + 2 * kTcTileBytes + kTcStages * 2 * kTcTileBytes;
+constexpr int kTcBM = 128;      // query rows per tile (UMMA M)
+constexpr int kTcBN = 64;       // keys per step (UMMA N of QK^T, K of PV)
+constexpr int kTcStages = 8;
+constexpr int kTcKBytes = kTcBN * 128;      // [64 keys][64 bf16]
+constexpr int kTcStageBytes = 2 * kTcKBytes;
+constexpr int kTcOutBytes = kTcBM * 128;    // output staging of one tile
+constexpr int kTcSmem = 1024 + 2 * kTcOutBytes + kTcStages * kTcStageBytes;
 
-constexpr uint32_t kColS = 0, kColO = 256, kColP = 384;
+constexpr uint32_t kColTile = 256, kColS = 0, kColO = 128, kColQ = 192;
 
 struct TcParams {
+  const tvi_bf16* q;
+  int64_t ldq;
   int S, Skv, heads;
-  int n_kv;       // key tiles
+  int n_kv;       // key steps
   float scale;
   float* lse;     // nullable, [batch*S, heads]
+};
+
+struct TcBarriers {
+  uint64_t q_full[2];
+  uint64_t kv_full[kTcStages];
+  uint64_t kv_empty[kTcStages];
+  uint64_t s_full[2][2];
+  uint64_t p_full[2][2];
+  uint64_t o_full[2];
 };
 
 #include "attn_spatial_tc_softmax.cuh"
 
 __global__ void __launch_bounds__(kTcThreads, 1)
-attn_spatial_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
-                       const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUtensorMap tmO,
-                       const TcParams p) {
+attn_spatial_tc_kernel(const __grid_constant__ CUtensorMap tmK, const __grid_constant__ CUtensorMap tmV,
+                       const __grid_constant__ CUtensorMap tmO, const TcParams p) {
   extern __shared__ uint8_t smem_raw[];
-  __shared__ __align__(8) uint64_t bar_q[2];
-  __shared__ __align__(8) uint64_t bar_k_full[kTcStages];
-  __shared__ __align__(8) uint64_t bar_v_full[kTcStages];
-  __shared__ __align__(8) uint64_t bar_kv_empty[kTcStages];
-  __shared__ __align__(8) uint64_t bar_s_full[2];
-  __shared__ __align__(8) uint64_t bar_p_full[2];
-  __shared__ __align__(8) uint64_t bar_o_full[2];
+  __shared__ __align__(8) TcBarriers bars;
   __shared__ uint32_t s_tmem_base;
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   uint8_t* base_ptr = smem_raw + (base - smem_u32(smem_raw));
-  // [Q0 | Q1 | (K,V) x stages]
-  const uint32_t sQ = base;
-  const uint32_t sKV = base + 2 * kTcTileBytes;
+  // [O staging tile 0 | O staging tile 1 | (K,V) x stages]
+  const uint32_t sKV = base + 2 * kTcOutBytes;
 
   const int bh = blockIdx.y;
   const int b = bh / p.heads, h = bh - b * p.heads;
   const int q0 = blockIdx.x * 2 * kTcBM;
 
   if (warp == 0 && lane == 0) {
-    tma_prefetch_desc(&tmQ);
     tma_prefetch_desc(&tmK);
     tma_prefetch_desc(&tmV);
     tma_prefetch_desc(&tmO);
     for (int t = 0; t < 2; ++t) {
-      mbar_init(&bar_q[t], 1);
-      mbar_init(&bar_s_full[t], 1);
-      mbar_init(&bar_p_full[t], 4);
-      mbar_init(&bar_o_full[t], 1);
+      mbar_init(&bars.q_full[t], 4);
+      mbar_init(&bars.o_full[t], 1);
+      for (int i = 0; i < 2; ++i) {
+        mbar_init(&bars.s_full[t][i], 1);
+        mbar_init(&bars.p_full[t][i], 4);
+      }
     }
     for (int s = 0; s < kTcStages; ++s) {
-      mbar_init(&bar_k_full[s], 1);
-      mbar_init(&bar_v_full[s], 1);
-      mbar_init(&bar_kv_empty[s], 1);
+      mbar_init(&bars.kv_full[s], 1);
+      mbar_init(&bars.kv_empty[s], 1);
     }
     mbar_fence_init();
   }
@@ -101,19 +109,14 @@ attn_spatial_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
   if (warp == 0) {
     // ===================== TMA producer =====================
     if (lane == 0) {
-      for (int t = 0; t < 2; ++t) {
-        mbar_arrive_expect_tx(&bar_q[t], kTcTileBytes);
-        tma_load_3d(base_ptr + t * kTcTileBytes, &tmQ, &bar_q[t], h * 64, q0 + t * kTcBM, b);
-      }
       int s = 0;
       uint32_t ph = 0;
       for (int j = 0; j < p.n_kv; ++j) {
-        mbar_wait(&bar_kv_empty[s], ph ^ 1);
-        uint8_t* kdst = base_ptr + 2 * kTcTileBytes + s * 2 * kTcTileBytes;
-        mbar_arrive_expect_tx(&bar_k_full[s], kTcTileBytes);
-        tma_load_3d(kdst, &tmK, &bar_k_full[s], h * 64, j * kTcBN, b);
-        mbar_arrive_expect_tx(&bar_v_full[s], kTcTileBytes);
-        tma_load_3d(kdst + kTcTileBytes, &tmV, &bar_v_full[s], h * 64, j * kTcBN, b);
+        mbar_wait(&bars.kv_empty[s], ph ^ 1);
+        uint8_t* kdst = base_ptr + 2 * kTcOutBytes + s * kTcStageBytes;
+        mbar_arrive_expect_tx(&bars.kv_full[s], kTcStageBytes);
+        tma_load_3d(kdst, &tmK, &bars.kv_full[s], h * 64, j * kTcBN, b);
+        tma_load_3d(kdst + kTcKBytes, &tmV, &bars.kv_full[s], h * 64, j * kTcBN, b);
         if (++s == kTcStages) {
           s = 0;
           ph ^= 1;
@@ -122,71 +125,72 @@ attn_spatial_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
     }
   } else if (warp == 1) {
     // ===================== MMA issuer =====================
-    if (lane == 0) {
-      const uint32_t idesc_qk = umma_idesc_bf16(kTcBM, kTcBN, 0, 0);
-      const uint32_t idesc_pv = umma_idesc_bf16(kTcBM, 64, 0, 1);  // B = V is MN-major ([keys][d])
-      auto issue_qk = [&](int t, int s) {
-        const uint32_t a_addr = sQ + t * kTcTileBytes;
-        const uint32_t b_addr = sKV + s * 2 * kTcTileBytes;
+    // The whole warp walks the loop (convergent control flow keeps every descriptor in uniform
+    // registers); only the elected lane's tcgen05 instructions are enabled.
+    const uint32_t leader = elect_one() ? 1u : 0u;
+    // 512 columns = the whole tensor memory of the SM, so the allocation can only start at column 0;
+    // using the literal keeps the TMEM operands compile-time uniform.
+    if (tmem_base != 0u) __trap();
+    const uint32_t idesc_qk = umma_idesc_bf16(kTcBM, kTcBN, 0, 0);
+    const uint32_t idesc_pv = umma_idesc_bf16(kTcBM, 64, 0, 1);  // B = V is MN-major ([keys][d])
+    auto issue_qk = [&](int t, int s, int j) {
+      const uint32_t k_addr = sKV + s * kTcStageBytes;
+      const uint32_t tile = t * kColTile;
 #pragma unroll
-        for (int kk = 0; kk < 4; ++kk) {
-          const uint64_t ad = umma_smem_desc(a_addr + kk * 32, 16, 1024, kUmmaLayoutSw128);
-          const uint64_t bd = umma_smem_desc(b_addr + kk * 32, 16, 1024, kUmmaLayoutSw128);
-          umma_bf16_ss(tmem_base + kColS + t * 128, ad, bd, idesc_qk, kk != 0 ? 1u : 0u);
-        }
-        umma_commit(&bar_s_full[t]);
-      };
-      auto issue_pv = [&](int t, int s, int j) {
-        const uint32_t v_addr = sKV + s * 2 * kTcTileBytes + kTcTileBytes;
+      for (int kk = 0; kk < 4; ++kk) {
+        const uint64_t bd = umma_smem_desc(k_addr + kk * 32, 16, 1024, kUmmaLayoutSw128);
+        umma_bf16_ts_pred(tile + kColS + (j & 1) * 64, tile + kColQ + kk * 8, bd, idesc_qk, kk != 0 ? 1u : 0u, leader);
+      }
+      umma_commit_pred(&bars.s_full[t][j & 1], leader);
+    };
+    auto issue_pv = [&](int t, int s, int j) {
+      const uint32_t v_addr = sKV + s * kTcStageBytes + kTcKBytes;
+      const uint32_t tile = t * kColTile;
 #pragma unroll
-        for (int kk = 0; kk < 8; ++kk) {
-          // 16 keys per MMA = two 8-row groups of 128-byte rows (SBO = 1024 B); one 64-wide N atom
-          const uint64_t bd = umma_smem_desc(v_addr + kk * 2048, 1024, 1024, kUmmaLayoutSw128);
-          umma_bf16_ts(tmem_base + kColO + t * 64, tmem_base + kColP + t * 64 + kk * 8, bd, idesc_pv,
-                       (j | kk) != 0 ? 1u : 0u);
-        }
-        umma_commit(&bar_o_full[t]);
-      };
-      mbar_wait(&bar_k_full[0], 0);
-      mbar_wait(&bar_q[0], 0);
-      tc_fence_after();
-      issue_qk(0, 0);
-      mbar_wait(&bar_q[1], 0);
-      tc_fence_after();
-      issue_qk(1, 0);
-      int s = 0;
-      uint32_t ph = 0;
-      for (int j = 0; j < p.n_kv; ++j) {
-        int sn = s + 1;
-        uint32_t phn = ph;
-        if (sn == kTcStages) {
-          sn = 0;
-          phn ^= 1;
-        }
-        const bool more = (j + 1) < p.n_kv;
-        mbar_wait(&bar_v_full[s], ph);
-        mbar_wait(&bar_p_full[0], j & 1);
+      for (int kk = 0; kk < 4; ++kk) {
+        // 16 keys per MMA = two 8-row groups of 128-byte rows (SBO = 1024 B); one 64-wide N atom
+        const uint64_t bd = umma_smem_desc(v_addr + kk * 2048, 1024, 1024, kUmmaLayoutSw128);
+        umma_bf16_ts_pred(tile + kColO, tile + kColS + (j & 1) * 64 + kk * 8, bd, idesc_pv, (j | kk) != 0 ? 1u : 0u,
+                          leader);
+      }
+      umma_commit_pred(&bars.o_full[t], leader);
+    };
+    mbar_wait(&bars.q_full[0], 0);
+    mbar_wait(&bars.q_full[1], 0);
+    tc_fence_after();
+    int s = 0, sp = 0;  // stage of step j, stage of step j-1
+    uint32_t ph = 0;
+    for (int j = 0; j <= p.n_kv; ++j) {
+      if (j < p.n_kv) {
+        mbar_wait(&bars.kv_full[s], ph);
         tc_fence_after();
-        issue_pv(0, s, j);
-        if (more) {
-          mbar_wait(&bar_k_full[sn], phn);
-          tc_fence_after();
-          issue_qk(0, sn);
-        }
-        mbar_wait(&bar_p_full[1], j & 1);
+        // S[j&1] last held P_{j-2}, read by PV_{j-2}: issued earlier, and MMAs complete in order
+        issue_qk(0, s, j);
+        issue_qk(1, s, j);
+      }
+      if (j >= 1) {
+        const int jj = j - 1;
+        const uint32_t par = (uint32_t)(jj >> 1) & 1u;
+        mbar_wait(&bars.p_full[0][jj & 1], par);
         tc_fence_after();
-        issue_pv(1, s, j);
-        umma_commit(&bar_kv_empty[s]);  // K_j and V_j fully consumed by both tiles
-        if (more) issue_qk(1, sn);
-        s = sn;
-        ph = phn;
+        issue_pv(0, sp, jj);
+        mbar_wait(&bars.p_full[1][jj & 1], par);
+        tc_fence_after();
+        issue_pv(1, sp, jj);
+        umma_commit_pred(&bars.kv_empty[sp], leader);  // K_jj and V_jj fully consumed by both tiles
+      }
+      sp = s;
+      if (++s == kTcStages) {
+        s = 0;
+        ph ^= 1;
       }
     }
+    __syncwarp();
   } else {
     // ===================== softmax + epilogue (warps 2..9) =====================
     const int t = (warp - 2) >> 2;
-    tc_softmax_role(p, tmem_base, t, warp, lane, b, h, q0 + t * kTcBM, base_ptr + t * kTcTileBytes, &bar_s_full[t],
-                    &bar_p_full[t], &bar_o_full[t], &tmO);
+    tc_softmax_role(p, tmem_base + t * kColTile, warp, lane, b, h, q0 + t * kTcBM, base_ptr + t * kTcOutBytes,
+                    &bars.q_full[t], bars.s_full[t], bars.p_full[t], &bars.o_full[t], &tmO);
   }
 
   tc_fence_before();
