@@ -61,6 +61,7 @@ struct TcBarriers {
 
 #include "attn_spatial_tc_softmax.cuh"
 
+template <uint32_t kPolyMask>
 __global__ void __launch_bounds__(kTcThreads, 1)
 attn_spatial_tc_kernel(const __grid_constant__ CUtensorMap tmK, const __grid_constant__ CUtensorMap tmV,
                        const __grid_constant__ CUtensorMap tmO, const TcParams p) {
@@ -189,7 +190,7 @@ attn_spatial_tc_kernel(const __grid_constant__ CUtensorMap tmK, const __grid_con
   } else {
     // ===================== softmax + epilogue (warps 2..9) =====================
     const int t = (warp - 2) >> 2;
-    tc_softmax_role(p, tmem_base + t * kColTile, warp, lane, b, h, q0 + t * kTcBM, base_ptr + t * kTcOutBytes,
+    tc_softmax_role<kPolyMask>(p, tmem_base + t * kColTile, warp, lane, b, h, q0 + t * kTcBM, base_ptr + t * kTcOutBytes,
                     &bars.q_full[t], bars.s_full[t], bars.p_full[t], &bars.o_full[t], &tmO);
   }
 

@@ -3,6 +3,30 @@
 // This is the softmax of src/models/attention_processor.py:598-615 (softmax over keys of
 // scale * QK^T) evaluated 64 keys at a time against a per-row reference maximum.
 
+// 2^x for a pair of fp32 values on the FMA / ALU pipes instead of the 16-per-clock MUFU unit:
+// n = round(x) through the 1.5*2^23 magic constant, f = x - n in [-0.5, 0.5], a cubic minimax
+// polynomial for 2^f (relative error 7.6e-5, far below the bf16 rounding of P) and n added
+// straight into the exponent field.  x is clamped at -125 (2^-125 instead of an underflowed 0).
+__device__ __forceinline__ uint64_t exp2_poly_x2(uint64_t x) {
+  float x0, x1;
+  f32x2_unpack(x, x0, x1);
+  const uint64_t xc = f32x2_pack(fmaxf(x0, -125.f), fmaxf(x1, -125.f));
+  const uint64_t t = f32x2_add(xc, f32x2_pack(12582912.f, 12582912.f));
+  const uint64_t n = f32x2_add(t, f32x2_pack(-12582912.f, -12582912.f));
+  const uint64_t f = f32x2_fma(n, f32x2_pack(-1.f, -1.f), xc);
+  uint64_t pl = f32x2_fma(f32x2_pack(0.05520550534f, 0.05520550534f), f, f32x2_pack(0.24261397123f, 0.24261397123f));
+  pl = f32x2_fma(pl, f, f32x2_pack(0.69325476885f, 0.69325476885f));
+  pl = f32x2_fma(pl, f, f32x2_pack(0.99992769957f, 0.99992769957f));
+  float t0, t1, p0, p1;
+  f32x2_unpack(t, t0, t1);
+  f32x2_unpack(pl, p0, p1);
+  const float r0 = __int_as_float((__float_as_int(t0) << 23) + __float_as_int(p0));
+  const float r1 = __int_as_float((__float_as_int(t1) << 23) + __float_as_int(p1));
+  return f32x2_pack(r0, r1);
+}
+
+// kPolyMask: bit i set = pair i (mod 8) of every 16 consecutive scores takes the polynomial path.
+template <uint32_t kPolyMask>
 __device__ __forceinline__ void tc_softmax_role(const TcParams& p, uint32_t tile_tmem, int warp, int lane, int b, int h,
                                                 int q_row0, uint8_t* stage_ptr, uint64_t* bar_q, uint64_t* bar_s,
                                                 uint64_t* bar_p, uint64_t* bar_o, const CUtensorMap* tmO) {
@@ -95,17 +119,29 @@ __device__ __forceinline__ void tc_softmax_role(const TcParams& p, uint32_t tile
     auto exp_pack = [&](const uint32_t* x, uint32_t* out) {
 #pragma unroll
       for (int c = 0; c < 32; c += 4) {
-        const uint64_t xa = f32x2_fma(f32x2_pack(__uint_as_float(x[c]), __uint_as_float(x[c + 1])), sl2x2, negx2);
-        const uint64_t xb = f32x2_fma(f32x2_pack(__uint_as_float(x[c + 2]), __uint_as_float(x[c + 3])), sl2x2, negx2);
+        uint64_t xa = f32x2_fma(f32x2_pack(__uint_as_float(x[c]), __uint_as_float(x[c + 1])), sl2x2, negx2);
+        uint64_t xb = f32x2_fma(f32x2_pack(__uint_as_float(x[c + 2]), __uint_as_float(x[c + 3])), sl2x2, negx2);
         float a0, a1, b0, b1;
-        f32x2_unpack(xa, a0, a1);
-        f32x2_unpack(xb, b0, b1);
-        a0 = fast_exp2(a0);
-        a1 = fast_exp2(a1);
-        b0 = fast_exp2(b0);
-        b1 = fast_exp2(b1);
-        sum_a = f32x2_add(sum_a, f32x2_pack(a0, a1));
-        sum_b = f32x2_add(sum_b, f32x2_pack(b0, b1));
+        if ((kPolyMask >> ((c >> 1) & 7)) & 1u) {
+          xa = exp2_poly_x2(xa);
+          f32x2_unpack(xa, a0, a1);
+        } else {
+          f32x2_unpack(xa, a0, a1);
+          a0 = fast_exp2(a0);
+          a1 = fast_exp2(a1);
+          xa = f32x2_pack(a0, a1);
+        }
+        if ((kPolyMask >> (((c >> 1) + 1) & 7)) & 1u) {
+          xb = exp2_poly_x2(xb);
+          f32x2_unpack(xb, b0, b1);
+        } else {
+          f32x2_unpack(xb, b0, b1);
+          b0 = fast_exp2(b0);
+          b1 = fast_exp2(b1);
+          xb = f32x2_pack(b0, b1);
+        }
+        sum_a = f32x2_add(sum_a, xa);
+        sum_b = f32x2_add(sum_b, xb);
         out[c >> 1] = pack_bf16x2(a0, a1);
         out[(c >> 1) + 1] = pack_bf16x2(b0, b1);
       }
@@ -128,6 +164,9 @@ __device__ __forceinline__ void tc_softmax_role(const TcParams& p, uint32_t tile
   }
 
   // ---- epilogue: O / l -> bf16 -> swizzled staging -> TMA store ------------------------------------
+  // PV of the last TWO steps may still be in flight (S of the last step only proves PV_{n-3}): wait
+  // for phase n-2 first, otherwise the parity of phase n-1 aliases the long-finished phase n-3.
+  if (p.n_kv >= 2) mbar_wait(bar_o, (uint32_t)(p.n_kv - 2) & 1u);
   mbar_wait(bar_o, (uint32_t)(p.n_kv - 1) & 1u);
   tc_fence_after();
   const float inv = 1.f / l;
