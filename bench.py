@@ -331,7 +331,7 @@ def main():
                     "ms_per_step": ms_e2e / args.steps},
             "gpu_launches": launches,
             "clocks": clocks,
-            "roofline": {"kernel": "attn_spatial_kernel", "bound": "tensor", "achieved": achieved, "peak": pk["tf_sust"],
+            "roofline": {"kernel": "attn_spatial_tc_kernel", "bound": "tensor", "achieved": achieved, "peak": pk["tf_sust"],
                          "unit": "TFLOP/s", "frac": achieved / pk["tf_sust"], "traffic": None, "peak_source": pk["src"] + " (sustained)",
                          "ms_per_launch": dom_avg_ms, "share_of_step": dom_avg_ms / (ms_total / args.steps),
                          "algorithmic_flops_per_launch": fl["spatial_core"]},

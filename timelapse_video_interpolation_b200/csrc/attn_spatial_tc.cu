@@ -5,18 +5,22 @@
 // (src/models/attention_processor.py:1243, :1156; caller src/models/attention.py:276-281).
 //
 // One CTA owns 256 query rows (two 128-row tiles) of one (frame, head) and streams the keys in
-// steps of 64.  320 threads, warp-specialised:
+// steps of 64.  352 threads, warp-specialised:
 //   warp 0        TMA producer: K_j / V_j ([64 keys x 64] each) into an 8-stage smem ring
 //                 (3-D tensor maps [heads*64, Skv, batch]: sequence tails are zero-filled).
-//   warp 1        tcgen05.mma issuer (one lane).  Both products take their A operand from tensor
-//                 memory, so shared memory only feeds the 64-wide B operands:
+//   warps 1, 10   tcgen05.mma issuers, one per tile (the whole warp walks the loop so descriptors stay
+//                 in uniform registers; one elected lane's instructions are enabled).  Both products
+//                 take their A operand from tensor memory, so shared memory only feeds the 64-wide B
+//                 operands:
 //                     S_t[j&1] = Q_t K_j^T      (M=128 N=64 K=64, A = Q_t in TMEM, B = K_j K-major)
 //                     O_t     += P_t[j&1] V_j   (M=128 N=64 K=64, A = P in TMEM, B = V_j MN-major)
-//                 issued as  QK0_j QK1_j PV0_{j-1} PV1_{j-1}: the scores of step j are produced while
-//                 the softmax warps are still working on step j-1 (S is double-buffered per tile).
+//                 issued per tile as  QK_j PV_{j-1}: the scores of step j are produced while the
+//                 softmax warps are still working on step j-1 (S is double-buffered per tile), and
+//                 the two tiles only meet at the K/V ring (a stage is freed by both tiles' commits).
 //   warps 2..5    softmax of tile 0, warps 6..9 softmax of tile 1: one thread per query row
 //                 (TMEM lane).  The thread first parks its Q row in TMEM, then per step reads its 64
-//                 scores with tcgen05.ld, does the fp32 online softmax (FMNMX3 / FFMA2 / ex2 / FADD2)
+//                 scores with tcgen05.ld, does the fp32 online softmax (FMNMX3 / FFMA2 / FADD2; ex2 on
+//                 the MUFU unit for 3 of 4 score pairs, a cubic polynomial on the FMA pipe for the rest)
 //                 and writes P as bf16 over the first half of the same S buffer with tcgen05.st.
 //                 The reference maximum only moves when the row maximum outgrows it by 2^8 (P stays
 //                 <= 256, exact in O / l), so the O accumulator in TMEM is rescaled rarely, by the
@@ -30,7 +34,7 @@
 namespace tvi {
 namespace {
 
-constexpr int kTcThreads = 320;
+constexpr int kTcThreads = 352;
 constexpr int kTcBM = 128;      // query rows per tile (UMMA M)
 constexpr int kTcBN = 64;       // keys per step (UMMA N of QK^T, K of PV)
 constexpr int kTcStages = 8;
@@ -94,7 +98,7 @@ attn_spatial_tc_kernel(const __grid_constant__ CUtensorMap tmK, const __grid_con
     }
     for (int s = 0; s < kTcStages; ++s) {
       mbar_init(&bars.kv_full[s], 1);
-      mbar_init(&bars.kv_empty[s], 1);
+      mbar_init(&bars.kv_empty[s], 2);
     }
     mbar_fence_init();
   }
@@ -124,14 +128,14 @@ attn_spatial_tc_kernel(const __grid_constant__ CUtensorMap tmK, const __grid_con
         }
       }
     }
-  } else if (warp == 1) {
-    // ===================== MMA issuer =====================
+  } else if (warp == 1 || warp == 10) {
+    // ===================== MMA issuers =====================
     // The whole warp walks the loop (convergent control flow keeps every descriptor in uniform
     // registers); only the elected lane's tcgen05 instructions are enabled.
     const uint32_t leader = elect_one() ? 1u : 0u;
     // 512 columns = the whole tensor memory of the SM, so the allocation can only start at column 0;
     // using the literal keeps the TMEM operands compile-time uniform.
-    if (tmem_base != 0u) __trap();
+    if (tmem_base != 0u) __trap();  // (both issuing warps check)
     const uint32_t idesc_qk = umma_idesc_bf16(kTcBM, kTcBN, 0, 0);
     const uint32_t idesc_pv = umma_idesc_bf16(kTcBM, 64, 0, 1);  // B = V is MN-major ([keys][d])
     auto issue_qk = [&](int t, int s, int j) {
@@ -156,8 +160,11 @@ attn_spatial_tc_kernel(const __grid_constant__ CUtensorMap tmK, const __grid_con
       }
       umma_commit_pred(&bars.o_full[t], leader);
     };
-    mbar_wait(&bars.q_full[0], 0);
-    mbar_wait(&bars.q_full[1], 0);
+    // One issuing warp per tile (warp 1 -> tile 0, warp 10 -> tile 1), each blocking only on its own
+    // tile's barriers: neither tile's softmax is gated by the other tile's progress until the 8-stage
+    // K/V ring runs out, so their exp phases can drift apart instead of colliding on the MUFU unit.
+    const int t = (warp == 1) ? 0 : 1;
+    mbar_wait(&bars.q_full[t], 0);
     tc_fence_after();
     int s = 0, sp = 0;  // stage of step j, stage of step j-1
     uint32_t ph = 0;
@@ -165,20 +172,15 @@ attn_spatial_tc_kernel(const __grid_constant__ CUtensorMap tmK, const __grid_con
       if (j < p.n_kv) {
         mbar_wait(&bars.kv_full[s], ph);
         tc_fence_after();
-        // S[j&1] last held P_{j-2}, read by PV_{j-2}: issued earlier, and MMAs complete in order
-        issue_qk(0, s, j);
-        issue_qk(1, s, j);
+        // S[j&1] last held P_{j-2}, read by PV_t(j-2): issued earlier by this thread, MMAs complete in order
+        issue_qk(t, s, j);
       }
       if (j >= 1) {
         const int jj = j - 1;
-        const uint32_t par = (uint32_t)(jj >> 1) & 1u;
-        mbar_wait(&bars.p_full[0][jj & 1], par);
+        mbar_wait(&bars.p_full[t][jj & 1], (uint32_t)(jj >> 1) & 1u);
         tc_fence_after();
-        issue_pv(0, sp, jj);
-        mbar_wait(&bars.p_full[1][jj & 1], par);
-        tc_fence_after();
-        issue_pv(1, sp, jj);
-        umma_commit_pred(&bars.kv_empty[sp], leader);  // K_jj and V_jj fully consumed by both tiles
+        issue_pv(t, sp, jj);
+        umma_commit_pred(&bars.kv_empty[sp], leader);  // this tile is done with K_jj / V_jj (2 arrivals free the stage)
       }
       sp = s;
       if (++s == kTcStages) {

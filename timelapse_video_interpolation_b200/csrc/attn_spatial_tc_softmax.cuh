@@ -25,6 +25,11 @@ __device__ __forceinline__ uint64_t exp2_poly_x2(uint64_t x) {
   return f32x2_pack(r0, r1);
 }
 
+template <bool B>
+struct TcTag {
+  static constexpr bool value = B;
+};
+
 // kPolyMask: bit i set = pair i (mod 8) of every 16 consecutive scores takes the polynomial path.
 template <uint32_t kPolyMask>
 __device__ __forceinline__ void tc_softmax_role(const TcParams& p, uint32_t tile_tmem, int warp, int lane, int b, int h,
@@ -67,15 +72,19 @@ __device__ __forceinline__ void tc_softmax_role(const TcParams& p, uint32_t tile
   float m_ref = -INFINITY;  // reference maximum of this row, in raw (unscaled) logit units
   float l = 0.f;            // running sum of exp2((s - m_ref) * sl2)
 
-  for (int j = 0; j < p.n_kv; ++j) {
+  uint32_t ra[32], rb[32];  // the 64 scores of the current step
+  mbar_wait(&bar_s[0], 0);
+  tc_fence_after();
+  tmem_ld_x32(tS, ra);
+  tmem_ld_x32(tS + 32, rb);
+
+  // One key step.  kRagged is only true for a last step that runs past Skv (peeled so that the
+  // 64 compare/selects of the mask stay out of the steady-state loop).
+  auto step = [&](int j, auto ragged_tag) {
+    constexpr bool kRagged = decltype(ragged_tag)::value;
     const int buf = j & 1;
-    mbar_wait(&bar_s[buf], (uint32_t)(j >> 1) & 1u);
-    tc_fence_after();
-    uint32_t ra[32], rb[32];
-    tmem_ld_x32(tS + buf * 64, ra);
-    tmem_ld_x32(tS + buf * 64 + 32, rb);
     tmem_ld_wait();
-    if (j == p.n_kv - 1 && (p.Skv & (kTcBN - 1)) != 0) {  // ragged last key step
+    if (kRagged) {
       const int valid = p.Skv - j * kTcBN;
 #pragma unroll
       for (int c = 0; c < 32; ++c) {
@@ -157,11 +166,23 @@ __device__ __forceinline__ void tc_softmax_role(const TcParams& p, uint32_t tile
       f32x2_unpack(sum_b, s2, s3);
       l += (s0 + s1) + (s2 + s3);
     }
+    // the next step's scores (other S buffer, normally long finished) travel to registers while the
+    // P store drains
+    if (j + 1 < p.n_kv) {
+      mbar_wait(&bar_s[buf ^ 1], (uint32_t)((j + 1) >> 1) & 1u);
+      tc_fence_after();
+      tmem_ld_x32(tS + (buf ^ 1) * 64, ra);
+      tmem_ld_x32(tS + (buf ^ 1) * 64 + 32, rb);
+    }
     tmem_st_wait();
     tc_fence_before();
     __syncwarp();
     if (lane == 0) mbar_arrive(&bar_p[buf]);
-  }
+  };
+  const bool last_ragged = (p.Skv & (kTcBN - 1)) != 0;
+  for (int j = 0; j < p.n_kv - 1; ++j) step(j, TcTag<false>{});
+  if (last_ragged) step(p.n_kv - 1, TcTag<true>{});
+  else step(p.n_kv - 1, TcTag<false>{});
 
   // ---- epilogue: O / l -> bf16 -> swizzled staging -> TMA store ------------------------------------
   // PV of the last TWO steps may still be in flight (S of the last step only proves PV_{n-3}): wait
