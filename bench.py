@@ -304,11 +304,10 @@ def main():
         barrier()
         ms_e2e = f0.elapsed_time(f1)
 
-    t = torch.tensor([ms_total, ms_e2e], dtype=torch.float64, device=dev)
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms_total, ms_e2e = float(t[0]), float(t[1])
-    frames_per_step = args.clips * T_FRAMES * world
+    from timelapse_video_interpolation_b200 import sharding
+    ms_total, ms_e2e = sharding.max_over_ranks(ms_total, dev), sharding.max_over_ranks(ms_e2e, dev)
+    # every rank owns `--clips` whole clips (weak scaling); the job's units are the sum over ranks
+    frames_per_step = int(sharding.sum_over_ranks(args.clips * T_FRAMES, dev))
     value = frames_per_step * args.steps / (ms_total * 1e-3)
     e2e_value = frames_per_step * args.steps / (ms_e2e * 1e-3)
 

@@ -106,40 +106,43 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_consta
     }
   } else if (warp == 1) {
     // ===================== MMA issuer =====================
-    if (lane == 0) {
-      const uint32_t idesc = umma_idesc_bf16(kBM, (uint32_t)p.BN, 0, 0);
-      int s = 0;
-      uint32_t ph = 0;
-      int as = 0;
-      uint32_t aph = 0;
-      for (int64_t tile = blockIdx.x; tile < n_tiles_total; tile += gridDim.x) {
-        mbar_wait(&bar_acc_empty[as], aph ^ 1);
+    // The whole warp walks the loop (convergent control flow keeps the descriptors in uniform
+    // registers); only the elected lane's tcgen05 instructions are enabled.  Issuing from inside
+    // `if (lane == 0)` makes nvcc wrap every MMA in an ELECT / BRA.U.ANY loop (~75 cycles each).
+    const uint32_t leader = elect_one() ? 1u : 0u;
+    const uint32_t idesc = umma_idesc_bf16(kBM, (uint32_t)p.BN, 0, 0);
+    int s = 0;
+    uint32_t ph = 0;
+    int as = 0;
+    uint32_t aph = 0;
+    for (int64_t tile = blockIdx.x; tile < n_tiles_total; tile += gridDim.x) {
+      mbar_wait(&bar_acc_empty[as], aph ^ 1);
+      tc_fence_after();
+      const uint32_t d_tmem = tmem_base + as * kAccStride;
+      for (int kb = 0; kb < p.k_blocks; ++kb) {
+        mbar_wait(&bar_full[s], ph);
         tc_fence_after();
-        const uint32_t d_tmem = tmem_base + as * kAccStride;
-        for (int kb = 0; kb < p.k_blocks; ++kb) {
-          mbar_wait(&bar_full[s], ph);
-          tc_fence_after();
-          const uint32_t a_addr = base + s * stage_bytes;
-          const uint32_t b_addr = a_addr + kABytes;
+        const uint32_t a_addr = base + s * stage_bytes;
+        const uint32_t b_addr = a_addr + kABytes;
 #pragma unroll
-          for (int kk = 0; kk < kBK / 16; ++kk) {
-            const uint64_t ad = umma_smem_desc(a_addr + kk * 32, 16, 1024, kUmmaLayoutSw128);
-            const uint64_t bd = umma_smem_desc(b_addr + kk * 32, 16, 1024, kUmmaLayoutSw128);
-            umma_bf16_ss(d_tmem, ad, bd, idesc, (kb | kk) != 0 ? 1u : 0u);
-          }
-          umma_commit(&bar_empty[s]);  // frees the smem stage once these MMAs have read it
-          if (++s == p.stages) {
-            s = 0;
-            ph ^= 1;
-          }
+        for (int kk = 0; kk < kBK / 16; ++kk) {
+          const uint64_t ad = umma_smem_desc(a_addr + kk * 32, 16, 1024, kUmmaLayoutSw128);
+          const uint64_t bd = umma_smem_desc(b_addr + kk * 32, 16, 1024, kUmmaLayoutSw128);
+          umma_bf16_ss_pred(d_tmem, ad, bd, idesc, (kb | kk) != 0 ? 1u : 0u, leader);
         }
-        umma_commit(&bar_acc_full[as]);  // accumulator complete -> epilogue
-        if (++as == 2) {
-          as = 0;
-          aph ^= 1;
+        umma_commit_pred(&bar_empty[s], leader);  // frees the smem stage once these MMAs have read it
+        if (++s == p.stages) {
+          s = 0;
+          ph ^= 1;
         }
       }
+      umma_commit_pred(&bar_acc_full[as], leader);  // accumulator complete -> epilogue
+      if (++as == 2) {
+        as = 0;
+        aph ^= 1;
+      }
     }
+    __syncwarp();
   } else {
     // ===================== epilogue (warps 2..5) =====================
     const int quad = warp & 3;  // TMEM lane quadrant this warp may read
