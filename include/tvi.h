@@ -84,6 +84,24 @@ int tvi_backward_warp_f32(const float* img2, const float* f_fwd, const float* f_
 int tvi_gemm_bf16_tn(const tvi_bf16* X, const tvi_bf16* W, const tvi_bf16* bias, tvi_bf16* Y, int64_t M, int N,
                      int K, int64_t ldx, int64_t ldw, int64_t ldy, void* stream);
 
+/* Backward of the projections (training config 5: src/train_decouples.py back-propagates through the
+ * same nn.Linear call sites; autograd's F.linear backward = two cuBLAS GEMMs + a bias column sum).
+ *   dgrad : dX[M,K] = dY[M,N] . W[N,K]          (W consumed in place, MN-major tcgen05 operand)
+ *   wgrad : dW[N,K] = dY[M,N]^T . X[M,K]        (token reduction split across CTAs; fp32 partials in
+ *           `workspace` = tvi_gemm_bf16_wgrad_workspace_bytes(M,N,K) bytes, summed in a fixed order)
+ *   colsum: out[g, c] = sum over the rows_per_group rows of group g of x[row, c]  (bias gradient with
+ *           one group; also the backward of the one-key cross-attention broadcast).  fp32 accumulation,
+ *           `workspace` = tvi_colsum_bf16_workspace_bytes(nrows, rows_per_group, C) bytes.
+ */
+int tvi_gemm_bf16_dgrad(const tvi_bf16* dY, const tvi_bf16* W, tvi_bf16* dX, int64_t M, int N, int K, int64_t lddy,
+                        int64_t ldw, int64_t lddx, void* stream);
+size_t tvi_gemm_bf16_wgrad_workspace_bytes(int64_t M, int N, int K);
+int tvi_gemm_bf16_wgrad(const tvi_bf16* dY, const tvi_bf16* X, tvi_bf16* dW, void* workspace, int64_t M, int N, int K,
+                        int64_t lddy, int64_t ldx, int64_t lddw, void* stream);
+size_t tvi_colsum_bf16_workspace_bytes(int64_t nrows, int64_t rows_per_group, int C);
+int tvi_colsum_bf16(const tvi_bf16* x, tvi_bf16* out, void* workspace, int64_t nrows, int64_t rows_per_group, int C,
+                    int64_t ldx, int64_t ldo, void* stream);
+
 /* ---------------------------------------------------------------------------------------------
  * A3c  short-sequence (temporal) attention core: nseq independent sequences, every head,
  * O = softmax(scale . Q K^T) V with fp32 softmax.  Sequence s owns query rows [s*Tq, (s+1)*Tq)

@@ -38,6 +38,11 @@ SIGNATURES = {
     "tvi_flow_cosine_f32": (_i32, [_ptr, _ptr, _ptr, _ptr, _i64, _i32, _i32, _i32, _ptr]),
     "tvi_backward_warp_f32": (_i32, [_ptr, _ptr, _ptr, _ptr, _ptr, _i64, _i32, _i32, _i32, _f32, _f32, _ptr]),
     "tvi_gemm_bf16_tn": (_i32, [_ptr, _ptr, _ptr, _ptr, _i64, _i32, _i32, _i64, _i64, _i64, _ptr]),
+    "tvi_gemm_bf16_dgrad": (_i32, [_ptr, _ptr, _ptr, _i64, _i32, _i32, _i64, _i64, _i64, _ptr]),
+    "tvi_gemm_bf16_wgrad_workspace_bytes": (_sz, [_i64, _i32, _i32]),
+    "tvi_gemm_bf16_wgrad": (_i32, [_ptr, _ptr, _ptr, _ptr, _i64, _i32, _i32, _i64, _i64, _i64, _ptr]),
+    "tvi_colsum_bf16_workspace_bytes": (_sz, [_i64, _i64, _i32]),
+    "tvi_colsum_bf16": (_i32, [_ptr, _ptr, _ptr, _i64, _i64, _i32, _i64, _i64, _ptr]),
     "tvi_attn_temporal_fwd": (_i32, [_ptr, _ptr, _ptr, _ptr, _ptr, _i64, _i32, _i32, _i32, _i32,
                                      _i64, _i64, _i64, _i64, _f32, _ptr]),
     "tvi_attn_fewkeys_fwd": (_i32, [_ptr, _ptr, _ptr, _ptr, _i64, _i64, _i32, _i32, _i32,

@@ -14,6 +14,14 @@
 // Tiles are walked N-fastest so the CTAs resident at one time share X rows through L2.
 // At the SVD shapes K is only 320..1280, so per tile the 128 x K read and 128 x BN write dominate:
 // the projections sit at or below the HBM/tensor ridge and one-CTA MMA is enough.
+//
+// The same kernel, with MN-major operand descriptors, is the backward of nn.Linear (training
+// config 5, what autograd derives from F.linear at the same call sites):
+//   kBMn          dX[M,K] = dY[M,N] . W[N,K]      W is consumed in place as an MN-major B operand
+//                 (TMA boxes of [64 reduction rows][64 contiguous columns], SWIZZLE_128B).
+//   kAMn + kBMn   dW[N,K] = dY[M,N]^T . X[M,K]    both operands MN-major, the token reduction is split
+//   + kSplit      across CTAs, fp32 partial tiles go to a workspace and wgrad_reduce_kernel sums them
+//                 in a fixed order (deterministic) into bf16.
 #include "tvi_common.cuh"
 
 namespace tvi {
@@ -30,16 +38,23 @@ constexpr int kMaxStages = 8;
 struct GemmParams {
   int64_t m_tiles;
   int n_tiles;
-  int k_blocks;
+  int k_blocks;        // k-blocks per tile (per split when kSplit)
+  int k_blocks_total;  // k-blocks of the whole reduction
   int BN;
   int N;
   int stages;
   const tvi_bf16* bias;
+  float* partial;      // kSplit: [splits][M_out][ldp] fp32
+  int64_t M_out;
+  int64_t ldp;
 };
 
+// kAMn / kBMn: the A / B operand is stored reduction-row-major ("MN-major": the output dimension is the
+// contiguous one).  kSplit: tiles are (split, m, n); fp32 partials instead of the bf16 TMA-store epilogue.
+template <bool kAMn, bool kBMn, bool kSplit>
 __global__ void __launch_bounds__(kGemmThreads, 1)
-gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CUtensorMap tmW,
-                    const __grid_constant__ CUtensorMap tmY, const GemmParams p) {
+gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CUtensorMap tmW,
+                 const __grid_constant__ CUtensorMap tmY, const GemmParams p) {
   extern __shared__ uint8_t smem_raw[];
   __shared__ __align__(8) uint64_t bar_full[kMaxStages];
   __shared__ __align__(8) uint64_t bar_empty[kMaxStages];
@@ -80,7 +95,8 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_consta
   tc_fence_after();
   const uint32_t tmem_base = s_tmem_base;
 
-  const int64_t n_tiles_total = p.m_tiles * p.n_tiles;
+  const int64_t mn_tiles = p.m_tiles * p.n_tiles;
+  const int64_t n_tiles_total = kSplit ? mn_tiles * ((p.k_blocks_total + p.k_blocks - 1) / p.k_blocks) : mn_tiles;
 
   if (warp == 0) {
     // ===================== TMA producer =====================
@@ -88,15 +104,30 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_consta
       int s = 0;
       uint32_t ph = 0;
       for (int64_t tile = blockIdx.x; tile < n_tiles_total; tile += gridDim.x) {
-        const int64_t mt = tile / p.n_tiles;
-        const int nt = (int)(tile - mt * p.n_tiles);
+        const int64_t split = kSplit ? tile / mn_tiles : 0;
+        const int64_t mn = tile - split * mn_tiles;
+        const int64_t mt = mn / p.n_tiles;
+        const int nt = (int)(mn - mt * p.n_tiles);
         const int m0 = (int)(mt * kBM), n0 = nt * p.BN;
-        for (int kb = 0; kb < p.k_blocks; ++kb) {
+        const int kb_lo = (int)split * p.k_blocks;
+        const int kb_hi = min(kb_lo + p.k_blocks, p.k_blocks_total);
+        for (int kb = kb_lo; kb < kb_hi; ++kb) {
           mbar_wait(&bar_empty[s], ph ^ 1);
           mbar_arrive_expect_tx(&bar_full[s], stage_bytes);
           uint8_t* a_dst = base_ptr + s * stage_bytes;
-          tma_load_2d(a_dst, &tmX, &bar_full[s], kb * kBK, m0);
-          tma_load_2d(a_dst + kABytes, &tmW, &bar_full[s], kb * kBK, n0);
+          if (!kAMn) {
+            tma_load_2d(a_dst, &tmX, &bar_full[s], kb * kBK, m0);
+          } else {
+            // [64 reduction rows][64 output columns] boxes, one per 64-wide MN atom
+            tma_load_2d(a_dst, &tmX, &bar_full[s], m0, kb * kBK);
+            tma_load_2d(a_dst + 8192, &tmX, &bar_full[s], m0 + 64, kb * kBK);
+          }
+          if (!kBMn) {
+            tma_load_2d(a_dst + kABytes, &tmW, &bar_full[s], kb * kBK, n0);
+          } else {
+            for (int hb = 0; hb < p.BN / 64; ++hb)
+              tma_load_2d(a_dst + kABytes + hb * 8192, &tmW, &bar_full[s], n0 + hb * 64, kb * kBK);
+          }
           if (++s == p.stages) {
             s = 0;
             ph ^= 1;
@@ -110,7 +141,7 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_consta
     // registers); only the elected lane's tcgen05 instructions are enabled.  Issuing from inside
     // `if (lane == 0)` makes nvcc wrap every MMA in an ELECT / BRA.U.ANY loop (~75 cycles each).
     const uint32_t leader = elect_one() ? 1u : 0u;
-    const uint32_t idesc = umma_idesc_bf16(kBM, (uint32_t)p.BN, 0, 0);
+    const uint32_t idesc = umma_idesc_bf16(kBM, (uint32_t)p.BN, kAMn ? 1 : 0, kBMn ? 1 : 0);
     int s = 0;
     uint32_t ph = 0;
     int as = 0;
@@ -119,15 +150,22 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_consta
       mbar_wait(&bar_acc_empty[as], aph ^ 1);
       tc_fence_after();
       const uint32_t d_tmem = tmem_base + as * kAccStride;
-      for (int kb = 0; kb < p.k_blocks; ++kb) {
+      const int64_t split = kSplit ? tile / mn_tiles : 0;
+      const int kb_lo = (int)split * p.k_blocks;
+      const int kb_n = min(kb_lo + p.k_blocks, p.k_blocks_total) - kb_lo;
+      for (int kb = 0; kb < kb_n; ++kb) {
         mbar_wait(&bar_full[s], ph);
         tc_fence_after();
         const uint32_t a_addr = base + s * stage_bytes;
         const uint32_t b_addr = a_addr + kABytes;
 #pragma unroll
         for (int kk = 0; kk < kBK / 16; ++kk) {
-          const uint64_t ad = umma_smem_desc(a_addr + kk * 32, 16, 1024, kUmmaLayoutSw128);
-          const uint64_t bd = umma_smem_desc(b_addr + kk * 32, 16, 1024, kUmmaLayoutSw128);
+          // K-major: 16 reduction elements = 32 bytes along the swizzled 128-byte row.
+          // MN-major: 16 reduction rows = two 8-row groups of 1024 B; 64-wide MN atoms are 8192 B apart.
+          const uint64_t ad = kAMn ? umma_smem_desc(a_addr + kk * 2048, 8192, 1024, kUmmaLayoutSw128)
+                                   : umma_smem_desc(a_addr + kk * 32, 16, 1024, kUmmaLayoutSw128);
+          const uint64_t bd = kBMn ? umma_smem_desc(b_addr + kk * 2048, 8192, 1024, kUmmaLayoutSw128)
+                                   : umma_smem_desc(b_addr + kk * 32, 16, 1024, kUmmaLayoutSw128);
           umma_bf16_ss_pred(d_tmem, ad, bd, idesc, (kb | kk) != 0 ? 1u : 0u, leader);
         }
         umma_commit_pred(&bar_empty[s], leader);  // frees the smem stage once these MMAs have read it
@@ -153,8 +191,10 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_consta
     uint32_t aph = 0;
     const int chunks = p.BN / 32;
     for (int64_t tile = blockIdx.x; tile < n_tiles_total; tile += gridDim.x) {
-      const int64_t mt = tile / p.n_tiles;
-      const int nt = (int)(tile - mt * p.n_tiles);
+      const int64_t split = kSplit ? tile / mn_tiles : 0;
+      const int64_t mn = tile - split * mn_tiles;
+      const int64_t mt = mn / p.n_tiles;
+      const int nt = (int)(mn - mt * p.n_tiles);
       const int m0 = (int)(mt * kBM), n0 = nt * p.BN;
       mbar_wait(&bar_acc_full[as], aph);
       tc_fence_after();
@@ -171,6 +211,18 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_consta
         }
         const int ncol0 = n0 + c * 32;
         if (ncol0 >= p.N) continue;  // tile column tail: nothing to store (warp-uniform)
+        if (kSplit) {
+          // fp32 partial tile: each thread owns 32 consecutive columns of one output row
+          const int64_t row = (int64_t)m0 + quad * 32 + lane;
+          if (row < p.M_out) {
+            float* dst = p.partial + ((int64_t)split * p.M_out + row) * p.ldp + ncol0;
+#pragma unroll
+            for (int j = 0; j < 32; j += 4)
+              if (ncol0 + j < p.N)  // N % 8 == 0: a float4 never straddles the end of the row
+                *reinterpret_cast<uint4*>(dst + j) = make_uint4(r[j], r[j + 1], r[j + 2], r[j + 3]);
+          }
+          continue;
+        }
         float f[32];
 #pragma unroll
         for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(r[j]);
@@ -225,10 +277,26 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_consta
   }
 }
 
-int pick_bn(int N) {
-  // largest tile width (multiple of 32, <= 256) with the least padded columns
-  int best = 32, best_waste = 1 << 30;
-  for (int bn = 256; bn >= 32; bn -= 32) {
+__global__ void wgrad_reduce_kernel(const float* __restrict__ partial, tvi_bf16* __restrict__ dw, int splits, int64_t rows,
+                                    int cols, int64_t ldp, int64_t lddw) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;  // one pair of columns per thread
+  const int half = cols / 2;
+  if (i >= rows * half) return;
+  const int64_t r = i / half;
+  const int c = (int)(i - r * half) * 2;
+  float a = 0.f, b = 0.f;
+  for (int s = 0; s < splits; ++s) {
+    const float2 v = *reinterpret_cast<const float2*>(partial + ((int64_t)s * rows + r) * ldp + c);
+    a += v.x;
+    b += v.y;
+  }
+  *reinterpret_cast<uint32_t*>(dw + r * lddw + c) = pack_bf16x2(a, b);
+}
+
+int pick_bn(int N, int step = 32) {
+  // largest tile width (multiple of `step`, <= 256) with the least padded columns
+  int best = step, best_waste = 1 << 30;
+  for (int bn = 256; bn >= step; bn -= step) {
     const int tiles = (N + bn - 1) / bn;
     const int waste = tiles * bn - N;
     if (waste < best_waste) {
@@ -237,6 +305,97 @@ int pick_bn(int N) {
     }
   }
   return best;
+}
+
+
+// Operand tensor map.  K-major: dims {reduction, rows}, box {64, rows_box}.  MN-major: dims {out, reduction},
+// box {64, 64}.
+int operand_map(CUtensorMap* tm, const tvi_bf16* base, bool mn_major, int64_t out_extent, int64_t red_extent, int64_t ld,
+                int rows_box) {
+  if (!mn_major) {
+    const uint64_t dims[2] = {(uint64_t)red_extent, (uint64_t)out_extent};
+    const uint64_t strides[1] = {(uint64_t)ld * 2};
+    const uint32_t box[2] = {(uint32_t)kBK, (uint32_t)rows_box};
+    return make_tensor_map(tm, base, 2, 2, dims, strides, box, Swizzle::B128);
+  }
+  const uint64_t dims[2] = {(uint64_t)out_extent, (uint64_t)red_extent};
+  const uint64_t strides[1] = {(uint64_t)ld * 2};
+  const uint32_t box[2] = {64u, (uint32_t)kBK};
+  return make_tensor_map(tm, base, 2, 2, dims, strides, box, Swizzle::B128);
+}
+
+template <bool kAMn, bool kBMn, bool kSplit>
+int configure_once() {
+  static bool configured[64] = {false};
+  int dev = 0;
+  TVI_CUDA_OK(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= 64 || !configured[dev]) {
+    TVI_CUDA_OK(cudaFuncSetAttribute(gemm_bf16_kernel<kAMn, kBMn, kSplit>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     227 * 1024 - 256));
+    if (dev >= 0 && dev < 64) configured[dev] = true;
+  }
+  return TVI_OK;
+}
+
+// D[Mo, No] = A . B over a reduction of length R.  A is [Mo, R] (K-major) or [R, Mo] (MN-major) with row stride
+// lda; B is [No, R] or [R, No] with row stride ldb.  Output: bf16 Y (ldy) through TMA, or fp32 partials when kSplit.
+template <bool kAMn, bool kBMn, bool kSplit>
+int launch_gemm(const char* name, const tvi_bf16* A, const tvi_bf16* B, const tvi_bf16* bias, tvi_bf16* Y, float* partial,
+                int splits, int64_t Mo, int No, int64_t R, int64_t lda, int64_t ldb, int64_t ldy, cudaStream_t st) {
+  GemmParams p;
+  p.BN = pick_bn(No, kBMn ? 64 : 32);
+  p.N = No;
+  p.m_tiles = (Mo + kBM - 1) / kBM;
+  p.n_tiles = (No + p.BN - 1) / p.BN;
+  p.k_blocks_total = (int)((R + kBK - 1) / kBK);
+  p.k_blocks = kSplit ? (p.k_blocks_total + splits - 1) / splits : p.k_blocks_total;
+  p.bias = bias;
+  p.partial = partial;
+  p.M_out = Mo;
+  p.ldp = No;
+  const int stage_bytes = kABytes + p.BN * kBK * 2;
+  const int smem_cap = 227 * 1024 - 1024 /*alignment slack*/ - kStagingBytes - 256 /*static*/;
+  int stages = smem_cap / stage_bytes;
+  if (stages > kMaxStages) stages = kMaxStages;
+  TVI_CHECK_ARG(stages >= 2, "%s: tile does not fit shared memory", name);
+  p.stages = stages;
+  const int smem_bytes = 1024 + stages * stage_bytes + kStagingBytes;
+
+  CUtensorMap tmA, tmB, tmY;
+  int rc = operand_map(&tmA, A, kAMn, Mo, R, lda, kBM);
+  if (rc) return rc;
+  rc = operand_map(&tmB, B, kBMn, No, R, ldb, p.BN);
+  if (rc) return rc;
+  if (!kSplit) {
+    const uint64_t dims[2] = {(uint64_t)No, (uint64_t)Mo};
+    const uint64_t strides[1] = {(uint64_t)ldy * 2};
+    const uint32_t box[2] = {32u, 32u};
+    rc = make_tensor_map(&tmY, Y, 2, 2, dims, strides, box, Swizzle::B64);
+    if (rc) return rc;
+  } else {
+    tmY = tmA;  // unused by the split epilogue
+  }
+  rc = configure_once<kAMn, kBMn, kSplit>();
+  if (rc) return rc;
+  int64_t grid = p.m_tiles * p.n_tiles;
+  if (kSplit) grid *= (p.k_blocks_total + p.k_blocks - 1) / p.k_blocks;
+  const int sms = num_sms();
+  if (grid > sms) grid = sms;
+  gemm_bf16_kernel<kAMn, kBMn, kSplit><<<(unsigned)grid, kGemmThreads, smem_bytes, st>>>(tmA, tmB, tmY, p);
+  TVI_LAUNCH_OK(name);
+  return TVI_OK;
+}
+
+int wgrad_splits(int64_t M, int N, int K) {
+  const int64_t tiles = ((N + kBM - 1) / kBM) * (int64_t)((K + pick_bn(K, 64) - 1) / pick_bn(K, 64));
+  const int64_t kblocks = (M + kBK - 1) / kBK;
+  int64_t s = (num_sms() + tiles - 1) / tiles;
+  if (s > kblocks) s = kblocks;
+  if (s < 1) s = 1;
+  // every split must own at least one k-block
+  const int64_t per = (kblocks + s - 1) / s;
+  s = (kblocks + per - 1) / per;
+  return (int)s;
 }
 
 }  // namespace
@@ -255,56 +414,53 @@ extern "C" int tvi_gemm_bf16_tn(const tvi_bf16* X, const tvi_bf16* W, const tvi_
   TVI_CHECK_ARG(((uintptr_t)X | (uintptr_t)W | (uintptr_t)Y) % 16 == 0, "tvi_gemm_bf16_tn: X, W, Y must be 16-byte aligned");
   TVI_CHECK_ARG(bias == nullptr || (uintptr_t)bias % 4 == 0, "tvi_gemm_bf16_tn: bias must be 4-byte aligned");
   TVI_CHECK_ARG(M < ((int64_t)1 << 31) - 256, "tvi_gemm_bf16_tn: M too large for one call");
+  return launch_gemm<false, false, false>("tvi_gemm_bf16_tn", X, W, bias, Y, nullptr, 1, M, N, K, ldx, ldw, ldy,
+                                          (cudaStream_t)stream);
+}
 
-  GemmParams p;
-  p.BN = pick_bn(N);
-  p.N = N;
-  p.m_tiles = (M + kBM - 1) / kBM;
-  p.n_tiles = (N + p.BN - 1) / p.BN;
-  p.k_blocks = (K + kBK - 1) / kBK;
-  p.bias = bias;
-  const int stage_bytes = kABytes + p.BN * kBK * 2;
-  const int smem_cap = 227 * 1024 - 1024 /*alignment slack*/ - kStagingBytes - 256 /*static*/;
-  int stages = smem_cap / stage_bytes;
-  if (stages > kMaxStages) stages = kMaxStages;
-  TVI_CHECK_ARG(stages >= 2, "tvi_gemm_bf16_tn: tile does not fit shared memory");
-  p.stages = stages;
-  const int smem_bytes = 1024 + stages * stage_bytes + kStagingBytes;
+extern "C" int tvi_gemm_bf16_dgrad(const tvi_bf16* dY, const tvi_bf16* W, tvi_bf16* dX, int64_t M, int N, int K,
+                                   int64_t lddy, int64_t ldw, int64_t lddx, void* stream) {
+  using namespace tvi;
+  TVI_CHECK_ARG(M >= 0 && N >= 0 && K >= 0, "tvi_gemm_bf16_dgrad: negative size");
+  if (M == 0 || K == 0) return TVI_OK;
+  TVI_CHECK_ARG(dY && W && dX, "tvi_gemm_bf16_dgrad: null pointer");
+  TVI_CHECK_ARG(N > 0, "tvi_gemm_bf16_dgrad: N must be positive");
+  TVI_CHECK_ARG(K % 8 == 0 && N % 8 == 0, "tvi_gemm_bf16_dgrad: N=%d and K=%d must be multiples of 8", N, K);
+  TVI_CHECK_ARG(lddy % 8 == 0 && ldw % 8 == 0 && lddx % 8 == 0, "tvi_gemm_bf16_dgrad: row strides must be multiples of 8 elements");
+  TVI_CHECK_ARG(lddy >= N && ldw >= K && lddx >= K, "tvi_gemm_bf16_dgrad: row stride smaller than the row");
+  TVI_CHECK_ARG(((uintptr_t)dY | (uintptr_t)W | (uintptr_t)dX) % 16 == 0, "tvi_gemm_bf16_dgrad: pointers must be 16-byte aligned");
+  TVI_CHECK_ARG(M < ((int64_t)1 << 31) - 256, "tvi_gemm_bf16_dgrad: M too large for one call");
+  // D[M, K] = A[M, N] . B, B = W stored [N (reduction), K (output, contiguous)] -> MN-major B operand
+  return launch_gemm<false, true, false>("tvi_gemm_bf16_dgrad", dY, W, nullptr, dX, nullptr, 1, M, K, N, lddy, ldw, lddx,
+                                         (cudaStream_t)stream);
+}
 
-  CUtensorMap tmX, tmW, tmY;
-  {
-    const uint64_t dims[2] = {(uint64_t)K, (uint64_t)M};
-    const uint64_t strides[1] = {(uint64_t)ldx * 2};
-    const uint32_t box[2] = {(uint32_t)kBK, (uint32_t)kBM};
-    int rc = make_tensor_map(&tmX, X, 2, 2, dims, strides, box, Swizzle::B128);
-    if (rc) return rc;
-  }
-  {
-    const uint64_t dims[2] = {(uint64_t)K, (uint64_t)N};
-    const uint64_t strides[1] = {(uint64_t)ldw * 2};
-    const uint32_t box[2] = {(uint32_t)kBK, (uint32_t)p.BN};
-    int rc = make_tensor_map(&tmW, W, 2, 2, dims, strides, box, Swizzle::B128);
-    if (rc) return rc;
-  }
-  {
-    const uint64_t dims[2] = {(uint64_t)N, (uint64_t)M};
-    const uint64_t strides[1] = {(uint64_t)ldy * 2};
-    const uint32_t box[2] = {32u, 32u};
-    int rc = make_tensor_map(&tmY, Y, 2, 2, dims, strides, box, Swizzle::B64);
-    if (rc) return rc;
-  }
+extern "C" size_t tvi_gemm_bf16_wgrad_workspace_bytes(int64_t M, int N, int K) {
+  if (M <= 0 || N <= 0 || K <= 0) return 0;
+  return (size_t)tvi::wgrad_splits(M, N, K) * (size_t)N * (size_t)K * sizeof(float);
+}
 
-  static bool configured[64] = {false};
-  int dev = 0;
-  TVI_CUDA_OK(cudaGetDevice(&dev));
-  if (dev < 0 || dev >= 64 || !configured[dev]) {
-    TVI_CUDA_OK(cudaFuncSetAttribute(gemm_bf16_tn_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 256));
-    if (dev >= 0 && dev < 64) configured[dev] = true;
-  }
-  int64_t grid = p.m_tiles * p.n_tiles;
-  const int sms = num_sms();
-  if (grid > sms) grid = sms;
-  gemm_bf16_tn_kernel<<<(unsigned)grid, kGemmThreads, smem_bytes, (cudaStream_t)stream>>>(tmX, tmW, tmY, p);
-  TVI_LAUNCH_OK("gemm_bf16_tn_kernel");
+extern "C" int tvi_gemm_bf16_wgrad(const tvi_bf16* dY, const tvi_bf16* X, tvi_bf16* dW, void* workspace, int64_t M, int N,
+                                   int K, int64_t lddy, int64_t ldx, int64_t lddw, void* stream) {
+  using namespace tvi;
+  TVI_CHECK_ARG(M >= 0 && N >= 0 && K >= 0, "tvi_gemm_bf16_wgrad: negative size");
+  if (N == 0 || K == 0) return TVI_OK;
+  TVI_CHECK_ARG(dY && X && dW && workspace, "tvi_gemm_bf16_wgrad: null pointer");
+  TVI_CHECK_ARG(M > 0, "tvi_gemm_bf16_wgrad: M must be positive");
+  TVI_CHECK_ARG(K % 8 == 0 && N % 8 == 0, "tvi_gemm_bf16_wgrad: N=%d and K=%d must be multiples of 8", N, K);
+  TVI_CHECK_ARG(lddy % 8 == 0 && ldx % 8 == 0 && lddw % 2 == 0, "tvi_gemm_bf16_wgrad: bad row strides");
+  TVI_CHECK_ARG(lddy >= N && ldx >= K && lddw >= K, "tvi_gemm_bf16_wgrad: row stride smaller than the row");
+  TVI_CHECK_ARG(((uintptr_t)dY | (uintptr_t)X | (uintptr_t)workspace) % 16 == 0 && (uintptr_t)dW % 4 == 0,
+                "tvi_gemm_bf16_wgrad: pointers must be 16-byte aligned (dW: 4)");
+  TVI_CHECK_ARG(M < ((int64_t)1 << 31) - 256, "tvi_gemm_bf16_wgrad: M too large for one call");
+  const int splits = wgrad_splits(M, N, K);
+  // D[N, K] = A . B with A = dY stored [M (reduction), N (output rows, contiguous)], B = X stored [M, K]
+  int rc = launch_gemm<true, true, true>("tvi_gemm_bf16_wgrad", dY, X, nullptr, nullptr, (float*)workspace, splits, N, K, M,
+                                         lddy, ldx, 0, (cudaStream_t)stream);
+  if (rc) return rc;
+  const int64_t pairs = (int64_t)N * (K / 2);
+  wgrad_reduce_kernel<<<(unsigned)((pairs + 255) / 256), 256, 0, (cudaStream_t)stream>>>((const float*)workspace, dW, splits,
+                                                                                          N, K, K, lddw);
+  TVI_LAUNCH_OK("wgrad_reduce_kernel");
   return TVI_OK;
 }

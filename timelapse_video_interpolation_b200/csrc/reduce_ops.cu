@@ -1,0 +1,123 @@
+// Grouped column sums over token-major bf16 activations (HBM-bound, fp32 accumulation):
+//   out[g, c] = sum_{r in group g} x[r, c]
+// Used by the backward pass (training config 5): the bias gradient of attn.to_out[0] (one group = all
+// tokens; autograd's sum over the batch for F.linear, src/models/attention_processor.py:754 / :1251)
+// and the backward of the one-key cross-attention broadcast (every query row of a group receives the
+// same projected value row, so its gradient is the column sum of dY over the group).
+// Each thread owns one 16-byte column chunk; a warp reads 512 contiguous bytes of a row; row tiles of
+// a large group go to fp32 partials that a second kernel adds in a fixed order (deterministic).
+#include "tvi_common.cuh"
+
+namespace tvi {
+namespace {
+
+constexpr int kCsTileRows = 1024;
+constexpr int kCsTy = 8;
+
+__global__ void __launch_bounds__(32 * kCsTy)
+colsum_kernel(const tvi_bf16* __restrict__ x, tvi_bf16* __restrict__ out, float* __restrict__ partial,
+              int64_t rows_per_group, int tiles_per_group, int C8, int64_t ldx, int64_t ldo) {
+  __shared__ float red[kCsTy][32][8];
+  const int cx = blockIdx.y * 32 + threadIdx.x;
+  const int ty = threadIdx.y;
+  const int64_t group = blockIdx.x / tiles_per_group;
+  const int tile = (int)(blockIdx.x - group * tiles_per_group);
+  const int64_t rlo = group * rows_per_group + (int64_t)tile * kCsTileRows;
+  int64_t rhi = rlo + kCsTileRows;
+  const int64_t gend = (group + 1) * rows_per_group;
+  if (rhi > gend) rhi = gend;
+  float acc[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) acc[j] = 0.f;
+  if (cx < C8) {
+    for (int64_t r = rlo + ty; r < rhi; r += kCsTy) {
+      const uint4 u = __ldg(reinterpret_cast<const uint4*>(x + r * ldx + cx * 8));
+      const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&u);
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const float2 t = __bfloat1622float2(h[i]);
+        acc[2 * i] += t.x;
+        acc[2 * i + 1] += t.y;
+      }
+    }
+  }
+#pragma unroll
+  for (int j = 0; j < 8; ++j) red[ty][threadIdx.x][j] = acc[j];
+  __syncthreads();
+  if (ty == 0 && cx < C8) {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      float s = 0.f;
+#pragma unroll
+      for (int t = 0; t < kCsTy; ++t) s += red[t][threadIdx.x][j];
+      acc[j] = s;
+    }
+    if (tiles_per_group == 1) {
+      uint4 v;
+      v.x = pack_bf16x2(acc[0], acc[1]);
+      v.y = pack_bf16x2(acc[2], acc[3]);
+      v.z = pack_bf16x2(acc[4], acc[5]);
+      v.w = pack_bf16x2(acc[6], acc[7]);
+      *reinterpret_cast<uint4*>(out + group * ldo + cx * 8) = v;
+    } else {
+      float* dst = partial + ((group * tiles_per_group + tile) * (int64_t)C8 + cx) * 8;
+      *reinterpret_cast<float4*>(dst) = make_float4(acc[0], acc[1], acc[2], acc[3]);
+      *reinterpret_cast<float4*>(dst + 4) = make_float4(acc[4], acc[5], acc[6], acc[7]);
+    }
+  }
+}
+
+__global__ void colsum_final_kernel(const float* __restrict__ partial, tvi_bf16* __restrict__ out, int64_t ngroups,
+                                    int tiles_per_group, int C, int64_t ldo) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;  // one column pair
+  const int half = C / 2;
+  if (i >= ngroups * half) return;
+  const int64_t g = i / half;
+  const int c = (int)(i - g * half) * 2;
+  float a = 0.f, b = 0.f;
+  for (int t = 0; t < tiles_per_group; ++t) {
+    const float2 v = *reinterpret_cast<const float2*>(partial + (g * tiles_per_group + t) * (int64_t)C + c);
+    a += v.x;
+    b += v.y;
+  }
+  *reinterpret_cast<uint32_t*>(out + g * ldo + c) = pack_bf16x2(a, b);
+}
+
+int cs_tiles(int64_t rows_per_group) { return (int)((rows_per_group + kCsTileRows - 1) / kCsTileRows); }
+
+}  // namespace
+}  // namespace tvi
+
+extern "C" size_t tvi_colsum_bf16_workspace_bytes(int64_t nrows, int64_t rows_per_group, int C) {
+  if (nrows <= 0 || rows_per_group <= 0 || C <= 0) return 0;
+  const int tiles = tvi::cs_tiles(rows_per_group);
+  if (tiles == 1) return 0;
+  return (size_t)(nrows / rows_per_group) * tiles * (size_t)C * sizeof(float);
+}
+
+extern "C" int tvi_colsum_bf16(const tvi_bf16* x, tvi_bf16* out, void* workspace, int64_t nrows, int64_t rows_per_group, int C,
+                               int64_t ldx, int64_t ldo, void* stream) {
+  using namespace tvi;
+  TVI_CHECK_ARG(nrows >= 0 && C >= 0, "tvi_colsum_bf16: negative size");
+  if (nrows == 0 || C == 0) return TVI_OK;
+  TVI_CHECK_ARG(x && out, "tvi_colsum_bf16: null pointer");
+  TVI_CHECK_ARG(rows_per_group >= 1 && nrows % rows_per_group == 0, "tvi_colsum_bf16: nrows must be a multiple of rows_per_group");
+  TVI_CHECK_ARG(C % 8 == 0 && ldx % 8 == 0 && ldo % 8 == 0 && ldx >= C && ldo >= C, "tvi_colsum_bf16: C and the row strides must be multiples of 8");
+  TVI_CHECK_ARG(((uintptr_t)x | (uintptr_t)out) % 16 == 0, "tvi_colsum_bf16: pointers must be 16-byte aligned");
+  const int64_t ngroups = nrows / rows_per_group;
+  const int tiles = cs_tiles(rows_per_group);
+  TVI_CHECK_ARG(tiles == 1 || (workspace != nullptr && (uintptr_t)workspace % 16 == 0), "tvi_colsum_bf16: workspace required (16-byte aligned)");
+  TVI_CHECK_ARG(ngroups * tiles < ((int64_t)1 << 31), "tvi_colsum_bf16: grid too large");
+  cudaStream_t st = (cudaStream_t)stream;
+  const int C8 = C / 8;
+  dim3 grid((unsigned)(ngroups * tiles), (unsigned)((C8 + 31) / 32));
+  dim3 block(32, kCsTy);
+  colsum_kernel<<<grid, block, 0, st>>>(x, out, (float*)workspace, rows_per_group, tiles, C8, ldx, ldo);
+  TVI_LAUNCH_OK("colsum_kernel");
+  if (tiles > 1) {
+    const int64_t pairs = ngroups * (C / 2);
+    colsum_final_kernel<<<(unsigned)((pairs + 255) / 256), 256, 0, st>>>((const float*)workspace, out, ngroups, tiles, C, ldo);
+    TVI_LAUNCH_OK("colsum_final_kernel");
+  }
+  return TVI_OK;
+}

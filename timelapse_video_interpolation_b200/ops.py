@@ -69,6 +69,75 @@ def gemm_bf16_tn(x: torch.Tensor, w: torch.Tensor, bias: torch.Tensor | None = N
     return out
 
 
+def _hooked(name: str, n_launches: int, fn, *args):
+    global LAUNCHES
+    if EVENT_HOOK is not None:
+        EVENT_HOOK(name, True)
+    _lib.check(fn(*args))
+    if EVENT_HOOK is not None:
+        EVENT_HOOK(name, False)
+    LAUNCHES += n_launches
+
+
+def _workspace(nbytes: int, device) -> torch.Tensor | None:
+    return torch.empty(max(1, (nbytes + 3) // 4), dtype=torch.float32, device=device) if nbytes else None
+
+
+def gemm_bf16_dgrad(dy: torch.Tensor, w: torch.Tensor, out: torch.Tensor | None = None) -> torch.Tensor:
+    """dx[..., K] = dy[..., N] @ w[N, K] — input gradient of nn.Linear; w is consumed in place."""
+    _need_cuda(dy, w)
+    dy, lddy = _rows2d(dy, "dy")
+    w, ldw = _rows2d(w, "w")
+    N, K = w.shape
+    if dy.shape[-1] != N:
+        raise _lib.TviError(_lib.TVI_ERR_INVALID, f"dgrad: dy has N={dy.shape[-1]}, w has N={N}")
+    M = dy.numel() // N if N else 0
+    if out is None:
+        out = torch.empty(*dy.shape[:-1], K, dtype=torch.bfloat16, device=dy.device)
+    out, lddx = _rows2d(out, "out")
+    _hooked("gemm_bf16_dgrad", 1, _lib.load().tvi_gemm_bf16_dgrad, dy.data_ptr(), w.data_ptr(), out.data_ptr(), M, N, K,
+            lddy, ldw, lddx, _stream())
+    return out
+
+
+def gemm_bf16_wgrad(dy: torch.Tensor, x: torch.Tensor, out: torch.Tensor | None = None) -> torch.Tensor:
+    """dw[N, K] = dy[M, N]^T @ x[M, K] — weight gradient of nn.Linear (split token reduction)."""
+    _need_cuda(dy, x)
+    dy, lddy = _rows2d(dy, "dy")
+    x, ldx = _rows2d(x, "x")
+    N, K = dy.shape[-1], x.shape[-1]
+    M = dy.numel() // N if N else 0
+    if x.numel() != M * K:
+        raise _lib.TviError(_lib.TVI_ERR_INVALID, "wgrad: dy and x have different row counts")
+    if out is None:
+        out = torch.empty(N, K, dtype=torch.bfloat16, device=dy.device)
+    out, lddw = _rows2d(out, "out")
+    lib = _lib.load()
+    ws = _workspace(lib.tvi_gemm_bf16_wgrad_workspace_bytes(M, N, K), dy.device)
+    _hooked("gemm_bf16_wgrad", 2, lib.tvi_gemm_bf16_wgrad, dy.data_ptr(), x.data_ptr(), out.data_ptr(),
+            ws.data_ptr() if ws is not None else None, M, N, K, lddy, ldx, lddw, _stream())
+    return out
+
+
+def colsum_bf16(x: torch.Tensor, rows_per_group: int | None = None, out: torch.Tensor | None = None) -> torch.Tensor:
+    """out[g, :] = sum of the rows of group g of x[nrows, C] (fp32 accumulation, bf16 result)."""
+    _need_cuda(x)
+    x, ldx = _rows2d(x, "x")
+    C = x.shape[-1]
+    nrows = x.numel() // C if C else 0
+    rpg = nrows if rows_per_group is None else int(rows_per_group)
+    ngroups = nrows // rpg if rpg else 0
+    if out is None:
+        out = torch.empty(ngroups, C, dtype=torch.bfloat16, device=x.device)
+    out, ldo = _rows2d(out, "out")
+    lib = _lib.load()
+    nb = lib.tvi_colsum_bf16_workspace_bytes(nrows, rpg, C)
+    ws = _workspace(nb, x.device)
+    _hooked("colsum_bf16", 2 if nb else 1, lib.tvi_colsum_bf16, x.data_ptr(), out.data_ptr(),
+            ws.data_ptr() if ws is not None else None, nrows, rpg, C, ldx, ldo, _stream())
+    return out
+
+
 def attn_temporal(q, k, v, nseq: int, heads: int, Tq: int, Tk: int, scale: float, out=None, lse=None):
     """Short-sequence attention core; q/k/v are [nseq*T, heads*64] row views (may be strided)."""
     global LAUNCHES
