@@ -155,6 +155,35 @@ int tvi_attn_spatial_fwd_algo(const tvi_bf16* q, const tvi_bf16* k, const tvi_bf
                               int batch, int heads, int S, int Skv, int d, int64_t ldq, int64_t ldk, int64_t ldv,
                               int64_t ldo, float scale, int algo, void* stream);
 
+/* ---------------------------------------------------------------------------------------------
+ * Backward of the attention cores (training config 5; what autograd derives for the call sites of
+ * rows A3a-A3d: src/models/attention_processor.py:598-615+:750, :1156, :1243).  With P = softmax(scale QK^T):
+ *   dV = P^T dO,  dS = P o (dO V^T - rowsum(dO o O)),  dQ = scale dS K,  dK = scale dS^T Q.
+ * All gradients are bf16 with the layout of the tensor they belong to (so dq/dk/dv may be the three
+ * column slices of one packed [tokens, 3C] buffer, lddq = lddk = lddv = 3C).
+ *
+ * spatial : flash-style recomputation from q, k, v and the forward's `lse`; `o` is the forward output.
+ *           workspace = tvi_attn_spatial_bwd_workspace_bytes(batch, heads, S) bytes.  d == 64.
+ * temporal: T <= 64, needs neither o nor lse.  d == 64.
+ * fewkeys : dk, dv are [ngroups*L, heads*d] (sum over the rows of each group); `bias` as in the forward
+ *           (a constant: no gradient); q == dq == NULL is allowed when L == 1 (softmax == 1).
+ *           workspace = tvi_attn_fewkeys_bwd_workspace_bytes(...) bytes (may be 0).
+ */
+size_t tvi_attn_spatial_bwd_workspace_bytes(int batch, int heads, int S);
+int tvi_attn_spatial_bwd(const tvi_bf16* q, const tvi_bf16* k, const tvi_bf16* v, const tvi_bf16* o, const tvi_bf16* dout,
+                         const float* lse, tvi_bf16* dq, tvi_bf16* dk, tvi_bf16* dv, void* workspace, int batch, int heads,
+                         int S, int Skv, int d, int64_t ldq, int64_t ldk, int64_t ldv, int64_t ldo, int64_t lddo,
+                         int64_t lddq, int64_t lddk, int64_t lddv, float scale, void* stream);
+int tvi_attn_temporal_bwd(const tvi_bf16* q, const tvi_bf16* k, const tvi_bf16* v, const tvi_bf16* dout, tvi_bf16* dq,
+                          tvi_bf16* dk, tvi_bf16* dv, int64_t nseq, int heads, int Tq, int Tk, int d, int64_t ldq,
+                          int64_t ldk, int64_t ldv, int64_t lddo, int64_t lddq, int64_t lddk, int64_t lddv, float scale,
+                          void* stream);
+size_t tvi_attn_fewkeys_bwd_workspace_bytes(int64_t nrows, int64_t rows_per_group, int heads, int L, int d);
+int tvi_attn_fewkeys_bwd(const tvi_bf16* q, const tvi_bf16* k, const tvi_bf16* v, const tvi_bf16* dout, tvi_bf16* dq,
+                         tvi_bf16* dk, tvi_bf16* dv, void* workspace, int64_t nrows, int64_t rows_per_group, int heads,
+                         int L, int d, int64_t ldq, int64_t ldk, int64_t ldv, int64_t lddo, int64_t lddq, int64_t lddk,
+                         int64_t lddv, float scale, int Tq, const float* bias, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -81,3 +81,110 @@ def test_colsum_matches_fp32_reference(cuda, nrows, rpg, C):
     torch.cuda.synchronize()
     ref = x.float().view(nrows // rpg, rpg, C).sum(1).cpu()
     _close(out, ref, rpg, "colsum")
+
+
+# ------------------------------------------------------------------------------------------------
+# attention cores: gradients vs fp32 autograd of the explicit softmax attention
+# (reference math: src/models/attention_processor.py:598-615 + :750) on the same bf16-rounded operands
+# ------------------------------------------------------------------------------------------------
+def _ref_attention_grads(q, k, v, dout, nseq, heads, Tq, Tk, scale, bias=None, groups_rows=None):
+    """q [nseq*Tq, C], k/v [nseq*Tk, C] (fp32, requires_grad) -> (o, dq, dk, dv) by autograd."""
+    C = q.shape[-1]
+    d = C // heads
+    q = q.detach().float().requires_grad_(True)
+    k = k.detach().float().requires_grad_(True)
+    v = v.detach().float().requires_grad_(True)
+    qh = q.view(nseq, Tq, heads, d).transpose(1, 2)
+    kh = k.view(nseq, Tk, heads, d).transpose(1, 2)
+    vh = v.view(nseq, Tk, heads, d).transpose(1, 2)
+    s = qh @ kh.transpose(-1, -2) * scale
+    if bias is not None:
+        s = s + bias
+    o = (s.softmax(-1) @ vh).transpose(1, 2).reshape(nseq * Tq, C)
+    o.backward(dout.float())
+    return o.detach(), q.grad, k.grad, v.grad
+
+
+def _grad_close(got, ref, what, tol=2e-2):
+    ref = ref.float()
+    err = float((got.float() - ref).abs().max())
+    scale = float(ref.abs().max()) + 1e-12
+    print(f"{what}: max abs err {err:.3e}, max |ref| {scale:.3e}, rel {err / scale:.3e}")
+    assert err <= tol * scale, f"{what}: {err:.4g} > {tol} * {scale:.4g}"
+
+
+def _packed_qkv(rows_q, rows_kv, C, g, dev, std=1.0):
+    """q, k, v as column slices of packed buffers (strided rows), like the fused projection output."""
+    if rows_q == rows_kv:
+        buf = (torch.randn(rows_q, 3 * C, generator=g) * std).to(torch.bfloat16).to(dev)
+        return buf[:, :C], buf[:, C:2 * C], buf[:, 2 * C:]
+    qb = (torch.randn(rows_q, C, generator=g) * std).to(torch.bfloat16).to(dev)
+    kvb = (torch.randn(rows_kv, 2 * C, generator=g) * std).to(torch.bfloat16).to(dev)
+    return qb, kvb[:, :C], kvb[:, C:]
+
+
+@pytest.mark.parametrize("nseq,heads,Tq,Tk", [(300, 5, 14, 14), (97, 5, 25, 25), (40, 2, 64, 64), (33, 3, 7, 7),
+                                              (21, 2, 16, 16), (19, 1, 14, 9), (11, 2, 33, 50), (4608, 5, 14, 14)])
+def test_temporal_bwd_matches_autograd(cuda, nseq, heads, Tq, Tk):
+    g = torch.Generator().manual_seed(nseq + Tq)
+    C = heads * 64
+    q, k, v = _packed_qkv(nseq * Tq, nseq * Tk, C, g, cuda)
+    dout = torch.randn(nseq * Tq, C, generator=g).to(torch.bfloat16).to(cuda)
+    scale = 0.125
+    dqkv = torch.zeros(nseq * max(Tq, Tk), 3 * C, dtype=torch.bfloat16, device=cuda)
+    if Tq == Tk:  # gradients written in place into a packed [rows, 3C] buffer
+        dq, dk, dv = ops.attn_temporal_bwd(q, k, v, dout, nseq, heads, Tq, Tk, scale, dq=dqkv[:, :C], dk=dqkv[:, C:2 * C],
+                                           dv=dqkv[:, 2 * C:])
+    else:
+        dq, dk, dv = ops.attn_temporal_bwd(q, k, v, dout, nseq, heads, Tq, Tk, scale)
+    torch.cuda.synchronize()
+    _, rq, rk, rv = _ref_attention_grads(q, k, v, dout, nseq, heads, Tq, Tk, scale)
+    _grad_close(dq, rq, "temporal dq")
+    _grad_close(dk, rk, "temporal dk")
+    _grad_close(dv, rv, "temporal dv")
+
+
+@pytest.mark.parametrize("batch,heads,S,Skv", [(2, 5, 144, 144), (2, 5, 576, 576), (1, 2, 1000, 1000), (2, 1, 300, 200),
+                                               (1, 3, 130, 65), (1, 5, 2304, 2304)])
+def test_spatial_bwd_matches_autograd(cuda, batch, heads, S, Skv):
+    g = torch.Generator().manual_seed(S + Skv)
+    C = heads * 64
+    q, k, v = _packed_qkv(batch * S, batch * Skv, C, g, cuda)
+    dout = torch.randn(batch * S, C, generator=g).to(torch.bfloat16).to(cuda)
+    scale = 0.125
+    lse = torch.empty(batch * S, heads, dtype=torch.float32, device=cuda)
+    o = ops.attn_spatial(q, k, v, batch, heads, S, Skv, scale, lse=lse)
+    dq, dk, dv = ops.attn_spatial_bwd(q, k, v, o, dout, lse, batch, heads, S, Skv, scale)
+    dq2, dk2, dv2 = ops.attn_spatial_bwd(q, k, v, o, dout, lse, batch, heads, S, Skv, scale)
+    torch.cuda.synchronize()
+    assert torch.equal(dq, dq2) and torch.equal(dk, dk2) and torch.equal(dv, dv2)  # no atomics: repeatable
+    ro, rq, rk, rv = _ref_attention_grads(q, k, v, dout, batch, heads, S, Skv, scale)
+    _grad_close(o, ro, "spatial o")
+    _grad_close(dq, rq, "spatial dq")
+    _grad_close(dk, rk, "spatial dk")
+    _grad_close(dv, rv, "spatial dv")
+
+
+@pytest.mark.parametrize("ngroups,rpg,heads,L,use_bias", [(50, 14, 5, 2, False), (50, 14, 5, 2, True), (3, 9216, 5, 2, False),
+                                                          (4, 1000, 10, 1, False), (6, 144, 20, 4, False), (5, 25, 5, 8, False),
+                                                          (2, 2304, 10, 2, False)])
+def test_fewkeys_bwd_matches_autograd(cuda, ngroups, rpg, heads, L, use_bias):
+    g = torch.Generator().manual_seed(ngroups + rpg + L)
+    C = heads * 64
+    nrows = ngroups * rpg
+    q = torch.randn(nrows, C, generator=g).to(torch.bfloat16).to(cuda)
+    kv = torch.randn(ngroups * L, 2 * C, generator=g).to(torch.bfloat16).to(cuda)
+    k, v = kv[:, :C], kv[:, C:]
+    dout = torch.randn(nrows, C, generator=g).to(torch.bfloat16).to(cuda)
+    scale = 0.125
+    bias = None
+    if use_bias:
+        w = torch.linspace(0, 1, rpg, device=cuda)
+        bias = torch.stack([1 - w, w], 1).contiguous()
+    dq, dk, dv = ops.attn_fewkeys_bwd(q, k, v, dout, nrows, rpg, heads, L, scale, Tq=rpg if use_bias else 1, bias=bias)
+    torch.cuda.synchronize()
+    _, rq, rk, rv = _ref_attention_grads(q, k, v, dout, ngroups, heads, rpg, L, scale,
+                                         bias=None if bias is None else bias.view(1, 1, rpg, L))
+    _grad_close(dq, rq, "fewkeys dq")
+    _grad_close(dk, rk, "fewkeys dk")
+    _grad_close(dv, rv, "fewkeys dv")

@@ -1,0 +1,911 @@
+// Backward of the three attention cores (training config 5: src/train_decouples.py back-propagates
+// through F.scaled_dot_product_attention / xformers / the eager baddbmm-softmax-bmm of
+// src/models/attention_processor.py:598-615, :750, :1243 at the call sites of rows A3a-A3d).
+//
+// With P = softmax(scale . Q K^T), O = P V and D_i = sum_d dO_id O_id = sum_j P_ij dP_ij:
+//     dV = P^T dO        dP = dO V^T        dS = P o (dP - D)        dQ = scale . dS K      dK = scale . dS^T Q
+//
+// tvi_attn_spatial_bwd  (long sequences, flash-style recomputation from Q, K, V, LSE; nothing S x Skv is
+//   ever stored).  Two passes of ONE mma.sync kernel template, so no atomics and a fixed summation order:
+//     rows = keys   : a CTA owns 128 key rows, streams the queries in blocks of 64, computes S^T = K Q^T
+//                     and dP^T = V dO^T, accumulates dV += P^T dO and dK += dS^T Q in registers;
+//     rows = queries: a CTA owns 128 query rows, streams the keys, accumulates dQ += dS K.
+//   P^T / dS^T (resp. dS) go from the accumulator registers straight into the next product's A operand.
+// tvi_attn_temporal_bwd (T <= 64): one warp per (sequence, head); P and dS of the whole T x T problem
+//   are staged in shared memory as bf16 and re-read transposed with ldmatrix.trans for dV and dK.
+//   Needs neither O nor LSE (D is recomputed from P and dP).  HBM bytes: 7 * rows * heads*d * 2.
+// tvi_attn_fewkeys_bwd  (1..8 context keys shared by rows_per_group query rows): one 16-byte channel
+//   chunk per thread; dK / dV of a group are accumulated in registers, reduced across the CTA's rows in
+//   shared memory in a fixed order, and across row tiles through fp32 partials.
+#include "mma_sync.cuh"
+
+namespace tvi {
+namespace {
+
+constexpr float kLog2e = 1.4426950408889634f;
+
+// ---------------------------------------------------------------------------------------------
+// D[row, head] = sum_d dO . O
+// ---------------------------------------------------------------------------------------------
+__global__ void attn_bwd_dot_kernel(const tvi_bf16* __restrict__ o, const tvi_bf16* __restrict__ dout, float* __restrict__ D,
+                                    int64_t nrows, int heads, int64_t ldo, int64_t lddo) {
+  // 8 lanes per (row, head): one 16-byte chunk each
+  const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const int64_t item = idx >> 3;
+  const int c = (int)(idx & 7);
+  const bool in = item < nrows * heads;
+  const int64_t row = in ? item / heads : 0;
+  const int h = in ? (int)(item - row * heads) : 0;
+  const uint4 a = __ldg(reinterpret_cast<const uint4*>(o + row * ldo + h * 64 + c * 8));
+  const uint4 b = __ldg(reinterpret_cast<const uint4*>(dout + row * lddo + h * 64 + c * 8));
+  const __nv_bfloat162* ha = reinterpret_cast<const __nv_bfloat162*>(&a);
+  const __nv_bfloat162* hb = reinterpret_cast<const __nv_bfloat162*>(&b);
+  float s = 0.f;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const float2 x = __bfloat1622float2(ha[i]), y = __bfloat1622float2(hb[i]);
+    s = fmaf(x.x, y.x, s);
+    s = fmaf(x.y, y.y, s);
+  }
+  s += __shfl_xor_sync(0xffffffffu, s, 1);
+  s += __shfl_xor_sync(0xffffffffu, s, 2);
+  s += __shfl_xor_sync(0xffffffffu, s, 4);
+  if (in && c == 0) D[item] = s;
+}
+
+// ---------------------------------------------------------------------------------------------
+// flash backward (spatial)
+// ---------------------------------------------------------------------------------------------
+constexpr int kFbBr = 128;  // rows per CTA
+constexpr int kFbBc = 64;   // streamed columns per stage
+constexpr int kFbStages = 3;
+constexpr int kFbThreads = 256;
+constexpr int kFbRowBytes = kFbBr * 128;
+constexpr int kFbColBytes = kFbBc * 128;
+constexpr int kFbStageBytes = 2 * kFbColBytes + 2 * kFbBc * 4;  // two tiles + lse[64] + D[64]
+constexpr int kFbSmem = 2 * kFbRowBytes + kFbStages * kFbStageBytes;
+
+struct FbParams {
+  const tvi_bf16 *r1, *r2;  // row operands      rows = keys: K, V     rows = queries: Q, dO
+  const tvi_bf16 *c1, *c2;  // streamed operands rows = keys: Q, dO    rows = queries: K, V
+  int64_t ldr1, ldr2, ldc1, ldc2;
+  const float *lse, *D;     // [batch * Sq, heads]
+  tvi_bf16 *out1, *out2;    // rows = keys: dK, dV     rows = queries: dQ, -
+  int64_t ldo1, ldo2;
+  int heads, nrows, ncols;  // per sequence
+  float scale;
+};
+
+template <bool kRowsAreKeys>
+__global__ void __launch_bounds__(kFbThreads, 1) attn_bwd_flash_kernel(const FbParams p) {
+  extern __shared__ __align__(128) uint8_t smem_raw[];
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int g = lane >> 2, qd = lane & 3;
+  const int bh = blockIdx.y;
+  const int b = bh / p.heads, h = bh - b * p.heads;
+  const int r0 = blockIdx.x * kFbBr;
+
+  const uint32_t sR1 = smem_u32(smem_raw);
+  const uint32_t sR2 = sR1 + kFbRowBytes;
+  const uint32_t sSt = sR2 + kFbRowBytes;
+  const tvi_bf16* r1b = p.r1 + ((int64_t)b * p.nrows) * p.ldr1 + h * 64;
+  const tvi_bf16* r2b = p.r2 + ((int64_t)b * p.nrows) * p.ldr2 + h * 64;
+  const tvi_bf16* c1b = p.c1 + ((int64_t)b * p.ncols) * p.ldc1 + h * 64;
+  const tvi_bf16* c2b = p.c2 + ((int64_t)b * p.ncols) * p.ldc2 + h * 64;
+  // lse / D are indexed by the query: a column when rows are keys, a row otherwise
+  const int nq = kRowsAreKeys ? p.ncols : p.nrows;
+  const float* lse_b = p.lse + ((int64_t)b * nq) * p.heads + h;
+  const float* D_b = p.D + ((int64_t)b * nq) * p.heads + h;
+
+  auto load_stage = [&](int st, int j0) {
+    const uint32_t dst = sSt + st * kFbStageBytes;
+#pragma unroll
+    for (int i = 0; i < (kFbBc * 8) / kFbThreads; ++i) {
+      const int idx = tid + i * kFbThreads;
+      const int r = idx >> 3, c = idx & 7;
+      const bool in = (j0 + r) < p.ncols;
+      const uint32_t off = tile_off(r, c);
+      const int64_t row = in ? (j0 + r) : 0;
+      asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst + off), "l"(c1b + row * p.ldc1 + c * 8),
+                   "r"(in ? 16 : 0)
+                   : "memory");
+      asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst + kFbColBytes + off),
+                   "l"(c2b + row * p.ldc2 + c * 8), "r"(in ? 16 : 0)
+                   : "memory");
+    }
+    if (kRowsAreKeys && tid < 2 * kFbBc) {
+      const int r = tid & (kFbBc - 1);
+      const bool in = (j0 + r) < p.ncols;
+      const float* src = (tid < kFbBc ? lse_b : D_b) + (int64_t)(in ? j0 + r : 0) * p.heads;
+      asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(dst + 2 * kFbColBytes + tid * 4), "l"(src),
+                   "r"(in ? 4 : 0)
+                   : "memory");
+    }
+  };
+
+  // ---- prologue: the two row tiles + first two column stages -------------------------------
+#pragma unroll
+  for (int i = 0; i < (kFbBr * 8) / kFbThreads; ++i) {
+    const int idx = tid + i * kFbThreads;
+    const int r = idx >> 3, c = idx & 7;
+    const bool in = (r0 + r) < p.nrows;
+    const int64_t row = in ? (r0 + r) : 0;
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(sR1 + tile_off(r, c)), "l"(r1b + row * p.ldr1 + c * 8),
+                 "r"(in ? 16 : 0)
+                 : "memory");
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(sR2 + tile_off(r, c)), "l"(r2b + row * p.ldr2 + c * 8),
+                 "r"(in ? 16 : 0)
+                 : "memory");
+  }
+  const int nblk = (p.ncols + kFbBc - 1) / kFbBc;
+  load_stage(0, 0);
+  cp_async_commit();
+  if (nblk > 1) load_stage(1, kFbBc);
+  cp_async_commit();
+
+  const float sl2 = p.scale * kLog2e;
+  // rows = queries: this thread's two rows' lse / D stay in registers
+  float lr0 = 0.f, lr1 = 0.f, dr0 = 0.f, dr1 = 0.f;
+  if (!kRowsAreKeys) {
+    const int q0 = r0 + warp * 16 + g, q1 = q0 + 8;
+    if (q0 < p.nrows) {
+      lr0 = __ldg(lse_b + (int64_t)q0 * p.heads) * kLog2e;
+      dr0 = __ldg(D_b + (int64_t)q0 * p.heads);
+    }
+    if (q1 < p.nrows) {
+      lr1 = __ldg(lse_b + (int64_t)q1 * p.heads) * kLog2e;
+      dr1 = __ldg(D_b + (int64_t)q1 * p.heads);
+    }
+  }
+
+  float acc1[8][4];                         // dS . C1  (dK or dQ)
+  float acc2[kRowsAreKeys ? 8 : 1][4];      // P . C2   (dV)
+#pragma unroll
+  for (int nt = 0; nt < 8; ++nt) acc1[nt][0] = acc1[nt][1] = acc1[nt][2] = acc1[nt][3] = 0.f;
+#pragma unroll
+  for (int nt = 0; nt < (kRowsAreKeys ? 8 : 1); ++nt) acc2[nt][0] = acc2[nt][1] = acc2[nt][2] = acc2[nt][3] = 0.f;
+
+  const int arow = warp * 16 + (lane & 7) + ((lane >> 3) & 1) * 8;  // ldmatrix row of this lane in the row tiles
+
+  for (int j = 0; j < nblk; ++j) {
+    cp_async_wait<1>();
+    __syncthreads();
+    if (j + 2 < nblk) load_stage((j + 2) % kFbStages, (j + 2) * kFbBc);
+    cp_async_commit();
+    const uint32_t sC1 = sSt + (j % kFbStages) * kFbStageBytes;
+    const uint32_t sC2 = sC1 + kFbColBytes;
+    const float* sLse = reinterpret_cast<const float*>(smem_raw + 2 * kFbRowBytes + (j % kFbStages) * kFbStageBytes +
+                                                       2 * kFbColBytes);
+    const float* sD = sLse + kFbBc;
+
+    // ---- S = R1 C1^T and dP = R2 C2^T (16 x 64 per warp) -------------------------------------
+    float s[8][4], dp[8][4];
+#pragma unroll
+    for (int nt = 0; nt < 8; ++nt) {
+      s[nt][0] = s[nt][1] = s[nt][2] = s[nt][3] = 0.f;
+      dp[nt][0] = dp[nt][1] = dp[nt][2] = dp[nt][3] = 0.f;
+    }
+#pragma unroll
+    for (int ks = 0; ks < 4; ++ks) {
+      uint32_t a1[4], a2[4];
+      ldsm_x4(sR1 + tile_off(arow, 2 * ks + (lane >> 4)), a1[0], a1[1], a1[2], a1[3]);
+      ldsm_x4(sR2 + tile_off(arow, 2 * ks + (lane >> 4)), a2[0], a2[1], a2[2], a2[3]);
+#pragma unroll
+      for (int np = 0; np < 4; ++np) {
+        uint32_t b0, b1, b2, b3;
+        const uint32_t boff = tile_off(np * 16 + (lane & 7) + (lane >> 4) * 8, 2 * ks + ((lane >> 3) & 1));
+        ldsm_x4(sC1 + boff, b0, b1, b2, b3);
+        mma_bf16_16816(s[2 * np], a1, b0, b1);
+        mma_bf16_16816(s[2 * np + 1], a1, b2, b3);
+        ldsm_x4(sC2 + boff, b0, b1, b2, b3);
+        mma_bf16_16816(dp[2 * np], a2, b0, b1);
+        mma_bf16_16816(dp[2 * np + 1], a2, b2, b3);
+      }
+    }
+    // ---- P = exp(scale S - lse), dS = P o (dP - D) -------------------------------------------
+    uint32_t pfr[8][2], dfr[8][2];
+    const int j0 = j * kFbBc;
+#pragma unroll
+    for (int nt = 0; nt < 8; ++nt) {
+      const int col = nt * 8 + qd * 2;
+      float l0a, l0b, l1a, l1b, d0a, d0b, d1a, d1b;  // (row g | g+8) x (col | col+1)
+      if (kRowsAreKeys) {
+        const float2 lv = *reinterpret_cast<const float2*>(sLse + col);
+        const float2 dv = *reinterpret_cast<const float2*>(sD + col);
+        l0a = l1a = lv.x * kLog2e;
+        l0b = l1b = lv.y * kLog2e;
+        d0a = d1a = dv.x;
+        d0b = d1b = dv.y;
+      } else {
+        l0a = l0b = lr0;
+        l1a = l1b = lr1;
+        d0a = d0b = dr0;
+        d1a = d1b = dr1;
+      }
+      float p0 = fast_exp2(fmaf(s[nt][0], sl2, -l0a)), p1 = fast_exp2(fmaf(s[nt][1], sl2, -l0b));
+      float p2 = fast_exp2(fmaf(s[nt][2], sl2, -l1a)), p3 = fast_exp2(fmaf(s[nt][3], sl2, -l1b));
+      if (j0 + col >= p.ncols) p0 = p2 = 0.f;  // streamed columns past the sequence
+      if (j0 + col + 1 >= p.ncols) p1 = p3 = 0.f;
+      pfr[nt][0] = pack_bf16x2(p0, p1);
+      pfr[nt][1] = pack_bf16x2(p2, p3);
+      dfr[nt][0] = pack_bf16x2(p0 * (dp[nt][0] - d0a), p1 * (dp[nt][1] - d0b));
+      dfr[nt][1] = pack_bf16x2(p2 * (dp[nt][2] - d1a), p3 * (dp[nt][3] - d1b));
+    }
+    // ---- acc1 += dS C1, acc2 += P C2 -----------------------------------------------------------
+#pragma unroll
+    for (int kk = 0; kk < 4; ++kk) {
+      const uint32_t ad[4] = {dfr[2 * kk][0], dfr[2 * kk][1], dfr[2 * kk + 1][0], dfr[2 * kk + 1][1]};
+      const uint32_t ap[4] = {pfr[2 * kk][0], pfr[2 * kk][1], pfr[2 * kk + 1][0], pfr[2 * kk + 1][1]};
+#pragma unroll
+      for (int nc = 0; nc < 8; nc += 2) {
+        uint32_t b0, b1, b2, b3;
+        const uint32_t boff = tile_off(kk * 16 + (lane & 7) + ((lane >> 3) & 1) * 8, nc + (lane >> 4));
+        ldsm_x4_t(sC1 + boff, b0, b1, b2, b3);
+        mma_bf16_16816(acc1[nc], ad, b0, b1);
+        mma_bf16_16816(acc1[nc + 1], ad, b2, b3);
+        if (kRowsAreKeys) {
+          ldsm_x4_t(sC2 + boff, b0, b1, b2, b3);
+          mma_bf16_16816(acc2[nc], ap, b0, b1);
+          mma_bf16_16816(acc2[nc + 1], ap, b2, b3);
+        }
+      }
+    }
+  }
+  cp_async_wait<0>();
+  __syncwarp();
+
+  // ---- epilogue: each warp stages its 16 rows over its own rows of the row tiles ----------------
+  uint8_t* pR1 = smem_raw;
+  uint8_t* pR2 = smem_raw + kFbRowBytes;
+  const int ra = warp * 16 + g, rb = ra + 8;
+#pragma unroll
+  for (int nt = 0; nt < 8; ++nt) {
+    *reinterpret_cast<uint32_t*>(pR1 + tile_off(ra, nt) + qd * 4) = pack_bf16x2(acc1[nt][0] * p.scale, acc1[nt][1] * p.scale);
+    *reinterpret_cast<uint32_t*>(pR1 + tile_off(rb, nt) + qd * 4) = pack_bf16x2(acc1[nt][2] * p.scale, acc1[nt][3] * p.scale);
+    if (kRowsAreKeys) {
+      *reinterpret_cast<uint32_t*>(pR2 + tile_off(ra, nt) + qd * 4) = pack_bf16x2(acc2[nt][0], acc2[nt][1]);
+      *reinterpret_cast<uint32_t*>(pR2 + tile_off(rb, nt) + qd * 4) = pack_bf16x2(acc2[nt][2], acc2[nt][3]);
+    }
+  }
+  __syncwarp();
+  tvi_bf16* o1b = p.out1 + ((int64_t)b * p.nrows) * p.ldo1 + h * 64;
+  tvi_bf16* o2b = kRowsAreKeys ? p.out2 + ((int64_t)b * p.nrows) * p.ldo2 + h * 64 : nullptr;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int r = warp * 16 + (lane >> 3) + 4 * i;
+    if (r0 + r < p.nrows) {
+      *reinterpret_cast<uint4*>(o1b + (int64_t)(r0 + r) * p.ldo1 + (lane & 7) * 8) =
+          *reinterpret_cast<const uint4*>(pR1 + tile_off(r, lane & 7));
+      if (kRowsAreKeys)
+        *reinterpret_cast<uint4*>(o2b + (int64_t)(r0 + r) * p.ldo2 + (lane & 7) * 8) =
+            *reinterpret_cast<const uint4*>(pR2 + tile_off(r, lane & 7));
+    }
+  }
+}
+
+template <bool kRowsAreKeys>
+int launch_flash_bwd(const FbParams& p, int batch, cudaStream_t st) {
+  static bool configured[64] = {false};
+  int dev = 0;
+  TVI_CUDA_OK(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= 64 || !configured[dev]) {
+    TVI_CUDA_OK(cudaFuncSetAttribute(attn_bwd_flash_kernel<kRowsAreKeys>, cudaFuncAttributeMaxDynamicSharedMemorySize, kFbSmem));
+    if (dev >= 0 && dev < 64) configured[dev] = true;
+  }
+  dim3 grid((unsigned)((p.nrows + kFbBr - 1) / kFbBr), (unsigned)(batch * p.heads));
+  attn_bwd_flash_kernel<kRowsAreKeys><<<grid, kFbThreads, kFbSmem, st>>>(p);
+  TVI_LAUNCH_OK("attn_bwd_flash_kernel");
+  return TVI_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// temporal (short-sequence) backward
+// ---------------------------------------------------------------------------------------------
+template <int MT>
+struct TemporalBwdCfg {
+  static constexpr int kRows = 16 * MT;
+  static constexpr int kTileBytes = kRows * 128;
+  static constexpr int kWarpBytes = 6 * kTileBytes + 16 * 128;  // Q K V dO | P dS | 16-row output staging
+  static constexpr int kWarps = (MT == 1) ? 8 : 4;
+  static constexpr int kSmemBytes = kWarps * kWarpBytes;
+};
+
+struct TbParams {
+  const tvi_bf16 *q, *k, *v, *dout;
+  tvi_bf16 *dq, *dk, *dv;
+  int64_t ldq, ldk, ldv, lddo, lddq, lddk, lddv;
+  int64_t nitems;
+  int heads, Tq, Tk;
+  float scale;
+};
+
+template <int MT>
+__global__ void __launch_bounds__(TemporalBwdCfg<MT>::kWarps * 32) attn_temporal_bwd_kernel(const TbParams p) {
+  using Cfg = TemporalBwdCfg<MT>;
+  constexpr int kRows = Cfg::kRows;
+  constexpr int NT = 2 * MT;
+  extern __shared__ __align__(128) uint8_t smem_raw[];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int g = lane >> 2, qd = lane & 3;
+  uint8_t* wptr = smem_raw + warp * Cfg::kWarpBytes;
+  const uint32_t sQ = smem_u32(wptr);
+  const uint32_t sK = sQ + Cfg::kTileBytes;
+  const uint32_t sV = sK + Cfg::kTileBytes;
+  const uint32_t sDO = sV + Cfg::kTileBytes;
+  const uint32_t sP = sDO + Cfg::kTileBytes;
+  const uint32_t sDS = sP + Cfg::kTileBytes;
+  uint8_t* pP = wptr + 4 * Cfg::kTileBytes;
+  uint8_t* pDS = pP + Cfg::kTileBytes;
+  uint8_t* pStage = wptr + 6 * Cfg::kTileBytes;
+  const float sl2 = p.scale * kLog2e;
+
+  // 16 staged rows -> coalesced 128-bit stores (rows past `limit` are dropped)
+  auto flush_rows = [&](tvi_bf16* dst, int64_t ld, int row0, int limit) {
+    __syncwarp();
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int r = (lane >> 3) + 4 * i;
+      if (row0 + r < limit)
+        *reinterpret_cast<uint4*>(dst + (int64_t)(row0 + r) * ld + (lane & 7) * 8) =
+            *reinterpret_cast<const uint4*>(pStage + tile_off(r, lane & 7));
+    }
+    __syncwarp();
+  };
+  auto stage_acc = [&](const float (*acc)[4], float mul) {
+#pragma unroll
+    for (int nt = 0; nt < 8; ++nt) {
+      *reinterpret_cast<uint32_t*>(pStage + tile_off(g, nt) + qd * 4) = pack_bf16x2(acc[nt][0] * mul, acc[nt][1] * mul);
+      *reinterpret_cast<uint32_t*>(pStage + tile_off(g + 8, nt) + qd * 4) = pack_bf16x2(acc[nt][2] * mul, acc[nt][3] * mul);
+    }
+  };
+
+  for (int64_t item = (int64_t)blockIdx.x * Cfg::kWarps + warp; item < p.nitems; item += (int64_t)gridDim.x * Cfg::kWarps) {
+    const int64_t seq = item / p.heads;
+    const int head = (int)(item - seq * p.heads);
+    const tvi_bf16* qb = p.q + seq * p.Tq * p.ldq + head * 64;
+    const tvi_bf16* kb = p.k + seq * p.Tk * p.ldk + head * 64;
+    const tvi_bf16* vb = p.v + seq * p.Tk * p.ldv + head * 64;
+    const tvi_bf16* dob = p.dout + seq * p.Tq * p.lddo + head * 64;
+    {
+      const int c = lane & 7;
+#pragma unroll
+      for (int i = 0; i < kRows / 4; ++i) {
+        const int r = (lane >> 3) + 4 * i;
+        const uint32_t off = tile_off(r, c);
+        const bool pq = r < p.Tq, pk = r < p.Tk;
+        cp_async_16(wptr + off, pq ? qb + r * p.ldq + c * 8 : qb, pq);
+        cp_async_16(wptr + Cfg::kTileBytes + off, pk ? kb + r * p.ldk + c * 8 : kb, pk);
+        cp_async_16(wptr + 2 * Cfg::kTileBytes + off, pk ? vb + r * p.ldv + c * 8 : vb, pk);
+        cp_async_16(wptr + 3 * Cfg::kTileBytes + off, pq ? dob + r * p.lddo + c * 8 : dob, pq);
+      }
+      cp_async_commit();
+      cp_async_wait<0>();
+      __syncwarp();
+    }
+
+    // ---- phase 1: per query tile: P, dP, dS (staged as bf16) and dQ ------------------------------
+#pragma unroll
+    for (int mt = 0; mt < MT; ++mt) {
+      if (mt * 16 >= p.Tq) break;
+      float s[NT][4], dp[NT][4];
+#pragma unroll
+      for (int nt = 0; nt < NT; ++nt) {
+        s[nt][0] = s[nt][1] = s[nt][2] = s[nt][3] = 0.f;
+        dp[nt][0] = dp[nt][1] = dp[nt][2] = dp[nt][3] = 0.f;
+      }
+#pragma unroll
+      for (int ks = 0; ks < 4; ++ks) {
+        uint32_t a1[4], a2[4];
+        const uint32_t aoff = tile_off(mt * 16 + (lane & 7) + ((lane >> 3) & 1) * 8, 2 * ks + (lane >> 4));
+        ldsm_x4(sQ + aoff, a1[0], a1[1], a1[2], a1[3]);
+        ldsm_x4(sDO + aoff, a2[0], a2[1], a2[2], a2[3]);
+#pragma unroll
+        for (int np = 0; np < MT; ++np) {
+          uint32_t b0, b1, b2, b3;
+          const uint32_t boff = tile_off(np * 16 + (lane & 7) + (lane >> 4) * 8, 2 * ks + ((lane >> 3) & 1));
+          ldsm_x4(sK + boff, b0, b1, b2, b3);
+          mma_bf16_16816(s[2 * np], a1, b0, b1);
+          mma_bf16_16816(s[2 * np + 1], a1, b2, b3);
+          ldsm_x4(sV + boff, b0, b1, b2, b3);
+          mma_bf16_16816(dp[2 * np], a2, b0, b1);
+          mma_bf16_16816(dp[2 * np + 1], a2, b2, b3);
+        }
+      }
+      float m0 = -INFINITY, m1 = -INFINITY;
+#pragma unroll
+      for (int nt = 0; nt < NT; ++nt) {
+        const int col = nt * 8 + qd * 2;
+        if (col >= p.Tk) s[nt][0] = s[nt][2] = -INFINITY;
+        if (col + 1 >= p.Tk) s[nt][1] = s[nt][3] = -INFINITY;
+        m0 = fmaxf(m0, fmaxf(s[nt][0], s[nt][1]));
+        m1 = fmaxf(m1, fmaxf(s[nt][2], s[nt][3]));
+      }
+      m0 = fmaxf(m0, __shfl_xor_sync(0xffffffffu, m0, 1));
+      m0 = fmaxf(m0, __shfl_xor_sync(0xffffffffu, m0, 2));
+      m1 = fmaxf(m1, __shfl_xor_sync(0xffffffffu, m1, 1));
+      m1 = fmaxf(m1, __shfl_xor_sync(0xffffffffu, m1, 2));
+      const float ms0 = m0 * sl2, ms1 = m1 * sl2;
+      float l0 = 0.f, l1 = 0.f;
+#pragma unroll
+      for (int nt = 0; nt < NT; ++nt) {
+        s[nt][0] = fast_exp2(fmaf(s[nt][0], sl2, -ms0));
+        s[nt][1] = fast_exp2(fmaf(s[nt][1], sl2, -ms0));
+        s[nt][2] = fast_exp2(fmaf(s[nt][2], sl2, -ms1));
+        s[nt][3] = fast_exp2(fmaf(s[nt][3], sl2, -ms1));
+        l0 += s[nt][0] + s[nt][1];
+        l1 += s[nt][2] + s[nt][3];
+      }
+      l0 += __shfl_xor_sync(0xffffffffu, l0, 1);
+      l0 += __shfl_xor_sync(0xffffffffu, l0, 2);
+      l1 += __shfl_xor_sync(0xffffffffu, l1, 1);
+      l1 += __shfl_xor_sync(0xffffffffu, l1, 2);
+      const float inv0 = 1.f / l0, inv1 = 1.f / l1;
+      float D0 = 0.f, D1 = 0.f;
+#pragma unroll
+      for (int nt = 0; nt < NT; ++nt) {
+        s[nt][0] *= inv0;
+        s[nt][1] *= inv0;
+        s[nt][2] *= inv1;
+        s[nt][3] *= inv1;
+        D0 += s[nt][0] * dp[nt][0] + s[nt][1] * dp[nt][1];
+        D1 += s[nt][2] * dp[nt][2] + s[nt][3] * dp[nt][3];
+      }
+      D0 += __shfl_xor_sync(0xffffffffu, D0, 1);
+      D0 += __shfl_xor_sync(0xffffffffu, D0, 2);
+      D1 += __shfl_xor_sync(0xffffffffu, D1, 1);
+      D1 += __shfl_xor_sync(0xffffffffu, D1, 2);
+      uint32_t dfr[NT][2];
+      const int ra = mt * 16 + g, rb = ra + 8;
+#pragma unroll
+      for (int nt = 0; nt < NT; ++nt) {
+        dfr[nt][0] = pack_bf16x2(s[nt][0] * (dp[nt][0] - D0) * p.scale, s[nt][1] * (dp[nt][1] - D0) * p.scale);
+        dfr[nt][1] = pack_bf16x2(s[nt][2] * (dp[nt][2] - D1) * p.scale, s[nt][3] * (dp[nt][3] - D1) * p.scale);
+        *reinterpret_cast<uint32_t*>(pP + tile_off(ra, nt) + qd * 4) = pack_bf16x2(s[nt][0], s[nt][1]);
+        *reinterpret_cast<uint32_t*>(pP + tile_off(rb, nt) + qd * 4) = pack_bf16x2(s[nt][2], s[nt][3]);
+        *reinterpret_cast<uint32_t*>(pDS + tile_off(ra, nt) + qd * 4) = dfr[nt][0];
+        *reinterpret_cast<uint32_t*>(pDS + tile_off(rb, nt) + qd * 4) = dfr[nt][1];
+      }
+      // dQ tile = dS K
+      float acc[8][4];
+#pragma unroll
+      for (int nt = 0; nt < 8; ++nt) acc[nt][0] = acc[nt][1] = acc[nt][2] = acc[nt][3] = 0.f;
+#pragma unroll
+      for (int kk = 0; kk < MT; ++kk) {
+        if (kk * 16 >= p.Tk) break;
+        const uint32_t a[4] = {dfr[2 * kk][0], dfr[2 * kk][1], dfr[2 * kk + 1][0], dfr[2 * kk + 1][1]};
+#pragma unroll
+        for (int nc = 0; nc < 8; nc += 2) {
+          uint32_t b0, b1, b2, b3;
+          ldsm_x4_t(sK + tile_off(kk * 16 + (lane & 7) + ((lane >> 3) & 1) * 8, nc + (lane >> 4)), b0, b1, b2, b3);
+          mma_bf16_16816(acc[nc], a, b0, b1);
+          mma_bf16_16816(acc[nc + 1], a, b2, b3);
+        }
+      }
+      stage_acc(acc, 1.f);
+      flush_rows(p.dq + seq * p.Tq * p.lddq + head * 64, p.lddq, mt * 16, p.Tq);
+    }
+    __syncwarp();
+
+    // ---- phase 2: per key tile: dV = P^T dO, dK = dS^T Q (A operands re-read transposed) ---------
+#pragma unroll
+    for (int kt = 0; kt < MT; ++kt) {
+      if (kt * 16 >= p.Tk) break;
+      float av[8][4], ak[8][4];
+#pragma unroll
+      for (int nt = 0; nt < 8; ++nt) {
+        av[nt][0] = av[nt][1] = av[nt][2] = av[nt][3] = 0.f;
+        ak[nt][0] = ak[nt][1] = ak[nt][2] = ak[nt][3] = 0.f;
+      }
+#pragma unroll
+      for (int qt = 0; qt < MT; ++qt) {
+        if (qt * 16 >= p.Tq) break;
+        // A[m = key][k = query] is stored as [query][key]: ldmatrix.trans; matrix i of the x4 load =
+        // (queries 8*(i>>1).., keys 8*(i&1)..)
+        const uint32_t aoff = tile_off(qt * 16 + ((lane >> 4) & 1) * 8 + (lane & 7), 2 * kt + ((lane >> 3) & 1));
+        uint32_t ap[4], ad[4];
+        ldsm_x4_t(sP + aoff, ap[0], ap[1], ap[2], ap[3]);
+        ldsm_x4_t(sDS + aoff, ad[0], ad[1], ad[2], ad[3]);
+#pragma unroll
+        for (int nc = 0; nc < 8; nc += 2) {
+          uint32_t b0, b1, b2, b3;
+          const uint32_t boff = tile_off(qt * 16 + (lane & 7) + ((lane >> 3) & 1) * 8, nc + (lane >> 4));
+          ldsm_x4_t(sDO + boff, b0, b1, b2, b3);
+          mma_bf16_16816(av[nc], ap, b0, b1);
+          mma_bf16_16816(av[nc + 1], ap, b2, b3);
+          ldsm_x4_t(sQ + boff, b0, b1, b2, b3);
+          mma_bf16_16816(ak[nc], ad, b0, b1);
+          mma_bf16_16816(ak[nc + 1], ad, b2, b3);
+        }
+      }
+      stage_acc(av, 1.f);
+      flush_rows(p.dv + seq * p.Tk * p.lddv + head * 64, p.lddv, kt * 16, p.Tk);
+      stage_acc(ak, 1.f);
+      flush_rows(p.dk + seq * p.Tk * p.lddk + head * 64, p.lddk, kt * 16, p.Tk);
+    }
+    __syncwarp();  // the tiles are refilled by the next item
+  }
+}
+
+template <int MT>
+int launch_temporal_bwd(const TbParams& p, cudaStream_t st) {
+  using Cfg = TemporalBwdCfg<MT>;
+  static bool configured = false;
+  if (!configured) {
+    TVI_CUDA_OK(cudaFuncSetAttribute(attn_temporal_bwd_kernel<MT>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes));
+    configured = true;
+  }
+  const int per_sm = (227 * 1024) / (Cfg::kSmemBytes + 1024);
+  int64_t grid = (p.nitems + Cfg::kWarps - 1) / Cfg::kWarps;
+  const int64_t cap = (int64_t)num_sms() * (per_sm > 0 ? per_sm : 1) * 4;
+  if (grid > cap) grid = cap;
+  attn_temporal_bwd_kernel<MT><<<(unsigned)grid, Cfg::kWarps * 32, Cfg::kSmemBytes, st>>>(p);
+  TVI_LAUNCH_OK("attn_temporal_bwd_kernel");
+  return TVI_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// few-key cross attention backward
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ void unpack8b(const uint4& u, float* f) {
+  const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&u);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const float2 t = __bfloat1622float2(h[i]);
+    f[2 * i] = t.x;
+    f[2 * i + 1] = t.y;
+  }
+}
+
+constexpr int kFewBwdRowsPerThread = 32;
+
+struct FkParams {
+  const tvi_bf16 *q, *k, *v, *dout;
+  tvi_bf16 *dq, *dk, *dv;
+  float* partial;  // [groups][tiles][2][L][C] fp32 when tiles_per_group > 1
+  int64_t ldq, ldk, ldv, lddo, lddq, lddk, lddv;
+  int64_t rows_per_group;
+  int tiles_per_group, L, Tq;
+  float scale;
+  const float* bias;
+};
+
+template <int LT, int LPH>
+__global__ void __launch_bounds__(256) attn_fewkeys_bwd_kernel(const FkParams p) {
+  extern __shared__ float s_red[];  // [2][LT][C]
+  const int cx = threadIdx.x;
+  const int ry = threadIdx.y, RY = blockDim.y;
+  const int C = blockDim.x * 8;
+  const int64_t group = blockIdx.x / p.tiles_per_group;
+  const int tile = blockIdx.x - (int)(group * p.tiles_per_group);
+  const int64_t rows_per_tile = (int64_t)RY * kFewBwdRowsPerThread;
+  const int64_t rlo = group * p.rows_per_group + (int64_t)tile * rows_per_tile;
+  int64_t rhi = rlo + rows_per_tile;
+  const int64_t gend = (group + 1) * p.rows_per_group;
+  if (rhi > gend) rhi = gend;
+  const int L = p.L;
+
+  float kf[LT][8], vf[LT][8], dk[LT][8], dv[LT][8];
+#pragma unroll
+  for (int l = 0; l < LT; ++l) {
+    if (l < L) {
+      unpack8b(__ldg(reinterpret_cast<const uint4*>(p.k + (group * L + l) * p.ldk + cx * 8)), kf[l]);
+      unpack8b(__ldg(reinterpret_cast<const uint4*>(p.v + (group * L + l) * p.ldv + cx * 8)), vf[l]);
+    } else {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) kf[l][j] = vf[l][j] = 0.f;
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) dk[l][j] = dv[l][j] = 0.f;
+  }
+
+  for (int it = 0; it < kFewBwdRowsPerThread; ++it) {
+    if (rlo + (int64_t)it * RY >= rhi) break;  // block-uniform
+    const int64_t rr = rlo + (int64_t)it * RY + ry;
+    const bool act = rr < rhi;
+    const int64_t r = act ? rr : rlo;
+    float qf[8], gof[8];
+    if (p.q != nullptr) unpack8b(__ldg(reinterpret_cast<const uint4*>(p.q + r * p.ldq + cx * 8)), qf);
+    else {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) qf[j] = 0.f;
+    }
+    unpack8b(__ldg(reinterpret_cast<const uint4*>(p.dout + r * p.lddo + cx * 8)), gof);
+    float logit[LT], dpv[LT];
+#pragma unroll
+    for (int l = 0; l < LT; ++l) {
+      float a = 0.f, b2 = 0.f;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        a = fmaf(qf[j], kf[l][j], a);
+        b2 = fmaf(gof[j], vf[l][j], b2);
+      }
+#pragma unroll
+      for (int off = LPH / 2; off > 0; off >>= 1) {
+        a += __shfl_xor_sync(0xffffffffu, a, off);
+        b2 += __shfl_xor_sync(0xffffffffu, b2, off);
+      }
+      logit[l] = a * p.scale;
+      dpv[l] = b2;
+    }
+    if (p.bias != nullptr) {
+      const int t = (int)(r % p.Tq);
+#pragma unroll
+      for (int l = 0; l < LT; ++l)
+        if (l < L) logit[l] += __ldg(p.bias + t * L + l);
+    }
+    float m = -INFINITY;
+#pragma unroll
+    for (int l = 0; l < LT; ++l) {
+      if (l >= L) logit[l] = -INFINITY;
+      m = fmaxf(m, logit[l]);
+    }
+    float sum = 0.f, pr[LT];
+#pragma unroll
+    for (int l = 0; l < LT; ++l) {
+      pr[l] = __expf(logit[l] - m);
+      sum += pr[l];
+    }
+    const float inv = act ? 1.f / sum : 0.f;  // inactive rows contribute nothing
+    float Dd = 0.f;
+#pragma unroll
+    for (int l = 0; l < LT; ++l) {
+      pr[l] *= inv;
+      Dd = fmaf(pr[l], dpv[l], Dd);
+    }
+    float dqf[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) dqf[j] = 0.f;
+#pragma unroll
+    for (int l = 0; l < LT; ++l) {
+      const float ds = pr[l] * (dpv[l] - Dd) * p.scale;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        dqf[j] = fmaf(ds, kf[l][j], dqf[j]);
+        dk[l][j] = fmaf(ds, qf[j], dk[l][j]);
+        dv[l][j] = fmaf(pr[l], gof[j], dv[l][j]);
+      }
+    }
+    if (act && p.dq != nullptr) {
+      uint4 o;
+      o.x = pack_bf16x2(dqf[0], dqf[1]);
+      o.y = pack_bf16x2(dqf[2], dqf[3]);
+      o.z = pack_bf16x2(dqf[4], dqf[5]);
+      o.w = pack_bf16x2(dqf[6], dqf[7]);
+      *reinterpret_cast<uint4*>(p.dq + r * p.lddq + cx * 8) = o;
+    }
+  }
+
+  // ---- fixed-order reduction over the CTA's row lanes ---------------------------------------------
+  for (int t = 0; t < RY; ++t) {
+    if (ry == t) {
+#pragma unroll
+      for (int l = 0; l < LT; ++l) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          float* a = &s_red[(0 * LT + l) * C + cx * 8 + j];
+          float* b2 = &s_red[(1 * LT + l) * C + cx * 8 + j];
+          *a = (t == 0 ? 0.f : *a) + dk[l][j];
+          *b2 = (t == 0 ? 0.f : *b2) + dv[l][j];
+        }
+      }
+    }
+    __syncthreads();
+  }
+  if (ry == 0) {
+#pragma unroll
+    for (int l = 0; l < LT; ++l) {
+      if (l >= L) continue;
+      const float* a = &s_red[(0 * LT + l) * C + cx * 8];
+      const float* b2 = &s_red[(1 * LT + l) * C + cx * 8];
+      if (p.tiles_per_group == 1) {
+        uint4 o;
+        o.x = pack_bf16x2(a[0], a[1]);
+        o.y = pack_bf16x2(a[2], a[3]);
+        o.z = pack_bf16x2(a[4], a[5]);
+        o.w = pack_bf16x2(a[6], a[7]);
+        *reinterpret_cast<uint4*>(p.dk + (group * L + l) * p.lddk + cx * 8) = o;
+        o.x = pack_bf16x2(b2[0], b2[1]);
+        o.y = pack_bf16x2(b2[2], b2[3]);
+        o.z = pack_bf16x2(b2[4], b2[5]);
+        o.w = pack_bf16x2(b2[6], b2[7]);
+        *reinterpret_cast<uint4*>(p.dv + (group * L + l) * p.lddv + cx * 8) = o;
+      } else {
+        float* dst = p.partial + (((group * p.tiles_per_group + tile) * 2 + 0) * (int64_t)L + l) * C + cx * 8;
+        *reinterpret_cast<float4*>(dst) = make_float4(a[0], a[1], a[2], a[3]);
+        *reinterpret_cast<float4*>(dst + 4) = make_float4(a[4], a[5], a[6], a[7]);
+        dst = p.partial + (((group * p.tiles_per_group + tile) * 2 + 1) * (int64_t)L + l) * C + cx * 8;
+        *reinterpret_cast<float4*>(dst) = make_float4(b2[0], b2[1], b2[2], b2[3]);
+        *reinterpret_cast<float4*>(dst + 4) = make_float4(b2[4], b2[5], b2[6], b2[7]);
+      }
+    }
+  }
+}
+
+__global__ void fewkeys_bwd_final_kernel(const float* __restrict__ partial, tvi_bf16* __restrict__ dk, tvi_bf16* __restrict__ dv,
+                                         int64_t ngroups, int tiles, int L, int C, int64_t lddk, int64_t lddv) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;  // (group, which, l, column pair)
+  const int half = C / 2;
+  const int64_t total = ngroups * 2 * L * half;
+  if (i >= total) return;
+  const int cp = (int)(i % half);
+  const int l = (int)((i / half) % L);
+  const int which = (int)((i / ((int64_t)half * L)) % 2);
+  const int64_t g = i / ((int64_t)half * L * 2);
+  float a = 0.f, b = 0.f;
+  for (int t = 0; t < tiles; ++t) {
+    const float2 v = *reinterpret_cast<const float2*>(partial + (((g * tiles + t) * 2 + which) * (int64_t)L + l) * C + cp * 2);
+    a += v.x;
+    b += v.y;
+  }
+  tvi_bf16* dst = which == 0 ? dk + (g * L + l) * lddk : dv + (g * L + l) * lddv;
+  *reinterpret_cast<uint32_t*>(dst + cp * 2) = pack_bf16x2(a, b);
+}
+
+int fk_block_rows(int C8) {
+  const int unit = (C8 % 32 == 0) ? 1 : (C8 % 16 == 0) ? 2 : 4;
+  int RY = unit * (256 / (C8 * unit) > 0 ? 256 / (C8 * unit) : 1);
+  return RY;
+}
+
+int fk_tiles(int64_t rows_per_group, int C8) {
+  const int64_t rows_per_tile = (int64_t)fk_block_rows(C8) * kFewBwdRowsPerThread;
+  return (int)((rows_per_group + rows_per_tile - 1) / rows_per_tile);
+}
+
+template <int LT, int LPH>
+int launch_fewkeys_bwd(const FkParams& p, int64_t ngroups, int C8, cudaStream_t st) {
+  const int RY = fk_block_rows(C8);
+  TVI_CHECK_ARG(C8 * RY <= 256, "tvi_attn_fewkeys_bwd: heads*d = %d is too wide for this kernel", C8 * 8);
+  const size_t sm = (size_t)2 * LT * C8 * 8 * sizeof(float);
+  TVI_CHECK_ARG(sm <= 160 * 1024, "tvi_attn_fewkeys_bwd: L*heads*d too large for the reduction buffer");
+  static size_t configured = 0;
+  if (sm > 48 * 1024 && sm > configured) {
+    TVI_CUDA_OK(cudaFuncSetAttribute(attn_fewkeys_bwd_kernel<LT, LPH>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
+    configured = sm;
+  }
+  TVI_CHECK_ARG((int64_t)p.tiles_per_group * ngroups < ((int64_t)1 << 31), "tvi_attn_fewkeys_bwd: grid too large");
+  dim3 block((unsigned)C8, (unsigned)RY);
+  dim3 grid((unsigned)(p.tiles_per_group * ngroups));
+  attn_fewkeys_bwd_kernel<LT, LPH><<<grid, block, sm, st>>>(p);
+  TVI_LAUNCH_OK("attn_fewkeys_bwd_kernel");
+  return TVI_OK;
+}
+
+}  // namespace
+}  // namespace tvi
+
+extern "C" {
+
+size_t tvi_attn_spatial_bwd_workspace_bytes(int batch, int heads, int S) {
+  if (batch <= 0 || heads <= 0 || S <= 0) return 0;
+  return (size_t)batch * S * heads * sizeof(float);
+}
+
+int tvi_attn_spatial_bwd(const tvi_bf16* q, const tvi_bf16* k, const tvi_bf16* v, const tvi_bf16* o, const tvi_bf16* dout,
+                         const float* lse, tvi_bf16* dq, tvi_bf16* dk, tvi_bf16* dv, void* workspace, int batch, int heads,
+                         int S, int Skv, int d, int64_t ldq, int64_t ldk, int64_t ldv, int64_t ldo, int64_t lddo,
+                         int64_t lddq, int64_t lddk, int64_t lddv, float scale, void* stream) {
+  using namespace tvi;
+  TVI_CHECK_ARG(batch >= 0 && heads >= 0 && S >= 0 && Skv >= 0, "tvi_attn_spatial_bwd: negative size");
+  if (batch == 0 || heads == 0 || S == 0) return TVI_OK;
+  TVI_CHECK_ARG(Skv >= 1, "tvi_attn_spatial_bwd: softmax over zero keys is undefined");
+  TVI_CHECK_ARG(q && k && v && o && dout && lse && dq && dk && dv && workspace, "tvi_attn_spatial_bwd: null pointer");
+  if (d != 64) return fail(TVI_ERR_UNSUPPORTED, "tvi_attn_spatial_bwd: head dim %d (only 64 is built)", d);
+  TVI_CHECK_ARG((ldq | ldk | ldv | ldo | lddo | lddq | lddk | lddv) % 8 == 0, "tvi_attn_spatial_bwd: row strides must be multiples of 8 elements");
+  const int64_t C = (int64_t)heads * 64;
+  TVI_CHECK_ARG(ldq >= C && ldk >= C && ldv >= C && ldo >= C && lddo >= C && lddq >= C && lddk >= C && lddv >= C,
+                "tvi_attn_spatial_bwd: row stride smaller than heads*d");
+  TVI_CHECK_ARG(((uintptr_t)q | (uintptr_t)k | (uintptr_t)v | (uintptr_t)o | (uintptr_t)dout | (uintptr_t)dq | (uintptr_t)dk |
+                 (uintptr_t)dv) % 16 == 0, "tvi_attn_spatial_bwd: pointers must be 16-byte aligned");
+  TVI_CHECK_ARG((int64_t)batch * heads <= 65535, "tvi_attn_spatial_bwd: batch*heads exceeds 65535");
+  cudaStream_t st = (cudaStream_t)stream;
+  float* D = (float*)workspace;
+  {
+    const int64_t nrows = (int64_t)batch * S;
+    const int64_t threads = nrows * heads * 8;
+    attn_bwd_dot_kernel<<<(unsigned)((threads + 255) / 256), 256, 0, st>>>(o, dout, D, nrows, heads, ldo, lddo);
+    TVI_LAUNCH_OK("attn_bwd_dot_kernel");
+  }
+  FbParams p;
+  p.lse = lse;
+  p.D = D;
+  p.heads = heads;
+  p.scale = scale;
+  // pass 1: rows = keys -> dK, dV
+  p.r1 = k; p.ldr1 = ldk; p.r2 = v; p.ldr2 = ldv;
+  p.c1 = q; p.ldc1 = ldq; p.c2 = dout; p.ldc2 = lddo;
+  p.out1 = dk; p.ldo1 = lddk; p.out2 = dv; p.ldo2 = lddv;
+  p.nrows = Skv; p.ncols = S;
+  int rc = launch_flash_bwd<true>(p, batch, st);
+  if (rc) return rc;
+  // pass 2: rows = queries -> dQ
+  p.r1 = q; p.ldr1 = ldq; p.r2 = dout; p.ldr2 = lddo;
+  p.c1 = k; p.ldc1 = ldk; p.c2 = v; p.ldc2 = ldv;
+  p.out1 = dq; p.ldo1 = lddq; p.out2 = nullptr; p.ldo2 = 0;
+  p.nrows = S; p.ncols = Skv;
+  return launch_flash_bwd<false>(p, batch, st);
+}
+
+int tvi_attn_temporal_bwd(const tvi_bf16* q, const tvi_bf16* k, const tvi_bf16* v, const tvi_bf16* dout, tvi_bf16* dq,
+                          tvi_bf16* dk, tvi_bf16* dv, int64_t nseq, int heads, int Tq, int Tk, int d, int64_t ldq, int64_t ldk,
+                          int64_t ldv, int64_t lddo, int64_t lddq, int64_t lddk, int64_t lddv, float scale, void* stream) {
+  using namespace tvi;
+  TVI_CHECK_ARG(nseq >= 0 && heads >= 0, "tvi_attn_temporal_bwd: negative size");
+  if (nseq == 0 || heads == 0) return TVI_OK;
+  TVI_CHECK_ARG(q && k && v && dout && dq && dk && dv, "tvi_attn_temporal_bwd: null pointer");
+  if (d != 64) return fail(TVI_ERR_UNSUPPORTED, "tvi_attn_temporal_bwd: head dim %d (only 64 is built)", d);
+  TVI_CHECK_ARG(Tq >= 1 && Tq <= 64 && Tk >= 1 && Tk <= 64, "tvi_attn_temporal_bwd: Tq=%d Tk=%d outside [1,64]", Tq, Tk);
+  TVI_CHECK_ARG((ldq | ldk | ldv | lddo | lddq | lddk | lddv) % 8 == 0, "tvi_attn_temporal_bwd: row strides must be multiples of 8 elements");
+  const int64_t C = (int64_t)heads * 64;
+  TVI_CHECK_ARG(ldq >= C && ldk >= C && ldv >= C && lddo >= C && lddq >= C && lddk >= C && lddv >= C,
+                "tvi_attn_temporal_bwd: row stride smaller than heads*d");
+  TVI_CHECK_ARG(((uintptr_t)q | (uintptr_t)k | (uintptr_t)v | (uintptr_t)dout | (uintptr_t)dq | (uintptr_t)dk | (uintptr_t)dv) % 16 == 0,
+                "tvi_attn_temporal_bwd: pointers must be 16-byte aligned");
+  TbParams p;
+  p.q = q; p.k = k; p.v = v; p.dout = dout; p.dq = dq; p.dk = dk; p.dv = dv;
+  p.ldq = ldq; p.ldk = ldk; p.ldv = ldv; p.lddo = lddo; p.lddq = lddq; p.lddk = lddk; p.lddv = lddv;
+  p.nitems = nseq * heads;
+  p.heads = heads; p.Tq = Tq; p.Tk = Tk; p.scale = scale;
+  const int T = Tq > Tk ? Tq : Tk;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (T <= 16) return launch_temporal_bwd<1>(p, st);
+  if (T <= 32) return launch_temporal_bwd<2>(p, st);
+  return launch_temporal_bwd<4>(p, st);
+}
+
+size_t tvi_attn_fewkeys_bwd_workspace_bytes(int64_t nrows, int64_t rows_per_group, int heads, int L, int d) {
+  if (nrows <= 0 || rows_per_group <= 0 || heads <= 0 || L <= 0 || d <= 0) return 0;
+  const int C = heads * d;
+  const int tiles = tvi::fk_tiles(rows_per_group, C / 8);
+  if (tiles == 1) return 0;
+  return (size_t)(nrows / rows_per_group) * tiles * 2 * L * (size_t)C * sizeof(float);
+}
+
+int tvi_attn_fewkeys_bwd(const tvi_bf16* q, const tvi_bf16* k, const tvi_bf16* v, const tvi_bf16* dout, tvi_bf16* dq,
+                         tvi_bf16* dk, tvi_bf16* dv, void* workspace, int64_t nrows, int64_t rows_per_group, int heads, int L,
+                         int d, int64_t ldq, int64_t ldk, int64_t ldv, int64_t lddo, int64_t lddq, int64_t lddk,
+                         int64_t lddv, float scale, int Tq, const float* bias, void* stream) {
+  using namespace tvi;
+  TVI_CHECK_ARG(nrows >= 0 && heads >= 0, "tvi_attn_fewkeys_bwd: negative size");
+  if (nrows == 0 || heads == 0) return TVI_OK;
+  TVI_CHECK_ARG(k && v && dout && dk && dv, "tvi_attn_fewkeys_bwd: null pointer");
+  TVI_CHECK_ARG((q == nullptr) == (dq == nullptr), "tvi_attn_fewkeys_bwd: q and dq must both be given or both be null");
+  TVI_CHECK_ARG(q != nullptr || L == 1, "tvi_attn_fewkeys_bwd: q may only be null when L == 1");
+  if (d != 64 && d != 128) return fail(TVI_ERR_UNSUPPORTED, "tvi_attn_fewkeys_bwd: head dim %d (64 and 128 are built)", d);
+  TVI_CHECK_ARG(L >= 1 && L <= 8, "tvi_attn_fewkeys_bwd: L=%d outside [1,8]", L);
+  TVI_CHECK_ARG(rows_per_group >= 1 && nrows % rows_per_group == 0, "tvi_attn_fewkeys_bwd: nrows must be a multiple of rows_per_group");
+  TVI_CHECK_ARG(Tq >= 1, "tvi_attn_fewkeys_bwd: Tq must be >= 1");
+  const int C = heads * d;
+  TVI_CHECK_ARG((ldk | ldv | lddo | lddk | lddv) % 8 == 0 && (q == nullptr || (ldq | lddq) % 8 == 0),
+                "tvi_attn_fewkeys_bwd: row strides must be multiples of 8 elements");
+  TVI_CHECK_ARG(((uintptr_t)q | (uintptr_t)k | (uintptr_t)v | (uintptr_t)dout | (uintptr_t)dq | (uintptr_t)dk | (uintptr_t)dv) % 16 == 0,
+                "tvi_attn_fewkeys_bwd: pointers must be 16-byte aligned");
+  const int64_t ngroups = nrows / rows_per_group;
+  FkParams p;
+  p.q = q; p.k = k; p.v = v; p.dout = dout; p.dq = dq; p.dk = dk; p.dv = dv;
+  p.partial = (float*)workspace;
+  p.ldq = ldq; p.ldk = ldk; p.ldv = ldv; p.lddo = lddo; p.lddq = lddq; p.lddk = lddk; p.lddv = lddv;
+  p.rows_per_group = rows_per_group;
+  p.tiles_per_group = fk_tiles(rows_per_group, C / 8);
+  p.L = L; p.Tq = Tq; p.scale = scale; p.bias = bias;
+  TVI_CHECK_ARG(p.tiles_per_group == 1 || (workspace != nullptr && (uintptr_t)workspace % 16 == 0),
+                "tvi_attn_fewkeys_bwd: workspace required (16-byte aligned)");
+  cudaStream_t st = (cudaStream_t)stream;
+  int rc;
+#define TVI_FEWB(LT) (d == 64 ? launch_fewkeys_bwd<LT, 8>(p, ngroups, C / 8, st) : launch_fewkeys_bwd<LT, 16>(p, ngroups, C / 8, st))
+  if (L == 1) rc = TVI_FEWB(1);
+  else if (L == 2) rc = TVI_FEWB(2);
+  else if (L <= 4) rc = TVI_FEWB(4);
+  else rc = TVI_FEWB(8);
+#undef TVI_FEWB
+  if (rc != TVI_OK) return rc;
+  if (p.tiles_per_group > 1) {
+    const int64_t total = ngroups * 2 * L * (C / 2);
+    fewkeys_bwd_final_kernel<<<(unsigned)((total + 255) / 256), 256, 0, st>>>((const float*)workspace, dk, dv, ngroups,
+                                                                              p.tiles_per_group, L, C, lddk, lddv);
+    TVI_LAUNCH_OK("fewkeys_bwd_final_kernel");
+  }
+  return TVI_OK;
+}
+
+}  // extern "C"

@@ -219,6 +219,87 @@ def attn_spatial(q, k, v, batch: int, heads: int, S: int, Skv: int, scale: float
     return out
 
 
+def _grad_like(t, rows, width):
+    return torch.empty(rows, width, dtype=torch.bfloat16, device=t.device)
+
+
+def attn_spatial_bwd(q, k, v, o, dout, lse, batch: int, heads: int, S: int, Skv: int, scale: float, dq=None, dk=None, dv=None):
+    """Gradients of the flash spatial core; q/k/v/o/dout are [rows, heads*64] row views, lse the forward's
+    [batch*S, heads] fp32 log-sum-exp.  Returns (dq, dk, dv)."""
+    _need_cuda(q, k, v, o, dout, lse)
+    q, ldq = _rows2d(q, "q")
+    k, ldk = _rows2d(k, "k")
+    v, ldv = _rows2d(v, "v")
+    o, ldo = _rows2d(o, "o")
+    dout, lddo = _rows2d(dout, "dout")
+    C_ = q.shape[-1]
+    d = C_ // heads
+    dq = _grad_like(q, batch * S, C_) if dq is None else dq
+    dk = _grad_like(q, batch * Skv, C_) if dk is None else dk
+    dv = _grad_like(q, batch * Skv, C_) if dv is None else dv
+    dq, lddq = _rows2d(dq, "dq")
+    dk, lddk = _rows2d(dk, "dk")
+    dv, lddv = _rows2d(dv, "dv")
+    if lse.dtype != torch.float32 or not lse.is_contiguous() or lse.numel() != batch * S * heads:
+        raise _lib.TviError(_lib.TVI_ERR_INVALID, "lse must be a contiguous fp32 [batch*S, heads] tensor")
+    lib = _lib.load()
+    ws = _workspace(lib.tvi_attn_spatial_bwd_workspace_bytes(batch, heads, S), q.device)
+    _hooked("attn_spatial_bwd", 3, lib.tvi_attn_spatial_bwd, q.data_ptr(), k.data_ptr(), v.data_ptr(), o.data_ptr(),
+            dout.data_ptr(), lse.data_ptr(), dq.data_ptr(), dk.data_ptr(), dv.data_ptr(), ws.data_ptr(), batch, heads, S, Skv,
+            d, ldq, ldk, ldv, ldo, lddo, lddq, lddk, lddv, float(scale), _stream())
+    return dq, dk, dv
+
+
+def attn_temporal_bwd(q, k, v, dout, nseq: int, heads: int, Tq: int, Tk: int, scale: float, dq=None, dk=None, dv=None):
+    """Gradients of the short-sequence core (recomputes the T x T softmax; needs neither o nor lse)."""
+    _need_cuda(q, k, v, dout)
+    q, ldq = _rows2d(q, "q")
+    k, ldk = _rows2d(k, "k")
+    v, ldv = _rows2d(v, "v")
+    dout, lddo = _rows2d(dout, "dout")
+    C_ = q.shape[-1]
+    d = C_ // heads
+    dq = _grad_like(q, nseq * Tq, C_) if dq is None else dq
+    dk = _grad_like(q, nseq * Tk, C_) if dk is None else dk
+    dv = _grad_like(q, nseq * Tk, C_) if dv is None else dv
+    dq, lddq = _rows2d(dq, "dq")
+    dk, lddk = _rows2d(dk, "dk")
+    dv, lddv = _rows2d(dv, "dv")
+    _hooked("attn_temporal_bwd", 1, _lib.load().tvi_attn_temporal_bwd, q.data_ptr(), k.data_ptr(), v.data_ptr(),
+            dout.data_ptr(), dq.data_ptr(), dk.data_ptr(), dv.data_ptr(), nseq, heads, Tq, Tk, d, ldq, ldk, ldv, lddo, lddq,
+            lddk, lddv, float(scale), _stream())
+    return dq, dk, dv
+
+
+def attn_fewkeys_bwd(q, k, v, dout, nrows: int, rows_per_group: int, heads: int, L: int, scale: float, Tq: int = 1, bias=None,
+                     dq=None, dk=None, dv=None):
+    """Gradients of the few-keys core; returns (dq or None, dk, dv) with dk/dv [ngroups*L, heads*d]."""
+    _need_cuda(q, k, v, dout, bias)
+    k, ldk = _rows2d(k, "k")
+    v, ldv = _rows2d(v, "v")
+    dout, lddo = _rows2d(dout, "dout")
+    C_ = k.shape[-1]
+    d = C_ // heads
+    ngroups = nrows // rows_per_group
+    ldq = lddq = 0
+    if q is not None:
+        q, ldq = _rows2d(q, "q")
+        dq = _grad_like(k, nrows, C_) if dq is None else dq
+        dq, lddq = _rows2d(dq, "dq")
+    dk = _grad_like(k, ngroups * L, C_) if dk is None else dk
+    dv = _grad_like(k, ngroups * L, C_) if dv is None else dv
+    dk, lddk = _rows2d(dk, "dk")
+    dv, lddv = _rows2d(dv, "dv")
+    lib = _lib.load()
+    nb = lib.tvi_attn_fewkeys_bwd_workspace_bytes(nrows, rows_per_group, heads, L, d)
+    ws = _workspace(nb, k.device)
+    _hooked("attn_fewkeys_bwd", 2 if nb else 1, lib.tvi_attn_fewkeys_bwd, q.data_ptr() if q is not None else None,
+            k.data_ptr(), v.data_ptr(), dout.data_ptr(), dq.data_ptr() if q is not None else None, dk.data_ptr(),
+            dv.data_ptr(), ws.data_ptr() if ws is not None else None, nrows, rows_per_group, heads, L, d, ldq, ldk, ldv,
+            lddo, lddq, lddk, lddv, float(scale), Tq, bias.data_ptr() if bias is not None else None, _stream())
+    return (dq if q is not None else None), dk, dv
+
+
 def slerp_f32(v0: torch.Tensor, v1: torch.Tensor, T: int, dot_threshold: float, out=None) -> torch.Tensor:
     global LAUNCHES
     _need_cuda(v0, v1)
