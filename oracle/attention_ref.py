@@ -110,3 +110,37 @@ def ca_temporal_forward_ref(attn, hidden_states, encoder_hidden_states=None, use
     p = torch.softmax(w, dim=-1)                                                       # :474
     o = (p @ v).transpose(1, 2).reshape(B, -1, wq.shape[0])                            # :476, :483
     return F.linear(o, wo, bo), stats                                                  # :486
+
+
+def attn_processor_grads_ref(attn, hidden_states, encoder_hidden_states, grad_output, use_attentionmask=False,
+                             dtype=torch.float32):
+    """Gradients of the processor call by torch autograd on CPU — what the reference's training scripts
+    compute (src/train_decouples.py back-propagates through AttnProcessor2_0 / the patched temporal
+    forward with plain autograd; there is no custom backward in the reference).
+
+    Same math as attn_processor_ref / ca_temporal_forward_ref (the optional (T,2) ramp bias of
+    :437-457 is a constant).  Returns (output, grads) with grads keyed
+    x, e, to_q, to_k, to_v, to_out_w, to_out_b; `e` is None for self-attention.
+    """
+    x = hidden_states.detach().to("cpu", dtype).requires_grad_(True)
+    do_cross = encoder_hidden_states is not None
+    e = encoder_hidden_states.detach().to("cpu", dtype).requires_grad_(True) if do_cross else None
+    heads = int(attn.heads)
+    ws = {n: getattr(attn, n).weight.detach().to("cpu", dtype).requires_grad_(True) for n in ("to_q", "to_k", "to_v")}
+    wo = attn.to_out[0].weight.detach().to("cpu", dtype).requires_grad_(True)
+    bo = attn.to_out[0].bias.detach().to("cpu", dtype).requires_grad_(True)
+    src = e if do_cross else x
+    query = head_to_batch_dim(F.linear(x, ws["to_q"]), heads)
+    key = head_to_batch_dim(F.linear(src, ws["to_k"]), heads)
+    value = head_to_batch_dim(F.linear(src, ws["to_v"]), heads)
+    bias = None
+    if use_attentionmask and do_cross:
+        L = x.shape[1]
+        w = torch.linspace(0, 1, steps=L, dtype=dtype)
+        bias = torch.stack([1 - w, w], dim=1)[None]
+    probs, _ = get_attention_scores(query, key, float(attn.scale), bias)
+    out = F.linear(batch_to_head_dim(torch.bmm(probs, value), heads), wo, bo)
+    out.backward(grad_output.detach().to("cpu", dtype))
+    grads = {"x": x.grad, "e": e.grad if do_cross else None, "to_q": ws["to_q"].grad, "to_k": ws["to_k"].grad,
+             "to_v": ws["to_v"].grad, "to_out_w": wo.grad, "to_out_b": bo.grad}
+    return out.detach(), grads

@@ -188,3 +188,101 @@ def test_fewkeys_bwd_matches_autograd(cuda, ngroups, rpg, heads, L, use_bias):
     _grad_close(dq, rq, "fewkeys dq")
     _grad_close(dk, rk, "fewkeys dk")
     _grad_close(dv, rv, "fewkeys dv")
+
+
+# ------------------------------------------------------------------------------------------------
+# whole processor calls on the autograd tape vs torch autograd of the oracle (gradients
+# within 2e-2 of max|grad| against the fp32 oracle fed the same bf16-rounded inputs and weights)
+# ------------------------------------------------------------------------------------------------
+from oracle import attention_ref  # noqa: E402
+from util import make_attn  # noqa: E402
+from timelapse_video_interpolation_b200 import TviAttnProcessor  # noqa: E402
+
+
+def _processor_grads(attn, x, e, dy):
+    for p in attn.parameters():
+        p.grad = None
+    xg = x.detach().clone().requires_grad_(True)
+    eg = e.detach().clone().requires_grad_(True) if e is not None else None
+    y = attn(xg, encoder_hidden_states=eg)
+    y.backward(dy)
+    torch.cuda.synchronize()
+    return y.detach(), {"x": xg.grad, "e": eg.grad if eg is not None else None, "to_q": attn.to_q.weight.grad,
+                        "to_k": attn.to_k.weight.grad, "to_v": attn.to_v.weight.grad,
+                        "to_out_w": attn.to_out[0].weight.grad, "to_out_b": attn.to_out[0].bias.grad}
+
+
+def _compare_grads(got, ref, what, zero_ok=()):
+    for key, r in ref.items():
+        gk = got[key]
+        if r is None:
+            assert gk is None, f"{what}: unexpected gradient for {key}"
+            continue
+        assert gk is not None, f"{what}: missing gradient for {key}"
+        assert gk.shape == r.shape, (what, key, gk.shape, r.shape)
+        if float(r.abs().max()) == 0.0 or key in zero_ok:
+            assert float(gk.float().abs().max()) <= 1e-6 + 2e-2 * float(r.abs().max()), f"{what}: {key} should vanish"
+            continue
+        _grad_close(gk.cpu(), r, f"{what} d{key}")
+
+
+@pytest.mark.parametrize("name,Bp,S,C,heads,cross,L,ramp", [
+    ("temporal self T=14", 288, 14, 320, 5, None, None, False),
+    ("temporal self T=25", 64, 25, 640, 10, None, None, False),
+    ("spatial self S=144", 4, 144, 1280, 20, None, None, False),
+    ("spatial self S=576", 2, 576, 320, 5, None, None, False),
+    ("spatial self S=1152 (tcgen05 forward)", 2, 1152, 320, 5, None, None, False),
+    ("spatial cross L=2", 4, 576, 320, 5, 1024, 2, False),
+    ("spatial cross L=1", 4, 576, 320, 5, 1024, 1, False),
+    ("temporal cross L=2 + ramp bias", 144, 14, 320, 5, 1024, 2, True),
+    ("temporal cross L=1", 144, 14, 640, 10, 1024, 1, False),
+])
+def test_processor_gradients_match_oracle_autograd(cuda, name, Bp, S, C, heads, cross, L, ramp):
+    attn = make_attn(C, cross, heads, seed=7, device=cuda, dtype=torch.bfloat16,
+                     processor=TviAttnProcessor(ramp_bias=ramp))
+    attn.train()
+    g = torch.Generator().manual_seed(S + C)
+    x = torch.randn(Bp, S, C, generator=g).to(torch.bfloat16).to(cuda)
+    e = torch.randn(Bp, L, cross, generator=g).to(torch.bfloat16).to(cuda) if cross else None
+    dy = (torch.randn(Bp, S, C, generator=g) / S ** 0.5).to(torch.bfloat16).to(cuda)
+    y, got = _processor_grads(attn, x, e, dy)
+    ry, ref = attention_ref.attn_processor_grads_ref(attn, x, e, dy, use_attentionmask=ramp)
+    _grad_close(y.cpu(), ry, f"{name} y")
+    # one key: the softmax is constant, so x / to_q / to_k receive exactly zero
+    _compare_grads(got, ref, name, zero_ok=("x", "to_q", "to_k") if L == 1 else ())
+
+
+def test_processor_backward_with_frozen_spatial_weights_and_checkpoint(cuda):
+    # train_decouples freezes everything but temporal_transformer_block*: spatial modules only pass
+    # gradients through to x; blocks run under torch.utils.checkpoint(use_reentrant=False)
+    # (src/models/transformer_temporal.py:322-327)
+    from torch.utils.checkpoint import checkpoint
+    attn = make_attn(320, None, 5, seed=3, device=cuda, dtype=torch.bfloat16, processor=TviAttnProcessor())
+    for p in attn.parameters():
+        p.requires_grad_(False)
+    g = torch.Generator().manual_seed(5)
+    x = torch.randn(2, 576, 320, generator=g).to(torch.bfloat16).to(cuda).requires_grad_(True)
+    dy = (torch.randn(2, 576, 320, generator=g) / 24).to(torch.bfloat16).to(cuda)
+    y = checkpoint(lambda t: attn(t), x, use_reentrant=False)
+    y.backward(dy)
+    torch.cuda.synchronize()
+    assert all(p.grad is None for p in attn.parameters())
+    _, ref = attention_ref.attn_processor_grads_ref(attn, x, None, dy)
+    _grad_close(x.grad.cpu(), ref["x"], "frozen-weights dx under checkpoint")
+
+
+def test_processor_backward_fp32_parameters_cast_inputs(cuda):
+    # the reference's shipped training configs keep fp32 parameters: gradients come back in fp32
+    attn = make_attn(320, None, 5, seed=4, device=cuda, dtype=torch.float32, processor=TviAttnProcessor(cast_inputs=True))
+    g = torch.Generator().manual_seed(6)
+    x = torch.randn(36, 14, 320, generator=g).to(cuda).requires_grad_(True)
+    dy = torch.randn(36, 14, 320, generator=g).to(cuda) / 4
+    y = attn(x)
+    assert y.dtype == torch.float32
+    y.backward(dy)
+    torch.cuda.synchronize()
+    assert attn.to_q.weight.grad.dtype == torch.float32 and x.grad.dtype == torch.float32
+    ref_attn = make_attn(320, None, 5, seed=4)
+    _, ref = attention_ref.attn_processor_grads_ref(ref_attn, x, None, dy)
+    _grad_close(x.grad.cpu(), ref["x"], "fp32 dx", tol=3e-2)
+    _grad_close(attn.to_v.weight.grad.cpu(), ref["to_v"], "fp32 dWv", tol=3e-2)

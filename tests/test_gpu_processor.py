@@ -98,11 +98,15 @@ def test_non_bf16_requires_opt_in(cuda):
     assert max_abs(y.cpu(), attention_ref.attn_processor_ref(attn, x.cpu())) < 2 * TOL
 
 
-def test_gradients_are_refused_not_dropped(cuda):
+def test_gradients_flow_through_the_processor(cuda):
+    # the full gradient parity suite is tests/test_gpu_backward.py; here: the call is on the autograd tape
     attn = make_attn(128, None, 2, seed=1, device=cuda, dtype=torch.bfloat16, processor=TviAttnProcessor())
     x = torch.randn(2, 14, 128, device=cuda, dtype=torch.bfloat16, requires_grad=True)
-    with pytest.raises(NotImplementedError):
-        attn(x)
+    y = attn(x)
+    assert y.requires_grad
+    y.float().sum().backward()
+    assert x.grad is not None and x.grad.shape == x.shape and bool(torch.isfinite(x.grad.float()).all())
+    assert attn.to_q.weight.grad is not None and attn.to_out[0].bias.grad is not None
 
 
 def test_launch_counter_counts_only_libtvi_kernels(cuda):

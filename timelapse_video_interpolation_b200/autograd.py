@@ -1,18 +1,28 @@
-"""Kernel sequencing of one attention call (forward), shared by the processor and the benchmarks.
+"""Kernel sequencing of one attention call, forward and backward, shared by the processor and the benchmarks.
 
 `attention_forward` is what `TviAttnProcessor.__call__` runs after validating the module: it only
-orders libtvi launches and owns the intermediate buffers.  Backward (training config 5) is not
-built yet: a call that needs gradients raises instead of silently detaching.
+orders libtvi launches and owns the intermediate buffers.  When gradients are required (training
+config 5: src/train_decouples.py back-propagates through every Attention module and updates the
+`temporal_transformer_block*` parameters) the same launches run inside `_AttentionFn`, whose backward
+is again nothing but libtvi kernels: projection dgrad / wgrad / bias column sums and the three
+attention-core backward kernels (include/tvi.h).  torch autograd is only the tape.
 """
 from __future__ import annotations
 
 import torch
+from torch.autograd.function import once_differentiable
 
 from . import _lib, ops
 
 
 def _to_bf16(t):
     return t if t is None or t.dtype == torch.bfloat16 else t.detach().to(torch.bfloat16)
+
+
+def _self_core(q, k, v, Bp, S, heads, scale, lse=None):
+    if S <= 64:
+        return ops.attn_temporal(q, k, v, Bp, heads, S, S, scale)
+    return ops.attn_spatial(q, k, v, Bp, heads, S, S, scale, lse=lse)
 
 
 def self_attention(x: torch.Tensor, w_qkv: torch.Tensor, w_o: torch.Tensor, b_o, heads: int, scale: float) -> torch.Tensor:
@@ -22,10 +32,7 @@ def self_attention(x: torch.Tensor, w_qkv: torch.Tensor, w_o: torch.Tensor, b_o,
     inner = w_qkv.shape[0] // 3
     qkv = ops.gemm_bf16_tn(x.view(Bp * S, C), w_qkv)  # [B'*S, 3*inner], heads stay packed along the row
     q, k, v = qkv[:, :inner], qkv[:, inner:2 * inner], qkv[:, 2 * inner:]
-    if S <= 64:
-        o = ops.attn_temporal(q, k, v, Bp, heads, S, S, scale)
-    else:
-        o = ops.attn_spatial(q, k, v, Bp, heads, S, S, scale)
+    o = _self_core(q, k, v, Bp, S, heads, scale)
     y = ops.gemm_bf16_tn(o, w_o, b_o)
     return y.view(Bp, S, -1)
 
@@ -36,10 +43,7 @@ def cross_attention(x: torch.Tensor, e: torch.Tensor, w_q: torch.Tensor, w_kv: t
     encoder_hidden_states given (keys/values from the context, :1225-1231)."""
     Bp, S, C = x.shape
     L = e.shape[1]
-    if e.shape[0] != Bp:
-        raise _lib.TviError(_lib.TVI_ERR_INVALID, "encoder_hidden_states batch does not match hidden_states")
-    if L > 8:
-        raise _lib.TviError(_lib.TVI_ERR_UNSUPPORTED, f"cross-attention with {L} context tokens (libtvi builds 1..8)")
+    _check_context(x, e)
     inner = w_kv.shape[0] // 2
     kv = ops.gemm_bf16_tn(e.view(Bp * L, e.shape[2]), w_kv)  # [B'*L, 2*inner]
     k, v = kv[:, :inner], kv[:, inner:]
@@ -56,17 +60,170 @@ def cross_attention(x: torch.Tensor, e: torch.Tensor, w_q: torch.Tensor, w_kv: t
     return y.view(Bp, S, -1)
 
 
+def _check_context(x, e):
+    if e.shape[0] != x.shape[0]:
+        raise _lib.TviError(_lib.TVI_ERR_INVALID, "encoder_hidden_states batch does not match hidden_states")
+    if e.shape[1] > 8:
+        raise _lib.TviError(_lib.TVI_ERR_UNSUPPORTED, f"cross-attention with {e.shape[1]} context tokens (libtvi builds 1..8)")
+
+
+class _AttentionFn(torch.autograd.Function):
+    """One attention call on the autograd tape.  Inputs that may receive gradients: x, e and the six
+    parameter tensors (SURVEY.md §8.2 row B "Autograd"); `cfg` carries the derived bf16 fused weights and
+    the non-differentiable options (ramp bias: a constant; statistics: the reference detaches them through
+    `.item()`, src/train_decouples.py:460-471, :1027-1029)."""
+
+    @staticmethod
+    def forward(ctx, x, e, wq, wk, wv, wo, bo, cfg):
+        heads, scale = cfg["heads"], cfg["scale"]
+        w_o, b_o = cfg["w_o"], cfg["b_o"]
+        Bp, S, C = x.shape
+        ctx.cfg = cfg
+        ctx.shape = (Bp, S, C)
+        ctx.param_dtypes = tuple(None if t is None else t.dtype for t in (wq, wk, wv, wo, bo))
+        if e is None:
+            w_qkv = cfg["w_qkv"]
+            inner = w_qkv.shape[0] // 3
+            x2 = x.view(Bp * S, C)
+            qkv = ops.gemm_bf16_tn(x2, w_qkv)
+            q, k, v = qkv[:, :inner], qkv[:, inner:2 * inner], qkv[:, 2 * inner:]
+            lse = torch.empty(Bp * S, heads, dtype=torch.float32, device=x.device) if S > 64 else None
+            o = _self_core(q, k, v, Bp, S, heads, scale, lse=lse)
+            y = ops.gemm_bf16_tn(o, w_o, b_o)
+            ctx.mode = "self"
+            ctx.save_for_backward(x2, qkv, o, lse, w_qkv, w_o)
+            return y.view(Bp, S, -1)
+        _check_context(x, e)
+        L = e.shape[1]
+        w_q, w_kv = cfg["w_q"], cfg["w_kv"]
+        inner = w_kv.shape[0] // 2
+        e2 = e.view(Bp * L, e.shape[2])
+        kv = ops.gemm_bf16_tn(e2, w_kv)
+        k, v = kv[:, :inner], kv[:, inner:]
+        bias, stats = cfg.get("bias"), cfg.get("stats")
+        if L == 1 and stats is None:
+            yv = ops.gemm_bf16_tn(v, w_o, b_o)
+            y = ops.attn_fewkeys(None, yv, yv, Bp * S, S, heads, 1, 1.0)
+            ctx.mode = "cross1"
+            ctx.save_for_backward(e2, kv, w_kv, w_o)
+            return y.view(Bp, S, -1)
+        x2 = x.view(Bp * S, C)
+        q = ops.gemm_bf16_tn(x2, w_q)
+        o = ops.attn_fewkeys(q, k, v, Bp * S, S, heads, L, scale, Tq=S if (bias is not None or stats is not None) else 1,
+                             bias=bias, stats=stats)
+        y = ops.gemm_bf16_tn(o, w_o, b_o)
+        ctx.mode = "cross"
+        ctx.save_for_backward(x2, e2, q, kv, o, w_q, w_kv, w_o)
+        return y.view(Bp, S, -1)
+
+    @staticmethod
+    @once_differentiable
+    def backward(ctx, dy):
+        cfg = ctx.cfg
+        heads, scale = cfg["heads"], cfg["scale"]
+        Bp, S, C = ctx.shape
+        need_x, need_e, need_wq, need_wk, need_wv, need_wo, need_bo, _ = ctx.needs_input_grad
+        dt_wq, dt_wk, dt_wv, dt_wo, dt_bo = ctx.param_dtypes
+        dy2 = dy.contiguous().view(Bp * S, -1)
+        if dy2.dtype != torch.bfloat16:
+            dy2 = dy2.to(torch.bfloat16)
+        dx = de = dwq = dwk = dwv = dwo = dbo = None
+
+        def cast(t, dt):
+            return t if t is None or t.dtype == dt else t.to(dt)
+
+        if ctx.mode == "self":
+            x2, qkv, o, lse, w_qkv, w_o = ctx.saved_tensors
+            inner = w_qkv.shape[0] // 3
+            if need_wo:
+                dwo = ops.gemm_bf16_wgrad(dy2, o)
+            if need_bo:
+                dbo = ops.colsum_bf16(dy2).view(-1)
+            do = ops.gemm_bf16_dgrad(dy2, w_o)
+            q, k, v = qkv[:, :inner], qkv[:, inner:2 * inner], qkv[:, 2 * inner:]
+            dqkv = torch.empty_like(qkv)  # dq | dk | dv written in place as column slices
+            dq, dk, dv = dqkv[:, :inner], dqkv[:, inner:2 * inner], dqkv[:, 2 * inner:]
+            if S <= 64:
+                ops.attn_temporal_bwd(q, k, v, do, Bp, heads, S, S, scale, dq=dq, dk=dk, dv=dv)
+            else:
+                ops.attn_spatial_bwd(q, k, v, o, do, lse, Bp, heads, S, S, scale, dq=dq, dk=dk, dv=dv)
+            if need_x:
+                dx = ops.gemm_bf16_dgrad(dqkv, w_qkv).view(Bp, S, C)
+            if need_wq and need_wk and need_wv:
+                dw = ops.gemm_bf16_wgrad(dqkv, x2)
+                dwq, dwk, dwv = dw[:inner], dw[inner:2 * inner], dw[2 * inner:]
+            else:
+                dwq = ops.gemm_bf16_wgrad(dq, x2) if need_wq else None
+                dwk = ops.gemm_bf16_wgrad(dk, x2) if need_wk else None
+                dwv = ops.gemm_bf16_wgrad(dv, x2) if need_wv else None
+        elif ctx.mode == "cross1":
+            e2, kv, w_kv, w_o = ctx.saved_tensors
+            inner = w_kv.shape[0] // 2
+            v = kv[:, inner:]
+            dyv = ops.colsum_bf16(dy2, S)  # [B', C]: every query row of a group received the same row
+            if need_wo:
+                dwo = ops.gemm_bf16_wgrad(dyv, v)
+            if need_bo:
+                dbo = ops.colsum_bf16(dyv).view(-1)
+            if need_e or need_wv:
+                dv = ops.gemm_bf16_dgrad(dyv, w_o)
+                if need_e:
+                    de = ops.gemm_bf16_dgrad(dv, w_kv[inner:]).view(Bp, -1, e2.shape[1])
+                if need_wv:
+                    dwv = ops.gemm_bf16_wgrad(dv, e2)
+            # softmax over one key is constant: nothing flows to the query path or to the key projection
+            if need_x:
+                dx = torch.zeros(Bp, S, C, dtype=torch.bfloat16, device=dy.device)
+            if need_wq:
+                dwq = torch.zeros(cfg["w_q"].shape, dtype=torch.bfloat16, device=dy.device)
+            if need_wk:
+                dwk = torch.zeros(inner, e2.shape[1], dtype=torch.bfloat16, device=dy.device)
+        else:
+            x2, e2, q, kv, o, w_q, w_kv, w_o = ctx.saved_tensors
+            inner = w_kv.shape[0] // 2
+            L = e2.shape[0] // Bp
+            k, v = kv[:, :inner], kv[:, inner:]
+            if need_wo:
+                dwo = ops.gemm_bf16_wgrad(dy2, o)
+            if need_bo:
+                dbo = ops.colsum_bf16(dy2).view(-1)
+            do = ops.gemm_bf16_dgrad(dy2, w_o)
+            bias = cfg.get("bias")
+            dkv = torch.empty_like(kv)
+            dq, _, _ = ops.attn_fewkeys_bwd(q, k, v, do, Bp * S, S, heads, L, scale, Tq=S if bias is not None else 1, bias=bias,
+                                            dk=dkv[:, :inner], dv=dkv[:, inner:])
+            if need_x:
+                dx = ops.gemm_bf16_dgrad(dq, w_q).view(Bp, S, C)
+            if need_wq:
+                dwq = ops.gemm_bf16_wgrad(dq, x2)
+            if need_e:
+                de = ops.gemm_bf16_dgrad(dkv, w_kv).view(Bp, L, e2.shape[1])
+            if need_wk and need_wv:
+                dw = ops.gemm_bf16_wgrad(dkv, e2)
+                dwk, dwv = dw[:inner], dw[inner:]
+            else:
+                dwk = ops.gemm_bf16_wgrad(dkv[:, :inner], e2) if need_wk else None
+                dwv = ops.gemm_bf16_wgrad(dkv[:, inner:], e2) if need_wv else None
+        return (dx, de, cast(dwq, dt_wq), cast(dwk, dt_wk), cast(dwv, dt_wv), cast(dwo, dt_wo), cast(dbo, dt_bo), None)
+
+
 def attention_forward(proc, attn, x, e, heads: int, scale: float, wo, bo, bias, stats) -> torch.Tensor:
-    needs_grad = torch.is_grad_enabled() and (
-        x.requires_grad or (e is not None and e.requires_grad) or wo.requires_grad
-        or attn.to_q.weight.requires_grad or attn.to_k.weight.requires_grad or attn.to_v.weight.requires_grad)
-    if needs_grad:
-        raise NotImplementedError(
-            "libtvi attention backward is not built yet: call under torch.no_grad() / inference_mode() "
-            "(training config 5 is tracked in DESIGN.md)")
+    wq, wk, wv = attn.to_q.weight, attn.to_k.weight, attn.to_v.weight
+    needs_grad = torch.is_grad_enabled() and any(
+        t is not None and t.requires_grad for t in (x, e, wq, wk, wv, wo, bo))
     w_o = _to_bf16(wo).contiguous()
     b_o = _to_bf16(bo).contiguous() if bo is not None else None
+    if not needs_grad:
+        if e is None:
+            return self_attention(x, proc._fused(attn, ("to_q", "to_k", "to_v")), w_o, b_o, heads, scale)
+        return cross_attention(x, e, proc._fused(attn, ("to_q",)), proc._fused(attn, ("to_k", "to_v")), w_o, b_o, heads,
+                               scale, bias, stats)
+    cfg = {"heads": heads, "scale": scale, "w_o": w_o, "b_o": b_o}
     if e is None:
-        return self_attention(x, proc._fused(attn, ("to_q", "to_k", "to_v")), w_o, b_o, heads, scale)
-    return cross_attention(x, e, proc._fused(attn, ("to_q",)), proc._fused(attn, ("to_k", "to_v")), w_o, b_o, heads,
-                           scale, bias, stats)
+        cfg["w_qkv"] = proc._fused(attn, ("to_q", "to_k", "to_v"))
+    else:
+        cfg["w_q"] = proc._fused(attn, ("to_q",))
+        cfg["w_kv"] = proc._fused(attn, ("to_k", "to_v"))
+        cfg["bias"] = bias
+        cfg["stats"] = stats
+    return _AttentionFn.apply(x, e, wq, wk, wv, wo, bo, cfg)
