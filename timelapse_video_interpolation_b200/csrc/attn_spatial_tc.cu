@@ -5,10 +5,10 @@
 // (src/models/attention_processor.py:1243, :1156; caller src/models/attention.py:276-281).
 //
 // One CTA owns 256 query rows (two 128-row tiles) of one (frame, head) and streams the keys in
-// steps of 64.  352 threads, warp-specialised:
+// steps of 64.  608 threads, warp-specialised:
 //   warp 0        TMA producer: K_j / V_j ([64 keys x 64] each) into an 8-stage smem ring
 //                 (3-D tensor maps [heads*64, Skv, batch]: sequence tails are zero-filled).
-//   warps 1, 10   tcgen05.mma issuers, one per tile (the whole warp walks the loop so descriptors stay
+//   warps 1, 2    tcgen05.mma issuers, one per tile (the whole warp walks the loop so descriptors stay
 //                 in uniform registers; one elected lane's instructions are enabled).  Both products
 //                 take their A operand from tensor memory, so shared memory only feeds the 64-wide B
 //                 operands:
@@ -17,11 +17,13 @@
 //                 issued per tile as  QK_j PV_{j-1}: the scores of step j are produced while the
 //                 softmax warps are still working on step j-1 (S is double-buffered per tile), and
 //                 the two tiles only meet at the K/V ring (a stage is freed by both tiles' commits).
-//   warps 2..5    softmax of tile 0, warps 6..9 softmax of tile 1: one thread per query row
-//                 (TMEM lane).  The thread first parks its Q row in TMEM, then per step reads its 64
-//                 scores with tcgen05.ld, does the fp32 online softmax (FMNMX3 / FFMA2 / FADD2; ex2 on
-//                 the MUFU unit for 3 of 4 score pairs, a cubic polynomial on the FMA pipe for the rest)
-//                 and writes P as bf16 over the first half of the same S buffer with tcgen05.st.
+//   warps 3..10   softmax of tile 0, warps 11..18 softmax of tile 1: TWO threads per query row
+//                 (TMEM lane), 32 of the step's 64 key columns each, so four softmax warps share every
+//                 SM sub-partition.  The threads first park their Q half-rows in TMEM, then per step read
+//                 their 32 scores with tcgen05.ld, exchange the row maximum through shared memory, do
+//                 the fp32 online softmax (FMNMX3 / FFMA2 / FADD2; ex2 on the MUFU unit for 3 of 4
+//                 score pairs, a cubic polynomial on the FMA pipe for the rest) and write P as bf16
+//                 over the first half of the same S buffer with tcgen05.st.
 //                 The reference maximum only moves when the row maximum outgrows it by 2^8 (P stays
 //                 <= 256, exact in O / l), so the O accumulator in TMEM is rescaled rarely, by the
 //                 same threads.
@@ -34,7 +36,7 @@
 namespace tvi {
 namespace {
 
-constexpr int kTcThreads = 352;
+constexpr int kTcThreads = 608;
 constexpr int kTcBM = 128;      // query rows per tile (UMMA M)
 constexpr int kTcBN = 64;       // keys per step (UMMA N of QK^T, K of PV)
 constexpr int kTcStages = 8;
@@ -61,6 +63,7 @@ struct TcBarriers {
   uint64_t s_full[2][2];
   uint64_t p_full[2][2];
   uint64_t o_full[2];
+  uint64_t o_done[2];  // completes once per tile, after the last PV product
 };
 
 #include "attn_spatial_tc_softmax.cuh"
@@ -72,6 +75,7 @@ attn_spatial_tc_kernel(const __grid_constant__ CUtensorMap tmK, const __grid_con
   extern __shared__ uint8_t smem_raw[];
   __shared__ __align__(8) TcBarriers bars;
   __shared__ uint32_t s_tmem_base;
+  __shared__ float s_xchg[2][2 * 256];  // per tile: [step parity][half][row] row-maximum / row-sum exchange
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -89,11 +93,12 @@ attn_spatial_tc_kernel(const __grid_constant__ CUtensorMap tmK, const __grid_con
     tma_prefetch_desc(&tmV);
     tma_prefetch_desc(&tmO);
     for (int t = 0; t < 2; ++t) {
-      mbar_init(&bars.q_full[t], 4);
+      mbar_init(&bars.q_full[t], 8);
       mbar_init(&bars.o_full[t], 1);
+      mbar_init(&bars.o_done[t], 1);
       for (int i = 0; i < 2; ++i) {
         mbar_init(&bars.s_full[t][i], 1);
-        mbar_init(&bars.p_full[t][i], 4);
+        mbar_init(&bars.p_full[t][i], 8);
       }
     }
     for (int s = 0; s < kTcStages; ++s) {
@@ -117,7 +122,7 @@ attn_spatial_tc_kernel(const __grid_constant__ CUtensorMap tmK, const __grid_con
       int s = 0;
       uint32_t ph = 0;
       for (int j = 0; j < p.n_kv; ++j) {
-        mbar_wait(&bars.kv_empty[s], ph ^ 1);
+        TVI_WAIT(&bars.kv_empty[s], ph ^ 1, 1, j);
         uint8_t* kdst = base_ptr + 2 * kTcOutBytes + s * kTcStageBytes;
         mbar_arrive_expect_tx(&bars.kv_full[s], kTcStageBytes);
         tma_load_3d(kdst, &tmK, &bars.kv_full[s], h * 64, j * kTcBN, b);
@@ -128,7 +133,7 @@ attn_spatial_tc_kernel(const __grid_constant__ CUtensorMap tmK, const __grid_con
         }
       }
     }
-  } else if (warp == 1 || warp == 10) {
+  } else if (warp == 1 || warp == 2) {
     // ===================== MMA issuers =====================
     // The whole warp walks the loop (convergent control flow keeps every descriptor in uniform
     // registers); only the elected lane's tcgen05 instructions are enabled.
@@ -160,27 +165,31 @@ attn_spatial_tc_kernel(const __grid_constant__ CUtensorMap tmK, const __grid_con
       }
       umma_commit_pred(&bars.o_full[t], leader);
     };
-    // One issuing warp per tile (warp 1 -> tile 0, warp 10 -> tile 1), each blocking only on its own
+    // One issuing warp per tile (warp 1 -> tile 0, warp 2 -> tile 1), each blocking only on its own
     // tile's barriers: neither tile's softmax is gated by the other tile's progress until the 8-stage
     // K/V ring runs out, so their exp phases can drift apart instead of colliding on the MUFU unit.
     const int t = (warp == 1) ? 0 : 1;
-    mbar_wait(&bars.q_full[t], 0);
+    TVI_WAIT(&bars.q_full[t], 0, 2, 0);
     tc_fence_after();
     int s = 0, sp = 0;  // stage of step j, stage of step j-1
     uint32_t ph = 0;
     for (int j = 0; j <= p.n_kv; ++j) {
       if (j < p.n_kv) {
-        mbar_wait(&bars.kv_full[s], ph);
+        TVI_WAIT(&bars.kv_full[s], ph, 3, j);
         tc_fence_after();
         // S[j&1] last held P_{j-2}, read by PV_t(j-2): issued earlier by this thread, MMAs complete in order
         issue_qk(t, s, j);
       }
       if (j >= 1) {
         const int jj = j - 1;
-        mbar_wait(&bars.p_full[t][jj & 1], (uint32_t)(jj >> 1) & 1u);
+        TVI_WAIT(&bars.p_full[t][jj & 1], (uint32_t)(jj >> 1) & 1u, 4, jj);
         tc_fence_after();
         issue_pv(t, sp, jj);
         umma_commit_pred(&bars.kv_empty[sp], leader);  // this tile is done with K_jj / V_jj (2 arrivals free the stage)
+        // the epilogue waits on a barrier of its own: a parity wait on o_full is only sound for a waiter
+        // that is at most one phase behind, and a softmax warp can reach the epilogue after BOTH of the
+        // last two PV products have completed
+        if (jj == p.n_kv - 1) umma_commit_pred(&bars.o_done[t], leader);
       }
       sp = s;
       if (++s == kTcStages) {
@@ -190,10 +199,13 @@ attn_spatial_tc_kernel(const __grid_constant__ CUtensorMap tmK, const __grid_con
     }
     __syncwarp();
   } else {
-    // ===================== softmax + epilogue (warps 2..9) =====================
-    const int t = (warp - 2) >> 2;
-    tc_softmax_role<kPolyMask>(p, tmem_base + t * kColTile, warp, lane, b, h, q0 + t * kTcBM, base_ptr + t * kTcOutBytes,
-                    &bars.q_full[t], bars.s_full[t], bars.p_full[t], &bars.o_full[t], &tmO);
+    // ===================== softmax + epilogue (warps 3..18) =====================
+    const int sw = warp - 3;
+    const int t = sw >> 3, half = (sw >> 2) & 1;
+    const int quad = warp & 3;  // the TMEM lane quadrant a warp may touch is fixed by its index
+    tc_softmax_role<kPolyMask>(p, tmem_base + t * kColTile, quad, half, 1u + t * 4 + quad, s_xchg[t], lane, b, h,
+                               q0 + t * kTcBM, base_ptr + t * kTcOutBytes, &bars.q_full[t], bars.s_full[t], bars.p_full[t],
+                               &bars.o_full[t], &bars.o_done[t], &tmO);
   }
 
   tc_fence_before();

@@ -125,6 +125,18 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
   while (!mbar_try_wait(bar, parity)) {
   }
 }
+#ifdef TVI_DEBUG_WAIT
+__device__ unsigned int g_dbg_prints = 0;
+__device__ __forceinline__ void mbar_wait_tag(uint64_t* bar, uint32_t parity, int tag, int j) {
+  for (long long it = 0; it < 4000000LL; ++it)
+    if (mbar_try_wait(bar, parity)) return;
+  if ((threadIdx.x & 31) == 0 && atomicAdd(&g_dbg_prints, 1u) < 200u)
+    printf("WAIT TIMEOUT block (%d,%d) warp %d tag %d j %d parity %u\n", blockIdx.x, blockIdx.y, threadIdx.x >> 5, tag, j, parity);
+}
+#define TVI_WAIT(bar, parity, tag, j) mbar_wait_tag(bar, parity, tag, j)
+#else
+#define TVI_WAIT(bar, parity, tag, j) mbar_wait(bar, parity)
+#endif
 
 // ---- proxies / fences -----------------------------------------------------------------
 __device__ __forceinline__ void fence_proxy_async_smem() {

@@ -1,0 +1,239 @@
+#!/usr/bin/env python
+"""Secondary measurements for the parity-test configs of BASELINE.json: bench.py keeps the
+headline line (configs[1]); this script times the other configurations on one B200 and prints one JSON
+line per config (copied under profiles/ per round).
+
+    python tools/bench_configs.py [--only slerp,flow,train,loop25,kernels] [--steps K]
+
+  slerp   config 1: latent slerp, clips in {1, 64, 4096}, T in {14, 25}          -> GB/s vs HBM peak
+  flow    config 4: 1080p flow cosine + backward warp / consistency, B in {1,8,32} -> GB/s vs HBM peak
+  train   config 5: forward + backward of one L0 block's four attention calls, 2 clips x T=14 (no CFG),
+          temporal modules trainable, spatial modules frozen (train_decouples)     -> ms, clip-frames/s
+  loop25  config 3: 25-frame, 25-step loop over the 23 block instances of UNet + ControlNet branch,
+          attention path only, 1 clip (CFG 2)                                      -> clip-frames/s
+  kernels per-kernel-family device time of one L0 forward and forward+backward step (CUDA events)
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import sys
+from collections import defaultdict
+from pathlib import Path
+
+ROOT = Path(__file__).resolve().parents[1]
+if str(ROOT) not in sys.path:
+    sys.path.insert(0, str(ROOT))
+
+import torch  # noqa: E402
+
+import bench  # noqa: E402
+import timelapse_video_interpolation_b200 as tvi  # noqa: E402
+from timelapse_video_interpolation_b200 import ops  # noqa: E402
+from timelapse_video_interpolation_b200.modules import Attention  # noqa: E402
+from timelapse_video_interpolation_b200.processor import TviAttnProcessor  # noqa: E402
+
+DEV = torch.device("cuda", 0)
+PK = bench.peaks()
+
+
+def timed(fn, steps, warmup=3):
+    for _ in range(warmup):
+        fn()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        fn()
+    e1.record()
+    torch.cuda.synchronize()
+    return e0.elapsed_time(e1) / steps
+
+
+def emit(d):
+    print(json.dumps(d), flush=True)
+
+
+def flush_l2():
+    # write a buffer larger than the 126 MB L2 between timed launches of small problems
+    if not hasattr(flush_l2, "buf"):
+        flush_l2.buf = torch.empty(256 << 20, dtype=torch.uint8, device=DEV)
+    flush_l2.buf.fill_(1)
+
+
+def cfg_slerp(steps):
+    n = 4 * 72 * 128
+    for T in (14, 25):
+        for clips in (1, 64, 4096):
+            g = torch.Generator().manual_seed(0)
+            v0 = torch.randn(clips, 4, 72, 128, generator=g).to(DEV)
+            v1 = torch.randn(clips, 4, 72, 128, generator=g).to(DEV)
+            out = torch.empty(clips, T, 4, 72, 128, device=DEV)
+            ms = timed(lambda: ops.slerp_f32(v0, v1, T, 0.9995, out=out), steps)
+            nbytes = (2 + T) * n * 4 * clips
+            gbs = nbytes / (ms * 1e-3) / 1e9
+            emit({"config": "slerp", "clips": clips, "T": T, "ms": ms, "clip_frames_per_s": clips * T / (ms * 1e-3),
+                  "algorithmic_bytes": nbytes, "gbs": gbs, "hbm_frac": gbs / PK["hbm"],
+                  "note": "working set < L2 for clips <= 64 (launch-bound)" if clips <= 64 else "5 GB working set"})
+
+
+def cfg_flow(steps):
+    H, W = 1080, 1920
+    for B in (1, 8, 32):
+        g = torch.Generator().manual_seed(B)
+        img = torch.rand(B, 3, H, W, generator=g).to(DEV)
+        f = (torch.randn(B, 2, H, W, generator=g) * 5).to(DEV)
+        fb = (-f + torch.randn(B, 2, H, W, generator=g).to(DEV) * 0.2)
+        fa_hwc = f.permute(0, 2, 3, 1).contiguous()
+        fb_hwc = fb.permute(0, 2, 3, 1).contiguous()
+        warped = torch.empty_like(img)
+        mask = torch.empty(B, H, W, dtype=torch.uint8, device=DEV)
+        ms_w = timed(lambda: ops.backward_warp_f32(img, f, fb, 0.01, 0.5, warped=warped, mask=mask), steps)
+        ms_c = timed(lambda: ops.flow_cosine_f32(fa_hwc, fb_hwc, True), steps)
+        bw = ((3 + 2 + 2) * 4 + 3 * 4 + 1) * H * W * B
+        bc = 2 * 2 * 4 * H * W * B
+        emit({"config": "flow_warp_check_1080p", "pairs": B, "ms": ms_w, "pairs_per_s": B / (ms_w * 1e-3), "algorithmic_bytes": bw,
+              "gbs": bw / (ms_w * 1e-3) / 1e9, "hbm_frac": bw / (ms_w * 1e-3) / 1e9 / PK["hbm"]})
+        emit({"config": "flow_cosine_1080p", "pairs": B, "ms": ms_c, "pairs_per_s": B / (ms_c * 1e-3), "algorithmic_bytes": bc,
+              "gbs": bc / (ms_c * 1e-3) / 1e9, "hbm_frac": bc / (ms_c * 1e-3) / 1e9 / PK["hbm"]})
+
+
+class KernelTimes:
+    """CUDA-event bracket around every libtvi launch (ops.EVENT_HOOK), aggregated per entry point."""
+
+    def __init__(self):
+        self.pairs = []
+        self.open = None
+
+    def hook(self, name, is_start):
+        ev = torch.cuda.Event(enable_timing=True)
+        ev.record()
+        if is_start:
+            self.open = (name, ev)
+        else:
+            self.pairs.append((self.open[0], self.open[1], ev))
+
+    def summary(self, steps):
+        torch.cuda.synchronize()
+        agg = defaultdict(lambda: [0, 0.0])
+        for name, a, b in self.pairs:
+            agg[name][0] += 1
+            agg[name][1] += a.elapsed_time(b)
+        return {k: {"launches_per_step": v[0] / steps, "ms_per_step": v[1] / steps} for k, v in sorted(agg.items())}
+
+
+def make_block(level, clips, cfg, T, trainable_temporal=False):
+    C, heads, h, w = bench.LEVELS[level]
+    S = h * w
+    g = torch.Generator().manual_seed(2)
+    proc = TviAttnProcessor()
+
+    def mk(cross):
+        a = Attention(C, cross, heads=heads, dim_head=64, processor=proc)
+        with torch.no_grad():
+            for p in a.parameters():
+                bound = p.shape[-1] ** -0.5 if p.dim() > 1 else C ** -0.5
+                p.copy_((torch.rand(p.shape, generator=g) * 2 - 1) * bound)
+        return a.to(device=DEV, dtype=torch.bfloat16)
+
+    mods = [mk(None), mk(1024), mk(None), mk(1024)]
+    for i, m in enumerate(mods):
+        for p in m.parameters():
+            p.requires_grad_(trainable_temporal and i >= 2)
+    BF, nseq = clips * cfg * T, clips * cfg * S
+    x = torch.randn(BF, S, C, generator=g).to(torch.bfloat16).to(DEV)
+    ctx_s = torch.randn(BF, 2, 1024, generator=g).to(torch.bfloat16).to(DEV)
+    ctx_t = torch.randn(nseq, 1, 1024, generator=g).to(torch.bfloat16).to(DEV)
+
+    def step(xin):
+        y1 = mods[0](xin)
+        y2 = mods[1](y1, encoder_hidden_states=ctx_s)
+        y3 = mods[2](y2.view(nseq, T, C))
+        return mods[3](y3, encoder_hidden_states=ctx_t)
+
+    return mods, x, step, (BF, S, C, nseq)
+
+
+def cfg_train(steps):
+    # accelerate config of the reference: per_gpu_batch_size 2, T = 14, no CFG -> BF = 28 frames at 576x1024
+    clips, T = 2, 14
+    mods, x, step, (BF, S, C, nseq) = make_block("L0", clips, 1, T, trainable_temporal=True)
+    xg = x.clone().requires_grad_(True)  # gradient flows on to the blocks below
+    dy = (torch.randn(nseq, T, C, device=DEV) / 8).to(torch.bfloat16)
+
+    def fwd():
+        with torch.no_grad():
+            step(x)
+
+    def fwd_bwd():
+        for m in mods:
+            for p in m.parameters():
+                p.grad = None
+        xg.grad = None
+        step(xg).backward(dy)
+
+    ms_f = timed(fwd, steps)
+    ms_fb = timed(fwd_bwd, steps)
+    kt = KernelTimes()
+    ops.EVENT_HOOK = kt.hook
+    for _ in range(3):
+        fwd_bwd()
+    ops.EVENT_HOOK = None
+    ngrad = sum(p.numel() for m in mods for p in m.parameters() if p.requires_grad)
+    emit({"config": "train_fwd_bwd_L0_block_attention", "clips_per_gpu": clips, "T": T, "resolution": "576x1024",
+          "trainable": "temporal attn1/attn2 (spatial frozen)", "trainable_params": ngrad, "ms_fwd": ms_f, "ms_fwd_bwd": ms_fb,
+          "clip_frames_per_s_fwd_bwd": clips * T / (ms_fb * 1e-3), "kernels": kt.summary(3)})
+
+
+def cfg_loop25(steps):
+    # 16 UNet + 7 ControlNet TransformerSpatioTemporalModel instances per denoising step:
+    # UNet: L0 x5, L1 x5, L2 x5, mid x1; ControlNet branch (down + mid): L0 x2, L1 x2, L2 x2, mid x1
+    T, n_steps = 25, 25
+    inst = {"L0": 7, "L1": 7, "L2": 7, "mid": 2}
+    blocks = {lv: make_block(lv, 1, 2, T) for lv in inst}
+    per_level = {}
+    with torch.no_grad():
+        for lv, (mods, x, step, _) in blocks.items():
+            per_level[lv] = timed(lambda: step(x), max(3, steps // 2))
+
+        def unet_step():
+            for lv, n in inst.items():
+                _, x, step, _ = blocks[lv]
+                for _ in range(n):
+                    step(x)
+
+        ms_step = timed(unet_step, 3, warmup=1)
+    total_ms = ms_step * n_steps
+    emit({"config": "loop25_attention_path", "frames": T, "denoise_steps": n_steps, "instances_per_step": sum(inst.values()),
+          "clips": 1, "cfg": 2, "ms_per_level_block": per_level, "ms_per_denoise_step": ms_step, "ms_per_clip": total_ms,
+          "clip_frames_per_s": T / (total_ms * 1e-3),
+          "note": "attention path only (the four processor calls of every block instance); resnets/convs/VAE are out of scope"})
+
+
+def cfg_kernels(steps):
+    mods, x, step, (BF, S, C, nseq) = make_block("L0", 1, 2, 14)
+    kt = KernelTimes()
+    with torch.no_grad():
+        for _ in range(3):
+            step(x)
+        ops.EVENT_HOOK = kt.hook
+        for _ in range(steps):
+            step(x)
+        ops.EVENT_HOOK = None
+    emit({"config": "kernels_L0_forward", "per_entry_point": kt.summary(steps)})
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--only", default="slerp,flow,train,loop25,kernels")
+    ap.add_argument("--steps", type=int, default=10)
+    args = ap.parse_args()
+    torch.cuda.set_device(0)
+    emit({"config": "env", "device": torch.cuda.get_device_name(0), "libtvi": tvi.version(), "peaks": PK})
+    table = {"slerp": cfg_slerp, "flow": cfg_flow, "train": cfg_train, "loop25": cfg_loop25, "kernels": cfg_kernels}
+    for name in args.only.split(","):
+        table[name.strip()](args.steps)
+
+
+if __name__ == "__main__":
+    main()
