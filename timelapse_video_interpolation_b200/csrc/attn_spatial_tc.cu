@@ -75,7 +75,7 @@ attn_spatial_tc_kernel(const __grid_constant__ CUtensorMap tmK, const __grid_con
   extern __shared__ uint8_t smem_raw[];
   __shared__ __align__(8) TcBarriers bars;
   __shared__ uint32_t s_tmem_base;
-  __shared__ float s_xchg[2][2 * 256];  // per tile: [step parity][half][row] row-maximum / row-sum exchange
+  __shared__ float s_xchg[2][4 * 256];  // per tile: {row sums, row maxima} x [step parity][half][row] exchange slots
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;

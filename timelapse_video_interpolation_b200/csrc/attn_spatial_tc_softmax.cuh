@@ -78,6 +78,9 @@ __device__ __forceinline__ void tc_softmax_role(const TcParams& p, uint32_t tile
   float l = 0.f;            // this half's running sum of exp2((s - m_ref) * sl2)
 
   uint32_t ra[32];  // this thread's 32 scores of the current step
+#ifdef TVI_DEBUG_WAIT
+  int n_slow = 0;
+#endif
   TVI_WAIT(&bar_s[0], 0, 5, 0);
   tc_fence_after();
   tmem_ld_x32(tS + half * 32, ra);
@@ -94,80 +97,99 @@ __device__ __forceinline__ void tc_softmax_role(const TcParams& p, uint32_t tile
       for (int c = 0; c < 32; ++c)
         if (c >= valid) ra[c] = 0xff800000u;  // -inf
     }
-    float mx0 = -INFINITY, mx1 = -INFINITY;
-#pragma unroll
-    for (int c = 0; c < 32; c += 4) {
-      mx0 = fmax3(mx0, __uint_as_float(ra[c]), __uint_as_float(ra[c + 1]));
-      mx1 = fmax3(mx1, __uint_as_float(ra[c + 2]), __uint_as_float(ra[c + 3]));
-    }
-    // the row maximum of the step = max over both halves (parity-double-buffered exchange slots)
-    float* slot = xchg + buf * 256;
-    const float mxl = fmaxf(mx0, mx1);
-    slot[half * 128 + rr] = mxl;
-    named_bar_sync(pair_bar, 64);
-    const float mx = fmaxf(mxl, slot[(half ^ 1) * 128 + rr]);
-    // advance the reference only when the row maximum outgrew it by more than 2^8
-    const bool need = (mx - m_ref) * sl2 > 8.f;
-    float alpha = 1.f;
-    if (need) {
-      alpha = fast_exp2((m_ref - mx) * sl2);  // 0 on the first step (m_ref = -inf)
-      m_ref = mx;
-      l *= alpha;
-    }
-    if (j > 0 && __any_sync(0xffffffffu, need)) {
-      // rescale this thread's half of the O accumulator: PV_{j-1} must have landed; PV_j is not issued
-      // before bar_p below
-      TVI_WAIT(bar_o, (uint32_t)(j - 1) & 1u, 6, j);
-      tc_fence_after();
-      uint32_t o[32];
-      tmem_ld_x32(tO, o);
-      tmem_ld_wait();
-#pragma unroll
-      for (int c = 0; c < 32; ++c) o[c] = __float_as_uint(__uint_as_float(o[c]) * alpha);
-      tmem_st_x32(tO, o);
-    }
-    const float neg = -m_ref * sl2;
-    const uint64_t negx2 = f32x2_pack(neg, neg);
-    uint64_t sum_a = f32x2_pack(0.f, 0.f), sum_b = sum_a;
+    // Speculative pass: evaluate the exponentials against the CURRENT reference maximum without looking
+    // for the row maximum first (32 FMNMX3 per step on a half-rate pipe).  The pair's row sum of the step
+    // tells whether that was sound: P <= sum <= 2^13 keeps every value far inside the bf16 / fp32 range,
+    // and the reference does not have to be the exact maximum (O and l carry the same factor).  A sum that
+    // is larger, infinite or NaN (first step: m_ref = -inf) sends the whole warp through the exact pass.
     uint32_t pk[16];
+    float hs;  // this half's sum of the step's exponentials
+    auto exp_pass = [&]() {
+      const float neg = -m_ref * sl2;
+      const uint64_t negx2 = f32x2_pack(neg, neg);
+      uint64_t sum_a = f32x2_pack(0.f, 0.f), sum_b = sum_a;
 #pragma unroll
-    for (int c = 0; c < 32; c += 4) {
-      uint64_t xa = f32x2_fma(f32x2_pack(__uint_as_float(ra[c]), __uint_as_float(ra[c + 1])), sl2x2, negx2);
-      uint64_t xb = f32x2_fma(f32x2_pack(__uint_as_float(ra[c + 2]), __uint_as_float(ra[c + 3])), sl2x2, negx2);
-      float a0, a1, b0, b1;
-      if ((kPolyMask >> ((c >> 1) & 7)) & 1u) {
-        xa = exp2_poly_x2(xa);
-        f32x2_unpack(xa, a0, a1);
-      } else {
-        f32x2_unpack(xa, a0, a1);
-        a0 = fast_exp2(a0);
-        a1 = fast_exp2(a1);
-        xa = f32x2_pack(a0, a1);
+      for (int c = 0; c < 32; c += 4) {
+        uint64_t xa = f32x2_fma(f32x2_pack(__uint_as_float(ra[c]), __uint_as_float(ra[c + 1])), sl2x2, negx2);
+        uint64_t xb = f32x2_fma(f32x2_pack(__uint_as_float(ra[c + 2]), __uint_as_float(ra[c + 3])), sl2x2, negx2);
+        float a0, a1, b0, b1;
+        if ((kPolyMask >> ((c >> 1) & 7)) & 1u) {
+          xa = exp2_poly_x2(xa);
+          f32x2_unpack(xa, a0, a1);
+        } else {
+          f32x2_unpack(xa, a0, a1);
+          a0 = fast_exp2(a0);
+          a1 = fast_exp2(a1);
+          xa = f32x2_pack(a0, a1);
+        }
+        if ((kPolyMask >> (((c >> 1) + 1) & 7)) & 1u) {
+          xb = exp2_poly_x2(xb);
+          f32x2_unpack(xb, b0, b1);
+        } else {
+          f32x2_unpack(xb, b0, b1);
+          b0 = fast_exp2(b0);
+          b1 = fast_exp2(b1);
+          xb = f32x2_pack(b0, b1);
+        }
+        sum_a = f32x2_add(sum_a, xa);
+        sum_b = f32x2_add(sum_b, xb);
+        pk[c >> 1] = pack_bf16x2(a0, a1);
+        pk[(c >> 1) + 1] = pack_bf16x2(b0, b1);
       }
-      if ((kPolyMask >> (((c >> 1) + 1) & 7)) & 1u) {
-        xb = exp2_poly_x2(xb);
-        f32x2_unpack(xb, b0, b1);
-      } else {
-        f32x2_unpack(xb, b0, b1);
-        b0 = fast_exp2(b0);
-        b1 = fast_exp2(b1);
-        xb = f32x2_pack(b0, b1);
+      float s0, s1, s2, s3;
+      f32x2_unpack(sum_a, s0, s1);
+      f32x2_unpack(sum_b, s2, s3);
+      hs = (s0 + s1) + (s2 + s3);
+    };
+    exp_pass();
+    // both halves see the same total (parity-double-buffered exchange slots), hence take the same branch
+    float* slot = xchg + buf * 256;
+    slot[half * 128 + rr] = hs;
+    named_bar_sync(pair_bar, 64);
+    const float total = hs + slot[(half ^ 1) * 128 + rr];
+    if (__any_sync(0xffffffffu, !(total <= 8192.f))) {
+#ifdef TVI_DEBUG_WAIT
+      ++n_slow;
+#endif
+      // ---- exact pass (rare): row maximum of the step over both halves, lazy reference update ----------
+      float mx0 = -INFINITY, mx1 = -INFINITY;
+#pragma unroll
+      for (int c = 0; c < 32; c += 4) {
+        mx0 = fmax3(mx0, __uint_as_float(ra[c]), __uint_as_float(ra[c + 1]));
+        mx1 = fmax3(mx1, __uint_as_float(ra[c + 2]), __uint_as_float(ra[c + 3]));
       }
-      sum_a = f32x2_add(sum_a, xa);
-      sum_b = f32x2_add(sum_b, xb);
-      pk[c >> 1] = pack_bf16x2(a0, a1);
-      pk[(c >> 1) + 1] = pack_bf16x2(b0, b1);
+      float* mslot = xchg + 512 + buf * 256;
+      const float mxl = fmaxf(mx0, mx1);
+      mslot[half * 128 + rr] = mxl;
+      named_bar_sync(pair_bar, 64);
+      const float mx = fmaxf(mxl, mslot[(half ^ 1) * 128 + rr]);
+      // advance the reference only when the row maximum outgrew it by more than 2^8
+      const bool need = (mx - m_ref) * sl2 > 8.f;
+      float alpha = 1.f;
+      if (need) {
+        alpha = fast_exp2((m_ref - mx) * sl2);  // 0 on the first step (m_ref = -inf)
+        m_ref = mx;
+        l *= alpha;
+      }
+      if (j > 0 && __any_sync(0xffffffffu, need)) {
+        // rescale this thread's half of the O accumulator: PV_{j-1} must have landed; PV_j is not issued
+        // before bar_p below
+        TVI_WAIT(bar_o, (uint32_t)(j - 1) & 1u, 6, j);
+        tc_fence_after();
+        uint32_t o[32];
+        tmem_ld_x32(tO, o);
+        tmem_ld_wait();
+#pragma unroll
+        for (int c = 0; c < 32; ++c) o[c] = __float_as_uint(__uint_as_float(o[c]) * alpha);
+        tmem_st_x32(tO, o);
+      }
+      exp_pass();
     }
+    l += hs;
     // P (64 bf16 = 32 columns) overwrites the first half of this S buffer; this thread writes the 16
     // columns of its 32 keys.  For half 1 those are score columns 16..31, which belong to half 0: its
     // tcgen05.ld of them completed before it arrived on the pair barrier above.
     tmem_st_x16(tS + buf * 64 + half * 16, pk);
-    {
-      float s0, s1, s2, s3;
-      f32x2_unpack(sum_a, s0, s1);
-      f32x2_unpack(sum_b, s2, s3);
-      l += (s0 + s1) + (s2 + s3);
-    }
     // the next step's scores (other S buffer, normally long finished) travel to registers while the
     // P store drains
     if (j + 1 < p.n_kv) {
@@ -185,6 +207,9 @@ __device__ __forceinline__ void tc_softmax_role(const TcParams& p, uint32_t tile
   if (last_ragged) step(p.n_kv - 1, TcTag<true>{});
   else step(p.n_kv - 1, TcTag<false>{});
 
+#ifdef TVI_DEBUG_WAIT
+  if (blockIdx.x < 2 && blockIdx.y == 0 && lane == 0) printf("block %d quad %d half %d: %d exact passes of %d steps\n", blockIdx.x, quad, half, n_slow, p.n_kv);
+#endif
   // ---- epilogue: O / l -> bf16 -> swizzled staging -> TMA store ------------------------------------
   // the two partial row sums meet (slots of the parity the last step did not use)
   float* slot = xchg + (p.n_kv & 1) * 256;

@@ -156,57 +156,57 @@ __device__ __forceinline__ float bilerp(const float* __restrict__ plane, const T
 
 constexpr int kWarpThreads = 256;
 
-template <bool VEC4>
+// PX pixels per thread, a block apart: every load / store of a warp covers 32 consecutive pixels (one or
+// two 128-byte lines for the gathers when the flow is smooth), and the PX independent pixels of a thread
+// keep 20 * PX gather loads in flight.  Measured on 32 pairs of 1080p with smooth flows: 0.82 ms
+// (3.3 TB/s of algorithmic traffic) against 1.18 ms for the first version (4 adjacent pixels per thread, 128-bit flow loads), whose
+// warp-level gathers span four lines each.  ncu (profiles/r1_c): DRAM traffic = 1.0 x algorithmic, ~300
+// SASS instructions per pixel (address arithmetic and tap predicates): the kernel is issue-bound, not HBM-bound.
+template <int PX>
 __global__ void __launch_bounds__(kWarpThreads)
 backward_warp_kernel(const float* __restrict__ img2, const float* __restrict__ f_fwd, const float* __restrict__ f_bwd,
-                     float* __restrict__ warped, uint8_t* __restrict__ mask, int C, int H, int W, float alpha,
-                     float beta) {
-  constexpr int PX = VEC4 ? 4 : 1;
+                             float* __restrict__ warped, uint8_t* __restrict__ mask, int C, int H, int W, float alpha,
+                             float beta) {
   const int64_t b = blockIdx.y;
   const int64_t npix = (int64_t)H * W;
-  const int64_t off = ((int64_t)blockIdx.x * kWarpThreads + threadIdx.x) * PX;  // W % PX == 0: never straddles a row
-  if (off >= npix) return;
-  const int y = (int)(off / W);
-  const int x = (int)(off - (int64_t)y * W);
+  const int64_t off0 = (int64_t)blockIdx.x * (kWarpThreads * PX) + threadIdx.x;
   const float* ff = f_fwd + b * 2 * npix;
   const float* fbw = f_bwd + b * 2 * npix;
   float fx[PX], fy[PX];
-  if constexpr (VEC4) {
-    const float4 vx = *reinterpret_cast<const float4*>(ff + off);
-    const float4 vy = *reinterpret_cast<const float4*>(ff + npix + off);
-    fx[0] = vx.x; fx[1] = vx.y; fx[2] = vx.z; fx[3] = vx.w;
-    fy[0] = vy.x; fy[1] = vy.y; fy[2] = vy.z; fy[3] = vy.w;
-  } else {
-    fx[0] = ff[off];
-    fy[0] = ff[npix + off];
-  }
-  Tap tap[PX];
-  uint32_t mbits = 0;
+  bool in[PX];
 #pragma unroll
   for (int i = 0; i < PX; ++i) {
-    tap[i] = make_tap(x + i, y, fx[i], fy[i], W, H);
-    const float bx = bilerp(fbw, tap[i], W);
-    const float by = bilerp(fbw + npix, tap[i], W);
-    const float sx = fx[i] + bx, sy = fy[i] + by;
-    const float lhs = sx * sx + sy * sy;
-    const float rhs = alpha * (fx[i] * fx[i] + fy[i] * fy[i] + bx * bx + by * by) + beta;
-    const uint32_t m = (lhs > rhs ? 1u : 0u) | (tap[i].valid ? 2u : 0u);
-    mbits |= m << (8 * i);
+    const int64_t off = off0 + (int64_t)i * kWarpThreads;
+    in[i] = off < npix;
+    fx[i] = in[i] ? __ldg(ff + off) : 0.f;
+    fy[i] = in[i] ? __ldg(ff + npix + off) : 0.f;
   }
-  if constexpr (VEC4)
-    *reinterpret_cast<uint32_t*>(mask + b * npix + off) = mbits;
-  else
-    mask[b * npix + off] = (uint8_t)mbits;
+  Tap tap[PX];
+  float bx[PX], by[PX];
+#pragma unroll
+  for (int i = 0; i < PX; ++i) {
+    const int64_t off = in[i] ? off0 + (int64_t)i * kWarpThreads : 0;
+    const int y = (int)(off / W);
+    const int x = (int)(off - (int64_t)y * W);
+    tap[i] = make_tap(x, y, fx[i], fy[i], W, H);
+    bx[i] = bilerp(fbw, tap[i], W);
+    by[i] = bilerp(fbw + npix, tap[i], W);
+  }
+#pragma unroll
+  for (int i = 0; i < PX; ++i) {
+    const float sx = fx[i] + bx[i], sy = fy[i] + by[i];
+    const float lhs = sx * sx + sy * sy;
+    const float rhs = alpha * (fx[i] * fx[i] + fy[i] * fy[i] + bx[i] * bx[i] + by[i] * by[i]) + beta;
+    if (in[i]) mask[b * npix + off0 + (int64_t)i * kWarpThreads] = (uint8_t)((lhs > rhs ? 1u : 0u) | (tap[i].valid ? 2u : 0u));
+  }
   for (int c = 0; c < C; ++c) {
     const float* plane = img2 + (b * C + c) * npix;
     float r[PX];
 #pragma unroll
     for (int i = 0; i < PX; ++i) r[i] = bilerp(plane, tap[i], W);
-    float* dst = warped + (b * C + c) * npix + off;
-    if constexpr (VEC4)
-      __stcs(reinterpret_cast<float4*>(dst), make_float4(r[0], r[1], r[2], r[3]));
-    else
-      dst[0] = r[0];
+#pragma unroll
+    for (int i = 0; i < PX; ++i)
+      if (in[i]) __stcs(warped + (b * C + c) * npix + off0 + (int64_t)i * kWarpThreads, r[i]);
   }
 }
 
@@ -253,16 +253,11 @@ int tvi_backward_warp_f32(const float* img2, const float* f_fwd, const float* f_
   TVI_CHECK_ARG(f_fwd && f_bwd && mask && (C == 0 || (img2 && warped)), "tvi_backward_warp_f32: null pointer");
   TVI_CHECK_ARG(B <= 65535, "tvi_backward_warp_f32: at most 65535 image pairs per call");
   cudaStream_t st = (cudaStream_t)stream;
-  const bool vec = (W % 4 == 0) &&
-                   (((uintptr_t)f_fwd | (uintptr_t)warped | (uintptr_t)mask) % 16 == 0);
   const int64_t npix = (int64_t)H * W;
-  if (vec) {
-    dim3 grid((unsigned)((npix / 4 + kWarpThreads - 1) / kWarpThreads), (unsigned)B);
-    backward_warp_kernel<true><<<grid, kWarpThreads, 0, st>>>(img2, f_fwd, f_bwd, warped, mask, C, H, W, alpha, beta);
-  } else {
-    dim3 grid((unsigned)((npix + kWarpThreads - 1) / kWarpThreads), (unsigned)B);
-    backward_warp_kernel<false><<<grid, kWarpThreads, 0, st>>>(img2, f_fwd, f_bwd, warped, mask, C, H, W, alpha, beta);
-  }
+  constexpr int kPx = 2;
+  TVI_CHECK_ARG((npix + kWarpThreads * kPx - 1) / (kWarpThreads * kPx) < ((int64_t)1 << 31), "tvi_backward_warp_f32: image too large");
+  dim3 grid((unsigned)((npix + kWarpThreads * kPx - 1) / (kWarpThreads * kPx)), (unsigned)B);
+  backward_warp_kernel<kPx><<<grid, kWarpThreads, 0, st>>>(img2, f_fwd, f_bwd, warped, mask, C, H, W, alpha, beta);
   TVI_LAUNCH_OK("backward_warp_kernel");
   return TVI_OK;
 }

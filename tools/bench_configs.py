@@ -82,7 +82,10 @@ def cfg_flow(steps):
     for B in (1, 8, 32):
         g = torch.Generator().manual_seed(B)
         img = torch.rand(B, 3, H, W, generator=g).to(DEV)
-        f = (torch.randn(B, 2, H, W, generator=g) * 5).to(DEV)
+        # smooth flow fields (N(0, 5 px) blurred at ~15 px): a coarse random field,
+        # bicubically upsampled; the backward flow is the negated forward flow plus N(0, 0.2) noise
+        coarse = torch.randn(B, 2, H // 30, W // 30, generator=g).to(DEV) * 5
+        f = torch.nn.functional.interpolate(coarse, size=(H, W), mode="bicubic", align_corners=False).contiguous()
         fb = (-f + torch.randn(B, 2, H, W, generator=g).to(DEV) * 0.2)
         fa_hwc = f.permute(0, 2, 3, 1).contiguous()
         fb_hwc = fb.permute(0, 2, 3, 1).contiguous()

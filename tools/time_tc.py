@@ -8,7 +8,7 @@ dev = torch.device("cuda:0")
 B, heads, S = 28, 5, 9216
 C = heads * 64
 g = torch.Generator(device=dev).manual_seed(0)
-qkv = torch.randn(B * S, 3 * C, device=dev, generator=g).bfloat16()
+qkv = (torch.randn(B * S, 3 * C, device=dev, generator=g) * float(os.environ.get("TVI_TC_STD", "1"))).bfloat16()
 out = torch.empty(B * S, C, dtype=torch.bfloat16, device=dev)
 fl = 4.0 * B * heads * S * S * 64
 run = lambda: ops.attn_spatial(qkv[:, :C], qkv[:, C:2 * C], qkv[:, 2 * C:], B, heads, S, S, 0.125, out=out, algo=_lib.SPATIAL_TCGEN05)
