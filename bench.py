@@ -61,6 +61,18 @@ def peaks():
     return {"hbm": 6650.0, "tf_burst": 1590.0, "tf_sust": 1400.0, "src": "fallback"}
 
 
+def measured_traffic(level, clips):
+    """DRAM bytes per launch of the dominant kernel from the committed `ncu --set full` capture of this very
+    command (profiles/dominant_kernel_traffic.json, written by tools/ncu_summary.py), or None."""
+    p = ROOT / "profiles" / "dominant_kernel_traffic.json"
+    if not p.exists():
+        return None, None
+    d = json.loads(p.read_text())
+    if d.get("workload") != workload_name(level, clips):
+        return None, None
+    return d.get("dram_bytes_per_launch"), d.get("source")
+
+
 def workload_name(level, clips):
     C, heads, h, w = LEVELS[level]
     return f"svd_xt_{level}_block_attention_576x1024_T{T_FRAMES}_cfg{CFG}_clips{clips}"
@@ -98,7 +110,7 @@ class ClockSampler:
     def start(self):
         try:
             self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}",
-                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                          "--format=csv,noheader,nounits", "-lms", "20"],
                                          stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.thread = threading.Thread(target=self._pump, daemon=True)
             self.thread.start()
@@ -286,7 +298,6 @@ def main():
         ops.EVENT_HOOK = None
         launches = ops.LAUNCHES - launches0
         ms_total = e0.elapsed_time(e1)
-        clocks = sampler.stop()
         dom_ms = [dom_events[i].elapsed_time(dom_events[i + 1]) for i in range(0, len(dom_events), 2)]
         # ---------------- timed region 2: host buffers, H2D + D2H inside (`e2e`) ----------------
         for _ in range(2):
@@ -303,6 +314,7 @@ def main():
         f1.record()
         barrier()
         ms_e2e = f0.elapsed_time(f1)
+        clocks = sampler.stop()  # samples cover both timed regions
 
     from timelapse_video_interpolation_b200 import sharding
     ms_total, ms_e2e = sharding.max_over_ranks(ms_total, dev), sharding.max_over_ranks(ms_e2e, dev)
@@ -315,6 +327,7 @@ def main():
         pk = peaks()
         fl = algorithmic_flops(args.level, args.clips)
         dom_avg_ms = sum(dom_ms) / len(dom_ms)
+        traffic, traffic_src = measured_traffic(args.level, args.clips)
         achieved = fl["spatial_core"] / (dom_avg_ms * 1e-3) / 1e12
         h2d = x_pin.numel() * 2 + cs_pin.numel() * 2 + ct_pin.numel() * 2
         line = {
@@ -331,7 +344,8 @@ def main():
             "gpu_launches": launches,
             "clocks": clocks,
             "roofline": {"kernel": "attn_spatial_tc_kernel", "bound": "tensor", "achieved": achieved, "peak": pk["tf_sust"],
-                         "unit": "TFLOP/s", "frac": achieved / pk["tf_sust"], "traffic": None, "peak_source": pk["src"] + " (sustained)",
+                         "unit": "TFLOP/s", "frac": achieved / pk["tf_sust"], "traffic": traffic, "traffic_source": traffic_src,
+                         "peak_source": pk["src"] + " (sustained)",
                          "ms_per_launch": dom_avg_ms, "share_of_step": dom_avg_ms / (ms_total / args.steps),
                          "algorithmic_flops_per_launch": fl["spatial_core"]},
             "step_tflops": fl["total"] / 1e12 / (ms_total / args.steps * 1e-3),
