@@ -286,3 +286,20 @@ def test_processor_backward_fp32_parameters_cast_inputs(cuda):
     _, ref = attention_ref.attn_processor_grads_ref(ref_attn, x, None, dy)
     _grad_close(x.grad.cpu(), ref["x"], "fp32 dx", tol=3e-2)
     _grad_close(attn.to_v.weight.grad.cpu(), ref["to_v"], "fp32 dWv", tol=3e-2)
+
+
+def test_backward_as_first_cuda_work_of_the_autograd_thread():
+    # regression: the autograd engine's worker thread reaches cuTensorMapEncodeTiled (a driver call) with no
+    # context bound when a libtvi GEMM is its very first CUDA work -> CUDA_ERROR_INVALID_CONTEXT
+    import subprocess
+    import sys
+    from pathlib import Path
+    root = Path(__file__).resolve().parents[1]
+    code = ("import torch, sys; sys.path.insert(0, %r)\n"
+            "from timelapse_video_interpolation_b200.modules import Attention\n"
+            "a = Attention(320, None, heads=5).to('cuda', torch.bfloat16)\n"
+            "x = torch.randn(4, 14, 320, device='cuda').to(torch.bfloat16).requires_grad_(True)\n"
+            "a(x).float().sum().backward(); torch.cuda.synchronize()\n"
+            "assert bool(torch.isfinite(x.grad.float()).all()); print('ok')\n") % str(root)
+    r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0 and "ok" in r.stdout, r.stderr[-2000:]

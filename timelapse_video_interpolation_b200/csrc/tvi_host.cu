@@ -61,6 +61,15 @@ int make_tensor_map(CUtensorMap* map, const void* base, int elem_bytes, int rank
                     const uint64_t* strides_bytes, const uint32_t* box, Swizzle swz) {
   EncodeTiledFn fn = encode_tiled_fn();
   if (!fn) return fail(TVI_ERR_CUDA, "cuTensorMapEncodeTiled is not available from this driver");
+  // cuTensorMapEncodeTiled is a DRIVER call: it needs a context current on the calling thread.  A thread that
+  // has only been handed a device by cudaSetDevice-less frameworks (the autograd engine's worker thread calls
+  // into libtvi with the backward GEMM as its very first CUDA work) may not have one bound yet
+  // (CUDA_ERROR_INVALID_CONTEXT); cudaFree(0) binds the runtime's primary context.  Once per thread.
+  static thread_local bool ctx_bound = false;
+  if (!ctx_bound) {
+    TVI_CUDA_OK(cudaFree(nullptr));
+    ctx_bound = true;
+  }
   CUtensorMapDataType dt;
   switch (elem_bytes) {
     case 2: dt = CU_TENSOR_MAP_DATA_TYPE_BFLOAT16; break;
