@@ -22,6 +22,8 @@
 //   kAMn + kBMn   dW[N,K] = dY[M,N]^T . X[M,K]    both operands MN-major, the token reduction is split
 //   + kSplit      across CTAs, fp32 partial tiles go to a workspace and wgrad_reduce_kernel sums them
 //                 in a fixed order (deterministic) into bf16.
+#include <stdlib.h>
+
 #include "tvi_common.cuh"
 
 namespace tvi {
@@ -29,10 +31,12 @@ namespace {
 
 constexpr int kBM = 128;
 constexpr int kBK = 64;
-constexpr int kGemmThreads = 192;
+constexpr int kEpiWarps = 4;                        // 4: one per TMEM lane quadrant; 8: two per quadrant, alternate chunks
+constexpr int kGemmThreads = 64 + 32 * kEpiWarps;
 constexpr int kAccStride = 256;                    // TMEM columns per accumulator stage
 constexpr int kABytes = kBM * kBK * 2;             // 16 KB
-constexpr int kStagingBytes = 4 * 2 * 32 * 64;     // 4 epilogue warps x 2 buffers x [32 rows][64 B]
+constexpr int kStageBufs = 2;                      // output staging buffers per epilogue warp (TMA stores in flight)
+constexpr int kStagingBytes = kEpiWarps * kStageBufs * 2048 + kEpiWarps * 1024;  // warps x bufs x [32 rows][64 B] + warps x 256 fp32 bias
 constexpr int kMaxStages = 8;
 
 struct GemmParams {
@@ -44,6 +48,7 @@ struct GemmParams {
   int N;
   int stages;
   const tvi_bf16* bias;
+  int res_b;           // the CTA's B slice [BN x K] stays resident in shared memory (grid is a multiple of n_tiles)
   float* partial;      // kSplit: [splits][M_out][ldp] fp32
   int64_t M_out;
   int64_t ldp;
@@ -60,6 +65,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
   __shared__ __align__(8) uint64_t bar_empty[kMaxStages];
   __shared__ __align__(8) uint64_t bar_acc_full[2];
   __shared__ __align__(8) uint64_t bar_acc_empty[2];
+  __shared__ __align__(8) uint64_t bar_w;
   __shared__ uint32_t s_tmem_base;
 
   const int warp = threadIdx.x >> 5;
@@ -68,9 +74,17 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   uint8_t* base_ptr = smem_raw + (base - smem_u32(smem_raw));
   const uint32_t b_bytes = (uint32_t)p.BN * kBK * 2;
-  const uint32_t stage_bytes = kABytes + b_bytes;
-  const uint32_t staging = base + p.stages * stage_bytes;
-  uint8_t* staging_ptr = base_ptr + p.stages * stage_bytes;
+  // Resident-B mode (forward projections at K = 320): with gridDim.x a multiple of n_tiles the walk
+  // tile = blockIdx.x + i * gridDim.x keeps nt = blockIdx.x % n_tiles, so the CTA's [BN x K] weight slice is
+  // loaded ONCE and only X streams through the ring.  Re-fetching the slice per tile made the L2 -> SM
+  // traffic 2.5x the X traffic (123 KB of W per 82 KB of X at N = 960) and capped the kernel at 3.8 TB/s.
+  const bool res_b = p.res_b != 0;
+  const uint32_t stage_bytes = res_b ? (uint32_t)kABytes : kABytes + b_bytes;
+  const uint32_t res_bytes = res_b ? (uint32_t)p.k_blocks_total * b_bytes : 0u;
+  const uint32_t wres = base + p.stages * stage_bytes;
+  uint8_t* wres_ptr = base_ptr + p.stages * stage_bytes;
+  const uint32_t staging = wres + res_bytes;
+  uint8_t* staging_ptr = wres_ptr + res_bytes;
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmX);
@@ -80,9 +94,10 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
       mbar_init(&bar_full[s], 1);
       mbar_init(&bar_empty[s], 1);
     }
+    mbar_init(&bar_w, 1);
     for (int s = 0; s < 2; ++s) {
       mbar_init(&bar_acc_full[s], 1);
-      mbar_init(&bar_acc_empty[s], 4);
+      mbar_init(&bar_acc_empty[s], kEpiWarps);
     }
     mbar_fence_init();
   }
@@ -103,6 +118,11 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
     if (lane == 0) {
       int s = 0;
       uint32_t ph = 0;
+      if (res_b && blockIdx.x < n_tiles_total) {
+        const int n0 = (int)(blockIdx.x % p.n_tiles) * p.BN;
+        mbar_arrive_expect_tx(&bar_w, res_bytes);
+        for (int kb = 0; kb < p.k_blocks_total; ++kb) tma_load_2d(wres_ptr + kb * b_bytes, &tmW, &bar_w, kb * kBK, n0);
+      }
       for (int64_t tile = blockIdx.x; tile < n_tiles_total; tile += gridDim.x) {
         const int64_t split = kSplit ? tile / mn_tiles : 0;
         const int64_t mn = tile - split * mn_tiles;
@@ -122,7 +142,9 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
             tma_load_2d(a_dst, &tmX, &bar_full[s], m0, kb * kBK);
             tma_load_2d(a_dst + 8192, &tmX, &bar_full[s], m0 + 64, kb * kBK);
           }
-          if (!kBMn) {
+          if (res_b) {
+            // B is resident
+          } else if (!kBMn) {
             tma_load_2d(a_dst + kABytes, &tmW, &bar_full[s], kb * kBK, n0);
           } else {
             for (int hb = 0; hb < p.BN / 64; ++hb)
@@ -146,6 +168,10 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
     uint32_t ph = 0;
     int as = 0;
     uint32_t aph = 0;
+    if (res_b && blockIdx.x < n_tiles_total) {
+      mbar_wait(&bar_w, 0);
+      tc_fence_after();
+    }
     for (int64_t tile = blockIdx.x; tile < n_tiles_total; tile += gridDim.x) {
       mbar_wait(&bar_acc_empty[as], aph ^ 1);
       tc_fence_after();
@@ -157,7 +183,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
         mbar_wait(&bar_full[s], ph);
         tc_fence_after();
         const uint32_t a_addr = base + s * stage_bytes;
-        const uint32_t b_addr = a_addr + kABytes;
+        const uint32_t b_addr = res_b ? wres + (uint32_t)(kb_lo + kb) * b_bytes : a_addr + kABytes;
 #pragma unroll
         for (int kk = 0; kk < kBK / 16; ++kk) {
           // K-major: 16 reduction elements = 32 bytes along the swizzled 128-byte row.
@@ -182,10 +208,15 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
     }
     __syncwarp();
   } else {
-    // ===================== epilogue (warps 2..5) =====================
+    // ===================== epilogue (warps 2 .. 2 + kEpiWarps) =====================
+    // kEpiWarps = 8 puts two warps on every TMEM lane quadrant (alternate 32-column chunks); measured at the L0
+    // shapes it buys nothing (the epilogue is not the critical path) and its staging costs two ring stages.
     const int quad = warp & 3;  // TMEM lane quadrant this warp may read
-    const uint32_t my_staging = staging + (warp - 2) * 2 * 2048;
-    uint8_t* my_staging_ptr = staging_ptr + (warp - 2) * 2 * 2048;
+    const int chalf = (warp - 2) >> 2;
+    constexpr int kChunkStep = kEpiWarps / 4;
+    const uint32_t my_staging = staging + (warp - 2) * kStageBufs * 2048;
+    uint8_t* my_staging_ptr = staging_ptr + (warp - 2) * kStageBufs * 2048;
+    float* my_bias = reinterpret_cast<float*>(staging_ptr + kEpiWarps * kStageBufs * 2048 + (warp - 2) * 1024);
     int buf = 0;
     int as = 0;
     uint32_t aph = 0;
@@ -196,14 +227,26 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
       const int64_t mt = mn / p.n_tiles;
       const int nt = (int)(mn - mt * p.n_tiles);
       const int m0 = (int)(mt * kBM), n0 = nt * p.BN;
+      if (!kSplit && p.bias != nullptr) {
+        // this tile's bias slice as fp32 in the warp's own shared-memory strip (read back as broadcast LDS.128)
+        __syncwarp();
+        for (int c = lane; c < p.BN; c += 32)
+          my_bias[c] = (n0 + c < p.N) ? __bfloat162float(*reinterpret_cast<const __nv_bfloat16*>(p.bias + n0 + c)) : 0.f;
+        __syncwarp();
+      }
       mbar_wait(&bar_acc_full[as], aph);
       tc_fence_after();
       const uint32_t t_row = tmem_base + ((uint32_t)(quad * 32) << 16) + as * kAccStride;
-      for (int c = 0; c < chunks; ++c) {
+      if (chalf >= chunks) {  // a one-chunk tile leaves the second warp of the quadrant without work
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&bar_acc_empty[as]);
+      }
+      for (int c = chalf; c < chunks; c += kChunkStep) {
         uint32_t r[32];
         tmem_ld_x32(t_row + c * 32, r);
         tmem_ld_wait();
-        if (c == chunks - 1) {
+        if (c + kChunkStep >= chunks) {
           // every column of this accumulator stage is now in registers
           tc_fence_before();
           __syncwarp();
@@ -228,18 +271,16 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
         for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(r[j]);
         if (p.bias != nullptr) {
 #pragma unroll
-          for (int j = 0; j < 32; j += 2) {
-            // N % 8 == 0, so a pair never straddles the end of the bias vector
-            if (ncol0 + j < p.N) {
-              const __nv_bfloat162 b2 = *reinterpret_cast<const __nv_bfloat162*>(p.bias + ncol0 + j);
-              const float2 bf = __bfloat1622float2(b2);
-              f[j] += bf.x;
-              f[j + 1] += bf.y;
-            }
+          for (int j = 0; j < 32; j += 4) {
+            const float4 b4 = *reinterpret_cast<const float4*>(my_bias + c * 32 + j);
+            f[j] += b4.x;
+            f[j + 1] += b4.y;
+            f[j + 2] += b4.z;
+            f[j + 3] += b4.w;
           }
         }
-        // staging buffer `buf` was last read by the TMA store issued two chunks ago
-        if (lane == 0) tma_store_wait_read<1>();
+        // staging buffer `buf` was last read by the TMA store issued kStageBufs chunks ago
+        if (lane == 0) tma_store_wait_read<kStageBufs - 1>();
         __syncwarp();
         uint8_t* row_ptr = my_staging_ptr + buf * 2048 + lane * 64;
         const int sw = (lane >> 1) & 3;
@@ -258,7 +299,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
           tma_store_2d(&tmY, reinterpret_cast<const void*>(my_staging_ptr + buf * 2048), ncol0, m0 + quad * 32);
           tma_store_commit();
         }
-        buf ^= 1;
+        buf = (buf + 1) & (kStageBufs - 1);
       }
       if (++as == 2) {
         as = 0;
@@ -344,6 +385,10 @@ int launch_gemm(const char* name, const tvi_bf16* A, const tvi_bf16* B, const tv
                 int splits, int64_t Mo, int No, int64_t R, int64_t lda, int64_t ldb, int64_t ldy, cudaStream_t st) {
   GemmParams p;
   p.BN = pick_bn(No, kBMn ? 64 : 32);
+  if (const char* e = getenv("TVI_GEMM_BN")) {
+    const int bn = atoi(e);
+    if (!kBMn && bn >= 32 && bn <= 256 && bn % 32 == 0) p.BN = bn;
+  }
   p.N = No;
   p.m_tiles = (Mo + kBM - 1) / kBM;
   p.n_tiles = (No + p.BN - 1) / p.BN;
@@ -353,13 +398,19 @@ int launch_gemm(const char* name, const tvi_bf16* A, const tvi_bf16* B, const tv
   p.partial = partial;
   p.M_out = Mo;
   p.ldp = No;
-  const int stage_bytes = kABytes + p.BN * kBK * 2;
-  const int smem_cap = 227 * 1024 - 1024 /*alignment slack*/ - kStagingBytes - 256 /*static*/;
+  const int b_bytes = p.BN * kBK * 2;
+  const int res_bytes = p.k_blocks_total * b_bytes;
+  const int sms = num_sms();
+  // resident weight slice: plain forward GEMM, slice <= 128 KB, and enough row tiles per CTA to amortise it
+  p.res_b = (!kAMn && !kBMn && !kSplit && res_bytes <= 128 * 1024 && p.n_tiles <= sms &&
+             p.m_tiles * p.n_tiles >= 4 * (int64_t)sms) ? 1 : 0;
+  const int stage_bytes = p.res_b ? kABytes : kABytes + b_bytes;
+  const int smem_cap = 227 * 1024 - 1024 /*alignment slack*/ - kStagingBytes - 256 /*static*/ - (p.res_b ? res_bytes : 0);
   int stages = smem_cap / stage_bytes;
   if (stages > kMaxStages) stages = kMaxStages;
   TVI_CHECK_ARG(stages >= 2, "%s: tile does not fit shared memory", name);
   p.stages = stages;
-  const int smem_bytes = 1024 + stages * stage_bytes + kStagingBytes;
+  const int smem_bytes = 1024 + stages * stage_bytes + kStagingBytes + (p.res_b ? res_bytes : 0);
 
   CUtensorMap tmA, tmB, tmY;
   int rc = operand_map(&tmA, A, kAMn, Mo, R, lda, kBM);
@@ -379,8 +430,7 @@ int launch_gemm(const char* name, const tvi_bf16* A, const tvi_bf16* B, const tv
   if (rc) return rc;
   int64_t grid = p.m_tiles * p.n_tiles;
   if (kSplit) grid *= (p.k_blocks_total + p.k_blocks - 1) / p.k_blocks;
-  const int sms = num_sms();
-  if (grid > sms) grid = sms;
+  if (grid > sms) grid = p.res_b ? (sms / p.n_tiles) * p.n_tiles : sms;
   gemm_bf16_kernel<kAMn, kBMn, kSplit><<<(unsigned)grid, kGemmThreads, smem_bytes, st>>>(tmA, tmB, tmY, p);
   TVI_LAUNCH_OK(name);
   return TVI_OK;
