@@ -84,6 +84,30 @@ int tvi_backward_warp_f32(const float* img2, const float* f_fwd, const float* f_
 int tvi_gemm_bf16_tn(const tvi_bf16* X, const tvi_bf16* W, const tvi_bf16* bias, tvi_bf16* Y, int64_t M, int N,
                      int K, int64_t ldx, int64_t ldw, int64_t ldy, void* stream);
 
+/* N1: the same GEMM with a fused epilogue, for FeedForward / GEGLU and residual adds.
+ * Replaces: FeedForward.forward (src/models/attention.py:481-535) = GEGLU.proj (nn.Linear dim -> 2*inner),
+ * chunk(2), hidden * gelu(gate), net[2] (nn.Linear inner -> dim), and the `ff_output + hidden_states` residual
+ * adds of BasicTransformerBlock / TemporalBasicTransformerBlock (:343, :449, :472).
+ *   epilogue NONE : Y[M,N]   = X . W^T + bias + residual
+ *   epilogue GEGLU: Y[M,N/2] = (X . Wv^T + bv) * gelu(X . Wg^T + bg) + residual, where W[N,K] / bias[N] hold the
+ *                   value and gate rows interleaved in blocks of H = tvi_geglu_block(N/2): rows
+ *                   [2Hb, 2Hb+H) = value rows [Hb, Hb+H), rows [2Hb+H, 2Hb+2H) = the gate rows of the same
+ *                   outputs (the host re-orders GEGLU.proj.weight once; erf-form gelu in fp32).
+ *   bias, residual nullable; residual is [M, N or N/2] with row stride ldr.
+ */
+#define TVI_EPILOGUE_NONE 0
+#define TVI_EPILOGUE_GEGLU 1
+int tvi_geglu_block(int inner);
+int tvi_gemm_bf16_tn_ex(const tvi_bf16* X, const tvi_bf16* W, const tvi_bf16* bias, const tvi_bf16* residual, tvi_bf16* Y,
+                        int64_t M, int N, int K, int64_t ldx, int64_t ldw, int64_t ldr, int64_t ldy, int epilogue,
+                        void* stream);
+
+/* LayerNorm over the channel dimension of token-major activations (fp32 statistics, bf16 in/out).
+ * Replaces: nn.LayerNorm norm1/norm2/norm3 and norm_in of the transformer blocks
+ * (src/models/attention.py:270, :300, :321 and :441, :446, :462).  gamma, beta nullable; C % 8 == 0, C <= 2048. */
+int tvi_layernorm_bf16(const tvi_bf16* x, const tvi_bf16* gamma, const tvi_bf16* beta, tvi_bf16* y, int64_t M, int C,
+                       int64_t ldx, int64_t ldy, float eps, void* stream);
+
 /* Backward of the projections (training config 5: src/train_decouples.py back-propagates through the
  * same nn.Linear call sites; autograd's F.linear backward = two cuBLAS GEMMs + a bias column sum).
  *   dgrad : dX[M,K] = dY[M,N] . W[N,K]          (W consumed in place, MN-major tcgen05 operand)

@@ -1,0 +1,96 @@
+"""GPU: FeedForward (GEGLU) / LayerNorm / fused-epilogue GEMM through the C ABI vs the CPU oracle on the same
+bf16-rounded inputs and weights (tolerance of the attention path: 2e-2 max-abs)."""
+import numpy as np
+import pytest
+import torch
+
+import timelapse_video_interpolation_b200 as tvi
+from oracle import feedforward_ref
+from timelapse_video_interpolation_b200 import ops
+from timelapse_video_interpolation_b200.modules import FeedForward
+
+pytestmark = pytest.mark.gpu
+TOL = 2e-2
+
+
+def _ff(dim, dim_out, seed, device):
+    g = torch.Generator().manual_seed(seed)
+    ff = FeedForward(dim, dim_out)
+    with torch.no_grad():
+        for p in ff.parameters():
+            p.copy_(torch.randn(p.shape, generator=g) * (p.shape[-1] ** -0.5 if p.dim() > 1 else 0.1))
+    return ff.to(device=device, dtype=torch.bfloat16).eval()
+
+
+@pytest.mark.parametrize("rows,dim,dim_out", [(300, 320, None), (4032, 320, None), (1000, 640, None), (777, 1280, None),
+                                              (130, 320, 640), (64, 96, None)])
+def test_feed_forward_matches_oracle(cuda, rows, dim, dim_out):
+    ff = _ff(dim, dim_out, rows + dim, cuda)
+    g = torch.Generator().manual_seed(rows)
+    x = torch.randn(2, rows // 2, dim, generator=g).to(torch.bfloat16).to(cuda)
+    with torch.no_grad():
+        y = tvi.feed_forward(ff, x)
+    torch.cuda.synchronize()
+    ref = feedforward_ref.feed_forward_ref(ff, x)
+    assert y.shape == ref.shape and y.dtype == torch.bfloat16
+    err = float((y.float().cpu() - ref).abs().max())
+    print(f"feed_forward rows={rows} dim={dim}: max abs err {err:.3e}, max |ref| {float(ref.abs().max()):.3f}")
+    assert err <= TOL * max(1.0, float(ref.abs().max()))
+
+
+def test_feed_forward_with_fused_residual_and_install(cuda):
+    ff = _ff(320, None, 5, cuda)
+    g = torch.Generator().manual_seed(5)
+    x = torch.randn(3, 200, 320, generator=g).to(torch.bfloat16).to(cuda)
+    res = torch.randn(3, 200, 320, generator=g).to(torch.bfloat16).to(cuda)
+    with torch.no_grad():
+        y = tvi.feed_forward(ff, x, residual=res)
+        assert tvi.install_feed_forward(ff) == 1
+        y2 = ff(x)           # the re-bound forward
+        assert tvi.uninstall_feed_forward(ff) == 1
+        y3 = ff(x)           # stock eager forward again (torch bf16)
+    torch.cuda.synchronize()
+    ref = feedforward_ref.feed_forward_ref(ff, x, residual=res)
+    assert float((y.float().cpu() - ref).abs().max()) <= TOL * max(1.0, float(ref.abs().max()))
+    ref2 = feedforward_ref.feed_forward_ref(ff, x)
+    assert float((y2.float().cpu() - ref2).abs().max()) <= TOL * max(1.0, float(ref2.abs().max()))
+    assert float((y3.float().cpu() - ref2).abs().max()) <= 2 * TOL * max(1.0, float(ref2.abs().max()))
+
+
+def test_feed_forward_refuses_gradients_and_bad_inputs(cuda):
+    ff = _ff(320, None, 6, cuda)
+    x = torch.randn(2, 16, 320, device=cuda).to(torch.bfloat16).requires_grad_(True)
+    with pytest.raises(NotImplementedError):
+        tvi.feed_forward(ff, x)
+    with torch.no_grad(), pytest.raises(tvi.TviError):
+        tvi.feed_forward(ff, x.float())
+
+
+@pytest.mark.parametrize("rows,C", [(1000, 320), (4032, 640), (333, 1280), (50, 2048), (7, 8)])
+def test_layer_norm_matches_oracle(cuda, rows, C):
+    g = torch.Generator().manual_seed(rows + C)
+    norm = torch.nn.LayerNorm(C)
+    with torch.no_grad():
+        norm.weight.copy_(1 + 0.1 * torch.randn(C, generator=g))
+        norm.bias.copy_(0.1 * torch.randn(C, generator=g))
+    norm = norm.to(cuda, torch.bfloat16)
+    x = (torch.randn(rows, C, generator=g) * 3 + 5).to(torch.bfloat16).to(cuda)  # large mean: two-pass variance
+    y = tvi.layer_norm(norm, x)
+    torch.cuda.synchronize()
+    ref = feedforward_ref.layer_norm_ref(norm, x)
+    err = float((y.float().cpu() - ref).abs().max())
+    print(f"layer_norm rows={rows} C={C}: max abs err {err:.3e}")
+    assert err <= 2 ** -7 * max(1.0, float(ref.abs().max()))  # one bf16 rounding of the result
+
+
+def test_gemm_residual_epilogue(cuda):
+    g = torch.Generator().manual_seed(11)
+    M, N, K = 1000, 320, 1280
+    x = torch.randn(M, K, generator=g).to(torch.bfloat16).to(cuda)
+    w = (torch.randn(N, K, generator=g) * K ** -0.5).to(torch.bfloat16).to(cuda)
+    b = torch.randn(N, generator=g).to(torch.bfloat16).to(cuda)
+    r = torch.randn(M, N, generator=g).to(torch.bfloat16).to(cuda)
+    y = ops.gemm_bf16_tn_ex(x, w, b, residual=r)
+    torch.cuda.synchronize()
+    ref = x.float().cpu() @ w.float().cpu().t() + b.float().cpu() + r.float().cpu()
+    assert float((y.float().cpu() - ref).abs().max()) <= 2 ** -7 * float(ref.abs().max()) + 1e-2

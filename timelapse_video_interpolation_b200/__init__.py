@@ -4,13 +4,16 @@ Public surface (mirrors the reference's interfaces for this path, SURVEY.md §8.
   TviAttnProcessor, install, uninstall   diffusers AttentionProcessor plugin
   slerp                                  first/last-frame latent slerp
   cosine_similarity, backward_warp_check optical-flow checks
+  feed_forward, layer_norm, install_feed_forward   FeedForward (GEGLU) / LayerNorm of the blocks
 Everything runs through libtvi.so (include/tvi.h); there is no CPU or torch fallback.
 """
 from . import _lib, ops  # noqa: F401
 from ._lib import TviError, version  # noqa: F401
+from .feedforward import feed_forward, install_feed_forward, layer_norm, uninstall_feed_forward  # noqa: F401
 from .flow import backward_warp_check, cosine_similarity, cosine_similarity_chw  # noqa: F401
 from .processor import TviAttnProcessor, install, uninstall  # noqa: F401
 from .slerp import slerp  # noqa: F401
 
 __all__ = ["TviAttnProcessor", "install", "uninstall", "slerp", "cosine_similarity", "cosine_similarity_chw",
-           "backward_warp_check", "TviError", "version", "ops"]
+           "backward_warp_check", "feed_forward", "layer_norm", "install_feed_forward", "uninstall_feed_forward",
+           "TviError", "version", "ops"]

@@ -38,6 +38,9 @@ SIGNATURES = {
     "tvi_flow_cosine_f32": (_i32, [_ptr, _ptr, _ptr, _ptr, _i64, _i32, _i32, _i32, _ptr]),
     "tvi_backward_warp_f32": (_i32, [_ptr, _ptr, _ptr, _ptr, _ptr, _i64, _i32, _i32, _i32, _f32, _f32, _ptr]),
     "tvi_gemm_bf16_tn": (_i32, [_ptr, _ptr, _ptr, _ptr, _i64, _i32, _i32, _i64, _i64, _i64, _ptr]),
+    "tvi_geglu_block": (_i32, [_i32]),
+    "tvi_gemm_bf16_tn_ex": (_i32, [_ptr, _ptr, _ptr, _ptr, _ptr, _i64, _i32, _i32, _i64, _i64, _i64, _i64, _i32, _ptr]),
+    "tvi_layernorm_bf16": (_i32, [_ptr, _ptr, _ptr, _ptr, _i64, _i32, _i64, _i64, _f32, _ptr]),
     "tvi_gemm_bf16_dgrad": (_i32, [_ptr, _ptr, _ptr, _i64, _i32, _i32, _i64, _i64, _i64, _ptr]),
     "tvi_gemm_bf16_wgrad_workspace_bytes": (_sz, [_i64, _i32, _i32]),
     "tvi_gemm_bf16_wgrad": (_i32, [_ptr, _ptr, _ptr, _ptr, _i64, _i32, _i32, _i64, _i64, _i64, _ptr]),
@@ -58,6 +61,7 @@ SIGNATURES = {
     "tvi_attn_fewkeys_bwd": (_i32, [_ptr] * 8 + [_i64, _i64, _i32, _i32, _i32] + [_i64] * 7 + [_f32, _i32, _ptr, _ptr]),
 }
 SPATIAL_AUTO, SPATIAL_MMA_SYNC, SPATIAL_TCGEN05 = 0, 1, 2
+EPILOGUE_NONE, EPILOGUE_GEGLU = 0, 1
 
 _lib = None
 

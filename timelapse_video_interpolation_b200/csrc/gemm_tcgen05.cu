@@ -48,6 +48,10 @@ struct GemmParams {
   int N;
   int stages;
   const tvi_bf16* bias;
+  int geglu;           // epilogue: columns [0, BN/2) of a tile are values, [BN/2, BN) their gates -> value * gelu(gate)
+  int N_store;         // columns of Y (N, or N/2 with the GEGLU epilogue)
+  const tvi_bf16* residual;  // nullable [M, N_store] (ldr): added after bias / activation
+  int64_t ldr;
   int res_b;           // the CTA's B slice [BN x K] stays resident in shared memory (grid is a multiple of n_tiles)
   float* partial;      // kSplit: [splits][M_out][ldp] fp32
   int64_t M_out;
@@ -242,18 +246,20 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
         __syncwarp();
         if (lane == 0) mbar_arrive(&bar_acc_empty[as]);
       }
-      for (int c = chalf; c < chunks; c += kChunkStep) {
-        uint32_t r[32];
+      const int out_chunks = p.geglu ? chunks / 2 : chunks;
+      for (int c = chalf; c < out_chunks; c += kChunkStep) {
+        uint32_t r[32], rg[32];
         tmem_ld_x32(t_row + c * 32, r);
+        if (p.geglu) tmem_ld_x32(t_row + (out_chunks + c) * 32, rg);
         tmem_ld_wait();
-        if (c + kChunkStep >= chunks) {
-          // every column of this accumulator stage is now in registers
+        if (c + kChunkStep >= out_chunks) {
+          // every column this warp needs of the accumulator stage is now in registers
           tc_fence_before();
           __syncwarp();
           if (lane == 0) mbar_arrive(&bar_acc_empty[as]);
         }
-        const int ncol0 = n0 + c * 32;
-        if (ncol0 >= p.N) continue;  // tile column tail: nothing to store (warp-uniform)
+        const int ncol0 = (p.geglu ? (n0 >> 1) : n0) + c * 32;
+        if (ncol0 >= p.N_store) continue;  // tile column tail: nothing to store (warp-uniform)
         if (kSplit) {
           // fp32 partial tile: each thread owns 32 consecutive columns of one output row
           const int64_t row = (int64_t)m0 + quad * 32 + lane;
@@ -277,6 +283,34 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
             f[j + 1] += b4.y;
             f[j + 2] += b4.z;
             f[j + 3] += b4.w;
+          }
+        }
+        if (p.geglu) {
+          // GEGLU (diffusers GEGLU.forward: hidden * F.gelu(gate), erf form): gate = the partner column
+#pragma unroll
+          for (int j = 0; j < 32; ++j) {
+            float g = __uint_as_float(rg[j]);
+            if (p.bias != nullptr) g += my_bias[(out_chunks + c) * 32 + j];
+            f[j] *= 0.5f * g * (1.0f + erff(g * 0.70710678118654752f));
+          }
+        }
+        if (p.residual != nullptr) {
+          const int64_t row = (int64_t)m0 + quad * 32 + lane;
+          if (row < p.M_out) {
+            const tvi_bf16* rp = p.residual + row * p.ldr + ncol0;
+#pragma unroll
+            for (int j = 0; j < 32; j += 8) {
+              if (ncol0 + j < p.N_store) {  // N_store % 8 == 0
+                const uint4 u = __ldg(reinterpret_cast<const uint4*>(rp + j));
+                const __nv_bfloat162* h2 = reinterpret_cast<const __nv_bfloat162*>(&u);
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                  const float2 t2 = __bfloat1622float2(h2[q]);
+                  f[j + 2 * q] += t2.x;
+                  f[j + 2 * q + 1] += t2.y;
+                }
+              }
+            }
           }
         }
         // staging buffer `buf` was last read by the TMA store issued kStageBufs chunks ago
@@ -382,13 +416,19 @@ int configure_once() {
 // lda; B is [No, R] or [R, No] with row stride ldb.  Output: bf16 Y (ldy) through TMA, or fp32 partials when kSplit.
 template <bool kAMn, bool kBMn, bool kSplit>
 int launch_gemm(const char* name, const tvi_bf16* A, const tvi_bf16* B, const tvi_bf16* bias, tvi_bf16* Y, float* partial,
-                int splits, int64_t Mo, int No, int64_t R, int64_t lda, int64_t ldb, int64_t ldy, cudaStream_t st) {
+                int splits, int64_t Mo, int No, int64_t R, int64_t lda, int64_t ldb, int64_t ldy, cudaStream_t st,
+                int geglu_block = 0, const tvi_bf16* residual = nullptr, int64_t ldr = 0) {
   GemmParams p;
   p.BN = pick_bn(No, kBMn ? 64 : 32);
   if (const char* e = getenv("TVI_GEMM_BN")) {
     const int bn = atoi(e);
     if (!kBMn && bn >= 32 && bn <= 256 && bn % 32 == 0) p.BN = bn;
   }
+  if (geglu_block > 0) p.BN = 2 * geglu_block;  // a tile = geglu_block value columns + their gate columns
+  p.geglu = geglu_block > 0 ? 1 : 0;
+  p.N_store = geglu_block > 0 ? No / 2 : No;
+  p.residual = residual;
+  p.ldr = ldr;
   p.N = No;
   p.m_tiles = (Mo + kBM - 1) / kBM;
   p.n_tiles = (No + p.BN - 1) / p.BN;
@@ -418,7 +458,7 @@ int launch_gemm(const char* name, const tvi_bf16* A, const tvi_bf16* B, const tv
   rc = operand_map(&tmB, B, kBMn, No, R, ldb, p.BN);
   if (rc) return rc;
   if (!kSplit) {
-    const uint64_t dims[2] = {(uint64_t)No, (uint64_t)Mo};
+    const uint64_t dims[2] = {(uint64_t)p.N_store, (uint64_t)Mo};
     const uint64_t strides[1] = {(uint64_t)ldy * 2};
     const uint32_t box[2] = {32u, 32u};
     rc = make_tensor_map(&tmY, Y, 2, 2, dims, strides, box, Swizzle::B64);
@@ -466,6 +506,42 @@ extern "C" int tvi_gemm_bf16_tn(const tvi_bf16* X, const tvi_bf16* W, const tvi_
   TVI_CHECK_ARG(M < ((int64_t)1 << 31) - 256, "tvi_gemm_bf16_tn: M too large for one call");
   return launch_gemm<false, false, false>("tvi_gemm_bf16_tn", X, W, bias, Y, nullptr, 1, M, N, K, ldx, ldw, ldy,
                                           (cudaStream_t)stream);
+}
+
+extern "C" int tvi_geglu_block(int inner) {
+  // width of the value / gate column blocks the fused GEGLU projection expects in its re-ordered weight
+  for (int h = 128; h >= 32; h -= 32)
+    if (inner > 0 && inner % h == 0) return h;
+  return 0;
+}
+
+extern "C" int tvi_gemm_bf16_tn_ex(const tvi_bf16* X, const tvi_bf16* W, const tvi_bf16* bias, const tvi_bf16* residual,
+                                   tvi_bf16* Y, int64_t M, int N, int K, int64_t ldx, int64_t ldw, int64_t ldr, int64_t ldy,
+                                   int epilogue, void* stream) {
+  using namespace tvi;
+  TVI_CHECK_ARG(M >= 0 && N >= 0 && K >= 0, "tvi_gemm_bf16_tn_ex: negative size");
+  if (M == 0 || N == 0) return TVI_OK;
+  TVI_CHECK_ARG(X && W && Y, "tvi_gemm_bf16_tn_ex: null pointer");
+  TVI_CHECK_ARG(K > 0 && K % 8 == 0 && N % 8 == 0, "tvi_gemm_bf16_tn_ex: N=%d and K=%d must be positive multiples of 8", N, K);
+  TVI_CHECK_ARG(epilogue == TVI_EPILOGUE_NONE || epilogue == TVI_EPILOGUE_GEGLU, "tvi_gemm_bf16_tn_ex: unknown epilogue %d", epilogue);
+  int block = 0;
+  int n_store = N;
+  if (epilogue == TVI_EPILOGUE_GEGLU) {
+    TVI_CHECK_ARG(N % 2 == 0, "tvi_gemm_bf16_tn_ex: GEGLU needs an even number of projection columns");
+    n_store = N / 2;
+    block = tvi_geglu_block(n_store);
+    TVI_CHECK_ARG(block > 0, "tvi_gemm_bf16_tn_ex: GEGLU inner width %d must be a multiple of 32", n_store);
+  }
+  TVI_CHECK_ARG(ldx % 8 == 0 && ldw % 8 == 0 && ldy % 8 == 0 && (residual == nullptr || ldr % 8 == 0),
+                "tvi_gemm_bf16_tn_ex: row strides must be multiples of 8 elements");
+  TVI_CHECK_ARG(ldx >= K && ldw >= K && ldy >= n_store && (residual == nullptr || ldr >= n_store),
+                "tvi_gemm_bf16_tn_ex: row stride smaller than the row");
+  TVI_CHECK_ARG(((uintptr_t)X | (uintptr_t)W | (uintptr_t)Y | (uintptr_t)residual) % 16 == 0,
+                "tvi_gemm_bf16_tn_ex: X, W, Y, residual must be 16-byte aligned");
+  TVI_CHECK_ARG(bias == nullptr || (uintptr_t)bias % 2 == 0, "tvi_gemm_bf16_tn_ex: bias must be 2-byte aligned");
+  TVI_CHECK_ARG(M < ((int64_t)1 << 31) - 256, "tvi_gemm_bf16_tn_ex: M too large for one call");
+  return launch_gemm<false, false, false>("tvi_gemm_bf16_tn_ex", X, W, bias, Y, nullptr, 1, M, N, K, ldx, ldw, ldy,
+                                          (cudaStream_t)stream, block, residual, ldr);
 }
 
 extern "C" int tvi_gemm_bf16_dgrad(const tvi_bf16* dY, const tvi_bf16* W, tvi_bf16* dX, int64_t M, int N, int K,

@@ -53,3 +53,32 @@ class Attention(nn.Module):
         # reference :522-528
         return self.processor(self, hidden_states, encoder_hidden_states=encoder_hidden_states,
                               attention_mask=attention_mask, **cross_attention_kwargs)
+
+
+class GEGLU(nn.Module):
+    """Parameter container of upstream diffusers' GEGLU (`proj = nn.Linear(dim_in, 2 * dim_out)`); the eager
+    forward below is only used where no libtvi forward is installed (CPU-side tests of the host logic)."""
+
+    def __init__(self, dim_in: int, dim_out: int):
+        super().__init__()
+        self.proj = nn.Linear(dim_in, dim_out * 2)
+
+    def forward(self, hidden_states, scale: float = 1.0):
+        hidden_states, gate = self.proj(hidden_states).chunk(2, dim=-1)
+        return hidden_states * torch.nn.functional.gelu(gate)
+
+
+class FeedForward(nn.Module):
+    """diffusers-free mirror of the reference `FeedForward` container (src/models/attention.py:481-535) for the
+    `geglu` activation SVD uses: same sub-module layout and state_dict keys (`net.0.proj.*`, `net.2.*`)."""
+
+    def __init__(self, dim: int, dim_out: Optional[int] = None, mult: int = 4, dropout: float = 0.0):
+        super().__init__()
+        inner_dim = int(dim * mult)
+        dim_out = dim_out if dim_out is not None else dim
+        self.net = nn.ModuleList([GEGLU(dim, inner_dim), nn.Dropout(dropout), nn.Linear(inner_dim, dim_out)])
+
+    def forward(self, hidden_states, scale: float = 1.0):
+        for module in self.net:  # reference :528-535
+            hidden_states = module(hidden_states)
+        return hidden_states

@@ -83,6 +83,56 @@ def _workspace(nbytes: int, device) -> torch.Tensor | None:
     return torch.empty(max(1, (nbytes + 3) // 4), dtype=torch.float32, device=device) if nbytes else None
 
 
+def gemm_bf16_tn_ex(x: torch.Tensor, w: torch.Tensor, bias: torch.Tensor | None = None, residual: torch.Tensor | None = None,
+                    geglu: bool = False, out: torch.Tensor | None = None) -> torch.Tensor:
+    """y = x @ w^T (+ bias) (+ residual); with `geglu` w / bias hold value and gate rows interleaved in blocks of
+    `geglu_block(inner)` and y[..., inner] = value * gelu(gate) (+ residual) — one tcgen05 GEMM, fused epilogue."""
+    _need_cuda(x, w, bias, residual)
+    x, ldx = _rows2d(x, "x")
+    w, ldw = _rows2d(w, "w")
+    K, N = x.shape[-1], w.shape[0]
+    if w.shape[1] != K:
+        raise _lib.TviError(_lib.TVI_ERR_INVALID, f"gemm: x has K={K}, w has K={w.shape[1]}")
+    n_out = N // 2 if geglu else N
+    M = x.numel() // K if K else 0
+    if out is None:
+        out = torch.empty(*x.shape[:-1], n_out, dtype=torch.bfloat16, device=x.device)
+    out, ldy = _rows2d(out, "out")
+    ldr = 0
+    if residual is not None:
+        residual, ldr = _rows2d(residual, "residual")
+        if residual.shape[-1] != n_out or residual.numel() != M * n_out:
+            raise _lib.TviError(_lib.TVI_ERR_INVALID, "gemm: residual must have the shape of the output")
+    if bias is not None and (bias.dtype != torch.bfloat16 or not bias.is_contiguous() or bias.numel() != N):
+        raise _lib.TviError(_lib.TVI_ERR_INVALID, "gemm: bias must be a contiguous bf16 vector of length N")
+    _hooked("gemm_bf16_tn_ex", 1, _lib.load().tvi_gemm_bf16_tn_ex, x.data_ptr(), w.data_ptr(),
+            bias.data_ptr() if bias is not None else None, residual.data_ptr() if residual is not None else None,
+            out.data_ptr(), M, N, K, ldx, ldw, ldr, ldy, _lib.EPILOGUE_GEGLU if geglu else _lib.EPILOGUE_NONE, _stream())
+    return out
+
+
+def geglu_block(inner: int) -> int:
+    return int(_lib.load().tvi_geglu_block(int(inner)))
+
+
+def layernorm_bf16(x: torch.Tensor, gamma: torch.Tensor | None, beta: torch.Tensor | None, eps: float,
+                   out: torch.Tensor | None = None) -> torch.Tensor:
+    """LayerNorm over the last dimension (fp32 statistics), bf16 in / out."""
+    _need_cuda(x, gamma, beta)
+    x, ldx = _rows2d(x, "x")
+    C = x.shape[-1]
+    M = x.numel() // C if C else 0
+    for t in (gamma, beta):
+        if t is not None and (t.dtype != torch.bfloat16 or not t.is_contiguous() or t.numel() != C):
+            raise _lib.TviError(_lib.TVI_ERR_INVALID, "layernorm: gamma / beta must be contiguous bf16 vectors of length C")
+    if out is None:
+        out = torch.empty(x.shape, dtype=torch.bfloat16, device=x.device)
+    out, ldy = _rows2d(out, "out")
+    _hooked("layernorm_bf16", 1, _lib.load().tvi_layernorm_bf16, x.data_ptr(), gamma.data_ptr() if gamma is not None else None,
+            beta.data_ptr() if beta is not None else None, out.data_ptr(), M, C, ldx, ldy, float(eps), _stream())
+    return out
+
+
 def gemm_bf16_dgrad(dy: torch.Tensor, w: torch.Tensor, out: torch.Tensor | None = None) -> torch.Tensor:
     """dx[..., K] = dy[..., N] @ w[N, K] — input gradient of nn.Linear; w is consumed in place."""
     _need_cuda(dy, w)
