@@ -108,6 +108,11 @@ int tvi_gemm_bf16_tn_ex(const tvi_bf16* X, const tvi_bf16* W, const tvi_bf16* bi
 int tvi_layernorm_bf16(const tvi_bf16* x, const tvi_bf16* gamma, const tvi_bf16* beta, tvi_bf16* y, int64_t M, int C,
                        int64_t ldx, int64_t ldy, float eps, void* stream);
 
+/* out[r, :] = v[r / rows_per_group, :] + residual[r, :] — the one-key cross-attention output (a row broadcast) with
+ * the block's `attn_output + hidden_states` (src/models/attention.py:316-317, :459-460) fused. */
+int tvi_bcast_rows_add_bf16(const tvi_bf16* v, const tvi_bf16* residual, tvi_bf16* out, int64_t nrows, int64_t rows_per_group,
+                            int C, int64_t ldv, int64_t ldr, int64_t ldo, void* stream);
+
 /* Backward of the projections (training config 5: src/train_decouples.py back-propagates through the
  * same nn.Linear call sites; autograd's F.linear backward = two cuBLAS GEMMs + a bias column sum).
  *   dgrad : dX[M,K] = dY[M,N] . W[N,K]          (W consumed in place, MN-major tcgen05 operand)

@@ -94,3 +94,63 @@ def test_gemm_residual_epilogue(cuda):
     torch.cuda.synchronize()
     ref = x.float().cpu() @ w.float().cpu().t() + b.float().cpu() + r.float().cpu()
     assert float((y.float().cpu() - ref).abs().max()) <= 2 ** -7 * float(ref.abs().max()) + 1e-2
+
+
+# ------------------------------------------------------------------------------------------------
+# block-level forwards vs the oracle's restatement of the reference blocks
+# ------------------------------------------------------------------------------------------------
+from oracle import blocks_ref  # noqa: E402
+from timelapse_video_interpolation_b200 import blocks  # noqa: E402
+from timelapse_video_interpolation_b200.modules import BasicTransformerBlock, TemporalBasicTransformerBlock  # noqa: E402
+
+
+def _init(module, seed, device):
+    g = torch.Generator().manual_seed(seed)
+    with torch.no_grad():
+        for name, p in module.named_parameters():
+            if "norm" in name:
+                p.copy_((1.0 if name.endswith("weight") else 0.0) + 0.1 * torch.randn(p.shape, generator=g))
+            else:
+                p.copy_(torch.randn(p.shape, generator=g) * (p.shape[-1] ** -0.5 if p.dim() > 1 else 0.05))
+    return module.to(device=device, dtype=torch.bfloat16).eval()
+
+
+@pytest.mark.parametrize("BF,S,C,heads,L", [(4, 576, 320, 5, 2), (2, 1152, 320, 5, 1), (4, 144, 640, 10, 2)])
+def test_basic_transformer_block_matches_oracle(cuda, BF, S, C, heads, L):
+    blk = _init(BasicTransformerBlock(C, heads, 1024), 3, cuda)
+    assert blocks.install_blocks(blk) == 1
+    g = torch.Generator().manual_seed(S)
+    x = torch.randn(BF, S, C, generator=g).to(torch.bfloat16).to(cuda)
+    e = torch.randn(BF, L, 1024, generator=g).to(torch.bfloat16).to(cuda)
+    with torch.no_grad():
+        y = blk(x, encoder_hidden_states=e)
+    torch.cuda.synchronize()
+    ref = blocks_ref.basic_transformer_block_ref(blk, x, e)
+    err = float((y.float().cpu() - ref).abs().max())
+    print(f"basic block S={S} C={C}: max abs err {err:.3e}, max |ref| {float(ref.abs().max()):.3f}")
+    assert err <= TOL * max(1.0, float(ref.abs().max()))
+    assert blocks.uninstall_blocks(blk) == 1
+
+
+@pytest.mark.parametrize("B,T,S,C,heads,L", [(2, 14, 144, 320, 5, 1), (1, 25, 64, 640, 10, 2)])
+def test_temporal_basic_transformer_block_matches_oracle(cuda, B, T, S, C, heads, L):
+    blk = _init(TemporalBasicTransformerBlock(C, C, heads, 1024), 4, cuda)
+    assert blocks.install_blocks(blk) == 1
+    g = torch.Generator().manual_seed(T)
+    x = torch.randn(B * T, S, C, generator=g).to(torch.bfloat16).to(cuda)
+    e = torch.randn(B * S, L, 1024, generator=g).to(torch.bfloat16).to(cuda)
+    with torch.no_grad():
+        y = blk(x, num_frames=T, encoder_hidden_states=e)
+    torch.cuda.synchronize()
+    ref = blocks_ref.temporal_basic_transformer_block_ref(blk, x, T, e)
+    err = float((y.float().cpu() - ref).abs().max())
+    print(f"temporal block T={T} C={C}: max abs err {err:.3e}, max |ref| {float(ref.abs().max()):.3f}")
+    assert y.shape == x.shape and err <= TOL * max(1.0, float(ref.abs().max()))
+
+
+def test_block_forward_refuses_gradients(cuda):
+    blk = _init(BasicTransformerBlock(320, 5, 1024), 5, cuda)
+    blocks.install_blocks(blk)
+    x = torch.randn(2, 64, 320, device=cuda).to(torch.bfloat16).requires_grad_(True)
+    with pytest.raises(NotImplementedError):
+        blk(x, encoder_hidden_states=torch.randn(2, 1, 1024, device=cuda).to(torch.bfloat16))

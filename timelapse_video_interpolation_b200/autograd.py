@@ -25,7 +25,14 @@ def _self_core(q, k, v, Bp, S, heads, scale, lse=None):
     return ops.attn_spatial(q, k, v, Bp, heads, S, S, scale, lse=lse)
 
 
-def self_attention(x: torch.Tensor, w_qkv: torch.Tensor, w_o: torch.Tensor, b_o, heads: int, scale: float) -> torch.Tensor:
+def _out_proj(o, w_o, b_o, residual):
+    if residual is None:
+        return ops.gemm_bf16_tn(o, w_o, b_o)
+    return ops.gemm_bf16_tn_ex(o, w_o, b_o, residual=residual.reshape(-1, residual.shape[-1]))
+
+
+def self_attention(x: torch.Tensor, w_qkv: torch.Tensor, w_o: torch.Tensor, b_o, heads: int, scale: float,
+                   residual=None) -> torch.Tensor:
     """x [B', S, C] bf16 -> [B', S, C].  Reference: AttnProcessor2_0.__call__ with
     encoder_hidden_states=None (src/models/attention_processor.py:1223-1261)."""
     Bp, S, C = x.shape
@@ -33,12 +40,12 @@ def self_attention(x: torch.Tensor, w_qkv: torch.Tensor, w_o: torch.Tensor, b_o,
     qkv = ops.gemm_bf16_tn(x.view(Bp * S, C), w_qkv)  # [B'*S, 3*inner], heads stay packed along the row
     q, k, v = qkv[:, :inner], qkv[:, inner:2 * inner], qkv[:, 2 * inner:]
     o = _self_core(q, k, v, Bp, S, heads, scale)
-    y = ops.gemm_bf16_tn(o, w_o, b_o)
+    y = _out_proj(o, w_o, b_o, residual)
     return y.view(Bp, S, -1)
 
 
 def cross_attention(x: torch.Tensor, e: torch.Tensor, w_q: torch.Tensor, w_kv: torch.Tensor, w_o: torch.Tensor, b_o,
-                    heads: int, scale: float, bias=None, stats=None) -> torch.Tensor:
+                    heads: int, scale: float, bias=None, stats=None, residual=None) -> torch.Tensor:
     """x [B', S, C], e [B', L, Ckv] -> [B', S, C].  Reference: same processor with
     encoder_hidden_states given (keys/values from the context, :1225-1231)."""
     Bp, S, C = x.shape
@@ -51,12 +58,14 @@ def cross_attention(x: torch.Tensor, e: torch.Tensor, w_q: torch.Tensor, w_kv: t
         # softmax over one key == 1: every query row of a group gets to_out(v_group); project the
         # B' value rows once and broadcast them (Q is never needed)
         yv = ops.gemm_bf16_tn(v, w_o, b_o)  # [B', C]
+        if residual is not None:
+            return ops.bcast_rows_add(yv, residual.reshape(Bp * S, -1), S).view(Bp, S, -1)
         y = ops.attn_fewkeys(None, yv, yv, Bp * S, S, heads, 1, 1.0)  # L == 1: pure row broadcast
         return y.view(Bp, S, -1)
     q = ops.gemm_bf16_tn(x.view(Bp * S, C), w_q)
     o = ops.attn_fewkeys(q, k, v, Bp * S, S, heads, L, scale, Tq=S if (bias is not None or stats is not None) else 1,
                          bias=bias, stats=stats)
-    y = ops.gemm_bf16_tn(o, w_o, b_o)
+    y = _out_proj(o, w_o, b_o, residual)
     return y.view(Bp, S, -1)
 
 
@@ -207,17 +216,19 @@ class _AttentionFn(torch.autograd.Function):
         return (dx, de, cast(dwq, dt_wq), cast(dwk, dt_wk), cast(dwv, dt_wv), cast(dwo, dt_wo), cast(dbo, dt_bo), None)
 
 
-def attention_forward(proc, attn, x, e, heads: int, scale: float, wo, bo, bias, stats) -> torch.Tensor:
+def attention_forward(proc, attn, x, e, heads: int, scale: float, wo, bo, bias, stats, residual=None) -> torch.Tensor:
     wq, wk, wv = attn.to_q.weight, attn.to_k.weight, attn.to_v.weight
     needs_grad = torch.is_grad_enabled() and any(
         t is not None and t.requires_grad for t in (x, e, wq, wk, wv, wo, bo))
     w_o = _to_bf16(wo).contiguous()
     b_o = _to_bf16(bo).contiguous() if bo is not None else None
-    if not needs_grad:
+    if not needs_grad and not (residual is not None and torch.is_grad_enabled() and residual.requires_grad):
         if e is None:
-            return self_attention(x, proc._fused(attn, ("to_q", "to_k", "to_v")), w_o, b_o, heads, scale)
+            return self_attention(x, proc._fused(attn, ("to_q", "to_k", "to_v")), w_o, b_o, heads, scale, residual)
         return cross_attention(x, e, proc._fused(attn, ("to_q",)), proc._fused(attn, ("to_k", "to_v")), w_o, b_o, heads,
-                               scale, bias, stats)
+                               scale, bias, stats, residual)
+    if residual is not None:  # training: the fused residual epilogue has no backward; add it on the tape
+        return attention_forward(proc, attn, x, e, heads, scale, wo, bo, bias, stats) + residual
     cfg = {"heads": heads, "scale": scale, "w_o": w_o, "b_o": b_o}
     if e is None:
         cfg["w_qkv"] = proc._fused(attn, ("to_q", "to_k", "to_v"))

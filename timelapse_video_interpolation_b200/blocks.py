@@ -1,0 +1,139 @@
+"""Block-level forwards on libtvi ("needs a block-level swap").
+
+Drop-in replacements for
+  BasicTransformerBlock.forward          reference src/models/attention.py:234-347 (the `use_layer_norm` branch SVD uses)
+  TemporalBasicTransformerBlock.forward  reference src/models/attention.py:423-478
+Every arithmetic step is a libtvi kernel: LayerNorm -> attention (processor path, residual add fused into the
+out-projection epilogue) -> LayerNorm -> cross-attention (+ residual) -> LayerNorm -> FeedForward (GEGLU fused into the
+first GEMM, bias + residual into the second).  The `[B*T, S, C] <-> [B*S, T, C]` re-layout of the temporal block
+(:436-438, :474-476) is still a torch permute copy (row N2 folds it into the GEMM descriptors).
+
+`install_blocks(model)` re-binds `forward` on every module with the block's attribute layout (duck-typed) and installs
+the attention processor on its Attention modules.  Inference only: the FeedForward / LayerNorm backward is not built,
+so a call that needs gradients raises instead of silently detaching.
+"""
+from __future__ import annotations
+
+import types
+from typing import Optional
+
+import torch
+
+from . import _lib
+from .feedforward import feed_forward, layer_norm
+from .processor import TviAttnProcessor
+
+__all__ = ["basic_transformer_block_forward", "temporal_basic_transformer_block_forward", "install_blocks", "uninstall_blocks"]
+
+
+def _no_grad_only(block, x):
+    if torch.is_grad_enabled() and (x.requires_grad or any(p.requires_grad for p in block.parameters())):
+        raise NotImplementedError("libtvi block forwards are inference-only (FeedForward / LayerNorm backward is not built): "
+                                  "call under torch.no_grad(), or install only the attention processor for training")
+
+
+def _attn(attn, x, e, residual):
+    proc = attn.processor
+    if not isinstance(proc, TviAttnProcessor):
+        raise _lib.TviError(_lib.TVI_ERR_INVALID, "block forward: the Attention module does not carry a TviAttnProcessor "
+                                                  "(call install_blocks / install first)")
+    return proc(attn, x, encoder_hidden_states=e, residual=residual)
+
+
+def _check_basic(block):
+    for flag in ("use_ada_layer_norm", "use_ada_layer_norm_zero", "use_ada_layer_norm_single"):
+        if getattr(block, flag, False):
+            raise _lib.TviError(_lib.TVI_ERR_UNSUPPORTED, f"block forward: {flag} is set; SVD blocks use plain LayerNorm")
+    if getattr(block, "pos_embed", None) is not None or getattr(block, "_chunk_size", None) is not None:
+        raise _lib.TviError(_lib.TVI_ERR_UNSUPPORTED, "block forward: pos_embed / chunked feed-forward are not supported")
+
+
+def basic_transformer_block_forward(block, hidden_states: torch.Tensor, attention_mask=None,
+                                    encoder_hidden_states: Optional[torch.Tensor] = None, encoder_attention_mask=None,
+                                    timestep=None, cross_attention_kwargs=None, class_labels=None) -> torch.Tensor:
+    """Same signature as BasicTransformerBlock.forward (:234-243)."""
+    _check_basic(block)
+    if attention_mask is not None or encoder_attention_mask is not None:
+        raise _lib.TviError(_lib.TVI_ERR_UNSUPPORTED, "block forward: attention masks are not supported (SVD never passes one)")
+    if cross_attention_kwargs and any(k != "scale" for k in cross_attention_kwargs):
+        raise _lib.TviError(_lib.TVI_ERR_UNSUPPORTED, "block forward: unsupported cross_attention_kwargs")
+    _no_grad_only(block, hidden_states)
+    x = hidden_states.contiguous()
+    # 0. self-attention (:270-287): norm1 -> attn1 -> + hidden_states
+    n = layer_norm(block.norm1, x)
+    x = _attn(block.attn1, n, encoder_hidden_states if getattr(block, "only_cross_attention", False) else None, x)
+    # 3. cross-attention (:296-317)
+    if getattr(block, "attn2", None) is not None:
+        n = layer_norm(block.norm2, x)
+        x = _attn(block.attn2, n, encoder_hidden_states, x)
+    # 4. feed-forward (:321-343): norm3 -> ff -> + hidden_states
+    n = layer_norm(block.norm3, x)
+    return feed_forward(block.ff, n, residual=x)
+
+
+def temporal_basic_transformer_block_forward(block, hidden_states: torch.Tensor, num_frames: int,
+                                             encoder_hidden_states: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """Same signature as TemporalBasicTransformerBlock.forward (:423-428)."""
+    if getattr(block, "_chunk_size", None) is not None:
+        raise _lib.TviError(_lib.TVI_ERR_UNSUPPORTED, "block forward: chunked feed-forward is not supported")
+    _no_grad_only(block, hidden_states)
+    BF, S, C = hidden_states.shape
+    B = BF // num_frames
+    # [B*T, S, C] -> [B*S, T, C] (:435-438)
+    x = hidden_states.reshape(B, num_frames, S, C).permute(0, 2, 1, 3).reshape(B * S, num_frames, C)
+    n = layer_norm(block.norm_in, x)
+    x = feed_forward(block.ff_in, n, residual=x if block.is_res else None)   # :441-449
+    n = layer_norm(block.norm1, x)
+    x = _attn(block.attn1, n, None, x)                                       # :451-453
+    if getattr(block, "attn2", None) is not None:
+        n = layer_norm(block.norm2, x)
+        x = _attn(block.attn2, n, encoder_hidden_states, x)                  # :456-460
+    n = layer_norm(block.norm3, x)
+    x = feed_forward(block.ff, n, residual=x if block.is_res else None)      # :462-472
+    # [B*S, T, C] -> [B*T, S, C] (:474-476)
+    return x.reshape(B, S, num_frames, x.shape[-1]).permute(0, 2, 1, 3).reshape(B * num_frames, S, x.shape[-1])
+
+
+def _is_basic(m) -> bool:
+    return all(hasattr(m, a) for a in ("norm1", "attn1", "norm3", "ff")) and not hasattr(m, "norm_in")
+
+
+def _is_temporal(m) -> bool:
+    return all(hasattr(m, a) for a in ("norm_in", "ff_in", "norm1", "attn1", "norm3", "ff", "is_res"))
+
+
+def install_blocks(model: torch.nn.Module, processor: Optional[TviAttnProcessor] = None) -> int:
+    """Re-binds the forward of every (Temporal)BasicTransformerBlock-shaped module; returns how many."""
+    proc = processor or TviAttnProcessor()
+    n = 0
+    for _, m in model.named_modules():
+        if _is_temporal(m):
+            fwd = temporal_basic_transformer_block_forward
+        elif _is_basic(m):
+            fwd = basic_transformer_block_forward
+        else:
+            continue
+        for a in ("attn1", "attn2"):
+            attn = getattr(m, a, None)
+            if attn is not None and not isinstance(getattr(attn, "processor", None), TviAttnProcessor):
+                if not hasattr(attn, "_tvi_saved_processor"):
+                    attn._tvi_saved_processor = attn.processor
+                attn.set_processor(proc) if hasattr(attn, "set_processor") else setattr(attn, "processor", proc)
+        if not hasattr(m, "_tvi_saved_block_forward"):
+            m._tvi_saved_block_forward = m.__dict__.get("forward")
+        m.forward = types.MethodType(fwd, m)
+        n += 1
+    return n
+
+
+def uninstall_blocks(model: torch.nn.Module) -> int:
+    n = 0
+    for _, m in model.named_modules():
+        if hasattr(m, "_tvi_saved_block_forward"):
+            if m._tvi_saved_block_forward is None:
+                m.__dict__.pop("forward", None)
+            else:
+                m.forward = m._tvi_saved_block_forward
+            del m._tvi_saved_block_forward
+            n += 1
+    return n

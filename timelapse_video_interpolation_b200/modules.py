@@ -82,3 +82,45 @@ class FeedForward(nn.Module):
         for module in self.net:  # reference :528-535
             hidden_states = module(hidden_states)
         return hidden_states
+
+
+class BasicTransformerBlock(nn.Module):
+    """Parameter container with the attribute layout of the reference's spatial block for SVD
+    (src/models/attention.py:90-232 with norm_type="layer_norm", GEGLU feed-forward, attention_bias=False):
+    norm1, attn1, norm2, attn2, norm3, ff.  The eager forward is the reference's order of operations."""
+
+    def __init__(self, dim: int, heads: int, cross_attention_dim: Optional[int] = None, processor=None):
+        super().__init__()
+        self.use_layer_norm = True
+        self.use_ada_layer_norm = self.use_ada_layer_norm_zero = self.use_ada_layer_norm_single = False
+        self.only_cross_attention = False
+        self.pos_embed = None
+        self._chunk_size = None
+        self.norm1 = nn.LayerNorm(dim)
+        self.attn1 = Attention(dim, None, heads=heads, processor=processor)
+        self.norm2 = nn.LayerNorm(dim)
+        self.attn2 = Attention(dim, cross_attention_dim, heads=heads, processor=processor)
+        self.norm3 = nn.LayerNorm(dim)
+        self.ff = FeedForward(dim)
+
+    def forward(self, hidden_states, attention_mask=None, encoder_hidden_states=None, **kw):
+        hidden_states = self.attn1(self.norm1(hidden_states)) + hidden_states
+        hidden_states = self.attn2(self.norm2(hidden_states), encoder_hidden_states=encoder_hidden_states) + hidden_states
+        return self.ff(self.norm3(hidden_states)) + hidden_states
+
+
+class TemporalBasicTransformerBlock(nn.Module):
+    """Attribute layout of the reference's temporal block (src/models/attention.py:350-478)."""
+
+    def __init__(self, dim: int, time_mix_inner_dim: int, heads: int, cross_attention_dim: Optional[int] = None, processor=None):
+        super().__init__()
+        self.is_res = dim == time_mix_inner_dim
+        self._chunk_size = None
+        self.norm_in = nn.LayerNorm(dim)
+        self.ff_in = FeedForward(dim, dim_out=time_mix_inner_dim)
+        self.norm1 = nn.LayerNorm(time_mix_inner_dim)
+        self.attn1 = Attention(time_mix_inner_dim, None, heads=heads, processor=processor)
+        self.norm2 = nn.LayerNorm(time_mix_inner_dim)
+        self.attn2 = Attention(time_mix_inner_dim, cross_attention_dim, heads=heads, processor=processor)
+        self.norm3 = nn.LayerNorm(time_mix_inner_dim)
+        self.ff = FeedForward(time_mix_inner_dim)

@@ -133,6 +133,21 @@ def layernorm_bf16(x: torch.Tensor, gamma: torch.Tensor | None, beta: torch.Tens
     return out
 
 
+def bcast_rows_add(v: torch.Tensor, residual: torch.Tensor, rows_per_group: int, out: torch.Tensor | None = None) -> torch.Tensor:
+    """out[r] = v[r // rows_per_group] + residual[r] (one-key cross-attention output + the block's residual)."""
+    _need_cuda(v, residual)
+    v, ldv = _rows2d(v, "v")
+    residual, ldr = _rows2d(residual, "residual")
+    C = v.shape[-1]
+    nrows = residual.numel() // C if C else 0
+    if out is None:
+        out = torch.empty(nrows, C, dtype=torch.bfloat16, device=v.device)
+    out, ldo = _rows2d(out, "out")
+    _hooked("bcast_rows_add", 1, _lib.load().tvi_bcast_rows_add_bf16, v.data_ptr(), residual.data_ptr(), out.data_ptr(), nrows,
+            int(rows_per_group), C, ldv, ldr, ldo, _stream())
+    return out
+
+
 def gemm_bf16_dgrad(dy: torch.Tensor, w: torch.Tensor, out: torch.Tensor | None = None) -> torch.Tensor:
     """dx[..., K] = dy[..., N] @ w[N, K] — input gradient of nn.Linear; w is consumed in place."""
     _need_cuda(dy, w)

@@ -111,7 +111,9 @@ class TviAttnProcessor:
     # ------------------------------------------------------------------ the call
     def __call__(self, attn, hidden_states: torch.Tensor, encoder_hidden_states: Optional[torch.Tensor] = None,
                  attention_mask: Optional[torch.Tensor] = None, temb: Optional[torch.Tensor] = None,
-                 scale: float = 1.0, *args, **kwargs) -> torch.Tensor:
+                 scale: float = 1.0, *args, residual: Optional[torch.Tensor] = None, **kwargs) -> torch.Tensor:
+        """`residual` (libtvi extension used by the block-level forwards of blocks.py): a tensor of the output's
+        shape added in the out-projection epilogue, i.e. the caller's `attn_output + hidden_states`."""
         self._check(attn, hidden_states, attention_mask)
         in_dtype = hidden_states.dtype
         if in_dtype != torch.bfloat16:
@@ -142,7 +144,11 @@ class TviAttnProcessor:
         else:
             e = None
 
-        y = attention_forward(self, attn, x, e, heads, float(attn.scale), wo, bo, bias, stats)
+        if residual is not None:
+            if residual.shape != hidden_states.shape:
+                raise _lib.TviError(_lib.TVI_ERR_INVALID, "residual must have the shape of hidden_states")
+            residual = residual.to(torch.bfloat16).contiguous()
+        y = attention_forward(self, attn, x, e, heads, float(attn.scale), wo, bo, bias, stats, residual)
 
         if stats is not None:
             self.stats_sink(stats, attn)
