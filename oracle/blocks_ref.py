@@ -2,6 +2,8 @@
 feed-forward restatements:
   BasicTransformerBlock.forward          src/models/attention.py:234-347 (use_layer_norm branch; no gligen / ada norms)
   TemporalBasicTransformerBlock.forward  src/models/attention.py:423-478
+Pinned by tests/golden/blocks.npz (outputs of the reference's own block classes, GEGLU leaf restated) in
+tests/test_oracle_golden.py.
 """
 from __future__ import annotations
 

@@ -3,9 +3,10 @@
   FeedForward.forward                  src/models/attention.py:526-535 (iterates net: GEGLU, Dropout(p=0), Linear)
   GEGLU.forward                        upstream diffusers 0.24 `models/activations.py` (NOT in the reference tree, the
                                        `thirdparty/diffusers` submodule is empty): proj -> chunk(2, dim=-1) ->
-                                       hidden_states * F.gelu(gate)  (erf form).  Parity for this class is UNPINNED by
-                                       the reference; tests/golden/feed_forward.npz pins the container logic by driving
-                                       the reference's own FeedForward class over a GEGLU with exactly this forward.
+                                       hidden_states * F.gelu(gate)  (erf form).  Parity for this LEAF is UNPINNED by
+                                       the reference; tests/golden/blocks.npz pins everything around it by driving
+                                       the reference's own FeedForward / block classes over a GEGLU with exactly this
+                                       forward (tests/golden/make_golden.py:make_blocks).
   residual add                         src/models/attention.py:343, :449, :472 (`ff_output + hidden_states`)
   nn.LayerNorm                         :270, :300, :321, :441, :446, :462
 """

@@ -12,6 +12,10 @@ container (needs /root/reference); the GPU box uses the .npz files.
 * temporal_patched.npz — src/train_decouples.py:377-495 (the monkey-patched temporal forward) cannot be
   imported (it is a closure inside `main`), so its source lines are extracted with `ast`/text slicing
   from the reference file at generation time and exec'd against the reference's `Attention`.
+* blocks.npz           — src/models/attention.py: the reference's own `FeedForward`, `BasicTransformerBlock` and
+  `TemporalBasicTransformerBlock` classes (fp32, CPU).  Their leaf `GEGLU` lives in the un-vendored diffusers 0.24
+  (`models/activations.py`); the shim below restates its published forward (`proj` -> chunk(2) -> hidden * F.gelu(gate))
+  — every other line that runs (the block forwards, the FeedForward container, Attention + processor) is the reference's.
 """
 from __future__ import annotations
 
@@ -173,8 +177,86 @@ def make_temporal_patched(ap):
     print("temporal_patched.npz", sorted({k.split(".")[0] for k in out}))
 
 
+def _shim_block_leaves(ap):
+    """The leaf classes src/models/attention.py:6-12 imports from diffusers; only GEGLU is ever instantiated here."""
+    act = types.ModuleType("diffusers.models.activations")
+
+    class GEGLU(torch.nn.Module):  # diffusers 0.24 models/activations.py (restated; USE_PEFT_BACKEND -> nn.Linear)
+        def __init__(self, dim_in, dim_out):
+            super().__init__()
+            self.proj = torch.nn.Linear(dim_in, dim_out * 2)
+
+        def forward(self, hidden_states, scale: float = 1.0):
+            hidden_states, gate = self.proj(hidden_states).chunk(2, dim=-1)
+            return hidden_states * torch.nn.functional.gelu(gate)
+
+    act.GEGLU = GEGLU
+    act.GELU = act.ApproximateGELU = type("Unused", (torch.nn.Module,), {})
+    emb = types.ModuleType("diffusers.models.embeddings")
+    emb.SinusoidalPositionalEmbedding = type("SinusoidalPositionalEmbedding", (torch.nn.Module,), {})
+    nrm = types.ModuleType("diffusers.models.normalization")
+    nrm.AdaLayerNorm = nrm.AdaLayerNormZero = type("Unused", (torch.nn.Module,), {})
+    pkg = types.ModuleType("models")
+    pkg.attention_processor = ap
+    for name, mod in {"diffusers.models.activations": act, "diffusers.models.embeddings": emb,
+                      "diffusers.models.normalization": nrm, "models": pkg, "models.attention_processor": ap}.items():
+        sys.modules[name] = mod
+
+
+def make_blocks(ap):
+    _shim_block_leaves(ap)
+    ra = _load(REF / "src/models/attention.py", "ref_attention")
+    out = {}
+
+    def randomise(m, g):
+        for name, p in m.named_parameters():
+            if "norm" in name:  # affine LayerNorm parameters away from (1, 0) so that they are exercised
+                p.data = (1.0 + 0.2 * torch.randn(p.shape, generator=g)) if name.endswith("weight") else 0.1 * torch.randn(p.shape, generator=g)
+            else:
+                p.data = torch.randn(p.shape, generator=g) * (p.shape[-1] ** -0.5 if p.dim() > 1 else 0.1)
+
+    def save(tag, m, **tensors):
+        for k, v in m.state_dict().items():
+            out[f"{tag}.sd.{k}"] = v.numpy()
+        for k, v in tensors.items():
+            out[f"{tag}.{k}"] = v.numpy()
+
+    g = torch.Generator().manual_seed(101)
+    ff = ra.FeedForward(64, dim_out=32, activation_fn="geglu")
+    randomise(ff, g)
+    x = torch.randn(3, 10, 64, generator=g)
+    with torch.no_grad():
+        save("ff", ff, x=x, y=ff(x))
+
+    C, heads, cross = 64, 1, 48
+    sb = ra.BasicTransformerBlock(C, heads, 64, cross_attention_dim=cross)
+    sb.attn1.set_processor(ap.AttnProcessor2_0())
+    sb.attn2.set_processor(ap.AttnProcessor2_0())
+    randomise(sb, g)
+    x = torch.randn(4, 48, C, generator=g)          # [B*F, S, C]
+    e = torch.randn(4, 2, cross, generator=g)
+    with torch.no_grad():
+        save("spatial", sb, x=x, e=e, y=sb(x, encoder_hidden_states=e))
+
+    # time_mix_inner_dim != dim cannot run in the reference (:474 reshapes the output with the INPUT channel count)
+    for tag, inner in (("temporal", C),):
+        tb = ra.TemporalBasicTransformerBlock(C, inner, inner // 64, 64, cross_attention_dim=cross)
+        tb.attn1.set_processor(ap.AttnProcessor2_0())
+        tb.attn2.set_processor(ap.AttnProcessor2_0())
+        randomise(tb, g)
+        T, S, B = 7, 12, 2
+        x = torch.randn(B * T, S, C, generator=g)
+        e = torch.randn(B * S, 1, cross, generator=g)
+        with torch.no_grad():
+            save(tag, tb, x=x, e=e, y=tb(x, num_frames=T, encoder_hidden_states=e))
+        out[f"{tag}.num_frames"] = np.int64(T)
+    np.savez_compressed(OUT / "blocks.npz", **out)
+    print("blocks.npz", sorted({k.split(".")[0] for k in out}), {k: tuple(v.shape) for k, v in out.items() if k.endswith(".y")})
+
+
 if __name__ == "__main__":
     torch.set_num_threads(4)
     make_flow()
     ap = make_attention()
     make_temporal_patched(ap)
+    make_blocks(ap)

@@ -226,14 +226,58 @@ def cfg_kernels(steps):
     emit({"config": "kernels_L0_forward", "per_entry_point": kt.summary(steps)})
 
 
+def cfg_block(steps):
+    """N1: one full L0 spatial + temporal transformer block pair (LayerNorms, attention, FeedForward, residuals) at the
+    bench shape (1 clip, CFG 2, T = 14, 576x1024), through blocks.install_blocks."""
+    from timelapse_video_interpolation_b200 import blocks
+    from timelapse_video_interpolation_b200.modules import BasicTransformerBlock, TemporalBasicTransformerBlock
+    C, heads, h, w = bench.LEVELS["L0"]
+    S, T, B = h * w, 14, 2
+    g = torch.Generator().manual_seed(3)
+
+    def init(m):
+        with torch.no_grad():
+            for name, p in m.named_parameters():
+                if "norm" in name:
+                    p.fill_(1.0 if name.endswith("weight") else 0.0)
+                else:
+                    p.copy_((torch.rand(p.shape, generator=g) * 2 - 1) * (p.shape[-1] ** -0.5 if p.dim() > 1 else C ** -0.5))
+        return m.to(DEV, torch.bfloat16).eval()
+
+    sb, tb = init(BasicTransformerBlock(C, heads, 1024)), init(TemporalBasicTransformerBlock(C, C, heads, 1024))
+    blocks.install_blocks(sb)
+    blocks.install_blocks(tb)
+    x = torch.randn(B * T, S, C, generator=g).to(torch.bfloat16).to(DEV)
+    ctx_s = torch.randn(B * T, 2, 1024, generator=g).to(torch.bfloat16).to(DEV)
+    ctx_t = torch.randn(B * S, 1, 1024, generator=g).to(torch.bfloat16).to(DEV)
+
+    def step():
+        y = sb(x, encoder_hidden_states=ctx_s)
+        return tb(y, num_frames=T, encoder_hidden_states=ctx_t)
+
+    with torch.no_grad():
+        ms = timed(step, steps)
+        kt = KernelTimes()
+        ops.EVENT_HOOK = kt.hook
+        for _ in range(3):
+            step()
+        ops.EVENT_HOOK = None
+    N = B * T * S
+    ff_flops = 3 * (2.0 * N * C * 8 * C + 2.0 * N * 4 * C * C)  # ff (spatial), ff_in + ff (temporal)
+    fl = bench.algorithmic_flops("L0", 1)["total"] + ff_flops
+    emit({"config": "block_L0_spatial_plus_temporal", "clips": 1, "cfg": 2, "T": T, "ms": ms, "clip_frames_per_s": T / (ms * 1e-3),
+          "tflop": fl / 1e12, "tflops": fl / 1e12 / (ms * 1e-3), "ff_tflop": ff_flops / 1e12, "kernels": kt.summary(3),
+          "note": "includes the two torch permute copies of the temporal block re-layout (row N2)"})
+
+
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument("--only", default="slerp,flow,train,loop25,kernels")
+    ap.add_argument("--only", default="slerp,flow,train,loop25,kernels,block")
     ap.add_argument("--steps", type=int, default=10)
     args = ap.parse_args()
     torch.cuda.set_device(0)
     emit({"config": "env", "device": torch.cuda.get_device_name(0), "libtvi": tvi.version(), "peaks": PK})
-    table = {"slerp": cfg_slerp, "flow": cfg_flow, "train": cfg_train, "loop25": cfg_loop25, "kernels": cfg_kernels}
+    table = {"slerp": cfg_slerp, "flow": cfg_flow, "train": cfg_train, "loop25": cfg_loop25, "kernels": cfg_kernels, "block": cfg_block}
     for name in args.only.split(","):
         table[name.strip()](args.steps)
 
