@@ -108,10 +108,13 @@ int tvi_gemm_bf16_tn_ex(const tvi_bf16* X, const tvi_bf16* W, const tvi_bf16* bi
 int tvi_layernorm_bf16(const tvi_bf16* x, const tvi_bf16* gamma, const tvi_bf16* beta, tvi_bf16* y, int64_t M, int C,
                        int64_t ldx, int64_t ldy, float eps, void* stream);
 
-/* out[r, :] = v[r / rows_per_group, :] + residual[r, :] — the one-key cross-attention output (a row broadcast) with
- * the block's `attn_output + hidden_states` (src/models/attention.py:316-317, :459-460) fused. */
+/* out[r, :] = v[group(r), :] (+ residual[r, :], nullable) — the one-key cross-attention output (a row broadcast) with
+ * the block's `attn_output + hidden_states` (src/models/attention.py:316-317, :459-460) fused.
+ * group(r) = (r / (group_inner * rows_per_group)) * group_inner + r % group_inner: group_inner == 1 is the contiguous
+ * [group, row] order; group_inner == S addresses the temporal groups (b, s) straight from the [B, T, S] token order,
+ * which folds the transposes of src/models/attention.py:436-438 / :474-476 away (row N2). */
 int tvi_bcast_rows_add_bf16(const tvi_bf16* v, const tvi_bf16* residual, tvi_bf16* out, int64_t nrows, int64_t rows_per_group,
-                            int C, int64_t ldv, int64_t ldr, int64_t ldo, void* stream);
+                            int64_t group_inner, int C, int64_t ldv, int64_t ldr, int64_t ldo, void* stream);
 
 /* Backward of the projections (training config 5: src/train_decouples.py back-propagates through the
  * same nn.Linear call sites; autograd's F.linear backward = two cuBLAS GEMMs + a bias column sum).
@@ -143,6 +146,16 @@ int tvi_colsum_bf16(const tvi_bf16* x, tvi_bf16* out, void* workspace, int64_t n
 int tvi_attn_temporal_fwd(const tvi_bf16* q, const tvi_bf16* k, const tvi_bf16* v, tvi_bf16* o, float* lse,
                           int64_t nseq, int heads, int Tq, int Tk, int d, int64_t ldq, int64_t ldk,
                           int64_t ldv, int64_t ldo, float scale, void* stream);
+
+/* The same core on INTERLEAVED sequences (row N2 of SURVEY 8.6): token t of sequence s is row
+ *   (s / seq_inner) * seq_inner * T + t * seq_inner + s % seq_inner
+ * of q / k / v / o (lse is indexed by the same row).  seq_inner == 1 is the layout above; seq_inner == S lets the
+ * temporal attention of TemporalBasicTransformerBlock read and write the [B*T, S, C] activations of the spatial
+ * block in place, replacing the two full-activation permute copies `[B*T,S,C] -> [B*S,T,C]` and back at
+ * src/models/attention.py:436-438 and :474-476 (every other op of that block is row-wise).  nseq % seq_inner == 0. */
+int tvi_attn_temporal_fwd_interleaved(const tvi_bf16* q, const tvi_bf16* k, const tvi_bf16* v, tvi_bf16* o, float* lse,
+                                      int64_t nseq, int heads, int Tq, int Tk, int d, int64_t seq_inner, int64_t ldq,
+                                      int64_t ldk, int64_t ldv, int64_t ldo, float scale, void* stream);
 
 /* ---------------------------------------------------------------------------------------------
  * A3b/A3d  few-key cross-attention core (image-embedding context, 1..8 keys): query row r attends

@@ -56,6 +56,25 @@ def test_temporal_core_reads_packed_qkv_in_place(cuda):
     assert (o.float().cpu().view(nseq, T, C) - ref).abs().max().item() < TOL
 
 
+@pytest.mark.parametrize("B,S,heads,T", [(2, 37, 5, 14), (1, 64, 2, 25), (3, 5, 1, 40), (2, 1, 2, 14)])
+def test_temporal_core_interleaved_sequences(cuda, B, S, heads, T):
+    # N2: sequences read straight out of the [B, T, S] token order == the contiguous kernel on permuted copies (bit-exact)
+    g = torch.Generator().manual_seed(S * 10 + T)
+    C = heads * 64
+    qkv, _ = _rand((B, T, S, 3 * C), g, cuda)
+    flat = qkv.view(-1, 3 * C)
+    lse = torch.full((B * T * S, heads), float("nan"), dtype=torch.float32, device=cuda)
+    o = ops.attn_temporal(flat[:, :C], flat[:, C:2 * C], flat[:, 2 * C:], B * S, heads, T, T, 0.125, lse=lse, seq_inner=S)
+    perm = qkv.permute(0, 2, 1, 3).contiguous().view(-1, 3 * C)          # [B*S*T, 3C]
+    lse_p = torch.empty(B * S * T, heads, dtype=torch.float32, device=cuda)
+    o_p = ops.attn_temporal(perm[:, :C], perm[:, C:2 * C], perm[:, 2 * C:], B * S, heads, T, T, 0.125, lse=lse_p)
+    torch.cuda.synchronize()
+    assert torch.equal(o.view(B, T, S, C), o_p.view(B, S, T, C).permute(0, 2, 1, 3))
+    assert torch.equal(lse.view(B, T, S, heads), lse_p.view(B, S, T, heads).permute(0, 2, 1, 3))
+    with pytest.raises(_lib.TviError):
+        ops.attn_temporal(flat[:, :C], flat[:, C:2 * C], flat[:, 2 * C:], B * S, heads, T, T, 0.125, seq_inner=B * S + 1)
+
+
 @pytest.mark.parametrize("B,heads,S,Skv", [
     (2, 2, 80, 80), (1, 5, 144, 144), (3, 1, 576, 576), (1, 2, 100, 100), (2, 2, 65, 130),
     (1, 1, 2304, 2304), (1, 2, 129, 63), (2, 5, 1000, 1000),

@@ -148,6 +148,36 @@ def test_temporal_basic_transformer_block_matches_oracle(cuda, B, T, S, C, heads
     assert y.shape == x.shape and err <= TOL * max(1.0, float(ref.abs().max()))
 
 
+def test_temporal_block_layout_fold_is_bit_exact(cuda):
+    # N2: the in-place [B*T, S, C] path (interleaved temporal cores) == the reference's permute -> block -> permute
+    B, T, S, C = 2, 14, 96, 320
+    blk = _init(TemporalBasicTransformerBlock(C, C, 5, 1024), 6, cuda)
+    blocks.install_blocks(blk)
+    g = torch.Generator().manual_seed(9)
+    x = torch.randn(B * T, S, C, generator=g).to(torch.bfloat16).to(cuda)
+    e = torch.randn(B * S, 1, 1024, generator=g).to(torch.bfloat16).to(cuda)
+    with torch.no_grad():
+        launches0 = ops.LAUNCHES
+        y_fold = blk(x, num_frames=T, encoder_hidden_states=e)
+        y_perm = blk(x, num_frames=T, encoder_hidden_states=e, fold_layout=False)
+    assert ops.LAUNCHES > launches0
+    assert torch.equal(y_fold, y_perm)
+
+
+def test_bcast_rows_add_group_inner(cuda):
+    B, T, S, C = 2, 5, 7, 64
+    g = torch.Generator().manual_seed(2)
+    v = torch.randn(B * S, C, generator=g).to(torch.bfloat16).to(cuda)
+    r = torch.randn(B * T * S, C, generator=g).to(torch.bfloat16).to(cuda)
+    got = ops.bcast_rows_add(v, r, T, group_inner=S)
+    want = (v.float().view(B, 1, S, C) + r.float().view(B, T, S, C)).to(torch.bfloat16).view(-1, C)
+    assert torch.equal(got, want)
+    got = ops.bcast_rows_add(v, None, T, group_inner=S)
+    assert torch.equal(got, v.view(B, 1, S, C).expand(B, T, S, C).reshape(-1, C))
+    got = ops.bcast_rows_add(v, None, T)  # contiguous groups
+    assert torch.equal(got, v.view(B * S, 1, C).expand(B * S, T, C).reshape(-1, C))
+
+
 def test_block_forward_refuses_gradients(cuda):
     blk = _init(BasicTransformerBlock(320, 5, 1024), 5, cuda)
     blocks.install_blocks(blk)

@@ -41,7 +41,7 @@ SIGNATURES = {
     "tvi_geglu_block": (_i32, [_i32]),
     "tvi_gemm_bf16_tn_ex": (_i32, [_ptr, _ptr, _ptr, _ptr, _ptr, _i64, _i32, _i32, _i64, _i64, _i64, _i64, _i32, _ptr]),
     "tvi_layernorm_bf16": (_i32, [_ptr, _ptr, _ptr, _ptr, _i64, _i32, _i64, _i64, _f32, _ptr]),
-    "tvi_bcast_rows_add_bf16": (_i32, [_ptr, _ptr, _ptr, _i64, _i64, _i32, _i64, _i64, _i64, _ptr]),
+    "tvi_bcast_rows_add_bf16": (_i32, [_ptr, _ptr, _ptr, _i64, _i64, _i64, _i32, _i64, _i64, _i64, _ptr]),
     "tvi_gemm_bf16_dgrad": (_i32, [_ptr, _ptr, _ptr, _i64, _i32, _i32, _i64, _i64, _i64, _ptr]),
     "tvi_gemm_bf16_wgrad_workspace_bytes": (_sz, [_i64, _i32, _i32]),
     "tvi_gemm_bf16_wgrad": (_i32, [_ptr, _ptr, _ptr, _ptr, _i64, _i32, _i32, _i64, _i64, _i64, _ptr]),
@@ -49,6 +49,8 @@ SIGNATURES = {
     "tvi_colsum_bf16": (_i32, [_ptr, _ptr, _ptr, _i64, _i64, _i32, _i64, _i64, _ptr]),
     "tvi_attn_temporal_fwd": (_i32, [_ptr, _ptr, _ptr, _ptr, _ptr, _i64, _i32, _i32, _i32, _i32,
                                      _i64, _i64, _i64, _i64, _f32, _ptr]),
+    "tvi_attn_temporal_fwd_interleaved": (_i32, [_ptr, _ptr, _ptr, _ptr, _ptr, _i64, _i32, _i32, _i32, _i32, _i64,
+                                                 _i64, _i64, _i64, _i64, _f32, _ptr]),
     "tvi_attn_fewkeys_fwd": (_i32, [_ptr, _ptr, _ptr, _ptr, _i64, _i64, _i32, _i32, _i32,
                                     _i64, _i64, _i64, _i64, _f32, _i32, _ptr, _ptr, _ptr, _ptr]),
     "tvi_attn_spatial_fwd": (_i32, [_ptr, _ptr, _ptr, _ptr, _ptr, _i32, _i32, _i32, _i32, _i32,

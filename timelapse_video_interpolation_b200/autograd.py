@@ -32,26 +32,43 @@ def _out_proj(o, w_o, b_o, residual):
 
 
 def self_attention(x: torch.Tensor, w_qkv: torch.Tensor, w_o: torch.Tensor, b_o, heads: int, scale: float,
-                   residual=None) -> torch.Tensor:
+                   residual=None, frames=None) -> torch.Tensor:
     """x [B', S, C] bf16 -> [B', S, C].  Reference: AttnProcessor2_0.__call__ with
-    encoder_hidden_states=None (src/models/attention_processor.py:1223-1261)."""
+    encoder_hidden_states=None (src/models/attention_processor.py:1223-1261).
+    `frames` = T: x is [B*T, S, C] in the SPATIAL token order and attention runs over the T tokens of every (b, s)
+    — the temporal block's self-attention without the permutes of src/models/attention.py:436-438 / :474-476."""
     Bp, S, C = x.shape
     inner = w_qkv.shape[0] // 3
     qkv = ops.gemm_bf16_tn(x.view(Bp * S, C), w_qkv)  # [B'*S, 3*inner], heads stay packed along the row
     q, k, v = qkv[:, :inner], qkv[:, inner:2 * inner], qkv[:, 2 * inner:]
-    o = _self_core(q, k, v, Bp, S, heads, scale)
+    if frames is not None:
+        o = ops.attn_temporal(q, k, v, Bp // frames * S, heads, frames, frames, scale, seq_inner=S)
+    else:
+        o = _self_core(q, k, v, Bp, S, heads, scale)
     y = _out_proj(o, w_o, b_o, residual)
     return y.view(Bp, S, -1)
 
 
 def cross_attention(x: torch.Tensor, e: torch.Tensor, w_q: torch.Tensor, w_kv: torch.Tensor, w_o: torch.Tensor, b_o,
-                    heads: int, scale: float, bias=None, stats=None, residual=None) -> torch.Tensor:
+                    heads: int, scale: float, bias=None, stats=None, residual=None, frames=None) -> torch.Tensor:
     """x [B', S, C], e [B', L, Ckv] -> [B', S, C].  Reference: same processor with
-    encoder_hidden_states given (keys/values from the context, :1225-1231)."""
+    encoder_hidden_states given (keys/values from the context, :1225-1231).
+    `frames` = T (one-key contexts only): x is [B*T, S, C] in the spatial token order, e is the temporal block's
+    [B*S, 1, Ckv] context; row (b, t, s) receives the projected value row of group (b, s)."""
     Bp, S, C = x.shape
     L = e.shape[1]
-    _check_context(x, e)
     inner = w_kv.shape[0] // 2
+    if frames is not None:
+        if L != 1 or stats is not None or bias is not None:
+            raise _lib.TviError(_lib.TVI_ERR_UNSUPPORTED, "frames= (temporal attention in the spatial token order) supports "
+                                                          "one-key contexts without bias / statistics")
+        if e.shape[0] != Bp // frames * S:
+            raise _lib.TviError(_lib.TVI_ERR_INVALID, "encoder_hidden_states batch does not match hidden_states (expects B*S rows)")
+        kv = ops.gemm_bf16_tn(e.view(-1, e.shape[2]), w_kv)
+        yv = ops.gemm_bf16_tn(kv[:, inner:], w_o, b_o)  # [B*S, C]
+        res2 = residual.reshape(Bp * S, -1) if residual is not None else None
+        return ops.bcast_rows_add(yv, res2, frames, group_inner=S, nrows=Bp * S).view(Bp, S, -1)
+    _check_context(x, e)
     kv = ops.gemm_bf16_tn(e.view(Bp * L, e.shape[2]), w_kv)  # [B'*L, 2*inner]
     k, v = kv[:, :inner], kv[:, inner:]
     if L == 1 and stats is None:
@@ -216,7 +233,7 @@ class _AttentionFn(torch.autograd.Function):
         return (dx, de, cast(dwq, dt_wq), cast(dwk, dt_wk), cast(dwv, dt_wv), cast(dwo, dt_wo), cast(dbo, dt_bo), None)
 
 
-def attention_forward(proc, attn, x, e, heads: int, scale: float, wo, bo, bias, stats, residual=None) -> torch.Tensor:
+def attention_forward(proc, attn, x, e, heads: int, scale: float, wo, bo, bias, stats, residual=None, frames=None) -> torch.Tensor:
     wq, wk, wv = attn.to_q.weight, attn.to_k.weight, attn.to_v.weight
     needs_grad = torch.is_grad_enabled() and any(
         t is not None and t.requires_grad for t in (x, e, wq, wk, wv, wo, bo))
@@ -224,9 +241,12 @@ def attention_forward(proc, attn, x, e, heads: int, scale: float, wo, bo, bias, 
     b_o = _to_bf16(bo).contiguous() if bo is not None else None
     if not needs_grad and not (residual is not None and torch.is_grad_enabled() and residual.requires_grad):
         if e is None:
-            return self_attention(x, proc._fused(attn, ("to_q", "to_k", "to_v")), w_o, b_o, heads, scale, residual)
+            return self_attention(x, proc._fused(attn, ("to_q", "to_k", "to_v")), w_o, b_o, heads, scale, residual, frames)
         return cross_attention(x, e, proc._fused(attn, ("to_q",)), proc._fused(attn, ("to_k", "to_v")), w_o, b_o, heads,
-                               scale, bias, stats, residual)
+                               scale, bias, stats, residual, frames)
+    if frames is not None:
+        raise NotImplementedError("frames= (temporal attention in the spatial token order) is inference-only: the backward "
+                                  "kernels take the [B*S, T, C] layout")
     if residual is not None:  # training: the fused residual epilogue has no backward; add it on the tape
         return attention_forward(proc, attn, x, e, heads, scale, wo, bo, bias, stats) + residual
     cfg = {"heads": heads, "scale": scale, "w_o": w_o, "b_o": b_o}

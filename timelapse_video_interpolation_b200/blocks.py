@@ -6,7 +6,10 @@ Drop-in replacements for
 Every arithmetic step is a libtvi kernel: LayerNorm -> attention (processor path, residual add fused into the
 out-projection epilogue) -> LayerNorm -> cross-attention (+ residual) -> LayerNorm -> FeedForward (GEGLU fused into the
 first GEMM, bias + residual into the second).  The `[B*T, S, C] <-> [B*S, T, C]` re-layout of the temporal block
-(:436-438, :474-476) is still a torch permute copy (row N2 folds it into the GEMM descriptors).
+(:436-438, :474-476) is folded away (row N2): LayerNorm / FeedForward / projections are row-wise, so the block runs on
+the spatial token order in place and only the attention cores address the T tokens of a (b, s) sequence with a
+row stride of S (`tvi_attn_temporal_fwd_interleaved`, `tvi_bcast_rows_add_bf16(group_inner=S)`).  Contexts with more
+than one key (or a ramp-bias / statistics processor) fall back to the permute copies.
 
 `install_blocks(model)` re-binds `forward` on every module with the block's attribute layout (duck-typed) and installs
 the attention processor on its Attention modules.  Inference only: the FeedForward / LayerNorm backward is not built,
@@ -32,12 +35,16 @@ def _no_grad_only(block, x):
                                   "call under torch.no_grad(), or install only the attention processor for training")
 
 
-def _attn(attn, x, e, residual):
+def _proc(attn):
     proc = attn.processor
     if not isinstance(proc, TviAttnProcessor):
         raise _lib.TviError(_lib.TVI_ERR_INVALID, "block forward: the Attention module does not carry a TviAttnProcessor "
                                                   "(call install_blocks / install first)")
-    return proc(attn, x, encoder_hidden_states=e, residual=residual)
+    return proc
+
+
+def _attn(attn, x, e, residual, frames=None):
+    return _proc(attn)(attn, x, encoder_hidden_states=e, residual=residual, frames=frames)
 
 
 def _check_basic(block):
@@ -72,13 +79,30 @@ def basic_transformer_block_forward(block, hidden_states: torch.Tensor, attentio
 
 
 def temporal_basic_transformer_block_forward(block, hidden_states: torch.Tensor, num_frames: int,
-                                             encoder_hidden_states: Optional[torch.Tensor] = None) -> torch.Tensor:
-    """Same signature as TemporalBasicTransformerBlock.forward (:423-428)."""
+                                             encoder_hidden_states: Optional[torch.Tensor] = None,
+                                             fold_layout: bool = True) -> torch.Tensor:
+    """Same signature as TemporalBasicTransformerBlock.forward (:423-428); `fold_layout=False` keeps the reference's two
+    permute copies (same results bit for bit — every kernel computes a row independently of its position)."""
     if getattr(block, "_chunk_size", None) is not None:
         raise _lib.TviError(_lib.TVI_ERR_UNSUPPORTED, "block forward: chunked feed-forward is not supported")
     _no_grad_only(block, hidden_states)
     BF, S, C = hidden_states.shape
     B = BF // num_frames
+    attn2 = getattr(block, "attn2", None)
+    in_place = fold_layout and num_frames <= 64 and (attn2 is None or encoder_hidden_states is None or (
+        encoder_hidden_states.shape[1] == 1 and not _proc(attn2).ramp_bias and _proc(attn2).stats_sink is None))
+    if in_place:
+        # every op but the attention cores is row-wise: stay in the [B*T, S, C] token order, no permute copies
+        x = hidden_states.contiguous()
+        n = layer_norm(block.norm_in, x)
+        x = feed_forward(block.ff_in, n, residual=x if block.is_res else None)   # :441-449
+        n = layer_norm(block.norm1, x)
+        x = _attn(block.attn1, n, None, x, frames=num_frames)                    # :451-453
+        if attn2 is not None:
+            n = layer_norm(block.norm2, x)
+            x = _attn(attn2, n, encoder_hidden_states, x, frames=num_frames)             # :456-460
+        n = layer_norm(block.norm3, x)
+        return feed_forward(block.ff, n, residual=x if block.is_res else None)   # :462-472
     # [B*T, S, C] -> [B*S, T, C] (:435-438)
     x = hidden_states.reshape(B, num_frames, S, C).permute(0, 2, 1, 3).reshape(B * S, num_frames, C)
     n = layer_norm(block.norm_in, x)

@@ -37,13 +37,19 @@ struct TemporalCfg {
 template <int MT>
 __device__ __forceinline__ void temporal_issue_loads(uint32_t stage_smem, const tvi_bf16* q, const tvi_bf16* k,
                                                      const tvi_bf16* v, int64_t item, int heads, int Tq, int Tk,
-                                                     int64_t ldq, int64_t ldk, int64_t ldv, int lane) {
+                                                     int64_t ldq, int64_t ldk, int64_t ldv, int64_t inner, int lane) {
   constexpr int kRows = 16 * MT;
   const int64_t seq = item / heads;
   const int head = (int)(item - seq * heads);
-  const tvi_bf16* qb = q + seq * Tq * ldq + head * 64;
-  const tvi_bf16* kb = k + seq * Tk * ldk + head * 64;
-  const tvi_bf16* vb = v + seq * Tk * ldv + head * 64;
+  // token t of sequence `seq` is row (seq / inner) * inner * T + t * inner + seq % inner: inner == 1 is the
+  // contiguous [nseq, T] layout, inner == S reads the temporal sequences straight out of the [B, T, S] token order
+  const int64_t so = seq / inner, si = seq - so * inner;
+  const tvi_bf16* qb = q + (so * inner * Tq + si) * ldq + head * 64;
+  const tvi_bf16* kb = k + (so * inner * Tk + si) * ldk + head * 64;
+  const tvi_bf16* vb = v + (so * inner * Tk + si) * ldv + head * 64;
+  ldq *= inner;  // consecutive tokens of a sequence are `inner` rows apart
+  ldk *= inner;
+  ldv *= inner;
   const int c = lane & 7;
 #pragma unroll
   for (int i = 0; i < kRows / 4; ++i) {
@@ -68,7 +74,7 @@ template <int MT>
 __global__ void __launch_bounds__(TemporalCfg<MT>::kWarps * 32)
 attn_temporal_kernel(const tvi_bf16* __restrict__ q, const tvi_bf16* __restrict__ k, const tvi_bf16* __restrict__ v,
                      tvi_bf16* __restrict__ o, float* __restrict__ lse, int64_t nitems, int heads, int Tq, int Tk,
-                     int64_t ldq, int64_t ldk, int64_t ldv, int64_t ldo, float scale) {
+                     int64_t ldq, int64_t ldk, int64_t ldv, int64_t ldo, float scale, int64_t inner) {
   using Cfg = TemporalCfg<MT>;
   constexpr int kRows = Cfg::kRows;
   constexpr int NT = 2 * MT;  // 8-key column tiles of S
@@ -84,14 +90,14 @@ attn_temporal_kernel(const tvi_bf16* __restrict__ q, const tvi_bf16* __restrict_
 
   int64_t item = gw;
   int stage = 0;
-  if (item < nitems) temporal_issue_loads<MT>(warp_smem, q, k, v, item, heads, Tq, Tk, ldq, ldk, ldv, lane);
+  if (item < nitems) temporal_issue_loads<MT>(warp_smem, q, k, v, item, heads, Tq, Tk, ldq, ldk, ldv, inner, lane);
   cp_async_commit();
 
   for (; item < nitems; item += stride, stage ^= 1) {
     const int64_t next = item + stride;
     if (next < nitems)
       temporal_issue_loads<MT>(warp_smem + (stage ^ 1) * Cfg::kStageBytes, q, k, v, next, heads, Tq, Tk, ldq, ldk, ldv,
-                               lane);
+                               inner, lane);
     cp_async_commit();
     cp_async_wait<1>();
     __syncwarp();
@@ -102,6 +108,8 @@ attn_temporal_kernel(const tvi_bf16* __restrict__ q, const tvi_bf16* __restrict_
     uint8_t* pQ = warp_ptr + stage * Cfg::kStageBytes;
     const int64_t seq = item / heads;
     const int head = (int)(item - seq * heads);
+    const int64_t so = seq / inner;
+    const int64_t row0 = so * inner * Tq + (seq - so * inner);  // first query row of this sequence; rows are `inner` apart
 
 #pragma unroll
     for (int mt = 0; mt < MT; ++mt) {
@@ -180,19 +188,19 @@ attn_temporal_kernel(const tvi_bf16* __restrict__ q, const tvi_bf16* __restrict_
       }
       if (lse != nullptr && qd == 0) {
         // natural-log-sum-exp of the scaled logits
-        if (r0 < Tq) lse[(seq * Tq + r0) * heads + head] = m0 * scale + __logf(l0);
-        if (r1 < Tq) lse[(seq * Tq + r1) * heads + head] = m1 * scale + __logf(l1);
+        if (r0 < Tq) lse[(row0 + r0 * inner) * heads + head] = m0 * scale + __logf(l0);
+        if (r1 < Tq) lse[(row0 + r1 * inner) * heads + head] = m1 * scale + __logf(l1);
       }
     }
     __syncwarp();
     // ---- coalesced 128-bit stores of the O tile --------------------------------------
-    tvi_bf16* ob = o + seq * Tq * ldo + head * 64;
+    tvi_bf16* ob = o + row0 * ldo + head * 64;
 #pragma unroll
     for (int i = 0; i < kRows / 4; ++i) {
       const int r = (lane >> 3) + 4 * i;
       if (r < Tq) {
         const uint4 val = *reinterpret_cast<const uint4*>(pQ + tile_off(r, lane & 7));
-        *reinterpret_cast<uint4*>(ob + r * ldo + (lane & 7) * 8) = val;
+        *reinterpret_cast<uint4*>(ob + r * inner * ldo + (lane & 7) * 8) = val;
       }
     }
     __syncwarp();  // the stage may be refilled by the next iteration's cp.async
@@ -203,7 +211,7 @@ attn_temporal_kernel(const tvi_bf16* __restrict__ q, const tvi_bf16* __restrict_
 template <int MT>
 int launch_temporal(const tvi_bf16* q, const tvi_bf16* k, const tvi_bf16* v, tvi_bf16* o, float* lse, int64_t nseq,
                     int heads, int Tq, int Tk, int64_t ldq, int64_t ldk, int64_t ldv, int64_t ldo, float scale,
-                    cudaStream_t st) {
+                    int64_t inner, cudaStream_t st) {
   using Cfg = TemporalCfg<MT>;
   static bool configured = false;
   if (!configured) {
@@ -216,7 +224,7 @@ int launch_temporal(const tvi_bf16* q, const tvi_bf16* k, const tvi_bf16* v, tvi
   const int64_t cap = (int64_t)num_sms() * per_sm;
   if (grid > cap) grid = cap;
   attn_temporal_kernel<MT><<<(unsigned)grid, Cfg::kWarps * 32, Cfg::kSmemBytes, st>>>(q, k, v, o, lse, nitems, heads, Tq, Tk,
-                                                                                     ldq, ldk, ldv, ldo, scale);
+                                                                                     ldq, ldk, ldv, ldo, scale, inner);
   TVI_LAUNCH_OK("attn_temporal_kernel");
   return TVI_OK;
 }
@@ -389,23 +397,30 @@ int launch_fewkeys(const tvi_bf16* q, const tvi_bf16* k, const tvi_bf16* v, tvi_
 
 extern "C" {
 
+int tvi_attn_temporal_fwd_interleaved(const tvi_bf16* q, const tvi_bf16* k, const tvi_bf16* v, tvi_bf16* o, float* lse,
+                                      int64_t nseq, int heads, int Tq, int Tk, int d, int64_t seq_inner, int64_t ldq,
+                                      int64_t ldk, int64_t ldv, int64_t ldo, float scale, void* stream) {
+  using namespace tvi;
+  TVI_CHECK_ARG(nseq >= 0 && heads >= 0, "tvi_attn_temporal_fwd_interleaved: negative size");
+  if (nseq == 0 || heads == 0) return TVI_OK;
+  TVI_CHECK_ARG(q && k && v && o, "tvi_attn_temporal_fwd_interleaved: null pointer");
+  if (d != 64) return fail(TVI_ERR_UNSUPPORTED, "tvi_attn_temporal_fwd_interleaved: head dim %d (only 64 is built)", d);
+  TVI_CHECK_ARG(Tq >= 1 && Tq <= 64 && Tk >= 1 && Tk <= 64, "tvi_attn_temporal_fwd_interleaved: Tq=%d Tk=%d outside [1,64]", Tq, Tk);
+  TVI_CHECK_ARG(ldq % 8 == 0 && ldk % 8 == 0 && ldv % 8 == 0 && ldo % 8 == 0, "tvi_attn_temporal_fwd_interleaved: row strides must be multiples of 8 elements");
+  TVI_CHECK_ARG(ldq >= heads * 64 && ldk >= heads * 64 && ldv >= heads * 64 && ldo >= heads * 64, "tvi_attn_temporal_fwd_interleaved: row stride smaller than heads*d");
+  TVI_CHECK_ARG(((uintptr_t)q | (uintptr_t)k | (uintptr_t)v | (uintptr_t)o) % 16 == 0, "tvi_attn_temporal_fwd_interleaved: pointers must be 16-byte aligned");
+  TVI_CHECK_ARG(seq_inner >= 1 && nseq % seq_inner == 0, "tvi_attn_temporal_fwd_interleaved: nseq must be a multiple of seq_inner");
+  cudaStream_t st = (cudaStream_t)stream;
+  const int T = Tq > Tk ? Tq : Tk;
+  if (T <= 16) return launch_temporal<1>(q, k, v, o, lse, nseq, heads, Tq, Tk, ldq, ldk, ldv, ldo, scale, seq_inner, st);
+  if (T <= 32) return launch_temporal<2>(q, k, v, o, lse, nseq, heads, Tq, Tk, ldq, ldk, ldv, ldo, scale, seq_inner, st);
+  return launch_temporal<4>(q, k, v, o, lse, nseq, heads, Tq, Tk, ldq, ldk, ldv, ldo, scale, seq_inner, st);
+}
+
 int tvi_attn_temporal_fwd(const tvi_bf16* q, const tvi_bf16* k, const tvi_bf16* v, tvi_bf16* o, float* lse, int64_t nseq,
                           int heads, int Tq, int Tk, int d, int64_t ldq, int64_t ldk, int64_t ldv, int64_t ldo,
                           float scale, void* stream) {
-  using namespace tvi;
-  TVI_CHECK_ARG(nseq >= 0 && heads >= 0, "tvi_attn_temporal_fwd: negative size");
-  if (nseq == 0 || heads == 0) return TVI_OK;
-  TVI_CHECK_ARG(q && k && v && o, "tvi_attn_temporal_fwd: null pointer");
-  if (d != 64) return fail(TVI_ERR_UNSUPPORTED, "tvi_attn_temporal_fwd: head dim %d (only 64 is built)", d);
-  TVI_CHECK_ARG(Tq >= 1 && Tq <= 64 && Tk >= 1 && Tk <= 64, "tvi_attn_temporal_fwd: Tq=%d Tk=%d outside [1,64]", Tq, Tk);
-  TVI_CHECK_ARG(ldq % 8 == 0 && ldk % 8 == 0 && ldv % 8 == 0 && ldo % 8 == 0, "tvi_attn_temporal_fwd: row strides must be multiples of 8 elements");
-  TVI_CHECK_ARG(ldq >= heads * 64 && ldk >= heads * 64 && ldv >= heads * 64 && ldo >= heads * 64, "tvi_attn_temporal_fwd: row stride smaller than heads*d");
-  TVI_CHECK_ARG(((uintptr_t)q | (uintptr_t)k | (uintptr_t)v | (uintptr_t)o) % 16 == 0, "tvi_attn_temporal_fwd: pointers must be 16-byte aligned");
-  cudaStream_t st = (cudaStream_t)stream;
-  const int T = Tq > Tk ? Tq : Tk;
-  if (T <= 16) return launch_temporal<1>(q, k, v, o, lse, nseq, heads, Tq, Tk, ldq, ldk, ldv, ldo, scale, st);
-  if (T <= 32) return launch_temporal<2>(q, k, v, o, lse, nseq, heads, Tq, Tk, ldq, ldk, ldv, ldo, scale, st);
-  return launch_temporal<4>(q, k, v, o, lse, nseq, heads, Tq, Tk, ldq, ldk, ldv, ldo, scale, st);
+  return tvi_attn_temporal_fwd_interleaved(q, k, v, o, lse, nseq, heads, Tq, Tk, d, 1, ldq, ldk, ldv, ldo, scale, stream);
 }
 
 int tvi_attn_fewkeys_fwd(const tvi_bf16* q, const tvi_bf16* k, const tvi_bf16* v, tvi_bf16* o, int64_t nrows,

@@ -36,8 +36,27 @@ constexpr int kGemmThreads = 64 + 32 * kEpiWarps;
 constexpr int kAccStride = 256;                    // TMEM columns per accumulator stage
 constexpr int kABytes = kBM * kBK * 2;             // 16 KB
 constexpr int kStageBufs = 2;                      // output staging buffers per epilogue warp (TMA stores in flight)
-constexpr int kStagingBytes = kEpiWarps * kStageBufs * 2048 + kEpiWarps * 1024;  // warps x bufs x [32 rows][64 B] + warps x 256 fp32 bias
+constexpr int kResStageBufs = 4;                   // with a residual: the buffers also receive the residual chunk two chunks ahead
+// warps x bufs x [32 rows][64 B] + warps x 256 fp32 bias
+constexpr int staging_bytes(int bufs) { return kEpiWarps * bufs * 2048 + kEpiWarps * 1024; }
 constexpr int kMaxStages = 8;
+
+// gelu(g) = g * Phi(g), Phi(g) = 0.5 * (1 + erf(g / sqrt 2)) (the erf form F.gelu computes).  Branch-free:
+// E = 0.5 * erfc(|g| / sqrt 2) = exp2(-1 + u * P(u)), u = min(|g|, 6), P a degree-5 minimax fit of
+// (log2(0.5 erfc(u / sqrt 2)) + 1) / u on [0, 6] (|log2 error| <= 7.1e-5); Phi = g < 0 ? E : 1 - E.  No cancellation on
+// the negative side; |gelu error| <= 7.4e-6 absolute and 4.9e-5 relative over the whole line -- 80x below the bf16
+// rounding of the stored product.  6 FMA + 1 MUFU.EX2 instead of erff's two divergent polynomial branches.
+__device__ __forceinline__ float gelu_erf(float g) {
+  const float u = fminf(fabsf(g), 6.0f);
+  float q = 2.3433244e-05f;
+  q = fmaf(q, u, -0.00061973924f);
+  q = fmaf(q, u, 0.007260352f);
+  q = fmaf(q, u, -0.051418606f);
+  q = fmaf(q, u, -0.46086353f);
+  q = fmaf(q, u, -1.1504804f);
+  const float e = fast_exp2(fmaf(q, u, -1.0f));
+  return g * (g < 0.f ? e : 1.0f - e);
+}
 
 struct GemmParams {
   int64_t m_tiles;
@@ -52,6 +71,7 @@ struct GemmParams {
   int N_store;         // columns of Y (N, or N/2 with the GEGLU epilogue)
   const tvi_bf16* residual;  // nullable [M, N_store] (ldr): added after bias / activation
   int64_t ldr;
+  int stage_bufs;      // staging buffers per epilogue warp (kStageBufs, or kResStageBufs with a residual)
   int res_b;           // the CTA's B slice [BN x K] stays resident in shared memory (grid is a multiple of n_tiles)
   float* partial;      // kSplit: [splits][M_out][ldp] fp32
   int64_t M_out;
@@ -63,13 +83,14 @@ struct GemmParams {
 template <bool kAMn, bool kBMn, bool kSplit>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CUtensorMap tmW,
-                 const __grid_constant__ CUtensorMap tmY, const GemmParams p) {
+                 const __grid_constant__ CUtensorMap tmY, const __grid_constant__ CUtensorMap tmR, const GemmParams p) {
   extern __shared__ uint8_t smem_raw[];
   __shared__ __align__(8) uint64_t bar_full[kMaxStages];
   __shared__ __align__(8) uint64_t bar_empty[kMaxStages];
   __shared__ __align__(8) uint64_t bar_acc_full[2];
   __shared__ __align__(8) uint64_t bar_acc_empty[2];
   __shared__ __align__(8) uint64_t bar_w;
+  __shared__ __align__(8) uint64_t bar_res[kEpiWarps][kResStageBufs];
   __shared__ uint32_t s_tmem_base;
 
   const int warp = threadIdx.x >> 5;
@@ -94,11 +115,14 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
     tma_prefetch_desc(&tmX);
     tma_prefetch_desc(&tmW);
     tma_prefetch_desc(&tmY);
+    tma_prefetch_desc(&tmR);
     for (int s = 0; s < p.stages; ++s) {
       mbar_init(&bar_full[s], 1);
       mbar_init(&bar_empty[s], 1);
     }
     mbar_init(&bar_w, 1);
+    for (int w = 0; w < kEpiWarps; ++w)
+      for (int b = 0; b < kResStageBufs; ++b) mbar_init(&bar_res[w][b], 1);
     for (int s = 0; s < 2; ++s) {
       mbar_init(&bar_acc_full[s], 1);
       mbar_init(&bar_acc_empty[s], kEpiWarps);
@@ -218,10 +242,45 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
     const int quad = warp & 3;  // TMEM lane quadrant this warp may read
     const int chalf = (warp - 2) >> 2;
     constexpr int kChunkStep = kEpiWarps / 4;
-    const uint32_t my_staging = staging + (warp - 2) * kStageBufs * 2048;
-    uint8_t* my_staging_ptr = staging_ptr + (warp - 2) * kStageBufs * 2048;
-    float* my_bias = reinterpret_cast<float*>(staging_ptr + kEpiWarps * kStageBufs * 2048 + (warp - 2) * 1024);
+    const int nbufs = p.stage_bufs;
+    uint8_t* my_staging_ptr = staging_ptr + (warp - 2) * nbufs * 2048;
+    float* my_bias = reinterpret_cast<float*>(staging_ptr + kEpiWarps * nbufs * 2048 + (warp - 2) * 1024);
     int buf = 0;
+    // Residual (Y = acc + bias + R): a per-chunk global read after the accumulator wait would expose one DRAM latency
+    // per 32 columns (out-projection at K = 320: 0.076 -> 0.180 ms).  Instead lane 0 TMA-loads the [32 x 32] residual
+    // chunk into the chunk's own staging buffer TWO chunks ahead (4 buffers per warp); the thread adds its row in
+    // place and the same buffer goes out through the TMA store.
+    const bool has_res = !kSplit && p.residual != nullptr;
+    uint64_t* my_res_bar = bar_res[warp - 2];
+    int64_t ptile = blockIdx.x;  // prefetch cursor: (tile, chunk) of the next residual chunk to request
+    int pc = chalf;
+    uint32_t pq = 0, qn = 0;     // chunks requested / consumed by this warp
+    auto valid_chunks = [&](int64_t tile) {  // chunks of this tile that start inside [0, N_store)
+      const int nt = (int)(tile % p.n_tiles);
+      const int n0s = p.geglu ? (nt * p.BN) >> 1 : nt * p.BN;
+      const int oc = p.geglu ? p.BN / 64 : p.BN / 32;
+      const int v = (p.N_store - n0s + 31) / 32;
+      return v < oc ? v : oc;
+    };
+    auto issue_residual = [&]() {  // lane 0
+      while (ptile < n_tiles_total && pc >= valid_chunks(ptile)) {
+        ptile += gridDim.x;
+        pc = chalf;
+      }
+      if (ptile >= n_tiles_total) return;
+      const int64_t mt = ptile / p.n_tiles;
+      const int nt = (int)(ptile - mt * p.n_tiles);
+      const int n0s = p.geglu ? (nt * p.BN) >> 1 : nt * p.BN;
+      const uint32_t b = pq & (kResStageBufs - 1);
+      mbar_arrive_expect_tx(&my_res_bar[b], 2048);
+      tma_load_2d(my_staging_ptr + b * 2048, &tmR, &my_res_bar[b], n0s + pc * 32, (int)(mt * kBM) + quad * 32);
+      ++pq;
+      pc += kChunkStep;
+    };
+    if (has_res && lane == 0) {
+      issue_residual();
+      issue_residual();
+    }
     int as = 0;
     uint32_t aph = 0;
     const int chunks = p.BN / 32;
@@ -287,37 +346,43 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
         }
         if (p.geglu) {
           // GEGLU (diffusers GEGLU.forward: hidden * F.gelu(gate), erf form): gate = the partner column
+          const float* gate_bias = my_bias + (out_chunks + c) * 32;
 #pragma unroll
-          for (int j = 0; j < 32; ++j) {
-            float g = __uint_as_float(rg[j]);
-            if (p.bias != nullptr) g += my_bias[(out_chunks + c) * 32 + j];
-            f[j] *= 0.5f * g * (1.0f + erff(g * 0.70710678118654752f));
+          for (int j = 0; j < 32; j += 4) {
+            float4 b4 = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (p.bias != nullptr) b4 = *reinterpret_cast<const float4*>(gate_bias + j);
+            f[j] *= gelu_erf(__uint_as_float(rg[j]) + b4.x);
+            f[j + 1] *= gelu_erf(__uint_as_float(rg[j + 1]) + b4.y);
+            f[j + 2] *= gelu_erf(__uint_as_float(rg[j + 2]) + b4.z);
+            f[j + 3] *= gelu_erf(__uint_as_float(rg[j + 3]) + b4.w);
           }
         }
-        if (p.residual != nullptr) {
-          const int64_t row = (int64_t)m0 + quad * 32 + lane;
-          if (row < p.M_out) {
-            const tvi_bf16* rp = p.residual + row * p.ldr + ncol0;
-#pragma unroll
-            for (int j = 0; j < 32; j += 8) {
-              if (ncol0 + j < p.N_store) {  // N_store % 8 == 0
-                const uint4 u = __ldg(reinterpret_cast<const uint4*>(rp + j));
-                const __nv_bfloat162* h2 = reinterpret_cast<const __nv_bfloat162*>(&u);
-#pragma unroll
-                for (int q = 0; q < 4; ++q) {
-                  const float2 t2 = __bfloat1622float2(h2[q]);
-                  f[j + 2 * q] += t2.x;
-                  f[j + 2 * q + 1] += t2.y;
-                }
-              }
-            }
-          }
-        }
-        // staging buffer `buf` was last read by the TMA store issued kStageBufs chunks ago
-        if (lane == 0) tma_store_wait_read<kStageBufs - 1>();
-        __syncwarp();
         uint8_t* row_ptr = my_staging_ptr + buf * 2048 + lane * 64;
         const int sw = (lane >> 1) & 3;
+        if (has_res) {
+          // buffer (qn + 2) % 4 was last read by the store of chunk qn - 2: all but the latest store have drained
+          if (lane == 0) {
+            tma_store_wait_read<1>();
+            issue_residual();
+          }
+          mbar_wait(&my_res_bar[buf], (qn >> 2) & 1);
+          ++qn;
+#pragma unroll
+          for (int ch = 0; ch < 4; ++ch) {
+            const uint4 u = *reinterpret_cast<const uint4*>(row_ptr + ((ch ^ sw) << 4));
+            const __nv_bfloat162* h2 = reinterpret_cast<const __nv_bfloat162*>(&u);
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+              const float2 t2 = __bfloat1622float2(h2[q]);
+              f[ch * 8 + 2 * q] += t2.x;
+              f[ch * 8 + 2 * q + 1] += t2.y;
+            }
+          }
+        } else {
+          // staging buffer `buf` was last read by the TMA store issued kStageBufs chunks ago
+          if (lane == 0) tma_store_wait_read<kStageBufs - 1>();
+        }
+        __syncwarp();
 #pragma unroll
         for (int ch = 0; ch < 4; ++ch) {
           uint4 v;
@@ -333,7 +398,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
           tma_store_2d(&tmY, reinterpret_cast<const void*>(my_staging_ptr + buf * 2048), ncol0, m0 + quad * 32);
           tma_store_commit();
         }
-        buf = (buf + 1) & (kStageBufs - 1);
+        buf = (buf + 1) & (nbufs - 1);
       }
       if (++as == 2) {
         as = 0;
@@ -341,7 +406,6 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
       }
     }
     if (lane == 0) tma_store_wait_all<0>();
-    (void)my_staging;
   }
 
   tc_fence_before();
@@ -406,7 +470,7 @@ int configure_once() {
   TVI_CUDA_OK(cudaGetDevice(&dev));
   if (dev < 0 || dev >= 64 || !configured[dev]) {
     TVI_CUDA_OK(cudaFuncSetAttribute(gemm_bf16_kernel<kAMn, kBMn, kSplit>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                     227 * 1024 - 256));
+                                     227 * 1024 - 512));
     if (dev >= 0 && dev < 64) configured[dev] = true;
   }
   return TVI_OK;
@@ -445,14 +509,16 @@ int launch_gemm(const char* name, const tvi_bf16* A, const tvi_bf16* B, const tv
   p.res_b = (!kAMn && !kBMn && !kSplit && res_bytes <= 128 * 1024 && p.n_tiles <= sms &&
              p.m_tiles * p.n_tiles >= 4 * (int64_t)sms) ? 1 : 0;
   const int stage_bytes = p.res_b ? kABytes : kABytes + b_bytes;
-  const int smem_cap = 227 * 1024 - 1024 /*alignment slack*/ - kStagingBytes - 256 /*static*/ - (p.res_b ? res_bytes : 0);
+  p.stage_bufs = (!kSplit && residual != nullptr) ? kResStageBufs : kStageBufs;
+  const int kStagingBytes = staging_bytes(p.stage_bufs);
+  const int smem_cap = 227 * 1024 - 1024 /*alignment slack*/ - kStagingBytes - 512 /*static*/ - (p.res_b ? res_bytes : 0);
   int stages = smem_cap / stage_bytes;
   if (stages > kMaxStages) stages = kMaxStages;
   TVI_CHECK_ARG(stages >= 2, "%s: tile does not fit shared memory", name);
   p.stages = stages;
   const int smem_bytes = 1024 + stages * stage_bytes + kStagingBytes + (p.res_b ? res_bytes : 0);
 
-  CUtensorMap tmA, tmB, tmY;
+  CUtensorMap tmA, tmB, tmY, tmR;
   int rc = operand_map(&tmA, A, kAMn, Mo, R, lda, kBM);
   if (rc) return rc;
   rc = operand_map(&tmB, B, kBMn, No, R, ldb, p.BN);
@@ -463,15 +529,22 @@ int launch_gemm(const char* name, const tvi_bf16* A, const tvi_bf16* B, const tv
     const uint32_t box[2] = {32u, 32u};
     rc = make_tensor_map(&tmY, Y, 2, 2, dims, strides, box, Swizzle::B64);
     if (rc) return rc;
+    tmR = tmY;
+    if (residual != nullptr) {
+      const uint64_t rstrides[1] = {(uint64_t)ldr * 2};
+      rc = make_tensor_map(&tmR, residual, 2, 2, dims, rstrides, box, Swizzle::B64);
+      if (rc) return rc;
+    }
   } else {
     tmY = tmA;  // unused by the split epilogue
+    tmR = tmA;
   }
   rc = configure_once<kAMn, kBMn, kSplit>();
   if (rc) return rc;
   int64_t grid = p.m_tiles * p.n_tiles;
   if (kSplit) grid *= (p.k_blocks_total + p.k_blocks - 1) / p.k_blocks;
   if (grid > sms) grid = p.res_b ? (sms / p.n_tiles) * p.n_tiles : sms;
-  gemm_bf16_kernel<kAMn, kBMn, kSplit><<<(unsigned)grid, kGemmThreads, smem_bytes, st>>>(tmA, tmB, tmY, p);
+  gemm_bf16_kernel<kAMn, kBMn, kSplit><<<(unsigned)grid, kGemmThreads, smem_bytes, st>>>(tmA, tmB, tmY, tmR, p);
   TVI_LAUNCH_OK(name);
   return TVI_OK;
 }

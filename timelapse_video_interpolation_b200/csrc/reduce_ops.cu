@@ -83,17 +83,24 @@ __global__ void colsum_final_kernel(const float* __restrict__ partial, tvi_bf16*
   *reinterpret_cast<uint32_t*>(out + g * ldo + c) = pack_bf16x2(a, b);
 }
 
-// out[r, :] = v[r / rows_per_group, :] + residual[r, :]: the one-key cross-attention result (every query row of a
-// group receives the group's projected value row) with the block's residual add fused
-// (`attn_output + hidden_states`, src/models/attention.py:316-317, :459-460).  One 16-byte chunk per thread.
+// out[r, :] = v[group(r), :] (+ residual[r, :]): the one-key cross-attention result (every query row of a group
+// receives the group's projected value row) with the block's residual add fused (`attn_output + hidden_states`,
+// src/models/attention.py:316-317, :459-460).  group(r) = (r / (inner * rows_per_group)) * inner + r % inner: inner == 1
+// is the contiguous [group, row] order, inner == S addresses the temporal groups (b, s) from the [B, T, S] token order
+// (the transposes at :436-438 / :474-476 folded away).  One 16-byte chunk per thread.
 __global__ void __launch_bounds__(256)
 bcast_rows_add_kernel(const tvi_bf16* __restrict__ v, const tvi_bf16* __restrict__ residual, tvi_bf16* __restrict__ out,
-                      int64_t nrows, int64_t rows_per_group, int C8, int64_t ldv, int64_t ldr, int64_t ldo) {
+                      int64_t nrows, int64_t rows_per_group, int64_t inner, int C8, int64_t ldv, int64_t ldr, int64_t ldo) {
   const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= nrows * C8) return;
   const int64_t r = idx / C8;
   const int c = (int)(idx - r * C8);
-  const uint4 a = __ldg(reinterpret_cast<const uint4*>(v + (r / rows_per_group) * ldv) + c);
+  const int64_t group = (r / (inner * rows_per_group)) * inner + r % inner;
+  const uint4 a = __ldg(reinterpret_cast<const uint4*>(v + group * ldv) + c);
+  if (residual == nullptr) {
+    *(reinterpret_cast<uint4*>(out + r * ldo) + c) = a;
+    return;
+  }
   const uint4 b = __ldg(reinterpret_cast<const uint4*>(residual + r * ldr) + c);
   const __nv_bfloat162* ha = reinterpret_cast<const __nv_bfloat162*>(&a);
   const __nv_bfloat162* hb = reinterpret_cast<const __nv_bfloat162*>(&b);
@@ -146,19 +153,21 @@ extern "C" int tvi_colsum_bf16(const tvi_bf16* x, tvi_bf16* out, void* workspace
 }
 
 extern "C" int tvi_bcast_rows_add_bf16(const tvi_bf16* v, const tvi_bf16* residual, tvi_bf16* out, int64_t nrows,
-                                       int64_t rows_per_group, int C, int64_t ldv, int64_t ldr, int64_t ldo, void* stream) {
+                                       int64_t rows_per_group, int64_t group_inner, int C, int64_t ldv, int64_t ldr, int64_t ldo,
+                                       void* stream) {
   using namespace tvi;
   TVI_CHECK_ARG(nrows >= 0 && C >= 0, "tvi_bcast_rows_add_bf16: negative size");
   if (nrows == 0 || C == 0) return TVI_OK;
-  TVI_CHECK_ARG(v && residual && out, "tvi_bcast_rows_add_bf16: null pointer");
-  TVI_CHECK_ARG(rows_per_group >= 1 && nrows % rows_per_group == 0, "tvi_bcast_rows_add_bf16: nrows must be a multiple of rows_per_group");
-  TVI_CHECK_ARG(C % 8 == 0 && ldv % 8 == 0 && ldr % 8 == 0 && ldo % 8 == 0 && ldv >= C && ldr >= C && ldo >= C,
+  TVI_CHECK_ARG(v && out, "tvi_bcast_rows_add_bf16: null pointer");
+  TVI_CHECK_ARG(rows_per_group >= 1 && group_inner >= 1 && nrows % (rows_per_group * group_inner) == 0,
+                "tvi_bcast_rows_add_bf16: nrows must be a multiple of rows_per_group * group_inner");
+  TVI_CHECK_ARG(C % 8 == 0 && ldv % 8 == 0 && ldo % 8 == 0 && ldv >= C && ldo >= C && (residual == nullptr || (ldr % 8 == 0 && ldr >= C)),
                 "tvi_bcast_rows_add_bf16: C and the row strides must be multiples of 8");
   TVI_CHECK_ARG(((uintptr_t)v | (uintptr_t)residual | (uintptr_t)out) % 16 == 0, "tvi_bcast_rows_add_bf16: pointers must be 16-byte aligned");
   const int64_t total = nrows * (C / 8);
   TVI_CHECK_ARG((total + 255) / 256 < ((int64_t)1 << 31), "tvi_bcast_rows_add_bf16: grid too large");
   bcast_rows_add_kernel<<<(unsigned)((total + 255) / 256), 256, 0, (cudaStream_t)stream>>>(v, residual, out, nrows, rows_per_group,
-                                                                                           C / 8, ldv, ldr, ldo);
+                                                                                           group_inner, C / 8, ldv, ldr, ldo);
   TVI_LAUNCH_OK("bcast_rows_add_kernel");
   return TVI_OK;
 }

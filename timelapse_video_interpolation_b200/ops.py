@@ -133,18 +133,25 @@ def layernorm_bf16(x: torch.Tensor, gamma: torch.Tensor | None, beta: torch.Tens
     return out
 
 
-def bcast_rows_add(v: torch.Tensor, residual: torch.Tensor, rows_per_group: int, out: torch.Tensor | None = None) -> torch.Tensor:
-    """out[r] = v[r // rows_per_group] + residual[r] (one-key cross-attention output + the block's residual)."""
+def bcast_rows_add(v: torch.Tensor, residual: torch.Tensor | None, rows_per_group: int, out: torch.Tensor | None = None,
+                   group_inner: int = 1, nrows: int | None = None) -> torch.Tensor:
+    """out[r] = v[group(r)] (+ residual[r]) — one-key cross-attention output (+ the block's residual);
+    group(r) = (r // (group_inner * rows_per_group)) * group_inner + r % group_inner."""
     _need_cuda(v, residual)
     v, ldv = _rows2d(v, "v")
-    residual, ldr = _rows2d(residual, "residual")
     C = v.shape[-1]
-    nrows = residual.numel() // C if C else 0
+    ldr = 0
+    if residual is not None:
+        residual, ldr = _rows2d(residual, "residual")
+        nrows = residual.numel() // C if C else 0
+    elif nrows is None:
+        nrows = v.shape[0] * int(rows_per_group)
     if out is None:
         out = torch.empty(nrows, C, dtype=torch.bfloat16, device=v.device)
     out, ldo = _rows2d(out, "out")
-    _hooked("bcast_rows_add", 1, _lib.load().tvi_bcast_rows_add_bf16, v.data_ptr(), residual.data_ptr(), out.data_ptr(), nrows,
-            int(rows_per_group), C, ldv, ldr, ldo, _stream())
+    _hooked("bcast_rows_add", 1, _lib.load().tvi_bcast_rows_add_bf16, v.data_ptr(),
+            residual.data_ptr() if residual is not None else None, out.data_ptr(), nrows, int(rows_per_group), int(group_inner), C,
+            ldv, ldr, ldo, _stream())
     return out
 
 
@@ -203,8 +210,9 @@ def colsum_bf16(x: torch.Tensor, rows_per_group: int | None = None, out: torch.T
     return out
 
 
-def attn_temporal(q, k, v, nseq: int, heads: int, Tq: int, Tk: int, scale: float, out=None, lse=None):
-    """Short-sequence attention core; q/k/v are [nseq*T, heads*64] row views (may be strided)."""
+def attn_temporal(q, k, v, nseq: int, heads: int, Tq: int, Tk: int, scale: float, out=None, lse=None, seq_inner: int = 1):
+    """Short-sequence attention core; q/k/v are [nseq*T, heads*64] row views (may be strided).  seq_inner > 1: the
+    sequences are interleaved (token t of sequence s is row (s // inner) * inner * T + t * inner + s % inner)."""
     global LAUNCHES
     _need_cuda(q, k, v)
     q, ldq = _rows2d(q, "q")
@@ -216,9 +224,9 @@ def attn_temporal(q, k, v, nseq: int, heads: int, Tq: int, Tk: int, scale: float
     out, ldo = _rows2d(out, "out")
     if EVENT_HOOK is not None:
         EVENT_HOOK("attn_temporal", True)
-    _lib.check(_lib.load().tvi_attn_temporal_fwd(q.data_ptr(), k.data_ptr(), v.data_ptr(), out.data_ptr(),
-                                                 lse.data_ptr() if lse is not None else None, nseq, heads, Tq, Tk, d,
-                                                 ldq, ldk, ldv, ldo, float(scale), _stream()))
+    _lib.check(_lib.load().tvi_attn_temporal_fwd_interleaved(q.data_ptr(), k.data_ptr(), v.data_ptr(), out.data_ptr(),
+                                                             lse.data_ptr() if lse is not None else None, nseq, heads, Tq, Tk,
+                                                             d, int(seq_inner), ldq, ldk, ldv, ldo, float(scale), _stream()))
     if EVENT_HOOK is not None:
         EVENT_HOOK("attn_temporal", False)
     LAUNCHES += 1

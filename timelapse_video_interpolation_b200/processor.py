@@ -111,9 +111,14 @@ class TviAttnProcessor:
     # ------------------------------------------------------------------ the call
     def __call__(self, attn, hidden_states: torch.Tensor, encoder_hidden_states: Optional[torch.Tensor] = None,
                  attention_mask: Optional[torch.Tensor] = None, temb: Optional[torch.Tensor] = None,
-                 scale: float = 1.0, *args, residual: Optional[torch.Tensor] = None, **kwargs) -> torch.Tensor:
-        """`residual` (libtvi extension used by the block-level forwards of blocks.py): a tensor of the output's
-        shape added in the out-projection epilogue, i.e. the caller's `attn_output + hidden_states`."""
+                 scale: float = 1.0, *args, residual: Optional[torch.Tensor] = None, frames: Optional[int] = None,
+                 **kwargs) -> torch.Tensor:
+        """libtvi extensions used by the block-level forwards of blocks.py:
+        `residual` — a tensor of the output's shape added in the out-projection epilogue, i.e. the caller's
+        `attn_output + hidden_states`;
+        `frames` = T — hidden_states is [B*T, S, C] in the spatial token order and attention runs over the T tokens of
+        every (b, s) (encoder_hidden_states: the temporal [B*S, 1, Ckv] context): the temporal block without its two
+        permute copies (src/models/attention.py:436-438, :474-476).  Inference only."""
         self._check(attn, hidden_states, attention_mask)
         in_dtype = hidden_states.dtype
         if in_dtype != torch.bfloat16:
@@ -134,6 +139,9 @@ class TviAttnProcessor:
             e = encoder_hidden_states.contiguous()
             L = e.shape[1]
             Tq = x.shape[1]
+            if frames is not None and (self.ramp_bias or self.stats_sink is not None):
+                raise _lib.TviError(_lib.TVI_ERR_UNSUPPORTED, "frames= is not available with ramp_bias / stats_sink "
+                                                              "(those read the [B*S, T, C] layout)")
             if self.ramp_bias:
                 if L != 2:
                     raise _lib.TviError(_lib.TVI_ERR_INVALID, "ramp_bias expects exactly 2 context tokens "
@@ -148,7 +156,9 @@ class TviAttnProcessor:
             if residual.shape != hidden_states.shape:
                 raise _lib.TviError(_lib.TVI_ERR_INVALID, "residual must have the shape of hidden_states")
             residual = residual.to(torch.bfloat16).contiguous()
-        y = attention_forward(self, attn, x, e, heads, float(attn.scale), wo, bo, bias, stats, residual)
+        if frames is not None and (frames < 1 or x.shape[0] % frames != 0):
+            raise _lib.TviError(_lib.TVI_ERR_INVALID, "frames must divide the batch dimension of hidden_states")
+        y = attention_forward(self, attn, x, e, heads, float(attn.scale), wo, bo, bias, stats, residual, frames)
 
         if stats is not None:
             self.stats_sink(stats, attn)

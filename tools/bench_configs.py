@@ -267,7 +267,7 @@ def cfg_block(steps):
     fl = bench.algorithmic_flops("L0", 1)["total"] + ff_flops
     emit({"config": "block_L0_spatial_plus_temporal", "clips": 1, "cfg": 2, "T": T, "ms": ms, "clip_frames_per_s": T / (ms * 1e-3),
           "tflop": fl / 1e12, "tflops": fl / 1e12 / (ms * 1e-3), "ff_tflop": ff_flops / 1e12, "kernels": kt.summary(3),
-          "note": "includes the two torch permute copies of the temporal block re-layout (row N2)"})
+          "note": "temporal block runs in the spatial token order (N2 fold): no permute copies"})
 
 
 def main():
