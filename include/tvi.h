@@ -116,6 +116,24 @@ int tvi_layernorm_bf16(const tvi_bf16* x, const tvi_bf16* gamma, const tvi_bf16*
 int tvi_bcast_rows_add_bf16(const tvi_bf16* v, const tvi_bf16* residual, tvi_bf16* out, int64_t nrows, int64_t rows_per_group,
                             int64_t group_inner, int C, int64_t ldv, int64_t ldr, int64_t ldo, void* stream);
 
+/* Layout glue of TransformerSpatioTemporalModel.forward (rows N1 "AlphaBlender" and N2 of SURVEY 8.6).
+ *   groupnorm_tokens : y[n, s, c] = GroupNorm(x)[n, c, s] — `self.norm` (nn.GroupNorm, biased variance, fp32/fp64
+ *       statistics) fused with `permute(0, 2, 3, 1).reshape(BF, H*W, C)`, src/models/transformer_temporal.py:300-304.
+ *       x is NCHW [N, C, HW] contiguous, y token-major [N*HW, C] (ldy); gamma / beta nullable;
+ *       `workspace` = tvi_groupnorm_tokens_workspace_bytes(N, C, HW, groups) bytes.  C % 8 == 0, HW % 8 == 0.
+ *   tokens_to_nchw_add : out[n, c, s] = y[n, s, c] (+ residual[n, c, s], nullable) — `reshape(BF, H, W, C)
+ *       .permute(0, 3, 1, 2).contiguous()` and `output = hidden_states + residual`, :354-357.
+ *   blend_rows : out[r, :] = alpha[r / rows_per_group] * x_spatial[r, :] + (1 - alpha[..]) * x_temporal[r, :] —
+ *       AlphaBlender.forward (diffusers 0.24 models/resnet.py) called at :349-351; alpha is fp32, one per image.
+ */
+size_t tvi_groupnorm_tokens_workspace_bytes(int64_t N, int C, int HW, int groups);
+int tvi_groupnorm_tokens_bf16(const tvi_bf16* x, const tvi_bf16* gamma, const tvi_bf16* beta, tvi_bf16* y, void* workspace,
+                              int64_t N, int C, int HW, int groups, int64_t ldy, float eps, void* stream);
+int tvi_tokens_to_nchw_add_bf16(const tvi_bf16* y, const tvi_bf16* residual, tvi_bf16* out, int64_t N, int C, int HW,
+                                int64_t ldy, void* stream);
+int tvi_blend_rows_bf16(const tvi_bf16* x_spatial, const tvi_bf16* x_temporal, const float* alpha, tvi_bf16* out,
+                        int64_t nrows, int64_t rows_per_group, int C, int64_t lds, int64_t ldt, int64_t ldo, void* stream);
+
 /* Backward of the projections (training config 5: src/train_decouples.py back-propagates through the
  * same nn.Linear call sites; autograd's F.linear backward = two cuBLAS GEMMs + a bias column sum).
  *   dgrad : dX[M,K] = dY[M,N] . W[N,K]          (W consumed in place, MN-major tcgen05 operand)

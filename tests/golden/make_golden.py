@@ -16,6 +16,9 @@ container (needs /root/reference); the GPU box uses the .npz files.
   `TemporalBasicTransformerBlock` classes (fp32, CPU).  Their leaf `GEGLU` lives in the un-vendored diffusers 0.24
   (`models/activations.py`); the shim below restates its published forward (`proj` -> chunk(2) -> hidden * F.gelu(gate))
   — every other line that runs (the block forwards, the FeedForward container, Attention + processor) is the reference's.
+* spatio_temporal.npz  — src/models/transformer_temporal.py: the reference's own `TransformerSpatioTemporalModel` (forward
+  :253-360) on its own blocks; the un-vendored diffusers leaves Timesteps / TimestepEmbedding / AlphaBlender are the
+  restatements in timelapse_video_interpolation_b200/modules.py.
 """
 from __future__ import annotations
 
@@ -254,9 +257,62 @@ def make_blocks(ap):
     print("blocks.npz", sorted({k.split(".")[0] for k in out}), {k: tuple(v.shape) for k, v in out.items() if k.endswith(".y")})
 
 
+def make_spatio_temporal(ap):
+    """src/models/transformer_temporal.py:TransformerSpatioTemporalModel (the reference's own class and forward) on top of
+    the reference's block classes; restated leaves: GEGLU (above), Timesteps / TimestepEmbedding (diffusers 0.24
+    models/embeddings.py), AlphaBlender (models/resnet.py) — taken from the package's diffusers-free mirrors."""
+    sys.path.insert(0, str(OUT.parents[1]))
+    from timelapse_video_interpolation_b200 import modules as mirrors
+    ra = sys.modules.get("ref_attention") or _load(REF / "src/models/attention.py", "ref_attention")
+    cfgu = types.ModuleType("diffusers.configuration_utils")
+    cfgu.ConfigMixin = type("ConfigMixin", (), {})
+    cfgu.register_to_config = lambda f: f
+    sys.modules["diffusers.utils"].BaseOutput = type("BaseOutput", (), {})
+    datt = types.ModuleType("diffusers.models.attention")
+    datt.BasicTransformerBlock, datt.TemporalBasicTransformerBlock = ra.BasicTransformerBlock, ra.TemporalBasicTransformerBlock
+    emb = sys.modules["diffusers.models.embeddings"]
+    emb.TimestepEmbedding, emb.Timesteps = mirrors.TimestepEmbedding, mirrors.Timesteps
+    mu = types.ModuleType("diffusers.models.modeling_utils")
+    mu.ModelMixin = torch.nn.Module
+    rn = types.ModuleType("diffusers.models.resnet")
+    rn.AlphaBlender = mirrors.AlphaBlender
+    sys.modules["models"].attention = ra
+    for name, mod in {"diffusers.configuration_utils": cfgu, "diffusers.models.attention": datt, "models.attention": ra,
+                      "diffusers.models.modeling_utils": mu, "diffusers.models.resnet": rn}.items():
+        sys.modules[name] = mod
+    rt = _load(REF / "src/models/transformer_temporal.py", "ref_transformer_temporal")
+    g = torch.Generator().manual_seed(77)
+    C, heads, cross = 64, 1, 48
+    m = rt.TransformerSpatioTemporalModel(heads, 64, in_channels=C, num_layers=1, cross_attention_dim=cross)
+    for mod in m.modules():
+        if isinstance(mod, ap.Attention):
+            mod.set_processor(ap.AttnProcessor2_0())
+    for name, p in m.named_parameters():
+        if name.endswith("mix_factor"):
+            p.data = torch.tensor([0.3])
+        elif "norm" in name:
+            p.data = (1.0 + 0.2 * torch.randn(p.shape, generator=g)) if name.endswith("weight") else 0.1 * torch.randn(p.shape, generator=g)
+        else:
+            p.data = torch.randn(p.shape, generator=g) * (p.shape[-1] ** -0.5 if p.dim() > 1 else 0.1)
+    B, T, H, W = 2, 5, 4, 6
+    x = torch.randn(B * T, C, H, W, generator=g)
+    e = torch.randn(B * T, 1, cross, generator=g)
+    ind = torch.zeros(B, T)
+    ind[1, 3] = 1.0  # one image-only frame: alpha == 1 there
+    out = {}
+    with torch.no_grad():
+        y = m(x, encoder_hidden_states=e, image_only_indicator=ind, return_dict=False)[0]
+    for k, v in m.state_dict().items():
+        out[f"sd.{k}"] = v.numpy()
+    out.update(x=x.numpy(), e=e.numpy(), ind=ind.numpy(), y=y.numpy())
+    np.savez_compressed(OUT / "spatio_temporal.npz", **out)
+    print("spatio_temporal.npz", tuple(y.shape), float(y.abs().max()))
+
+
 if __name__ == "__main__":
     torch.set_num_threads(4)
     make_flow()
     ap = make_attention()
     make_temporal_patched(ap)
     make_blocks(ap)
+    make_spatio_temporal(ap)

@@ -1,0 +1,134 @@
+"""GPU parity of the model-level forward (TransformerSpatioTemporalModel) and its layout kernels against the oracle."""
+import numpy as np
+import pytest
+import torch
+import torch.nn.functional as F
+
+from oracle import spatio_temporal_ref
+from timelapse_video_interpolation_b200 import _lib, ops, spatio_temporal
+from timelapse_video_interpolation_b200.modules import TransformerSpatioTemporalModel
+
+pytestmark = pytest.mark.gpu
+TOL = 2e-2
+
+
+def _bf(t, cuda):
+    return t.to(torch.bfloat16).to(cuda)
+
+
+@pytest.mark.parametrize("N,C,H,W,groups", [(3, 320, 8, 16, 32), (2, 64, 4, 6, 32), (1, 640, 24, 40, 32), (2, 96, 10, 12, 4)])
+def test_groupnorm_tokens(cuda, N, C, H, W, groups):
+    g = torch.Generator().manual_seed(C + H)
+    x = _bf(torch.randn(N, C, H, W, generator=g) * 2 + 0.7, cuda)
+    gamma, beta = _bf(1 + 0.3 * torch.randn(C, generator=g), cuda), _bf(0.2 * torch.randn(C, generator=g), cuda)
+    y = ops.groupnorm_tokens(x, gamma, beta, groups, 1e-6)
+    ref = F.group_norm(x.float().cpu(), groups, gamma.float().cpu(), beta.float().cpu(), 1e-6).permute(0, 2, 3, 1).reshape(N, H * W, C)
+    assert y.shape == (N, H * W, C)
+    err = float((y.float().cpu() - ref).abs().max())
+    assert err <= 2 ** -7 * max(1.0, float(ref.abs().max())), err  # one bf16 rounding of the result
+    y2 = ops.groupnorm_tokens(x, None, None, groups, 1e-6)
+    ref2 = F.group_norm(x.float().cpu(), groups, None, None, 1e-6).permute(0, 2, 3, 1).reshape(N, H * W, C)
+    assert float((y2.float().cpu() - ref2).abs().max()) <= 2 ** -7 * max(1.0, float(ref2.abs().max()))
+
+
+def test_groupnorm_tokens_large_mean_does_not_cancel(cuda):
+    x = _bf(torch.randn(1, 64, 16, 16) * 0.05 + 30.0, cuda)
+    y = ops.groupnorm_tokens(x, None, None, 32, 1e-6)
+    ref = F.group_norm(x.float().cpu(), 32, None, None, 1e-6).permute(0, 2, 3, 1).reshape(1, 256, 64)
+    assert float((y.float().cpu() - ref).abs().max()) < 5e-2
+
+
+@pytest.mark.parametrize("N,C,H,W", [(3, 320, 8, 16), (2, 64, 4, 6), (1, 72, 10, 12)])
+def test_tokens_to_nchw_add(cuda, N, C, H, W):
+    g = torch.Generator().manual_seed(C)
+    y = _bf(torch.randn(N, H * W, C, generator=g), cuda)
+    r = _bf(torch.randn(N, C, H, W, generator=g), cuda)
+    got = ops.tokens_to_nchw_add(y, r, H, W)
+    want = (y.float().view(N, H, W, C).permute(0, 3, 1, 2) + r.float()).to(torch.bfloat16)
+    assert torch.equal(got, want)
+    assert torch.equal(ops.tokens_to_nchw_add(y, None, H, W), y.view(N, H, W, C).permute(0, 3, 1, 2).contiguous())
+
+
+def test_blend_rows(cuda):
+    g = torch.Generator().manual_seed(4)
+    BF, S, C = 6, 50, 320
+    xs, xt = _bf(torch.randn(BF, S, C, generator=g), cuda), _bf(torch.randn(BF, S, C, generator=g), cuda)
+    xt[2] = float("nan")                                  # an image-only frame never reads the temporal branch
+    alpha = torch.tensor([0.3, 0.5, 1.0, 0.0, 0.7310, 0.25], device=cuda)
+    got = ops.blend_rows(xs, xt, alpha, S)
+    a = alpha.view(BF, 1, 1)
+    want = torch.addcmul(a * xs.float(), (1 - a), xt.float())
+    ok = torch.ones(BF, dtype=torch.bool)
+    ok[2] = False
+    assert float((got.float() - want)[ok].abs().max()) <= 2 ** -7 * 4
+    assert torch.equal(got[2], xs[2]) and torch.equal(got[3], xt[3])
+    with pytest.raises(_lib.TviError):
+        ops.blend_rows(xs, xt, alpha[:5].contiguous(), S)
+
+
+def _model(C, heads, cross, seed, cuda):
+    m = TransformerSpatioTemporalModel(heads, 64, in_channels=C, num_layers=1, cross_attention_dim=cross)
+    g = torch.Generator().manual_seed(seed)
+    with torch.no_grad():
+        for name, p in m.named_parameters():
+            if name.endswith("mix_factor"):
+                p.fill_(0.4)
+            elif "norm" in name:
+                p.copy_(1.0 + 0.1 * torch.randn(p.shape, generator=g) if name.endswith("weight") else 0.05 * torch.randn(p.shape, generator=g))
+            else:
+                p.copy_(torch.randn(p.shape, generator=g) * (p.shape[-1] ** -0.5 if p.dim() > 1 else 0.05))
+    return m.to(cuda, torch.bfloat16).eval()
+
+
+@pytest.mark.parametrize("B,T,H,W,C,heads", [(2, 14, 8, 16, 320, 5), (1, 25, 8, 8, 640, 10)])
+def test_transformer_spatio_temporal_model_matches_oracle(cuda, B, T, H, W, C, heads):
+    m = _model(C, heads, 1024, 11, cuda)
+    assert spatio_temporal.install_spatio_temporal(m) == 1
+    g = torch.Generator().manual_seed(T)
+    x = _bf(torch.randn(B * T, C, H, W, generator=g), cuda)
+    e = _bf(torch.randn(B * T, 1, 1024, generator=g), cuda)
+    ind = torch.zeros(B, T, device=cuda)
+    ind[0, 2] = 1.0
+    launches0 = ops.LAUNCHES
+    with torch.no_grad():
+        out = m(x, encoder_hidden_states=e, image_only_indicator=ind)
+        y = out.sample
+        y_tuple = m(x, encoder_hidden_states=(e, e), image_only_indicator=ind, return_dict=False)[0]
+    torch.cuda.synchronize()
+    assert ops.LAUNCHES - launches0 >= 2 * 30
+    assert torch.equal(y, y_tuple) and y.shape == x.shape and y.dtype == torch.bfloat16
+    ref = spatio_temporal_ref.transformer_spatio_temporal_ref(m, x, e, ind, alpha_dtype=torch.bfloat16)
+    err = float((y.float().cpu() - ref).abs().max())
+    print(f"spatio-temporal model C={C} T={T}: max abs err {err:.3e}, max |ref| {float(ref.abs().max()):.3f}")
+    assert err <= TOL * max(1.0, float(ref.abs().max()))
+    assert spatio_temporal.uninstall_spatio_temporal(m) == 1
+    with pytest.raises(RuntimeError):
+        m(x, encoder_hidden_states=e, image_only_indicator=ind)
+
+
+def test_model_forward_matches_reference_golden(cuda, golden_dir):
+    # the reference's own module output (fp32, CPU) vs the libtvi forward in bf16 on the same weights
+    z = np.load(golden_dir / "spatio_temporal.npz")
+    m = TransformerSpatioTemporalModel(1, 64, in_channels=64, num_layers=1, cross_attention_dim=48)
+    m.load_state_dict({k[3:]: torch.from_numpy(z[k]) for k in z.files if k.startswith("sd.")}, strict=True)
+    m = m.to(cuda, torch.bfloat16).eval()
+    spatio_temporal.install_spatio_temporal(m)
+    with torch.no_grad():
+        y = m(_bf(torch.from_numpy(z["x"]), cuda), encoder_hidden_states=_bf(torch.from_numpy(z["e"]), cuda),
+              image_only_indicator=torch.from_numpy(z["ind"]).to(cuda), return_dict=False)[0]
+    ref = torch.from_numpy(z["y"])
+    err = float((y.float().cpu() - ref).abs().max())
+    print(f"vs reference golden: max abs err {err:.3e}, max |ref| {float(ref.abs().max()):.3f}")
+    assert err <= 2 * TOL * max(1.0, float(ref.abs().max()))  # bf16 inputs AND bf16 weights against the fp32 reference
+
+
+def test_model_forward_refuses_gradients_and_cpu(cuda):
+    m = _model(320, 5, 1024, 3, cuda)
+    spatio_temporal.install_spatio_temporal(m)
+    x = torch.randn(2, 320, 8, 8, device=cuda).to(torch.bfloat16)
+    e = torch.randn(2, 1, 1024, device=cuda).to(torch.bfloat16)
+    ind = torch.zeros(1, 2, device=cuda)
+    with pytest.raises(NotImplementedError):
+        m(x.requires_grad_(True), encoder_hidden_states=e, image_only_indicator=ind)
+    with torch.no_grad(), pytest.raises(_lib.TviError):
+        m(x.detach().cpu(), encoder_hidden_states=e, image_only_indicator=ind)

@@ -157,3 +157,25 @@ def test_block_oracles_match_reference_block_forwards(golden_dir):
     x, e, T = torch.from_numpy(z["temporal.x"]), torch.from_numpy(z["temporal.e"]), int(z["temporal.num_frames"])
     y = blocks_ref.temporal_basic_transformer_block_ref(tb, x, T, e)
     assert max_abs(y, z["temporal.y"]) < 5e-5
+
+
+def test_spatio_temporal_oracle_matches_reference_model(golden_dir):
+    # the reference's own TransformerSpatioTemporalModel.forward (src/models/transformer_temporal.py:253-360)
+    from oracle import spatio_temporal_ref
+    from timelapse_video_interpolation_b200.modules import TransformerSpatioTemporalModel
+    z = np.load(golden_dir / "spatio_temporal.npz")
+    m = TransformerSpatioTemporalModel(1, 64, in_channels=64, num_layers=1, cross_attention_dim=48)
+    sd = {k[3:]: torch.from_numpy(z[k]) for k in z.files if k.startswith("sd.")}
+    missing, unexpected = m.load_state_dict(sd, strict=True)   # same state_dict keys as the reference module
+    assert not missing and not unexpected
+    x, e, ind = (torch.from_numpy(z[k]) for k in ("x", "e", "ind"))
+    y = spatio_temporal_ref.transformer_spatio_temporal_ref(m.eval(), x, e, ind)
+    assert y.shape == x.shape
+    assert max_abs(y, z["y"]) < 1e-4
+    # the image-only frame (alpha == 1) takes the spatial branch only: perturbing the temporal blocks leaves it unchanged
+    with torch.no_grad():
+        for p in m.temporal_transformer_blocks.parameters():
+            p.add_(0.5)
+    y2 = spatio_temporal_ref.transformer_spatio_temporal_ref(m, x, e, ind)
+    frame = 1 * 5 + 3
+    assert max_abs(y2[frame], z["y"][frame]) < 1e-4 and max_abs(y2, z["y"]) > 1e-2

@@ -42,6 +42,10 @@ SIGNATURES = {
     "tvi_gemm_bf16_tn_ex": (_i32, [_ptr, _ptr, _ptr, _ptr, _ptr, _i64, _i32, _i32, _i64, _i64, _i64, _i64, _i32, _ptr]),
     "tvi_layernorm_bf16": (_i32, [_ptr, _ptr, _ptr, _ptr, _i64, _i32, _i64, _i64, _f32, _ptr]),
     "tvi_bcast_rows_add_bf16": (_i32, [_ptr, _ptr, _ptr, _i64, _i64, _i64, _i32, _i64, _i64, _i64, _ptr]),
+    "tvi_groupnorm_tokens_workspace_bytes": (_sz, [_i64, _i32, _i32, _i32]),
+    "tvi_groupnorm_tokens_bf16": (_i32, [_ptr, _ptr, _ptr, _ptr, _ptr, _i64, _i32, _i32, _i32, _i64, _f32, _ptr]),
+    "tvi_tokens_to_nchw_add_bf16": (_i32, [_ptr, _ptr, _ptr, _i64, _i32, _i32, _i64, _ptr]),
+    "tvi_blend_rows_bf16": (_i32, [_ptr, _ptr, _ptr, _ptr, _i64, _i64, _i32, _i64, _i64, _i64, _ptr]),
     "tvi_gemm_bf16_dgrad": (_i32, [_ptr, _ptr, _ptr, _i64, _i32, _i32, _i64, _i64, _i64, _ptr]),
     "tvi_gemm_bf16_wgrad_workspace_bytes": (_sz, [_i64, _i32, _i32]),
     "tvi_gemm_bf16_wgrad": (_i32, [_ptr, _ptr, _ptr, _ptr, _i64, _i32, _i32, _i64, _i64, _i64, _ptr]),

@@ -1,0 +1,266 @@
+// Layout glue of TransformerSpatioTemporalModel.forward (rows N1 "AlphaBlender" and N2 of SURVEY.md 8.6), all HBM-bound:
+//   groupnorm_stats_kernel / groupnorm_tokens_kernel
+//       self.norm (GroupNorm, 32 groups, eps 1e-6) on the NCHW feature map fused with
+//       `permute(0, 2, 3, 1).reshape(BF, H*W, C)` (src/models/transformer_temporal.py:300-304): statistics per
+//       (image, group) in one read, then normalise + affine + NCHW -> token-major transpose through a shared-memory tile.
+//   tokens_to_nchw_add_kernel
+//       `reshape(BF, H, W, C).permute(0, 3, 1, 2).contiguous()` + `hidden_states + residual` (:354-357).
+//   blend_rows_kernel
+//       AlphaBlender.forward (diffusers 0.24 models/resnet.py, called at :349-351):
+//       out = alpha * x_spatial + (1 - alpha) * x_temporal with one alpha per image (frame).
+// Every kernel moves 16 bytes per thread per access; the transposes go through a [64][72] bf16 tile so that both the
+// NCHW side (64 spatial positions = 128 contiguous bytes per channel) and the token side (64 channels = 128 bytes per
+// token) are read and written in full 128-byte segments.
+#include "tvi_common.cuh"
+
+namespace tvi {
+namespace {
+
+constexpr int kGnSlice = 16384;  // elements of one (image, group) span per statistics CTA
+constexpr int kTile = 64;
+constexpr int kPitch = 72;       // bf16 elements per tile row (144 B: 16-byte aligned, 4-bank shift per row)
+
+__device__ __forceinline__ void unpack8f(const uint4& u, float* f) {
+  const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&u);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const float2 t = __bfloat1622float2(h[i]);
+    f[2 * i] = t.x;
+    f[2 * i + 1] = t.y;
+  }
+}
+
+// partial[(ng * nsplit + split)] = (sum, sum of squares) of one slice of the contiguous span of group ng
+__global__ void __launch_bounds__(256)
+groupnorm_stats_kernel(const tvi_bf16* __restrict__ x, double2* __restrict__ partial, int64_t span, int nsplit) {
+  const int64_t ng = blockIdx.x / nsplit;
+  const int split = (int)(blockIdx.x - ng * nsplit);
+  const int64_t lo = (int64_t)split * kGnSlice;
+  int64_t hi = lo + kGnSlice;
+  if (hi > span) hi = span;
+  const tvi_bf16* base = x + ng * span;
+  float s = 0.f, ss = 0.f;
+  for (int64_t i = lo + threadIdx.x * 8; i < hi; i += 256 * 8) {  // span % 8 == 0
+    float f[8];
+    unpack8f(__ldg(reinterpret_cast<const uint4*>(base + i)), f);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      s += f[j];
+      ss = fmaf(f[j], f[j], ss);
+    }
+  }
+  // fixed-order block reduction in double
+  __shared__ double red[2][8];
+  double ds = s, dss = ss;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    ds += __shfl_xor_sync(0xffffffffu, ds, o);
+    dss += __shfl_xor_sync(0xffffffffu, dss, o);
+  }
+  if ((threadIdx.x & 31) == 0) {
+    red[0][threadIdx.x >> 5] = ds;
+    red[1][threadIdx.x >> 5] = dss;
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    double a = 0.0, b = 0.0;
+    for (int w = 0; w < 8; ++w) {
+      a += red[0][w];
+      b += red[1][w];
+    }
+    partial[blockIdx.x] = make_double2(a, b);
+  }
+}
+
+// y[n, s, c] = (x[n, c, s] - mean[n, g(c)]) * rstd[n, g(c)] * gamma[c] + beta[c]
+__global__ void __launch_bounds__(256)
+groupnorm_tokens_kernel(const tvi_bf16* __restrict__ x, const double2* __restrict__ partial, const tvi_bf16* __restrict__ gamma,
+                        const tvi_bf16* __restrict__ beta, tvi_bf16* __restrict__ y, int C, int HW, int groups, int nsplit,
+                        int64_t ldy, float eps) {
+  __shared__ __align__(16) __nv_bfloat16 tile[kTile][kPitch];  // [spatial][channel]
+  __shared__ float s_scale[kTile], s_shift[kTile];
+  const int n = blockIdx.z;
+  const int c0 = blockIdx.y * kTile, s0 = blockIdx.x * kTile;
+  const int cpg = C / groups;
+  if (threadIdx.x < kTile) {
+    const int c = c0 + threadIdx.x;
+    float sc = 0.f, sh = 0.f;
+    if (c < C) {
+      const int g = c / cpg;
+      const double2* pp = partial + ((int64_t)n * groups + g) * nsplit;
+      double a = 0.0, b = 0.0;
+      for (int i = 0; i < nsplit; ++i) {
+        a += pp[i].x;
+        b += pp[i].y;
+      }
+      const double cnt = (double)cpg * HW;
+      const double mean = a / cnt;
+      double var = b / cnt - mean * mean;
+      if (var < 0.0) var = 0.0;
+      const float rstd = (float)(1.0 / sqrt(var + (double)eps));
+      const float ga = gamma ? __bfloat162float(*reinterpret_cast<const __nv_bfloat16*>(gamma + c)) : 1.f;
+      const float be = beta ? __bfloat162float(*reinterpret_cast<const __nv_bfloat16*>(beta + c)) : 0.f;
+      sc = rstd * ga;
+      sh = be - (float)mean * sc;
+    }
+    s_scale[threadIdx.x] = sc;
+    s_shift[threadIdx.x] = sh;
+  }
+  __syncthreads();
+  const int chunk = threadIdx.x & 7;
+#pragma unroll
+  for (int j = 0; j < 2; ++j) {
+    const int cl = (threadIdx.x >> 3) + 32 * j;
+    const int c = c0 + cl, s = s0 + chunk * 8;
+    if (c < C && s < HW) {  // HW % 8 == 0
+      float f[8];
+      unpack8f(__ldg(reinterpret_cast<const uint4*>(x + ((int64_t)n * C + c) * HW + s)), f);
+      const float sc = s_scale[cl], sh = s_shift[cl];
+#pragma unroll
+      for (int i = 0; i < 8; ++i) tile[chunk * 8 + i][cl] = __float2bfloat16_rn(fmaf(f[i], sc, sh));
+    }
+  }
+  __syncthreads();
+#pragma unroll
+  for (int j = 0; j < 2; ++j) {
+    const int sl = (threadIdx.x >> 3) + 32 * j;
+    const int s = s0 + sl, c = c0 + chunk * 8;
+    if (s < HW && c < C)  // C % 8 == 0
+      *reinterpret_cast<uint4*>(y + ((int64_t)n * HW + s) * ldy + c) = *reinterpret_cast<const uint4*>(&tile[sl][chunk * 8]);
+  }
+}
+
+// out[n, c, s] = y[n, s, c] + residual[n, c, s]
+__global__ void __launch_bounds__(256)
+tokens_to_nchw_add_kernel(const tvi_bf16* __restrict__ y, const tvi_bf16* __restrict__ residual, tvi_bf16* __restrict__ out,
+                          int C, int HW, int64_t ldy) {
+  __shared__ __align__(16) __nv_bfloat16 tile[kTile][kPitch];  // [channel][spatial]
+  const int n = blockIdx.z;
+  const int c0 = blockIdx.y * kTile, s0 = blockIdx.x * kTile;
+  const int chunk = threadIdx.x & 7;
+#pragma unroll
+  for (int j = 0; j < 2; ++j) {
+    const int sl = (threadIdx.x >> 3) + 32 * j;
+    const int s = s0 + sl, c = c0 + chunk * 8;
+    if (s < HW && c < C) {
+      const uint4 u = __ldg(reinterpret_cast<const uint4*>(y + ((int64_t)n * HW + s) * ldy + c));
+      const __nv_bfloat16* h = reinterpret_cast<const __nv_bfloat16*>(&u);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) tile[chunk * 8 + i][sl] = h[i];
+    }
+  }
+  __syncthreads();
+#pragma unroll
+  for (int j = 0; j < 2; ++j) {
+    const int cl = (threadIdx.x >> 3) + 32 * j;
+    const int c = c0 + cl, s = s0 + chunk * 8;
+    if (c < C && s < HW) {
+      const int64_t off = ((int64_t)n * C + c) * HW + s;
+      float a[8], b[8];
+      unpack8f(*reinterpret_cast<const uint4*>(&tile[cl][chunk * 8]), a);
+      if (residual != nullptr) {
+        unpack8f(__ldg(reinterpret_cast<const uint4*>(residual + off)), b);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) a[i] += b[i];
+      }
+      *reinterpret_cast<uint4*>(out + off) =
+          make_uint4(pack_bf16x2(a[0], a[1]), pack_bf16x2(a[2], a[3]), pack_bf16x2(a[4], a[5]), pack_bf16x2(a[6], a[7]));
+    }
+  }
+}
+
+// out[r, :] = alpha[r / rows_per_group] * xs[r, :] + (1 - alpha[...]) * xt[r, :]
+__global__ void __launch_bounds__(256)
+blend_rows_kernel(const tvi_bf16* __restrict__ xs, const tvi_bf16* __restrict__ xt, const float* __restrict__ alpha,
+                  tvi_bf16* __restrict__ out, int64_t nrows, int64_t rows_per_group, int C8, int64_t lds, int64_t ldt, int64_t ldo) {
+  const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= nrows * C8) return;
+  const int64_t r = idx / C8;
+  const int c = (int)(idx - r * C8);
+  const float a = __ldg(alpha + r / rows_per_group);
+  const uint4 us = __ldg(reinterpret_cast<const uint4*>(xs + r * lds) + c);
+  if (a == 1.0f) {  // image-only frames take the spatial branch untouched (also when x_temporal is not finite)
+    *(reinterpret_cast<uint4*>(out + r * ldo) + c) = us;
+    return;
+  }
+  float fs[8], ft[8];
+  unpack8f(us, fs);
+  unpack8f(__ldg(reinterpret_cast<const uint4*>(xt + r * ldt) + c), ft);
+  const float b = 1.0f - a;
+  uint32_t o[4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i)
+    o[i] = pack_bf16x2(fmaf(a, fs[2 * i], b * ft[2 * i]), fmaf(a, fs[2 * i + 1], b * ft[2 * i + 1]));
+  *(reinterpret_cast<uint4*>(out + r * ldo) + c) = make_uint4(o[0], o[1], o[2], o[3]);
+}
+
+int gn_splits(int64_t span) { return (int)((span + kGnSlice - 1) / kGnSlice); }
+
+}  // namespace
+}  // namespace tvi
+
+extern "C" size_t tvi_groupnorm_tokens_workspace_bytes(int64_t N, int C, int HW, int groups) {
+  if (N <= 0 || C <= 0 || HW <= 0 || groups <= 0 || C % groups != 0) return 0;
+  return (size_t)N * groups * tvi::gn_splits((int64_t)(C / groups) * HW) * sizeof(double2);
+}
+
+extern "C" int tvi_groupnorm_tokens_bf16(const tvi_bf16* x, const tvi_bf16* gamma, const tvi_bf16* beta, tvi_bf16* y,
+                                         void* workspace, int64_t N, int C, int HW, int groups, int64_t ldy, float eps,
+                                         void* stream) {
+  using namespace tvi;
+  TVI_CHECK_ARG(N >= 0 && C >= 0 && HW >= 0, "tvi_groupnorm_tokens_bf16: negative size");
+  if (N == 0 || C == 0 || HW == 0) return TVI_OK;
+  TVI_CHECK_ARG(x && y && workspace, "tvi_groupnorm_tokens_bf16: null pointer");
+  TVI_CHECK_ARG(groups >= 1 && C % groups == 0, "tvi_groupnorm_tokens_bf16: C=%d is not a multiple of groups=%d", C, groups);
+  TVI_CHECK_ARG(C % 8 == 0 && HW % 8 == 0, "tvi_groupnorm_tokens_bf16: C=%d and H*W=%d must be multiples of 8", C, HW);
+  TVI_CHECK_ARG(ldy % 8 == 0 && ldy >= C, "tvi_groupnorm_tokens_bf16: bad output row stride");
+  TVI_CHECK_ARG(((uintptr_t)x | (uintptr_t)y | (uintptr_t)workspace) % 16 == 0, "tvi_groupnorm_tokens_bf16: pointers must be 16-byte aligned");
+  TVI_CHECK_ARG(eps > 0.f, "tvi_groupnorm_tokens_bf16: eps must be positive");
+  TVI_CHECK_ARG(N <= 65535, "tvi_groupnorm_tokens_bf16: more than 65535 images in one call");
+  const int64_t span = (int64_t)(C / groups) * HW;
+  const int nsplit = gn_splits(span);
+  TVI_CHECK_ARG(N * groups * nsplit < ((int64_t)1 << 31), "tvi_groupnorm_tokens_bf16: grid too large");
+  cudaStream_t st = (cudaStream_t)stream;
+  groupnorm_stats_kernel<<<(unsigned)(N * groups * nsplit), 256, 0, st>>>(x, (double2*)workspace, span, nsplit);
+  TVI_LAUNCH_OK("groupnorm_stats_kernel");
+  dim3 grid((HW + kTile - 1) / kTile, (C + kTile - 1) / kTile, (unsigned)N);
+  groupnorm_tokens_kernel<<<grid, 256, 0, st>>>(x, (const double2*)workspace, gamma, beta, y, C, HW, groups, nsplit, ldy, eps);
+  TVI_LAUNCH_OK("groupnorm_tokens_kernel");
+  return TVI_OK;
+}
+
+extern "C" int tvi_tokens_to_nchw_add_bf16(const tvi_bf16* y, const tvi_bf16* residual, tvi_bf16* out, int64_t N, int C, int HW,
+                                           int64_t ldy, void* stream) {
+  using namespace tvi;
+  TVI_CHECK_ARG(N >= 0 && C >= 0 && HW >= 0, "tvi_tokens_to_nchw_add_bf16: negative size");
+  if (N == 0 || C == 0 || HW == 0) return TVI_OK;
+  TVI_CHECK_ARG(y && out, "tvi_tokens_to_nchw_add_bf16: null pointer");
+  TVI_CHECK_ARG(C % 8 == 0 && HW % 8 == 0, "tvi_tokens_to_nchw_add_bf16: C=%d and H*W=%d must be multiples of 8", C, HW);
+  TVI_CHECK_ARG(ldy % 8 == 0 && ldy >= C, "tvi_tokens_to_nchw_add_bf16: bad row stride");
+  TVI_CHECK_ARG(((uintptr_t)y | (uintptr_t)residual | (uintptr_t)out) % 16 == 0, "tvi_tokens_to_nchw_add_bf16: pointers must be 16-byte aligned");
+  TVI_CHECK_ARG(N <= 65535, "tvi_tokens_to_nchw_add_bf16: more than 65535 images in one call");
+  dim3 grid((HW + kTile - 1) / kTile, (C + kTile - 1) / kTile, (unsigned)N);
+  tokens_to_nchw_add_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(y, residual, out, C, HW, ldy);
+  TVI_LAUNCH_OK("tokens_to_nchw_add_kernel");
+  return TVI_OK;
+}
+
+extern "C" int tvi_blend_rows_bf16(const tvi_bf16* x_spatial, const tvi_bf16* x_temporal, const float* alpha, tvi_bf16* out,
+                                   int64_t nrows, int64_t rows_per_group, int C, int64_t lds, int64_t ldt, int64_t ldo,
+                                   void* stream) {
+  using namespace tvi;
+  TVI_CHECK_ARG(nrows >= 0 && C >= 0, "tvi_blend_rows_bf16: negative size");
+  if (nrows == 0 || C == 0) return TVI_OK;
+  TVI_CHECK_ARG(x_spatial && x_temporal && alpha && out, "tvi_blend_rows_bf16: null pointer");
+  TVI_CHECK_ARG(rows_per_group >= 1 && nrows % rows_per_group == 0, "tvi_blend_rows_bf16: nrows must be a multiple of rows_per_group");
+  TVI_CHECK_ARG(C % 8 == 0 && lds % 8 == 0 && ldt % 8 == 0 && ldo % 8 == 0 && lds >= C && ldt >= C && ldo >= C,
+                "tvi_blend_rows_bf16: C and the row strides must be multiples of 8");
+  TVI_CHECK_ARG(((uintptr_t)x_spatial | (uintptr_t)x_temporal | (uintptr_t)out) % 16 == 0 && (uintptr_t)alpha % 4 == 0,
+                "tvi_blend_rows_bf16: pointers must be 16-byte aligned");
+  const int64_t total = nrows * (C / 8);
+  TVI_CHECK_ARG((total + 255) / 256 < ((int64_t)1 << 31), "tvi_blend_rows_bf16: grid too large");
+  blend_rows_kernel<<<(unsigned)((total + 255) / 256), 256, 0, (cudaStream_t)stream>>>(x_spatial, x_temporal, alpha, out, nrows,
+                                                                                       rows_per_group, C / 8, lds, ldt, ldo);
+  TVI_LAUNCH_OK("blend_rows_kernel");
+  return TVI_OK;
+}

@@ -124,3 +124,98 @@ class TemporalBasicTransformerBlock(nn.Module):
         self.attn2 = Attention(time_mix_inner_dim, cross_attention_dim, heads=heads, processor=processor)
         self.norm3 = nn.LayerNorm(time_mix_inner_dim)
         self.ff = FeedForward(time_mix_inner_dim)
+
+
+class Timesteps(nn.Module):
+    """Sinusoidal frame-position embedding (upstream diffusers 0.24 `models/embeddings.py:Timesteps` /
+    `get_timestep_embedding`, not vendored by the reference): exponent_i = -ln(10000) * i / (half - shift),
+    emb = t * exp(exponent), [sin | cos] swapped to [cos | sin] when `flip_sin_to_cos`."""
+
+    def __init__(self, num_channels: int, flip_sin_to_cos: bool, downscale_freq_shift: float):
+        super().__init__()
+        self.num_channels, self.flip_sin_to_cos, self.downscale_freq_shift = num_channels, flip_sin_to_cos, downscale_freq_shift
+
+    def forward(self, timesteps):
+        import math
+        half = self.num_channels // 2
+        exponent = -math.log(10000) * torch.arange(half, dtype=torch.float32, device=timesteps.device) / (half - self.downscale_freq_shift)
+        emb = timesteps[:, None].float() * torch.exp(exponent)[None, :]
+        emb = torch.cat([torch.sin(emb), torch.cos(emb)], dim=-1)
+        if self.flip_sin_to_cos:
+            emb = torch.cat([emb[:, half:], emb[:, :half]], dim=-1)
+        if self.num_channels % 2 == 1:
+            emb = torch.nn.functional.pad(emb, (0, 1, 0, 0))
+        return emb
+
+
+class TimestepEmbedding(nn.Module):
+    """linear_1 -> SiLU -> linear_2 (upstream diffusers 0.24 `models/embeddings.py:TimestepEmbedding`)."""
+
+    def __init__(self, in_channels: int, time_embed_dim: int, out_dim: Optional[int] = None):
+        super().__init__()
+        self.linear_1 = nn.Linear(in_channels, time_embed_dim)
+        self.act = nn.SiLU()
+        self.linear_2 = nn.Linear(time_embed_dim, out_dim if out_dim is not None else time_embed_dim)
+
+    def forward(self, sample):
+        return self.linear_2(self.act(self.linear_1(sample)))
+
+
+class AlphaBlender(nn.Module):
+    """upstream diffusers 0.24 `models/resnet.py:AlphaBlender`, `merge_strategy="learned_with_images"` (the one
+    TransformerSpatioTemporalModel builds, src/models/transformer_temporal.py:243): alpha = 1 where
+    image_only_indicator, sigmoid(mix_factor) elsewhere; out = alpha * x_spatial + (1 - alpha) * x_temporal."""
+
+    def __init__(self, alpha: float, merge_strategy: str = "learned_with_images", switch_spatial_to_temporal_mix: bool = False):
+        super().__init__()
+        self.merge_strategy = merge_strategy
+        self.switch_spatial_to_temporal_mix = switch_spatial_to_temporal_mix
+        if merge_strategy == "fixed":
+            self.register_buffer("mix_factor", torch.Tensor([alpha]))
+        else:
+            self.register_parameter("mix_factor", nn.Parameter(torch.Tensor([alpha])))
+
+    def get_alpha(self, image_only_indicator, ndims: int):
+        if self.merge_strategy == "fixed":
+            alpha = self.mix_factor
+        elif self.merge_strategy == "learned":
+            alpha = torch.sigmoid(self.mix_factor)
+        else:
+            alpha = torch.where(image_only_indicator.bool(), torch.ones(1, 1, device=image_only_indicator.device),
+                                torch.sigmoid(self.mix_factor)[..., None])
+            alpha = alpha.reshape(-1)[:, None, None] if ndims == 3 else alpha[:, None, :, None, None]
+        return alpha
+
+    def forward(self, x_spatial, x_temporal, image_only_indicator=None):
+        alpha = self.get_alpha(image_only_indicator, x_spatial.ndim).to(x_spatial.dtype)
+        if self.switch_spatial_to_temporal_mix:
+            alpha = 1.0 - alpha
+        return alpha * x_spatial + (1.0 - alpha) * x_temporal
+
+
+class TransformerSpatioTemporalModel(nn.Module):
+    """Attribute layout and state_dict keys of the reference module (src/models/transformer_temporal.py:207-251)."""
+
+    def __init__(self, num_attention_heads: int = 16, attention_head_dim: int = 88, in_channels: int = 320,
+                 out_channels: Optional[int] = None, num_layers: int = 1, cross_attention_dim: Optional[int] = None):
+        super().__init__()
+        if attention_head_dim != 64:
+            raise ValueError("the mirror builds d = 64 heads (every SVD level)")
+        inner_dim = num_attention_heads * attention_head_dim
+        self.num_attention_heads, self.attention_head_dim = num_attention_heads, attention_head_dim
+        self.inner_dim, self.in_channels = inner_dim, in_channels
+        self.norm = nn.GroupNorm(num_groups=32, num_channels=in_channels, eps=1e-6)
+        self.proj_in = nn.Linear(in_channels, inner_dim)
+        self.transformer_blocks = nn.ModuleList(
+            [BasicTransformerBlock(inner_dim, num_attention_heads, cross_attention_dim) for _ in range(num_layers)])
+        self.temporal_transformer_blocks = nn.ModuleList(
+            [TemporalBasicTransformerBlock(inner_dim, inner_dim, num_attention_heads, cross_attention_dim) for _ in range(num_layers)])
+        self.time_pos_embed = TimestepEmbedding(in_channels, in_channels * 4, out_dim=in_channels)
+        self.time_proj = Timesteps(in_channels, True, 0)
+        self.time_mixer = AlphaBlender(alpha=0.5, merge_strategy="learned_with_images")
+        self.out_channels = in_channels if out_channels is None else out_channels
+        self.proj_out = nn.Linear(inner_dim, in_channels)
+        self.gradient_checkpointing = False
+
+    def forward(self, hidden_states, encoder_hidden_states=None, image_only_indicator=None, return_dict: bool = True):
+        raise RuntimeError("parameter container: call spatio_temporal.install_spatio_temporal(model) to bind the libtvi forward")

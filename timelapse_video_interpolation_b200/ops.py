@@ -155,6 +155,61 @@ def bcast_rows_add(v: torch.Tensor, residual: torch.Tensor | None, rows_per_grou
     return out
 
 
+def groupnorm_tokens(x: torch.Tensor, gamma, beta, groups: int, eps: float, out: torch.Tensor | None = None) -> torch.Tensor:
+    """GroupNorm of an NCHW bf16 feature map written token-major: [N, C, H, W] -> [N, H*W, C]."""
+    _need_cuda(x, gamma, beta)
+    if x.dim() != 4 or x.dtype != torch.bfloat16 or not x.is_contiguous():
+        raise _lib.TviError(_lib.TVI_ERR_INVALID, "groupnorm_tokens: x must be a contiguous bf16 [N, C, H, W] tensor")
+    N, C, H, W = x.shape
+    for t in (gamma, beta):
+        if t is not None and (t.dtype != torch.bfloat16 or not t.is_contiguous() or t.numel() != C):
+            raise _lib.TviError(_lib.TVI_ERR_INVALID, "groupnorm_tokens: gamma / beta must be contiguous bf16 vectors of length C")
+    if out is None:
+        out = torch.empty(N, H * W, C, dtype=torch.bfloat16, device=x.device)
+    o2, ldy = _rows2d(out, "out")
+    ws = _workspace(_lib.load().tvi_groupnorm_tokens_workspace_bytes(N, C, H * W, int(groups)), x.device)
+    _hooked("groupnorm_tokens", 2, _lib.load().tvi_groupnorm_tokens_bf16, x.data_ptr(),
+            gamma.data_ptr() if gamma is not None else None, beta.data_ptr() if beta is not None else None, o2.data_ptr(),
+            ws.data_ptr() if ws is not None else None, N, C, H * W, int(groups), ldy, float(eps), _stream())
+    return out
+
+
+def tokens_to_nchw_add(y: torch.Tensor, residual: torch.Tensor | None, H: int, W: int, out: torch.Tensor | None = None) -> torch.Tensor:
+    """[N, H*W, C] token-major -> NCHW [N, C, H, W] (+ residual of that shape)."""
+    _need_cuda(y, residual)
+    if y.dim() != 3 or y.shape[1] != H * W:
+        raise _lib.TviError(_lib.TVI_ERR_INVALID, "tokens_to_nchw_add: y must be [N, H*W, C]")
+    N, HW, C = y.shape
+    y2, ldy = _rows2d(y, "y")
+    if residual is not None and (residual.shape != (N, C, H, W) or residual.dtype != torch.bfloat16 or not residual.is_contiguous()):
+        raise _lib.TviError(_lib.TVI_ERR_INVALID, "tokens_to_nchw_add: residual must be a contiguous bf16 [N, C, H, W] tensor")
+    if out is None:
+        out = torch.empty(N, C, H, W, dtype=torch.bfloat16, device=y.device)
+    _hooked("tokens_to_nchw_add", 1, _lib.load().tvi_tokens_to_nchw_add_bf16, y2.data_ptr(),
+            residual.data_ptr() if residual is not None else None, out.data_ptr(), N, C, HW, ldy, _stream())
+    return out
+
+
+def blend_rows(x_spatial: torch.Tensor, x_temporal: torch.Tensor, alpha: torch.Tensor, rows_per_group: int,
+               out: torch.Tensor | None = None) -> torch.Tensor:
+    """out[r] = alpha[r // rows_per_group] * x_spatial[r] + (1 - alpha[...]) * x_temporal[r]; alpha fp32."""
+    _need_cuda(x_spatial, x_temporal, alpha)
+    xs, lds = _rows2d(x_spatial, "x_spatial")
+    xt, ldt = _rows2d(x_temporal, "x_temporal")
+    C = xs.shape[-1]
+    nrows = xs.numel() // C if C else 0
+    if xt.shape != xs.shape:
+        raise _lib.TviError(_lib.TVI_ERR_INVALID, "blend_rows: x_spatial and x_temporal differ in shape")
+    if alpha.dtype != torch.float32 or not alpha.is_contiguous() or alpha.numel() * int(rows_per_group) != nrows:
+        raise _lib.TviError(_lib.TVI_ERR_INVALID, "blend_rows: alpha must be a contiguous fp32 vector with one entry per row group")
+    if out is None:
+        out = torch.empty(x_spatial.shape, dtype=torch.bfloat16, device=xs.device)
+    o2, ldo = _rows2d(out, "out")
+    _hooked("blend_rows", 1, _lib.load().tvi_blend_rows_bf16, xs.data_ptr(), xt.data_ptr(), alpha.data_ptr(), o2.data_ptr(), nrows,
+            int(rows_per_group), C, lds, ldt, ldo, _stream())
+    return out
+
+
 def gemm_bf16_dgrad(dy: torch.Tensor, w: torch.Tensor, out: torch.Tensor | None = None) -> torch.Tensor:
     """dx[..., K] = dy[..., N] @ w[N, K] — input gradient of nn.Linear; w is consumed in place."""
     _need_cuda(dy, w)

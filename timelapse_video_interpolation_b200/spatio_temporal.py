@@ -1,0 +1,153 @@
+"""`TransformerSpatioTemporalModel.forward` on libtvi (reference src/models/transformer_temporal.py:253-360, the module
+the author marks "Most Important Block"; SURVEY.md §8.6 rows N1 "AlphaBlender" and N2 "layout glue").
+
+Same signature, same results; what changes is where the bytes go:
+  * `self.norm` + `permute(0, 2, 3, 1).reshape` (:300-304)  -> one GroupNorm kernel pair that writes token-major
+  * `proj_in` / `proj_out` (:306, :353)                      -> the tcgen05 GEMM
+  * `time_proj` + `time_pos_embed` (:308-315)                -> input-independent (frame index only): computed once per
+                                                               (weights, B, T) in fp32 and cached
+  * `hidden_states + emb` (:333)                             -> row-broadcast add kernel
+  * the two blocks (:329-347)                                -> blocks.py forwards (the temporal one without permutes)
+  * `time_mixer` (:349-351)                                  -> blend kernel, one fp32 alpha per frame
+  * `reshape.permute(0, 3, 1, 2).contiguous() + residual`    -> one transpose-add kernel
+Inference only (see blocks.py); `install_spatio_temporal(model)` rebinds every module with this attribute layout.
+"""
+from __future__ import annotations
+
+import sys
+import types
+from dataclasses import dataclass
+from typing import Optional
+
+import torch
+
+from . import _lib, ops
+from .blocks import (_no_grad_only, basic_transformer_block_forward, install_blocks,
+                     temporal_basic_transformer_block_forward)
+from .feedforward import _bf16 as _bf16_param
+
+__all__ = ["transformer_spatio_temporal_forward", "install_spatio_temporal", "uninstall_spatio_temporal"]
+
+
+@dataclass
+class TransformerTemporalModelOutput:
+    """Stand-in for the reference's output dataclass (:28-38) when its module is not importable."""
+    sample: torch.Tensor
+
+
+def _frame_embedding(model, batch_size: int, num_frames: int, device) -> torch.Tensor:
+    """emb[b*T + t] = time_pos_embed(time_proj(t)) (:308-315): depends on the frame index and the weights only."""
+    tp = model.time_pos_embed
+    ws = (tp.linear_1.weight, tp.linear_1.bias, tp.linear_2.weight, tp.linear_2.bias)
+    sig = (batch_size, num_frames, str(device)) + tuple((w.data_ptr(), w._version) for w in ws)
+    hit = getattr(model, "_tvi_frame_emb", None)
+    if hit is not None and hit[0] == sig:
+        return hit[1]
+    with torch.no_grad():
+        idx = torch.arange(num_frames, device=device).repeat(batch_size, 1).reshape(-1)
+        t_emb = model.time_proj(idx).to(torch.bfloat16)          # the reference casts to hidden_states.dtype (:313)
+        emb = tp(t_emb.to(tp.linear_1.weight.dtype)).to(torch.bfloat16).contiguous()
+    model._tvi_frame_emb = (sig, emb)
+    return emb
+
+
+def _alpha(mixer, image_only_indicator: torch.Tensor) -> torch.Tensor:
+    """One fp32 alpha per frame: AlphaBlender.get_alpha for ndims == 3, with the reference's cast to the activation
+    dtype (`.to(x_spatial.dtype)`) applied so that the blend weights are the bf16-rounded ones."""
+    strategy = getattr(mixer, "merge_strategy", "learned_with_images")
+    ind = image_only_indicator.reshape(-1)
+    mf = mixer.mix_factor.detach().float().reshape(-1)[:1]
+    if strategy == "fixed":
+        a = mf.expand(ind.numel())
+    elif strategy == "learned":
+        a = torch.sigmoid(mf).expand(ind.numel())
+    elif strategy == "learned_with_images":
+        a = torch.where(ind.bool(), torch.ones(1, device=ind.device), torch.sigmoid(mf).to(ind.device))
+    else:
+        raise _lib.TviError(_lib.TVI_ERR_UNSUPPORTED, f"AlphaBlender merge_strategy {strategy!r}")
+    a = a.to(torch.bfloat16).float()
+    if getattr(mixer, "switch_spatial_to_temporal_mix", False):
+        a = 1.0 - a
+    return a.contiguous()
+
+
+def transformer_spatio_temporal_forward(model, hidden_states: torch.Tensor, encoder_hidden_states=None,
+                                        image_only_indicator: Optional[torch.Tensor] = None, return_dict: bool = True):
+    """Same signature as TransformerSpatioTemporalModel.forward (:253-259)."""
+    if hidden_states.dim() != 4:
+        raise _lib.TviError(_lib.TVI_ERR_INVALID, "hidden_states must be [batch*frames, channels, height, width]")
+    if image_only_indicator is None:
+        raise _lib.TviError(_lib.TVI_ERR_INVALID, "image_only_indicator [batch, frames] is required (it carries num_frames)")
+    if not hidden_states.is_cuda:
+        raise _lib.TviError(_lib.TVI_ERR_INVALID, "hidden_states is not on a CUDA device (there is no CPU fallback)")
+    if hidden_states.dtype != torch.bfloat16:
+        raise _lib.TviError(_lib.TVI_ERR_UNSUPPORTED, f"hidden_states is {hidden_states.dtype}; the libtvi path is bf16")
+    _no_grad_only(model, hidden_states)
+    BF, C, H, W = hidden_states.shape
+    T = image_only_indicator.shape[-1]
+    B = BF // T
+    S = H * W
+    if B * T != BF:
+        raise _lib.TviError(_lib.TVI_ERR_INVALID, "batch*frames is not a multiple of image_only_indicator.shape[-1]")
+    if isinstance(encoder_hidden_states, tuple):                                     # :274-279
+        spatial_ctx, temporal_ctx = encoder_hidden_states
+    else:
+        spatial_ctx = temporal_ctx = encoder_hidden_states
+    # :281-296 — the first frame's context of every clip, broadcast over the H*W positions ([hw, batch] major, as written)
+    tc = temporal_ctx[None, :].reshape(B, T, -1, temporal_ctx.shape[-1])[:, 0]
+    time_context = tc[None, :].broadcast_to(S, B, tc.shape[-2], tc.shape[-1]).reshape(S * B, tc.shape[-2], tc.shape[-1])
+
+    residual = hidden_states.contiguous()
+    norm = model.norm
+    x = ops.groupnorm_tokens(residual, _bf16_param(norm.weight), _bf16_param(norm.bias), int(norm.num_groups), float(norm.eps))
+    x = ops.gemm_bf16_tn(x, _bf16_param(model.proj_in.weight), _bf16_param(model.proj_in.bias))   # [BF, S, inner]
+    emb = _frame_embedding(model, B, T, hidden_states.device)                                     # [BF, C]
+    if emb.shape[-1] != x.shape[-1]:
+        raise _lib.TviError(_lib.TVI_ERR_UNSUPPORTED, "in_channels != inner_dim: the frame embedding cannot be added (:333)")
+    alpha = _alpha(model.time_mixer, image_only_indicator.to(hidden_states.device))
+    for block, temporal_block in zip(model.transformer_blocks, model.temporal_transformer_blocks):
+        x = basic_transformer_block_forward(block, x, encoder_hidden_states=spatial_ctx)           # :337-339
+        x_mix = ops.bcast_rows_add(emb, x, S)                                                     # :341-342
+        x_mix = temporal_basic_transformer_block_forward(temporal_block, x_mix.view(BF, S, -1), num_frames=T,
+                                                         encoder_hidden_states=time_context)      # :343-347
+        x = ops.blend_rows(x, x_mix, alpha, S)                                                    # :349-351
+    y = ops.gemm_bf16_tn(x, _bf16_param(model.proj_out.weight), _bf16_param(model.proj_out.bias))  # :353
+    out = ops.tokens_to_nchw_add(y.view(BF, S, -1), residual, H, W)                               # :354-357
+    if not return_dict:
+        return (out,)
+    mod = sys.modules.get(type(model).__module__)
+    cls = getattr(mod, "TransformerTemporalModelOutput", None) or TransformerTemporalModelOutput
+    return cls(sample=out)
+
+
+def _is_spatio_temporal(m) -> bool:
+    return all(hasattr(m, a) for a in ("norm", "proj_in", "transformer_blocks", "temporal_transformer_blocks", "time_pos_embed",
+                                       "time_proj", "time_mixer", "proj_out"))
+
+
+def install_spatio_temporal(model: torch.nn.Module, processor=None) -> int:
+    """Rebinds `forward` of every TransformerSpatioTemporalModel-shaped module (and of its blocks); returns how many."""
+    n = 0
+    for _, m in model.named_modules():
+        if _is_spatio_temporal(m):
+            install_blocks(m, processor)
+            if not hasattr(m, "_tvi_saved_model_forward"):
+                m._tvi_saved_model_forward = m.__dict__.get("forward")
+            m.forward = types.MethodType(transformer_spatio_temporal_forward, m)
+            n += 1
+    return n
+
+
+def uninstall_spatio_temporal(model: torch.nn.Module) -> int:
+    from .blocks import uninstall_blocks
+    n = 0
+    for _, m in model.named_modules():
+        if hasattr(m, "_tvi_saved_model_forward"):
+            if m._tvi_saved_model_forward is None:
+                m.__dict__.pop("forward", None)
+            else:
+                m.forward = m._tvi_saved_model_forward
+            del m._tvi_saved_model_forward
+            uninstall_blocks(m)
+            n += 1
+    return n

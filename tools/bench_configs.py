@@ -270,14 +270,53 @@ def cfg_block(steps):
           "note": "temporal block runs in the spatial token order (N2 fold): no permute copies"})
 
 
+def cfg_model(steps):
+    """The whole L0 TransformerSpatioTemporalModel.forward (GroupNorm -> proj_in -> spatial block -> +frame embedding ->
+    temporal block -> AlphaBlender -> proj_out -> NCHW + residual) at the bench shape, NCHW in, NCHW out."""
+    from timelapse_video_interpolation_b200 import spatio_temporal
+    from timelapse_video_interpolation_b200.modules import TransformerSpatioTemporalModel
+    C, heads, h, w = bench.LEVELS["L0"]
+    T, B = 14, 2
+    g = torch.Generator().manual_seed(5)
+    m = TransformerSpatioTemporalModel(heads, 64, in_channels=C, num_layers=1, cross_attention_dim=1024)
+    with torch.no_grad():
+        for name, p in m.named_parameters():
+            if name.endswith("mix_factor"):
+                p.fill_(0.0)
+            elif "norm" in name:
+                p.fill_(1.0 if name.endswith("weight") else 0.0)
+            else:
+                p.copy_((torch.rand(p.shape, generator=g) * 2 - 1) * (p.shape[-1] ** -0.5 if p.dim() > 1 else C ** -0.5))
+    m = m.to(DEV, torch.bfloat16).eval()
+    spatio_temporal.install_spatio_temporal(m)
+    x = torch.randn(B * T, C, h, w, generator=g).to(torch.bfloat16).to(DEV)
+    e = torch.randn(B * T, 1, 1024, generator=g).to(torch.bfloat16).to(DEV)
+    ind = torch.zeros(B, T, device=DEV)
+
+    def step():
+        return m(x, encoder_hidden_states=e, image_only_indicator=ind, return_dict=False)[0]
+
+    with torch.no_grad():
+        ms = timed(step, steps)
+        kt = KernelTimes()
+        ops.EVENT_HOOK = kt.hook
+        for _ in range(3):
+            step()
+        ops.EVENT_HOOK = None
+    N = B * T * h * w
+    fl = bench.algorithmic_flops("L0", 1)["total"] + 3 * (2.0 * N * C * 8 * C + 2.0 * N * 4 * C * C) + 2 * 2.0 * N * C * C
+    emit({"config": "model_L0_TransformerSpatioTemporalModel", "clips": 1, "cfg": 2, "T": T, "ms": ms,
+          "clip_frames_per_s": T / (ms * 1e-3), "tflop": fl / 1e12, "tflops": fl / 1e12 / (ms * 1e-3), "kernels": kt.summary(3)})
+
+
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument("--only", default="slerp,flow,train,loop25,kernels,block")
+    ap.add_argument("--only", default="slerp,flow,train,loop25,kernels,block,model")
     ap.add_argument("--steps", type=int, default=10)
     args = ap.parse_args()
     torch.cuda.set_device(0)
     emit({"config": "env", "device": torch.cuda.get_device_name(0), "libtvi": tvi.version(), "peaks": PK})
-    table = {"slerp": cfg_slerp, "flow": cfg_flow, "train": cfg_train, "loop25": cfg_loop25, "kernels": cfg_kernels, "block": cfg_block}
+    table = {"slerp": cfg_slerp, "flow": cfg_flow, "train": cfg_train, "loop25": cfg_loop25, "kernels": cfg_kernels, "block": cfg_block, "model": cfg_model}
     for name in args.only.split(","):
         table[name.strip()](args.steps)
 
