@@ -6,6 +6,8 @@
 // loads before the first use, so 1.3+ KB per warp are in flight; a row stays in registers between the statistics and
 // the normalisation (C <= 2048: up to 8 chunks of 8 channels per lane); two-pass variance (sum of squared
 // deviations) so that large means do not cancel.
+#include <cstdlib>
+
 #include "tvi_common.cuh"
 
 namespace tvi {
@@ -104,6 +106,121 @@ layernorm_kernel(const tvi_bf16* __restrict__ x, const tvi_bf16* __restrict__ ga
   }
 }
 
+// The three SVD widths (C = 320 / 640 / 1280) as a FLAT chunk array: a warp owns R = 160 / (C / 8) consecutive rows =
+// exactly 160 16-byte chunks = 5 per lane, every lane busy in every iteration (the row-per-warp layout above leaves
+// 24 of 64 lane slots idle at C = 320 and was issue-bound at 3.5 TB/s).  Chunk k = lane + 32 i belongs to row k / C8;
+// per-row sums are formed lane-locally (select by row) and butterfly-reduced for all R rows; packed f32x2 arithmetic.
+template <int R>
+__global__ void __launch_bounds__(kLnWarps * 32)
+layernorm_flat_kernel(const tvi_bf16* __restrict__ x, const tvi_bf16* __restrict__ gamma, const tvi_bf16* __restrict__ beta,
+                      tvi_bf16* __restrict__ y, int64_t M, int64_t ldx, int64_t ldy, float eps) {
+  constexpr int C8 = 160 / R;
+  constexpr int NCH = 5;
+  const int lane = threadIdx.x & 31;
+  const int64_t row0 = ((int64_t)blockIdx.x * kLnWarps + (threadIdx.x >> 5)) * R;
+  if (row0 >= M) return;
+  uint4 raw[NCH];
+  int rw[NCH], col[NCH];
+#pragma unroll
+  for (int i = 0; i < NCH; ++i) {
+    const int k = lane + 32 * i;
+    rw[i] = k / C8;
+    col[i] = k - rw[i] * C8;
+    const int64_t row = row0 + rw[i] < M ? row0 + rw[i] : M - 1;  // tail rows re-read the last row (never stored)
+    raw[i] = __ldg(reinterpret_cast<const uint4*>(x + row * ldx) + col[i]);
+  }
+  uint64_t v[NCH][4];
+  float part[R];
+#pragma unroll
+  for (int r = 0; r < R; ++r) part[r] = 0.f;
+#pragma unroll
+  for (int i = 0; i < NCH; ++i) {
+    const uint32_t w[4] = {raw[i].x, raw[i].y, raw[i].z, raw[i].w};
+    uint64_t acc = f32x2_pack(0.f, 0.f);
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      v[i][q] = f32x2_pack(__uint_as_float(w[q] << 16), __uint_as_float(w[q] & 0xffff0000u));
+      acc = f32x2_add(acc, v[i][q]);
+    }
+    float a0, a1;
+    f32x2_unpack(acc, a0, a1);
+    const float s = a0 + a1;
+#pragma unroll
+    for (int r = 0; r < R; ++r) part[r] += (rw[i] == r) ? s : 0.f;
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+#pragma unroll
+    for (int r = 0; r < R; ++r) part[r] += __shfl_xor_sync(0xffffffffu, part[r], o);
+  }
+  constexpr float inv_c = 1.0f / (float)(C8 * 8);
+  float negmean[NCH];
+#pragma unroll
+  for (int i = 0; i < NCH; ++i) {
+    float m = part[0];
+#pragma unroll
+    for (int r = 1; r < R; ++r) m = (rw[i] == r) ? part[r] : m;
+    negmean[i] = -m * inv_c;
+  }
+#pragma unroll
+  for (int r = 0; r < R; ++r) part[r] = 0.f;
+#pragma unroll
+  for (int i = 0; i < NCH; ++i) {
+    const uint64_t nm = f32x2_pack(negmean[i], negmean[i]);
+    uint64_t acc = f32x2_pack(0.f, 0.f);
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      v[i][q] = f32x2_add(v[i][q], nm);  // deviations
+      acc = f32x2_fma(v[i][q], v[i][q], acc);
+    }
+    float a0, a1;
+    f32x2_unpack(acc, a0, a1);
+    const float s = a0 + a1;
+#pragma unroll
+    for (int r = 0; r < R; ++r) part[r] += (rw[i] == r) ? s : 0.f;
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+#pragma unroll
+    for (int r = 0; r < R; ++r) part[r] += __shfl_xor_sync(0xffffffffu, part[r], o);
+  }
+#pragma unroll
+  for (int r = 0; r < R; ++r) part[r] = rsqrtf(part[r] * inv_c + eps);
+#pragma unroll
+  for (int i = 0; i < NCH; ++i) {
+    float rs = part[0];
+#pragma unroll
+    for (int r = 1; r < R; ++r) rs = (rw[i] == r) ? part[r] : rs;
+    const uint64_t rs2 = f32x2_pack(rs, rs);
+    uint4 ug = make_uint4(0x3f803f80u, 0x3f803f80u, 0x3f803f80u, 0x3f803f80u);  // bf16 1.0 pairs
+    uint4 ub = make_uint4(0u, 0u, 0u, 0u);
+    if (gamma != nullptr) ug = __ldg(reinterpret_cast<const uint4*>(gamma) + col[i]);
+    if (beta != nullptr) ub = __ldg(reinterpret_cast<const uint4*>(beta) + col[i]);
+    const uint32_t wg[4] = {ug.x, ug.y, ug.z, ug.w}, wb[4] = {ub.x, ub.y, ub.z, ub.w};
+    uint32_t o[4];
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const uint64_t g2 = f32x2_pack(__uint_as_float(wg[q] << 16), __uint_as_float(wg[q] & 0xffff0000u));
+      const uint64_t b2 = f32x2_pack(__uint_as_float(wb[q] << 16), __uint_as_float(wb[q] & 0xffff0000u));
+      float lo, hi;
+      f32x2_unpack(f32x2_fma(f32x2_mul(v[i][q], rs2), g2, b2), lo, hi);
+      o[q] = pack_bf16x2(lo, hi);
+    }
+    if (row0 + rw[i] < M) *(reinterpret_cast<uint4*>(y + (row0 + rw[i]) * ldy) + col[i]) = make_uint4(o[0], o[1], o[2], o[3]);
+  }
+}
+
+template <int R>
+int launch_ln_flat(const tvi_bf16* x, const tvi_bf16* gamma, const tvi_bf16* beta, tvi_bf16* y, int64_t M, int64_t ldx, int64_t ldy,
+                   float eps, cudaStream_t st) {
+  const int64_t rows_per_block = (int64_t)kLnWarps * R;
+  const int64_t blocks = (M + rows_per_block - 1) / rows_per_block;
+  TVI_CHECK_ARG(blocks < ((int64_t)1 << 31), "tvi_layernorm_bf16: too many rows for one call");
+  layernorm_flat_kernel<R><<<(unsigned)blocks, kLnWarps * 32, 0, st>>>(x, gamma, beta, y, M, ldx, ldy, eps);
+  TVI_LAUNCH_OK("layernorm_flat_kernel");
+  return TVI_OK;
+}
+
 template <int NCH, int R>
 int launch_ln(const tvi_bf16* x, const tvi_bf16* gamma, const tvi_bf16* beta, tvi_bf16* y, int64_t M, int C8, int64_t ldx,
               int64_t ldy, float eps, cudaStream_t st) {
@@ -131,6 +248,11 @@ extern "C" int tvi_layernorm_bf16(const tvi_bf16* x, const tvi_bf16* gamma, cons
   TVI_CHECK_ARG(eps > 0.f, "tvi_layernorm_bf16: eps must be positive");
   cudaStream_t st = (cudaStream_t)stream;
   const int C8 = C / 8;
+  if (getenv("TVI_LN_GENERIC") == nullptr) {
+    if (C8 == 40) return launch_ln_flat<4>(x, gamma, beta, y, M, ldx, ldy, eps, st);
+    if (C8 == 80) return launch_ln_flat<2>(x, gamma, beta, y, M, ldx, ldy, eps, st);
+    if (C8 == 160) return launch_ln_flat<1>(x, gamma, beta, y, M, ldx, ldy, eps, st);
+  }
   // rows per warp: measured at C = 320, M = 258 048: 1 row 0.106 ms, 2 rows 0.094 ms, 4 rows 0.096 ms
   if (C8 <= 64) return launch_ln<2, 2>(x, gamma, beta, y, M, C8, ldx, ldy, eps, st);
   if (C8 <= 128) return launch_ln<4, 2>(x, gamma, beta, y, M, C8, ldx, ldy, eps, st);
