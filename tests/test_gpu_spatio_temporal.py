@@ -132,3 +132,25 @@ def test_model_forward_refuses_gradients_and_cpu(cuda):
         m(x.requires_grad_(True), encoder_hidden_states=e, image_only_indicator=ind)
     with torch.no_grad(), pytest.raises(_lib.TviError):
         m(x.detach().cpu(), encoder_hidden_states=e, image_only_indicator=ind)
+
+
+def test_graphed_forward_replays_bit_exact(cuda):
+    from timelapse_video_interpolation_b200.graphs import GraphedForward
+    m = _model(320, 5, 1024, 21, cuda)
+    spatio_temporal.install_spatio_temporal(m)
+    g = torch.Generator().manual_seed(1)
+    B, T, H, W = 1, 14, 8, 8
+    mk = lambda: (_bf(torch.randn(B * T, 320, H, W, generator=g), cuda), _bf(torch.randn(B * T, 1, 1024, generator=g), cuda))
+    x0, e0 = mk()
+    ind = torch.zeros(B, T, device=cuda)
+    fwd = GraphedForward(m, x0, encoder_hidden_states=e0, image_only_indicator=ind, return_dict=False)
+    for _ in range(2):  # new inputs: copied into the static buffers, one graph launch
+        x, e = mk()
+        launches0 = ops.LAUNCHES
+        y = fwd(x, encoder_hidden_states=e, image_only_indicator=ind)[0].clone()
+        assert ops.LAUNCHES == launches0  # no Python-side launches on replay
+        with torch.no_grad():
+            want = m(x, encoder_hidden_states=e, image_only_indicator=ind, return_dict=False)[0]
+        assert torch.equal(y, want)
+    with pytest.raises(_lib.TviError):
+        fwd(x[:7], encoder_hidden_states=e, image_only_indicator=ind)

@@ -31,7 +31,7 @@ namespace {
 
 constexpr int kBM = 128;
 constexpr int kBK = 64;
-constexpr int kEpiWarps = 8;                        // two per TMEM lane quadrant, alternating 32-column chunks
+constexpr int kEpiWarps = 8;                        // two per TMEM lane quadrant, alternating 32-column chunks (12: no further gain)
 constexpr int kGemmThreads = 64 + 32 * kEpiWarps;
 constexpr int kAccStride = 256;                    // TMEM columns per accumulator stage
 constexpr int kABytes = kBM * kBK * 2;             // 16 KB
@@ -42,7 +42,8 @@ constexpr int kABytes = kBM * kBK * 2;             // 16 KB
 constexpr int kStageBufs = 1;
 constexpr int kResStageBufs = 4;                   // with a residual: the buffers also receive the residual chunk two chunks ahead
 // warps x bufs x [32 rows][64 B] + warps x 256 fp32 bias
-constexpr int staging_bytes(int bufs) { return kEpiWarps * bufs * 2048 + kEpiWarps * 1024; }
+constexpr int kBiasBytes = 2 * 256 * 4;            // one fp32 bias strip per accumulator stage, shared by the epilogue warps
+constexpr int staging_bytes(int bufs) { return kEpiWarps * bufs * 2048 + kBiasBytes; }
 constexpr int kMaxStages = 8;
 
 // gelu(g) = g * Phi(g), Phi(g) = 0.5 * (1 + erf(g / sqrt 2)) (the erf form F.gelu computes).  Branch-free:
@@ -246,11 +247,12 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
     constexpr int kChunkStep = kEpiWarps / 4;
     const int nbufs = p.stage_bufs;
     uint8_t* my_staging_ptr = staging_ptr + (warp - 2) * nbufs * 2048;
-    float* my_bias = reinterpret_cast<float*>(staging_ptr + kEpiWarps * nbufs * 2048 + (warp - 2) * 1024);
+    float* bias_strips = reinterpret_cast<float*>(staging_ptr + kEpiWarps * nbufs * 2048);
+    const int epi_tid = threadIdx.x - 64;
     int buf = 0;
     // Residual (Y = acc + bias + R): a per-chunk global read after the accumulator wait would expose one DRAM latency
     // per 32 columns (out-projection at K = 320: 0.076 -> 0.180 ms).  Instead lane 0 TMA-loads the [32 x 32] residual
-    // chunk into the chunk's own staging buffer TWO chunks ahead (4 buffers per warp); the thread adds its row in
+    // chunk into the chunk's own staging buffer TWO chunks ahead (4 buffers per warp; one ahead with 3 buffers: 0.125 vs 0.105 ms); the thread adds its row in
     // place and the same buffer goes out through the TMA store.
     const bool has_res = !kSplit && p.residual != nullptr;
     uint64_t* my_res_bar = bar_res[warp - 2];
@@ -273,7 +275,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
       const int64_t mt = ptile / p.n_tiles;
       const int nt = (int)(ptile - mt * p.n_tiles);
       const int n0s = p.geglu ? (nt * p.BN) >> 1 : nt * p.BN;
-      const uint32_t b = pq & (kResStageBufs - 1);
+      const uint32_t b = pq % kResStageBufs;
       mbar_arrive_expect_tx(&my_res_bar[b], 2048);
       tma_load_2d(my_staging_ptr + b * 2048, &tmR, &my_res_bar[b], n0s + pc * 32, (int)(mt * kBM) + quad * 32);
       ++pq;
@@ -292,12 +294,15 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
       const int64_t mt = mn / p.n_tiles;
       const int nt = (int)(mn - mt * p.n_tiles);
       const int m0 = (int)(mt * kBM), n0 = nt * p.BN;
+      const float* my_bias = bias_strips + as * 256;
       if (!kSplit && p.bias != nullptr) {
-        // this tile's bias slice as fp32 in the warp's own shared-memory strip (read back as broadcast LDS.128)
-        __syncwarp();
-        for (int c = lane; c < p.BN; c += 32)
-          my_bias[c] = (n0 + c < p.N) ? __bfloat162float(*reinterpret_cast<const __nv_bfloat16*>(p.bias + n0 + c)) : 0.f;
-        __syncwarp();
+        // This tile's bias slice as fp32 in the strip of accumulator stage `as` (read back as broadcast LDS.128).  One
+        // barrier per tile among the epilogue warps: a warp that passes it knows every warp has finished tile i - 1's
+        // predecessor, so the strip of tile i + 1 (same stage as i - 1) is free once the NEXT barrier is passed.
+        if (epi_tid < p.BN)
+          bias_strips[as * 256 + epi_tid] =
+              (n0 + epi_tid < p.N) ? __bfloat162float(*reinterpret_cast<const __nv_bfloat16*>(p.bias + n0 + epi_tid)) : 0.f;
+        named_bar_sync(1, 32 * kEpiWarps);
       }
       mbar_wait(&bar_acc_full[as], aph);
       tc_fence_after();
@@ -367,7 +372,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
             tma_store_wait_read<1>();
             issue_residual();
           }
-          mbar_wait(&my_res_bar[buf], (qn >> 2) & 1);
+          mbar_wait(&my_res_bar[buf], (qn / kResStageBufs) & 1);
           ++qn;
 #pragma unroll
           for (int ch = 0; ch < 4; ++ch) {
@@ -400,7 +405,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
           tma_store_2d(&tmY, reinterpret_cast<const void*>(my_staging_ptr + buf * 2048), ncol0, m0 + quad * 32);
           tma_store_commit();
         }
-        buf = (buf + 1) & (nbufs - 1);
+        buf = (buf + 1 == nbufs) ? 0 : buf + 1;
       }
       if (++as == 2) {
         as = 0;
@@ -472,7 +477,7 @@ int configure_once() {
   TVI_CUDA_OK(cudaGetDevice(&dev));
   if (dev < 0 || dev >= 64 || !configured[dev]) {
     TVI_CUDA_OK(cudaFuncSetAttribute(gemm_bf16_kernel<kAMn, kBMn, kSplit>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                     227 * 1024 - 512));
+                                     227 * 1024 - 1024));
     if (dev >= 0 && dev < 64) configured[dev] = true;
   }
   return TVI_OK;
@@ -513,7 +518,7 @@ int launch_gemm(const char* name, const tvi_bf16* A, const tvi_bf16* B, const tv
   const int stage_bytes = p.res_b ? kABytes : kABytes + b_bytes;
   p.stage_bufs = (!kSplit && residual != nullptr) ? kResStageBufs : kStageBufs;
   const int kStagingBytes = staging_bytes(p.stage_bufs);
-  const int smem_cap = 227 * 1024 - 1024 /*alignment slack*/ - kStagingBytes - 512 /*static*/ - (p.res_b ? res_bytes : 0);
+  const int smem_cap = 227 * 1024 - 1024 /*alignment slack*/ - kStagingBytes - 1024 /*static*/ - (p.res_b ? res_bytes : 0);
   int stages = smem_cap / stage_bytes;
   if (stages > kMaxStages) stages = kMaxStages;
   TVI_CHECK_ARG(stages >= 2, "%s: tile does not fit shared memory", name);

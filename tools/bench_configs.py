@@ -309,14 +309,62 @@ def cfg_model(steps):
           "clip_frames_per_s": T / (ms * 1e-3), "tflop": fl / 1e12, "tflops": fl / 1e12 / (ms * 1e-3), "kernels": kt.summary(3)})
 
 
+def _st_model(level, T, B, seed=5):
+    from timelapse_video_interpolation_b200 import spatio_temporal
+    from timelapse_video_interpolation_b200.modules import TransformerSpatioTemporalModel
+    C, heads, h, w = bench.LEVELS[level]
+    g = torch.Generator().manual_seed(seed)
+    m = TransformerSpatioTemporalModel(heads, 64, in_channels=C, num_layers=1, cross_attention_dim=1024)
+    with torch.no_grad():
+        for name, p in m.named_parameters():
+            if name.endswith("mix_factor"):
+                p.fill_(0.0)
+            elif "norm" in name:
+                p.fill_(1.0 if name.endswith("weight") else 0.0)
+            else:
+                p.copy_((torch.rand(p.shape, generator=g) * 2 - 1) * (p.shape[-1] ** -0.5 if p.dim() > 1 else C ** -0.5))
+    m = m.to(DEV, torch.bfloat16).eval()
+    spatio_temporal.install_spatio_temporal(m)
+    x = torch.randn(B * T, C, h, w, generator=g).to(torch.bfloat16).to(DEV)
+    e = torch.randn(B * T, 1, 1024, generator=g).to(torch.bfloat16).to(DEV)
+    ind = torch.zeros(B, T, device=DEV)
+    return m, x, e, ind
+
+
+def cfg_levels(steps):
+    """Config 3 shape (T = 25, CFG 2): the whole TransformerSpatioTemporalModel.forward at every UNet level, eager vs one
+    CUDA graph per module (graphs.GraphedForward); 23 instances per denoising step (16 UNet + 7 ControlNet)."""
+    from timelapse_video_interpolation_b200.graphs import GraphedForward
+    T, B = 25, 2
+    inst = {"L0": 7, "L1": 7, "L2": 7, "mid": 2}
+    eager, graphed = {}, {}
+    with torch.no_grad():
+        for lv in inst:
+            m, x, e, ind = _st_model(lv, T, B)
+            kw = dict(encoder_hidden_states=e, image_only_indicator=ind, return_dict=False)
+            eager[lv] = timed(lambda: m(x, **kw), steps)
+            gf = GraphedForward(m, x, **kw)
+            y_ref = m(x, **kw)[0]
+            assert torch.equal(gf(x, **kw)[0], y_ref)
+            graphed[lv] = timed(lambda: gf(x, **kw), steps)
+            del m, gf
+            torch.cuda.empty_cache()
+    step_eager = sum(eager[lv] * n for lv, n in inst.items())
+    step_graph = sum(graphed[lv] * n for lv, n in inst.items())
+    emit({"config": "levels_T25_TransformerSpatioTemporalModel", "frames": T, "cfg": 2, "instances_per_step": inst,
+          "ms_eager": eager, "ms_graphed": graphed, "ms_per_denoise_step_eager": step_eager, "ms_per_denoise_step_graphed": step_graph,
+          "clip_frames_per_s_25_steps_graphed": T / (25 * step_graph * 1e-3),
+          "note": "transformer modules only (resnets / convs / VAE are out of scope); graphed = one cudaGraphLaunch per module"})
+
+
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument("--only", default="slerp,flow,train,loop25,kernels,block,model")
+    ap.add_argument("--only", default="slerp,flow,train,loop25,kernels,block,model,levels")
     ap.add_argument("--steps", type=int, default=10)
     args = ap.parse_args()
     torch.cuda.set_device(0)
     emit({"config": "env", "device": torch.cuda.get_device_name(0), "libtvi": tvi.version(), "peaks": PK})
-    table = {"slerp": cfg_slerp, "flow": cfg_flow, "train": cfg_train, "loop25": cfg_loop25, "kernels": cfg_kernels, "block": cfg_block, "model": cfg_model}
+    table = {"slerp": cfg_slerp, "flow": cfg_flow, "train": cfg_train, "loop25": cfg_loop25, "kernels": cfg_kernels, "block": cfg_block, "model": cfg_model, "levels": cfg_levels}
     for name in args.only.split(","):
         table[name.strip()](args.steps)
 
