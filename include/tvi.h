@@ -134,6 +134,24 @@ int tvi_tokens_to_nchw_add_bf16(const tvi_bf16* y, const tvi_bf16* residual, tvi
 int tvi_blend_rows_bf16(const tvi_bf16* x_spatial, const tvi_bf16* x_temporal, const float* alpha, tvi_bf16* out,
                         int64_t nrows, int64_t rows_per_group, int C, int64_t lds, int64_t ldt, int64_t ldo, void* stream);
 
+/* Per-denoising-step glue of the pipeline loop (row N4 of SURVEY 8.6), one launch per step:
+ *   cfg_euler_step : per-frame classifier-free guidance `uncond + guidance[b, t] * (cond - uncond)`
+ *       (src/pipelines/pipeline_stable_video_diffusion_efficient_interp.py:565-566), EulerDiscreteScheduler.step with
+ *       s_churn = 0 (:569; diffusers 0.24, fp32 as in its upcast) on the fp32 master `latents` [B, T, C, HW] IN PLACE, and
+ *       — when `model_input` is given — channels [0, C) of both CFG halves of the NEXT step's UNet input
+ *       [2, B, T, Cin, HW] = latents / sqrt(sigma_next^2 + 1) (:542-546).  noise_pred is [2, B, T, C, HW] bf16
+ *       (uncond half first, as `noise_pred.chunk(2)`); guidance is fp32, element (b, t) at b * guidance_stride_b + t.
+ *   model_input : the whole UNet input of the first step: scaled latents in channels [0, C) and `image_latents`
+ *       [2, B*T, Cin - C, HW] (constant over the loop) in channels [C, Cin).
+ */
+#define TVI_PRED_EPSILON 0
+#define TVI_PRED_V 1
+int tvi_cfg_euler_step_f32(const tvi_bf16* noise_pred, float* latents, const float* guidance, tvi_bf16* model_input, int64_t B,
+                           int T, int C, int Cin, int64_t HW, int64_t guidance_stride_b, float sigma, float sigma_next,
+                           int prediction_type, void* stream);
+int tvi_model_input_bf16(const float* latents, const tvi_bf16* image_latents, tvi_bf16* model_input, int64_t BT, int C, int Cin,
+                         int64_t HW, float scale, void* stream);
+
 /* Backward of the projections (training config 5: src/train_decouples.py back-propagates through the
  * same nn.Linear call sites; autograd's F.linear backward = two cuBLAS GEMMs + a bias column sum).
  *   dgrad : dX[M,K] = dY[M,N] . W[N,K]          (W consumed in place, MN-major tcgen05 operand)

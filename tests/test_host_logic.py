@@ -104,3 +104,21 @@ def test_fused_weight_cache_tracks_parameter_updates():
     w2 = p._fused(attn, ("to_q", "to_k", "to_v"))
     assert w2 is not w1 and torch.equal(w2[128:256], attn.to_k.weight.to(torch.bfloat16))
     assert "fused" not in "".join(attn.state_dict())
+
+
+def test_step_oracle_known_answers():
+    # N4 oracle: stepping to sigma_next = 0 lands on the predicted clean sample; CFG with scale 1 is the cond branch
+    import torch
+    from oracle import step_ref
+    g = torch.Generator().manual_seed(0)
+    x, e = torch.randn(1, 3, 4, 2, 2, generator=g, dtype=torch.float64), torch.randn(1, 3, 4, 2, 2, generator=g, dtype=torch.float64)
+    sigma = 2.5
+    assert torch.allclose(step_ref.euler_step_ref(e, x, sigma, 0.0, "epsilon"), x - sigma * e)
+    v0 = e * (-sigma / (sigma ** 2 + 1) ** 0.5) + x / (sigma ** 2 + 1)
+    assert torch.allclose(step_ref.euler_step_ref(e, x, sigma, 0.0, "v_prediction"), v0)
+    assert torch.allclose(step_ref.euler_step_ref(e, x, sigma, sigma, "v_prediction"), x)  # dt = 0
+    pair = torch.cat([x, e])
+    assert torch.allclose(step_ref.cfg_ref(pair, torch.ones(1, 3, 1, 1, 1)), e)
+    assert torch.allclose(step_ref.cfg_ref(pair, torch.zeros(1, 3, 1, 1, 1)), x)
+    mi = step_ref.model_input_ref(x, torch.ones(2, 3, 5, 2, 2), 1.0)
+    assert mi.shape == (2, 3, 9, 2, 2) and torch.allclose(mi[:, :, :4], torch.cat([x, x]) / 2 ** 0.5)

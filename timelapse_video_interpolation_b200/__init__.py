@@ -7,6 +7,7 @@ Public surface (mirrors the reference's interfaces for this path, SURVEY.md §8.
   feed_forward, layer_norm, install_feed_forward   FeedForward (GEGLU) / LayerNorm of the blocks
   install_blocks                         BasicTransformerBlock / TemporalBasicTransformerBlock forwards (N1, N2)
   install_spatio_temporal                TransformerSpatioTemporalModel.forward (GroupNorm, proj_in/out, AlphaBlender, layout)
+  EulerCfgStepper, graphs.GraphedForward per-step glue (CFG + Euler + next model input in one launch), CUDA-graph capture (N4)
 Everything runs through libtvi.so (include/tvi.h); there is no CPU or torch fallback.
 """
 from . import _lib, ops  # noqa: F401
@@ -16,9 +17,10 @@ from .feedforward import feed_forward, install_feed_forward, layer_norm, uninsta
 from .flow import backward_warp_check, cosine_similarity, cosine_similarity_chw  # noqa: F401
 from .processor import TviAttnProcessor, install, uninstall  # noqa: F401
 from .slerp import slerp  # noqa: F401
+from .step import EulerCfgStepper  # noqa: F401
 from .spatio_temporal import install_spatio_temporal, uninstall_spatio_temporal  # noqa: F401
 
 __all__ = ["TviAttnProcessor", "install", "uninstall", "slerp", "cosine_similarity", "cosine_similarity_chw",
            "backward_warp_check", "feed_forward", "layer_norm", "install_feed_forward", "uninstall_feed_forward",
-           "install_blocks", "uninstall_blocks", "install_spatio_temporal", "uninstall_spatio_temporal",
+           "install_blocks", "uninstall_blocks", "EulerCfgStepper", "install_spatio_temporal", "uninstall_spatio_temporal",
            "TviError", "version", "ops"]

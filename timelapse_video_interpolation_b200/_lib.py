@@ -46,6 +46,8 @@ SIGNATURES = {
     "tvi_groupnorm_tokens_bf16": (_i32, [_ptr, _ptr, _ptr, _ptr, _ptr, _i64, _i32, _i32, _i32, _i64, _f32, _ptr]),
     "tvi_tokens_to_nchw_add_bf16": (_i32, [_ptr, _ptr, _ptr, _i64, _i32, _i32, _i64, _ptr]),
     "tvi_blend_rows_bf16": (_i32, [_ptr, _ptr, _ptr, _ptr, _i64, _i64, _i32, _i64, _i64, _i64, _ptr]),
+    "tvi_cfg_euler_step_f32": (_i32, [_ptr, _ptr, _ptr, _ptr, _i64, _i32, _i32, _i32, _i64, _i64, _f32, _f32, _i32, _ptr]),
+    "tvi_model_input_bf16": (_i32, [_ptr, _ptr, _ptr, _i64, _i32, _i32, _i64, _f32, _ptr]),
     "tvi_gemm_bf16_dgrad": (_i32, [_ptr, _ptr, _ptr, _i64, _i32, _i32, _i64, _i64, _i64, _ptr]),
     "tvi_gemm_bf16_wgrad_workspace_bytes": (_sz, [_i64, _i32, _i32]),
     "tvi_gemm_bf16_wgrad": (_i32, [_ptr, _ptr, _ptr, _ptr, _i64, _i32, _i32, _i64, _i64, _i64, _ptr]),
@@ -69,6 +71,7 @@ SIGNATURES = {
 }
 SPATIAL_AUTO, SPATIAL_MMA_SYNC, SPATIAL_TCGEN05 = 0, 1, 2
 EPILOGUE_NONE, EPILOGUE_GEGLU = 0, 1
+PRED_EPSILON, PRED_V = 0, 1
 
 _lib = None
 
