@@ -152,6 +152,16 @@ int tvi_cfg_euler_step_f32(const tvi_bf16* noise_pred, float* latents, const flo
 int tvi_model_input_bf16(const float* latents, const tvi_bf16* image_latents, tvi_bf16* model_input, int64_t BT, int C, int Cin,
                          int64_t HW, float scale, void* stream);
 
+/* Dense optical flow after Farneback (row N3 of SURVEY 8.6): the computation of cv2.calcOpticalFlowFarneback(prev, next,
+ * None, pyr_scale, levels, winsize, iterations, poly_n, poly_sigma, flags=0) as called at
+ * dataset_construction/step4_flow_check.py:13-22 (0.5, 3, 15, 3, 5, 1.2), including the cv2.cvtColor(BGR2GRAY) in front
+ * of it when channels == 3.  prev / next: 8-bit device images [H, W, channels] (1 = gray, 3 = BGR); flow: [H, W, 2] fp32
+ * (dx, dy); `workspace` = tvi_farneback_workspace_bytes(H, W) bytes.  ~26 launches per pyramid level, no host sync.
+ */
+size_t tvi_farneback_workspace_bytes(int H, int W);
+int tvi_farneback_f32(const uint8_t* prev, const uint8_t* next, int channels, float* flow, void* workspace, int H, int W,
+                      double pyr_scale, int levels, int winsize, int iterations, int poly_n, double poly_sigma, void* stream);
+
 /* Backward of the projections (training config 5: src/train_decouples.py back-propagates through the
  * same nn.Linear call sites; autograd's F.linear backward = two cuBLAS GEMMs + a bias column sum).
  *   dgrad : dX[M,K] = dY[M,N] . W[N,K]          (W consumed in place, MN-major tcgen05 operand)

@@ -19,6 +19,8 @@ container (needs /root/reference); the GPU box uses the .npz files.
 * spatio_temporal.npz  — src/models/transformer_temporal.py: the reference's own `TransformerSpatioTemporalModel` (forward
   :253-360) on its own blocks; the un-vendored diffusers leaves Timesteps / TimestepEmbedding / AlphaBlender are the
   restatements in timelapse_video_interpolation_b200/modules.py.
+* farneback.npz        — dataset_construction/step4_flow_check.py:compute_optical_flow_farneback imported as is, i.e. the
+  output of cv2.cvtColor + cv2.calcOpticalFlowFarneback (third-party OpenCV, 4.13.0 here) on synthetic frames.
 """
 from __future__ import annotations
 
@@ -309,6 +311,25 @@ def make_spatio_temporal(ap):
     print("spatio_temporal.npz", tuple(y.shape), float(y.abs().max()))
 
 
+def make_farneback():
+    """cv2.calcOpticalFlowFarneback itself (OpenCV 4.13 in this image) with the reference's parameters
+    (dataset_construction/step4_flow_check.py:13-22) on synthetic textured BGR frames related by a small affine motion."""
+    import cv2
+    ref = _load(REF / "dataset_construction/step4_flow_check.py", "ref_step4b")
+    out = {"opencv_version": np.array(cv2.__version__)}
+    for i, (h, w) in enumerate([(96, 128), (135, 240), (70, 81), (40, 200)]):
+        r = np.random.default_rng(10 + i)
+        base = cv2.resize(r.random((h // 8 + 2, w // 8 + 2, 3)).astype(np.float32), (w, h), interpolation=cv2.INTER_CUBIC)
+        a = np.clip((base + 0.15 * r.random((h, w, 3)).astype(np.float32)) * 255, 0, 255).astype(np.uint8)
+        A = np.float32([[1, 0.02, 1.7 - i], [-0.01, 1, -1.2 + 0.5 * i]])
+        b = cv2.warpAffine(a, A, (w, h), borderMode=cv2.BORDER_REFLECT)
+        out[f"a{i}"], out[f"b{i}"] = a, b
+        out[f"gray{i}"] = cv2.cvtColor(a, cv2.COLOR_BGR2GRAY)
+        out[f"flow{i}"] = ref.compute_optical_flow_farneback(a, b)      # the reference's own function
+    np.savez_compressed(OUT / "farneback.npz", **out)
+    print("farneback.npz", {k: tuple(v.shape) for k, v in out.items() if k.startswith("flow")})
+
+
 if __name__ == "__main__":
     torch.set_num_threads(4)
     make_flow()
@@ -316,3 +337,4 @@ if __name__ == "__main__":
     make_temporal_patched(ap)
     make_blocks(ap)
     make_spatio_temporal(ap)
+    make_farneback()

@@ -5,6 +5,7 @@ import pytest
 import torch
 
 import timelapse_video_interpolation_b200 as tvi
+from timelapse_video_interpolation_b200 import _lib, ops
 from oracle import flow_ref, slerp_ref
 
 pytestmark = pytest.mark.gpu
@@ -126,3 +127,51 @@ def test_backward_warp_identity_and_1080p_roundtrip(cuda):
     assert torch.equal(warped[:, :, 2:, :-3], img[:, :, :-2, 3:])
     assert not bool(valid[:, :2].any()) and not bool(valid[:, :, -3:].any()) and bool(valid[:, 2:, :-3].all())
     assert not bool(occ[:, 4:, :-6].any())
+
+
+@pytest.mark.parametrize("i", range(4))
+def test_farneback_matches_opencv_golden_and_oracle(cuda, golden_dir, i):
+    import numpy as np
+    from oracle import farneback_ref
+    from timelapse_video_interpolation_b200 import compute_optical_flow_farneback
+    z = np.load(golden_dir / "farneback.npz")
+    a, b = z[f"a{i}"], z[f"b{i}"]
+    flow = compute_optical_flow_farneback(a, b)                      # numpy BGR in -> numpy (H, W, 2) out
+    ref = z[f"flow{i}"]
+    assert isinstance(flow, np.ndarray) and flow.shape == ref.shape and flow.dtype == np.float32
+    err = np.abs(flow - ref)
+    print(f"farneback {ref.shape}: vs cv2 max {err.max():.2e} mean {err.mean():.2e} (max |flow| {np.abs(ref).max():.2f})")
+    assert err.max() < 5e-3 and err.mean() < 5e-5
+    ora = farneback_ref.calc_optical_flow_farneback(farneback_ref.gray_from_bgr(a), farneback_ref.gray_from_bgr(b))
+    assert np.abs(flow - ora).max() < 5e-3
+    # gray input path and CUDA-tensor path
+    ga = torch.from_numpy(z[f"gray{i}"]).to(cuda)
+    gb = torch.from_numpy(farneback_ref.gray_from_bgr(b)).to(cuda)
+    f2 = ops.farneback(ga, gb)
+    assert torch.equal(f2.cpu(), torch.from_numpy(flow))
+
+
+def test_farneback_full_hd_and_edge_cases(cuda):
+    import numpy as np
+    from oracle import farneback_ref
+    rng = np.random.default_rng(0)
+    # 1080p: identical frames -> zero flow; shifted frame -> the shift (size-independent properties)
+    base = rng.random((1080 // 8 + 2, 1920 // 8 + 2)).astype(np.float32)
+    t = torch.nn.functional.interpolate(torch.from_numpy(base)[None, None], size=(1080 + 8, 1920 + 8), mode="bicubic")[0, 0]
+    img = (t.clamp(0, 1) * 255).to(torch.uint8)
+    a, b = img[4:-4, 4:-4].contiguous().to(cuda), img[2:-6, 7:-1].contiguous().to(cuda)  # b(y, x) = a(y - 2, x + 3)
+    f0 = ops.farneback(a, a)   # identical frames: zero flow away from the image border (the border terms are OpenCV's)
+    assert float(f0[300:-300, 300:-300].abs().max()) < 1e-3
+    f = ops.farneback(a, b)
+    core = f[100:-100, 100:-100]
+    assert abs(float(core[..., 0].median()) + 3.0) < 0.1 and abs(float(core[..., 1].median()) - 2.0) < 0.1
+    # tiny image (pyramid collapses to one level) against the oracle
+    sa = (rng.random((33, 40)) * 255).astype(np.uint8)
+    sb = np.roll(sa, 1, axis=1)
+    got = ops.farneback(torch.from_numpy(sa).to(cuda), torch.from_numpy(sb).to(cuda)).cpu().numpy()
+    want = farneback_ref.calc_optical_flow_farneback(sa, sb)
+    assert np.abs(got - want).max() < 5e-3 * max(1.0, np.abs(want).max())
+    with pytest.raises(_lib.TviError):
+        ops.farneback(torch.zeros(8, 8, 2, dtype=torch.uint8, device=cuda), torch.zeros(8, 8, 2, dtype=torch.uint8, device=cuda))
+    with pytest.raises(_lib.TviError):
+        ops.farneback(torch.zeros(8, 8, dtype=torch.float32, device=cuda), torch.zeros(8, 8, dtype=torch.float32, device=cuda))

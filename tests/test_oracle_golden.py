@@ -179,3 +179,20 @@ def test_spatio_temporal_oracle_matches_reference_model(golden_dir):
     y2 = spatio_temporal_ref.transformer_spatio_temporal_ref(m, x, e, ind)
     frame = 1 * 5 + 3
     assert max_abs(y2[frame], z["y"][frame]) < 1e-4 and max_abs(y2, z["y"]) > 1e-2
+
+
+@pytest.mark.parametrize("i", range(4))
+def test_farneback_oracle_matches_opencv(golden_dir, i):
+    # golden = the reference's compute_optical_flow_farneback (cv2.cvtColor + cv2.calcOpticalFlowFarneback) itself
+    from oracle import farneback_ref
+    z = np.load(golden_dir / "farneback.npz")
+    a, b = z[f"a{i}"], z[f"b{i}"]
+    gray = farneback_ref.gray_from_bgr(a)
+    assert np.array_equal(gray, z[f"gray{i}"])                      # integer work: bit-exact
+    flow = farneback_ref.calc_optical_flow_farneback(gray, farneback_ref.gray_from_bgr(b))
+    ref = z[f"flow{i}"]
+    assert flow.shape == ref.shape and flow.dtype == np.float32
+    err = np.abs(flow - ref)
+    # OpenCV accumulates the blur / polynomial passes in float SIMD, the restatement in double: tolerance 1e-3 px
+    assert err.max() < 1e-3 and err.mean() < 1e-5, (err.max(), err.mean())
+    assert np.abs(ref).max() > 1.0                                   # the fixture really moves

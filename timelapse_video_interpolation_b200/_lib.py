@@ -26,7 +26,7 @@ class TviError(RuntimeError):
         self.code = code
 
 
-_i64, _i32, _f32, _ptr, _sz = C.c_int64, C.c_int, C.c_float, C.c_void_p, C.c_size_t
+_i64, _i32, _f32, _f64, _ptr, _sz = C.c_int64, C.c_int, C.c_float, C.c_double, C.c_void_p, C.c_size_t
 
 # name -> (restype, argtypes); mirrors include/tvi.h one to one (checked by tests/test_abi.py)
 SIGNATURES = {
@@ -48,6 +48,8 @@ SIGNATURES = {
     "tvi_blend_rows_bf16": (_i32, [_ptr, _ptr, _ptr, _ptr, _i64, _i64, _i32, _i64, _i64, _i64, _ptr]),
     "tvi_cfg_euler_step_f32": (_i32, [_ptr, _ptr, _ptr, _ptr, _i64, _i32, _i32, _i32, _i64, _i64, _f32, _f32, _i32, _ptr]),
     "tvi_model_input_bf16": (_i32, [_ptr, _ptr, _ptr, _i64, _i32, _i32, _i64, _f32, _ptr]),
+    "tvi_farneback_workspace_bytes": (_sz, [_i32, _i32]),
+    "tvi_farneback_f32": (_i32, [_ptr, _ptr, _i32, _ptr, _ptr, _i32, _i32, _f64, _i32, _i32, _i32, _i32, _f64, _ptr]),
     "tvi_gemm_bf16_dgrad": (_i32, [_ptr, _ptr, _ptr, _i64, _i32, _i32, _i64, _i64, _i64, _ptr]),
     "tvi_gemm_bf16_wgrad_workspace_bytes": (_sz, [_i64, _i32, _i32]),
     "tvi_gemm_bf16_wgrad": (_i32, [_ptr, _ptr, _ptr, _ptr, _i64, _i32, _i32, _i64, _i64, _i64, _ptr]),

@@ -1,4 +1,4 @@
-"""Optical-flow checks: drop-in `cosine_similarity` and the backward-warp consistency check.
+"""Optical-flow path: drop-in `compute_optical_flow_farneback`, `cosine_similarity` and the backward-warp consistency check.
 
 `cosine_similarity(flow_a, flow_b)` has the name, arity and return type of the reference function
 (dataset_construction/step4_flow_check.py:25-34): two (H, W, 2) float32 numpy arrays in OpenCV's HWC
@@ -18,6 +18,17 @@ from . import ops
 
 OCC_ALPHA = 0.01
 OCC_BETA = 0.5
+
+
+def compute_optical_flow_farneback(img1, img2):
+    """Drop-in for the reference function of the same name (dataset_construction/step4_flow_check.py:13-22): two BGR uint8
+    images (H, W, 3) -> flow (H, W, 2) float32, the computation of cv2.cvtColor(BGR2GRAY) + cv2.calcOpticalFlowFarneback(
+    0.5, 3, 15, 3, 5, 1.2, 0) on the GPU.  numpy in -> numpy out; CUDA uint8 tensors in -> CUDA tensor out (no host sync)."""
+    if isinstance(img1, np.ndarray):
+        a = torch.from_numpy(np.ascontiguousarray(img1, dtype=np.uint8)).cuda(non_blocking=True)
+        b = torch.from_numpy(np.ascontiguousarray(img2, dtype=np.uint8)).cuda(non_blocking=True)
+        return ops.farneback(a, b).cpu().numpy()
+    return ops.farneback(img1, img2)
 
 
 def cosine_similarity(flow_a, flow_b):

@@ -210,6 +210,24 @@ def blend_rows(x_spatial: torch.Tensor, x_temporal: torch.Tensor, alpha: torch.T
     return out
 
 
+def farneback(prev: torch.Tensor, nxt: torch.Tensor, pyr_scale: float = 0.5, levels: int = 3, winsize: int = 15, iterations: int = 3,
+              poly_n: int = 5, poly_sigma: float = 1.2, out: torch.Tensor | None = None) -> torch.Tensor:
+    """Farneback dense flow of two uint8 CUDA images [H, W] (gray) or [H, W, 3] (BGR) -> [H, W, 2] fp32."""
+    _need_cuda(prev, nxt)
+    if prev.dtype != torch.uint8 or nxt.dtype != torch.uint8 or prev.shape != nxt.shape or prev.dim() not in (2, 3):
+        raise _lib.TviError(_lib.TVI_ERR_INVALID, "farneback: expected two uint8 images of the same shape, [H, W] or [H, W, 3]")
+    ch = 1 if prev.dim() == 2 else prev.shape[2]
+    H, W = prev.shape[:2]
+    prev, nxt = prev.contiguous(), nxt.contiguous()
+    if out is None:
+        out = torch.empty(H, W, 2, dtype=torch.float32, device=prev.device)
+    ws = _workspace(_lib.load().tvi_farneback_workspace_bytes(H, W), prev.device)
+    _hooked("farneback", 26 * (levels + 1), _lib.load().tvi_farneback_f32, prev.data_ptr(), nxt.data_ptr(), ch, out.data_ptr(),
+            ws.data_ptr() if ws is not None else None, H, W, float(pyr_scale), int(levels), int(winsize), int(iterations), int(poly_n),
+            float(poly_sigma), _stream())
+    return out
+
+
 def gemm_bf16_dgrad(dy: torch.Tensor, w: torch.Tensor, out: torch.Tensor | None = None) -> torch.Tensor:
     """dx[..., K] = dy[..., N] @ w[N, K] — input gradient of nn.Linear; w is consumed in place."""
     _need_cuda(dy, w)

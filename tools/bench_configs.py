@@ -357,14 +357,43 @@ def cfg_levels(steps):
           "note": "transformer modules only (resnets / convs / VAE are out of scope); graphed = one cudaGraphLaunch per module"})
 
 
+def cfg_farneback(steps):
+    """N3: Farneback flow of 1080p BGR frame pairs (device-resident uint8), and OpenCV's CPU implementation beside it."""
+    import numpy as np
+    H, W = 1080, 1920
+    rng = np.random.default_rng(0)
+    base = torch.from_numpy(rng.random((H // 8 + 2, W // 8 + 2, 3)).astype(np.float32)).permute(2, 0, 1)[None]
+    img = torch.nn.functional.interpolate(base, size=(H + 8, W + 8), mode="bicubic")[0].permute(1, 2, 0)
+    img = (img.clamp(0, 1) * 255).to(torch.uint8)
+    a, b = img[4:-4, 4:-4].contiguous(), img[2:-6, 7:-1].contiguous()
+    da, db = a.to(DEV), b.to(DEV)
+    out = torch.empty(H, W, 2, dtype=torch.float32, device=DEV)
+    ms = timed(lambda: ops.farneback(da, db, out=out), steps)
+    rec = {"config": "farneback_1080p_pair", "ms_per_pair": ms, "pairs_per_s": 1e3 / ms, "median_flow": [float(out[..., 0].median()), float(out[..., 1].median())]}
+    try:
+        import cv2
+        import time
+        an, bn = a.numpy(), b.numpy()
+        t0 = time.perf_counter()
+        for _ in range(3):
+            ga, gb = cv2.cvtColor(an, cv2.COLOR_BGR2GRAY), cv2.cvtColor(bn, cv2.COLOR_BGR2GRAY)
+            ref = cv2.calcOpticalFlowFarneback(ga, gb, None, 0.5, 3, 15, 3, 5, 1.2, 0)
+        rec["opencv_cpu_ms_per_pair"] = (time.perf_counter() - t0) / 3 * 1e3
+        rec["opencv_threads"] = cv2.getNumThreads()
+        rec["max_abs_diff_vs_opencv"] = float(np.abs(out.cpu().numpy() - ref).max())
+    except ImportError:
+        rec["opencv_cpu_ms_per_pair"] = None
+    emit(rec)
+
+
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument("--only", default="slerp,flow,train,loop25,kernels,block,model,levels")
+    ap.add_argument("--only", default="slerp,flow,train,loop25,kernels,block,model,levels,farneback")
     ap.add_argument("--steps", type=int, default=10)
     args = ap.parse_args()
     torch.cuda.set_device(0)
     emit({"config": "env", "device": torch.cuda.get_device_name(0), "libtvi": tvi.version(), "peaks": PK})
-    table = {"slerp": cfg_slerp, "flow": cfg_flow, "train": cfg_train, "loop25": cfg_loop25, "kernels": cfg_kernels, "block": cfg_block, "model": cfg_model, "levels": cfg_levels}
+    table = {"slerp": cfg_slerp, "flow": cfg_flow, "train": cfg_train, "loop25": cfg_loop25, "kernels": cfg_kernels, "block": cfg_block, "model": cfg_model, "levels": cfg_levels, "farneback": cfg_farneback}
     for name in args.only.split(","):
         table[name.strip()](args.steps)
 
