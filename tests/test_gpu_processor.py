@@ -144,3 +144,24 @@ def test_full_size_l0_block_properties(cuda):
     idx = torch.randint(0, 18432, (256,), generator=g)
     ref = attention_ref.attn_processor_ref(attn, xt[idx.to(cuda)].float().cpu())
     assert max_abs(yt[idx.to(cuda)].float().cpu(), ref) < TOL
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.float16])
+def test_reference_script_shape_512x320_fp32_and_fp16(cuda, dtype):
+    # every script of the reference runs 512x320 (latent 64x40 = 2 560 tokens per frame, T = 14) in fp32 or
+    # fp16, never bf16: the four processor calls of an L0 block at that shape, through cast_inputs=True
+    proc = TviAttnProcessor(cast_inputs=True)
+    S, T, B = 64 * 40, 14, 1
+    g = torch.Generator().manual_seed(7)
+    for name, rows, seq, cross, L in [("spatial self", B * T, S, None, None), ("spatial cross", B * T, S, 1024, 2),
+                                      ("temporal self", 512, T, None, None), ("temporal cross", 512, T, 1024, 1)]:
+        attn = make_attn(320, cross, 5, seed=len(name), device=cuda, dtype=dtype, processor=proc)
+        x = torch.randn(rows, seq, 320, generator=g).to(dtype).to(cuda)
+        e = torch.randn(rows, L, cross, generator=g).to(dtype).to(cuda) if cross else None
+        with torch.no_grad():
+            y = attn(x, encoder_hidden_states=e)
+        assert y.dtype == dtype and y.shape == x.shape
+        ref = attention_ref.attn_processor_ref(attn, x.float().cpu(), None if e is None else e.float().cpu())
+        err = max_abs(y.float().cpu(), ref)
+        print(f"512x320 {name} {dtype}: max abs err {err:.3e}")
+        assert err < 2 * TOL, name   # inputs AND weights are rounded to bf16 on entry

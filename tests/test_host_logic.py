@@ -122,3 +122,29 @@ def test_step_oracle_known_answers():
     assert torch.allclose(step_ref.cfg_ref(pair, torch.zeros(1, 3, 1, 1, 1)), x)
     mi = step_ref.model_input_ref(x, torch.ones(2, 3, 5, 2, 2), 1.0)
     assert mi.shape == (2, 3, 9, 2, 2) and torch.allclose(mi[:, :, :4], torch.cat([x, x]) / 2 ** 0.5)
+
+
+def test_weight_caches_are_keyed_by_live_modules():
+    # regression: an id()-keyed cache served a dead module's fused weights to a new module that recycled its id and
+    # parameter addresses; the caches are WeakKeyDictionaries now and drop their entries with the module
+    import gc
+    import weakref
+    import torch
+    from timelapse_video_interpolation_b200 import feedforward
+    from timelapse_video_interpolation_b200.modules import Attention
+    from timelapse_video_interpolation_b200.processor import TviAttnProcessor
+    proc = TviAttnProcessor()
+    assert isinstance(proc._wcache, weakref.WeakKeyDictionary) and isinstance(feedforward._cache, weakref.WeakKeyDictionary)
+    for seed in range(3):
+        torch.manual_seed(seed)
+        attn = Attention(64, None, heads=1, processor=proc).to(torch.bfloat16)
+        fused = proc._fused(attn, ("to_q", "to_k", "to_v"))
+        want = torch.cat([attn.to_q.weight, attn.to_k.weight, attn.to_v.weight]).detach()
+        assert torch.equal(fused, want)
+        assert proc._fused(attn, ("to_q", "to_k", "to_v")) is fused          # cache hit
+        with torch.no_grad():
+            attn.to_k.weight.add_(1.0)                                        # in-place update bumps _version
+        assert torch.equal(proc._fused(attn, ("to_q", "to_k", "to_v"))[64:128], attn.to_k.weight.detach())
+        del attn, fused, want
+        gc.collect()
+        assert len(proc._wcache) == 0

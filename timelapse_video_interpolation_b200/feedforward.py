@@ -15,6 +15,7 @@ plugin).  Inference only for now: a call that needs gradients raises (the backwa
 from __future__ import annotations
 
 import types
+import weakref
 from typing import Optional
 
 import torch
@@ -23,7 +24,7 @@ from . import _lib, ops
 
 __all__ = ["feed_forward", "layer_norm", "install_feed_forward", "uninstall_feed_forward"]
 
-_cache: dict = {}
+_cache: weakref.WeakKeyDictionary = weakref.WeakKeyDictionary()  # weak: an id() key could be recycled by a later module
 
 
 def _is_feed_forward(m) -> bool:
@@ -37,7 +38,7 @@ def _geglu_weights(proj):
     blocks of H = tvi_geglu_block(inner); cached per (data_ptr, version) so state_dict keys stay untouched."""
     w, b = proj.weight, proj.bias
     sig = (w.data_ptr(), w._version, w.dtype, None if b is None else (b.data_ptr(), b._version))
-    hit = _cache.get(id(proj))
+    hit = _cache.get(proj)
     if hit is not None and hit[0] == sig:
         return hit[1], hit[2]
     inner = w.shape[0] // 2
@@ -52,7 +53,7 @@ def _geglu_weights(proj):
         if b is not None:
             bb = b.detach().to(torch.bfloat16)
             bi = torch.stack([bb[:inner].view(inner // H, H), bb[inner:].view(inner // H, H)], dim=1).reshape(-1).contiguous()
-    _cache[id(proj)] = (sig, wi, bi)
+    _cache[proj] = (sig, wi, bi)
     return wi, bi
 
 

@@ -22,6 +22,7 @@ Per call (all kernels from libtvi, on the current CUDA stream, no host sync):
 from __future__ import annotations
 
 import types
+import weakref
 from typing import Optional
 
 import torch
@@ -55,7 +56,9 @@ class TviAttnProcessor:
         self.ramp_bias = ramp_bias
         self.stats_sink = stats_sink
         self.cast_inputs = cast_inputs
-        self._wcache: dict = {}
+        # keyed by the module OBJECT (weakly): an id() key can be recycled by a later module whose parameters land on
+        # the freed addresses, which would serve the dead module's fused weights
+        self._wcache: weakref.WeakKeyDictionary = weakref.WeakKeyDictionary()
         self._bias_cache: dict = {}
 
     # ------------------------------------------------------------------ weight caches
@@ -63,15 +66,17 @@ class TviAttnProcessor:
         """Derived, never-registered fused weight ([sum(out), in], bf16); rebuilt when any source
         parameter changes (optimizer step bumps `_version`) so state_dict keys are untouched."""
         ws = [_linear_weight(getattr(attn, n), n) for n in names]
-        key = (id(attn), names)
         sig = tuple((w.data_ptr(), w._version, w.dtype, w.device) for w in ws)
-        hit = self._wcache.get(key)
+        per_module = self._wcache.get(attn)
+        if per_module is None:
+            per_module = self._wcache.setdefault(attn, {})
+        hit = per_module.get(names)
         if hit is not None and hit[0] == sig:
             return hit[1]
         with torch.no_grad():
             fused = torch.cat([w.detach().to(torch.bfloat16) for w in ws], dim=0).contiguous() if len(ws) > 1 \
                 else ws[0].detach().to(torch.bfloat16).contiguous()
-        self._wcache[key] = (sig, fused)
+        per_module[names] = (sig, fused)
         return fused
 
     def _ramp(self, T: int, device) -> torch.Tensor:
