@@ -55,10 +55,17 @@ __global__ void gauss_kernel(const float* __restrict__ src, float* __restrict__ 
   const int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y;
   if (x >= w) return;
   const int r = taps.n / 2;
+  const int c = kVertical ? y : x, n = kVertical ? h : w;
+  const int64_t stride = kVertical ? w : 1;
   float acc = 0.f;
-  for (int t = 0; t < taps.n; ++t) {
-    const float v = kVertical ? src[(int64_t)reflect101(y + t - r, h) * w + x] : src[(int64_t)y * w + reflect101(x + t - r, w)];
-    acc = fmaf(taps.k[t], v, acc);
+  if (c >= r && c + r < n) {  // interior: no border arithmetic (the reflect path costs two integer divisions per tap)
+    const float* p = src + (int64_t)y * w + x - (int64_t)r * stride;
+    for (int t = 0; t < taps.n; ++t) acc = fmaf(taps.k[t], p[(int64_t)t * stride], acc);
+  } else {
+    for (int t = 0; t < taps.n; ++t) {
+      const float v = kVertical ? src[(int64_t)reflect101(y + t - r, h) * w + x] : src[(int64_t)y * w + reflect101(x + t - r, w)];
+      acc = fmaf(taps.k[t], v, acc);
+    }
   }
   dst[(int64_t)y * w + x] = acc;
 }
@@ -204,13 +211,21 @@ __global__ void update_matrices_kernel(const float* __restrict__ R0, const float
   o[4] = r6 * r2 + r5 * r3;
 }
 
-// vertical box sums (rows y-m .. y+m, replicated), fp64
+// vertical box sums (rows y-m .. y+m, replicated), fp64.  A thread owns one (column, channel) over a strip of kBoxRows
+// rows and slides the window: two loads per output instead of 2m+1 (OpenCV slides one fp64 sum down the whole column).
+constexpr int kBoxRows = 32;
 __global__ void box_v_kernel(const float* __restrict__ M, double* __restrict__ V, int h, int w, int m) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y;  // i over w * 5
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;  // over w * 5
   if (i >= w * 5) return;
+  const int y0 = blockIdx.y * kBoxRows;
+  const int64_t pitch = (int64_t)w * 5;
   double s = 0.0;
-  for (int j = -m; j <= m; ++j) s += (double)M[(int64_t)min(max(y + j, 0), h - 1) * w * 5 + i];
-  V[(int64_t)y * w * 5 + i] = s;
+  for (int j = -m; j <= m; ++j) s += (double)M[(int64_t)min(max(y0 + j, 0), h - 1) * pitch + i];
+  const int y1 = min(y0 + kBoxRows, h);
+  for (int y = y0; y < y1; ++y) {
+    V[(int64_t)y * pitch + i] = s;
+    s += (double)M[(int64_t)min(y + 1 + m, h - 1) * pitch + i] - (double)M[(int64_t)max(y - m, 0) * pitch + i];
+  }
 }
 
 // horizontal box sums + the 2x2 solve of FarnebackUpdateFlow_Blur
@@ -410,7 +425,7 @@ extern "C" int tvi_farneback_f32(const uint8_t* prev, const uint8_t* next, int c
     if (smooth < 3) smooth = 3;
     TVI_CHECK_ARG(smooth <= kMaxTaps, "tvi_farneback_f32: pyramid too deep for the blur kernel (%d taps)", smooth);
     const int w = cv_round(W * scale), h = cv_round(H * scale);
-    const dim3 grid_full((W + 127) / 128, H), grid((w + 127) / 128, h), grid5((w * 5 + 127) / 128, h);
+    const dim3 grid_full((W + 127) / 128, H), grid((w + 127) / 128, h);
     float* fl = (k == 0) ? flow : ws + l.flow[cur];
     if (!have_prev) {
       TVI_CUDA_OK(cudaMemsetAsync(fl, 0, sizeof(float) * 2 * (size_t)h * w, st));
@@ -429,7 +444,7 @@ extern "C" int tvi_farneback_f32(const uint8_t* prev, const uint8_t* next, int c
     }
     update_matrices_kernel<<<grid, 128, 0, st>>>(ws + l.R[0], ws + l.R[1], fl, ws + l.M, h, w);
     for (int it = 0; it < iterations; ++it) {
-      box_v_kernel<<<grid5, 128, 0, st>>>(ws + l.M, (double*)(ws + l.V), h, w, winsize / 2);
+      box_v_kernel<<<dim3((w * 5 + 127) / 128, (h + kBoxRows - 1) / kBoxRows), 128, 0, st>>>(ws + l.M, (double*)(ws + l.V), h, w, winsize / 2);
       box_h_solve_kernel<<<grid, 128, 0, st>>>((const double*)(ws + l.V), fl, h, w, winsize / 2, 1.0 / ((double)winsize * winsize));
       if (it < iterations - 1) update_matrices_kernel<<<grid, 128, 0, st>>>(ws + l.R[0], ws + l.R[1], fl, ws + l.M, h, w);
       TVI_LAUNCH_OK("farneback iteration");
