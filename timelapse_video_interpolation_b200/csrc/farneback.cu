@@ -228,14 +228,27 @@ __global__ void box_v_kernel(const float* __restrict__ M, double* __restrict__ V
   }
 }
 
-// horizontal box sums + the 2x2 solve of FarnebackUpdateFlow_Blur
-__global__ void box_h_solve_kernel(const double* __restrict__ V, float* __restrict__ flow, int h, int w, int m, double scale) {
-  const int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y;
-  if (x >= w) return;
+// horizontal box sums + the 2x2 solve of FarnebackUpdateFlow_Blur.  The row segment of the block (kBoxCols + 2m pixels x 5
+// fp64 sums, replicated at the row ends) is staged in shared memory with coalesced loads; each thread then sums its
+// 2m+1 neighbours from there (75 strided L1 hits per pixel before).
+constexpr int kBoxCols = 128;
+constexpr int kBoxMaxM = 15;
+__global__ void __launch_bounds__(kBoxCols)
+box_h_solve_kernel(const double* __restrict__ V, float* __restrict__ flow, int h, int w, int m, double scale) {
+  __shared__ double seg[(kBoxCols + 2 * kBoxMaxM) * 5];
+  const int x0 = blockIdx.x * kBoxCols, y = blockIdx.y;
   const double* row = V + (int64_t)y * w * 5;
+  const int npix = kBoxCols + 2 * m;
+  for (int i = threadIdx.x; i < npix * 5; i += kBoxCols) {
+    const int px = i / 5, c = i - px * 5;
+    seg[i] = row[min(max(x0 - m + px, 0), w - 1) * 5 + c];
+  }
+  __syncthreads();
+  const int x = x0 + threadIdx.x;
+  if (x >= w) return;
   double g11 = 0, g12 = 0, g22 = 0, h1 = 0, h2 = 0;
-  for (int j = -m; j <= m; ++j) {
-    const double* p = row + min(max(x + j, 0), w - 1) * 5;
+  const double* p = seg + threadIdx.x * 5;
+  for (int j = 0; j <= 2 * m; ++j, p += 5) {
     g11 += p[0];
     g12 += p[1];
     g22 += p[2];
@@ -389,7 +402,8 @@ extern "C" int tvi_farneback_f32(const uint8_t* prev, const uint8_t* next, int c
   TVI_CHECK_ARG(prev && next && flow && workspace, "tvi_farneback_f32: null pointer");
   TVI_CHECK_ARG(channels == 1 || channels == 3, "tvi_farneback_f32: images must be 8-bit gray (1) or BGR (3), got %d channels", channels);
   TVI_CHECK_ARG(pyr_scale > 0 && pyr_scale < 1 && levels >= 0, "tvi_farneback_f32: pyr_scale must be in (0, 1) and levels >= 0");
-  TVI_CHECK_ARG(winsize >= 1 && winsize % 2 == 1 && iterations >= 1, "tvi_farneback_f32: winsize must be odd, iterations >= 1");
+  TVI_CHECK_ARG(winsize >= 1 && winsize % 2 == 1 && winsize <= 2 * kBoxMaxM + 1 && iterations >= 1,
+                "tvi_farneback_f32: winsize must be odd and at most %d, iterations >= 1", 2 * kBoxMaxM + 1);
   TVI_CHECK_ARG(poly_n >= 1 && poly_n <= 15, "tvi_farneback_f32: poly_n=%d outside [1, 15]", poly_n);
   TVI_CHECK_ARG((uintptr_t)workspace % 16 == 0 && (uintptr_t)flow % 8 == 0, "tvi_farneback_f32: misaligned pointer");
   TVI_CHECK_ARG(H <= 65535, "tvi_farneback_f32: more than 65535 rows");
