@@ -175,3 +175,25 @@ def test_farneback_full_hd_and_edge_cases(cuda):
         ops.farneback(torch.zeros(8, 8, 2, dtype=torch.uint8, device=cuda), torch.zeros(8, 8, 2, dtype=torch.uint8, device=cuda))
     with pytest.raises(_lib.TviError):
         ops.farneback(torch.zeros(8, 8, dtype=torch.float32, device=cuda), torch.zeros(8, 8, dtype=torch.float32, device=cuda))
+
+
+def test_check_clip_flows_matches_the_reference_loop(cuda):
+    # dataset_construction/step4_flow_check.py:55-81 on a 5-frame clip: steady shift, then a jump backwards (an outlier)
+    import numpy as np
+    from oracle import farneback_ref
+    rng = np.random.default_rng(3)
+    base = np.kron(rng.random((12, 14, 3)), np.ones((8, 8, 1)))
+    base = (base * 200 + 25 * rng.random(base.shape)).astype(np.uint8)
+    shifts = [0, 2, 4, 6, 1]
+    frames = np.stack([np.roll(base, s, axis=1)[8:-8, 8:-8] for s in shifts])          # [5, 80, 96, 3]
+    flows, sims, flagged = tvi.check_clip_flows(frames)
+    assert flows.shape == (4, 80, 96, 2) and sims.shape == (3,) and flagged.dtype == torch.bool
+    want_flows = [farneback_ref.calc_optical_flow_farneback(farneback_ref.gray_from_bgr(frames[i]), farneback_ref.gray_from_bgr(frames[i + 1]))
+                  for i in range(4)]
+    for i in range(4):
+        assert np.abs(flows[i].cpu().numpy() - want_flows[i]).max() < 5e-3
+    want_sims = [flow_ref.cosine_similarity(want_flows[i], want_flows[i + 1]) for i in range(3)]
+    assert np.abs(sims.cpu().numpy() - np.array(want_sims)).max() < 1e-4
+    assert flagged.cpu().tolist() == [bool(s < 0.5) for s in want_sims] == [False, False, True]
+    with pytest.raises(ValueError):
+        tvi.check_clip_flows(frames[:2])

@@ -14,13 +14,13 @@ from . import _lib, ops  # noqa: F401
 from ._lib import TviError, version  # noqa: F401
 from .blocks import install_blocks, uninstall_blocks  # noqa: F401
 from .feedforward import feed_forward, install_feed_forward, layer_norm, uninstall_feed_forward  # noqa: F401
-from .flow import backward_warp_check, compute_optical_flow_farneback, cosine_similarity, cosine_similarity_chw  # noqa: F401
+from .flow import backward_warp_check, check_clip_flows, compute_optical_flow_farneback, cosine_similarity, cosine_similarity_chw  # noqa: F401
 from .processor import TviAttnProcessor, install, uninstall  # noqa: F401
 from .slerp import slerp  # noqa: F401
 from .step import EulerCfgStepper  # noqa: F401
 from .spatio_temporal import install_spatio_temporal, uninstall_spatio_temporal  # noqa: F401
 
 __all__ = ["TviAttnProcessor", "install", "uninstall", "slerp", "cosine_similarity", "cosine_similarity_chw",
-           "backward_warp_check", "compute_optical_flow_farneback", "feed_forward", "layer_norm", "install_feed_forward", "uninstall_feed_forward",
+           "backward_warp_check", "compute_optical_flow_farneback", "check_clip_flows", "feed_forward", "layer_norm", "install_feed_forward", "uninstall_feed_forward",
            "install_blocks", "uninstall_blocks", "EulerCfgStepper", "install_spatio_temporal", "uninstall_spatio_temporal",
            "TviError", "version", "ops"]

@@ -31,6 +31,22 @@ def compute_optical_flow_farneback(img1, img2):
     return ops.farneback(img1, img2)
 
 
+def check_clip_flows(frames, threshold: float = 0.5):
+    """The per-video body of dataset_construction/step4_flow_check.py:55-81 without leaving the device: Farneback flow of
+    every consecutive frame pair, cosine similarity of every consecutive flow pair, outlier flag `sim < threshold` (:80).
+    frames: [N, H, W, 3] BGR uint8 (numpy or CUDA tensor), N >= 3 (:50).  Returns (flows [N-1, H, W, 2] fp32 CUDA,
+    sims [N-2] fp32 CUDA, flagged [N-2] bool CUDA); nothing synchronises the host."""
+    t = torch.from_numpy(np.ascontiguousarray(frames, dtype=np.uint8)).cuda(non_blocking=True) if isinstance(frames, np.ndarray) else frames
+    if t.dim() != 4 or t.shape[0] < 3 or t.shape[-1] != 3 or t.dtype != torch.uint8:
+        raise ValueError("frames must be [N >= 3, H, W, 3] uint8 (the reference skips shorter clips, :50-51)")
+    N, H, W, _ = t.shape
+    flows = torch.empty(N - 1, H, W, 2, dtype=torch.float32, device=t.device)
+    for i in range(N - 1):
+        ops.farneback(t[i], t[i + 1], out=flows[i])
+    sims = ops.flow_cosine_f32(flows[:-1], flows[1:], hwc=True)
+    return flows, sims, sims < threshold
+
+
 def cosine_similarity(flow_a, flow_b):
     if isinstance(flow_a, np.ndarray):
         a = torch.from_numpy(np.ascontiguousarray(flow_a, dtype=np.float32))
