@@ -154,3 +154,21 @@ def test_graphed_forward_replays_bit_exact(cuda):
         assert torch.equal(y, want)
     with pytest.raises(_lib.TviError):
         fwd(x[:7], encoder_hidden_states=e, image_only_indicator=ind)
+
+
+def test_alpha_cache_follows_the_indicator(cuda):
+    m = _model(320, 5, 1024, 5, cuda)
+    spatio_temporal.install_spatio_temporal(m)
+    g = torch.Generator().manual_seed(2)
+    x = _bf(torch.randn(4, 320, 8, 8, generator=g), cuda)
+    e = _bf(torch.randn(4, 1, 1024, generator=g), cuda)
+    ind = torch.zeros(1, 4, device=cuda)
+    with torch.no_grad():
+        y0 = m(x, encoder_hidden_states=e, image_only_indicator=ind, return_dict=False)[0]
+        y0b = m(x, encoder_hidden_states=e, image_only_indicator=ind, return_dict=False)[0]   # cached alpha
+        ind[0, 1] = 1.0                                                                          # in-place edit bumps _version
+        y1 = m(x, encoder_hidden_states=e, image_only_indicator=ind, return_dict=False)[0]
+    assert torch.equal(y0, y0b)
+    assert torch.equal(y0[[0, 2, 3]], y1[[0, 2, 3]]) and not torch.equal(y0[1], y1[1])
+    ref = spatio_temporal_ref.transformer_spatio_temporal_ref(m, x, e, ind, alpha_dtype=torch.bfloat16)
+    assert float((y1.float().cpu() - ref).abs().max()) <= TOL * max(1.0, float(ref.abs().max()))

@@ -16,6 +16,7 @@ from __future__ import annotations
 
 import sys
 import types
+import weakref
 from dataclasses import dataclass
 from typing import Optional
 
@@ -55,6 +56,20 @@ def _alpha(mixer, image_only_indicator: torch.Tensor) -> torch.Tensor:
     """One fp32 alpha per frame: AlphaBlender.get_alpha for ndims == 3, with the reference's cast to the activation
     dtype (`.to(x_spatial.dtype)`) applied so that the blend weights are the bf16-rounded ones."""
     strategy = getattr(mixer, "merge_strategy", "learned_with_images")
+    # the same indicator tensor comes back for every module of every denoising step: cache on (tensor, version)
+    sig = (image_only_indicator.data_ptr(), image_only_indicator._version, tuple(image_only_indicator.shape),
+           mixer.mix_factor.data_ptr(), mixer.mix_factor._version)
+    if torch.cuda.is_current_stream_capturing():  # a CUDA graph must recompute alpha from the static indicator buffer
+        return _alpha_uncached(mixer, image_only_indicator, strategy)
+    hit = getattr(mixer, "_tvi_alpha", None)
+    if hit is not None and hit[0] == sig and hit[1]() is image_only_indicator:
+        return hit[2]
+    a = _alpha_uncached(mixer, image_only_indicator, strategy)
+    mixer._tvi_alpha = (sig, weakref.ref(image_only_indicator), a)
+    return a
+
+
+def _alpha_uncached(mixer, image_only_indicator: torch.Tensor, strategy: str) -> torch.Tensor:
     ind = image_only_indicator.reshape(-1)
     mf = mixer.mix_factor.detach().float().reshape(-1)[:1]
     if strategy == "fixed":
