@@ -116,6 +116,20 @@ int tvi_layernorm_bf16(const tvi_bf16* x, const tvi_bf16* gamma, const tvi_bf16*
 int tvi_bcast_rows_add_bf16(const tvi_bf16* v, const tvi_bf16* residual, tvi_bf16* out, int64_t nrows, int64_t rows_per_group,
                             int64_t group_inner, int C, int64_t ldv, int64_t ldr, int64_t ldo, void* stream);
 
+/* Backward of the N1 row (training config 5 through the block-level swap; autograd's native_layer_norm_backward and the
+ * backward of diffusers' GEGLU.forward):
+ *   layernorm_bwd : dx (nullable), dgamma, dbeta (nullable) from x, dy, gamma; statistics are recomputed from x;
+ *       `workspace` = tvi_layernorm_bwd_workspace_bytes(M, C) bytes of fp32 partials, summed in a fixed order.
+ *   geglu_bwd     : pre = [value | gate] ([M, 2*inner], the recomputed first projection), dh [M, inner] ->
+ *       h = value * gelu(gate) (nullable) and dpre = [dh * gelu(gate) | dh * value * gelu'(gate)] ([M, 2*inner]).
+ */
+size_t tvi_layernorm_bwd_workspace_bytes(int64_t M, int C);
+int tvi_layernorm_bwd_bf16(const tvi_bf16* x, const tvi_bf16* dy, const tvi_bf16* gamma, tvi_bf16* dx, tvi_bf16* dgamma,
+                           tvi_bf16* dbeta, void* workspace, int64_t M, int C, int64_t ldx, int64_t lddy, int64_t lddx, float eps,
+                           void* stream);
+int tvi_geglu_bwd_bf16(const tvi_bf16* pre, const tvi_bf16* dh, tvi_bf16* h, tvi_bf16* dpre, int64_t M, int inner, int64_t ldpre,
+                       int64_t lddh, int64_t ldh, int64_t lddpre, void* stream);
+
 /* Layout glue of TransformerSpatioTemporalModel.forward (rows N1 "AlphaBlender" and N2 of SURVEY 8.6).
  *   groupnorm_tokens : y[n, s, c] = GroupNorm(x)[n, c, s] — `self.norm` (nn.GroupNorm, biased variance, fp32/fp64
  *       statistics) fused with `permute(0, 2, 3, 1).reshape(BF, H*W, C)`, src/models/transformer_temporal.py:300-304.

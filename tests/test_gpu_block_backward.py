@@ -1,0 +1,162 @@
+"""GPU: gradients through the block-level swap (training config 5): LayerNorm, FeedForward (GEGLU) and whole-block backward
+against fp32 autograd of the same math (tolerance 2e-2 of max |grad|, as for the attention backward)."""
+import pytest
+import torch
+import torch.nn.functional as F
+
+import timelapse_video_interpolation_b200 as tvi
+from timelapse_video_interpolation_b200 import blocks, ops
+from timelapse_video_interpolation_b200.modules import BasicTransformerBlock, FeedForward, TemporalBasicTransformerBlock
+
+pytestmark = pytest.mark.gpu
+GTOL = 2e-2
+
+
+def _close(name, got, ref):
+    ref = ref.float().cpu()
+    err = float((got.float().cpu() - ref).abs().max())
+    scale = max(float(ref.abs().max()), 1e-6)
+    print(f"  {name}: max abs err {err:.3e} / max |ref| {scale:.3e}")
+    assert err <= GTOL * scale, name
+
+
+@pytest.mark.parametrize("rows,C", [(300, 320), (130, 640), (77, 1280), (64, 96), (40, 2048)])
+def test_layer_norm_backward(cuda, rows, C):
+    g = torch.Generator().manual_seed(rows + C)
+    norm = torch.nn.LayerNorm(C)
+    with torch.no_grad():
+        norm.weight.copy_(1 + 0.2 * torch.randn(C, generator=g))
+        norm.bias.copy_(0.1 * torch.randn(C, generator=g))
+    norm = norm.to(cuda, torch.bfloat16)
+    x = (torch.randn(rows, C, generator=g) * 1.5 + 0.3).to(torch.bfloat16).to(cuda).requires_grad_(True)
+    wgt = torch.randn(rows, C, generator=g).to(torch.bfloat16).to(cuda)
+    y = tvi.layer_norm(norm, x)
+    assert y.requires_grad
+    (y.float() * wgt.float()).sum().backward()
+    xr = x.detach().float().cpu().requires_grad_(True)
+    gr, br = norm.weight.detach().float().cpu().requires_grad_(True), norm.bias.detach().float().cpu().requires_grad_(True)
+    (F.layer_norm(xr, (C,), gr, br, norm.eps) * wgt.float().cpu()).sum().backward()
+    _close("dx", x.grad, xr.grad)
+    _close("dgamma", norm.weight.grad, gr.grad)
+    _close("dbeta", norm.bias.grad, br.grad)
+
+
+def _ff_ref(x, w1, b1, w2, b2):
+    hidden, gate = F.linear(x, w1, b1).chunk(2, dim=-1)
+    return F.linear(hidden * F.gelu(gate), w2, b2)
+
+
+@pytest.mark.parametrize("rows,dim", [(300, 320), (1000, 640), (64, 96)])
+def test_feed_forward_backward(cuda, rows, dim):
+    g = torch.Generator().manual_seed(rows)
+    ff = FeedForward(dim)
+    with torch.no_grad():
+        for p in ff.parameters():
+            p.copy_(torch.randn(p.shape, generator=g) * (p.shape[-1] ** -0.5 if p.dim() > 1 else 0.1))
+    ff = ff.to(cuda, torch.bfloat16)
+    x = torch.randn(rows, dim, generator=g).to(torch.bfloat16).to(cuda).requires_grad_(True)
+    wgt = torch.randn(rows, dim, generator=g).to(torch.bfloat16).to(cuda)
+    launches0 = ops.LAUNCHES
+    y = tvi.feed_forward(ff, x)
+    (y.float() * wgt.float()).sum().backward()
+    assert ops.LAUNCHES - launches0 >= 9      # 2 forward GEMMs, recompute, dgrad x2, geglu_bwd, wgrad x2, column sums
+    names = ["net.0.proj.weight", "net.0.proj.bias", "net.2.weight", "net.2.bias"]
+    ps = dict(ff.named_parameters())
+    ref = [ps[n].detach().float().cpu().requires_grad_(True) for n in names]
+    xr = x.detach().float().cpu().requires_grad_(True)
+    (_ff_ref(xr, *ref) * wgt.float().cpu()).sum().backward()
+    _close("dx", x.grad, xr.grad)
+    for n, r in zip(names, ref):
+        _close(n, ps[n].grad, r.grad)
+    # frozen weights: only dx is produced
+    for p in ff.parameters():
+        p.requires_grad_(False)
+        p.grad = None
+    x2 = x.detach().clone().requires_grad_(True)
+    (tvi.feed_forward(ff, x2).float() * wgt.float()).sum().backward()
+    assert torch.equal(x2.grad, x.grad) and all(p.grad is None for p in ff.parameters())
+
+
+def _attn_ref(x, e, wq, wk, wv, wo, bo, heads):
+    B, S, C = x.shape
+    ctx = x if e is None else e
+    q, k, v = F.linear(x, wq), F.linear(ctx, wk), F.linear(ctx, wv)
+    d = C // heads
+    sp = lambda t: t.view(B, -1, heads, d).transpose(1, 2)
+    o = torch.softmax(sp(q) @ sp(k).transpose(-1, -2) * d ** -0.5, dim=-1) @ sp(v)
+    return F.linear(o.transpose(1, 2).reshape(B, S, C), wo, bo)
+
+
+def _block_ref(P, x, e, heads, temporal=False, T=None):
+    ln = lambda n, t: F.layer_norm(t, (t.shape[-1],), P[n + ".weight"], P[n + ".bias"], 1e-5)
+    at = lambda n, t, c: _attn_ref(t, c, P[n + ".to_q.weight"], P[n + ".to_k.weight"], P[n + ".to_v.weight"], P[n + ".to_out.0.weight"],
+                                   P[n + ".to_out.0.bias"], heads)
+    ffn = lambda n, t: _ff_ref(t, P[n + ".net.0.proj.weight"], P[n + ".net.0.proj.bias"], P[n + ".net.2.weight"], P[n + ".net.2.bias"])
+    if temporal:
+        BF, S, C = x.shape
+        B = BF // T
+        x = x.reshape(B, T, S, C).permute(0, 2, 1, 3).reshape(B * S, T, C)
+        x = ffn("ff_in", ln("norm_in", x)) + x
+    x = at("attn1", ln("norm1", x), None) + x
+    x = at("attn2", ln("norm2", x), e) + x
+    x = ffn("ff", ln("norm3", x)) + x
+    if temporal:
+        x = x.reshape(B, S, T, C).permute(0, 2, 1, 3).reshape(B * T, S, C)
+    return x
+
+
+def _init_block(blk, seed, cuda):
+    g = torch.Generator().manual_seed(seed)
+    with torch.no_grad():
+        for name, p in blk.named_parameters():
+            if "norm" in name:
+                p.copy_(1 + 0.1 * torch.randn(p.shape, generator=g) if name.endswith("weight") else 0.05 * torch.randn(p.shape, generator=g))
+            else:
+                p.copy_(torch.randn(p.shape, generator=g) * (p.shape[-1] ** -0.5 if p.dim() > 1 else 0.05))
+    return blk.to(cuda, torch.bfloat16)
+
+
+CHECK = ["norm1.weight", "norm3.bias", "attn1.to_q.weight", "attn2.to_v.weight", "attn2.to_out.0.bias", "ff.net.0.proj.weight",
+         "ff.net.0.proj.bias", "ff.net.2.weight"]
+
+
+@pytest.mark.parametrize("temporal", [False, True], ids=["spatial", "temporal"])
+def test_block_backward_matches_fp32_autograd(cuda, temporal):
+    C, heads, T = 320, 5, 14
+    if temporal:
+        blk = _init_block(TemporalBasicTransformerBlock(C, C, heads, 1024), 8, cuda)
+        B, S, L = 1, 24, 2
+        x_shape, e_shape = (B * T, S, C), (B * S, L, 1024)
+    else:
+        blk = _init_block(BasicTransformerBlock(C, heads, 1024), 7, cuda)
+        x_shape, e_shape = (2, 144, C), (2, 2, 1024)
+    blocks.install_blocks(blk)
+    g = torch.Generator().manual_seed(5)
+    x = torch.randn(x_shape, generator=g).to(torch.bfloat16).to(cuda).requires_grad_(True)
+    e = torch.randn(e_shape, generator=g).to(torch.bfloat16).to(cuda).requires_grad_(True)
+    wgt = torch.randn(x_shape, generator=g).to(torch.bfloat16).to(cuda)
+    y = blk(x, num_frames=T, encoder_hidden_states=e) if temporal else blk(x, encoder_hidden_states=e)
+    assert y.requires_grad and y.shape == x.shape
+    (y.float() * wgt.float()).sum().backward()
+    P = {n: p.detach().float().cpu().requires_grad_(True) for n, p in blk.named_parameters()}
+    xr, er = x.detach().float().cpu().requires_grad_(True), e.detach().float().cpu().requires_grad_(True)
+    yr = _block_ref(P, xr, er, heads, temporal, T)
+    _close("forward", y.detach(), yr.detach())
+    (yr * wgt.float().cpu()).sum().backward()
+    _close("dx", x.grad, xr.grad)
+    _close("d encoder_hidden_states", e.grad, er.grad)
+    ps = dict(blk.named_parameters())
+    for n in CHECK + (["norm_in.weight", "ff_in.net.2.bias"] if temporal else []):
+        _close(n, ps[n].grad, P[n].grad)
+
+
+def test_frozen_spatial_block_under_no_grad_still_uses_the_fast_path(cuda):
+    blk = _init_block(BasicTransformerBlock(320, 5, 1024), 9, cuda)
+    blocks.install_blocks(blk)
+    x = torch.randn(2, 64, 320, device=cuda).to(torch.bfloat16)
+    e = torch.randn(2, 1, 1024, device=cuda).to(torch.bfloat16)
+    with torch.no_grad():
+        y0 = blk(x, encoder_hidden_states=e)
+    y1 = blk(x.clone().requires_grad_(True), encoder_hidden_states=e)     # tape path
+    assert not y0.requires_grad and y1.requires_grad
+    assert float((y0.float() - y1.detach().float()).abs().max()) <= 2e-2 * max(1.0, float(y0.float().abs().max()))

@@ -57,13 +57,13 @@ def test_feed_forward_with_fused_residual_and_install(cuda):
     assert float((y3.float().cpu() - ref2).abs().max()) <= 2 * TOL * max(1.0, float(ref2.abs().max()))
 
 
-def test_feed_forward_refuses_gradients_and_bad_inputs(cuda):
+def test_feed_forward_rejects_bad_inputs(cuda):
     ff = _ff(320, None, 6, cuda)
-    x = torch.randn(2, 16, 320, device=cuda).to(torch.bfloat16).requires_grad_(True)
-    with pytest.raises(NotImplementedError):
-        tvi.feed_forward(ff, x)
+    x = torch.randn(2, 16, 320, device=cuda).to(torch.bfloat16)
     with torch.no_grad(), pytest.raises(tvi.TviError):
         tvi.feed_forward(ff, x.float())
+    with torch.no_grad(), pytest.raises(tvi.TviError):
+        tvi.feed_forward(ff, x.cpu())
 
 
 @pytest.mark.parametrize("rows,C", [(1000, 320), (4032, 640), (333, 1280), (50, 2048), (7, 8)])
@@ -176,11 +176,3 @@ def test_bcast_rows_add_group_inner(cuda):
     assert torch.equal(got, v.view(B, 1, S, C).expand(B, T, S, C).reshape(-1, C))
     got = ops.bcast_rows_add(v, None, T)  # contiguous groups
     assert torch.equal(got, v.view(B * S, 1, C).expand(B * S, T, C).reshape(-1, C))
-
-
-def test_block_forward_refuses_gradients(cuda):
-    blk = _init(BasicTransformerBlock(320, 5, 1024), 5, cuda)
-    blocks.install_blocks(blk)
-    x = torch.randn(2, 64, 320, device=cuda).to(torch.bfloat16).requires_grad_(True)
-    with pytest.raises(NotImplementedError):
-        blk(x, encoder_hidden_states=torch.randn(2, 1, 1024, device=cuda).to(torch.bfloat16))

@@ -12,8 +12,10 @@ row stride of S (`tvi_attn_temporal_fwd_interleaved`, `tvi_bcast_rows_add_bf16(g
 than one key (or a ramp-bias / statistics processor) fall back to the permute copies.
 
 `install_blocks(model)` re-binds `forward` on every module with the block's attribute layout (duck-typed) and installs
-the attention processor on its Attention modules.  Inference only: the FeedForward / LayerNorm backward is not built,
-so a call that needs gradients raises instead of silently detaching.
+the attention processor on its Attention modules.  Training (config 5) works through the same forwards: when a gradient is
+required LayerNorm, attention and FeedForward go on the autograd tape through their libtvi Functions (forward and backward
+kernels), the residual adds and the temporal re-layout are torch ops on the tape (the fused-residual / folded-layout
+fast paths are inference-only).
 """
 from __future__ import annotations
 
@@ -30,9 +32,16 @@ __all__ = ["basic_transformer_block_forward", "temporal_basic_transformer_block_
 
 
 def _no_grad_only(block, x):
+    """The MODULE-level forward (GroupNorm / layout kernels) has no backward; the block forwards do (see _training)."""
     if torch.is_grad_enabled() and (x.requires_grad or any(p.requires_grad for p in block.parameters())):
-        raise NotImplementedError("libtvi block forwards are inference-only (FeedForward / LayerNorm backward is not built): "
-                                  "call under torch.no_grad(), or install only the attention processor for training")
+        raise NotImplementedError("the libtvi TransformerSpatioTemporalModel forward is inference-only (GroupNorm / layout "
+                                  "kernels have no backward): call under torch.no_grad(), or install only the blocks for training")
+
+
+def _training(block, x) -> bool:
+    """True when the call must go on the autograd tape: LayerNorm, attention and FeedForward then run through their
+    autograd Functions (libtvi forward AND backward kernels); residual adds and the temporal re-layout stay torch ops."""
+    return torch.is_grad_enabled() and (x.requires_grad or any(p.requires_grad for p in block.parameters()))
 
 
 def _proc(attn):
@@ -64,7 +73,6 @@ def basic_transformer_block_forward(block, hidden_states: torch.Tensor, attentio
         raise _lib.TviError(_lib.TVI_ERR_UNSUPPORTED, "block forward: attention masks are not supported (SVD never passes one)")
     if cross_attention_kwargs and any(k != "scale" for k in cross_attention_kwargs):
         raise _lib.TviError(_lib.TVI_ERR_UNSUPPORTED, "block forward: unsupported cross_attention_kwargs")
-    _no_grad_only(block, hidden_states)
     x = hidden_states.contiguous()
     # 0. self-attention (:270-287): norm1 -> attn1 -> + hidden_states
     n = layer_norm(block.norm1, x)
@@ -85,11 +93,10 @@ def temporal_basic_transformer_block_forward(block, hidden_states: torch.Tensor,
     permute copies (same results bit for bit — every kernel computes a row independently of its position)."""
     if getattr(block, "_chunk_size", None) is not None:
         raise _lib.TviError(_lib.TVI_ERR_UNSUPPORTED, "block forward: chunked feed-forward is not supported")
-    _no_grad_only(block, hidden_states)
     BF, S, C = hidden_states.shape
     B = BF // num_frames
     attn2 = getattr(block, "attn2", None)
-    in_place = fold_layout and num_frames <= 64 and (attn2 is None or encoder_hidden_states is None or (
+    in_place = fold_layout and not _training(block, hidden_states) and num_frames <= 64 and (attn2 is None or encoder_hidden_states is None or (
         encoder_hidden_states.shape[1] == 1 and not _proc(attn2).ramp_bias and _proc(attn2).stats_sink is None))
     if in_place:
         # every op but the attention cores is row-wise: stay in the [B*T, S, C] token order, no permute copies

@@ -258,3 +258,216 @@ extern "C" int tvi_layernorm_bf16(const tvi_bf16* x, const tvi_bf16* gamma, cons
   if (C8 <= 128) return launch_ln<4, 2>(x, gamma, beta, y, M, C8, ldx, ldy, eps, st);
   return launch_ln<8, 1>(x, gamma, beta, y, M, C8, ldx, ldy, eps, st);
 }
+
+// ---------------------------------------------------------------------------------------------------------------
+// LayerNorm backward (training config 5 through the block-level swap): with xhat = (x - mean) * rstd, g = dy * gamma
+//   dx     = rstd * (g - mean_c(g) - xhat * mean_c(g * xhat))
+//   dgamma = sum_rows dy * xhat,   dbeta = sum_rows dy
+// (autograd's native_layer_norm_backward).  One warp per row recomputes the statistics from x (nothing is saved by the
+// forward); the row sums of dgamma / dbeta are accumulated per block in shared memory in a fixed order and written as
+// fp32 partials [blocks][2][C]; `ln_bwd_final_kernel` adds the partials in order -> deterministic, no atomics.
+namespace tvi {
+namespace {
+
+constexpr int kLnBwdWarps = 8;
+constexpr int kLnBwdRowsPerWarp = 16;
+
+template <int NCH>
+__global__ void __launch_bounds__(kLnBwdWarps * 32)
+layernorm_bwd_kernel(const tvi_bf16* __restrict__ x, const tvi_bf16* __restrict__ dy, const tvi_bf16* __restrict__ gamma,
+                     tvi_bf16* __restrict__ dx, float* __restrict__ partial, int64_t M, int C8, int64_t ldx, int64_t lddy,
+                     int64_t lddx, float eps) {
+  extern __shared__ float s_acc[];  // [warps][2][C]
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int C = C8 * 8;
+  float dg[NCH][8], db[NCH][8], gm[NCH][8];
+#pragma unroll
+  for (int i = 0; i < NCH; ++i) {
+    const int c = lane + 32 * i;
+#pragma unroll
+    for (int q = 0; q < 8; ++q) dg[i][q] = db[i][q] = 0.f, gm[i][q] = 1.f;
+    if (c < C8 && gamma != nullptr) {
+      const uint4 u = __ldg(reinterpret_cast<const uint4*>(gamma) + c);
+      const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&u);
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const float2 t = __bfloat1622float2(h[q]);
+        gm[i][2 * q] = t.x;
+        gm[i][2 * q + 1] = t.y;
+      }
+    }
+  }
+  const float inv_c = 1.0f / (float)C;
+  const int64_t row0 = ((int64_t)blockIdx.x * kLnBwdWarps + warp) * kLnBwdRowsPerWarp;
+  for (int r = 0; r < kLnBwdRowsPerWarp; ++r) {
+    const int64_t row = row0 + r;
+    if (row >= M) break;
+    float xv[NCH][8], gv[NCH][8];
+    float sum = 0.f;
+#pragma unroll
+    for (int i = 0; i < NCH; ++i) {
+      const int c = lane + 32 * i;
+      if (c < C8) {
+        const uint4 ux = __ldg(reinterpret_cast<const uint4*>(x + row * ldx) + c);
+        const uint4 ud = __ldg(reinterpret_cast<const uint4*>(dy + row * lddy) + c);
+        const __nv_bfloat162* hx = reinterpret_cast<const __nv_bfloat162*>(&ux);
+        const __nv_bfloat162* hd = reinterpret_cast<const __nv_bfloat162*>(&ud);
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          const float2 a = __bfloat1622float2(hx[q]), b = __bfloat1622float2(hd[q]);
+          xv[i][2 * q] = a.x;
+          xv[i][2 * q + 1] = a.y;
+          gv[i][2 * q] = b.x;
+          gv[i][2 * q + 1] = b.y;
+          sum += a.x + a.y;
+        }
+      } else {
+#pragma unroll
+        for (int q = 0; q < 8; ++q) xv[i][q] = gv[i][q] = 0.f;
+      }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+    const float mean = sum * inv_c;
+    float sq = 0.f;
+#pragma unroll
+    for (int i = 0; i < NCH; ++i)
+      if (lane + 32 * i < C8) {
+#pragma unroll
+        for (int q = 0; q < 8; ++q) {
+          xv[i][q] -= mean;
+          sq = fmaf(xv[i][q], xv[i][q], sq);
+        }
+      }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) sq += __shfl_xor_sync(0xffffffffu, sq, o);
+    const float rstd = rsqrtf(sq * inv_c + eps);
+    float s1 = 0.f, s2 = 0.f;  // sum g, sum g * xhat
+#pragma unroll
+    for (int i = 0; i < NCH; ++i)
+      if (lane + 32 * i < C8) {
+#pragma unroll
+        for (int q = 0; q < 8; ++q) {
+          const float xhat = xv[i][q] * rstd;
+          const float dyv = gv[i][q];
+          dg[i][q] = fmaf(dyv, xhat, dg[i][q]);
+          db[i][q] += dyv;
+          const float g = dyv * gm[i][q];
+          xv[i][q] = xhat;
+          gv[i][q] = g;
+          s1 += g;
+          s2 = fmaf(g, xhat, s2);
+        }
+      }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      s1 += __shfl_xor_sync(0xffffffffu, s1, o);
+      s2 += __shfl_xor_sync(0xffffffffu, s2, o);
+    }
+    s1 *= inv_c;
+    s2 *= inv_c;
+    if (dx != nullptr) {
+#pragma unroll
+      for (int i = 0; i < NCH; ++i) {
+        const int c = lane + 32 * i;
+        if (c < C8) {
+          float o[8];
+#pragma unroll
+          for (int q = 0; q < 8; ++q) o[q] = rstd * (gv[i][q] - s1 - xv[i][q] * s2);
+          *(reinterpret_cast<uint4*>(dx + row * lddx) + c) =
+              make_uint4(pack_bf16x2(o[0], o[1]), pack_bf16x2(o[2], o[3]), pack_bf16x2(o[4], o[5]), pack_bf16x2(o[6], o[7]));
+        }
+      }
+    }
+  }
+  // per-block reduction over the warps in a fixed order
+  float* mine = s_acc + (size_t)warp * 2 * C;
+#pragma unroll
+  for (int i = 0; i < NCH; ++i) {
+    const int c = lane + 32 * i;
+    if (c < C8) {
+#pragma unroll
+      for (int q = 0; q < 8; ++q) {
+        mine[c * 8 + q] = dg[i][q];
+        mine[C + c * 8 + q] = db[i][q];
+      }
+    }
+  }
+  __syncthreads();
+  for (int j = threadIdx.x; j < 2 * C; j += blockDim.x) {
+    float s = 0.f;
+    for (int w = 0; w < kLnBwdWarps; ++w) s += s_acc[(size_t)w * 2 * C + j];
+    partial[(size_t)blockIdx.x * 2 * C + j] = s;
+  }
+}
+
+__global__ void ln_bwd_final_kernel(const float* __restrict__ partial, tvi_bf16* __restrict__ dgamma, tvi_bf16* __restrict__ dbeta,
+                                    int nblocks, int C) {
+  const int j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= 2 * C) return;
+  float s = 0.f;
+  for (int b = 0; b < nblocks; ++b) s += partial[(size_t)b * 2 * C + j];
+  tvi_bf16* dst = j < C ? dgamma : dbeta;
+  if (dst != nullptr) reinterpret_cast<__nv_bfloat16*>(dst)[j < C ? j : j - C] = __float2bfloat16_rn(s);
+}
+
+int64_t ln_bwd_blocks(int64_t M) {
+  const int64_t rows_per_block = (int64_t)kLnBwdWarps * kLnBwdRowsPerWarp;
+  return (M + rows_per_block - 1) / rows_per_block;
+}
+
+template <int NCH>
+int launch_ln_bwd(const tvi_bf16* x, const tvi_bf16* dy, const tvi_bf16* gamma, tvi_bf16* dx, float* partial, int64_t M, int C8,
+                  int64_t ldx, int64_t lddy, int64_t lddx, float eps, cudaStream_t st) {
+  const size_t smem = (size_t)kLnBwdWarps * 2 * C8 * 8 * sizeof(float);
+  static bool configured = false;
+  if (!configured) {
+    TVI_CUDA_OK(cudaFuncSetAttribute(layernorm_bwd_kernel<NCH>, cudaFuncAttributeMaxDynamicSharedMemorySize, 8 * 2 * 2048 * 4));
+    configured = true;
+  }
+  layernorm_bwd_kernel<NCH><<<(unsigned)ln_bwd_blocks(M), kLnBwdWarps * 32, smem, st>>>(x, dy, gamma, dx, partial, M, C8, ldx, lddy,
+                                                                                         lddx, eps);
+  TVI_LAUNCH_OK("layernorm_bwd_kernel");
+  return TVI_OK;
+}
+
+}  // namespace
+}  // namespace tvi
+
+extern "C" size_t tvi_layernorm_bwd_workspace_bytes(int64_t M, int C) {
+  if (M <= 0 || C <= 0) return 0;
+  return (size_t)tvi::ln_bwd_blocks(M) * 2 * (size_t)C * sizeof(float);
+}
+
+extern "C" int tvi_layernorm_bwd_bf16(const tvi_bf16* x, const tvi_bf16* dy, const tvi_bf16* gamma, tvi_bf16* dx, tvi_bf16* dgamma,
+                                      tvi_bf16* dbeta, void* workspace, int64_t M, int C, int64_t ldx, int64_t lddy, int64_t lddx,
+                                      float eps, void* stream) {
+  using namespace tvi;
+  TVI_CHECK_ARG(M >= 0 && C >= 0, "tvi_layernorm_bwd_bf16: negative size");
+  if (M == 0 || C == 0) return TVI_OK;
+  TVI_CHECK_ARG(x && dy && workspace, "tvi_layernorm_bwd_bf16: null pointer");
+  TVI_CHECK_ARG(C % 8 == 0 && C <= 2048, "tvi_layernorm_bwd_bf16: C=%d must be a multiple of 8 and at most 2048", C);
+  TVI_CHECK_ARG(ldx % 8 == 0 && lddy % 8 == 0 && ldx >= C && lddy >= C && (dx == nullptr || (lddx % 8 == 0 && lddx >= C)),
+                "tvi_layernorm_bwd_bf16: bad row strides");
+  TVI_CHECK_ARG(((uintptr_t)x | (uintptr_t)dy | (uintptr_t)dx | (uintptr_t)gamma | (uintptr_t)workspace) % 16 == 0,
+                "tvi_layernorm_bwd_bf16: pointers must be 16-byte aligned");
+  TVI_CHECK_ARG(eps > 0.f, "tvi_layernorm_bwd_bf16: eps must be positive");
+  TVI_CHECK_ARG(ln_bwd_blocks(M) < ((int64_t)1 << 31), "tvi_layernorm_bwd_bf16: too many rows for one call");
+  cudaStream_t st = (cudaStream_t)stream;
+  const int C8 = C / 8;
+  int rc;
+  if (C8 <= 64)
+    rc = launch_ln_bwd<2>(x, dy, gamma, dx, (float*)workspace, M, C8, ldx, lddy, lddx, eps, st);
+  else if (C8 <= 128)
+    rc = launch_ln_bwd<4>(x, dy, gamma, dx, (float*)workspace, M, C8, ldx, lddy, lddx, eps, st);
+  else if (C8 <= 160)
+    rc = launch_ln_bwd<5>(x, dy, gamma, dx, (float*)workspace, M, C8, ldx, lddy, lddx, eps, st);
+  else
+    rc = launch_ln_bwd<8>(x, dy, gamma, dx, (float*)workspace, M, C8, ldx, lddy, lddx, eps, st);
+  if (rc) return rc;
+  if (dgamma != nullptr || dbeta != nullptr) {
+    ln_bwd_final_kernel<<<(2 * C + 255) / 256, 256, 0, st>>>((const float*)workspace, dgamma, dbeta, (int)ln_bwd_blocks(M), C);
+    TVI_LAUNCH_OK("ln_bwd_final_kernel");
+  }
+  return TVI_OK;
+}

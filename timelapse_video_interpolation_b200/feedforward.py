@@ -61,6 +61,75 @@ def _bf16(t):
     return None if t is None else (t if t.dtype == torch.bfloat16 else t.detach().to(torch.bfloat16)).contiguous()
 
 
+def _cast_grad(g, like):
+    return None if g is None else (g if g.dtype == like.dtype else g.to(like.dtype)).view(like.shape)
+
+
+class _FeedForwardFn(torch.autograd.Function):
+    """Tape entry of `Linear(C -> 2*inner) -> GEGLU -> Linear(inner -> C_out)` (reference src/models/attention.py:526-535).
+    Saves only x: the backward recomputes the first projection with the plain GEMM (the fused forward never writes it),
+    gets h and d(pre) from one elementwise kernel, and runs the dgrad / wgrad / column-sum kernels of the projections."""
+
+    @staticmethod
+    def forward(ctx, x, w1, b1, w2, b2):
+        x2 = x.detach().contiguous().view(-1, x.shape[-1])
+        with torch.no_grad():
+            w1b, w2b = _bf16(w1), _bf16(w2)
+            inner = w1b.shape[0] // 2
+            H = ops.geglu_block(inner)
+            if H == 0:
+                raise _lib.TviError(_lib.TVI_ERR_UNSUPPORTED, f"GEGLU inner width {inner} is not a multiple of 32")
+            wi = torch.stack([w1b[:inner].view(inner // H, H, -1), w1b[inner:].view(inner // H, H, -1)], dim=1).reshape(2 * inner, -1)
+            bi = None
+            if b1 is not None:
+                bb = _bf16(b1)
+                bi = torch.stack([bb[:inner].view(inner // H, H), bb[inner:].view(inner // H, H)], dim=1).reshape(-1).contiguous()
+            h = ops.gemm_bf16_tn_ex(x2, wi.contiguous(), bi, geglu=True)
+            y = ops.gemm_bf16_tn(h, w2b, _bf16(b2))
+        ctx.save_for_backward(x2, w1, b1, w2, b2)
+        ctx.x_shape = x.shape
+        return y.view(*x.shape[:-1], -1)
+
+    @staticmethod
+    def backward(ctx, dy):
+        x2, w1, b1, w2, b2 = ctx.saved_tensors
+        need_x, need_w1, need_b1, need_w2, need_b2 = ctx.needs_input_grad
+        dy2 = dy.contiguous().view(-1, dy.shape[-1]).to(torch.bfloat16)
+        w1b, w2b = _bf16(w1), _bf16(w2)
+        pre = ops.gemm_bf16_tn(x2, w1b, _bf16(b1))                       # [M, 2*inner] = [value | gate]
+        dh = ops.gemm_bf16_dgrad(dy2, w2b)                               # [M, inner]
+        h, dpre = ops.geglu_bwd(pre, dh, need_h=need_w2)
+        dw2 = ops.gemm_bf16_wgrad(dy2, h) if need_w2 else None
+        db2 = ops.colsum_bf16(dy2, dy2.shape[0]).view(-1) if (need_b2 and b2 is not None) else None
+        dw1 = ops.gemm_bf16_wgrad(dpre, x2) if need_w1 else None
+        db1 = ops.colsum_bf16(dpre, dpre.shape[0]).view(-1) if (need_b1 and b1 is not None) else None
+        dx = ops.gemm_bf16_dgrad(dpre, w1b).view(ctx.x_shape) if need_x else None
+        return dx, _cast_grad(dw1, w1), _cast_grad(db1, b1) if b1 is not None else None, _cast_grad(dw2, w2), \
+            _cast_grad(db2, b2) if b2 is not None else None
+
+
+class _LayerNormFn(torch.autograd.Function):
+    """Tape entry of nn.LayerNorm over the last dimension; the backward recomputes the statistics from x."""
+
+    @staticmethod
+    def forward(ctx, x, gamma, beta, eps):
+        xc = x.detach().contiguous()
+        y = ops.layernorm_bf16(xc, _bf16(gamma), _bf16(beta), eps)
+        ctx.save_for_backward(xc, gamma, beta)
+        ctx.eps = eps
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        xc, gamma, beta = ctx.saved_tensors
+        need_x, need_g, need_b, _ = ctx.needs_input_grad
+        affine = (need_g and gamma is not None) or (need_b and beta is not None)
+        dx, dgamma, dbeta = ops.layernorm_bwd(xc, dy.contiguous().to(torch.bfloat16), _bf16(gamma), ctx.eps, need_dx=need_x,
+                                              need_affine=affine)
+        return dx, _cast_grad(dgamma, gamma) if (need_g and gamma is not None) else None, \
+            _cast_grad(dbeta, beta) if (need_b and beta is not None) else None, None
+
+
 def feed_forward(ff, hidden_states: torch.Tensor, scale: float = 1.0, residual: Optional[torch.Tensor] = None) -> torch.Tensor:
     """`ff(hidden_states)` of a FeedForward module with GEGLU activation; `residual` (same shape as the output)
     is added in the second GEMM's epilogue (the blocks' `ff_output + hidden_states`)."""
@@ -77,8 +146,10 @@ def feed_forward(ff, hidden_states: torch.Tensor, scale: float = 1.0, residual: 
     if x.dtype != torch.bfloat16:
         raise _lib.TviError(_lib.TVI_ERR_UNSUPPORTED, f"feed_forward: hidden_states is {x.dtype}; the libtvi path is bf16")
     if torch.is_grad_enabled() and (x.requires_grad or any(p.requires_grad for p in ff.parameters())):
-        raise NotImplementedError("libtvi FeedForward backward is not built: call under torch.no_grad() or keep the stock "
-                                  "FeedForward for training (DESIGN.md §7)")
+        # training: the call goes on the autograd tape; the residual add has no fused backward and is added on the tape
+        proj, out_lin = ff.net[0].proj, ff.net[2]
+        y = _FeedForwardFn.apply(x, proj.weight, proj.bias, out_lin.weight, out_lin.bias)
+        return y if residual is None else y + residual
     x = x.contiguous()
     wi, bi = _geglu_weights(ff.net[0].proj)
     h = ops.gemm_bf16_tn_ex(x.view(-1, x.shape[-1]), wi, bi, geglu=True)
@@ -96,6 +167,8 @@ def layer_norm(norm, x: torch.Tensor) -> torch.Tensor:
         raise _lib.TviError(_lib.TVI_ERR_UNSUPPORTED, "layer_norm: only normalisation over the last dimension is built")
     if x.dtype != torch.bfloat16 or not x.is_cuda:
         raise _lib.TviError(_lib.TVI_ERR_UNSUPPORTED, "layer_norm: expected a CUDA bfloat16 tensor")
+    if torch.is_grad_enabled() and (x.requires_grad or any(p.requires_grad for p in norm.parameters())):
+        return _LayerNormFn.apply(x, norm.weight, norm.bias, float(norm.eps))
     return ops.layernorm_bf16(x.contiguous(), _bf16(norm.weight), _bf16(norm.bias), norm.eps)
 
 

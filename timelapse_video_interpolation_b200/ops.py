@@ -228,6 +228,42 @@ def farneback(prev: torch.Tensor, nxt: torch.Tensor, pyr_scale: float = 0.5, lev
     return out
 
 
+def layernorm_bwd(x: torch.Tensor, dy: torch.Tensor, gamma: torch.Tensor | None, eps: float, need_dx: bool = True,
+                  need_affine: bool = True):
+    """Backward of layernorm_bf16: returns (dx or None, dgamma or None, dbeta or None), all bf16."""
+    _need_cuda(x, dy, gamma)
+    x, ldx = _rows2d(x, "x")
+    dy, lddy = _rows2d(dy, "dy")
+    C = x.shape[-1]
+    M = x.numel() // C if C else 0
+    dx = torch.empty(x.shape, dtype=torch.bfloat16, device=x.device) if need_dx else None
+    dgamma = torch.empty(C, dtype=torch.bfloat16, device=x.device) if need_affine else None
+    dbeta = torch.empty(C, dtype=torch.bfloat16, device=x.device) if need_affine else None
+    ws = _workspace(_lib.load().tvi_layernorm_bwd_workspace_bytes(M, C), x.device)
+    lddx = _rows2d(dx, "dx")[1] if dx is not None else 0
+    _hooked("layernorm_bwd", 2 if need_affine else 1, _lib.load().tvi_layernorm_bwd_bf16, x.data_ptr(), dy.data_ptr(),
+            gamma.data_ptr() if gamma is not None else None, dx.data_ptr() if dx is not None else None,
+            dgamma.data_ptr() if dgamma is not None else None, dbeta.data_ptr() if dbeta is not None else None,
+            ws.data_ptr() if ws is not None else None, M, C, ldx, lddy, lddx, float(eps), _stream())
+    return dx, dgamma, dbeta
+
+
+def geglu_bwd(pre: torch.Tensor, dh: torch.Tensor, need_h: bool = True):
+    """pre [M, 2*inner] = [value | gate], dh [M, inner] -> (h or None [M, inner], dpre [M, 2*inner])."""
+    _need_cuda(pre, dh)
+    pre, ldpre = _rows2d(pre, "pre")
+    dh, lddh = _rows2d(dh, "dh")
+    inner = dh.shape[-1]
+    if pre.shape[-1] != 2 * inner:
+        raise _lib.TviError(_lib.TVI_ERR_INVALID, "geglu_bwd: pre must be twice as wide as dh")
+    M = dh.numel() // inner if inner else 0
+    h = torch.empty(M, inner, dtype=torch.bfloat16, device=pre.device) if need_h else None
+    dpre = torch.empty(M, 2 * inner, dtype=torch.bfloat16, device=pre.device)
+    _hooked("geglu_bwd", 1, _lib.load().tvi_geglu_bwd_bf16, pre.data_ptr(), dh.data_ptr(), h.data_ptr() if h is not None else None,
+            dpre.data_ptr(), M, inner, ldpre, lddh, inner, 2 * inner, _stream())
+    return h, dpre
+
+
 def gemm_bf16_dgrad(dy: torch.Tensor, w: torch.Tensor, out: torch.Tensor | None = None) -> torch.Tensor:
     """dx[..., K] = dy[..., N] @ w[N, K] — input gradient of nn.Linear; w is consumed in place."""
     _need_cuda(dy, w)
