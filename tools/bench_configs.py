@@ -188,6 +188,59 @@ def cfg_train(steps):
           "clip_frames_per_s_fwd_bwd": clips * T / (ms_fb * 1e-3), "kernels": kt.summary(3)})
 
 
+def cfg_train_block(steps):
+    """Config 5 through the block-level swap: spatial block frozen, temporal block trainable (src/train_decouples.py:707-720),
+    2 clips x T = 14 at 576x1024, no CFG; forward + backward of LayerNorm / attention / FeedForward on libtvi."""
+    from timelapse_video_interpolation_b200 import blocks
+    from timelapse_video_interpolation_b200.modules import BasicTransformerBlock, TemporalBasicTransformerBlock
+    C, heads, h, w = bench.LEVELS["L0"]
+    S, T, B = h * w, 14, 2
+    g = torch.Generator().manual_seed(3)
+
+    def init(m, trainable):
+        with torch.no_grad():
+            for name, p in m.named_parameters():
+                if "norm" in name:
+                    p.fill_(1.0 if name.endswith("weight") else 0.0)
+                else:
+                    p.copy_((torch.rand(p.shape, generator=g) * 2 - 1) * (p.shape[-1] ** -0.5 if p.dim() > 1 else C ** -0.5))
+                p.requires_grad_(trainable)
+        return m.to(DEV, torch.bfloat16)
+
+    sb, tb = init(BasicTransformerBlock(C, heads, 1024), False), init(TemporalBasicTransformerBlock(C, C, heads, 1024), True)
+    blocks.install_blocks(sb)
+    blocks.install_blocks(tb)
+    x = torch.randn(B * T, S, C, generator=g).to(torch.bfloat16).to(DEV)
+    xg = x.clone().requires_grad_(True)
+    ctx_s = torch.randn(B * T, 2, 1024, generator=g).to(torch.bfloat16).to(DEV)
+    ctx_t = torch.randn(B * S, 1, 1024, generator=g).to(torch.bfloat16).to(DEV)
+    dy = (torch.randn(B * T, S, C, generator=g) / 8).to(torch.bfloat16).to(DEV)
+
+    def fwd_bwd():
+        for p in tb.parameters():
+            p.grad = None
+        xg.grad = None
+        y = tb(sb(xg, encoder_hidden_states=ctx_s), num_frames=T, encoder_hidden_states=ctx_t)
+        y.backward(dy)
+
+    def fwd():
+        with torch.no_grad():
+            tb(sb(x, encoder_hidden_states=ctx_s), num_frames=T, encoder_hidden_states=ctx_t)
+
+    ms_f = timed(fwd, steps)
+    ms_fb = timed(fwd_bwd, max(3, steps // 2))
+    kt = KernelTimes()
+    ops.EVENT_HOOK = kt.hook
+    for _ in range(2):
+        fwd_bwd()
+    ops.EVENT_HOOK = None
+    emit({"config": "train_fwd_bwd_L0_block_pair", "clips_per_gpu": B, "T": T, "resolution": "576x1024",
+          "trainable": "temporal block (spatial block frozen, gradient flows through it to the input)",
+          "trainable_params": sum(p.numel() for p in tb.parameters()), "ms_fwd": ms_f, "ms_fwd_bwd": ms_fb,
+          "clip_frames_per_s_fwd_bwd": B * T / (ms_fb * 1e-3), "peak_mem_gb": torch.cuda.max_memory_allocated() / 2 ** 30,
+          "kernels": kt.summary(2)})
+
+
 def cfg_loop25(steps):
     # 16 UNet + 7 ControlNet TransformerSpatioTemporalModel instances per denoising step (SURVEY §8.0):
     # UNet: L0 x5, L1 x5, L2 x5, mid x1; ControlNet branch (down + mid): L0 x2, L1 x2, L2 x2, mid x1
@@ -388,12 +441,12 @@ def cfg_farneback(steps):
 
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument("--only", default="slerp,flow,train,loop25,kernels,block,model,levels,farneback")
+    ap.add_argument("--only", default="slerp,flow,train,train_block,loop25,kernels,block,model,levels,farneback")
     ap.add_argument("--steps", type=int, default=10)
     args = ap.parse_args()
     torch.cuda.set_device(0)
     emit({"config": "env", "device": torch.cuda.get_device_name(0), "libtvi": tvi.version(), "peaks": PK})
-    table = {"slerp": cfg_slerp, "flow": cfg_flow, "train": cfg_train, "loop25": cfg_loop25, "kernels": cfg_kernels, "block": cfg_block, "model": cfg_model, "levels": cfg_levels, "farneback": cfg_farneback}
+    table = {"slerp": cfg_slerp, "flow": cfg_flow, "train": cfg_train, "loop25": cfg_loop25, "kernels": cfg_kernels, "block": cfg_block, "model": cfg_model, "levels": cfg_levels, "farneback": cfg_farneback, "train_block": cfg_train_block}
     for name in args.only.split(","):
         table[name.strip()](args.steps)
 
