@@ -160,3 +160,30 @@ def test_frozen_spatial_block_under_no_grad_still_uses_the_fast_path(cuda):
     y1 = blk(x.clone().requires_grad_(True), encoder_hidden_states=e)     # tape path
     assert not y0.requires_grad and y1.requires_grad
     assert float((y0.float() - y1.detach().float()).abs().max()) <= 2e-2 * max(1.0, float(y0.float().abs().max()))
+
+
+def test_block_under_gradient_checkpointing_gives_identical_gradients(cuda):
+    # the reference wraps the blocks in torch.utils.checkpoint(..., use_reentrant=False) when training
+    # (src/models/transformer_temporal.py:329-336); the libtvi Functions are deterministic, so the gradients are bit-identical
+    from torch.utils.checkpoint import checkpoint
+    blk = _init_block(TemporalBasicTransformerBlock(320, 320, 5, 1024), 12, cuda)
+    blocks.install_blocks(blk)
+    g = torch.Generator().manual_seed(6)
+    T, S = 14, 16
+    x = torch.randn(T, S, 320, generator=g).to(torch.bfloat16).to(cuda)
+    e = torch.randn(S, 1, 1024, generator=g).to(torch.bfloat16).to(cuda)
+    wgt = torch.randn(T, S, 320, generator=g).to(torch.bfloat16).to(cuda)
+
+    def run(use_ckpt):
+        for p in blk.parameters():
+            p.grad = None
+        xi = x.clone().requires_grad_(True)
+        y = checkpoint(blk, xi, T, e, use_reentrant=False) if use_ckpt else blk(xi, T, e)
+        (y.float() * wgt.float()).sum().backward()
+        return xi.grad.clone(), {n: p.grad.clone() for n, p in blk.named_parameters()}
+
+    dx0, g0 = run(False)
+    dx1, g1 = run(True)
+    assert torch.equal(dx0, dx1)
+    for n in g0:
+        assert torch.equal(g0[n], g1[n]), n
