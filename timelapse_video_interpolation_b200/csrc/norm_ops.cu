@@ -270,7 +270,7 @@ namespace tvi {
 namespace {
 
 constexpr int kLnBwdWarps = 8;
-constexpr int kLnBwdRowsPerWarp = 16;
+constexpr int kLnBwdRowsPerWarp = 8;
 
 template <int NCH>
 __global__ void __launch_bounds__(kLnBwdWarps * 32)
@@ -298,7 +298,24 @@ layernorm_bwd_kernel(const tvi_bf16* __restrict__ x, const tvi_bf16* __restrict_
     }
   }
   const float inv_c = 1.0f / (float)C;
-  const int64_t row0 = ((int64_t)blockIdx.x * kLnBwdWarps + warp) * kLnBwdRowsPerWarp;
+  // persistent: a warp walks row groups with a grid stride, so the number of dgamma / dbeta partials is the (small) grid size
+  for (int64_t row0 = ((int64_t)blockIdx.x * kLnBwdWarps + warp) * kLnBwdRowsPerWarp; row0 < M;
+       row0 += (int64_t)gridDim.x * kLnBwdWarps * kLnBwdRowsPerWarp) {
+  // the next row's x / dy are requested before the current row's four dependent warp reductions (latency-bound otherwise)
+  uint4 nx[NCH], nd[NCH];
+  auto fetch = [&](int64_t row) {
+#pragma unroll
+    for (int i = 0; i < NCH; ++i) {
+      const int c = lane + 32 * i;
+      if (c < C8 && row < M) {
+        nx[i] = __ldg(reinterpret_cast<const uint4*>(x + row * ldx) + c);
+        nd[i] = __ldg(reinterpret_cast<const uint4*>(dy + row * lddy) + c);
+      } else {
+        nx[i] = nd[i] = make_uint4(0u, 0u, 0u, 0u);
+      }
+    }
+  };
+  fetch(row0);
   for (int r = 0; r < kLnBwdRowsPerWarp; ++r) {
     const int64_t row = row0 + r;
     if (row >= M) break;
@@ -306,26 +323,19 @@ layernorm_bwd_kernel(const tvi_bf16* __restrict__ x, const tvi_bf16* __restrict_
     float sum = 0.f;
 #pragma unroll
     for (int i = 0; i < NCH; ++i) {
-      const int c = lane + 32 * i;
-      if (c < C8) {
-        const uint4 ux = __ldg(reinterpret_cast<const uint4*>(x + row * ldx) + c);
-        const uint4 ud = __ldg(reinterpret_cast<const uint4*>(dy + row * lddy) + c);
-        const __nv_bfloat162* hx = reinterpret_cast<const __nv_bfloat162*>(&ux);
-        const __nv_bfloat162* hd = reinterpret_cast<const __nv_bfloat162*>(&ud);
+      const __nv_bfloat162* hx = reinterpret_cast<const __nv_bfloat162*>(&nx[i]);
+      const __nv_bfloat162* hd = reinterpret_cast<const __nv_bfloat162*>(&nd[i]);
 #pragma unroll
-        for (int q = 0; q < 4; ++q) {
-          const float2 a = __bfloat1622float2(hx[q]), b = __bfloat1622float2(hd[q]);
-          xv[i][2 * q] = a.x;
-          xv[i][2 * q + 1] = a.y;
-          gv[i][2 * q] = b.x;
-          gv[i][2 * q + 1] = b.y;
-          sum += a.x + a.y;
-        }
-      } else {
-#pragma unroll
-        for (int q = 0; q < 8; ++q) xv[i][q] = gv[i][q] = 0.f;
+      for (int q = 0; q < 4; ++q) {
+        const float2 a = __bfloat1622float2(hx[q]), b = __bfloat1622float2(hd[q]);
+        xv[i][2 * q] = a.x;
+        xv[i][2 * q + 1] = a.y;
+        gv[i][2 * q] = b.x;
+        gv[i][2 * q + 1] = b.y;
+        sum += a.x + a.y;
       }
     }
+    if (r + 1 < kLnBwdRowsPerWarp) fetch(row + 1);
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
     const float mean = sum * inv_c;
@@ -380,6 +390,7 @@ layernorm_bwd_kernel(const tvi_bf16* __restrict__ x, const tvi_bf16* __restrict_
       }
     }
   }
+  }
   // per-block reduction over the warps in a fixed order
   float* mine = s_acc + (size_t)warp * 2 * C;
 #pragma unroll
@@ -413,7 +424,9 @@ __global__ void ln_bwd_final_kernel(const float* __restrict__ partial, tvi_bf16*
 
 int64_t ln_bwd_blocks(int64_t M) {
   const int64_t rows_per_block = (int64_t)kLnBwdWarps * kLnBwdRowsPerWarp;
-  return (M + rows_per_block - 1) / rows_per_block;
+  const int64_t need = (M + rows_per_block - 1) / rows_per_block;
+  const int64_t cap = 2 * (int64_t)num_sms();
+  return need < cap ? need : cap;
 }
 
 template <int NCH>
@@ -436,7 +449,9 @@ int launch_ln_bwd(const tvi_bf16* x, const tvi_bf16* dy, const tvi_bf16* gamma, 
 
 extern "C" size_t tvi_layernorm_bwd_workspace_bytes(int64_t M, int C) {
   if (M <= 0 || C <= 0) return 0;
-  return (size_t)tvi::ln_bwd_blocks(M) * 2 * (size_t)C * sizeof(float);
+  // device-independent upper bound of the partial count (the launch uses min(row groups, 2 x SMs) blocks)
+  const int64_t need = (M + tvi::kLnBwdWarps * tvi::kLnBwdRowsPerWarp - 1) / (tvi::kLnBwdWarps * tvi::kLnBwdRowsPerWarp);
+  return (size_t)(need < 4096 ? need : 4096) * 2 * (size_t)C * sizeof(float);
 }
 
 extern "C" int tvi_layernorm_bwd_bf16(const tvi_bf16* x, const tvi_bf16* dy, const tvi_bf16* gamma, tvi_bf16* dx, tvi_bf16* dgamma,
