@@ -170,11 +170,17 @@ int tvi_model_input_bf16(const float* latents, const tvi_bf16* image_latents, tv
  * None, pyr_scale, levels, winsize, iterations, poly_n, poly_sigma, flags=0) as called at
  * dataset_construction/step4_flow_check.py:13-22 (0.5, 3, 15, 3, 5, 1.2), including the cv2.cvtColor(BGR2GRAY) in front
  * of it when channels == 3.  prev / next: 8-bit device images [H, W, channels] (1 = gray, 3 = BGR); flow: [H, W, 2] fp32
- * (dx, dy); `workspace` = tvi_farneback_workspace_bytes(H, W) bytes.  ~26 launches per pyramid level, no host sync.
+ * (dx, dy); `workspace` = tvi_farneback_workspace_bytes(H, W, pyr_scale, levels) bytes.  ~20 launches per pyramid level, no host sync.
  */
-size_t tvi_farneback_workspace_bytes(int H, int W);
+size_t tvi_farneback_workspace_bytes(int H, int W, double pyr_scale, int levels);
 int tvi_farneback_f32(const uint8_t* prev, const uint8_t* next, int channels, float* flow, void* workspace, int H, int W,
                       double pyr_scale, int levels, int winsize, int iterations, int poly_n, double poly_sigma, void* stream);
+/* The flows of every consecutive pair of a clip (the loop at step4_flow_check.py:55-70): frames [nframes, H, W, channels],
+ * flows [nframes - 1, H, W, 2].  Each frame's blur / polynomial-expansion pyramid is built once and serves as "next" of
+ * one pair and "prev" of the following one.  `second`: NULL, or a separately stored second frame when nframes == 2. */
+int tvi_farneback_clip_f32(const uint8_t* frames, const uint8_t* second, int64_t nframes, int channels, float* flows,
+                           void* workspace, int H, int W, double pyr_scale, int levels, int winsize, int iterations, int poly_n,
+                           double poly_sigma, void* stream);
 
 /* Backward of the projections (training config 5: src/train_decouples.py back-propagates through the
  * same nn.Linear call sites; autograd's F.linear backward = two cuBLAS GEMMs + a bias column sum).

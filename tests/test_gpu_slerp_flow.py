@@ -197,3 +197,16 @@ def test_check_clip_flows_matches_the_reference_loop(cuda):
     assert flagged.cpu().tolist() == [bool(s < 0.5) for s in want_sims] == [False, False, True]
     with pytest.raises(ValueError):
         tvi.check_clip_flows(frames[:2])
+
+
+def test_farneback_clip_equals_pairwise_calls(cuda):
+    import numpy as np
+    rng = np.random.default_rng(5)
+    base = (np.kron(rng.random((14, 18)), np.ones((8, 8))) * 255).astype(np.uint8)
+    clip = torch.from_numpy(np.stack([np.roll(base, (i, 2 * i), axis=(0, 1)) for i in range(5)])).to(cuda)   # [5, 112, 144] gray
+    flows = ops.farneback_clip(clip)
+    assert flows.shape == (4, 112, 144, 2)
+    for i in range(4):
+        assert torch.equal(flows[i], ops.farneback(clip[i], clip[i + 1]))   # the shared pyramids change nothing
+    with pytest.raises(_lib.TviError):
+        ops.farneback_clip(clip[:1])

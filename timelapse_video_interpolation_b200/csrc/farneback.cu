@@ -357,116 +357,179 @@ PolyTaps poly_taps(int n, double sigma) {  // FarnebackPrepareGaussian
 
 int cv_round(double v) { return (int)nearbyint(v); }  // round-half-to-even under the default rounding mode
 
-struct Layout {  // workspace carve-up, in floats
-  size_t img[2], tmp, blur, I, row3, R[2], M, V, flow[2], total;
+constexpr int kMaxLevels = 12;
+struct Plan {  // pyramid geometry + workspace carve-up (offsets in floats)
+  int levels;                       // usable pyramid depth (OpenCV: min_size = 32)
+  int h[kMaxLevels + 1], w[kMaxLevels + 1];
+  size_t r_off[kMaxLevels + 1];     // offset of level k inside one frame's R pyramid (5 floats per pixel)
+  size_t pyr_floats;                // one frame's R pyramid
+  size_t img, tmp, blur, I, row3, pyr[2], M, V, flow[2], total;
 };
-Layout layout(int64_t H, int64_t W) {
-  Layout l;
-  const size_t n = (size_t)H * W;
+int make_plan(Plan& p, int H, int W, double pyr_scale, int levels) {
+  int k = 0;
+  double scale = 1.0;
+  for (; k < levels && k < kMaxLevels; ++k) {
+    scale *= pyr_scale;
+    if (W * scale < 32 || H * scale < 32) break;
+  }
+  p.levels = k;
   size_t o = 0;
-  auto take = [&](size_t k) {
+  for (k = 0; k <= p.levels; ++k) {
+    scale = 1.0;
+    for (int i = 0; i < k; ++i) scale *= pyr_scale;
+    p.w[k] = cv_round(W * scale);
+    p.h[k] = cv_round(H * scale);
+    p.r_off[k] = o;
+    o += ((size_t)p.h[k] * p.w[k] * 5 + 3) & ~(size_t)3;
+  }
+  p.pyr_floats = o;
+  const size_t n = (size_t)H * W;
+  o = 0;
+  auto take = [&](size_t cnt) {
     const size_t at = o;
-    o += (k + 3) & ~(size_t)3;
+    o += (cnt + 3) & ~(size_t)3;
     return at;
   };
-  l.img[0] = take(n);
-  l.img[1] = take(n);
-  l.tmp = take(n);
-  l.blur = take(n);
-  l.I = take(n);
-  l.row3 = take(3 * n);
-  l.R[0] = take(5 * n);
-  l.R[1] = take(5 * n);
-  l.M = take(5 * n);
-  l.V = take(10 * n);  // 5 doubles per pixel
-  l.flow[0] = take(2 * n);
-  l.flow[1] = take(2 * n);
-  l.total = o;
-  return l;
+  p.img = take(n);
+  p.tmp = take(n);
+  p.blur = take(n);
+  p.I = take(n);
+  p.row3 = take(3 * n);
+  p.pyr[0] = take(p.pyr_floats);
+  p.pyr[1] = take(p.pyr_floats);
+  p.M = take(5 * n);
+  p.V = take(10 * n);  // 5 doubles per pixel
+  p.flow[0] = take(2 * n);
+  p.flow[1] = take(2 * n);
+  p.total = o;
+  return TVI_OK;
+}
+
+struct Params {
+  int H, W, channels, winsize, iterations;
+  double pyr_scale;
+  PolyTaps pt;
+};
+
+// one frame: 8-bit image -> polynomial-expansion pyramid R[level] (each level blurs the FULL-resolution frame, as OpenCV)
+int prepare_frame(const uint8_t* img, float* ws, const Plan& p, const Params& a, float* pyr, cudaStream_t st) {
+  const int64_t npix = (int64_t)a.H * a.W;
+  const unsigned nb = (unsigned)((npix + 255) / 256);
+  if (a.channels == 3)
+    bgr_to_gray_kernel<<<nb, 256, 0, st>>>(img, ws + p.img, npix);
+  else
+    u8_to_f32_kernel<<<nb, 256, 0, st>>>(img, ws + p.img, npix);
+  TVI_LAUNCH_OK("farneback input conversion");
+  const dim3 grid_full((a.W + 127) / 128, a.H);
+  for (int k = p.levels; k >= 0; --k) {
+    double scale = 1.0;
+    for (int i = 0; i < k; ++i) scale *= a.pyr_scale;
+    const double sigma = (1.0 / scale - 1) * 0.5;
+    int smooth = cv_round(sigma * 5) | 1;
+    if (smooth < 3) smooth = 3;
+    TVI_CHECK_ARG(smooth <= kMaxTaps, "tvi_farneback: pyramid too deep for the blur kernel (%d taps)", smooth);
+    const Taps gt = gaussian_taps(smooth, sigma);
+    const int h = p.h[k], w = p.w[k];
+    const dim3 grid((w + 127) / 128, h);
+    gauss_kernel<false><<<grid_full, 128, 0, st>>>(ws + p.img, ws + p.tmp, a.H, a.W, gt);
+    gauss_kernel<true><<<grid_full, 128, 0, st>>>(ws + p.tmp, ws + p.blur, a.H, a.W, gt);
+    resize_kernel<1><<<grid, 128, 0, st>>>(ws + p.blur, ws + p.I, a.H, a.W, h, w, 1.0f);
+    polyexp_v_kernel<<<grid, 128, 0, st>>>(ws + p.I, ws + p.row3, h, w, a.pt);
+    polyexp_h_kernel<<<grid, 128, 0, st>>>(ws + p.row3, pyr + p.r_off[k], h, w, a.pt);
+    TVI_LAUNCH_OK("farneback pyramid level");
+  }
+  return TVI_OK;
+}
+
+// one pair: coarse-to-fine flow from the two frames' pyramids
+int solve_pair(const float* pyr0, const float* pyr1, float* ws, const Plan& p, const Params& a, float* flow, cudaStream_t st) {
+  int cur = 0;
+  for (int k = p.levels; k >= 0; --k) {
+    const int h = p.h[k], w = p.w[k];
+    const dim3 grid((w + 127) / 128, h);
+    float* fl = (k == 0) ? flow : ws + p.flow[cur];
+    if (k == p.levels) {
+      TVI_CUDA_OK(cudaMemsetAsync(fl, 0, sizeof(float) * 2 * (size_t)h * w, st));
+    } else {
+      resize_kernel<2><<<grid, 128, 0, st>>>(ws + p.flow[cur ^ 1], fl, p.h[k + 1], p.w[k + 1], h, w, (float)(1.0 / a.pyr_scale));
+      TVI_LAUNCH_OK("farneback resize_flow");
+    }
+    const float* R0 = pyr0 + p.r_off[k];
+    const float* R1 = pyr1 + p.r_off[k];
+    update_matrices_kernel<<<grid, 128, 0, st>>>(R0, R1, fl, ws + p.M, h, w);
+    for (int it = 0; it < a.iterations; ++it) {
+      box_v_kernel<<<dim3((w * 5 + 127) / 128, (h + kBoxRows - 1) / kBoxRows), 128, 0, st>>>(ws + p.M, (double*)(ws + p.V), h, w,
+                                                                                            a.winsize / 2);
+      box_h_solve_kernel<<<grid, 128, 0, st>>>((const double*)(ws + p.V), fl, h, w, a.winsize / 2,
+                                               1.0 / ((double)a.winsize * a.winsize));
+      if (it < a.iterations - 1) update_matrices_kernel<<<grid, 128, 0, st>>>(R0, R1, fl, ws + p.M, h, w);
+      TVI_LAUNCH_OK("farneback iteration");
+    }
+    cur ^= 1;
+  }
+  return TVI_OK;
+}
+
+int check_params(const char* fn, int H, int W, int channels, double pyr_scale, int levels, int winsize, int iterations, int poly_n) {
+  TVI_CHECK_ARG(channels == 1 || channels == 3, "%s: images must be 8-bit gray (1) or BGR (3), got %d channels", fn, channels);
+  TVI_CHECK_ARG(pyr_scale > 0 && pyr_scale < 1 && levels >= 0, "%s: pyr_scale must be in (0, 1) and levels >= 0", fn);
+  TVI_CHECK_ARG(winsize >= 1 && winsize % 2 == 1 && winsize <= 2 * kBoxMaxM + 1 && iterations >= 1,
+                "%s: winsize must be odd and at most %d, iterations >= 1", fn, 2 * kBoxMaxM + 1);
+  TVI_CHECK_ARG(poly_n >= 1 && poly_n <= 15, "%s: poly_n=%d outside [1, 15]", fn, poly_n);
+  TVI_CHECK_ARG(H <= 65535, "%s: more than 65535 rows", fn);
+  return TVI_OK;
 }
 
 }  // namespace
 }  // namespace tvi
 
-extern "C" size_t tvi_farneback_workspace_bytes(int H, int W) {
-  if (H <= 0 || W <= 0) return 0;
-  return tvi::layout(H, W).total * sizeof(float);
+extern "C" size_t tvi_farneback_workspace_bytes(int H, int W, double pyr_scale, int levels) {
+  if (H <= 0 || W <= 0 || !(pyr_scale > 0 && pyr_scale < 1) || levels < 0) return 0;
+  tvi::Plan p;
+  tvi::make_plan(p, H, W, pyr_scale, levels);
+  return p.total * sizeof(float);
 }
 
 extern "C" int tvi_farneback_f32(const uint8_t* prev, const uint8_t* next, int channels, float* flow, void* workspace, int H, int W,
                                  double pyr_scale, int levels, int winsize, int iterations, int poly_n, double poly_sigma,
                                  void* stream) {
+  return tvi_farneback_clip_f32(prev, next, 2, channels, flow, workspace, H, W, pyr_scale, levels, winsize, iterations, poly_n,
+                                poly_sigma, stream);
+}
+
+extern "C" int tvi_farneback_clip_f32(const uint8_t* frames, const uint8_t* second, int64_t nframes, int channels, float* flows,
+                                      void* workspace, int H, int W, double pyr_scale, int levels, int winsize, int iterations,
+                                      int poly_n, double poly_sigma, void* stream) {
   using namespace tvi;
-  TVI_CHECK_ARG(H >= 0 && W >= 0, "tvi_farneback_f32: negative size");
-  if (H == 0 || W == 0) return TVI_OK;
-  TVI_CHECK_ARG(prev && next && flow && workspace, "tvi_farneback_f32: null pointer");
-  TVI_CHECK_ARG(channels == 1 || channels == 3, "tvi_farneback_f32: images must be 8-bit gray (1) or BGR (3), got %d channels", channels);
-  TVI_CHECK_ARG(pyr_scale > 0 && pyr_scale < 1 && levels >= 0, "tvi_farneback_f32: pyr_scale must be in (0, 1) and levels >= 0");
-  TVI_CHECK_ARG(winsize >= 1 && winsize % 2 == 1 && winsize <= 2 * kBoxMaxM + 1 && iterations >= 1,
-                "tvi_farneback_f32: winsize must be odd and at most %d, iterations >= 1", 2 * kBoxMaxM + 1);
-  TVI_CHECK_ARG(poly_n >= 1 && poly_n <= 15, "tvi_farneback_f32: poly_n=%d outside [1, 15]", poly_n);
-  TVI_CHECK_ARG((uintptr_t)workspace % 16 == 0 && (uintptr_t)flow % 8 == 0, "tvi_farneback_f32: misaligned pointer");
-  TVI_CHECK_ARG(H <= 65535, "tvi_farneback_f32: more than 65535 rows");
+  TVI_CHECK_ARG(H >= 0 && W >= 0 && nframes >= 0, "tvi_farneback_clip_f32: negative size");
+  if (H == 0 || W == 0 || nframes < 2) return TVI_OK;
+  TVI_CHECK_ARG(frames && flows && workspace, "tvi_farneback_clip_f32: null pointer");
+  TVI_CHECK_ARG(second == nullptr || nframes == 2, "tvi_farneback_clip_f32: a separate second frame is only meaningful for one pair");
+  int rc = check_params("tvi_farneback_clip_f32", H, W, channels, pyr_scale, levels, winsize, iterations, poly_n);
+  if (rc) return rc;
+  TVI_CHECK_ARG((uintptr_t)workspace % 16 == 0 && (uintptr_t)flows % 8 == 0, "tvi_farneback_clip_f32: misaligned pointer");
   cudaStream_t st = (cudaStream_t)stream;
   float* ws = (float*)workspace;
-  const Layout l = layout(H, W);
-  const int64_t npix = (int64_t)H * W;
-  const unsigned nb = (unsigned)((npix + 255) / 256);
-  const uint8_t* src[2] = {prev, next};
-  for (int i = 0; i < 2; ++i) {
-    if (channels == 3)
-      bgr_to_gray_kernel<<<nb, 256, 0, st>>>(src[i], ws + l.img[i], npix);
-    else
-      u8_to_f32_kernel<<<nb, 256, 0, st>>>(src[i], ws + l.img[i], npix);
-    TVI_LAUNCH_OK("farneback input conversion");
-  }
-  // usable pyramid depth (min_size = 32, as OpenCV)
-  int k = 0;
-  double scale = 1.0;
-  for (; k < levels; ++k) {
-    scale *= pyr_scale;
-    if (W * scale < 32 || H * scale < 32) break;
-  }
-  levels = k;
-  const PolyTaps pt = poly_taps(poly_n, poly_sigma);
-  int cur = 0, ph = 0, pw = 0;  // flow buffer index / size of the previous (coarser) level
-  bool have_prev = false;
-  for (k = levels; k >= 0; --k) {
-    scale = 1.0;
-    for (int i = 0; i < k; ++i) scale *= pyr_scale;
-    const double sigma = (1.0 / scale - 1) * 0.5;
-    int smooth = cv_round(sigma * 5) | 1;
-    if (smooth < 3) smooth = 3;
-    TVI_CHECK_ARG(smooth <= kMaxTaps, "tvi_farneback_f32: pyramid too deep for the blur kernel (%d taps)", smooth);
-    const int w = cv_round(W * scale), h = cv_round(H * scale);
-    const dim3 grid_full((W + 127) / 128, H), grid((w + 127) / 128, h);
-    float* fl = (k == 0) ? flow : ws + l.flow[cur];
-    if (!have_prev) {
-      TVI_CUDA_OK(cudaMemsetAsync(fl, 0, sizeof(float) * 2 * (size_t)h * w, st));
-    } else {
-      resize_kernel<2><<<grid, 128, 0, st>>>(ws + l.flow[cur ^ 1], fl, ph, pw, h, w, (float)(1.0 / pyr_scale));
-      TVI_LAUNCH_OK("farneback resize_flow");
-    }
-    const Taps gt = gaussian_taps(smooth, sigma);
-    for (int i = 0; i < 2; ++i) {
-      gauss_kernel<false><<<grid_full, 128, 0, st>>>(ws + l.img[i], ws + l.tmp, H, W, gt);
-      gauss_kernel<true><<<grid_full, 128, 0, st>>>(ws + l.tmp, ws + l.blur, H, W, gt);
-      resize_kernel<1><<<grid, 128, 0, st>>>(ws + l.blur, ws + l.I, H, W, h, w, 1.0f);
-      polyexp_v_kernel<<<grid, 128, 0, st>>>(ws + l.I, ws + l.row3, h, w, pt);
-      polyexp_h_kernel<<<grid, 128, 0, st>>>(ws + l.row3, ws + l.R[i], h, w, pt);
-      TVI_LAUNCH_OK("farneback pyramid level");
-    }
-    update_matrices_kernel<<<grid, 128, 0, st>>>(ws + l.R[0], ws + l.R[1], fl, ws + l.M, h, w);
-    for (int it = 0; it < iterations; ++it) {
-      box_v_kernel<<<dim3((w * 5 + 127) / 128, (h + kBoxRows - 1) / kBoxRows), 128, 0, st>>>(ws + l.M, (double*)(ws + l.V), h, w, winsize / 2);
-      box_h_solve_kernel<<<grid, 128, 0, st>>>((const double*)(ws + l.V), fl, h, w, winsize / 2, 1.0 / ((double)winsize * winsize));
-      if (it < iterations - 1) update_matrices_kernel<<<grid, 128, 0, st>>>(ws + l.R[0], ws + l.R[1], fl, ws + l.M, h, w);
-      TVI_LAUNCH_OK("farneback iteration");
-    }
-    have_prev = true;
-    ph = h;
-    pw = w;
-    cur ^= 1;
+  Plan p;
+  make_plan(p, H, W, pyr_scale, levels);
+  Params a;
+  a.H = H;
+  a.W = W;
+  a.channels = channels;
+  a.winsize = winsize;
+  a.iterations = iterations;
+  a.pyr_scale = pyr_scale;
+  a.pt = poly_taps(poly_n, poly_sigma);
+  const size_t frame_bytes = (size_t)H * W * channels;
+  // every frame's pyramid is built ONCE: frame i + 1 is "next" of pair i and "prev" of pair i + 1 (ping-pong buffers)
+  rc = prepare_frame(frames, ws, p, a, ws + p.pyr[0], st);
+  if (rc) return rc;
+  for (int64_t i = 0; i + 1 < nframes; ++i) {
+    const uint8_t* nxt = second != nullptr ? second : frames + (size_t)(i + 1) * frame_bytes;
+    rc = prepare_frame(nxt, ws, p, a, ws + p.pyr[(i + 1) & 1], st);
+    if (rc) return rc;
+    rc = solve_pair(ws + p.pyr[i & 1], ws + p.pyr[(i + 1) & 1], ws, p, a, flows + (size_t)i * H * W * 2, st);
+    if (rc) return rc;
   }
   return TVI_OK;
 }

@@ -40,9 +40,7 @@ def check_clip_flows(frames, threshold: float = 0.5):
     if t.dim() != 4 or t.shape[0] < 3 or t.shape[-1] != 3 or t.dtype != torch.uint8:
         raise ValueError("frames must be [N >= 3, H, W, 3] uint8 (the reference skips shorter clips, :50-51)")
     N, H, W, _ = t.shape
-    flows = torch.empty(N - 1, H, W, 2, dtype=torch.float32, device=t.device)
-    for i in range(N - 1):
-        ops.farneback(t[i], t[i + 1], out=flows[i])
+    flows = ops.farneback_clip(t)   # every frame's pyramid is built once (half the per-pair preparation work)
     sims = ops.flow_cosine_f32(flows[:-1], flows[1:], hwc=True)
     return flows, sims, sims < threshold
 

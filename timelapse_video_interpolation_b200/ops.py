@@ -221,7 +221,7 @@ def farneback(prev: torch.Tensor, nxt: torch.Tensor, pyr_scale: float = 0.5, lev
     prev, nxt = prev.contiguous(), nxt.contiguous()
     if out is None:
         out = torch.empty(H, W, 2, dtype=torch.float32, device=prev.device)
-    ws = _workspace(_lib.load().tvi_farneback_workspace_bytes(H, W), prev.device)
+    ws = _workspace(_lib.load().tvi_farneback_workspace_bytes(H, W, float(pyr_scale), int(levels)), prev.device)
     _hooked("farneback", 26 * (levels + 1), _lib.load().tvi_farneback_f32, prev.data_ptr(), nxt.data_ptr(), ch, out.data_ptr(),
             ws.data_ptr() if ws is not None else None, H, W, float(pyr_scale), int(levels), int(winsize), int(iterations), int(poly_n),
             float(poly_sigma), _stream())
@@ -262,6 +262,25 @@ def geglu_bwd(pre: torch.Tensor, dh: torch.Tensor, need_h: bool = True):
     _hooked("geglu_bwd", 1, _lib.load().tvi_geglu_bwd_bf16, pre.data_ptr(), dh.data_ptr(), h.data_ptr() if h is not None else None,
             dpre.data_ptr(), M, inner, ldpre, lddh, inner, 2 * inner, _stream())
     return h, dpre
+
+
+def farneback_clip(frames: torch.Tensor, pyr_scale: float = 0.5, levels: int = 3, winsize: int = 15, iterations: int = 3,
+                   poly_n: int = 5, poly_sigma: float = 1.2, out: torch.Tensor | None = None) -> torch.Tensor:
+    """Flows of every consecutive frame pair of a uint8 CUDA clip [N, H, W] / [N, H, W, 3] -> [N - 1, H, W, 2] fp32; every
+    frame's pyramid is built once."""
+    _need_cuda(frames)
+    if frames.dtype != torch.uint8 or frames.dim() not in (3, 4) or frames.shape[0] < 2:
+        raise _lib.TviError(_lib.TVI_ERR_INVALID, "farneback_clip: expected a uint8 clip [N >= 2, H, W] or [N, H, W, 3]")
+    ch = 1 if frames.dim() == 3 else frames.shape[3]
+    N, H, W = frames.shape[:3]
+    frames = frames.contiguous()
+    if out is None:
+        out = torch.empty(N - 1, H, W, 2, dtype=torch.float32, device=frames.device)
+    ws = _workspace(_lib.load().tvi_farneback_workspace_bytes(H, W, float(pyr_scale), int(levels)), frames.device)
+    _hooked("farneback_clip", 20 * (levels + 1) * (N - 1), _lib.load().tvi_farneback_clip_f32, frames.data_ptr(), None, N, ch,
+            out.data_ptr(), ws.data_ptr() if ws is not None else None, H, W, float(pyr_scale), int(levels), int(winsize),
+            int(iterations), int(poly_n), float(poly_sigma), _stream())
+    return out
 
 
 def gemm_bf16_dgrad(dy: torch.Tensor, w: torch.Tensor, out: torch.Tensor | None = None) -> torch.Tensor:

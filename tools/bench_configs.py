@@ -423,6 +423,11 @@ def cfg_farneback(steps):
     out = torch.empty(H, W, 2, dtype=torch.float32, device=DEV)
     ms = timed(lambda: ops.farneback(da, db, out=out), steps)
     rec = {"config": "farneback_1080p_pair", "ms_per_pair": ms, "pairs_per_s": 1e3 / ms, "median_flow": [float(out[..., 0].median()), float(out[..., 1].median())]}
+    clip = torch.stack([torch.roll(da, (i, 2 * i), dims=(0, 1)) for i in range(14)])          # a 14-frame clip, 13 pairs
+    cflows = torch.empty(13, H, W, 2, dtype=torch.float32, device=DEV)
+    ms_clip = timed(lambda: ops.farneback_clip(clip, out=cflows), max(3, steps // 2))
+    rec["clip14_ms_per_pair"] = ms_clip / 13
+    rec["clip14_pairs_per_s"] = 13e3 / ms_clip
     try:
         import cv2
         import time
