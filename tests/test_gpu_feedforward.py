@@ -176,3 +176,19 @@ def test_bcast_rows_add_group_inner(cuda):
     assert torch.equal(got, v.view(B, 1, S, C).expand(B, T, S, C).reshape(-1, C))
     got = ops.bcast_rows_add(v, None, T)  # contiguous groups
     assert torch.equal(got, v.view(B * S, 1, C).expand(B * S, T, C).reshape(-1, C))
+
+
+def test_empty_and_ragged_inputs(cuda):
+    # zero rows are a no-op (no launch), ragged row counts (not a multiple of any tile) are covered by the TMA tails
+    ff = _ff(320, None, 8, cuda)
+    norm = torch.nn.LayerNorm(320).to(cuda, torch.bfloat16)
+    empty = torch.empty(0, 7, 320, dtype=torch.bfloat16, device=cuda)
+    with torch.no_grad():
+        assert tvi.feed_forward(ff, empty).shape == (0, 7, 320)
+        assert tvi.layer_norm(norm, empty).shape == (0, 7, 320)
+        assert ops.blend_rows(empty, empty, torch.empty(0, device=cuda), 7).shape == (0, 7, 320)
+        for rows in (1, 127, 129, 4099):
+            x = torch.randn(rows, 320, device=cuda).to(torch.bfloat16)
+            y = tvi.feed_forward(ff, x, residual=x)
+            ref = feedforward_ref.feed_forward_ref(ff, x, residual=x)
+            assert float((y.float().cpu() - ref).abs().max()) <= 2e-2 * max(1.0, float(ref.abs().max())), rows

@@ -165,3 +165,14 @@ def test_reference_script_shape_512x320_fp32_and_fp16(cuda, dtype):
         err = max_abs(y.float().cpu(), ref)
         print(f"512x320 {name} {dtype}: max abs err {err:.3e}")
         assert err < 2 * TOL, name   # inputs AND weights are rounded to bf16 on entry
+
+
+def test_empty_batch_is_a_no_op(cuda):
+    attn = make_attn(320, None, 5, seed=2, device=cuda, dtype=torch.bfloat16, processor=TviAttnProcessor())
+    cross = make_attn(320, 1024, 5, seed=3, device=cuda, dtype=torch.bfloat16, processor=TviAttnProcessor())
+    with torch.no_grad():
+        assert attn(torch.empty(0, 14, 320, dtype=torch.bfloat16, device=cuda)).shape == (0, 14, 320)
+        for L in (1, 2):
+            y = cross(torch.empty(0, 14, 320, dtype=torch.bfloat16, device=cuda),
+                      encoder_hidden_states=torch.empty(0, L, 1024, dtype=torch.bfloat16, device=cuda))
+            assert y.shape == (0, 14, 320)

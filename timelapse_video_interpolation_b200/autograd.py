@@ -28,7 +28,7 @@ def _self_core(q, k, v, Bp, S, heads, scale, lse=None):
 def _out_proj(o, w_o, b_o, residual):
     if residual is None:
         return ops.gemm_bf16_tn(o, w_o, b_o)
-    return ops.gemm_bf16_tn_ex(o, w_o, b_o, residual=residual.reshape(-1, residual.shape[-1]))
+    return ops.gemm_bf16_tn_ex(o, w_o, b_o, residual=residual.reshape(o.shape[0], residual.shape[-1]))
 
 
 def self_attention(x: torch.Tensor, w_qkv: torch.Tensor, w_o: torch.Tensor, b_o, heads: int, scale: float,
@@ -46,7 +46,7 @@ def self_attention(x: torch.Tensor, w_qkv: torch.Tensor, w_o: torch.Tensor, b_o,
     else:
         o = _self_core(q, k, v, Bp, S, heads, scale)
     y = _out_proj(o, w_o, b_o, residual)
-    return y.view(Bp, S, -1)
+    return y.view(Bp, S, y.shape[-1])
 
 
 def cross_attention(x: torch.Tensor, e: torch.Tensor, w_q: torch.Tensor, w_kv: torch.Tensor, w_o: torch.Tensor, b_o,
@@ -66,8 +66,8 @@ def cross_attention(x: torch.Tensor, e: torch.Tensor, w_q: torch.Tensor, w_kv: t
             raise _lib.TviError(_lib.TVI_ERR_INVALID, "encoder_hidden_states batch does not match hidden_states (expects B*S rows)")
         kv = ops.gemm_bf16_tn(e.view(-1, e.shape[2]), w_kv)
         yv = ops.gemm_bf16_tn(kv[:, inner:], w_o, b_o)  # [B*S, C]
-        res2 = residual.reshape(Bp * S, -1) if residual is not None else None
-        return ops.bcast_rows_add(yv, res2, frames, group_inner=S, nrows=Bp * S).view(Bp, S, -1)
+        res2 = residual.reshape(Bp * S, residual.shape[-1]) if residual is not None else None
+        return ops.bcast_rows_add(yv, res2, frames, group_inner=S, nrows=Bp * S).view(Bp, S, yv.shape[-1])
     _check_context(x, e)
     kv = ops.gemm_bf16_tn(e.view(Bp * L, e.shape[2]), w_kv)  # [B'*L, 2*inner]
     k, v = kv[:, :inner], kv[:, inner:]
@@ -76,14 +76,14 @@ def cross_attention(x: torch.Tensor, e: torch.Tensor, w_q: torch.Tensor, w_kv: t
         # B' value rows once and broadcast them (Q is never needed)
         yv = ops.gemm_bf16_tn(v, w_o, b_o)  # [B', C]
         if residual is not None:
-            return ops.bcast_rows_add(yv, residual.reshape(Bp * S, -1), S).view(Bp, S, -1)
+            return ops.bcast_rows_add(yv, residual.reshape(Bp * S, residual.shape[-1]), S).view(Bp, S, yv.shape[-1])
         y = ops.attn_fewkeys(None, yv, yv, Bp * S, S, heads, 1, 1.0)  # L == 1: pure row broadcast
-        return y.view(Bp, S, -1)
+        return y.view(Bp, S, y.shape[-1])
     q = ops.gemm_bf16_tn(x.view(Bp * S, C), w_q)
     o = ops.attn_fewkeys(q, k, v, Bp * S, S, heads, L, scale, Tq=S if (bias is not None or stats is not None) else 1,
                          bias=bias, stats=stats)
     y = _out_proj(o, w_o, b_o, residual)
-    return y.view(Bp, S, -1)
+    return y.view(Bp, S, y.shape[-1])
 
 
 def _check_context(x, e):
@@ -118,7 +118,7 @@ class _AttentionFn(torch.autograd.Function):
             y = ops.gemm_bf16_tn(o, w_o, b_o)
             ctx.mode = "self"
             ctx.save_for_backward(x2, qkv, o, lse, w_qkv, w_o)
-            return y.view(Bp, S, -1)
+            return y.view(Bp, S, y.shape[-1])
         _check_context(x, e)
         L = e.shape[1]
         w_q, w_kv = cfg["w_q"], cfg["w_kv"]
@@ -132,7 +132,7 @@ class _AttentionFn(torch.autograd.Function):
             y = ops.attn_fewkeys(None, yv, yv, Bp * S, S, heads, 1, 1.0)
             ctx.mode = "cross1"
             ctx.save_for_backward(e2, kv, w_kv, w_o)
-            return y.view(Bp, S, -1)
+            return y.view(Bp, S, y.shape[-1])
         x2 = x.view(Bp * S, C)
         q = ops.gemm_bf16_tn(x2, w_q)
         o = ops.attn_fewkeys(q, k, v, Bp * S, S, heads, L, scale, Tq=S if (bias is not None or stats is not None) else 1,
@@ -140,7 +140,7 @@ class _AttentionFn(torch.autograd.Function):
         y = ops.gemm_bf16_tn(o, w_o, b_o)
         ctx.mode = "cross"
         ctx.save_for_backward(x2, e2, q, kv, o, w_q, w_kv, w_o)
-        return y.view(Bp, S, -1)
+        return y.view(Bp, S, y.shape[-1])
 
     @staticmethod
     @once_differentiable
@@ -150,7 +150,7 @@ class _AttentionFn(torch.autograd.Function):
         Bp, S, C = ctx.shape
         need_x, need_e, need_wq, need_wk, need_wv, need_wo, need_bo, _ = ctx.needs_input_grad
         dt_wq, dt_wk, dt_wv, dt_wo, dt_bo = ctx.param_dtypes
-        dy2 = dy.contiguous().view(Bp * S, -1)
+        dy2 = dy.contiguous().view(Bp * S, dy.shape[-1])
         if dy2.dtype != torch.bfloat16:
             dy2 = dy2.to(torch.bfloat16)
         dx = de = dwq = dwk = dwv = dwo = dbo = None

@@ -72,7 +72,7 @@ class _FeedForwardFn(torch.autograd.Function):
 
     @staticmethod
     def forward(ctx, x, w1, b1, w2, b2):
-        x2 = x.detach().contiguous().view(-1, x.shape[-1])
+        x2 = x.detach().contiguous().view(x.numel() // max(x.shape[-1], 1), x.shape[-1])
         with torch.no_grad():
             w1b, w2b = _bf16(w1), _bf16(w2)
             inner = w1b.shape[0] // 2
@@ -88,7 +88,7 @@ class _FeedForwardFn(torch.autograd.Function):
             y = ops.gemm_bf16_tn(h, w2b, _bf16(b2))
         ctx.save_for_backward(x2, w1, b1, w2, b2)
         ctx.x_shape = x.shape
-        return y.view(*x.shape[:-1], -1)
+        return y.view(*x.shape[:-1], y.shape[-1])
 
     @staticmethod
     def backward(ctx, dy):
@@ -152,13 +152,13 @@ def feed_forward(ff, hidden_states: torch.Tensor, scale: float = 1.0, residual: 
         return y if residual is None else y + residual
     x = x.contiguous()
     wi, bi = _geglu_weights(ff.net[0].proj)
-    h = ops.gemm_bf16_tn_ex(x.view(-1, x.shape[-1]), wi, bi, geglu=True)
+    h = ops.gemm_bf16_tn_ex(x.view(x.numel() // x.shape[-1], x.shape[-1]), wi, bi, geglu=True)
     out_lin = ff.net[2]
     r2 = None
     if residual is not None:
-        r2 = residual.contiguous().view(-1, residual.shape[-1])
+        r2 = residual.contiguous().view(residual.numel() // residual.shape[-1], residual.shape[-1])
     y = ops.gemm_bf16_tn_ex(h, _bf16(out_lin.weight), _bf16(out_lin.bias), residual=r2)
-    return y.view(*x.shape[:-1], -1)
+    return y.view(*x.shape[:-1], y.shape[-1])
 
 
 def layer_norm(norm, x: torch.Tensor) -> torch.Tensor:

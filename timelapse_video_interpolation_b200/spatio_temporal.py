@@ -123,11 +123,11 @@ def transformer_spatio_temporal_forward(model, hidden_states: torch.Tensor, enco
     for block, temporal_block in zip(model.transformer_blocks, model.temporal_transformer_blocks):
         x = basic_transformer_block_forward(block, x, encoder_hidden_states=spatial_ctx)           # :337-339
         x_mix = ops.bcast_rows_add(emb, x, S)                                                     # :341-342
-        x_mix = temporal_basic_transformer_block_forward(temporal_block, x_mix.view(BF, S, -1), num_frames=T,
+        x_mix = temporal_basic_transformer_block_forward(temporal_block, x_mix.view(BF, S, x_mix.shape[-1]), num_frames=T,
                                                          encoder_hidden_states=time_context)      # :343-347
         x = ops.blend_rows(x, x_mix, alpha, S)                                                    # :349-351
     y = ops.gemm_bf16_tn(x, _bf16_param(model.proj_out.weight), _bf16_param(model.proj_out.bias))  # :353
-    out = ops.tokens_to_nchw_add(y.view(BF, S, -1), residual, H, W)                               # :354-357
+    out = ops.tokens_to_nchw_add(y.view(BF, S, y.shape[-1]), residual, H, W)                               # :354-357
     if not return_dict:
         return (out,)
     mod = sys.modules.get(type(model).__module__)
