@@ -83,3 +83,21 @@ def test_gemm_rejects_bad_arguments(cuda):
         ops.gemm_bf16_tn(x.float(), torch.zeros(16, 64, dtype=torch.bfloat16, device=cuda))
     y = ops.gemm_bf16_tn(x[:0], torch.zeros(16, 64, dtype=torch.bfloat16, device=cuda))
     assert y.shape == (0, 16)
+
+
+@pytest.mark.parametrize("M,inner,K,bias", [(4304, 416, 64, True), (300, 32, 320, False), (129, 96, 72, True), (5000, 160, 640, True)])
+def test_geglu_epilogue_narrow_blocks(cuda, M, inner, K, bias):
+    # regression: GEGLU tiles with fewer output chunks than epilogue warps per quadrant (value/gate block of 32 -> BN = 64)
+    # never released their accumulator stage and the kernel hung (found by tools/gemm_soak.py)
+    g = torch.Generator().manual_seed(inner)
+    H = ops.geglu_block(inner)
+    x = torch.randn(M, K, generator=g).to(torch.bfloat16).to(cuda)
+    w = (torch.randn(2 * inner, K, generator=g) * K ** -0.5).to(torch.bfloat16).to(cuda)
+    b = torch.randn(2 * inner, generator=g).to(torch.bfloat16).to(cuda) if bias else None
+    wi = torch.stack([w[:inner].view(inner // H, H, -1), w[inner:].view(inner // H, H, -1)], dim=1).reshape(2 * inner, -1).contiguous()
+    bi = torch.stack([b[:inner].view(inner // H, H), b[inner:].view(inner // H, H)], dim=1).reshape(-1).contiguous() if bias else None
+    y = ops.gemm_bf16_tn_ex(x, wi, bi, geglu=True)
+    torch.cuda.synchronize()
+    pre = x.float() @ w.float().T + (b.float() if bias else 0)
+    ref = pre[:, :inner] * torch.nn.functional.gelu(pre[:, inner:])
+    assert float((y.float() - ref).abs().max()) <= 2e-2 * max(1.0, float(ref.abs().max()))

@@ -307,12 +307,15 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
       mbar_wait(&bar_acc_full[as], aph);
       tc_fence_after();
       const uint32_t t_row = tmem_base + ((uint32_t)(quad * 32) << 16) + as * kAccStride;
-      if (chalf >= chunks) {  // a one-chunk tile leaves the second warp of the quadrant without work
+      const int out_chunks = p.geglu ? chunks / 2 : chunks;
+      if (chalf >= out_chunks) {
+        // A tile with fewer OUTPUT chunks than warps per quadrant (BN = 32, or BN = 64 with GEGLU) leaves this warp without
+        // work; it must still release the accumulator stage.  (Testing `chunks` here hung GEGLU tiles of BN = 64: the loop
+        // below runs over out_chunks.)
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive(&bar_acc_empty[as]);
       }
-      const int out_chunks = p.geglu ? chunks / 2 : chunks;
       for (int c = chalf; c < out_chunks; c += kChunkStep) {
         uint32_t r[32], rg[32];
         tmem_ld_x32(t_row + c * 32, r);
