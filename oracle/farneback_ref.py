@@ -192,7 +192,11 @@ def update_matrices(R0: np.ndarray, R1: np.ndarray, flow: np.ndarray) -> np.ndar
                 sc[i] *= BORDER[n - i - 1]
         return sc[idx]
 
-    scale = edge(xs, w) * edge(ys, h)
+    # OpenCV tests `(unsigned)(x - BORDER) >= (unsigned)(width - BORDER*2) || (unsigned)(y - BORDER) >= (unsigned)(height - BORDER*2)`:
+    # with a dimension below 10 the right-hand side wraps around and the attenuation is skipped for most pixels
+    u32 = lambda v: np.mod(v, 1 << 32)
+    on_border = (u32(xs - nb) >= u32(w - 2 * nb)) | (u32(ys - nb) >= u32(h - 2 * nb))
+    scale = np.where(on_border, edge(xs, w) * edge(ys, h), f32(1)).astype(f32)
     r2, r3, r4, r5, r6 = (v * scale for v in (r2, r3, r4, r5, r6))
     M = np.empty((h, w, 5), dtype=f32)
     M[..., 0] = r4 * r4 + r6 * r6

@@ -317,7 +317,7 @@ def make_farneback():
     import cv2
     ref = _load(REF / "dataset_construction/step4_flow_check.py", "ref_step4b")
     out = {"opencv_version": np.array(cv2.__version__)}
-    for i, (h, w) in enumerate([(96, 128), (135, 240), (70, 81), (40, 200)]):
+    for i, (h, w) in enumerate([(96, 128), (135, 240), (70, 81), (40, 200), (6, 60), (40, 7)]):  # the last two: a side < 10 (border test wraps)
         r = np.random.default_rng(10 + i)
         base = cv2.resize(r.random((h // 8 + 2, w // 8 + 2, 3)).astype(np.float32), (w, h), interpolation=cv2.INTER_CUBIC)
         a = np.clip((base + 0.15 * r.random((h, w, 3)).astype(np.float32)) * 255, 0, 255).astype(np.uint8)

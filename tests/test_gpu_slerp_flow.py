@@ -129,7 +129,7 @@ def test_backward_warp_identity_and_1080p_roundtrip(cuda):
     assert not bool(occ[:, 4:, :-6].any())
 
 
-@pytest.mark.parametrize("i", range(4))
+@pytest.mark.parametrize("i", range(6))
 def test_farneback_matches_opencv_golden_and_oracle(cuda, golden_dir, i):
     import numpy as np
     from oracle import farneback_ref
@@ -141,9 +141,10 @@ def test_farneback_matches_opencv_golden_and_oracle(cuda, golden_dir, i):
     assert isinstance(flow, np.ndarray) and flow.shape == ref.shape and flow.dtype == np.float32
     err = np.abs(flow - ref)
     print(f"farneback {ref.shape}: vs cv2 max {err.max():.2e} mean {err.mean():.2e} (max |flow| {np.abs(ref).max():.2f})")
-    assert err.max() < 5e-3 and err.mean() < 5e-5
+    mag = max(1.0, float(np.abs(ref).max()))
+    assert err.max() < 5e-3 * mag and err.mean() < 5e-5 * mag
     ora = farneback_ref.calc_optical_flow_farneback(farneback_ref.gray_from_bgr(a), farneback_ref.gray_from_bgr(b))
-    assert np.abs(flow - ora).max() < 5e-3
+    assert np.abs(flow - ora).max() < 5e-3 * mag
     # gray input path and CUDA-tensor path
     ga = torch.from_numpy(z[f"gray{i}"]).to(cuda)
     gb = torch.from_numpy(farneback_ref.gray_from_bgr(b)).to(cuda)
