@@ -78,7 +78,7 @@ def test_layer_norm_matches_oracle(cuda, rows, C):
     y = tvi.layer_norm(norm, x)
     torch.cuda.synchronize()
     ref = feedforward_ref.layer_norm_ref(norm, x)
-    err = float((y.float().cpu() - ref).abs().max())
+    err = float((y.detach().float().cpu() - ref.detach()).abs().max())
     print(f"layer_norm rows={rows} C={C}: max abs err {err:.3e}")
     assert err <= 2 ** -7 * max(1.0, float(ref.abs().max()))  # one bf16 rounding of the result
 
