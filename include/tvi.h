@@ -254,7 +254,7 @@ int tvi_attn_spatial_fwd(const tvi_bf16* q, const tvi_bf16* k, const tvi_bf16* v
 
 /* Same call with an explicit kernel choice (parity tests exercise both; AUTO is what
  * tvi_attn_spatial_fwd uses: tcgen05 when S and Skv are >= 1024, mma.sync otherwise).
- * TVI_SPATIAL_TCGEN05: TMA-fed tcgen05.mma, S/P/O in tensor memory, 256 query rows per CTA.
+ * TVI_SPATIAL_TCGEN05: persistent TMA-fed tcgen05.mma kernel, S/P/O in tensor memory, work items of 256 query rows.
  * TVI_SPATIAL_MMA_SYNC: register-resident flash kernel on mma.sync (short sequences). */
 #define TVI_SPATIAL_AUTO 0
 #define TVI_SPATIAL_MMA_SYNC 1

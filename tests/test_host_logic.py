@@ -148,3 +148,38 @@ def test_weight_caches_are_keyed_by_live_modules():
         del attn, fused, want
         gc.collect()
         assert len(proc._wcache) == 0
+
+
+def test_cache_generation_tracks_data_copy():
+    """`param.data.copy_()` (diffusers EMAModel.copy_to / restore, reference
+    src/train_decouples.py:1122-1124, :1199) does not bump `_version`; the derived-weight caches are keyed on a
+    generation that `invalidate_caches()`, every install / uninstall and the train -> no-grad transition advance."""
+    import torch
+    from timelapse_video_interpolation_b200 import caches, invalidate_caches
+    from timelapse_video_interpolation_b200.modules import Attention
+    from timelapse_video_interpolation_b200.processor import TviAttnProcessor
+
+    proc = TviAttnProcessor()
+    attn = Attention(64, None, heads=1, dim_head=64, processor=proc).to(torch.bfloat16)
+    w1 = proc._fused(attn, ("to_q", "to_k", "to_v"))
+    assert proc._fused(attn, ("to_q", "to_k", "to_v")) is w1            # cache hit
+    v0 = attn.to_q.weight._version
+    attn.to_q.weight.data.copy_(torch.ones_like(attn.to_q.weight))     # invisible to _version ...
+    assert attn.to_q.weight._version == v0
+    assert proc._fused(attn, ("to_q", "to_k", "to_v")) is w1            # ... so the stale copy is still served
+    invalidate_caches(attn)
+    w2 = proc._fused(attn, ("to_q", "to_k", "to_v"))
+    assert w2 is not w1 and torch.equal(w2[:64], torch.ones(64, 64, dtype=torch.bfloat16))
+    # train -> no-grad transition (the reference's train / EMA copy_to / validate sequence) starts a new generation
+    g0 = caches.generation()
+    caches.note_call(True)
+    caches.note_call(True)
+    assert caches.generation() == g0
+    caches.note_call(False)
+    assert caches.generation() == g0 + 1
+    caches.note_call(False)
+    assert caches.generation() == g0 + 1
+    # an optimizer-style in-place update (bumps _version) is seen without any of that
+    with torch.no_grad():
+        attn.to_k.weight.add_(1.0)
+    assert proc._fused(attn, ("to_q", "to_k", "to_v")) is not w2

@@ -12,7 +12,7 @@ from __future__ import annotations
 import torch
 from torch.autograd.function import once_differentiable
 
-from . import _lib, ops
+from . import _lib, caches, ops
 
 
 def _to_bf16(t):
@@ -237,6 +237,7 @@ def attention_forward(proc, attn, x, e, heads: int, scale: float, wo, bo, bias, 
     wq, wk, wv = attn.to_q.weight, attn.to_k.weight, attn.to_v.weight
     needs_grad = torch.is_grad_enabled() and any(
         t is not None and t.requires_grad for t in (x, e, wq, wk, wv, wo, bo))
+    caches.note_call(needs_grad)
     w_o = _to_bf16(wo).contiguous()
     b_o = _to_bf16(bo).contiguous() if bo is not None else None
     if not needs_grad and not (residual is not None and torch.is_grad_enabled() and residual.requires_grad):

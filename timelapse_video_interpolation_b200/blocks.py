@@ -24,7 +24,7 @@ from typing import Optional
 
 import torch
 
-from . import _lib
+from . import _lib, caches
 from .feedforward import feed_forward, layer_norm
 from .processor import TviAttnProcessor
 
@@ -136,6 +136,7 @@ def _is_temporal(m) -> bool:
 def install_blocks(model: torch.nn.Module, processor: Optional[TviAttnProcessor] = None) -> int:
     """Re-binds the forward of every (Temporal)BasicTransformerBlock-shaped module; returns how many."""
     proc = processor or TviAttnProcessor()
+    caches.invalidate_caches()
     n = 0
     for _, m in model.named_modules():
         if _is_temporal(m):
@@ -158,6 +159,7 @@ def install_blocks(model: torch.nn.Module, processor: Optional[TviAttnProcessor]
 
 
 def uninstall_blocks(model: torch.nn.Module) -> int:
+    caches.invalidate_caches()
     n = 0
     for _, m in model.named_modules():
         if hasattr(m, "_tvi_saved_block_forward"):

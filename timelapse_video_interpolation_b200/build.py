@@ -40,7 +40,7 @@ def sources() -> list[Path]:
 
 
 def _headers() -> list[Path]:
-    return sorted(CSRC.glob("*.cuh")) + sorted((PKG.parent / "include").glob("*.h"))
+    return sorted(CSRC.glob("*.cuh")) + sorted(CSRC.glob("*.inc")) + sorted((PKG.parent / "include").glob("*.h"))
 
 
 def _stale(target: Path, deps: list[Path]) -> bool:

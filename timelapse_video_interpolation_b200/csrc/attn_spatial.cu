@@ -213,7 +213,7 @@ attn_spatial_kernel(const tvi_bf16* __restrict__ q, const tvi_bf16* __restrict__
 
 namespace tvi {
 int launch_spatial_tc(const tvi_bf16* q, const tvi_bf16* k, const tvi_bf16* v, tvi_bf16* o, float* lse, int batch, int heads,
-                      int S, int Skv, int64_t ldq, int64_t ldk, int64_t ldv, int64_t ldo, float scale, cudaStream_t st);
+                       int S, int Skv, int64_t ldq, int64_t ldk, int64_t ldv, int64_t ldo, float scale, int poly, cudaStream_t st);
 }
 
 extern "C" int tvi_attn_spatial_fwd_algo(const tvi_bf16* q, const tvi_bf16* k, const tvi_bf16* v, tvi_bf16* o, float* lse,
@@ -235,8 +235,18 @@ extern "C" int tvi_attn_spatial_fwd_algo(const tvi_bf16* q, const tvi_bf16* k, c
     // prologue; short sequences (L2 / mid level: 576, 144 tokens) stay on the mma.sync kernel
     algo = (S >= 1024 && Skv >= 1024) ? TVI_SPATIAL_TCGEN05 : TVI_SPATIAL_MMA_SYNC;
   }
-  if (algo == TVI_SPATIAL_TCGEN05)
-    return launch_spatial_tc(q, k, v, o, lse, batch, heads, S, Skv, ldq, ldk, ldv, ldo, scale, (cudaStream_t)stream);
+  if (algo == TVI_SPATIAL_TCGEN05) {
+    int poly = 4;
+#ifdef TVI_TC_POLY_SWEEP  // tuning builds only (tools/micro): share of exponentials on the FMA pipe from the environment
+    static int env_poly = -1;
+    if (env_poly < 0) {
+      const char* e = getenv("TVI_TC_POLY");
+      env_poly = e ? atoi(e) : 4;
+    }
+    poly = env_poly;
+#endif
+    return launch_spatial_tc(q, k, v, o, lse, batch, heads, S, Skv, ldq, ldk, ldv, ldo, scale, poly, (cudaStream_t)stream);
+  }
   static bool configured[64] = {false};
   int dev = 0;
   TVI_CUDA_OK(cudaGetDevice(&dev));

@@ -10,7 +10,8 @@ Drop-in for `FeedForward.forward(hidden_states, scale=1.0)` (reference src/model
     y = h W2^T + b2 (+ residual)   bias and the block's residual add fused in the epilogue
 
 `install_feed_forward(model)` re-binds `forward` on every FeedForward-shaped module (duck-typed like the attention
-plugin).  Inference only for now: a call that needs gradients raises (the backward of this path is not built).
+plugin).  A call that needs gradients goes on the autograd tape through `_FeedForwardFn` / `_LayerNormFn` (backward
+kernels: geglu_bwd, layernorm_bwd, GEMM dgrad / wgrad); the no-grad path uses the fused GEGLU / residual epilogues.
 """
 from __future__ import annotations
 
@@ -20,7 +21,7 @@ from typing import Optional
 
 import torch
 
-from . import _lib, ops
+from . import _lib, caches, ops
 
 __all__ = ["feed_forward", "layer_norm", "install_feed_forward", "uninstall_feed_forward"]
 
@@ -35,9 +36,10 @@ def _is_feed_forward(m) -> bool:
 
 def _geglu_weights(proj):
     """proj.weight [2*inner, dim] (value rows then gate rows, the `.chunk(2, -1)` order) -> rows interleaved in
-    blocks of H = tvi_geglu_block(inner); cached per (data_ptr, version) so state_dict keys stay untouched."""
+    blocks of H = tvi_geglu_block(inner); cached per (cache generation, data_ptr, version) so state_dict keys stay
+    untouched (caches.py explains the generation: `.data` writes do not bump `_version`)."""
     w, b = proj.weight, proj.bias
-    sig = (w.data_ptr(), w._version, w.dtype, None if b is None else (b.data_ptr(), b._version))
+    sig = (caches.generation(), w.data_ptr(), w._version, w.dtype, None if b is None else (b.data_ptr(), b._version))
     hit = _cache.get(proj)
     if hit is not None and hit[0] == sig:
         return hit[1], hit[2]
@@ -145,7 +147,9 @@ def feed_forward(ff, hidden_states: torch.Tensor, scale: float = 1.0, residual: 
         raise _lib.TviError(_lib.TVI_ERR_INVALID, "feed_forward: hidden_states is not on a CUDA device (there is no CPU fallback)")
     if x.dtype != torch.bfloat16:
         raise _lib.TviError(_lib.TVI_ERR_UNSUPPORTED, f"feed_forward: hidden_states is {x.dtype}; the libtvi path is bf16")
-    if torch.is_grad_enabled() and (x.requires_grad or any(p.requires_grad for p in ff.parameters())):
+    on_tape = torch.is_grad_enabled() and (x.requires_grad or any(p.requires_grad for p in ff.parameters()))
+    caches.note_call(on_tape)
+    if on_tape:
         # training: the call goes on the autograd tape; the residual add has no fused backward and is added on the tape
         proj, out_lin = ff.net[0].proj, ff.net[2]
         y = _FeedForwardFn.apply(x, proj.weight, proj.bias, out_lin.weight, out_lin.bias)
@@ -174,6 +178,7 @@ def layer_norm(norm, x: torch.Tensor) -> torch.Tensor:
 
 def install_feed_forward(model: torch.nn.Module) -> int:
     """Re-binds `forward` of every FeedForward-shaped module of `model` to the libtvi path; returns how many."""
+    caches.invalidate_caches()
     n = 0
     for _, m in model.named_modules():
         if not _is_feed_forward(m):
@@ -190,6 +195,7 @@ def install_feed_forward(model: torch.nn.Module) -> int:
 
 
 def uninstall_feed_forward(model: torch.nn.Module) -> int:
+    caches.invalidate_caches()
     n = 0
     for _, m in model.named_modules():
         if hasattr(m, "_tvi_saved_ff_forward"):

@@ -27,7 +27,7 @@ from typing import Optional
 
 import torch
 
-from . import _lib, ops
+from . import _lib, caches, ops
 from .autograd import attention_forward
 
 __all__ = ["TviAttnProcessor", "install", "uninstall"]
@@ -64,9 +64,10 @@ class TviAttnProcessor:
     # ------------------------------------------------------------------ weight caches
     def _fused(self, attn, names: tuple[str, ...]) -> torch.Tensor:
         """Derived, never-registered fused weight ([sum(out), in], bf16); rebuilt when any source
-        parameter changes (optimizer step bumps `_version`) so state_dict keys are untouched."""
+        parameter changes (optimizer step bumps `_version`) or the cache generation advances (caches.py: `.data`
+        writes such as EMA copy_to are invisible to `_version`), so state_dict keys are untouched."""
         ws = [_linear_weight(getattr(attn, n), n) for n in names]
-        sig = tuple((w.data_ptr(), w._version, w.dtype, w.device) for w in ws)
+        sig = (caches.generation(),) + tuple((w.data_ptr(), w._version, w.dtype, w.device) for w in ws)
         per_module = self._wcache.get(attn)
         if per_module is None:
             per_module = self._wcache.setdefault(attn, {})
@@ -192,6 +193,7 @@ def install(model: torch.nn.Module, processor: Optional[TviAttnProcessor] = None
     are replaced by a forward that dispatches to the processor with the same bias / statistics
     semantics (options `temporal_ramp_bias`, `temporal_stats_sink`).
     """
+    caches.invalidate_caches()
     shared = processor or TviAttnProcessor()
     temporal = None
     n = 0
@@ -229,6 +231,7 @@ def install(model: torch.nn.Module, processor: Optional[TviAttnProcessor] = None
 
 def uninstall(model: torch.nn.Module) -> int:
     """Restores the processors / forwards that `install` replaced."""
+    caches.invalidate_caches()
     n = 0
     for _, m in model.named_modules():
         if hasattr(m, "_tvi_saved_processor"):

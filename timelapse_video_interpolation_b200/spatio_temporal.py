@@ -22,7 +22,7 @@ from typing import Optional
 
 import torch
 
-from . import _lib, ops
+from . import _lib, caches, ops
 from .blocks import (_no_grad_only, basic_transformer_block_forward, install_blocks,
                      temporal_basic_transformer_block_forward)
 from .feedforward import _bf16 as _bf16_param
@@ -40,7 +40,7 @@ def _frame_embedding(model, batch_size: int, num_frames: int, device) -> torch.T
     """emb[b*T + t] = time_pos_embed(time_proj(t)) (:308-315): depends on the frame index and the weights only."""
     tp = model.time_pos_embed
     ws = (tp.linear_1.weight, tp.linear_1.bias, tp.linear_2.weight, tp.linear_2.bias)
-    sig = (batch_size, num_frames, str(device)) + tuple((w.data_ptr(), w._version) for w in ws)
+    sig = (caches.generation(), batch_size, num_frames, str(device)) + tuple((w.data_ptr(), w._version) for w in ws)
     hit = getattr(model, "_tvi_frame_emb", None)
     if hit is not None and hit[0] == sig:
         return hit[1]
@@ -57,7 +57,7 @@ def _alpha(mixer, image_only_indicator: torch.Tensor) -> torch.Tensor:
     dtype (`.to(x_spatial.dtype)`) applied so that the blend weights are the bf16-rounded ones."""
     strategy = getattr(mixer, "merge_strategy", "learned_with_images")
     # the same indicator tensor comes back for every module of every denoising step: cache on (tensor, version)
-    sig = (image_only_indicator.data_ptr(), image_only_indicator._version, tuple(image_only_indicator.shape),
+    sig = (caches.generation(), image_only_indicator.data_ptr(), image_only_indicator._version, tuple(image_only_indicator.shape),
            mixer.mix_factor.data_ptr(), mixer.mix_factor._version)
     if torch.cuda.is_current_stream_capturing():  # a CUDA graph must recompute alpha from the static indicator buffer
         return _alpha_uncached(mixer, image_only_indicator, strategy)
@@ -142,6 +142,7 @@ def _is_spatio_temporal(m) -> bool:
 
 def install_spatio_temporal(model: torch.nn.Module, processor=None) -> int:
     """Rebinds `forward` of every TransformerSpatioTemporalModel-shaped module (and of its blocks); returns how many."""
+    caches.invalidate_caches()
     n = 0
     for _, m in model.named_modules():
         if _is_spatio_temporal(m):
@@ -155,6 +156,7 @@ def install_spatio_temporal(model: torch.nn.Module, processor=None) -> int:
 
 def uninstall_spatio_temporal(model: torch.nn.Module) -> int:
     from .blocks import uninstall_blocks
+    caches.invalidate_caches()
     n = 0
     for _, m in model.named_modules():
         if hasattr(m, "_tvi_saved_model_forward"):

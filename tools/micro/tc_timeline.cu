@@ -1,0 +1,139 @@
+// Debug harness for attn_spatial_tc_kernel (not part of libtvi): times the L0 launch (28 frames x 5 heads x 9216
+// tokens) with CUDA events and, when built with -DTVI_TC_TIMELINE, prints the cycle stamps the softmax and MMA warps
+// of one CTA recorded over 16 key steps.  Built by tools/micro/build_micro.sh from the library's own sources.
+//   ./tc_timeline [poly 0|4|5|6] [batch] [S] [reps]
+#include <cuda_runtime.h>
+#include <cuda_bf16.h>
+#include <cstdint>
+#include <cstdio>
+#include <cstdlib>
+#include <vector>
+#include "../../include/tvi.h"
+
+#ifdef TVI_TC_TIMELINE
+extern "C" int tvi_debug_tc_timeline(long long* dev_buf);
+#endif
+
+int main(int argc, char** argv) {
+  const char* poly = argc > 1 ? argv[1] : "0";
+  setenv("TVI_TC_POLY", poly, 1);
+  const int algo = TVI_SPATIAL_TCGEN05;
+  const int batch = argc > 2 ? atoi(argv[2]) : 28;
+  const int S = argc > 3 ? atoi(argv[3]) : 9216;
+  const int heads = 5, C = 320;
+  const size_t n = (size_t)batch * S;
+  std::vector<__nv_bfloat16> h(n * 3 * C);
+  uint32_t s = 777u;
+  for (size_t i = 0; i < h.size(); ++i) {
+    s = s * 1664525u + 1013904223u;
+    // sum of two uniforms ~ roughly bell shaped, unit-ish variance
+    const float u = ((s >> 8) * (1.0f / 16777216.0f) - 0.5f);
+    s = s * 1664525u + 1013904223u;
+    const float v = ((s >> 8) * (1.0f / 16777216.0f) - 0.5f);
+    h[i] = __float2bfloat16((u + v) * 2.45f);
+  }
+  __nv_bfloat16 *qkv, *o;
+  cudaMalloc(&qkv, h.size() * 2);
+  cudaMalloc(&o, n * C * 2);
+  cudaMemcpy(qkv, h.data(), h.size() * 2, cudaMemcpyHostToDevice);
+  float* lse;
+  cudaMalloc(&lse, n * heads * 4);
+  auto call_algo = [&](int a, __nv_bfloat16* out) {
+    return tvi_attn_spatial_fwd_algo((const tvi_bf16*)qkv, (const tvi_bf16*)(qkv + C), (const tvi_bf16*)(qkv + 2 * C), (tvi_bf16*)out, lse,
+                                     batch, heads, S, S, 64, 3 * C, 3 * C, 3 * C, C, 0.125f, a, nullptr);
+  };
+  auto call = [&]() { return call_algo(algo, o); };
+  for (int i = 0; i < 3; ++i) {
+    const int rc = call();
+    if (rc) {
+      printf("call failed: %s\n", tvi_last_error());
+      return 1;
+    }
+  }
+  cudaEvent_t e0, e1;
+  cudaEventCreate(&e0);
+  cudaEventCreate(&e1);
+  const int reps = argc > 4 ? atoi(argv[4]) : 10;
+  cudaEventRecord(e0);
+  for (int i = 0; i < reps; ++i) call();
+  cudaEventRecord(e1);
+  cudaEventSynchronize(e1);
+  float ms;
+  cudaEventElapsedTime(&ms, e0, e1);
+  ms /= reps;
+  const double flop = 4.0 * batch * heads * (double)S * S * 64;
+  printf("poly %s batch %d S %d: %.4f ms per launch, %.1f TFLOP/s\n", poly, batch, S, ms, flop / ms * 1e-9);
+  // checksum so that variants can be compared for gross errors
+  std::vector<__nv_bfloat16> ho(n * C);
+  cudaMemcpy(ho.data(), o, ho.size() * 2, cudaMemcpyDeviceToHost);
+  double cs = 0, ca = 0;
+  for (size_t i = 0; i < ho.size(); i += 97) {
+    const double v = __bfloat162float(ho[i]);
+    cs += v;
+    ca += v < 0 ? -v : v;
+  }
+  printf("checksum %.6f abs %.6f\n", cs, ca);
+  {  // compare with the mma.sync kernel (independent code path)
+    __nv_bfloat16* o2;
+    cudaMalloc(&o2, n * C * 2);
+    std::vector<float> l1(n * heads), l2(n * heads);
+    cudaMemcpy(l1.data(), lse, l1.size() * 4, cudaMemcpyDeviceToHost);
+    if (call_algo(TVI_SPATIAL_MMA_SYNC, o2)) printf("reference call failed: %s\n", tvi_last_error());
+    cudaDeviceSynchronize();
+    std::vector<__nv_bfloat16> h2(n * C);
+    cudaMemcpy(h2.data(), o2, h2.size() * 2, cudaMemcpyDeviceToHost);
+    cudaMemcpy(l2.data(), lse, l2.size() * 4, cudaMemcpyDeviceToHost);
+    double md = 0, mv = 0, ml = 0;
+    size_t bad = 0;
+    for (size_t i = 0; i < ho.size(); ++i) {
+      const double a = __bfloat162float(ho[i]), b = __bfloat162float(h2[i]);
+      const double d = a > b ? a - b : b - a;
+      if (!(d <= 1e30)) ++bad;
+      if (d > md) md = d;
+      if ((b < 0 ? -b : b) > mv) mv = b < 0 ? -b : b;
+    }
+    for (size_t i = 0; i < l1.size(); ++i) {
+      const double d = l1[i] > l2[i] ? l1[i] - l2[i] : l2[i] - l1[i];
+      if (d > ml) ml = d;
+    }
+    printf("vs mma.sync kernel: max |diff| %.5f (max |o| %.4f), non-finite %zu, max |lse diff| %.6f\n", md, mv, bad, ml);
+    cudaFree(o2);
+  }
+  cudaError_t ce = cudaDeviceSynchronize();
+  if (ce != cudaSuccess) printf("CUDA error: %s\n", cudaGetErrorString(ce));
+#ifdef TVI_TC_TIMELINE
+  long long* tl;
+  const int kWords = 2048 + 2 * 16 * 8;
+  cudaMalloc(&tl, kWords * 8);
+  cudaMemset(tl, 0, kWords * 8);
+  tvi_debug_tc_timeline(tl);
+  call();
+  cudaDeviceSynchronize();
+  std::vector<long long> t(kWords);
+  cudaMemcpy(t.data(), tl, kWords * 8, cudaMemcpyDeviceToHost);
+  long long t0 = t[0];
+  const int nsw = 16, nev = 5, nmev = 3, mstride = 8;
+  printf("softmax warps: step start (rel.) | deltas between consecutive stamps ; (step period)\n");
+  for (int w = 0; w < nsw; ++w) {
+    printf("softmax warp %2d:\n", w);
+    for (int j = 0; j < 16; ++j) {
+      const long long* e = &t[(w * 16 + j) * 8];
+      const long long prev = j ? t[(w * 16 + j - 1) * 8] : e[0];
+      printf("  step %2d: %7lld |", j, e[0] - t0);
+      for (int k = 1; k < nev; ++k) printf(" %5lld |", e[k] - e[k - 1]);
+      printf(" ; (%lld)\n", e[0] - prev);
+    }
+  }
+  printf("mma warps: first stamp (rel.) | deltas ; period\n");
+  for (int w = 0; w < 2; ++w) {
+    for (int j = 0; j < 16; ++j) {
+      const long long* e = &t[2048 + (w * 16 + j) * mstride];
+      const long long prev = j ? t[2048 + (w * 16 + j - 1) * mstride] : e[0];
+      printf("  tile %d step %2d: %7lld |", w, j, e[0] - t0);
+      for (int k = 1; k < nmev; ++k) printf(" %5lld |", e[k] - e[k - 1]);
+      printf(" ; (%lld)\n", e[0] - prev);
+    }
+  }
+#endif
+  return 0;
+}
