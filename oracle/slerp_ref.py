@@ -1,6 +1,16 @@
 """CPU restatement of the latent slerp spec (test infrastructure).  PARITY UNPINNED: the reference's
 frame_slerp_interp.py is a 0-byte file (unused flags at src/train_decouples.py:1566-1567,
 src/test.py:648-649), so this file and SURVEY.md §8.1 row A1 ARE the specification.
+
+The algorithm is the one every Stable-Diffusion latent-interpolation script uses — the public `slerp(t, v0, v1,
+DOT_THRESHOLD=0.9995)` gist by Andrej Karpathy / Xander Steenbrugge ("stablediffusionwalk.py", 2022; copied into the
+diffusers community pipelines `examples/community/interpolate_stable_diffusion.py` and `unclip_*_interpolation.py`):
+    dot = sum(v0 * v1 / (norm(v0) * norm(v1)))
+    if abs(dot) > DOT_THRESHOLD:  v2 = (1 - t) * v0 + t * v1                       # nearly colinear: lerp
+    else:  theta_0 = arccos(dot); theta_t = theta_0 * t
+           v2 = sin(theta_0 - theta_t) / sin(theta_0) * v0 + sin(theta_t) / sin(theta_0) * v1
+with the whole latent of a clip as one vector and t = i / (T - 1).  That named algorithm — threshold, lerp fallback, the
+two sine coefficients — is what is restated below (coefficients in fp64, the blend in fp32 like the fp32 torch original).
 """
 from __future__ import annotations
 

@@ -18,7 +18,15 @@ container (needs /root/reference); the GPU box uses the .npz files.
   — every other line that runs (the block forwards, the FeedForward container, Attention + processor) is the reference's.
 * spatio_temporal.npz  — src/models/transformer_temporal.py: the reference's own `TransformerSpatioTemporalModel` (forward
   :253-360) on its own blocks; the un-vendored diffusers leaves Timesteps / TimestepEmbedding / AlphaBlender are the
-  restatements in timelapse_video_interpolation_b200/modules.py.
+  restatements in timelapse_video_interpolation_b200/modules.py.  NOTE (circularity): for those three leaves this golden
+  pins the package's OWN mirrors against themselves — it proves the reference's module code around them (GroupNorm,
+  proj_in / proj_out, block order, `+ emb`, blend call, residual, layouts), not the leaves' arithmetic, which stays
+  "restated from the published diffusers 0.24 source, unpinned" (DESIGN.md §2).
+* step_glue.npz        — src/pipelines/pipeline_stable_video_diffusion_efficient_interp.py:542-546 (CFG duplication,
+  scale_model_input, concat with the image latents over dim 2) and :563-566 (per-frame guidance combine): those source
+  lines are sliced out of the reference file at generation time and exec'd, the way temporal_patched.npz is made.  The one
+  leaf they call, `scheduler.scale_model_input` (un-vendored diffusers EulerDiscreteScheduler), is the published
+  `sample / sqrt(sigma^2 + 1)`; `scheduler.step` is NOT part of this golden (declared-unpinned leaf, oracle/step_ref.py).
 * farneback.npz        — dataset_construction/step4_flow_check.py:compute_optical_flow_farneback imported as is, i.e. the
   output of cv2.cvtColor + cv2.calcOpticalFlowFarneback (third-party OpenCV, 4.13.0 here) on synthetic frames.
 """
@@ -311,6 +319,49 @@ def make_spatio_temporal(ap):
     print("spatio_temporal.npz", tuple(y.shape), float(y.abs().max()))
 
 
+def make_step():
+    """Pins oracle/step_ref.py:model_input_ref / cfg_ref to the reference's own loop-body lines."""
+    src = (REF / "src/pipelines/pipeline_stable_video_diffusion_efficient_interp.py").read_text().splitlines()
+
+    def block(first_marker, n):
+        i = next(k for k, l in enumerate(src) if first_marker in l)
+        return i, "\n".join(src[i:i + n])
+
+    i_in, _ = block("latent_model_input = torch.cat([latents] * 2) if do_classifier_free_guidance else latents", 1)
+    i_cat = next(k for k in range(i_in, i_in + 8) if "latent_model_input = torch.cat([latent_model_input, image_latents], dim=2)" in src[k])
+    code_in = textwrap.dedent("\n".join(l for l in src[i_in:i_cat + 1] if l.strip() and not l.strip().startswith("#")))
+    i_cfg = next(k for k, l in enumerate(src) if "noise_pred_uncond, noise_pred_cond = noise_pred.chunk(2)" in l)
+    code_cfg = textwrap.dedent("\n".join(src[i_cfg:i_cfg + 2]))
+    assert "self.guidance_scale * (noise_pred_cond - noise_pred_uncond)" in code_cfg
+    print("step glue lines:", i_in + 1, "-", i_cat + 1, "and", i_cfg + 1, "-", i_cfg + 2)
+
+    class Scheduler:  # diffusers EulerDiscreteScheduler.scale_model_input (published formula; the only leaf these lines call)
+        def __init__(self, sigma):
+            self.sigma = sigma
+
+        def scale_model_input(self, sample, t):
+            return sample / ((self.sigma ** 2 + 1) ** 0.5)
+
+    out = {}
+    g = torch.Generator().manual_seed(31)
+    for tag, B, T, C, H, W, sigma in (("a", 1, 14, 4, 9, 16, 7.5), ("b", 2, 5, 4, 6, 8, 0.31)):
+        latents = torch.randn(B, T, C, H, W, generator=g) * sigma
+        image_latents = torch.randn(2 * B, T, C, H, W, generator=g)
+        noise_pred = torch.randn(2 * B, T, C, H, W, generator=g)
+        # per-frame guidance (:518-530): linspace(min, max, T)[None] -> repeated per clip -> _append_dims to 5-D
+        gs = torch.linspace(1.0, 3.0, T)[None].repeat(B, 1)[:, :, None, None, None]
+        this = types.SimpleNamespace(scheduler=Scheduler(sigma), guidance_scale=gs)
+        ns = {"torch": torch, "self": this, "latents": latents, "image_latents": image_latents, "t": None,
+              "do_classifier_free_guidance": True, "noise_pred": noise_pred.clone()}
+        exec(code_in, ns)
+        exec(code_cfg, ns)
+        out.update({f"{tag}.latents": latents.numpy(), f"{tag}.image_latents": image_latents.numpy(), f"{tag}.noise_pred": noise_pred.numpy(),
+                    f"{tag}.guidance_scale": gs.numpy(), f"{tag}.sigma": np.float64(sigma),
+                    f"{tag}.latent_model_input": ns["latent_model_input"].numpy(), f"{tag}.guided": ns["noise_pred"].numpy()})
+    np.savez_compressed(OUT / "step_glue.npz", **out)
+    print("step_glue.npz", {k: tuple(v.shape) for k, v in out.items() if k.endswith("latent_model_input") or k.endswith("guided")})
+
+
 def make_farneback():
     """cv2.calcOpticalFlowFarneback itself (OpenCV 4.13 in this image) with the reference's parameters
     (dataset_construction/step4_flow_check.py:13-22) on synthetic textured BGR frames related by a small affine motion."""
@@ -337,4 +388,5 @@ if __name__ == "__main__":
     make_temporal_patched(ap)
     make_blocks(ap)
     make_spatio_temporal(ap)
+    make_step()
     make_farneback()

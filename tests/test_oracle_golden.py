@@ -197,3 +197,22 @@ def test_farneback_oracle_matches_opencv(golden_dir, i):
     mag = max(1.0, float(np.abs(ref).max()))   # cases 4, 5 have a side < 10: OpenCV's unsigned border test wraps, flows are large
     assert err.max() < 1e-3 * mag and err.mean() < 1e-5 * mag, (err.max(), err.mean())
     assert np.abs(ref).max() > 1.0                                   # the fixture really moves
+
+
+def test_step_glue_oracle_matches_reference_loop_lines(golden_dir):
+    """oracle/step_ref.py:model_input_ref / cfg_ref against the reference's own loop-body lines
+    (src/pipelines/pipeline_stable_video_diffusion_efficient_interp.py:542-546, :565-566; tests/golden/make_golden.py:make_step).
+    The Euler scheduler step stays a declared-unpinned leaf."""
+    from oracle import step_ref
+    z = np.load(golden_dir / "step_glue.npz")
+    for tag in ("a", "b"):
+        lat, img = torch.from_numpy(z[f"{tag}.latents"]), torch.from_numpy(z[f"{tag}.image_latents"])
+        sigma = float(z[f"{tag}.sigma"])
+        got = step_ref.model_input_ref(lat, img, sigma)
+        want = torch.from_numpy(z[f"{tag}.latent_model_input"])
+        assert got.shape == want.shape
+        assert float((got.double() - want.double()).abs().max()) <= 1e-6 * max(1.0, float(want.abs().max()))
+        guided = step_ref.cfg_ref(torch.from_numpy(z[f"{tag}.noise_pred"]), torch.from_numpy(z[f"{tag}.guidance_scale"]))
+        want = torch.from_numpy(z[f"{tag}.guided"])
+        assert guided.shape == want.shape
+        assert float((guided - want.double()).abs().max()) <= 1e-6 * max(1.0, float(want.abs().max()))

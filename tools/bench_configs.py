@@ -444,6 +444,192 @@ def cfg_farneback(steps):
     emit(rec)
 
 
+# ---------------------------------------------------------------------------------------------------
+# bench.py's extra keys (`secondary`, `unet_step`, `train_step`): short runs after its timed regions, rank 0 / N = 1
+# ---------------------------------------------------------------------------------------------------
+def _frac(nbytes, ms, hbm):
+    gbs = nbytes / (ms * 1e-3) / 1e9
+    return {"ms": ms, "algorithmic_bytes": int(nbytes), "gbs": gbs, "frac": gbs / hbm, "bound": "hbm"}
+
+
+def _secondary(pk, steps=5):
+    hbm = pk["hbm"]
+    sec = {"peak_hbm_gbs": hbm, "peak_source": pk["src"]}
+    # config 1: slerp, 4096 clips, T = 14
+    n, T, clips = 4 * 72 * 128, 14, 4096
+    g = torch.Generator().manual_seed(0)
+    v0 = torch.randn(clips, 4, 72, 128, generator=g).to(DEV)
+    v1 = torch.randn(clips, 4, 72, 128, generator=g).to(DEV)
+    out = torch.empty(clips, T, 4, 72, 128, device=DEV)
+    ms = timed(lambda: ops.slerp_f32(v0, v1, T, 0.9995, out=out), steps)
+    sec["slerp_4096clips_T14"] = dict(_frac((2 + T) * n * 4 * clips, ms, hbm), clip_frames_per_s=clips * T / (ms * 1e-3))
+    del v0, v1, out
+    torch.cuda.empty_cache()
+    # config 4: flow cosine + backward warp / consistency, 32 pairs of 1080p
+    H, W, B = 1080, 1920, 32
+    g = torch.Generator().manual_seed(B)
+    img = torch.rand(B, 3, H, W, generator=g).to(DEV)
+    coarse = torch.randn(B, 2, H // 30, W // 30, generator=g).to(DEV) * 5
+    f = torch.nn.functional.interpolate(coarse, size=(H, W), mode="bicubic", align_corners=False).contiguous()
+    fb = (-f + torch.randn(B, 2, H, W, generator=g).to(DEV) * 0.2)
+    fa_hwc, fb_hwc = f.permute(0, 2, 3, 1).contiguous(), fb.permute(0, 2, 3, 1).contiguous()
+    warped, mask = torch.empty_like(img), torch.empty(B, H, W, dtype=torch.uint8, device=DEV)
+    ms = timed(lambda: ops.backward_warp_f32(img, f, fb, 0.01, 0.5, warped=warped, mask=mask), steps)
+    sec["flow_warp_check_32x1080p"] = dict(_frac(((3 + 2 + 2) * 4 + 3 * 4 + 1) * H * W * B, ms, hbm), pairs_per_s=B / (ms * 1e-3))
+    ms = timed(lambda: ops.flow_cosine_f32(fa_hwc, fb_hwc, True), steps)
+    sec["flow_cosine_32x1080p"] = dict(_frac(2 * 2 * 4 * H * W * B, ms, hbm), pairs_per_s=B / (ms * 1e-3))
+    del img, coarse, f, fb, fa_hwc, fb_hwc, warped, mask
+    torch.cuda.empty_cache()
+    # N3: Farneback, one 1080p pair and a 14-frame clip (13 pairs)
+    import numpy as np
+    rng = np.random.default_rng(0)
+    base = torch.from_numpy(rng.random((H // 8 + 2, W // 8 + 2, 3)).astype(np.float32)).permute(2, 0, 1)[None]
+    im = torch.nn.functional.interpolate(base, size=(H + 8, W + 8), mode="bicubic")[0].permute(1, 2, 0)
+    im = (im.clamp(0, 1) * 255).to(torch.uint8)
+    da, db = im[4:-4, 4:-4].contiguous().to(DEV), im[2:-6, 7:-1].contiguous().to(DEV)
+    fo = torch.empty(H, W, 2, dtype=torch.float32, device=DEV)
+    ms = timed(lambda: ops.farneback(da, db, out=fo), steps)
+    clip = torch.stack([torch.roll(da, (i, 2 * i), dims=(0, 1)) for i in range(14)])
+    cflows = torch.empty(13, H, W, 2, dtype=torch.float32, device=DEV)
+    ms_clip = timed(lambda: ops.farneback_clip(clip, out=cflows), 3)
+    sec["farneback_1080p"] = {"ms_per_pair": ms, "pairs_per_s": 1e3 / ms, "clip14_ms_per_pair": ms_clip / 13,
+                              "algorithmic_bytes": int(FARNEBACK_BYTES_1080P), "gbs": FARNEBACK_BYTES_1080P / (ms * 1e-3) / 1e9,
+                              "frac": FARNEBACK_BYTES_1080P / (ms * 1e-3) / 1e9 / hbm, "bound": "hbm"}
+    del da, db, fo, clip, cflows
+    torch.cuda.empty_cache()
+    # the streaming attention cores at the L0 bench shape (N = 258 048 tokens, C = 320, 5 heads)
+    C, heads, S, Tn, Bc = 320, 5, 9216, 14, 2
+    N, nseq = Bc * Tn * S, Bc * S
+    g = torch.Generator().manual_seed(4)
+    qkv = torch.randn(N, 3 * C, generator=g).to(torch.bfloat16).to(DEV)
+    q, k, v = qkv[:, :C], qkv[:, C:2 * C], qkv[:, 2 * C:]
+    o = torch.empty(N, C, dtype=torch.bfloat16, device=DEV)
+    do = torch.randn(N, C, generator=g).to(torch.bfloat16).to(DEV)
+    scale = 0.125
+    ms = timed(lambda: ops.attn_temporal(q, k, v, nseq, heads, Tn, Tn, scale, out=o), steps)
+    sec["temporal_core_fwd_L0"] = _frac(4 * N * C * 2, ms, hbm)
+    dqkv = torch.empty_like(qkv)
+    ms = timed(lambda: ops.attn_temporal_bwd(q, k, v, do, nseq, heads, Tn, Tn, scale, dq=dqkv[:, :C], dk=dqkv[:, C:2 * C],
+                                             dv=dqkv[:, 2 * C:]), steps)
+    sec["temporal_core_bwd_L0"] = _frac(7 * N * C * 2, ms, hbm)
+    del dqkv
+    # few keys, L = 2: spatial cross-attention (one context group per frame)
+    L = 2
+    kv = torch.randn(Bc * Tn * L, 2 * C, generator=g).to(torch.bfloat16).to(DEV)
+    qc = qkv[:, :C].contiguous()
+    ms = timed(lambda: ops.attn_fewkeys(qc, kv[:, :C], kv[:, C:], N, S, heads, L, scale, out=o), steps)
+    sec["fewkeys_L2_fwd_L0"] = _frac(2 * N * C * 2, ms, hbm)
+    dq = torch.empty(N, C, dtype=torch.bfloat16, device=DEV)
+    dkv = torch.empty(Bc * Tn * L, 2 * C, dtype=torch.bfloat16, device=DEV)
+    ms = timed(lambda: ops.attn_fewkeys_bwd(qc, kv[:, :C], kv[:, C:], do, N, S, heads, L, scale, dq=dq, dk=dkv[:, :C], dv=dkv[:, C:]),
+               steps)
+    sec["fewkeys_L2_bwd_L0"] = _frac(3 * N * C * 2, ms, hbm)
+    del qkv, o, do, kv, qc, dq, dkv
+    torch.cuda.empty_cache()
+    return sec
+
+
+# Farneback at 1080p, (pyr_scale 0.5, 3 levels, winsize 15, 3 iterations, poly_n 5): algorithmic HBM bytes per pair of the
+# unfused pass structure: levels 1, 1/4, 1/16 of 2.07 Mpx ~ 2.72 Mpx-equivalents, per pixel and level:
+# blur + resize 2 frames (16 B), polynomial expansion 2 x (4 read + 20 written), per iteration matrix update
+# (5 R1 gathered + 20 + 8 read, 20 written), box sums (20 read, 20 written), solve (20 read, 8 written) -> ~ 740 B.
+FARNEBACK_BYTES_1080P = 2.72e6 * 740
+
+
+def _unet_step(steps=5):
+    """Whole TransformerSpatioTemporalModel.forward per UNet level, CFG 2, 1 clip: config 2 topology (T = 14, 16 instances per
+    UNet step: 5/5/5/1) and config 3 topology (T = 25, 23 instances incl. the ControlNet branch: 7/7/7/2)."""
+    out = {}
+    for name, T, inst in (("T14_unet16", 14, {"L0": 5, "L1": 5, "L2": 5, "mid": 1}),
+                          ("T25_unet16_controlnet7", 25, {"L0": 7, "L1": 7, "L2": 7, "mid": 2})):
+        per, tfl = {}, {}
+        with torch.no_grad():
+            for lv in inst:
+                m, x, e, ind = _st_model(lv, T, 2)
+                kw = dict(encoder_hidden_states=e, image_only_indicator=ind, return_dict=False)
+                per[lv] = timed(lambda: m(x, **kw), steps)
+                C, heads, h, w = bench.LEVELS[lv]
+                S, BF = h * w, 2 * T
+                N = BF * S
+                fl = (4.0 * BF * heads * S * S * 64 + 4.0 * 2 * S * heads * T * T * 64      # attention cores
+                      + 2.0 * N * C * C * (4 + 2 + 4 + 1) + 2 * 2.0 * N * C * C            # q/k/v/o projections, proj_in/out
+                      + 3 * (2.0 * N * C * 8 * C + 2.0 * N * 4 * C * C))                    # three GEGLU feed-forwards
+                tfl[lv] = fl / 1e12 / (per[lv] * 1e-3)
+                del m, x, e, ind
+                torch.cuda.empty_cache()
+        ms_step = sum(per[lv] * n for lv, n in inst.items())
+        out[name] = {"frames": T, "cfg_batch": 2, "instances": inst, "ms_per_module": per, "tflops_per_module": tfl,
+                     "ms_per_unet_step": ms_step, "clip_frames_per_s_per_step": T / (ms_step * 1e-3),
+                     "note": "transformer modules only; resnets / convs / VAE / scheduler are out of scope (SURVEY 8)"}
+    return out
+
+
+def _train_step(steps=3):
+    """Config 5 at one GPU: forward + backward through the L0 block pair, spatial block frozen (gradient flows through it),
+    temporal block trainable (src/train_decouples.py:707-720), per_gpu_batch_size 2, T = 14, no CFG, 576x1024."""
+    from timelapse_video_interpolation_b200 import blocks
+    from timelapse_video_interpolation_b200.modules import BasicTransformerBlock, TemporalBasicTransformerBlock
+    C, heads, h, w = bench.LEVELS["L0"]
+    S, T, B = h * w, 14, 2
+    g = torch.Generator().manual_seed(3)
+
+    def init(m, trainable):
+        with torch.no_grad():
+            for name, p in m.named_parameters():
+                if "norm" in name:
+                    p.fill_(1.0 if name.endswith("weight") else 0.0)
+                else:
+                    p.copy_((torch.rand(p.shape, generator=g) * 2 - 1) * (p.shape[-1] ** -0.5 if p.dim() > 1 else C ** -0.5))
+                p.requires_grad_(trainable)
+        return m.to(DEV, torch.bfloat16)
+
+    sb, tb = init(BasicTransformerBlock(C, heads, 1024), False), init(TemporalBasicTransformerBlock(C, C, heads, 1024), True)
+    blocks.install_blocks(sb)
+    blocks.install_blocks(tb)
+    x = torch.randn(B * T, S, C, generator=g).to(torch.bfloat16).to(DEV)
+    xg = x.clone().requires_grad_(True)
+    ctx_s = torch.randn(B * T, 2, 1024, generator=g).to(torch.bfloat16).to(DEV)
+    ctx_t = torch.randn(B * S, 1, 1024, generator=g).to(torch.bfloat16).to(DEV)
+    dy = (torch.randn(B * T, S, C, generator=g) / 8).to(torch.bfloat16).to(DEV)
+
+    def fwd_bwd():
+        for p in tb.parameters():
+            p.grad = None
+        xg.grad = None
+        tb(sb(xg, encoder_hidden_states=ctx_s), num_frames=T, encoder_hidden_states=ctx_t).backward(dy)
+
+    def fwd():
+        with torch.no_grad():
+            tb(sb(x, encoder_hidden_states=ctx_s), num_frames=T, encoder_hidden_states=ctx_t)
+
+    ms_f = timed(fwd, steps)
+    ms_fb = timed(fwd_bwd, steps)
+    kt = KernelTimes()
+    ops.EVENT_HOOK = kt.hook
+    fwd_bwd()
+    ops.EVENT_HOOK = None
+    ks = kt.summary(1)
+    return {"config": "train_fwd_bwd_L0_block_pair_576x1024", "clips_per_gpu": B, "frames": T, "cfg_batch": 1,
+            "trainable": "temporal block (spatial block frozen, gradient flows through it to the input)",
+            "trainable_params": sum(p.numel() for p in tb.parameters()), "ms_fwd": ms_f, "ms_fwd_bwd": ms_fb,
+            "clip_frames_per_s_fwd_bwd": B * T / (ms_fb * 1e-3),
+            "ms_spatial_attention_bwd": ks.get("attn_spatial_bwd", {}).get("ms_per_step"),
+            "ms_by_entry_point": {k: round(v["ms_per_step"], 4) for k, v in ks.items()}}
+
+
+def driver_extras(dev, pk):
+    """The extra keys of bench.py's JSON line (VERDICT r1 task 4): every config the driver cannot otherwise see."""
+    global DEV
+    DEV = dev
+    out = {"secondary": _secondary(pk)}
+    torch.cuda.empty_cache()
+    out["unet_step"] = _unet_step()
+    torch.cuda.empty_cache()
+    out["train_step"] = _train_step()
+    torch.cuda.empty_cache()
+    return out
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--only", default="slerp,flow,train,train_block,loop25,kernels,block,model,levels,farneback")
