@@ -277,13 +277,25 @@ attn_spatial_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
     struct QkDesc {
       uint64_t a[4], b[4];
     };
+    // Shared-memory descriptors differ only in their 14-bit start-address field (every operand sits below 256 KB and is
+    // 16-byte aligned, so adding byte_offset >> 4 to the low word never carries out of it): one add per descriptor
+    // instead of re-encoding it - the issuing warps share their sub-partitions' issue slots with four softmax warps.
+    const uint32_t hi_desc = (1024u >> 4) | (1u << 14) | (kUmmaLayoutSw128 << 29);  // SBO 1024 B, version 1, 128-byte swizzle
+    const uint32_t lo_q0 = (((sQ + (uint32_t)(t * 2) * kP2QBytes) >> 4) & 0x3FFFu) | ((16u >> 4) << 16);   // K-major: LBO 16
+    const uint32_t lo_k0 = ((sKV >> 4) & 0x3FFFu) | ((16u >> 4) << 16);
+    const uint32_t lo_v0 = (((sKV + kP2KBytes) >> 4) & 0x3FFFu) | ((1024u >> 4) << 16);                    // MN-major: LBO 1024
+    auto desc64 = [&](uint32_t lo) {
+      uint64_t d;
+      asm("mov.b64 %0, {%1,%2};" : "=l"(d) : "r"(lo), "r"(hi_desc));
+      return d;
+    };
     auto make_qk = [&](const Cursor& c, QkDesc& d) {
-      const uint32_t q_addr = sQ + (uint32_t)(t * 2 + (c.item & 1)) * kP2QBytes;
-      const uint32_t k_addr = sKV + (uint32_t)c.s * kP2StageBytes;
+      const uint32_t lo_q = lo_q0 + (uint32_t)(c.item & 1) * (kP2QBytes >> 4);
+      const uint32_t lo_k = lo_k0 + (uint32_t)c.s * (kP2StageBytes >> 4);
 #pragma unroll
       for (int kk = 0; kk < 4; ++kk) {
-        d.a[kk] = umma_smem_desc(q_addr + kk * 32, 16, 1024, kUmmaLayoutSw128);
-        d.b[kk] = umma_smem_desc(k_addr + kk * 32, 16, 1024, kUmmaLayoutSw128);
+        d.a[kk] = desc64(lo_q + kk * 2);   // 32 bytes (16 bf16 of the reduction) per MMA
+        d.b[kk] = desc64(lo_k + kk * 2);
       }
     };
     auto issue_qk = [&](const QkDesc& d, int g) {
@@ -305,12 +317,12 @@ attn_spatial_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
     if (total > 2) wait_inputs(cq);
     for (int g = 0; g < total; ++g) {
       // everything the two products of this iteration need, before the wait
-      const uint32_t v_addr = sKV + (uint32_t)cp.s * kP2StageBytes + kP2KBytes;
+      const uint32_t lo_v = lo_v0 + (uint32_t)cp.s * (kP2StageBytes >> 4);
       const uint32_t pcol = tile + kP2ColS + (uint32_t)(g & 1) * 64;
       uint64_t vd[4];
 #pragma unroll
       for (int kk = 0; kk < 4; ++kk)  // 16 keys per MMA = two 8-row groups of 128-byte rows (SBO = 1024 B); one 64-wide N atom
-        vd[kk] = umma_smem_desc(v_addr + kk * 2048, 1024, 1024, kUmmaLayoutSw128);
+        vd[kk] = desc64(lo_v + kk * (2048 >> 4));
       const uint32_t acc0 = cp.j != 0 ? 1u : 0u;
       const bool last_of_item = cp.j == p.n_kv - 1;
       uint64_t* bar_kv_empty = &bars.kv_empty[cp.s];
@@ -361,21 +373,24 @@ attn_spatial_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
     const uint64_t sl2x2 = f32x2_pack(sl2, sl2);
     const bool last_ragged = (p.Skv & (kP2BN - 1)) != 0;
     uint32_t ra[32];  // this thread's 32 scores of the current step
-    int g = 0;        // global step of this CTA (S buffer = g & 1, barrier phases follow g)
+    // global step g of this CTA: S buffer = g & 1, barrier phase = (g >> 1) & 1, kept as two toggled registers
+    uint32_t buf = 0, ph = 0;
+#ifdef TVI_TC_TIMELINE
+    int g = 0;
+#endif
 
     for (int i = 0; i < n_my; ++i) {
       float m_ref = -INFINITY;      // reference maximum of this half-row, raw (unscaled) logit units
       float l = 0.f;                // running sum of exp2((s - m_ref) * sl2) over this half's key columns
       // first scores of the item (QK_0 of this item ran under the previous item's epilogue)
-      TVI_WAIT(&bar_s[g & 1], (uint32_t)(g >> 1) & 1u, 5, i);
+      TVI_WAIT(&bar_s[buf], ph, 5, i);
       tc_fence_after();
-      tmem_ld_x32(tS + (g & 1) * 64, ra);
+      tmem_ld_x32(tS + buf * 64, ra);
 
       // One key step.  kRagged: last step of an item that runs past Skv.  kFirst: first step of an item (no
       // reference yet: the exact pass is taken unconditionally).
       auto step = [&](int j, auto ragged_tag) {
         constexpr bool kRagged = decltype(ragged_tag)::value;
-        const int buf = g & 1;
         tmem_ld_wait();
         P2_TL(0);
         uint32_t pk[16];
@@ -462,7 +477,7 @@ attn_spatial_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
             if (__any_sync(0xffffffffu, need)) {
               // rescale this half's accumulator: the PV products of step g-1 must have landed; those of step g are
               // not issued before this warp arrives on bar_p below
-              TVI_WAIT(bar_o, (uint32_t)(g - 1) & 1u, 6, j);
+              TVI_WAIT(bar_o, buf ^ 1u, 6, j);  // one completion per step: parity of step g-1
               tc_fence_after();
 #pragma unroll 1
               for (int c0 = 0; c0 < 64; c0 += 8) {  // small chunks: the 32 scores stay in registers for the second pass
@@ -484,7 +499,7 @@ attn_spatial_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
         P2_TL(2);
         // the next step's scores (other S buffer, normally long finished) travel to registers while the P store drains
         if (j + 1 < p.n_kv) {
-          TVI_WAIT(&bar_s[buf ^ 1], (uint32_t)((g + 1) >> 1) & 1u, 7, j);
+          TVI_WAIT(&bar_s[buf ^ 1], ph ^ buf, 7, j);  // phase of step g+1 (flips when the buffer index wraps)
           tc_fence_after();
           tmem_ld_x32(tS + (buf ^ 1) * 64, ra);
         }
@@ -494,7 +509,11 @@ attn_spatial_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
         P2_TL(4);
         __syncwarp();
         if (lane == 0) mbar_arrive(&bar_p[buf]);
+        ph ^= buf;
+        buf ^= 1u;
+#ifdef TVI_TC_TIMELINE
         ++g;
+#endif
       };
       for (int j = 0; j < p.n_kv - 1; ++j) step(j, P2Tag<false>{});
       if (last_ragged) step(p.n_kv - 1, P2Tag<true>{});
@@ -600,11 +619,13 @@ int launch_spatial_tc(const tvi_bf16* q, const tvi_bf16* k, const tvi_bf16* v, t
   int slot;
   switch (poly) {
     case 0: kern = attn_spatial_tc_kernel<0x0000u>; slot = 0; break;
+    case 2: kern = attn_spatial_tc_kernel<0x0101u>; slot = 4; break;
+    case 3: kern = attn_spatial_tc_kernel<0x0421u>; slot = 5; break;
     case 5: kern = attn_spatial_tc_kernel<0x1249u>; slot = 2; break;
     case 6: kern = attn_spatial_tc_kernel<0x2525u>; slot = 3; break;
     default: kern = attn_spatial_tc_kernel<0x1111u>; slot = 1; break;
   }
-  static bool configured[64][4] = {};
+  static bool configured[64][6] = {};
   int dev = 0;
   TVI_CUDA_OK(cudaGetDevice(&dev));
   if (dev < 0 || dev >= 64 || !configured[dev][slot]) {
