@@ -282,6 +282,12 @@ int tvi_attn_spatial_bwd(const tvi_bf16* q, const tvi_bf16* k, const tvi_bf16* v
                          const float* lse, tvi_bf16* dq, tvi_bf16* dk, tvi_bf16* dv, void* workspace, int batch, int heads,
                          int S, int Skv, int d, int64_t ldq, int64_t ldk, int64_t ldv, int64_t ldo, int64_t lddo,
                          int64_t lddq, int64_t lddk, int64_t lddv, float scale, void* stream);
+/* Same with an explicit kernel choice (TVI_SPATIAL_AUTO / _MMA_SYNC / _TCGEN05, as for the forward): AUTO takes the
+ * tcgen05 / TMEM / TMA passes for S, Skv >= 1024 and the mma.sync passes below. */
+int tvi_attn_spatial_bwd_algo(const tvi_bf16* q, const tvi_bf16* k, const tvi_bf16* v, const tvi_bf16* o, const tvi_bf16* dout,
+                              const float* lse, tvi_bf16* dq, tvi_bf16* dk, tvi_bf16* dv, void* workspace, int batch, int heads,
+                              int S, int Skv, int d, int64_t ldq, int64_t ldk, int64_t ldv, int64_t ldo, int64_t lddo,
+                              int64_t lddq, int64_t lddk, int64_t lddv, float scale, int algo, void* stream);
 int tvi_attn_temporal_bwd(const tvi_bf16* q, const tvi_bf16* k, const tvi_bf16* v, const tvi_bf16* dout, tvi_bf16* dq,
                           tvi_bf16* dk, tvi_bf16* dv, int64_t nseq, int heads, int Tq, int Tk, int d, int64_t ldq,
                           int64_t ldk, int64_t ldv, int64_t lddo, int64_t lddq, int64_t lddk, int64_t lddv, float scale,

@@ -144,9 +144,14 @@ def test_temporal_bwd_matches_autograd(cuda, nseq, heads, Tq, Tk):
     _grad_close(dv, rv, "temporal dv")
 
 
+@pytest.mark.parametrize("algo", ["mma_sync", "tcgen05"])
 @pytest.mark.parametrize("batch,heads,S,Skv", [(2, 5, 144, 144), (2, 5, 576, 576), (1, 2, 1000, 1000), (2, 1, 300, 200),
-                                               (1, 3, 130, 65), (1, 5, 2304, 2304)])
-def test_spatial_bwd_matches_autograd(cuda, batch, heads, S, Skv):
+                                               (1, 3, 130, 65), (1, 5, 2304, 2304), (3, 2, 1111, 1111), (1, 1, 128, 256)])
+def test_spatial_bwd_matches_autograd(cuda, batch, heads, S, Skv, algo):
+    """Both implementations at every shape (AUTO picks tcgen05 from 1024 tokens): the tcgen05 / TMEM / TMA passes must also
+    be right on ragged tiles (row / column counts that are not multiples of 128) and when S != Skv."""
+    from timelapse_video_interpolation_b200 import _lib
+    algo_id = {"mma_sync": _lib.SPATIAL_MMA_SYNC, "tcgen05": _lib.SPATIAL_TCGEN05}[algo]
     g = torch.Generator().manual_seed(S + Skv)
     C = heads * 64
     q, k, v = _packed_qkv(batch * S, batch * Skv, C, g, cuda)
@@ -154,15 +159,35 @@ def test_spatial_bwd_matches_autograd(cuda, batch, heads, S, Skv):
     scale = 0.125
     lse = torch.empty(batch * S, heads, dtype=torch.float32, device=cuda)
     o = ops.attn_spatial(q, k, v, batch, heads, S, Skv, scale, lse=lse)
-    dq, dk, dv = ops.attn_spatial_bwd(q, k, v, o, dout, lse, batch, heads, S, Skv, scale)
-    dq2, dk2, dv2 = ops.attn_spatial_bwd(q, k, v, o, dout, lse, batch, heads, S, Skv, scale)
+    dq, dk, dv = ops.attn_spatial_bwd(q, k, v, o, dout, lse, batch, heads, S, Skv, scale, algo=algo_id)
+    dq2, dk2, dv2 = ops.attn_spatial_bwd(q, k, v, o, dout, lse, batch, heads, S, Skv, scale, algo=algo_id)
     torch.cuda.synchronize()
     assert torch.equal(dq, dq2) and torch.equal(dk, dk2) and torch.equal(dv, dv2)  # no atomics: repeatable
     ro, rq, rk, rv = _ref_attention_grads(q, k, v, dout, batch, heads, S, Skv, scale)
     _grad_close(o, ro, "spatial o")
-    _grad_close(dq, rq, "spatial dq")
-    _grad_close(dk, rk, "spatial dk")
-    _grad_close(dv, rv, "spatial dv")
+    _grad_close(dq, rq, f"spatial dq ({algo})")
+    _grad_close(dk, rk, f"spatial dk ({algo})")
+    _grad_close(dv, rv, f"spatial dv ({algo})")
+
+
+def test_spatial_bwd_tcgen05_in_place_packed_gradients(cuda):
+    """dq | dk | dv written as the three column slices of one packed [tokens, 3C] buffer (how autograd._AttentionFn
+    calls it), at a shape AUTO sends to the tcgen05 passes."""
+    batch, heads, S = 2, 5, 1152
+    C = heads * 64
+    g = torch.Generator().manual_seed(77)
+    q, k, v = _packed_qkv(batch * S, batch * S, C, g, cuda)
+    dout = torch.randn(batch * S, C, generator=g).to(torch.bfloat16).to(cuda)
+    lse = torch.empty(batch * S, heads, dtype=torch.float32, device=cuda)
+    o = ops.attn_spatial(q, k, v, batch, heads, S, S, 0.125, lse=lse)
+    dqkv = torch.zeros(batch * S, 3 * C, dtype=torch.bfloat16, device=cuda)
+    dq, dk, dv = ops.attn_spatial_bwd(q, k, v, o, dout, lse, batch, heads, S, S, 0.125, dq=dqkv[:, :C], dk=dqkv[:, C:2 * C],
+                                      dv=dqkv[:, 2 * C:])
+    torch.cuda.synchronize()
+    _, rq, rk, rv = _ref_attention_grads(q, k, v, dout, batch, heads, S, S, 0.125)
+    _grad_close(dq, rq, "packed dq")
+    _grad_close(dk, rk, "packed dk")
+    _grad_close(dv, rv, "packed dv")
 
 
 @pytest.mark.parametrize("ngroups,rpg,heads,L,use_bias", [(50, 14, 5, 2, False), (50, 14, 5, 2, True), (3, 9216, 5, 2, False),

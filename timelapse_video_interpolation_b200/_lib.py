@@ -71,6 +71,7 @@ SIGNATURES = {
                                          _i64, _i64, _i64, _i64, _f32, _i32, _ptr]),
     "tvi_attn_spatial_bwd_workspace_bytes": (_sz, [_i32, _i32, _i32]),
     "tvi_attn_spatial_bwd": (_i32, [_ptr] * 10 + [_i32] * 5 + [_i64] * 8 + [_f32, _ptr]),
+    "tvi_attn_spatial_bwd_algo": (_i32, [_ptr] * 10 + [_i32] * 5 + [_i64] * 8 + [_f32, _i32, _ptr]),
     "tvi_attn_temporal_bwd": (_i32, [_ptr] * 7 + [_i64, _i32, _i32, _i32, _i32] + [_i64] * 7 + [_f32, _ptr]),
     "tvi_attn_fewkeys_bwd_workspace_bytes": (_sz, [_i64, _i64, _i32, _i32, _i32]),
     "tvi_attn_fewkeys_bwd": (_i32, [_ptr] * 8 + [_i64, _i64, _i32, _i32, _i32] + [_i64] * 7 + [_f32, _i32, _ptr, _ptr]),

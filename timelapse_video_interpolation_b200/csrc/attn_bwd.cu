@@ -774,17 +774,26 @@ int launch_fewkeys_bwd(const FkParams& p, int64_t ngroups, int C8, cudaStream_t 
 }  // namespace
 }  // namespace tvi
 
+namespace tvi {
+size_t spatial_bwd_tc_workspace_bytes(int batch, int heads, int S);
+int launch_spatial_bwd_tc(const tvi_bf16* q, const tvi_bf16* k, const tvi_bf16* v, const tvi_bf16* o, const tvi_bf16* dout, const float* lse,
+                          tvi_bf16* dq, tvi_bf16* dk, tvi_bf16* dv, void* workspace, int batch, int heads, int S, int Skv, int64_t ldq,
+                          int64_t ldk, int64_t ldv, int64_t ldo, int64_t lddo, int64_t lddq, int64_t lddk, int64_t lddv, float scale,
+                          cudaStream_t st);
+}  // namespace tvi
+
 extern "C" {
 
 size_t tvi_attn_spatial_bwd_workspace_bytes(int batch, int heads, int S) {
   if (batch <= 0 || heads <= 0 || S <= 0) return 0;
-  return (size_t)batch * S * heads * sizeof(float);
+  // the tcgen05 passes keep lse2 and -D as [batch*heads][S padded to 128] planes; the mma.sync passes need D only
+  return tvi::spatial_bwd_tc_workspace_bytes(batch, heads, S);
 }
 
-int tvi_attn_spatial_bwd(const tvi_bf16* q, const tvi_bf16* k, const tvi_bf16* v, const tvi_bf16* o, const tvi_bf16* dout,
-                         const float* lse, tvi_bf16* dq, tvi_bf16* dk, tvi_bf16* dv, void* workspace, int batch, int heads,
-                         int S, int Skv, int d, int64_t ldq, int64_t ldk, int64_t ldv, int64_t ldo, int64_t lddo,
-                         int64_t lddq, int64_t lddk, int64_t lddv, float scale, void* stream) {
+int tvi_attn_spatial_bwd_algo(const tvi_bf16* q, const tvi_bf16* k, const tvi_bf16* v, const tvi_bf16* o, const tvi_bf16* dout,
+                              const float* lse, tvi_bf16* dq, tvi_bf16* dk, tvi_bf16* dv, void* workspace, int batch, int heads,
+                              int S, int Skv, int d, int64_t ldq, int64_t ldk, int64_t ldv, int64_t ldo, int64_t lddo,
+                              int64_t lddq, int64_t lddk, int64_t lddv, float scale, int algo, void* stream) {
   using namespace tvi;
   TVI_CHECK_ARG(batch >= 0 && heads >= 0 && S >= 0 && Skv >= 0, "tvi_attn_spatial_bwd: negative size");
   if (batch == 0 || heads == 0 || S == 0) return TVI_OK;
@@ -798,7 +807,16 @@ int tvi_attn_spatial_bwd(const tvi_bf16* q, const tvi_bf16* k, const tvi_bf16* v
   TVI_CHECK_ARG(((uintptr_t)q | (uintptr_t)k | (uintptr_t)v | (uintptr_t)o | (uintptr_t)dout | (uintptr_t)dq | (uintptr_t)dk |
                  (uintptr_t)dv) % 16 == 0, "tvi_attn_spatial_bwd: pointers must be 16-byte aligned");
   TVI_CHECK_ARG((int64_t)batch * heads <= 65535, "tvi_attn_spatial_bwd: batch*heads exceeds 65535");
+  TVI_CHECK_ARG(algo >= TVI_SPATIAL_AUTO && algo <= TVI_SPATIAL_TCGEN05, "tvi_attn_spatial_bwd_algo: unknown algo %d", algo);
   cudaStream_t st = (cudaStream_t)stream;
+  if (algo == TVI_SPATIAL_AUTO) {
+    // a CTA of the tcgen05 passes owns 128 rows and streams the other side in steps of 128; short sequences (L2 / mid
+    // level: 576, 144 tokens) stay on the mma.sync passes, like the forward
+    algo = (S >= 1024 && Skv >= 1024) ? TVI_SPATIAL_TCGEN05 : TVI_SPATIAL_MMA_SYNC;
+  }
+  if (algo == TVI_SPATIAL_TCGEN05)
+    return launch_spatial_bwd_tc(q, k, v, o, dout, lse, dq, dk, dv, workspace, batch, heads, S, Skv, ldq, ldk, ldv, ldo, lddo, lddq, lddk,
+                                 lddv, scale, st);
   float* D = (float*)workspace;
   {
     const int64_t nrows = (int64_t)batch * S;
@@ -824,6 +842,14 @@ int tvi_attn_spatial_bwd(const tvi_bf16* q, const tvi_bf16* k, const tvi_bf16* v
   p.out1 = dq; p.ldo1 = lddq; p.out2 = nullptr; p.ldo2 = 0;
   p.nrows = S; p.ncols = Skv;
   return launch_flash_bwd<false>(p, batch, st);
+}
+
+int tvi_attn_spatial_bwd(const tvi_bf16* q, const tvi_bf16* k, const tvi_bf16* v, const tvi_bf16* o, const tvi_bf16* dout,
+                         const float* lse, tvi_bf16* dq, tvi_bf16* dk, tvi_bf16* dv, void* workspace, int batch, int heads,
+                         int S, int Skv, int d, int64_t ldq, int64_t ldk, int64_t ldv, int64_t ldo, int64_t lddo,
+                         int64_t lddq, int64_t lddk, int64_t lddv, float scale, void* stream) {
+  return tvi_attn_spatial_bwd_algo(q, k, v, o, dout, lse, dq, dk, dv, workspace, batch, heads, S, Skv, d, ldq, ldk, ldv, ldo, lddo, lddq,
+                                   lddk, lddv, scale, TVI_SPATIAL_AUTO, stream);
 }
 
 int tvi_attn_temporal_bwd(const tvi_bf16* q, const tvi_bf16* k, const tvi_bf16* v, const tvi_bf16* dout, tvi_bf16* dq,

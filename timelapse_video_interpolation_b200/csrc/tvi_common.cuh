@@ -171,6 +171,12 @@ __device__ __forceinline__ void tma_load_3d(void* smem, const CUtensorMap* m, ui
       "l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2)
       : "memory");
 }
+// 1-D bulk copy global -> shared (16-byte aligned, size a multiple of 16), completion on an mbarrier
+__device__ __forceinline__ void tma_load_1d(void* smem, const void* gmem, uint32_t bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(smem)),
+               "l"(reinterpret_cast<uint64_t>(gmem)), "r"(bytes), "r"(smem_u32(bar))
+               : "memory");
+}
 __device__ __forceinline__ void tma_store_2d(const CUtensorMap* m, const void* smem, int c0, int c1) {
   asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];" ::"l"(
                    reinterpret_cast<uint64_t>(m)),
@@ -394,6 +400,40 @@ __device__ __forceinline__ float fmax3(float a, float b, float c) {
   float d;
   asm("max.f32 %0, %1, %2, %3;" : "=f"(d) : "f"(a), "f"(b), "f"(c));
   return d;
+}
+
+// every lane polls, the loop condition is a vote: warp-uniform, so loop state stays in uniform registers
+__device__ __forceinline__ void mbar_wait_uniform(uint64_t* bar, uint32_t parity) {
+#ifdef TVI_DEBUG_WAIT
+  for (long long it = 0; it < 4000000LL; ++it)
+    if (__any_sync(0xffffffffu, mbar_try_wait(bar, parity))) return;
+  if ((threadIdx.x & 31) == 0 && atomicAdd(&g_dbg_prints, 1u) < 200u)
+    printf("MMA WAIT TIMEOUT block %d warp %d bar +%d parity %u\n", blockIdx.x, threadIdx.x >> 5, (int)(smem_u32(bar) & 0xfff), parity);
+#else
+  while (!__any_sync(0xffffffffu, mbar_try_wait(bar, parity))) {
+  }
+#endif
+}
+
+// 2^x for a pair of fp32 values on the FMA pipe instead of the 16-per-clock MUFU unit: n = round(x) through the
+// 1.5*2^23 magic constant, f = x - n in [-0.5, 0.5], cubic minimax polynomial for 2^f (relative error 7.6e-5, far
+// below the bf16 rounding of P), n added into the exponent field.  x is clamped at -125.
+__device__ __forceinline__ uint64_t exp2_poly_x2(uint64_t x) {
+  float x0, x1;
+  f32x2_unpack(x, x0, x1);
+  const uint64_t xc = f32x2_pack(fmaxf(x0, -125.f), fmaxf(x1, -125.f));
+  const uint64_t t = f32x2_add(xc, f32x2_pack(12582912.f, 12582912.f));
+  const uint64_t n = f32x2_add(t, f32x2_pack(-12582912.f, -12582912.f));
+  const uint64_t f = f32x2_fma(n, f32x2_pack(-1.f, -1.f), xc);
+  uint64_t pl = f32x2_fma(f32x2_pack(0.05520550534f, 0.05520550534f), f, f32x2_pack(0.24261397123f, 0.24261397123f));
+  pl = f32x2_fma(pl, f, f32x2_pack(0.69325476885f, 0.69325476885f));
+  pl = f32x2_fma(pl, f, f32x2_pack(0.99992769957f, 0.99992769957f));
+  float t0, t1, p0, p1;
+  f32x2_unpack(t, t0, t1);
+  f32x2_unpack(pl, p0, p1);
+  const float r0 = __int_as_float((__float_as_int(t0) << 23) + __float_as_int(p0));
+  const float r1 = __int_as_float((__float_as_int(t1) << 23) + __float_as_int(p1));
+  return f32x2_pack(r0, r1);
 }
 
 __device__ __forceinline__ void cp_async_16(void* smem, const void* gmem, bool pred) {

@@ -424,9 +424,11 @@ def _grad_like(t, rows, width):
     return torch.empty(rows, width, dtype=torch.bfloat16, device=t.device)
 
 
-def attn_spatial_bwd(q, k, v, o, dout, lse, batch: int, heads: int, S: int, Skv: int, scale: float, dq=None, dk=None, dv=None):
+def attn_spatial_bwd(q, k, v, o, dout, lse, batch: int, heads: int, S: int, Skv: int, scale: float, dq=None, dk=None, dv=None,
+                     algo: int = _lib.SPATIAL_AUTO):
     """Gradients of the flash spatial core; q/k/v/o/dout are [rows, heads*64] row views, lse the forward's
-    [batch*S, heads] fp32 log-sum-exp.  Returns (dq, dk, dv)."""
+    [batch*S, heads] fp32 log-sum-exp.  Returns (dq, dk, dv).  `algo` as for the forward (AUTO: tcgen05 passes for
+    S, Skv >= 1024, mma.sync passes below)."""
     _need_cuda(q, k, v, o, dout, lse)
     q, ldq = _rows2d(q, "q")
     k, ldk = _rows2d(k, "k")
@@ -445,9 +447,9 @@ def attn_spatial_bwd(q, k, v, o, dout, lse, batch: int, heads: int, S: int, Skv:
         raise _lib.TviError(_lib.TVI_ERR_INVALID, "lse must be a contiguous fp32 [batch*S, heads] tensor")
     lib = _lib.load()
     ws = _workspace(lib.tvi_attn_spatial_bwd_workspace_bytes(batch, heads, S), q.device)
-    _hooked("attn_spatial_bwd", 3, lib.tvi_attn_spatial_bwd, q.data_ptr(), k.data_ptr(), v.data_ptr(), o.data_ptr(),
+    _hooked("attn_spatial_bwd", 3, lib.tvi_attn_spatial_bwd_algo, q.data_ptr(), k.data_ptr(), v.data_ptr(), o.data_ptr(),
             dout.data_ptr(), lse.data_ptr(), dq.data_ptr(), dk.data_ptr(), dv.data_ptr(), ws.data_ptr(), batch, heads, S, Skv,
-            d, ldq, ldk, ldv, ldo, lddo, lddq, lddk, lddv, float(scale), _stream())
+            d, ldq, ldk, ldv, ldo, lddo, lddq, lddk, lddv, float(scale), int(algo), _stream())
     return dq, dk, dv
 
 
