@@ -13,20 +13,26 @@
 //     dS' = P' o (dP' - D[query])                -> bf16 over the first half of the dP' buffer      (Y warps)
 //     accP += P'  C2   (M=128 N=64 K=128, TS, C2 MN-major)      pass 1 only: dV
 //     accD += dS' C1   (M=128 N=64 K=128, TS, C1 MN-major)      pass 1: dK   pass 2: dQ          (scale in the epilogue)
-// 384 threads, warp-specialised: warp 0 TMA producer (resident R tiles, a 4-stage ring of C tiles and, in pass 1, the
+// 640 threads, warp-specialised: warp 0 TMA producer (resident R tiles, a 4-stage ring of C tiles and, in pass 1, the
 // per-query lse2 / -D vectors of the step), warp 1 MMA issuer (warp-uniform loop), warp 2 owns the tensor memory,
-// warps 4..7 "X" (one thread per row: the exponentials; the 16-per-clock MUFU unit is this role's resource, 1 of 4
-// score pairs takes the FMA-pipe polynomial), warps 8..11 "Y" (one thread per row: dS on the FMA / ALU pipes).  X and Y
-// share each sub-partition, so the exponentials of step i+1 overlap the dS arithmetic of step i; S' is double-buffered
-// so that the tensor pipe computes S'_{i+2} / dP'_{i+1} under them.
-// TMEM columns: S'[0] [0,128)  S'[1] [128,256)  dP' [256,384)  accP [384,448)  accD [448,512).
+// warps 4..11 "X" (two threads per row, 64 of the step's 128 columns each: the exponentials; the 16-per-clock MUFU unit is
+// this role's resource, 1 of 4 score pairs takes the FMA-pipe polynomial), warps 12..19 "Y" (two threads per row: dS on the
+// FMA / ALU pipes).  Every sub-partition holds two X and two Y warps: a single warp per role could not issue its ~480
+// dependent instructions per step faster than one per 4 cycles (2150 cycles per step against 1024 of tensor work), and
+// the exponentials of step i+1 overlap the dS arithmetic of step i.  A thread's P' / dS' go over the first 32 columns of
+// its OWN 64 score columns (behind its read front), so the bf16 A operands sit at columns [0,32) and [64,96) of a buffer.
+// Tensor memory: three rotating 128-column buffers B0 B1 B2 at [0,384), accP [384,448), accD [448,512).  Step i keeps S'_i
+// (then P'_i) in B[2i mod 3] and dP'_i (then dS'_i) in B[(2i+1) mod 3]; the third buffer already holds S'_{i+1}.  dP'_{i+1}
+// goes into the buffer of P'_i as soon as the Y warps have copied P'_i into registers (p_read) and accP_i is issued, i.e.
+// while dS'_i is still being computed, and S'_{i+2} into the buffer of dS'_i after accD_i: no product waits on the step
+// before it, the X warps run one step ahead of the Y warps, and Y_{i+1} starts as soon as Y_i ends.
 // Nothing of size S x Skv reaches memory.  7 GEMM units of 2 B h S Skv 64 FLOPs per launch pair (S' and dP' twice).
 #include "tvi_common.cuh"
 
 namespace tvi {
 namespace {
 
-constexpr int kBtThreads = 384;
+constexpr int kBtThreads = 640;
 constexpr int kBtRows = 128;      // rows per CTA (UMMA M)
 constexpr int kBtCols = 128;      // streamed columns per step (UMMA N of S' / dP', K of the accumulating products)
 constexpr int kBtStages = 4;
@@ -35,7 +41,7 @@ constexpr int kBtVec = kBtCols * 4;                    // one fp32 vector of the
 constexpr int kBtStageBytes = 2 * kBtTile + 2 * kBtVec;  // C1 | C2 | lse2 | -D
 constexpr int kBtSmem = 1024 + 2 * kBtTile + kBtStages * kBtStageBytes;
 
-constexpr uint32_t kBtColS = 0, kBtColDp = 256, kBtColAccP = 384, kBtColAccD = 448;
+constexpr uint32_t kBtColAccP = 384, kBtColAccD = 448;  // rotating buffers: column 128 * k
 
 struct BtParams {
   int nrows, ncols;     // per sequence: pass 1 (Skv, S), pass 2 (S, Skv)
@@ -54,10 +60,14 @@ struct BtBarriers {
   uint64_t r_full;
   uint64_t c_full[kBtStages];
   uint64_t c_empty[kBtStages];
-  uint64_t s_full[2];    // S' of a step is in tensor memory            (one completion per two steps and buffer)
+  // by step parity (one completion per two steps): a parity wait is only sound for a waiter at most one phase behind,
+  // and the X warps run a step ahead of the Y warps
+  uint64_t s_full[2];    // S' of a step is in tensor memory
   uint64_t p_full[2];    // P' of a step is stored (4 X warps)
-  uint64_t dp_full;      // dP' of a step is in tensor memory           (one completion per step)
-  uint64_t ds_full;      // dS' of a step is stored, P' has been read   (4 Y warps; the issuing warp is the only waiter)
+  uint64_t dp_full[2];   // dP' of a step is in tensor memory
+  // one completion per step; the issuing warp, which takes them in program order, is the only waiter
+  uint64_t p_read;       // the Y warps hold P' of a step in registers: its buffer may take dP' of the next step
+  uint64_t ds_full;      // dS' of a step is stored (4 Y warps)
   uint64_t acc_done;
 };
 
@@ -92,10 +102,11 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmR1, const __grid_consta
     }
     for (int i = 0; i < 2; ++i) {
       mbar_init(&bars.s_full[i], 1);
-      mbar_init(&bars.p_full[i], 4);
+      mbar_init(&bars.p_full[i], 8);
+      mbar_init(&bars.dp_full[i], 1);
     }
-    mbar_init(&bars.dp_full, 1);
-    mbar_init(&bars.ds_full, 4);
+    mbar_init(&bars.p_read, 8);
+    mbar_init(&bars.ds_full, 8);
     mbar_init(&bars.acc_done, 1);
     mbar_fence_init();
   }
@@ -149,68 +160,75 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmR1, const __grid_consta
     const uint32_t lo_c0_k = ((sStage >> 4) & 0x3FFFu) | (1u << 16);    // C tiles as K-major B operand (LBO 16)
     const uint32_t lo_c0_mn = ((sStage >> 4) & 0x3FFFu) | (64u << 16);  // C tiles as MN-major B operand (LBO 1024)
     constexpr uint32_t kStage16 = kBtStageBytes >> 4, kTile16 = kBtTile >> 4;
-    auto issue_s = [&](int st, int buf) {       // S' = R1 C1^T
+    auto issue_s = [&](int st, uint32_t col, int par) {       // S' = R1 C1^T
 #pragma unroll
       for (int kk = 0; kk < 4; ++kk)
-        umma_bf16_ss_pred(kBtColS + (uint32_t)buf * 128, desc64(lo_r1 + kk * 2), desc64(lo_c0_k + (uint32_t)st * kStage16 + kk * 2), idesc_ss,
-                          kk != 0 ? 1u : 0u, leader);
-      umma_commit_pred(&bars.s_full[buf], leader);
+        umma_bf16_ss_pred(col, desc64(lo_r1 + kk * 2), desc64(lo_c0_k + (uint32_t)st * kStage16 + kk * 2), idesc_ss, kk != 0 ? 1u : 0u,
+                          leader);
+      umma_commit_pred(&bars.s_full[par], leader);
     };
-    auto issue_dp = [&](int st) {               // dP' = R2 C2^T
+    auto issue_dp = [&](int st, uint32_t col, int par) {      // dP' = R2 C2^T
 #pragma unroll
       for (int kk = 0; kk < 4; ++kk)
-        umma_bf16_ss_pred(kBtColDp, desc64(lo_r2 + kk * 2), desc64(lo_c0_k + (uint32_t)st * kStage16 + kTile16 + kk * 2), idesc_ss,
+        umma_bf16_ss_pred(col, desc64(lo_r2 + kk * 2), desc64(lo_c0_k + (uint32_t)st * kStage16 + kTile16 + kk * 2), idesc_ss,
                           kk != 0 ? 1u : 0u, leader);
-      umma_commit_pred(&bars.dp_full, leader);
+      umma_commit_pred(&bars.dp_full[par], leader);
     };
     const int n = p.n_steps;
     mbar_wait_uniform(&bars.r_full, 0);
     mbar_wait_uniform(&bars.c_full[0], 0);
     tc_fence_after();
-    issue_s(0, 0);
-    issue_dp(0);
+    issue_s(0, 0, 0);        // S'_0 -> B0
+    issue_dp(0, 128, 0);     // dP'_0 -> B1
     if (n > 1) {
       mbar_wait_uniform(&bars.c_full[1], 0);
       tc_fence_after();
-      issue_s(1, 1);
+      issue_s(1, 256, 1);    // S'_1 -> B2
     }
-    int st = 0;           // ring stage of step i
+    int st = 0;              // ring stage of step i
+    uint32_t cs = 0;         // column of the buffer of S'_i / P'_i; dP'_i / dS'_i sit in the next buffer (mod 3)
     for (int i = 0; i < n; ++i) {
-      const int buf = i & 1;
+      const int par = i & 1;
+      const uint32_t cd = cs == 256 ? 0u : cs + 128;
       const uint32_t acc = i != 0 ? 1u : 0u;
       const uint32_t lo_mn = lo_c0_mn + (uint32_t)st * kStage16;
+      const int st1 = (st + 1) & (kBtStages - 1);
       if (kKeysOnRows) {
         // accP += P'_i C2_i
-        mbar_wait_uniform(&bars.p_full[buf], (uint32_t)(i >> 1) & 1u);
+        mbar_wait_uniform(&bars.p_full[par], (uint32_t)(i >> 1) & 1u);
         tc_fence_after();
 #pragma unroll
         for (int kk = 0; kk < 8; ++kk)
-          umma_bf16_ts_pred(kBtColAccP, kBtColS + (uint32_t)buf * 128 + kk * 8, desc64(lo_mn + kTile16 + kk * 128), idesc_ts,
+          umma_bf16_ts_pred(kBtColAccP, cs + (kk >> 2) * 64 + (kk & 3) * 8, desc64(lo_mn + kTile16 + kk * 128), idesc_ts,
                             kk != 0 ? 1u : acc, leader);
       }
+      // dP'_{i+1} into the buffer of P'_i: the Y warps have it in registers, accP_i (just issued) reads it first (in order)
+      mbar_wait_uniform(&bars.p_read, (uint32_t)i & 1u);
+      tc_fence_after();
+      if (i + 1 < n) issue_dp(st1, cs, par ^ 1);
       // accD += dS'_i C1_i
       mbar_wait_uniform(&bars.ds_full, (uint32_t)i & 1u);
       tc_fence_after();
 #pragma unroll
       for (int kk = 0; kk < 8; ++kk)
-        umma_bf16_ts_pred(kBtColAccD, kBtColDp + kk * 8, desc64(lo_mn + kk * 128), idesc_ts, kk != 0 ? 1u : acc, leader);
+        umma_bf16_ts_pred(kBtColAccD, cd + (kk >> 2) * 64 + (kk & 3) * 8, desc64(lo_mn + kk * 128), idesc_ts, kk != 0 ? 1u : acc, leader);
       umma_commit_pred(&bars.c_empty[st], leader);  // the stage's tiles have been read once these products complete
-      const int st1 = (st + 1) & (kBtStages - 1);
-      if (i + 1 < n) issue_dp(st1);                 // dP' buffer: dS'_i is consumed by the products just issued (in order)
       if (i + 2 < n) {
         const int st2 = (st + 2) & (kBtStages - 1);
         mbar_wait_uniform(&bars.c_full[st2], (uint32_t)((i + 2) / kBtStages) & 1u);
         tc_fence_after();
-        issue_s(st2, buf);                          // S'[buf]: P'_i was read by accP_i and by the Y warps (ds_full)
+        issue_s(st2, cd, par);                      // S'_{i+2} into the buffer of dS'_i (read by accD_i, in order)
       }
       st = st1;
+      cs = cd == 256 ? 0u : cd + 128;               // S'_{i+1} sits two buffers on
     }
     umma_commit_pred(&bars.acc_done, leader);
     __syncwarp();
   } else if (warp >= 4) {
     // ===================== X (exponentials) / Y (dS) warps, then the epilogue =====================
-    const bool is_x = warp < 8;
+    const bool is_x = warp < 12;
     const int quad = warp & 3;  // the TMEM lane quadrant a warp may touch is fixed by its index
+    const int ch = ((warp - 4) >> 2) & 1;  // which 64 of the step's 128 columns
     const uint32_t lane_base = (uint32_t)(quad * 32) << 16;
     const uint32_t tm = tmem_base + lane_base;
     const int rr = quad * 32 + lane;
@@ -224,17 +242,18 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmR1, const __grid_consta
       row_negd = p.negd[(int64_t)bh * p.q_pad + row];
     }
     int st = 0;
+    uint32_t cs = 0;  // column of the buffer of S'_i / P'_i
     if (is_x) {
       for (int i = 0; i < p.n_steps; ++i) {
-        const int buf = i & 1;
+        const int par = i & 1;
         const float* vec = reinterpret_cast<const float*>(base_ptr + 2 * kBtTile + st * kBtStageBytes + 2 * kBtTile);  // lse2 of the columns
         // the lse2 vector of the step arrived with the stage's tiles (observe that barrier itself before reading it)
         if (kKeysOnRows) TVI_WAIT(&bars.c_full[st], (uint32_t)(i / kBtStages) & 1u, 6, i);
-        TVI_WAIT(&bars.s_full[buf], (uint32_t)(i >> 1) & 1u, 2, i);
+        TVI_WAIT(&bars.s_full[par], (uint32_t)(i >> 1) & 1u, 2, i);
         tc_fence_after();
-        const uint32_t tS = tm + kBtColS + (uint32_t)buf * 128;
-#pragma unroll 1
-        for (int c = 0; c < 4; ++c) {
+        const uint32_t tS = tm + cs + ch * 64;
+#pragma unroll
+        for (int c = 0; c < 2; ++c) {
           uint32_t ra[32];
           tmem_ld_x32(tS + c * 32, ra);
           tmem_ld_wait();
@@ -243,7 +262,7 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmR1, const __grid_consta
           for (int k = 0; k < 32; k += 4) {
             float n0, n1, n2, n3;
             if (kKeysOnRows) {
-              const float4 l4 = *reinterpret_cast<const float4*>(vec + c * 32 + k);  // same address in every lane: broadcast
+              const float4 l4 = *reinterpret_cast<const float4*>(vec + ch * 64 + c * 32 + k);  // same address in every lane: broadcast
               n0 = -l4.x, n1 = -l4.y, n2 = -l4.z, n3 = -l4.w;
             } else {
               n0 = n1 = n2 = n3 = -row_lse2;
@@ -270,29 +289,36 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmR1, const __grid_consta
             pk[k >> 1] = pack_bf16x2(a0, a1);
             pk[(k >> 1) + 1] = pack_bf16x2(b0, b1);
           }
-          // P' chunk c (32 bf16 = 16 columns) over columns [16c, 16c+16) of the S' buffer: behind this thread's read front
+          // P' chunk c (32 bf16 = 16 columns) over columns [16c, 16c+16) of this thread's own 64 score columns: behind its read front
           tmem_st_x16(tS + c * 16, pk);
         }
         tmem_st_wait();
         tc_fence_before();
         __syncwarp();
-        if (lane == 0) mbar_arrive(&bars.p_full[buf]);
+        if (lane == 0) mbar_arrive(&bars.p_full[par]);
         if (++st == kBtStages) st = 0;
+        cs = cs >= 128 ? cs - 128 : 256;  // + 2 buffers (mod 3)
       }
     } else {
       for (int i = 0; i < p.n_steps; ++i) {
-        const int buf = i & 1;
+        const int par = i & 1;
         const float* vec = reinterpret_cast<const float*>(base_ptr + 2 * kBtTile + st * kBtStageBytes + 2 * kBtTile + kBtVec);  // -D of the columns
         if (kKeysOnRows) TVI_WAIT(&bars.c_full[st], (uint32_t)(i / kBtStages) & 1u, 7, i);
-        TVI_WAIT(&bars.p_full[buf], (uint32_t)(i >> 1) & 1u, 3, i);
-        TVI_WAIT(&bars.dp_full, (uint32_t)i & 1u, 4, i);
+        TVI_WAIT(&bars.p_full[par], (uint32_t)(i >> 1) & 1u, 3, i);
         tc_fence_after();
-        const uint32_t tP = tm + kBtColS + (uint32_t)buf * 128;
-        const uint32_t tD = tm + kBtColDp;
-#pragma unroll 1
-        for (int c = 0; c < 4; ++c) {
-          uint32_t pp[16], dp[32];
-          tmem_ld_x16(tP + c * 16, pp);
+        // this thread's P'_i (64 bf16 = 32 columns) into registers at once, so that the buffer can take dP' of the next step
+        uint32_t pp[32];
+        tmem_ld_x32(tm + cs + ch * 64, pp);
+        tmem_ld_wait();
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&bars.p_read);
+        TVI_WAIT(&bars.dp_full[par], (uint32_t)(i >> 1) & 1u, 4, i);
+        tc_fence_after();
+        const uint32_t tD = tm + (cs == 256 ? 0u : cs + 128) + ch * 64;
+#pragma unroll
+        for (int c = 0; c < 2; ++c) {
+          uint32_t dp[32];
           tmem_ld_x32(tD + c * 32, dp);
           tmem_ld_wait();
           uint32_t dk[16];
@@ -300,12 +326,12 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmR1, const __grid_consta
           for (int k = 0; k < 32; k += 4) {
             float n0, n1, n2, n3;
             if (kKeysOnRows) {
-              const float4 d4 = *reinterpret_cast<const float4*>(vec + c * 32 + k);
+              const float4 d4 = *reinterpret_cast<const float4*>(vec + ch * 64 + c * 32 + k);
               n0 = d4.x, n1 = d4.y, n2 = d4.z, n3 = d4.w;
             } else {
               n0 = n1 = n2 = n3 = row_negd;
             }
-            const uint32_t w0 = pp[k >> 1], w1 = pp[(k >> 1) + 1];
+            const uint32_t w0 = pp[c * 16 + (k >> 1)], w1 = pp[c * 16 + (k >> 1) + 1];
             const uint64_t p01 = f32x2_pack(__uint_as_float(w0 << 16), __uint_as_float(w0 & 0xffff0000u));
             const uint64_t p23 = f32x2_pack(__uint_as_float(w1 << 16), __uint_as_float(w1 & 0xffff0000u));
             const uint64_t t01 = f32x2_add(f32x2_pack(__uint_as_float(dp[k]), __uint_as_float(dp[k + 1])), f32x2_pack(n0, n1));
@@ -316,54 +342,39 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmR1, const __grid_consta
             dk[k >> 1] = pack_bf16x2(a0, a1);
             dk[(k >> 1) + 1] = pack_bf16x2(b0, b1);
           }
-          tmem_st_x16(tD + c * 16, dk);  // dS' chunk c over columns [16c, 16c+16) of the dP' buffer
+          tmem_st_x16(tD + c * 16, dk);  // dS' chunk c over columns [16c, 16c+16) of this thread's own 64 dP' columns
         }
         tmem_st_wait();
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive(&bars.ds_full);
         if (++st == kBtStages) st = 0;
+        cs = cs >= 128 ? cs - 128 : 256;  // + 2 buffers (mod 3)
       }
     }
     // ---- epilogue: accumulators -> bf16 -> global (one full 128-byte row segment per thread) ----
     TVI_WAIT(&bars.acc_done, 0, 5, 0);
     tc_fence_after();
-    if (kKeysOnRows) {
-      // X warps store accP (dV), Y warps accD (dK, times scale)
-      const uint32_t tA = tm + (is_x ? kBtColAccP : kBtColAccD);
-      tvi_bf16* out = is_x ? p.outP : p.outD;
-      const int64_t ld = is_x ? p.ldoP : p.ldoD;
-      const float f = is_x ? 1.f : p.scale;
-      uint4* dst = reinterpret_cast<uint4*>(out + ((int64_t)b * p.nrows + row) * ld + h * 64);
-#pragma unroll
-      for (int c = 0; c < 2; ++c) {
+    // one role (X: accP = dV in pass 1; Y: accD = dK resp. dQ, times scale) per accumulator, 32 of its 64 columns per warp
+    {
+      const bool mine = kKeysOnRows || !is_x;   // pass 2 has only accD: the Y warps store it
+      const uint32_t tA = tm + ((kKeysOnRows && is_x) ? kBtColAccP : kBtColAccD) + ch * 32;
+      tvi_bf16* out = (kKeysOnRows && is_x) ? p.outP : p.outD;
+      const int64_t ld = (kKeysOnRows && is_x) ? p.ldoP : p.ldoD;
+      const float f = (kKeysOnRows && is_x) ? 1.f : p.scale;
+      if (mine) {
+        uint4* dst = reinterpret_cast<uint4*>(out + ((int64_t)b * p.nrows + row) * ld + h * 64 + ch * 32);
         uint32_t a[32];
-        tmem_ld_x32(tA + c * 32, a);
+        tmem_ld_x32(tA, a);
         tmem_ld_wait();
         if (row < p.nrows) {
 #pragma unroll
           for (int k = 0; k < 32; k += 8)
-            dst[c * 4 + (k >> 3)] = make_uint4(pack_bf16x2(__uint_as_float(a[k]) * f, __uint_as_float(a[k + 1]) * f),
-                                                pack_bf16x2(__uint_as_float(a[k + 2]) * f, __uint_as_float(a[k + 3]) * f),
-                                                pack_bf16x2(__uint_as_float(a[k + 4]) * f, __uint_as_float(a[k + 5]) * f),
-                                                pack_bf16x2(__uint_as_float(a[k + 6]) * f, __uint_as_float(a[k + 7]) * f));
+            dst[k >> 3] = make_uint4(pack_bf16x2(__uint_as_float(a[k]) * f, __uint_as_float(a[k + 1]) * f),
+                                     pack_bf16x2(__uint_as_float(a[k + 2]) * f, __uint_as_float(a[k + 3]) * f),
+                                     pack_bf16x2(__uint_as_float(a[k + 4]) * f, __uint_as_float(a[k + 5]) * f),
+                                     pack_bf16x2(__uint_as_float(a[k + 6]) * f, __uint_as_float(a[k + 7]) * f));
         }
-      }
-    } else {
-      // accD (dQ, times scale): X warps columns [0, 32), Y warps [32, 64)
-      const int c = is_x ? 0 : 1;
-      uint4* dst = reinterpret_cast<uint4*>(p.outD + ((int64_t)b * p.nrows + row) * p.ldoD + h * 64);
-      uint32_t a[32];
-      tmem_ld_x32(tm + kBtColAccD + c * 32, a);
-      tmem_ld_wait();
-      const float f = p.scale;
-      if (row < p.nrows) {
-#pragma unroll
-        for (int k = 0; k < 32; k += 8)
-          dst[c * 4 + (k >> 3)] = make_uint4(pack_bf16x2(__uint_as_float(a[k]) * f, __uint_as_float(a[k + 1]) * f),
-                                              pack_bf16x2(__uint_as_float(a[k + 2]) * f, __uint_as_float(a[k + 3]) * f),
-                                              pack_bf16x2(__uint_as_float(a[k + 4]) * f, __uint_as_float(a[k + 5]) * f),
-                                              pack_bf16x2(__uint_as_float(a[k + 6]) * f, __uint_as_float(a[k + 7]) * f));
       }
     }
   }
