@@ -29,6 +29,10 @@
 // Nothing of size S x Skv reaches memory.  7 GEMM units of 2 B h S Skv 64 FLOPs per launch pair (S' and dP' twice).
 #include "tvi_common.cuh"
 
+#ifndef TVI_BWD_POLY
+#define TVI_BWD_POLY 0x00u
+#endif
+
 namespace tvi {
 namespace {
 
@@ -458,7 +462,7 @@ int launch_spatial_bwd_tc(const tvi_bf16* q, const tvi_bf16* k, const tvi_bf16* 
   if ((rc = make(&tmK, k, Skv, ldk))) return rc;
   if ((rc = make(&tmV, v, Skv, ldv))) return rc;
   if ((rc = make(&tmDo, dout, S, lddo))) return rc;
-  constexpr uint32_t kPoly = 0x11u;  // 2 of every 8 score pairs on the FMA-pipe polynomial
+  constexpr uint32_t kPoly = TVI_BWD_POLY;  // score pairs (of every 8) on the FMA-pipe polynomial
   static bool configured[64] = {};
   int dev = 0;
   TVI_CUDA_OK(cudaGetDevice(&dev));
