@@ -598,18 +598,30 @@ __global__ void __launch_bounds__(256) attn_fewkeys_bwd_kernel(const FkParams p)
     for (int j = 0; j < 8; ++j) dk[l][j] = dv[l][j] = 0.f;
   }
 
-  for (int it = 0; it < kFewBwdRowsPerThread; ++it) {
+  // the Q / dO chunks of kUnroll rows are requested before the first of them is used (memory-level parallelism: the
+  // arithmetic of a row is a dependent chain of ~150 instructions)
+  constexpr int kUnroll = 2;
+  static_assert(kFewBwdRowsPerThread % kUnroll == 0, "row loop is unrolled in groups");
+  for (int it0 = 0; it0 < kFewBwdRowsPerThread; it0 += kUnroll) {
+    if (rlo + (int64_t)it0 * RY >= rhi) break;  // block-uniform
+    uint4 qv[kUnroll], gv[kUnroll];
+#pragma unroll
+    for (int u = 0; u < kUnroll; ++u) {
+      const int64_t rr = rlo + (int64_t)(it0 + u) * RY + ry;
+      const int64_t r = rr < rhi ? rr : rlo;
+      qv[u] = p.q != nullptr ? __ldg(reinterpret_cast<const uint4*>(p.q + r * p.ldq + cx * 8)) : make_uint4(0, 0, 0, 0);
+      gv[u] = __ldg(reinterpret_cast<const uint4*>(p.dout + r * p.lddo + cx * 8));
+    }
+#pragma unroll
+    for (int u = 0; u < kUnroll; ++u) {
+    const int it = it0 + u;
     if (rlo + (int64_t)it * RY >= rhi) break;  // block-uniform
     const int64_t rr = rlo + (int64_t)it * RY + ry;
     const bool act = rr < rhi;
     const int64_t r = act ? rr : rlo;
     float qf[8], gof[8];
-    if (p.q != nullptr) unpack8b(__ldg(reinterpret_cast<const uint4*>(p.q + r * p.ldq + cx * 8)), qf);
-    else {
-#pragma unroll
-      for (int j = 0; j < 8; ++j) qf[j] = 0.f;
-    }
-    unpack8b(__ldg(reinterpret_cast<const uint4*>(p.dout + r * p.lddo + cx * 8)), gof);
+    unpack8b(qv[u], qf);
+    unpack8b(gv[u], gof);
     float logit[LT], dpv[LT];
 #pragma unroll
     for (int l = 0; l < LT; ++l) {
@@ -672,6 +684,7 @@ __global__ void __launch_bounds__(256) attn_fewkeys_bwd_kernel(const FkParams p)
       o.z = pack_bf16x2(dqf[4], dqf[5]);
       o.w = pack_bf16x2(dqf[6], dqf[7]);
       *reinterpret_cast<uint4*>(p.dq + r * p.lddq + cx * 8) = o;
+    }
     }
   }
 

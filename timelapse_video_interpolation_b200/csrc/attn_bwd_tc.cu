@@ -30,7 +30,7 @@
 #include "tvi_common.cuh"
 
 #ifndef TVI_BWD_POLY
-#define TVI_BWD_POLY 0x00u
+#define TVI_BWD_POLY 0x11u
 #endif
 
 namespace tvi {

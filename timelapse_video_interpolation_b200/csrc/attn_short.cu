@@ -287,14 +287,27 @@ attn_fewkeys_kernel(const tvi_bf16* __restrict__ q, const tvi_bf16* __restrict__
 
   // A warp can straddle two rows (blockDim.x = 40 at C = 320), so the trip count is made
   // block-uniform and rows past the tile are predicated: every lane reaches every shuffle.
-#pragma unroll 2
-  for (int it = 0; it < kFewRowsPerThread; ++it) {
+  // The Q chunks of kFewUnroll rows are requested before the first of them is used: a streaming kernel with ~80
+  // instructions per 32 bytes needs the loads of several rows in flight per thread to cover the HBM latency.
+  constexpr int kFewUnroll = 4;
+  static_assert(kFewRowsPerThread % kFewUnroll == 0, "row loop is unrolled in groups");
+  for (int it0 = 0; it0 < kFewRowsPerThread; it0 += kFewUnroll) {
+    if (rlo + (int64_t)it0 * RY >= rhi) break;
+    uint4 qv[kFewUnroll];
+#pragma unroll
+    for (int u = 0; u < kFewUnroll; ++u) {
+      const int64_t rr = rlo + (int64_t)(it0 + u) * RY + ry;
+      qv[u] = __ldg(reinterpret_cast<const uint4*>(q + (rr < rhi ? rr : rlo) * ldq + cx * 8));
+    }
+#pragma unroll
+    for (int u = 0; u < kFewUnroll; ++u) {
+    const int it = it0 + u;
     if (rlo + (int64_t)it * RY >= rhi) break;
     const int64_t rr = rlo + (int64_t)it * RY + ry;
     const bool act = rr < rhi;
     const int64_t r = act ? rr : rlo;
     float qf[8];
-    unpack8(__ldg(reinterpret_cast<const uint4*>(q + r * ldq + cx * 8)), qf);
+    unpack8(qv[u], qf);
     float logit[LT];
 #pragma unroll
     for (int l = 0; l < LT; ++l) {
@@ -350,6 +363,7 @@ attn_fewkeys_kernel(const tvi_bf16* __restrict__ q, const tvi_bf16* __restrict__
     outv.z = pack_bf16x2(of[4], of[5]);
     outv.w = pack_bf16x2(of[6], of[7]);
     if (act) *reinterpret_cast<uint4*>(o + r * ldo + cx * 8) = outv;
+    }
   }
 
   if (STATS) {
