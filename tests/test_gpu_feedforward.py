@@ -126,7 +126,7 @@ def test_basic_transformer_block_matches_oracle(cuda, BF, S, C, heads, L):
         y = blk(x, encoder_hidden_states=e)
     torch.cuda.synchronize()
     ref = blocks_ref.basic_transformer_block_ref(blk, x, e)
-    assert_block_close(f"basic block S={S} C={C}", y, ref)
+    assert_block_close(f"basic block S={S} C={C}", y, ref, stores=3)
     assert blocks.uninstall_blocks(blk) == 1
 
 
@@ -142,7 +142,7 @@ def test_temporal_basic_transformer_block_matches_oracle(cuda, B, T, S, C, heads
     torch.cuda.synchronize()
     ref = blocks_ref.temporal_basic_transformer_block_ref(blk, x, T, e)
     assert y.shape == x.shape
-    assert_block_close(f"temporal block T={T} C={C}", y, ref)
+    assert_block_close(f"temporal block T={T} C={C}", y, ref, stores=4)
 
 
 def test_temporal_block_layout_fold_is_bit_exact(cuda):

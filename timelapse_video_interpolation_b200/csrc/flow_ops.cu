@@ -113,16 +113,10 @@ int cosine_blocks(int64_t npix) {
 // ---------------------------------------------------------------------------------------------
 // backward warp + consistency
 // ---------------------------------------------------------------------------------------------
-// Everything about a sample point that does not depend on the plane, computed ONCE per pixel and reused by the two flow
-// planes and the image channels: the four tap offsets (clamped into the plane, so a tap can always be fetched), the four
-// grid_sample weights and which taps fall outside the image (their value is 0 - padding_mode='zeros' - whatever the
-// clamped fetch returned, NaN included).  Round 1 redid the address arithmetic, the tap predicates and the weight
-// products for every plane: ~300 SASS instructions per pixel, issue-bound at half the HBM rate.
 struct Tap {
-  int i00, i01, i10, i11;      // offsets inside a plane
-  float w00, w01, w10, w11;    // nw = (1-wx)(1-wy), ne = wx(1-wy), sw = (1-wx)wy, se = wx wy
-  uint32_t in;                 // bit k: tap k is inside the image
-  bool valid;
+  int x0, y0;      // top-left integer tap
+  float wx, wy;    // fractional weights (exact: f - floor(f))
+  bool in00, in01, in10, in11, valid;
 };
 
 __device__ __forceinline__ Tap make_tap(int x, int y, float fx, float fy, int W, int H) {
@@ -130,36 +124,34 @@ __device__ __forceinline__ Tap make_tap(int x, int y, float fx, float fy, int W,
   // p + f with p integer: floor(p + f) = p + floor(f) and frac(p + f) = f - floor(f), both exact
   // in fp32, so the bilinear weights carry no coordinate rounding at all.
   const float flx = floorf(fx), fly = floorf(fy);
-  const float wx = fx - flx, wy = fy - fly;
+  t.wx = fx - flx;
+  t.wy = fy - fly;
   // clamp the integer part far outside the image so the int conversion cannot overflow
   const float cx = fminf(fmaxf(flx, -1.0e6f), 1.0e6f), cy = fminf(fmaxf(fly, -1.0e6f), 1.0e6f);
-  const int x0 = x + (int)cx, y0 = y + (int)cy;
-  const bool xin0 = x0 >= 0 && x0 < W, xin1 = x0 + 1 >= 0 && x0 + 1 < W;
-  const bool yin0 = y0 >= 0 && y0 < H, yin1 = y0 + 1 >= 0 && y0 + 1 < H;
-  t.in = (xin0 && yin0 ? 1u : 0u) | (xin1 && yin0 ? 2u : 0u) | (xin0 && yin1 ? 4u : 0u) | (xin1 && yin1 ? 8u : 0u);
-  const int xa = min(max(x0, 0), W - 1), xb = min(max(x0 + 1, 0), W - 1);
-  const int ya = min(max(y0, 0), H - 1) * W, yb = min(max(y0 + 1, 0), H - 1) * W;
-  t.i00 = ya + xa;
-  t.i01 = ya + xb;
-  t.i10 = yb + xa;
-  t.i11 = yb + xb;
-  const float ux = 1.0f - wx, uy = 1.0f - wy;
-  t.w00 = ux * uy;
-  t.w01 = wx * uy;
-  t.w10 = ux * wy;
-  t.w11 = wx * wy;
+  t.x0 = x + (int)cx;
+  t.y0 = y + (int)cy;
+  const bool xin0 = t.x0 >= 0 && t.x0 < W, xin1 = t.x0 + 1 >= 0 && t.x0 + 1 < W;
+  const bool yin0 = t.y0 >= 0 && t.y0 < H, yin1 = t.y0 + 1 >= 0 && t.y0 + 1 < H;
+  t.in00 = xin0 && yin0;
+  t.in01 = xin1 && yin0;
+  t.in10 = xin0 && yin1;
+  t.in11 = xin1 && yin1;
   // sample point inside [0, W-1] x [0, H-1] (closed); NaN flows are invalid
-  const bool vx = (x0 >= 0) && (x0 < W - 1 || (x0 == W - 1 && wx == 0.0f));
-  const bool vy = (y0 >= 0) && (y0 < H - 1 || (y0 == H - 1 && wy == 0.0f));
+  const bool vx = (t.x0 >= 0) && (t.x0 < W - 1 || (t.x0 == W - 1 && t.wx == 0.0f));
+  const bool vy = (t.y0 >= 0) && (t.y0 < H - 1 || (t.y0 == H - 1 && t.wy == 0.0f));
   t.valid = vx && vy && (fx == fx) && (fy == fy);
   return t;
 }
 
-__device__ __forceinline__ float bilerp(const float* __restrict__ plane, const Tap& t) {
-  const float l00 = __ldg(plane + t.i00), l01 = __ldg(plane + t.i01), l10 = __ldg(plane + t.i10), l11 = __ldg(plane + t.i11);
-  const float v00 = (t.in & 1u) ? l00 : 0.0f, v01 = (t.in & 2u) ? l01 : 0.0f;
-  const float v10 = (t.in & 4u) ? l10 : 0.0f, v11 = (t.in & 8u) ? l11 : 0.0f;
-  return v00 * t.w00 + v01 * t.w01 + v10 * t.w10 + v11 * t.w11;
+__device__ __forceinline__ float bilerp(const float* __restrict__ plane, const Tap& t, int W) {
+  const int64_t base = (int64_t)t.y0 * W + t.x0;
+  const float v00 = t.in00 ? __ldg(plane + base) : 0.0f;
+  const float v01 = t.in01 ? __ldg(plane + base + 1) : 0.0f;
+  const float v10 = t.in10 ? __ldg(plane + base + W) : 0.0f;
+  const float v11 = t.in11 ? __ldg(plane + base + W + 1) : 0.0f;
+  // grid_sample's weights: nw = (1-wx)(1-wy), ne = wx(1-wy), sw = (1-wx)wy, se = wx wy
+  const float ux = 1.0f - t.wx, uy = 1.0f - t.wy;
+  return v00 * (ux * uy) + v01 * (t.wx * uy) + v10 * (ux * t.wy) + v11 * (t.wx * t.wy);
 }
 
 constexpr int kWarpThreads = 256;
@@ -169,8 +161,13 @@ constexpr int kWarpThreads = 256;
 // keep 20 * PX gather loads in flight.  Measured on 32 pairs of 1080p with smooth flows: 0.82 ms
 // (3.3 TB/s of algorithmic traffic) against 1.18 ms for the first version (4 adjacent pixels per thread, 128-bit flow loads), whose
 // warp-level gathers span four lines each.  ncu (profiles/r1_c): DRAM traffic = 1.0 x algorithmic, ~300
-// SASS instructions per pixel (address arithmetic and tap predicates): issue-bound, not HBM-bound; round 2 moved all the
-// per-plane redundancy into `Tap` (see above).
+// SASS instructions per pixel (address arithmetic and tap predicates): the kernel is issue-bound, not HBM-bound.
+// Round 2 tried to shrink the instruction stream and measured every variant against this one on the same box
+// (0.818 ms for 32 pairs of 1080p): tap offsets + weight products hoisted into the tap record with clamped
+// unconditional loads 2.10 ms (87 registers), the same with a 48- / 40-register cap 1.07 / 1.13 ms, predicated loads +
+// hoisted weights + float-reciprocal pixel decode (no emulated 64-bit division) 1.10 ms, only the division replaced
+// 1.18 ms (54 registers).  Fewer instructions made ptxas unroll the channel loop and hoist more gathers per thread; the
+// kernel's speed comes from many resident warps each with few gathers in flight, and this version is kept.
 template <int PX>
 __global__ void __launch_bounds__(kWarpThreads)
 backward_warp_kernel(const float* __restrict__ img2, const float* __restrict__ f_fwd, const float* __restrict__ f_bwd,
@@ -198,8 +195,8 @@ backward_warp_kernel(const float* __restrict__ img2, const float* __restrict__ f
     const int y = (int)(off / W);
     const int x = (int)(off - (int64_t)y * W);
     tap[i] = make_tap(x, y, fx[i], fy[i], W, H);
-    bx[i] = bilerp(fbw, tap[i]);
-    by[i] = bilerp(fbw + npix, tap[i]);
+    bx[i] = bilerp(fbw, tap[i], W);
+    by[i] = bilerp(fbw + npix, tap[i], W);
   }
 #pragma unroll
   for (int i = 0; i < PX; ++i) {
@@ -212,7 +209,7 @@ backward_warp_kernel(const float* __restrict__ img2, const float* __restrict__ f
     const float* plane = img2 + (b * C + c) * npix;
     float r[PX];
 #pragma unroll
-    for (int i = 0; i < PX; ++i) r[i] = bilerp(plane, tap[i]);
+    for (int i = 0; i < PX; ++i) r[i] = bilerp(plane, tap[i], W);
 #pragma unroll
     for (int i = 0; i < PX; ++i)
       if (in[i]) __stcs(warped + (b * C + c) * npix + off0 + (int64_t)i * kWarpThreads, r[i]);
@@ -264,7 +261,7 @@ int tvi_backward_warp_f32(const float* img2, const float* f_fwd, const float* f_
   cudaStream_t st = (cudaStream_t)stream;
   const int64_t npix = (int64_t)H * W;
   constexpr int kPx = 2;
-  TVI_CHECK_ARG(npix < ((int64_t)1 << 31), "tvi_backward_warp_f32: image too large (tap offsets are 32-bit)");
+  TVI_CHECK_ARG((npix + kWarpThreads * kPx - 1) / (kWarpThreads * kPx) < ((int64_t)1 << 31), "tvi_backward_warp_f32: image too large");
   dim3 grid((unsigned)((npix + kWarpThreads * kPx - 1) / (kWarpThreads * kPx)), (unsigned)B);
   backward_warp_kernel<kPx><<<grid, kWarpThreads, 0, st>>>(img2, f_fwd, f_bwd, warped, mask, C, H, W, alpha, beta);
   TVI_LAUNCH_OK("backward_warp_kernel");

@@ -1,3 +1,3 @@
-timeout 900 python -m pytest tests -m gpu -x -q > gpurun_out/r2e_pytest.log 2>&1; echo "pytest rc $?" >> gpurun_out/r2e_pytest.log
-timeout 300 python bench.py --steps 20 --warmup 5 > gpurun_out/r2e_bench.json 2> gpurun_out/r2e_bench.err; echo "bench rc $?"
-tail -5 gpurun_out/r2e_pytest.log; head -c 600 gpurun_out/r2e_bench.json
+timeout 900 python -m pytest tests -m gpu -x -q > gpurun_out/r2j_pytest.log 2>&1; echo "pytest rc $?" >> gpurun_out/r2j_pytest.log
+timeout 600 python bench.py --steps 20 --warmup 5 > gpurun_out/r2j_bench.json 2> gpurun_out/r2j_bench.err; echo "bench rc $?"
+tail -4 gpurun_out/r2j_pytest.log
