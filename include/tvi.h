@@ -239,6 +239,14 @@ int tvi_attn_fewkeys_fwd(const tvi_bf16* q, const tvi_bf16* k, const tvi_bf16* v
                          int64_t rows_per_group, int heads, int L, int d, int64_t ldq, int64_t ldk,
                          int64_t ldv, int64_t ldo, float scale, int Tq, const float* bias, float* stats,
                          void* stats_ws, void* stream);
+/* Same over INTERLEAVED groups: logical row i of group g = (b, s), s < group_inner, is physical row
+ * (b * rows_per_group + i) * group_inner + s of q / o — the temporal block's cross-attention (rows_per_group = T frames,
+ * group_inner = H*W) read straight from the [B*T, S, C] token order, without the permute copies of
+ * src/models/attention.py:436-438 / :474-476.  bias / stats index the logical row (i % Tq).  group_inner == 1 is the call above. */
+int tvi_attn_fewkeys_fwd_interleaved(const tvi_bf16* q, const tvi_bf16* k, const tvi_bf16* v, tvi_bf16* o, int64_t nrows,
+                                     int64_t rows_per_group, int heads, int L, int d, int64_t group_inner, int64_t ldq,
+                                     int64_t ldk, int64_t ldv, int64_t ldo, float scale, int Tq, const float* bias,
+                                     float* stats, void* stats_ws, void* stream);
 
 /* ---------------------------------------------------------------------------------------------
  * A3a  spatial self-attention core (flash-style, tcgen05 QK^T and PV, online fp32 softmax):

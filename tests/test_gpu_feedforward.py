@@ -6,7 +6,7 @@ import torch
 
 import timelapse_video_interpolation_b200 as tvi
 from oracle import feedforward_ref
-from timelapse_video_interpolation_b200 import ops
+from timelapse_video_interpolation_b200 import _lib, ops
 from timelapse_video_interpolation_b200.modules import FeedForward
 
 pytestmark = pytest.mark.gpu
@@ -159,6 +159,44 @@ def test_temporal_block_layout_fold_is_bit_exact(cuda):
         y_perm = blk(x, num_frames=T, encoder_hidden_states=e, fold_layout=False)
     assert ops.LAUNCHES > launches0
     assert torch.equal(y_fold, y_perm)
+
+
+@pytest.mark.parametrize("L,ramp", [(2, False), (2, True), (1, True), (5, False)])
+def test_temporal_block_layout_fold_with_several_keys_bias_and_statistics(cuda, L, ramp):
+    # the patched temporal attn2 of src/train_decouples.py:377-495 (two key frames, ramp bias :437-457, logit statistics
+    # :460-471) runs in the spatial token order too: `tvi_attn_fewkeys_fwd_interleaved`
+    from timelapse_video_interpolation_b200 import TviAttnProcessor
+    B, T, S, C = 2, 14, 40, 320
+    blk = _init(TemporalBasicTransformerBlock(C, C, 5, 1024), 16, cuda)
+    got = []
+    if ramp:
+        blk.attn2.processor = TviAttnProcessor(ramp_bias=(L == 2), stats_sink=lambda st, a: got.append(st.clone()))
+    blocks.install_blocks(blk)
+    g = torch.Generator().manual_seed(L)
+    x = torch.randn(B * T, S, C, generator=g).to(torch.bfloat16).to(cuda)
+    e = torch.randn(B * S, L, 1024, generator=g).to(torch.bfloat16).to(cuda)
+    with torch.no_grad():
+        y_fold = blk(x, num_frames=T, encoder_hidden_states=e)
+        y_perm = blk(x, num_frames=T, encoder_hidden_states=e, fold_layout=False)
+    assert torch.equal(y_fold, y_perm)
+    if ramp:
+        assert len(got) == 2 and got[0].shape == (T, L)
+        assert float((got[0] - got[1]).abs().max()) <= 1e-4 * max(1.0, float(got[1].abs().max()))  # atomics: order differs
+
+
+def test_fewkeys_interleaved_groups(cuda):
+    g = torch.Generator().manual_seed(12)
+    B, T, S, heads, L = 3, 7, 11, 5, 2
+    C = heads * 64
+    q = torch.randn(B, T, S, C, generator=g).to(torch.bfloat16).to(cuda)            # spatial token order
+    k = torch.randn(B * S * L, C, generator=g).to(torch.bfloat16).to(cuda)
+    v = torch.randn(B * S * L, C, generator=g).to(torch.bfloat16).to(cuda)
+    o_int = ops.attn_fewkeys(q.view(-1, C), k, v, B * T * S, T, heads, L, 0.125, group_inner=S)
+    q_perm = q.permute(0, 2, 1, 3).contiguous()                                   # [B, S, T, C]
+    o_ref = ops.attn_fewkeys(q_perm.view(-1, C), k, v, B * T * S, T, heads, L, 0.125)
+    assert torch.equal(o_int.view(B, T, S, C), o_ref.view(B, S, T, C).permute(0, 2, 1, 3))
+    with pytest.raises(_lib.TviError):
+        ops.attn_fewkeys(q.view(-1, C), k, v, B * T * S, T, heads, L, 0.125, group_inner=S + 1)
 
 
 def test_bcast_rows_add_group_inner(cuda):

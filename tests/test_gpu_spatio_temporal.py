@@ -121,16 +121,84 @@ def test_model_forward_matches_reference_golden(cuda, golden_dir):
     assert_block_close("vs reference golden", y, ref, factor=2.0, stores=9)
 
 
-def test_model_forward_refuses_gradients_and_cpu(cuda):
+def test_model_forward_refuses_cpu_tensors(cuda):
     m = _model(320, 5, 1024, 3, cuda)
     spatio_temporal.install_spatio_temporal(m)
     x = torch.randn(2, 320, 8, 8, device=cuda).to(torch.bfloat16)
     e = torch.randn(2, 1, 1024, device=cuda).to(torch.bfloat16)
     ind = torch.zeros(1, 2, device=cuda)
-    with pytest.raises(NotImplementedError):
-        m(x.requires_grad_(True), encoder_hidden_states=e, image_only_indicator=ind)
     with torch.no_grad(), pytest.raises(_lib.TviError):
         m(x.detach().cpu(), encoder_hidden_states=e, image_only_indicator=ind)
+
+
+def _model_ref(P, x, e, ind, heads, T):
+    """fp32 autograd restatement of the forward (:253-360) over a dict of leaf parameters (gradients flow to them)."""
+    from test_gpu_block_backward import _block_ref
+    BF, C, H, W = x.shape
+    B = BF // T
+    sub = lambda pre: {k[len(pre):]: v for k, v in P.items() if k.startswith(pre)}
+    tc = e.reshape(B, T, -1, e.shape[-1])[:, 0]
+    tc = tc[None, :].broadcast_to(H * W, B, tc.shape[-2], tc.shape[-1]).reshape(H * W * B, tc.shape[-2], tc.shape[-1])
+    h = F.group_norm(x, 32, P["norm.weight"], P["norm.bias"], 1e-6).permute(0, 2, 3, 1).reshape(BF, H * W, C)
+    h = F.linear(h, P["proj_in.weight"], P["proj_in.bias"])
+    t_emb = spatio_temporal_ref.timesteps_ref(torch.arange(T).repeat(B, 1).reshape(-1), C)
+    emb = F.linear(F.silu(F.linear(t_emb, P["time_pos_embed.linear_1.weight"], P["time_pos_embed.linear_1.bias"])),
+                   P["time_pos_embed.linear_2.weight"], P["time_pos_embed.linear_2.bias"])[:, None, :]
+    alpha = torch.where(ind.bool().reshape(-1), torch.ones(1), torch.sigmoid(P["time_mixer.mix_factor"])).reshape(-1, 1, 1)
+    h = _block_ref(sub("transformer_blocks.0."), h, e, heads)
+    hm = _block_ref(sub("temporal_transformer_blocks.0."), h + emb, tc, heads, True, T)
+    h = alpha * h + (1.0 - alpha) * hm
+    h = F.linear(h, P["proj_out.weight"], P["proj_out.bias"])
+    return h.reshape(BF, H, W, C).permute(0, 3, 1, 2) + x
+
+
+MODEL_CHECK = ["norm.weight", "norm.bias", "proj_in.weight", "proj_in.bias", "proj_out.weight", "proj_out.bias",
+               "time_pos_embed.linear_1.weight", "time_pos_embed.linear_2.bias", "time_mixer.mix_factor",
+               "transformer_blocks.0.attn1.to_q.weight", "transformer_blocks.0.ff.net.2.weight",
+               "temporal_transformer_blocks.0.ff_in.net.0.proj.weight", "temporal_transformer_blocks.0.attn2.to_v.weight",
+               "temporal_transformer_blocks.0.norm3.weight"]
+
+
+@pytest.mark.parametrize("ckpt", [False, True], ids=["plain", "checkpointed"])
+def test_model_forward_trains(cuda, ckpt):
+    # src/train.py back-propagates through this module; with gradient_checkpointing the spatial block runs under
+    # torch.utils.checkpoint(..., use_reentrant=False) (src/models/transformer_temporal.py:321-327)
+    B, T, H, W, C, heads = 1, 7, 6, 8, 320, 5
+    m = _model(C, heads, 1024, 17, cuda).train()
+    m.gradient_checkpointing = ckpt
+    spatio_temporal.install_spatio_temporal(m)
+    g = torch.Generator().manual_seed(3)
+    x = _bf(torch.randn(B * T, C, H, W, generator=g), cuda).requires_grad_(True)
+    e = _bf(torch.randn(B * T, 1, 1024, generator=g), cuda)
+    wgt = _bf(torch.randn(B * T, C, H, W, generator=g), cuda)
+    ind = torch.zeros(B, T, device=cuda)
+    ind[0, 1] = 1.0
+    launches0 = ops.LAUNCHES
+    y = m(x, encoder_hidden_states=e, image_only_indicator=ind, return_dict=False)[0]
+    assert y.requires_grad and y.shape == x.shape
+    (y.float() * wgt.float()).sum().backward()
+    torch.cuda.synchronize()
+    assert ops.LAUNCHES - launches0 >= 100          # the GEMMs, LayerNorms, attention cores and their backward kernels
+    P = {n: p.detach().float().cpu().requires_grad_(True) for n, p in m.named_parameters()}
+    xr = x.detach().float().cpu().requires_grad_(True)
+    yr = _model_ref(P, xr, e.float().cpu(), ind.cpu(), heads, T)
+    (yr * wgt.float().cpu()).sum().backward()
+
+    def close(name, got, ref):
+        err, scale = float((got.float().cpu() - ref).abs().max()), max(float(ref.abs().max()), 1e-6)
+        print(f"  {name}: max abs err {err:.3e} / max |ref| {scale:.3e}")
+        assert err <= 2e-2 * scale, name
+
+    close("forward", y.detach(), yr.detach())
+    close("dx", x.grad, xr.grad)
+    ps = dict(m.named_parameters())
+    for n in MODEL_CHECK:
+        assert ps[n].grad is not None, n
+        close(n, ps[n].grad, P[n].grad)
+    # the no-grad fast path (fused glue kernels) and the tape path agree
+    with torch.no_grad():
+        y0 = m(x.detach(), encoder_hidden_states=e, image_only_indicator=ind, return_dict=False)[0]
+    assert_block_close("fused vs tape", y0, y.detach().float().cpu(), stores=9)
 
 
 def test_graphed_forward_replays_bit_exact(cuda):

@@ -65,6 +65,8 @@ SIGNATURES = {
                                                  _i64, _i64, _i64, _i64, _f32, _ptr]),
     "tvi_attn_fewkeys_fwd": (_i32, [_ptr, _ptr, _ptr, _ptr, _i64, _i64, _i32, _i32, _i32,
                                     _i64, _i64, _i64, _i64, _f32, _i32, _ptr, _ptr, _ptr, _ptr]),
+    "tvi_attn_fewkeys_fwd_interleaved": (_i32, [_ptr, _ptr, _ptr, _ptr, _i64, _i64, _i32, _i32, _i32, _i64,
+                                                _i64, _i64, _i64, _i64, _f32, _i32, _ptr, _ptr, _ptr, _ptr]),
     "tvi_attn_spatial_fwd": (_i32, [_ptr, _ptr, _ptr, _ptr, _ptr, _i32, _i32, _i32, _i32, _i32,
                                     _i64, _i64, _i64, _i64, _f32, _ptr]),
     "tvi_attn_spatial_fwd_algo": (_i32, [_ptr, _ptr, _ptr, _ptr, _ptr, _i32, _i32, _i32, _i32, _i32,

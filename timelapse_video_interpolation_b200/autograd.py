@@ -53,21 +53,28 @@ def cross_attention(x: torch.Tensor, e: torch.Tensor, w_q: torch.Tensor, w_kv: t
                     heads: int, scale: float, bias=None, stats=None, residual=None, frames=None) -> torch.Tensor:
     """x [B', S, C], e [B', L, Ckv] -> [B', S, C].  Reference: same processor with
     encoder_hidden_states given (keys/values from the context, :1225-1231).
-    `frames` = T (one-key contexts only): x is [B*T, S, C] in the spatial token order, e is the temporal block's
-    [B*S, 1, Ckv] context; row (b, t, s) receives the projected value row of group (b, s)."""
+    `frames` = T: x is [B*T, S, C] in the spatial token order, e is the temporal block's [B*S, L, Ckv] context; row
+    (b, t, s) attends to the L keys of group (b, s) (one key: it receives that group's projected value row)."""
     Bp, S, C = x.shape
     L = e.shape[1]
     inner = w_kv.shape[0] // 2
     if frames is not None:
-        if L != 1 or stats is not None or bias is not None:
-            raise _lib.TviError(_lib.TVI_ERR_UNSUPPORTED, "frames= (temporal attention in the spatial token order) supports "
-                                                          "one-key contexts without bias / statistics")
         if e.shape[0] != Bp // frames * S:
             raise _lib.TviError(_lib.TVI_ERR_INVALID, "encoder_hidden_states batch does not match hidden_states (expects B*S rows)")
-        kv = ops.gemm_bf16_tn(e.view(-1, e.shape[2]), w_kv)
-        yv = ops.gemm_bf16_tn(kv[:, inner:], w_o, b_o)  # [B*S, C]
-        res2 = residual.reshape(Bp * S, residual.shape[-1]) if residual is not None else None
-        return ops.bcast_rows_add(yv, res2, frames, group_inner=S, nrows=Bp * S).view(Bp, S, yv.shape[-1])
+        if L > 8:
+            raise _lib.TviError(_lib.TVI_ERR_UNSUPPORTED, f"cross-attention with {L} context tokens (libtvi builds 1..8)")
+        kv = ops.gemm_bf16_tn(e.view(-1, e.shape[2]), w_kv)                              # [B*S*L, 2*inner]
+        if L == 1 and stats is None:
+            yv = ops.gemm_bf16_tn(kv[:, inner:], w_o, b_o)  # [B*S, C]
+            res2 = residual.reshape(Bp * S, residual.shape[-1]) if residual is not None else None
+            return ops.bcast_rows_add(yv, res2, frames, group_inner=S, nrows=Bp * S).view(Bp, S, yv.shape[-1])
+        # more keys, the ramp bias or the statistics: the few-keys core reads the T query rows of group (b, s) with a
+        # row stride of S (bias / statistics rows are the frame index t)
+        q = ops.gemm_bf16_tn(x.view(Bp * S, C), w_q)
+        o = ops.attn_fewkeys(q, kv[:, :inner], kv[:, inner:], Bp * S, frames, heads, L, scale,
+                             Tq=frames if (bias is not None or stats is not None) else 1, bias=bias, stats=stats, group_inner=S)
+        y = _out_proj(o, w_o, b_o, residual)
+        return y.view(Bp, S, y.shape[-1])
     _check_context(x, e)
     kv = ops.gemm_bf16_tn(e.view(Bp * L, e.shape[2]), w_kv)  # [B'*L, 2*inner]
     k, v = kv[:, :inner], kv[:, inner:]

@@ -8,8 +8,8 @@ out-projection epilogue) -> LayerNorm -> cross-attention (+ residual) -> LayerNo
 first GEMM, bias + residual into the second).  The `[B*T, S, C] <-> [B*S, T, C]` re-layout of the temporal block
 (:436-438, :474-476) is folded away (row N2): LayerNorm / FeedForward / projections are row-wise, so the block runs on
 the spatial token order in place and only the attention cores address the T tokens of a (b, s) sequence with a
-row stride of S (`tvi_attn_temporal_fwd_interleaved`, `tvi_bcast_rows_add_bf16(group_inner=S)`).  Contexts with more
-than one key (or a ramp-bias / statistics processor) fall back to the permute copies.
+row stride of S (`tvi_attn_temporal_fwd_interleaved`, `tvi_bcast_rows_add_bf16(group_inner=S)` for one-key contexts,
+`tvi_attn_fewkeys_fwd_interleaved` for 2..8 keys, the ramp bias and the logit statistics).
 
 `install_blocks(model)` re-binds `forward` on every module with the block's attribute layout (duck-typed) and installs
 the attention processor on its Attention modules.  Training (config 5) works through the same forwards: when a gradient is
@@ -96,8 +96,8 @@ def temporal_basic_transformer_block_forward(block, hidden_states: torch.Tensor,
     BF, S, C = hidden_states.shape
     B = BF // num_frames
     attn2 = getattr(block, "attn2", None)
-    in_place = fold_layout and not _training(block, hidden_states) and num_frames <= 64 and (attn2 is None or encoder_hidden_states is None or (
-        encoder_hidden_states.shape[1] == 1 and not _proc(attn2).ramp_bias and _proc(attn2).stats_sink is None))
+    in_place = fold_layout and not _training(block, hidden_states) and num_frames <= 64 and (
+        attn2 is None or encoder_hidden_states is None or encoder_hidden_states.shape[1] <= 8)
     if in_place:
         # every op but the attention cores is row-wise: stay in the [B*T, S, C] token order, no permute copies
         x = hidden_states.contiguous()

@@ -249,7 +249,7 @@ __global__ void __launch_bounds__(512)
 attn_fewkeys_kernel(const tvi_bf16* __restrict__ q, const tvi_bf16* __restrict__ k, const tvi_bf16* __restrict__ v,
                     tvi_bf16* __restrict__ o, int64_t rows_per_group, int tiles_per_group, int L, int64_t ldq,
                     int64_t ldk, int64_t ldv, int64_t ldo, float scale, int Tq, const float* __restrict__ bias,
-                    double* __restrict__ stats_acc) {
+                    double* __restrict__ stats_acc, int64_t inner) {
   const int cx = threadIdx.x;               // 16-byte channel chunk of the row
   const int ry = threadIdx.y, RY = blockDim.y;
   const int64_t group = blockIdx.x / tiles_per_group;
@@ -259,6 +259,11 @@ attn_fewkeys_kernel(const tvi_bf16* __restrict__ q, const tvi_bf16* __restrict__
   int64_t rhi = rlo + rows_per_tile;
   const int64_t gend = (group + 1) * rows_per_group;
   if (rhi > gend) rhi = gend;
+  // inner > 1: the groups are interleaved — logical row i of group (b, s) (s < inner) is physical row
+  // (b * rows_per_group + i) * inner + s, i.e. the [B*T, S, C] token order read as [B*S, T, C] (T = rows_per_group)
+  const int64_t gbase = group * rows_per_group;
+  const int64_t pbase = (group / inner) * rows_per_group * inner + group % inner;
+  auto phys = [&](int64_t r) -> int64_t { return inner == 1 ? r : pbase + (r - gbase) * inner; };
 
   extern __shared__ float s_stats[];  // [Tq * LT] when STATS
   if (STATS) {
@@ -281,7 +286,7 @@ attn_fewkeys_kernel(const tvi_bf16* __restrict__ q, const tvi_bf16* __restrict__
 
   if (LT == 1 && !STATS) {
     // softmax over one key is exactly 1: O = V broadcast, Q is never read
-    for (int64_t r = rlo + ry; r < rhi; r += RY) *reinterpret_cast<uint4*>(o + r * ldo + cx * 8) = vr[0];
+    for (int64_t r = rlo + ry; r < rhi; r += RY) *reinterpret_cast<uint4*>(o + phys(r) * ldo + cx * 8) = vr[0];
     return;
   }
 
@@ -297,7 +302,7 @@ attn_fewkeys_kernel(const tvi_bf16* __restrict__ q, const tvi_bf16* __restrict__
 #pragma unroll
     for (int u = 0; u < kFewUnroll; ++u) {
       const int64_t rr = rlo + (int64_t)(it0 + u) * RY + ry;
-      qv[u] = __ldg(reinterpret_cast<const uint4*>(q + (rr < rhi ? rr : rlo) * ldq + cx * 8));
+      qv[u] = __ldg(reinterpret_cast<const uint4*>(q + phys(rr < rhi ? rr : rlo) * ldq + cx * 8));
     }
 #pragma unroll
     for (int u = 0; u < kFewUnroll; ++u) {
@@ -362,7 +367,7 @@ attn_fewkeys_kernel(const tvi_bf16* __restrict__ q, const tvi_bf16* __restrict__
     outv.y = pack_bf16x2(of[2], of[3]);
     outv.z = pack_bf16x2(of[4], of[5]);
     outv.w = pack_bf16x2(of[6], of[7]);
-    if (act) *reinterpret_cast<uint4*>(o + r * ldo + cx * 8) = outv;
+    if (act) *reinterpret_cast<uint4*>(o + phys(r) * ldo + cx * 8) = outv;
     }
   }
 
@@ -383,7 +388,7 @@ __global__ void fewkeys_stats_final_kernel(const double* __restrict__ acc, float
 template <int LT, int LPH>
 int launch_fewkeys(const tvi_bf16* q, const tvi_bf16* k, const tvi_bf16* v, tvi_bf16* o, int64_t ngroups,
                    int64_t rows_per_group, int C8, int L, int64_t ldq, int64_t ldk, int64_t ldv, int64_t ldo,
-                   float scale, int Tq, const float* bias, double* stats_acc, cudaStream_t st) {
+                   float scale, int Tq, const float* bias, double* stats_acc, int64_t inner, cudaStream_t st) {
   // whole warps only: blockDim.x * blockDim.y must be a multiple of 32 (C8 is a multiple of 8)
   const int unit = (C8 % 32 == 0) ? 1 : (C8 % 16 == 0) ? 2 : 4;
   int RY = unit * (256 / (C8 * unit) > 0 ? 256 / (C8 * unit) : 1);
@@ -397,10 +402,10 @@ int launch_fewkeys(const tvi_bf16* q, const tvi_bf16* k, const tvi_bf16* v, tvi_
     const size_t sm = (size_t)Tq * LT * sizeof(float);
     TVI_CHECK_ARG(sm <= 48 * 1024, "tvi_attn_fewkeys_fwd: Tq*L too large for the statistics buffer");
     attn_fewkeys_kernel<LT, LPH, true><<<grid, block, sm, st>>>(q, k, v, o, rows_per_group, (int)tiles, L, ldq, ldk, ldv, ldo,
-                                                                scale, Tq, bias, stats_acc);
+                                                                scale, Tq, bias, stats_acc, inner);
   } else {
     attn_fewkeys_kernel<LT, LPH, false><<<grid, block, 0, st>>>(q, k, v, o, rows_per_group, (int)tiles, L, ldq, ldk, ldv, ldo,
-                                                                scale, Tq, bias, nullptr);
+                                                                scale, Tq, bias, nullptr, inner);
   }
   TVI_LAUNCH_OK("attn_fewkeys_kernel");
   return TVI_OK;
@@ -440,6 +445,14 @@ int tvi_attn_temporal_fwd(const tvi_bf16* q, const tvi_bf16* k, const tvi_bf16* 
 int tvi_attn_fewkeys_fwd(const tvi_bf16* q, const tvi_bf16* k, const tvi_bf16* v, tvi_bf16* o, int64_t nrows,
                          int64_t rows_per_group, int heads, int L, int d, int64_t ldq, int64_t ldk, int64_t ldv,
                          int64_t ldo, float scale, int Tq, const float* bias, float* stats, void* stats_ws, void* stream) {
+  return tvi_attn_fewkeys_fwd_interleaved(q, k, v, o, nrows, rows_per_group, heads, L, d, 1, ldq, ldk, ldv, ldo, scale, Tq, bias,
+                                          stats, stats_ws, stream);
+}
+
+int tvi_attn_fewkeys_fwd_interleaved(const tvi_bf16* q, const tvi_bf16* k, const tvi_bf16* v, tvi_bf16* o, int64_t nrows,
+                                     int64_t rows_per_group, int heads, int L, int d, int64_t group_inner, int64_t ldq,
+                                     int64_t ldk, int64_t ldv, int64_t ldo, float scale, int Tq, const float* bias,
+                                     float* stats, void* stats_ws, void* stream) {
   using namespace tvi;
   TVI_CHECK_ARG(nrows >= 0 && heads >= 0, "tvi_attn_fewkeys_fwd: negative size");
   if (nrows == 0 || heads == 0) return TVI_OK;
@@ -456,6 +469,7 @@ int tvi_attn_fewkeys_fwd(const tvi_bf16* q, const tvi_bf16* k, const tvi_bf16* v
   TVI_CHECK_ARG(((uintptr_t)q | (uintptr_t)k | (uintptr_t)v | (uintptr_t)o) % 16 == 0, "tvi_attn_fewkeys_fwd: pointers must be 16-byte aligned");
   cudaStream_t st = (cudaStream_t)stream;
   const int64_t ngroups = nrows / rows_per_group;
+  TVI_CHECK_ARG(group_inner >= 1 && ngroups % group_inner == 0, "tvi_attn_fewkeys_fwd: the group count must be a multiple of group_inner");
   double* acc = nullptr;
   if (stats != nullptr) {
     acc = (double*)stats_ws;
@@ -463,8 +477,8 @@ int tvi_attn_fewkeys_fwd(const tvi_bf16* q, const tvi_bf16* k, const tvi_bf16* v
   }
   int rc;
 #define TVI_FEW(LT)                                                                                              \
-  (d == 64 ? launch_fewkeys<LT, 8>(q, k, v, o, ngroups, rows_per_group, C / 8, L, ldq, ldk, ldv, ldo, scale, Tq, bias, acc, st) \
-           : launch_fewkeys<LT, 16>(q, k, v, o, ngroups, rows_per_group, C / 8, L, ldq, ldk, ldv, ldo, scale, Tq, bias, acc, st))
+  (d == 64 ? launch_fewkeys<LT, 8>(q, k, v, o, ngroups, rows_per_group, C / 8, L, ldq, ldk, ldv, ldo, scale, Tq, bias, acc, group_inner, st) \
+           : launch_fewkeys<LT, 16>(q, k, v, o, ngroups, rows_per_group, C / 8, L, ldq, ldk, ldv, ldo, scale, Tq, bias, acc, group_inner, st))
   if (L == 1) rc = TVI_FEW(1);
   else if (L == 2) rc = TVI_FEW(2);
   else if (L <= 4) rc = TVI_FEW(4);

@@ -23,7 +23,7 @@ import torch
 
 from . import _lib, caches, ops
 
-__all__ = ["feed_forward", "layer_norm", "install_feed_forward", "uninstall_feed_forward"]
+__all__ = ["feed_forward", "layer_norm", "linear", "install_feed_forward", "uninstall_feed_forward"]
 
 _cache: weakref.WeakKeyDictionary = weakref.WeakKeyDictionary()  # weak: an id() key could be recycled by a later module
 
@@ -108,6 +108,39 @@ class _FeedForwardFn(torch.autograd.Function):
         dx = ops.gemm_bf16_dgrad(dpre, w1b).view(ctx.x_shape) if need_x else None
         return dx, _cast_grad(dw1, w1), _cast_grad(db1, b1) if b1 is not None else None, _cast_grad(dw2, w2), \
             _cast_grad(db2, b2) if b2 is not None else None
+
+
+class _LinearFn(torch.autograd.Function):
+    """Tape entry of `F.linear(x, w, b)` on the tcgen05 GEMM: dx = dy W (dgrad), dW = dy^T x (wgrad, fixed summation order),
+    db = column sums.  Used for proj_in / proj_out of the module-level forward when it trains."""
+
+    @staticmethod
+    def forward(ctx, x, w, b):
+        x2 = x.detach().contiguous().view(x.numel() // max(x.shape[-1], 1), x.shape[-1])
+        y = ops.gemm_bf16_tn(x2, _bf16(w), _bf16(b))
+        ctx.save_for_backward(x2, w, b)
+        ctx.xshape = x.shape
+        return y.view(*x.shape[:-1], y.shape[-1])
+
+    @staticmethod
+    def backward(ctx, dy):
+        x2, w, b = ctx.saved_tensors
+        need_x, need_w, need_b = ctx.needs_input_grad
+        dy2 = dy.contiguous().to(torch.bfloat16).view(x2.shape[0], -1)
+        dx = ops.gemm_bf16_dgrad(dy2, _bf16(w)).view(ctx.xshape) if need_x else None
+        dw = _cast_grad(ops.gemm_bf16_wgrad(dy2, x2), w) if need_w else None
+        db = _cast_grad(ops.colsum_bf16(dy2).view(-1), b) if (need_b and b is not None) else None
+        return dx, dw, db
+
+
+def linear(lin, x: torch.Tensor) -> torch.Tensor:
+    """`lin(x)` for an nn.Linear-shaped module on the libtvi GEMM; on the autograd tape when a gradient is needed."""
+    if getattr(lin, "lora_layer", None) is not None:
+        raise _lib.TviError(_lib.TVI_ERR_UNSUPPORTED, "linear: LoRA layers are not supported by the libtvi path")
+    if torch.is_grad_enabled() and (x.requires_grad or lin.weight.requires_grad or (lin.bias is not None and lin.bias.requires_grad)):
+        return _LinearFn.apply(x, lin.weight, lin.bias)
+    x2 = x.contiguous().view(x.numel() // max(x.shape[-1], 1), x.shape[-1])
+    return ops.gemm_bf16_tn(x2, _bf16(lin.weight), _bf16(lin.bias)).view(*x.shape[:-1], lin.weight.shape[0])
 
 
 class _LayerNormFn(torch.autograd.Function):

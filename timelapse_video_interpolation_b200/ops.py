@@ -362,8 +362,9 @@ def attn_temporal(q, k, v, nseq: int, heads: int, Tq: int, Tk: int, scale: float
 
 
 def attn_fewkeys(q, k, v, nrows: int, rows_per_group: int, heads: int, L: int, scale: float, out=None,
-                 Tq: int = 1, bias=None, stats=None):
-    """Few-key cross-attention core; k/v are [ngroups*L, heads*d]; q may be None when L == 1."""
+                 Tq: int = 1, bias=None, stats=None, group_inner: int = 1):
+    """Few-key cross-attention core; k/v are [ngroups*L, heads*d]; q may be None when L == 1.  group_inner > 1: the
+    groups are interleaved (logical row i of group (b, s) is physical row (b * rows_per_group + i) * group_inner + s)."""
     global LAUNCHES
     _need_cuda(q, k, v, bias, stats)
     k, ldk = _rows2d(k, "k")
@@ -385,11 +386,10 @@ def attn_fewkeys(q, k, v, nrows: int, rows_per_group: int, heads: int, L: int, s
         raise _lib.TviError(_lib.TVI_ERR_INVALID, "bias must be a contiguous fp32 [Tq, L] tensor")
     if EVENT_HOOK is not None:
         EVENT_HOOK("attn_fewkeys", True)
-    _lib.check(_lib.load().tvi_attn_fewkeys_fwd(q.data_ptr() if q is not None else None, k.data_ptr(), v.data_ptr(),
-                                                out.data_ptr(), nrows, rows_per_group, heads, L, d, ldq, ldk, ldv, ldo,
-                                                float(scale), Tq, bias.data_ptr() if bias is not None else None,
-                                                stats.data_ptr() if stats is not None else None,
-                                                ws.data_ptr() if ws is not None else None, _stream()))
+    _lib.check(_lib.load().tvi_attn_fewkeys_fwd_interleaved(
+        q.data_ptr() if q is not None else None, k.data_ptr(), v.data_ptr(), out.data_ptr(), nrows, rows_per_group, heads, L, d,
+        int(group_inner), ldq, ldk, ldv, ldo, float(scale), Tq, bias.data_ptr() if bias is not None else None,
+        stats.data_ptr() if stats is not None else None, ws.data_ptr() if ws is not None else None, _stream()))
     if EVENT_HOOK is not None:
         EVENT_HOOK("attn_fewkeys", False)
     LAUNCHES += 1 if stats is None else 2

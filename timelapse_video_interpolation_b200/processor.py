@@ -123,7 +123,7 @@ class TviAttnProcessor:
         `residual` — a tensor of the output's shape added in the out-projection epilogue, i.e. the caller's
         `attn_output + hidden_states`;
         `frames` = T — hidden_states is [B*T, S, C] in the spatial token order and attention runs over the T tokens of
-        every (b, s) (encoder_hidden_states: the temporal [B*S, 1, Ckv] context): the temporal block without its two
+        every (b, s) (encoder_hidden_states: the temporal [B*S, L, Ckv] context): the temporal block without its two
         permute copies (src/models/attention.py:436-438, :474-476).  Inference only."""
         self._check(attn, hidden_states, attention_mask)
         in_dtype = hidden_states.dtype
@@ -144,10 +144,7 @@ class TviAttnProcessor:
         if is_cross:
             e = encoder_hidden_states.contiguous()
             L = e.shape[1]
-            Tq = x.shape[1]
-            if frames is not None and (self.ramp_bias or self.stats_sink is not None):
-                raise _lib.TviError(_lib.TVI_ERR_UNSUPPORTED, "frames= is not available with ramp_bias / stats_sink "
-                                                              "(those read the [B*S, T, C] layout)")
+            Tq = x.shape[1] if frames is None else int(frames)   # bias / statistics rows are the query's frame index
             if self.ramp_bias:
                 if L != 2:
                     raise _lib.TviError(_lib.TVI_ERR_INVALID, "ramp_bias expects exactly 2 context tokens "

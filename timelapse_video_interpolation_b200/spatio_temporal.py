@@ -10,7 +10,13 @@ Same signature, same results; what changes is where the bytes go:
   * the two blocks (:329-347)                                -> blocks.py forwards (the temporal one without permutes)
   * `time_mixer` (:349-351)                                  -> blend kernel, one fp32 alpha per frame
   * `reshape.permute(0, 3, 1, 2).contiguous() + residual`    -> one transpose-add kernel
-Inference only (see blocks.py); `install_spatio_temporal(model)` rebinds every module with this attribute layout.
+`install_spatio_temporal(model)` rebinds every module with this attribute layout.
+
+Training (src/train.py back-propagates through this forward, the spatial block under `torch.utils.checkpoint(...,
+use_reentrant=False)` at :321-327): when a gradient is needed the call goes on the autograd tape — proj_in / proj_out, the
+blocks' LayerNorms, attention and FeedForward through their libtvi autograd Functions (forward AND backward kernels),
+the thin glue (GroupNorm + NCHW<->token permutes, frame-embedding add, AlphaBlender, module residual) as torch ops:
+their fused kernels above have no backward yet and are the inference fast path.
 """
 from __future__ import annotations
 
@@ -21,11 +27,13 @@ from dataclasses import dataclass
 from typing import Optional
 
 import torch
+import torch.utils.checkpoint
 
 from . import _lib, caches, ops
-from .blocks import (_no_grad_only, basic_transformer_block_forward, install_blocks,
+from .blocks import (_training, basic_transformer_block_forward, install_blocks,
                      temporal_basic_transformer_block_forward)
 from .feedforward import _bf16 as _bf16_param
+from .feedforward import linear as _linear
 
 __all__ = ["transformer_spatio_temporal_forward", "install_spatio_temporal", "uninstall_spatio_temporal"]
 
@@ -97,7 +105,6 @@ def transformer_spatio_temporal_forward(model, hidden_states: torch.Tensor, enco
         raise _lib.TviError(_lib.TVI_ERR_INVALID, "hidden_states is not on a CUDA device (there is no CPU fallback)")
     if hidden_states.dtype != torch.bfloat16:
         raise _lib.TviError(_lib.TVI_ERR_UNSUPPORTED, f"hidden_states is {hidden_states.dtype}; the libtvi path is bf16")
-    _no_grad_only(model, hidden_states)
     BF, C, H, W = hidden_states.shape
     T = image_only_indicator.shape[-1]
     B = BF // T
@@ -112,6 +119,20 @@ def transformer_spatio_temporal_forward(model, hidden_states: torch.Tensor, enco
     tc = temporal_ctx[None, :].reshape(B, T, -1, temporal_ctx.shape[-1])[:, 0]
     time_context = tc[None, :].broadcast_to(S, B, tc.shape[-2], tc.shape[-1]).reshape(S * B, tc.shape[-2], tc.shape[-1])
 
+    if _training(model, hidden_states):
+        out = _forward_on_tape(model, hidden_states, spatial_ctx, time_context, image_only_indicator, B, T, H, W)
+    else:
+        out = _forward_fused(model, hidden_states, spatial_ctx, time_context, image_only_indicator, B, T, H, W)
+    if not return_dict:
+        return (out,)
+    mod = sys.modules.get(type(model).__module__)
+    cls = getattr(mod, "TransformerTemporalModelOutput", None) or TransformerTemporalModelOutput
+    return cls(sample=out)
+
+
+def _forward_fused(model, hidden_states, spatial_ctx, time_context, image_only_indicator, B, T, H, W):
+    """No-grad path: fused GroupNorm / layout / blend kernels, cached frame embedding and alpha."""
+    BF, S = B * T, H * W
     residual = hidden_states.contiguous()
     norm = model.norm
     x = ops.groupnorm_tokens(residual, _bf16_param(norm.weight), _bf16_param(norm.bias), int(norm.num_groups), float(norm.eps))
@@ -127,12 +148,58 @@ def transformer_spatio_temporal_forward(model, hidden_states: torch.Tensor, enco
                                                          encoder_hidden_states=time_context)      # :343-347
         x = ops.blend_rows(x, x_mix, alpha, S)                                                    # :349-351
     y = ops.gemm_bf16_tn(x, _bf16_param(model.proj_out.weight), _bf16_param(model.proj_out.bias))  # :353
-    out = ops.tokens_to_nchw_add(y.view(BF, S, y.shape[-1]), residual, H, W)                               # :354-357
-    if not return_dict:
-        return (out,)
-    mod = sys.modules.get(type(model).__module__)
-    cls = getattr(mod, "TransformerTemporalModelOutput", None) or TransformerTemporalModelOutput
-    return cls(sample=out)
+    return ops.tokens_to_nchw_add(y.view(BF, S, y.shape[-1]), residual, H, W)                      # :354-357
+
+
+def _forward_on_tape(model, hidden_states, spatial_ctx, time_context, image_only_indicator, B, T, H, W):
+    """Training path (see the module docstring): same order of operations as :300-357, glue as torch ops on the tape."""
+    BF, S, C = B * T, H * W, hidden_states.shape[1]
+    residual = hidden_states
+    norm = model.norm
+    x = torch.nn.functional.group_norm(hidden_states, int(norm.num_groups), _cast_like(norm.weight, hidden_states),
+                                       _cast_like(norm.bias, hidden_states), float(norm.eps))    # :300
+    x = x.permute(0, 2, 3, 1).reshape(BF, S, C)                                                   # :302-304
+    x = _linear(model.proj_in, x)                                                                 # :306
+    idx = torch.arange(T, device=hidden_states.device).repeat(B, 1).reshape(-1)                   # :308-315
+    tp = model.time_pos_embed
+    t_emb = model.time_proj(idx).to(hidden_states.dtype)
+    emb = tp(t_emb.to(tp.linear_1.weight.dtype)).to(hidden_states.dtype)[:, None, :]
+    if emb.shape[-1] != x.shape[-1]:
+        raise _lib.TviError(_lib.TVI_ERR_UNSUPPORTED, "in_channels != inner_dim: the frame embedding cannot be added (:333)")
+    alpha = _alpha_on_tape(model.time_mixer, image_only_indicator.to(hidden_states.device)).to(hidden_states.dtype)  # [BF, 1, 1]
+    use_ckpt = bool(getattr(model, "gradient_checkpointing", False)) and model.training
+    for block, temporal_block in zip(model.transformer_blocks, model.temporal_transformer_blocks):
+        if use_ckpt:  # :321-327
+            x = torch.utils.checkpoint.checkpoint(block, x, None, spatial_ctx, None, use_reentrant=False)
+        else:
+            x = block(x, encoder_hidden_states=spatial_ctx)                                        # :329-333
+        x_mix = x + emb                                                                            # :341-342
+        x_mix = temporal_block(x_mix, num_frames=T, encoder_hidden_states=time_context)            # :343-347
+        x = alpha * x + (1.0 - alpha) * x_mix                                                      # :349-351 (AlphaBlender.forward)
+    y = _linear(model.proj_out, x)                                                                 # :353
+    return y.reshape(BF, H, W, y.shape[-1]).permute(0, 3, 1, 2).contiguous() + residual           # :354-357
+
+
+def _cast_like(p, x):
+    return None if p is None else (p if p.dtype == x.dtype else p.to(x.dtype))
+
+
+def _alpha_on_tape(mixer, image_only_indicator: torch.Tensor) -> torch.Tensor:
+    """AlphaBlender.get_alpha for ndims == 3 as differentiable torch ops (mix_factor may train): [B*T, 1, 1]."""
+    strategy = getattr(mixer, "merge_strategy", "learned_with_images")
+    ind = image_only_indicator.reshape(-1)
+    mf = mixer.mix_factor.float().reshape(-1)[:1]
+    if strategy == "fixed":
+        a = mf.expand(ind.numel())
+    elif strategy == "learned":
+        a = torch.sigmoid(mf).expand(ind.numel())
+    elif strategy == "learned_with_images":
+        a = torch.where(ind.bool(), torch.ones(1, device=ind.device), torch.sigmoid(mf).to(ind.device))
+    else:
+        raise _lib.TviError(_lib.TVI_ERR_UNSUPPORTED, f"AlphaBlender merge_strategy {strategy!r}")
+    if getattr(mixer, "switch_spatial_to_temporal_mix", False):
+        a = 1.0 - a
+    return a.reshape(-1, 1, 1)
 
 
 def _is_spatio_temporal(m) -> bool:

@@ -609,12 +609,53 @@ def _train_step(steps=3):
     fwd_bwd()
     ops.EVENT_HOOK = None
     ks = kt.summary(1)
-    return {"config": "train_fwd_bwd_L0_block_pair_576x1024", "clips_per_gpu": B, "frames": T, "cfg_batch": 1,
+    del sb, tb, x, xg, dy
+    torch.cuda.empty_cache()
+    module = _train_step_module(B, T, C, heads, h, w, g, steps)
+    return {"config": "train_fwd_bwd_L0_block_pair_576x1024", "clips_per_gpu": B, "frames": T, "cfg_batch": 1, "module": module,
             "trainable": "temporal block (spatial block frozen, gradient flows through it to the input)",
             "trainable_params": sum(p.numel() for p in tb.parameters()), "ms_fwd": ms_f, "ms_fwd_bwd": ms_fb,
             "clip_frames_per_s_fwd_bwd": B * T / (ms_fb * 1e-3),
             "ms_spatial_attention_bwd": ks.get("attn_spatial_bwd", {}).get("ms_per_step"),
             "ms_by_entry_point": {k: round(v["ms_per_step"], 4) for k, v in ks.items()}}
+
+
+def _train_step_module(B, T, C, heads, h, w, g, steps):
+    """The same step through the MODULE-level swap (`install_spatio_temporal`): TransformerSpatioTemporalModel.forward at L0
+    (GroupNorm, proj_in, the block pair, AlphaBlender, proj_out, residual) trained the way src/train.py does — temporal
+    block + time_mixer trainable, everything else frozen, plain and with the spatial block under
+    torch.utils.checkpoint(use_reentrant=False) (src/models/transformer_temporal.py:321-327)."""
+    from timelapse_video_interpolation_b200 import spatio_temporal
+    from timelapse_video_interpolation_b200.modules import TransformerSpatioTemporalModel
+    m = TransformerSpatioTemporalModel(heads, C // heads, in_channels=C, num_layers=1, cross_attention_dim=1024)
+    with torch.no_grad():
+        for name, p in m.named_parameters():
+            if name.endswith("mix_factor"):
+                p.fill_(0.5)
+            elif "norm" in name:
+                p.fill_(1.0 if name.endswith("weight") else 0.0)
+            else:
+                p.copy_((torch.rand(p.shape, generator=g) * 2 - 1) * (p.shape[-1] ** -0.5 if p.dim() > 1 else C ** -0.5))
+            p.requires_grad_("temporal_transformer_blocks" in name or "time_mixer" in name)
+    m = m.to(DEV, torch.bfloat16).train()
+    spatio_temporal.install_spatio_temporal(m)
+    x = torch.randn(B * T, C, h, w, generator=g).to(torch.bfloat16).to(DEV).requires_grad_(True)
+    ctx = torch.randn(B * T, 1, 1024, generator=g).to(torch.bfloat16).to(DEV)
+    ind = torch.zeros(B, T, device=DEV)
+    dy = (torch.randn(B * T, C, h, w, generator=g) / 8).to(torch.bfloat16).to(DEV)
+
+    def fwd_bwd():
+        for p in m.parameters():
+            p.grad = None
+        x.grad = None
+        m(x, encoder_hidden_states=ctx, image_only_indicator=ind, return_dict=False)[0].backward(dy)
+
+    out = {"config": "train_fwd_bwd_L0_module_576x1024", "trainable_params": sum(p.numel() for p in m.parameters() if p.requires_grad)}
+    for key, ck in (("ms_fwd_bwd", False), ("ms_fwd_bwd_checkpointed", True)):
+        m.gradient_checkpointing = ck
+        out[key] = timed(fwd_bwd, steps)
+    out["clip_frames_per_s_fwd_bwd"] = B * T / (out["ms_fwd_bwd"] * 1e-3)
+    return out
 
 
 def driver_extras(dev, pk):
