@@ -203,7 +203,7 @@ int tvi_colsum_bf16(const tvi_bf16* x, tvi_bf16* out, void* workspace, int64_t n
 /* ---------------------------------------------------------------------------------------------
  * A3c  short-sequence (temporal) attention core: nseq independent sequences, every head,
  * O = softmax(scale . Q K^T) V with fp32 softmax.  Sequence s owns query rows [s*Tq, (s+1)*Tq)
- * and key/value rows [s*Tk, (s+1)*Tk).  1 <= Tq, Tk <= 64, d == 64.
+ * and key/value rows [s*Tk, (s+1)*Tk).  1 <= Tq, Tk <= 64, d in {64, 128}.
  * Replaces: F.scaled_dot_product_attention / xformers / baddbmm+softmax+bmm on the
  * [B*S, T, C] operands, src/models/attention_processor.py:1243, :1156, :598-615+:750, called from
  * src/models/attention.py:451-453.
@@ -253,7 +253,7 @@ int tvi_attn_fewkeys_fwd_interleaved(const tvi_bf16* q, const tvi_bf16* k, const
  * batch independent sequences of S query rows and Skv key rows, no mask, non-causal.
  * Replaces: F.scaled_dot_product_attention / xformers.ops.memory_efficient_attention on
  * [BF, h, S, 64], src/models/attention_processor.py:1243, :1156 (called from
- * src/models/attention.py:276-281).  d == 64.
+ * src/models/attention.py:276-281).  d in {64, 128} (128: the mma.sync kernel; TVI_SPATIAL_TCGEN05 is built for d == 64).
  *   lse (nullable): [batch*S, heads] fp32.
  */
 int tvi_attn_spatial_fwd(const tvi_bf16* q, const tvi_bf16* k, const tvi_bf16* v, tvi_bf16* o, float* lse,

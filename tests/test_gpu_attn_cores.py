@@ -44,6 +44,56 @@ def test_temporal_core(cuda, nseq, heads, Tq, Tk):
     assert (lse.cpu() - ref_lse).abs().max().item() < 1e-3
 
 
+@pytest.mark.parametrize("nseq,heads,Tq,Tk", [(64, 10, 14, 14), (37, 3, 25, 25), (300, 1, 1, 1), (9, 2, 40, 40), (7, 2, 14, 3),
+                                              (2000, 10, 14, 14)])
+def test_temporal_core_head_dim_128(cuda, nseq, heads, Tq, Tk):
+    # the class default num_attention_heads=(5, 10, 10, 20) gives d = 1280 / 10 = 128 at level 2
+    # (src/models/unet_spatio_temporal_condition.py:94)
+    g = torch.Generator().manual_seed(nseq + Tq)
+    C = heads * 128
+    q, qf = _rand((nseq, Tq, C), g, cuda)
+    k, kf = _rand((nseq, Tk, C), g, cuda)
+    v, vf = _rand((nseq, Tk, C), g, cuda)
+    scale = 128 ** -0.5
+    lse = torch.empty(nseq * Tq, heads, dtype=torch.float32, device=cuda)
+    o = ops.attn_temporal(q.view(-1, C), k.view(-1, C), v.view(-1, C), nseq, heads, Tq, Tk, scale, lse=lse)
+    torch.cuda.synchronize()
+    ref, logits = _core_ref(qf, kf, vf, heads, scale)
+    assert (o.float().cpu().view(nseq, Tq, C) - ref).abs().max().item() < TOL
+    ref_lse = torch.logsumexp(logits, dim=-1).view(nseq, heads, Tq).permute(0, 2, 1).reshape(nseq * Tq, heads)
+    assert (lse.cpu() - ref_lse).abs().max().item() < 1e-3
+    # interleaved sequences (N2) at d = 128: bit-identical to the contiguous kernel on permuted copies
+    if Tq == Tk and nseq % 4 == 0:
+        B, S = 4, nseq // 4
+        qkv, _ = _rand((B, Tq, S, 3 * C), g, cuda)
+        flat = qkv.view(-1, 3 * C)
+        o_i = ops.attn_temporal(flat[:, :C], flat[:, C:2 * C], flat[:, 2 * C:], B * S, heads, Tq, Tq, scale, seq_inner=S)
+        perm = qkv.permute(0, 2, 1, 3).contiguous().view(-1, 3 * C)
+        o_p = ops.attn_temporal(perm[:, :C], perm[:, C:2 * C], perm[:, 2 * C:], B * S, heads, Tq, Tq, scale)
+        assert torch.equal(o_i.view(B, Tq, S, C), o_p.view(B, S, Tq, C).permute(0, 2, 1, 3))
+
+
+@pytest.mark.parametrize("B,heads,S,Skv", [(2, 2, 80, 80), (1, 10, 576, 576), (1, 2, 129, 63), (2, 3, 1000, 1000), (1, 1, 2304, 2304)])
+def test_spatial_core_head_dim_128(cuda, B, heads, S, Skv):
+    g = torch.Generator().manual_seed(S + Skv + 1)
+    C = heads * 128
+    q, qf = _rand((B, S, C), g, cuda)
+    k, kf = _rand((B, Skv, C), g, cuda)
+    v, vf = _rand((B, Skv, C), g, cuda)
+    scale = 128 ** -0.5
+    lse = torch.empty(B * S, heads, dtype=torch.float32, device=cuda)
+    o = ops.attn_spatial(q.view(-1, C), k.view(-1, C), v.view(-1, C), B, heads, S, Skv, scale, lse=lse)   # AUTO -> mma.sync
+    torch.cuda.synchronize()
+    ref, logits = _core_ref(qf, kf, vf, heads, scale)
+    err = (o.float().cpu().view(B, S, C) - ref).abs().max().item()
+    print(f"spatial core d=128 B={B} h={heads} S={S}x{Skv}: max abs err {err:.3e}")
+    assert err < TOL
+    ref_lse = torch.logsumexp(logits, dim=-1).view(B, heads, S).permute(0, 2, 1).reshape(B * S, heads)
+    assert (lse.cpu() - ref_lse).abs().max().item() < 1e-3
+    with pytest.raises(_lib.TviError):      # the tcgen05 kernel is built for 64-wide heads: asking for it explicitly is an error
+        ops.attn_spatial(q.view(-1, C), k.view(-1, C), v.view(-1, C), B, heads, S, Skv, scale, algo=_lib.SPATIAL_TCGEN05)
+
+
 def test_temporal_core_reads_packed_qkv_in_place(cuda):
     g = torch.Generator().manual_seed(3)
     nseq, heads, T = 50, 5, 14

@@ -68,8 +68,8 @@ def test_blend_rows(cuda):
         ops.blend_rows(xs, xt, alpha[:5].contiguous(), S)
 
 
-def _model(C, heads, cross, seed, cuda):
-    m = TransformerSpatioTemporalModel(heads, 64, in_channels=C, num_layers=1, cross_attention_dim=cross)
+def _model(C, heads, cross, seed, cuda, head_dim=64):
+    m = TransformerSpatioTemporalModel(heads, head_dim, in_channels=C, num_layers=1, cross_attention_dim=cross)
     g = torch.Generator().manual_seed(seed)
     with torch.no_grad():
         for name, p in m.named_parameters():
@@ -104,6 +104,22 @@ def test_transformer_spatio_temporal_model_matches_oracle(cuda, B, T, H, W, C, h
     assert spatio_temporal.uninstall_spatio_temporal(m) == 1
     with pytest.raises(RuntimeError):
         m(x, encoder_hidden_states=e, image_only_indicator=ind)
+
+
+def test_model_with_128_wide_heads_matches_oracle(cuda):
+    # level 2 of a UNet built from the class defaults: C = 1280, 10 heads of 128 (src/models/unet_spatio_temporal_condition.py:94)
+    B, T, H, W, C, heads = 1, 14, 6, 8, 1280, 10
+    m = _model(C, heads, 1024, 13, cuda, head_dim=128)
+    assert m.transformer_blocks[0].attn1.scale == 128 ** -0.5
+    spatio_temporal.install_spatio_temporal(m)
+    g = torch.Generator().manual_seed(2)
+    x = _bf(torch.randn(B * T, C, H, W, generator=g), cuda)
+    e = _bf(torch.randn(B * T, 1, 1024, generator=g), cuda)
+    ind = torch.zeros(B, T, device=cuda)
+    with torch.no_grad():
+        y = m(x, encoder_hidden_states=e, image_only_indicator=ind, return_dict=False)[0]
+    ref = spatio_temporal_ref.transformer_spatio_temporal_ref(m, x, e, ind, alpha_dtype=torch.bfloat16)
+    assert_block_close("spatio-temporal model d=128", y, ref, stores=9)
 
 
 def test_model_forward_matches_reference_golden(cuda, golden_dir):

@@ -1,6 +1,6 @@
 // A3c / A3b / A3d — the two HBM-bound attention cores.
 //
-// tvi_attn_temporal_fwd : nseq x heads independent problems of T<=64 tokens, d=64.  One warp
+// tvi_attn_temporal_fwd : nseq x heads independent problems of T<=64 tokens, d=64 or 128.  One warp
 //   per (sequence, head): the three T x 64 bf16 tiles are staged in shared memory with 128-bit
 //   cp.async copies (each tile row is one full 128-byte line; rows live in XOR-swizzled 16-byte
 //   chunks so ldmatrix is conflict-free), double-buffered per warp so the next problem's loads
@@ -25,58 +25,63 @@ namespace {
 // ---------------------------------------------------------------------------------------------
 // temporal (short-sequence) attention
 // ---------------------------------------------------------------------------------------------
-template <int MT>
+// DH = d / 64: a tile is DH swizzled [rows][64] halves (d = 128 is the class default at C = 1280 / 10 heads,
+// src/models/unet_spatio_temporal_condition.py:94)
+template <int MT, int DH>
 struct TemporalCfg {
   static constexpr int kRows = 16 * MT;
-  static constexpr int kTileBytes = kRows * 128;
+  static constexpr int kHalfBytes = kRows * 128;
+  static constexpr int kTileBytes = DH * kHalfBytes;
   static constexpr int kStageBytes = 3 * kTileBytes;
-  static constexpr int kWarps = (MT == 4) ? 4 : 8;
+  static constexpr int kWarps = DH == 1 ? ((MT == 4) ? 4 : 8) : (MT == 1 ? 8 : MT == 2 ? 4 : 2);
   static constexpr int kSmemBytes = kWarps * 2 * kStageBytes;
 };
 
-template <int MT>
+template <int MT, int DH>
 __device__ __forceinline__ void temporal_issue_loads(uint32_t stage_smem, const tvi_bf16* q, const tvi_bf16* k,
                                                      const tvi_bf16* v, int64_t item, int heads, int Tq, int Tk,
                                                      int64_t ldq, int64_t ldk, int64_t ldv, int64_t inner, int lane) {
   constexpr int kRows = 16 * MT;
+  constexpr int kTile = TemporalCfg<MT, DH>::kTileBytes;
   const int64_t seq = item / heads;
   const int head = (int)(item - seq * heads);
   // token t of sequence `seq` is row (seq / inner) * inner * T + t * inner + seq % inner: inner == 1 is the
   // contiguous [nseq, T] layout, inner == S reads the temporal sequences straight out of the [B, T, S] token order
   const int64_t so = seq / inner, si = seq - so * inner;
-  const tvi_bf16* qb = q + (so * inner * Tq + si) * ldq + head * 64;
-  const tvi_bf16* kb = k + (so * inner * Tk + si) * ldk + head * 64;
-  const tvi_bf16* vb = v + (so * inner * Tk + si) * ldv + head * 64;
+  const tvi_bf16* qb = q + (so * inner * Tq + si) * ldq + head * 64 * DH;
+  const tvi_bf16* kb = k + (so * inner * Tk + si) * ldk + head * 64 * DH;
+  const tvi_bf16* vb = v + (so * inner * Tk + si) * ldv + head * 64 * DH;
   ldq *= inner;  // consecutive tokens of a sequence are `inner` rows apart
   ldk *= inner;
   ldv *= inner;
-  const int c = lane & 7;
 #pragma unroll
-  for (int i = 0; i < kRows / 4; ++i) {
-    const int r = (lane >> 3) + 4 * i;
-    const uint32_t off = tile_off(r, c);
+  for (int i = 0; i < kRows * DH / 4; ++i) {
+    const int idx = lane + 32 * i;
+    const int r = idx / (8 * DH), c = idx % (8 * DH);
+    const uint32_t off = (c >> 3) * (kRows * 128) + tile_off(r, c & 7);
     const bool pq = r < Tq, pk = r < Tk;
     // rows past the sequence are zero-filled (src-size 0): padded K rows are masked in the
     // softmax, padded V rows must be finite because they are multiplied by P = 0.
     asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(stage_smem + off),
                  "l"(pq ? qb + r * ldq + c * 8 : qb), "r"(pq ? 16 : 0)
                  : "memory");
-    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(stage_smem + kRows * 128 + off),
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(stage_smem + kTile + off),
                  "l"(pk ? kb + r * ldk + c * 8 : kb), "r"(pk ? 16 : 0)
                  : "memory");
-    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(stage_smem + 2 * kRows * 128 + off),
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(stage_smem + 2 * kTile + off),
                  "l"(pk ? vb + r * ldv + c * 8 : vb), "r"(pk ? 16 : 0)
                  : "memory");
   }
 }
 
-template <int MT>
-__global__ void __launch_bounds__(TemporalCfg<MT>::kWarps * 32)
+template <int MT, int DH>
+__global__ void __launch_bounds__(TemporalCfg<MT, DH>::kWarps * 32)
 attn_temporal_kernel(const tvi_bf16* __restrict__ q, const tvi_bf16* __restrict__ k, const tvi_bf16* __restrict__ v,
                      tvi_bf16* __restrict__ o, float* __restrict__ lse, int64_t nitems, int heads, int Tq, int Tk,
                      int64_t ldq, int64_t ldk, int64_t ldv, int64_t ldo, float scale, int64_t inner) {
-  using Cfg = TemporalCfg<MT>;
+  using Cfg = TemporalCfg<MT, DH>;
   constexpr int kRows = Cfg::kRows;
+  constexpr int kHalf = Cfg::kHalfBytes;
   constexpr int NT = 2 * MT;  // 8-key column tiles of S
   extern __shared__ __align__(128) uint8_t smem_raw[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -90,21 +95,21 @@ attn_temporal_kernel(const tvi_bf16* __restrict__ q, const tvi_bf16* __restrict_
 
   int64_t item = gw;
   int stage = 0;
-  if (item < nitems) temporal_issue_loads<MT>(warp_smem, q, k, v, item, heads, Tq, Tk, ldq, ldk, ldv, inner, lane);
+  if (item < nitems) temporal_issue_loads<MT, DH>(warp_smem, q, k, v, item, heads, Tq, Tk, ldq, ldk, ldv, inner, lane);
   cp_async_commit();
 
   for (; item < nitems; item += stride, stage ^= 1) {
     const int64_t next = item + stride;
     if (next < nitems)
-      temporal_issue_loads<MT>(warp_smem + (stage ^ 1) * Cfg::kStageBytes, q, k, v, next, heads, Tq, Tk, ldq, ldk, ldv,
-                               inner, lane);
+      temporal_issue_loads<MT, DH>(warp_smem + (stage ^ 1) * Cfg::kStageBytes, q, k, v, next, heads, Tq, Tk, ldq, ldk, ldv,
+                                   inner, lane);
     cp_async_commit();
     cp_async_wait<1>();
     __syncwarp();
 
     const uint32_t sQ = warp_smem + stage * Cfg::kStageBytes;
-    const uint32_t sK = sQ + kRows * 128;
-    const uint32_t sV = sK + kRows * 128;
+    const uint32_t sK = sQ + Cfg::kTileBytes;
+    const uint32_t sV = sK + Cfg::kTileBytes;
     uint8_t* pQ = warp_ptr + stage * Cfg::kStageBytes;
     const int64_t seq = item / heads;
     const int head = (int)(item - seq * heads);
@@ -119,13 +124,15 @@ attn_temporal_kernel(const tvi_bf16* __restrict__ q, const tvi_bf16* __restrict_
 #pragma unroll
       for (int nt = 0; nt < NT; ++nt) s[nt][0] = s[nt][1] = s[nt][2] = s[nt][3] = 0.f;
 #pragma unroll
-      for (int ks = 0; ks < 4; ++ks) {
+      for (int ks = 0; ks < 4 * DH; ++ks) {
         uint32_t a[4];
-        ldsm_x4(sQ + tile_off(mt * 16 + (lane & 7) + ((lane >> 3) & 1) * 8, 2 * ks + (lane >> 4)), a[0], a[1], a[2], a[3]);
+        ldsm_x4(sQ + (ks >> 2) * kHalf + tile_off(mt * 16 + (lane & 7) + ((lane >> 3) & 1) * 8, 2 * (ks & 3) + (lane >> 4)),
+                a[0], a[1], a[2], a[3]);
 #pragma unroll
         for (int np = 0; np < MT; ++np) {
           uint32_t b0, b1, b2, b3;
-          ldsm_x4(sK + tile_off(np * 16 + (lane & 7) + (lane >> 4) * 8, 2 * ks + ((lane >> 3) & 1)), b0, b1, b2, b3);
+          ldsm_x4(sK + (ks >> 2) * kHalf + tile_off(np * 16 + (lane & 7) + (lane >> 4) * 8, 2 * (ks & 3) + ((lane >> 3) & 1)),
+                  b0, b1, b2, b3);
           mma_bf16_16816(s[2 * np], a, b0, b1);
           mma_bf16_16816(s[2 * np + 1], a, b2, b3);
         }
@@ -161,17 +168,18 @@ attn_temporal_kernel(const tvi_bf16* __restrict__ q, const tvi_bf16* __restrict_
       l1 += __shfl_xor_sync(0xffffffffu, l1, 1);
       l1 += __shfl_xor_sync(0xffffffffu, l1, 2);
       // ---- O = P V ------------------------------------------------------------------
-      float acc[8][4];
+      float acc[8 * DH][4];
 #pragma unroll
-      for (int nt = 0; nt < 8; ++nt) acc[nt][0] = acc[nt][1] = acc[nt][2] = acc[nt][3] = 0.f;
+      for (int nt = 0; nt < 8 * DH; ++nt) acc[nt][0] = acc[nt][1] = acc[nt][2] = acc[nt][3] = 0.f;
 #pragma unroll
       for (int kk = 0; kk < MT; ++kk) {
         if (kk * 16 >= Tk) break;
         const uint32_t a[4] = {p[2 * kk][0], p[2 * kk][1], p[2 * kk + 1][0], p[2 * kk + 1][1]};
 #pragma unroll
-        for (int nc = 0; nc < 8; nc += 2) {
+        for (int nc = 0; nc < 8 * DH; nc += 2) {
           uint32_t b0, b1, b2, b3;
-          ldsm_x4_t(sV + tile_off(kk * 16 + (lane & 7) + ((lane >> 3) & 1) * 8, nc + (lane >> 4)), b0, b1, b2, b3);
+          ldsm_x4_t(sV + (nc >> 3) * kHalf + tile_off(kk * 16 + (lane & 7) + ((lane >> 3) & 1) * 8, (nc & 7) + (lane >> 4)),
+                    b0, b1, b2, b3);
           mma_bf16_16816(acc[nc], a, b0, b1);
           mma_bf16_16816(acc[nc + 1], a, b2, b3);
         }
@@ -182,9 +190,10 @@ attn_temporal_kernel(const tvi_bf16* __restrict__ q, const tvi_bf16* __restrict_
       __syncwarp();
       const int r0 = mt * 16 + g, r1 = r0 + 8;
 #pragma unroll
-      for (int nt = 0; nt < 8; ++nt) {
-        *reinterpret_cast<uint32_t*>(pQ + tile_off(r0, nt) + qd * 4) = pack_bf16x2(acc[nt][0] * inv0, acc[nt][1] * inv0);
-        *reinterpret_cast<uint32_t*>(pQ + tile_off(r1, nt) + qd * 4) = pack_bf16x2(acc[nt][2] * inv1, acc[nt][3] * inv1);
+      for (int nt = 0; nt < 8 * DH; ++nt) {
+        uint8_t* ph = pQ + (nt >> 3) * kHalf;
+        *reinterpret_cast<uint32_t*>(ph + tile_off(r0, nt & 7) + qd * 4) = pack_bf16x2(acc[nt][0] * inv0, acc[nt][1] * inv0);
+        *reinterpret_cast<uint32_t*>(ph + tile_off(r1, nt & 7) + qd * 4) = pack_bf16x2(acc[nt][2] * inv1, acc[nt][3] * inv1);
       }
       if (lse != nullptr && qd == 0) {
         // natural-log-sum-exp of the scaled logits
@@ -194,13 +203,14 @@ attn_temporal_kernel(const tvi_bf16* __restrict__ q, const tvi_bf16* __restrict_
     }
     __syncwarp();
     // ---- coalesced 128-bit stores of the O tile --------------------------------------
-    tvi_bf16* ob = o + row0 * ldo + head * 64;
+    tvi_bf16* ob = o + row0 * ldo + head * 64 * DH;
 #pragma unroll
-    for (int i = 0; i < kRows / 4; ++i) {
-      const int r = (lane >> 3) + 4 * i;
+    for (int i = 0; i < kRows * DH / 4; ++i) {
+      const int idx = lane + 32 * i;
+      const int r = idx / (8 * DH), c = idx % (8 * DH);
       if (r < Tq) {
-        const uint4 val = *reinterpret_cast<const uint4*>(pQ + tile_off(r, lane & 7));
-        *reinterpret_cast<uint4*>(ob + r * inner * ldo + (lane & 7) * 8) = val;
+        const uint4 val = *reinterpret_cast<const uint4*>(pQ + (c >> 3) * kHalf + tile_off(r, c & 7));
+        *reinterpret_cast<uint4*>(ob + r * inner * ldo + c * 8) = val;
       }
     }
     __syncwarp();  // the stage may be refilled by the next iteration's cp.async
@@ -208,22 +218,22 @@ attn_temporal_kernel(const tvi_bf16* __restrict__ q, const tvi_bf16* __restrict_
   cp_async_wait<0>();
 }
 
-template <int MT>
+template <int MT, int DH>
 int launch_temporal(const tvi_bf16* q, const tvi_bf16* k, const tvi_bf16* v, tvi_bf16* o, float* lse, int64_t nseq,
                     int heads, int Tq, int Tk, int64_t ldq, int64_t ldk, int64_t ldv, int64_t ldo, float scale,
                     int64_t inner, cudaStream_t st) {
-  using Cfg = TemporalCfg<MT>;
+  using Cfg = TemporalCfg<MT, DH>;
   static bool configured = false;
   if (!configured) {
-    TVI_CUDA_OK(cudaFuncSetAttribute(attn_temporal_kernel<MT>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes));
+    TVI_CUDA_OK(cudaFuncSetAttribute(attn_temporal_kernel<MT, DH>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes));
     configured = true;
   }
   const int64_t nitems = nseq * heads;
-  const int per_sm = (MT == 1) ? 2 : 1;
+  const int per_sm = (MT == 1 && DH == 1) ? 2 : 1;
   int64_t grid = (nitems + Cfg::kWarps - 1) / Cfg::kWarps;
   const int64_t cap = (int64_t)num_sms() * per_sm;
   if (grid > cap) grid = cap;
-  attn_temporal_kernel<MT><<<(unsigned)grid, Cfg::kWarps * 32, Cfg::kSmemBytes, st>>>(q, k, v, o, lse, nitems, heads, Tq, Tk,
+  attn_temporal_kernel<MT, DH><<<(unsigned)grid, Cfg::kWarps * 32, Cfg::kSmemBytes, st>>>(q, k, v, o, lse, nitems, heads, Tq, Tk,
                                                                                      ldq, ldk, ldv, ldo, scale, inner);
   TVI_LAUNCH_OK("attn_temporal_kernel");
   return TVI_OK;
@@ -423,17 +433,21 @@ int tvi_attn_temporal_fwd_interleaved(const tvi_bf16* q, const tvi_bf16* k, cons
   TVI_CHECK_ARG(nseq >= 0 && heads >= 0, "tvi_attn_temporal_fwd_interleaved: negative size");
   if (nseq == 0 || heads == 0) return TVI_OK;
   TVI_CHECK_ARG(q && k && v && o, "tvi_attn_temporal_fwd_interleaved: null pointer");
-  if (d != 64) return fail(TVI_ERR_UNSUPPORTED, "tvi_attn_temporal_fwd_interleaved: head dim %d (only 64 is built)", d);
+  if (d != 64 && d != 128) return fail(TVI_ERR_UNSUPPORTED, "tvi_attn_temporal_fwd_interleaved: head dim %d (64 and 128 are built)", d);
   TVI_CHECK_ARG(Tq >= 1 && Tq <= 64 && Tk >= 1 && Tk <= 64, "tvi_attn_temporal_fwd_interleaved: Tq=%d Tk=%d outside [1,64]", Tq, Tk);
   TVI_CHECK_ARG(ldq % 8 == 0 && ldk % 8 == 0 && ldv % 8 == 0 && ldo % 8 == 0, "tvi_attn_temporal_fwd_interleaved: row strides must be multiples of 8 elements");
-  TVI_CHECK_ARG(ldq >= heads * 64 && ldk >= heads * 64 && ldv >= heads * 64 && ldo >= heads * 64, "tvi_attn_temporal_fwd_interleaved: row stride smaller than heads*d");
+  TVI_CHECK_ARG(ldq >= heads * d && ldk >= heads * d && ldv >= heads * d && ldo >= heads * d, "tvi_attn_temporal_fwd_interleaved: row stride smaller than heads*d");
   TVI_CHECK_ARG(((uintptr_t)q | (uintptr_t)k | (uintptr_t)v | (uintptr_t)o) % 16 == 0, "tvi_attn_temporal_fwd_interleaved: pointers must be 16-byte aligned");
   TVI_CHECK_ARG(seq_inner >= 1 && nseq % seq_inner == 0, "tvi_attn_temporal_fwd_interleaved: nseq must be a multiple of seq_inner");
   cudaStream_t st = (cudaStream_t)stream;
   const int T = Tq > Tk ? Tq : Tk;
-  if (T <= 16) return launch_temporal<1>(q, k, v, o, lse, nseq, heads, Tq, Tk, ldq, ldk, ldv, ldo, scale, seq_inner, st);
-  if (T <= 32) return launch_temporal<2>(q, k, v, o, lse, nseq, heads, Tq, Tk, ldq, ldk, ldv, ldo, scale, seq_inner, st);
-  return launch_temporal<4>(q, k, v, o, lse, nseq, heads, Tq, Tk, ldq, ldk, ldv, ldo, scale, seq_inner, st);
+#define TVI_TEMPORAL(MT)                                                                                                  \
+  (d == 64 ? launch_temporal<MT, 1>(q, k, v, o, lse, nseq, heads, Tq, Tk, ldq, ldk, ldv, ldo, scale, seq_inner, st)       \
+           : launch_temporal<MT, 2>(q, k, v, o, lse, nseq, heads, Tq, Tk, ldq, ldk, ldv, ldo, scale, seq_inner, st))
+  if (T <= 16) return TVI_TEMPORAL(1);
+  if (T <= 32) return TVI_TEMPORAL(2);
+  return TVI_TEMPORAL(4);
+#undef TVI_TEMPORAL
 }
 
 int tvi_attn_temporal_fwd(const tvi_bf16* q, const tvi_bf16* k, const tvi_bf16* v, tvi_bf16* o, float* lse, int64_t nseq,

@@ -89,17 +89,19 @@ class BasicTransformerBlock(nn.Module):
     (src/models/attention.py:90-232 with norm_type="layer_norm", GEGLU feed-forward, attention_bias=False):
     norm1, attn1, norm2, attn2, norm3, ff.  The eager forward is the reference's order of operations."""
 
-    def __init__(self, dim: int, heads: int, cross_attention_dim: Optional[int] = None, processor=None):
+    def __init__(self, dim: int, heads: int, cross_attention_dim: Optional[int] = None, processor=None,
+                 attention_head_dim: Optional[int] = None):
         super().__init__()
+        dh = attention_head_dim if attention_head_dim is not None else (dim // heads if dim % heads == 0 and dim // heads in (64, 128) else 64)
         self.use_layer_norm = True
         self.use_ada_layer_norm = self.use_ada_layer_norm_zero = self.use_ada_layer_norm_single = False
         self.only_cross_attention = False
         self.pos_embed = None
         self._chunk_size = None
         self.norm1 = nn.LayerNorm(dim)
-        self.attn1 = Attention(dim, None, heads=heads, processor=processor)
+        self.attn1 = Attention(dim, None, heads=heads, dim_head=dh, processor=processor)
         self.norm2 = nn.LayerNorm(dim)
-        self.attn2 = Attention(dim, cross_attention_dim, heads=heads, processor=processor)
+        self.attn2 = Attention(dim, cross_attention_dim, heads=heads, dim_head=dh, processor=processor)
         self.norm3 = nn.LayerNorm(dim)
         self.ff = FeedForward(dim)
 
@@ -112,16 +114,19 @@ class BasicTransformerBlock(nn.Module):
 class TemporalBasicTransformerBlock(nn.Module):
     """Attribute layout of the reference's temporal block (src/models/attention.py:350-478)."""
 
-    def __init__(self, dim: int, time_mix_inner_dim: int, heads: int, cross_attention_dim: Optional[int] = None, processor=None):
+    def __init__(self, dim: int, time_mix_inner_dim: int, heads: int, cross_attention_dim: Optional[int] = None, processor=None,
+                 attention_head_dim: Optional[int] = None):
         super().__init__()
+        t = time_mix_inner_dim
+        dh = attention_head_dim if attention_head_dim is not None else (t // heads if t % heads == 0 and t // heads in (64, 128) else 64)
         self.is_res = dim == time_mix_inner_dim
         self._chunk_size = None
         self.norm_in = nn.LayerNorm(dim)
         self.ff_in = FeedForward(dim, dim_out=time_mix_inner_dim)
         self.norm1 = nn.LayerNorm(time_mix_inner_dim)
-        self.attn1 = Attention(time_mix_inner_dim, None, heads=heads, processor=processor)
+        self.attn1 = Attention(time_mix_inner_dim, None, heads=heads, dim_head=dh, processor=processor)
         self.norm2 = nn.LayerNorm(time_mix_inner_dim)
-        self.attn2 = Attention(time_mix_inner_dim, cross_attention_dim, heads=heads, processor=processor)
+        self.attn2 = Attention(time_mix_inner_dim, cross_attention_dim, heads=heads, dim_head=dh, processor=processor)
         self.norm3 = nn.LayerNorm(time_mix_inner_dim)
         self.ff = FeedForward(time_mix_inner_dim)
 
@@ -199,17 +204,20 @@ class TransformerSpatioTemporalModel(nn.Module):
     def __init__(self, num_attention_heads: int = 16, attention_head_dim: int = 88, in_channels: int = 320,
                  out_channels: Optional[int] = None, num_layers: int = 1, cross_attention_dim: Optional[int] = None):
         super().__init__()
-        if attention_head_dim != 64:
-            raise ValueError("the mirror builds d = 64 heads (every SVD level)")
+        if attention_head_dim not in (64, 128):
+            raise ValueError("libtvi builds d = 64 (every level of the SVD checkpoint) and d = 128 heads (the class default "
+                             "num_attention_heads=(5, 10, 10, 20) at C = 1280)")
         inner_dim = num_attention_heads * attention_head_dim
         self.num_attention_heads, self.attention_head_dim = num_attention_heads, attention_head_dim
         self.inner_dim, self.in_channels = inner_dim, in_channels
         self.norm = nn.GroupNorm(num_groups=32, num_channels=in_channels, eps=1e-6)
         self.proj_in = nn.Linear(in_channels, inner_dim)
         self.transformer_blocks = nn.ModuleList(
-            [BasicTransformerBlock(inner_dim, num_attention_heads, cross_attention_dim) for _ in range(num_layers)])
+            [BasicTransformerBlock(inner_dim, num_attention_heads, cross_attention_dim, attention_head_dim=attention_head_dim)
+             for _ in range(num_layers)])
         self.temporal_transformer_blocks = nn.ModuleList(
-            [TemporalBasicTransformerBlock(inner_dim, inner_dim, num_attention_heads, cross_attention_dim) for _ in range(num_layers)])
+            [TemporalBasicTransformerBlock(inner_dim, inner_dim, num_attention_heads, cross_attention_dim,
+                                           attention_head_dim=attention_head_dim) for _ in range(num_layers)])
         self.time_pos_embed = TimestepEmbedding(in_channels, in_channels * 4, out_dim=in_channels)
         self.time_proj = Timesteps(in_channels, True, 0)
         self.time_mixer = AlphaBlender(alpha=0.5, merge_strategy="learned_with_images")

@@ -236,7 +236,7 @@ def cfg_train_block(steps):
     ops.EVENT_HOOK = None
     emit({"config": "train_fwd_bwd_L0_block_pair", "clips_per_gpu": B, "T": T, "resolution": "576x1024",
           "trainable": "temporal block (spatial block frozen, gradient flows through it to the input)",
-          "trainable_params": sum(p.numel() for p in tb.parameters()), "ms_fwd": ms_f, "ms_fwd_bwd": ms_fb,
+          "trainable_params": n_trainable, "ms_fwd": ms_f, "ms_fwd_bwd": ms_fb,
           "clip_frames_per_s_fwd_bwd": B * T / (ms_fb * 1e-3), "peak_mem_gb": torch.cuda.max_memory_allocated() / 2 ** 30,
           "kernels": kt.summary(2)})
 
@@ -609,12 +609,13 @@ def _train_step(steps=3):
     fwd_bwd()
     ops.EVENT_HOOK = None
     ks = kt.summary(1)
+    n_trainable = sum(p.numel() for p in tb.parameters())
     del sb, tb, x, xg, dy
     torch.cuda.empty_cache()
     module = _train_step_module(B, T, C, heads, h, w, g, steps)
     return {"config": "train_fwd_bwd_L0_block_pair_576x1024", "clips_per_gpu": B, "frames": T, "cfg_batch": 1, "module": module,
             "trainable": "temporal block (spatial block frozen, gradient flows through it to the input)",
-            "trainable_params": sum(p.numel() for p in tb.parameters()), "ms_fwd": ms_f, "ms_fwd_bwd": ms_fb,
+            "trainable_params": n_trainable, "ms_fwd": ms_f, "ms_fwd_bwd": ms_fb,
             "clip_frames_per_s_fwd_bwd": B * T / (ms_fb * 1e-3),
             "ms_spatial_attention_bwd": ks.get("attn_spatial_bwd", {}).get("ms_per_step"),
             "ms_by_entry_point": {k: round(v["ms_per_step"], 4) for k, v in ks.items()}}
