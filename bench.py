@@ -481,7 +481,10 @@ def main():
         ys = [None, None]  # results whose D2H copy may still be in flight (kept alive; no record_stream, so the
         #                    allocator's reuse pattern is the same every step and settles during the warm-up)
 
+        step_done = []  # compute-stream events after every e2e step: (last - first) / (K - 1) is the steady-state step
+
         def e2e_steps(n):
+            step_done.clear()
             for k in range(n):
                 b = k & 1
                 with torch.cuda.stream(s_in):
@@ -497,6 +500,8 @@ def main():
                 ys[b] = None
                 ys[b] = y = wl.step(dbuf[b][0], dbuf[b][1], wl.expand_time_context(dbuf[b][2]))
                 ev_free[b].record(cur)
+                step_done.append(torch.cuda.Event(enable_timing=True))
+                step_done[-1].record(cur)
                 s_out.wait_stream(cur)
                 with torch.cuda.stream(s_out):
                     out_pins[b].copy_(y, non_blocking=True)
@@ -514,6 +519,7 @@ def main():
         f1.record()
         barrier()
         ms_e2e = f0.elapsed_time(f1)
+        ms_e2e_steady = step_done[0].elapsed_time(step_done[-1]) / max(1, len(step_done) - 1)
         gc.enable()
         clocks = sampler.stop()  # samples cover both timed regions
 
@@ -567,6 +573,10 @@ def main():
                     # memory / PCIe path sets for this N; e2e within ~15 % of it is copy-bound, not a software stall
                     "host_ceiling_ms": ms_copy / args.steps,
                     "kernel_ms_per_step": ms_total / args.steps,
+                    # the timed region is bracketed by synchronisations, so it also holds the pipeline's fill (the first
+                    # step's H2D, nothing to overlap it with) and drain (the last step's D2H): ~2 copies / K per step.
+                    # steady_ms_per_step is the spacing of consecutive steps' completions inside the same region (rank 0).
+                    "steady_ms_per_step": ms_e2e_steady,
                     "rank_cores": cores_bound,
                     "note": "temporal context travels as [B, Ltm, 1024] and is broadcast on the device "
                             "(reference src/models/transformer_temporal.py:279-297)"},

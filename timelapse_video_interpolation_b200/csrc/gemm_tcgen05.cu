@@ -562,13 +562,28 @@ int launch_gemm(const char* name, const tvi_bf16* A, const tvi_bf16* B, const tv
 int wgrad_splits(int64_t M, int N, int K) {
   const int64_t tiles = ((N + kBM - 1) / kBM) * (int64_t)((K + pick_bn(K, 64) - 1) / pick_bn(K, 64));
   const int64_t kblocks = (M + kBK - 1) / kBK;
-  int64_t s = (num_sms() + tiles - 1) / tiles;
-  if (s > kblocks) s = kblocks;
-  if (s < 1) s = 1;
+  const int64_t sms = num_sms();
+  // The persistent grid works through tiles * splits equal items in rounds of `sms`: pick the split count whose last
+  // round is fullest.  (ceil(sms / tiles) alone lands just past a round boundary for every SVD shape — 40 tiles x 4,
+  // 16 x 10, 6 x 25, 15 x 10 items on 148 SMs — and ran a second, almost empty round: ~52 % of the machine.)
+  // Up to ~4 rounds are considered; a split keeps at least 16 k-blocks so the fp32 partial tile stays a small
+  // fraction of what it reads.
+  int64_t smax = (4 * sms + tiles - 1) / tiles;
+  if (smax > kblocks / 16) smax = kblocks / 16;
+  if (smax < 1) smax = 1;
+  int64_t best = 1;
+  double best_eff = 0.0;
+  for (int64_t s = 1; s <= smax; ++s) {
+    const int64_t items = tiles * s, rounds = (items + sms - 1) / sms;
+    const double eff = (double)items / (double)(rounds * sms);
+    if (eff > best_eff + 0.01) {  // ties go to the smaller workspace
+      best_eff = eff;
+      best = s;
+    }
+  }
   // every split must own at least one k-block
-  const int64_t per = (kblocks + s - 1) / s;
-  s = (kblocks + per - 1) / per;
-  return (int)s;
+  const int64_t per = (kblocks + best - 1) / best;
+  return (int)((kblocks + per - 1) / per);
 }
 
 }  // namespace
