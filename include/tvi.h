@@ -248,6 +248,19 @@ int tvi_attn_fewkeys_fwd_interleaved(const tvi_bf16* q, const tvi_bf16* k, const
                                      int64_t ldk, int64_t ldv, int64_t ldo, float scale, int Tq, const float* bias,
                                      float* stats, void* stats_ws, void* stream);
 
+/* No-allocation variant of tvi_attn_fewkeys_fwd with statistics.  It has NO counterpart in the reference: it was added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight
+ * serving loops, harnesses that forbid it).  Same arguments and results as tvi_attn_fewkeys_fwd minus `stats_ws`: the
+ * Tq*L fp64 accumulators live in a static device array inside the library (TVI_FEWKEYS_STATIC_MAX_STATS entries =
+ * 32 KB per GPU that loads the library, held until exit).  Tq*L beyond that limit -> TVI_ERR_INVALID.  The call
+ * allocates nothing (no cudaMalloc / cudaFree / allocating library routine); the caller passes inputs and outputs.
+ * All calls on a device share the array, which keeps the last call's contents: the entries a call uses are cleared
+ * on `stream` first, and calls that OVERLAP on the GPU (different streams) race on it — serialise them. */
+#define TVI_FEWKEYS_STATIC_MAX_STATS 4096
+int tvi_attn_fewkeys_fwd_static(const tvi_bf16* q, const tvi_bf16* k, const tvi_bf16* v, tvi_bf16* o, int64_t nrows,
+                                int64_t rows_per_group, int heads, int L, int d, int64_t ldq, int64_t ldk, int64_t ldv,
+                                int64_t ldo, float scale, int Tq, const float* bias, float* stats, void* stream);
+
 /* ---------------------------------------------------------------------------------------------
  * A3a  spatial self-attention core (flash-style, tcgen05 QK^T and PV, online fp32 softmax):
  * batch independent sequences of S query rows and Skv key rows, no mask, non-causal.

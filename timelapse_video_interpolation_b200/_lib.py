@@ -65,6 +65,8 @@ SIGNATURES = {
                                                  _i64, _i64, _i64, _i64, _f32, _ptr]),
     "tvi_attn_fewkeys_fwd": (_i32, [_ptr, _ptr, _ptr, _ptr, _i64, _i64, _i32, _i32, _i32,
                                     _i64, _i64, _i64, _i64, _f32, _i32, _ptr, _ptr, _ptr, _ptr]),
+    "tvi_attn_fewkeys_fwd_static": (_i32, [_ptr, _ptr, _ptr, _ptr, _i64, _i64, _i32, _i32, _i32,
+                                           _i64, _i64, _i64, _i64, _f32, _i32, _ptr, _ptr, _ptr]),
     "tvi_attn_fewkeys_fwd_interleaved": (_i32, [_ptr, _ptr, _ptr, _ptr, _i64, _i64, _i32, _i32, _i32, _i64,
                                                 _i64, _i64, _i64, _i64, _f32, _i32, _ptr, _ptr, _ptr, _ptr]),
     "tvi_attn_spatial_fwd": (_i32, [_ptr, _ptr, _ptr, _ptr, _ptr, _i32, _i32, _i32, _i32, _i32,
@@ -80,6 +82,7 @@ SIGNATURES = {
 }
 SPATIAL_AUTO, SPATIAL_MMA_SYNC, SPATIAL_TCGEN05 = 0, 1, 2
 EPILOGUE_NONE, EPILOGUE_GEGLU = 0, 1
+FEWKEYS_STATIC_MAX_STATS = 4096  # TVI_FEWKEYS_STATIC_MAX_STATS of include/tvi.h
 PRED_EPSILON, PRED_V = 0, 1
 
 _lib = None

@@ -508,4 +508,65 @@ int tvi_attn_fewkeys_fwd_interleaved(const tvi_bf16* q, const tvi_bf16* k, const
   return TVI_OK;
 }
 
+// ---------------------------------------------------------------------------------------------
+// No-allocation variant of the few-keys core with statistics (no counterpart in the reference; added
+// for callers that cannot call cudaMalloc: CUDA graph capture, tight serving loops).
+// The Tq*L fp64 accumulators live in a file-scope device array instead of a caller-provided workspace.  In host code
+// the array's NAME is only a host-side stand-in, never a device address: the address is taken once per device with
+// cudaGetSymbolAddress (that device current) and handed to the unchanged entry point above as `stats_ws`.
+// Every call on a device shares the array and it keeps the last call's contents: the call clears the Tq*L entries it
+// uses (cudaMemsetAsync on `stream`, as the entry point above does) — calls that overlap on the GPU (different
+// streams) race on it.  32 KB per GPU that loads the library, held until exit.
+// ---------------------------------------------------------------------------------------------
+}  // extern "C"
+
+static __device__ __align__(256) double g_tvi_fewkeys_stats_scratch[TVI_FEWKEYS_STATIC_MAX_STATS];
+
+namespace tvi {
+namespace {
+constexpr int kMaxDevices = 64;
+// device address of g_tvi_fewkeys_stats_scratch on the CURRENT device (resolved once per device); nullptr + *rc on error
+double* fewkeys_static_scratch(int* rc) {
+  static double* ptrs[kMaxDevices] = {nullptr};
+  *rc = TVI_OK;
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess || dev < 0 || dev >= kMaxDevices) {
+    *rc = fail(TVI_ERR_CUDA, "tvi_attn_fewkeys_fwd_static: cudaGetDevice failed or device %d outside [0, %d)", dev, kMaxDevices);
+    return nullptr;
+  }
+  double* p = __atomic_load_n(&ptrs[dev], __ATOMIC_ACQUIRE);
+  if (p == nullptr) {  // racing first calls resolve the same address twice: harmless
+    e = cudaGetSymbolAddress((void**)&p, g_tvi_fewkeys_stats_scratch);
+    if (e != cudaSuccess || p == nullptr) {
+      *rc = fail(TVI_ERR_CUDA, "tvi_attn_fewkeys_fwd_static: cudaGetSymbolAddress failed: %s", cudaGetErrorString(e));
+      return nullptr;
+    }
+    __atomic_store_n(&ptrs[dev], p, __ATOMIC_RELEASE);
+  }
+  return p;
+}
+}  // namespace
+}  // namespace tvi
+
+extern "C" {
+
+int tvi_attn_fewkeys_fwd_static(const tvi_bf16* q, const tvi_bf16* k, const tvi_bf16* v, tvi_bf16* o, int64_t nrows,
+                                int64_t rows_per_group, int heads, int L, int d, int64_t ldq, int64_t ldk, int64_t ldv,
+                                int64_t ldo, float scale, int Tq, const float* bias, float* stats, void* stream) {
+  using namespace tvi;
+  TVI_CHECK_ARG(Tq >= 1 && L >= 1 && L <= 8, "tvi_attn_fewkeys_fwd_static: Tq=%d must be >= 1 and L=%d in [1, 8]", Tq, L);
+  TVI_CHECK_ARG((int64_t)Tq * L <= TVI_FEWKEYS_STATIC_MAX_STATS,
+                "tvi_attn_fewkeys_fwd_static: Tq*L = %lld statistics exceed the static scratch of %d entries "
+                "(use tvi_attn_fewkeys_fwd with a caller-provided stats_ws)", (long long)Tq * L, TVI_FEWKEYS_STATIC_MAX_STATS);
+  double* ws = nullptr;
+  if (stats != nullptr) {
+    int rc = TVI_OK;
+    ws = fewkeys_static_scratch(&rc);
+    if (ws == nullptr) return rc;
+  }
+  return tvi_attn_fewkeys_fwd_interleaved(q, k, v, o, nrows, rows_per_group, heads, L, d, 1, ldq, ldk, ldv, ldo, scale, Tq, bias,
+                                          stats, ws, stream);
+}
+
 }  // extern "C"
