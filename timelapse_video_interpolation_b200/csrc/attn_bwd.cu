@@ -598,6 +598,75 @@ __global__ void __launch_bounds__(256) attn_fewkeys_bwd_kernel(const FkParams p)
     for (int j = 0; j < 8; ++j) dk[l][j] = dv[l][j] = 0.f;
   }
 
+  if constexpr (LT == 2) {
+    // Two keys (L == 2): P = [w, 1 - w], w = sigma(z), z = scale * q . (k0 - k1) + (b0 - b1).  With g = dO . (v0 - v1):
+    // dS0 = -dS1 = w (1 - w) g, so dQ = scale dS0 (k0 - k1), dK0 = -dK1 = scale sum dS0 q: two dot products and 24
+    // accumulators per row instead of four and 32.
+    float kd[8], vd[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      kd[j] = kf[0][j] - kf[1][j];
+      vd[j] = vf[0][j] - vf[1][j];
+    }
+    constexpr int kU = 4;  // 4 rows x (Q, dO) = 128 bytes in flight per thread
+    for (int it0 = 0; it0 < kFewBwdRowsPerThread; it0 += kU) {
+      if (rlo + (int64_t)it0 * RY >= rhi) break;  // block-uniform
+      uint4 qv[kU], gv[kU];
+#pragma unroll
+      for (int u = 0; u < kU; ++u) {
+        const int64_t rr = rlo + (int64_t)(it0 + u) * RY + ry;
+        const int64_t r = rr < rhi ? rr : rlo;
+        qv[u] = __ldg(reinterpret_cast<const uint4*>(p.q + r * p.ldq + cx * 8));
+        gv[u] = __ldg(reinterpret_cast<const uint4*>(p.dout + r * p.lddo + cx * 8));
+      }
+#pragma unroll
+      for (int u = 0; u < kU; ++u) {
+        if (rlo + (int64_t)(it0 + u) * RY >= rhi) break;  // block-uniform
+        const int64_t rr = rlo + (int64_t)(it0 + u) * RY + ry;
+        const bool act = rr < rhi;
+        const int64_t r = act ? rr : rlo;
+        float qf[8], gof[8];
+        unpack8b(qv[u], qf);
+        unpack8b(gv[u], gof);
+        float z = 0.f, g = 0.f;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          z = fmaf(qf[j], kd[j], z);
+          g = fmaf(gof[j], vd[j], g);
+        }
+#pragma unroll
+        for (int off = LPH / 2; off > 0; off >>= 1) {
+          z += __shfl_xor_sync(0xffffffffu, z, off);
+          g += __shfl_xor_sync(0xffffffffu, g, off);
+        }
+        z *= p.scale;
+        if (p.bias != nullptr) {
+          const int t = (int)(r % p.Tq);
+          z += __ldg(p.bias + t * 2) - __ldg(p.bias + t * 2 + 1);
+        }
+        float w = __fdividef(1.f, 1.f + __expf(-z));
+        float w1 = 1.f - w;
+        if (!act) w = w1 = 0.f;  // inactive rows contribute nothing
+        const float ds = w * w1 * g * p.scale;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          dk[0][j] = fmaf(ds, qf[j], dk[0][j]);
+          dv[0][j] = fmaf(w, gof[j], dv[0][j]);
+          dv[1][j] = fmaf(w1, gof[j], dv[1][j]);
+        }
+        if (act && p.dq != nullptr) {
+          uint4 o;
+          o.x = pack_bf16x2(ds * kd[0], ds * kd[1]);
+          o.y = pack_bf16x2(ds * kd[2], ds * kd[3]);
+          o.z = pack_bf16x2(ds * kd[4], ds * kd[5]);
+          o.w = pack_bf16x2(ds * kd[6], ds * kd[7]);
+          *reinterpret_cast<uint4*>(p.dq + r * p.lddq + cx * 8) = o;
+        }
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) dk[1][j] = -dk[0][j];
+  } else {
   // the Q / dO chunks of kUnroll rows are requested before the first of them is used (memory-level parallelism: the
   // arithmetic of a row is a dependent chain of ~150 instructions)
   constexpr int kUnroll = 2;
@@ -687,6 +756,8 @@ __global__ void __launch_bounds__(256) attn_fewkeys_bwd_kernel(const FkParams p)
     }
     }
   }
+
+  }  // LT != 2
 
   // ---- fixed-order reduction over the CTA's row lanes ---------------------------------------------
   for (int t = 0; t < RY; ++t) {

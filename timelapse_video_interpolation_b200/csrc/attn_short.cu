@@ -300,6 +300,59 @@ attn_fewkeys_kernel(const tvi_bf16* __restrict__ q, const tvi_bf16* __restrict__
     return;
   }
 
+  if constexpr (LT == 2 && !STATS) {
+    // Two keys: softmax([l0, l1]) = [sigma(z), 1 - sigma(z)] with z = l0 - l1 = scale * q . (k0 - k1) + (b0 - b1), and
+    // O = v1 + sigma(z) * (v0 - v1): ONE dot product and one shuffle chain per row instead of two, no max / sum.
+    float kd[8], vd[8], v1f[8];
+    {
+      float a[8], b[8];
+      unpack8(kr[0], a);
+      unpack8(kr[1], b);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) kd[j] = (a[j] - b[j]) * (scale * 1.4426950408889634f);   // z in log2 units
+      unpack8(vr[0], a);
+      unpack8(vr[1], v1f);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) vd[j] = a[j] - v1f[j];
+    }
+    constexpr int kU = 4;
+    for (int it0 = 0; it0 < kFewRowsPerThread; it0 += kU) {
+      if (rlo + (int64_t)it0 * RY >= rhi) break;  // block-uniform
+      uint4 qv[kU];
+#pragma unroll
+      for (int u = 0; u < kU; ++u) {
+        const int64_t rr = rlo + (int64_t)(it0 + u) * RY + ry;
+        qv[u] = __ldg(reinterpret_cast<const uint4*>(q + phys(rr < rhi ? rr : rlo) * ldq + cx * 8));
+      }
+#pragma unroll
+      for (int u = 0; u < kU; ++u) {
+        if (rlo + (int64_t)(it0 + u) * RY >= rhi) break;  // block-uniform: every lane reaches every shuffle
+        const int64_t rr = rlo + (int64_t)(it0 + u) * RY + ry;
+        const bool act = rr < rhi;
+        const int64_t r = act ? rr : rlo;
+        float qf[8];
+        unpack8(qv[u], qf);
+        float z = 0.f;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) z = fmaf(qf[j], kd[j], z);
+#pragma unroll
+        for (int off = LPH / 2; off > 0; off >>= 1) z += __shfl_xor_sync(0xffffffffu, z, off);
+        if (bias != nullptr) {
+          const int t = (int)(r % Tq);
+          z = fmaf(__ldg(bias + t * 2) - __ldg(bias + t * 2 + 1), 1.4426950408889634f, z);
+        }
+        const float w = __fdividef(1.f, 1.f + fast_exp2(-z));   // sigma; exp2(+inf) = inf -> w = 0
+        uint4 outv;
+        outv.x = pack_bf16x2(fmaf(w, vd[0], v1f[0]), fmaf(w, vd[1], v1f[1]));
+        outv.y = pack_bf16x2(fmaf(w, vd[2], v1f[2]), fmaf(w, vd[3], v1f[3]));
+        outv.z = pack_bf16x2(fmaf(w, vd[4], v1f[4]), fmaf(w, vd[5], v1f[5]));
+        outv.w = pack_bf16x2(fmaf(w, vd[6], v1f[6]), fmaf(w, vd[7], v1f[7]));
+        if (act) *reinterpret_cast<uint4*>(o + phys(r) * ldo + cx * 8) = outv;
+      }
+    }
+    return;
+  }
+
   // A warp can straddle two rows (blockDim.x = 40 at C = 320), so the trip count is made
   // block-uniform and rows past the tile are predicated: every lane reaches every shuffle.
   // The Q chunks of kFewUnroll rows are requested before the first of them is used: a streaming kernel with ~80
