@@ -102,6 +102,19 @@ int tvi_gemm_bf16_tn_ex(const tvi_bf16* X, const tvi_bf16* W, const tvi_bf16* bi
                         int64_t M, int N, int K, int64_t ldx, int64_t ldw, int64_t ldr, int64_t ldy, int epilogue,
                         void* stream);
 
+/* LayerNorm folded into the GEMM that consumes it (SURVEY 8.6 N1 "LN prologue"; the LayerNorm -> Linear pairs of
+ * src/models/attention.py:255+:276 (norm1 -> to_q/k/v), :321+:343 (norm3 -> ff), :441-446 (norm_in -> ff_in), :451, :462):
+ *   LN(x) W^T + b = rstd * (x Wg^T - mean * colsum) + bias',  Wg = gamma (.) W (bf16),  colsum_n = sum_k Wg[n, k] (fp32,
+ *   summed from the ROUNDED Wg so the mean term cancels exactly),  bias'_n = W_n . beta + b_n.
+ * tvi_layernorm_stats_f32 writes stats[M][2] = (mean, rstd) in one read-only pass (C in {320, 640, 1280});
+ * tvi_gemm_bf16_tn_ln is tvi_gemm_bf16_tn_ex on the RAW rows X with that affine map in the epilogue (before GEGLU /
+ * the residual).  The normalised activations never reach HBM. */
+int tvi_layernorm_stats_supported(int C);
+int tvi_layernorm_stats_f32(const tvi_bf16* x, float* stats, int64_t M, int C, int64_t ldx, float eps, void* stream);
+int tvi_gemm_bf16_tn_ln(const tvi_bf16* X, const tvi_bf16* Wg, const tvi_bf16* bias, const float* colsum, const float* stats,
+                        const tvi_bf16* residual, tvi_bf16* Y, int64_t M, int N, int K, int64_t ldx, int64_t ldw, int64_t ldr,
+                        int64_t ldy, int epilogue, void* stream);
+
 /* LayerNorm over the channel dimension of token-major activations (fp32 statistics, bf16 in/out).
  * Replaces: nn.LayerNorm norm1/norm2/norm3 and norm_in of the transformer blocks
  * (src/models/attention.py:270, :300, :321 and :441, :446, :462).  gamma, beta nullable; C % 8 == 0, C <= 2048. */

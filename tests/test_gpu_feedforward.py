@@ -3,6 +3,7 @@ bf16-rounded inputs and weights (tolerance of the attent
 import numpy as np
 import pytest
 import torch
+import torch.nn.functional as F
 
 import timelapse_video_interpolation_b200 as tvi
 from oracle import feedforward_ref
@@ -197,6 +198,81 @@ def test_fewkeys_interleaved_groups(cuda):
     assert torch.equal(o_int.view(B, T, S, C), o_ref.view(B, S, T, C).permute(0, 2, 1, 3))
     with pytest.raises(_lib.TviError):
         ops.attn_fewkeys(q.view(-1, C), k, v, B * T * S, T, heads, L, 0.125, group_inner=S + 1)
+
+
+@pytest.mark.parametrize("M,C,N,geglu,res", [(300, 320, 960, False, False), (1000, 640, 5120, True, False), (257, 1280, 1280, False, True),
+                                             (4096, 320, 2560, True, False), (130, 320, 320, False, True)])
+def test_layernorm_folded_into_the_gemm(cuda, M, C, N, geglu, res):
+    # SURVEY 8.6 N1 "LN prologue": LN(x) W^T + b from the raw rows = rstd * (x Wg^T - mean * colsum) + (W beta + b)
+    from timelapse_video_interpolation_b200 import lnfold
+    g = torch.Generator().manual_seed(M + N)
+    norm = torch.nn.LayerNorm(C)
+    lin = torch.nn.Linear(C, N)
+    with torch.no_grad():
+        norm.weight.copy_(1 + 0.3 * torch.randn(C, generator=g))
+        norm.bias.copy_(0.2 * torch.randn(C, generator=g))
+        lin.weight.copy_(torch.randn(N, C, generator=g) * C ** -0.5)
+        lin.bias.copy_(0.1 * torch.randn(N, generator=g))
+    norm, lin = norm.to(cuda, torch.bfloat16), lin.to(cuda, torch.bfloat16)
+    # rows with a mean several times their spread: the mean term must cancel, not round away
+    x = (torch.randn(M, C, generator=g) * 0.7 + 3.0 * torch.randn(M, 1, generator=g)).to(torch.bfloat16).to(cuda)
+    r = torch.randn(M, N // 2 if geglu else N, generator=g).to(torch.bfloat16).to(cuda) if res else None
+    w, b = lin.weight.detach(), lin.bias.detach()
+    if geglu:  # value | gate rows interleaved in blocks of H, as feedforward._geglu_weights does
+        inner, H = N // 2, ops.geglu_block(N // 2)
+        w = torch.stack([w[:inner].view(inner // H, H, -1), w[inner:].view(inner // H, H, -1)], dim=1).reshape(N, -1).contiguous()
+        b = torch.stack([b[:inner].view(inner // H, H), b[inner:].view(inner // H, H)], dim=1).reshape(-1).contiguous()
+    stats = ops.layernorm_stats(x, norm.eps)
+    xf = x.float().cpu()
+    assert float((stats[:, 0].cpu() - xf.mean(1)).abs().max()) < 1e-5 * 10
+    assert float((stats[:, 1].cpu() * torch.sqrt(xf.var(1, unbiased=False) + norm.eps) - 1).abs().max()) < 1e-4
+    wg, colsum, cb = lnfold.folded(lin, "t", w, b, norm)
+    y = ops.gemm_bf16_tn_ln(x, wg, cb, colsum, stats, residual=r, geglu=geglu)
+    n_ref = F.layer_norm(xf, (C,), norm.weight.float().cpu(), norm.bias.float().cpu(), norm.eps)
+    ref = F.linear(n_ref, lin.weight.float().cpu(), lin.bias.float().cpu())
+    if geglu:
+        ref = ref[:, :N // 2] * F.gelu(ref[:, N // 2:])
+    if res:
+        ref = ref + r.float().cpu()
+    # against the two-kernel path (bf16 normalised rows in between): the same bound holds for both
+    y2 = ops.gemm_bf16_tn_ex(ops.layernorm_bf16(x, norm.weight, norm.bias, norm.eps), w, b, residual=r, geglu=geglu)
+    e_fold, e_two = float((y.float().cpu() - ref).abs().max()), float((y2.float().cpu() - ref).abs().max())
+    print(f"  folded {e_fold:.3e}  two-kernel {e_two:.3e}  max |ref| {float(ref.abs().max()):.2f}")
+    assert_block_close("LN folded GEMM", y, ref, stores=1)
+    assert e_fold <= 2.0 * e_two + 1e-3
+    assert lnfold.folded(lin, "t", w, b, norm)[0] is wg          # cached
+    with torch.no_grad():
+        norm.weight.mul_(2.0)                                        # in-place update bumps _version -> rebuilt
+    assert lnfold.folded(lin, "t", w, b, norm)[0] is not wg
+
+
+def test_blocks_with_the_layernorm_fold_enabled(cuda, monkeypatch):
+    # TVI_LN_FOLD=1: norm1 -> QKV, norm3 / norm_in -> GEGLU projections go through tvi_gemm_bf16_tn_ln; same bound as the default path
+    monkeypatch.setenv("TVI_LN_FOLD", "1")
+    B, T, S, C = 1, 14, 96, 320
+    g = torch.Generator().manual_seed(31)
+    sb = _init(BasicTransformerBlock(C, 5, 1024), 21, cuda)
+    tb = _init(TemporalBasicTransformerBlock(C, C, 5, 1024), 22, cuda)
+    blocks.install_blocks(sb)
+    blocks.install_blocks(tb)
+    x = (torch.randn(B * T, S, C, generator=g) + 0.5).to(torch.bfloat16).to(cuda)
+    es = torch.randn(B * T, 2, 1024, generator=g).to(torch.bfloat16).to(cuda)
+    et = torch.randn(B * S, 1, 1024, generator=g).to(torch.bfloat16).to(cuda)
+    seen = []
+    ops.EVENT_HOOK = lambda name, start: seen.append(name) if start else None
+    try:
+        with torch.no_grad():
+            ys = sb(x, encoder_hidden_states=es)
+            yt = tb(x, num_frames=T, encoder_hidden_states=et)
+    finally:
+        ops.EVENT_HOOK = None
+    assert seen.count("gemm_bf16_tn_ln") == 3 + 3 and seen.count("layernorm_stats") == 6 and "layernorm_bf16" not in seen
+    assert_block_close("spatial block, LN folded", ys, blocks_ref.basic_transformer_block_ref(sb, x, es), stores=3)
+    assert_block_close("temporal block, LN folded", yt, blocks_ref.temporal_basic_transformer_block_ref(tb, x, T, et), stores=4)
+    monkeypatch.setenv("TVI_LN_FOLD", "0")
+    with torch.no_grad():
+        ys0 = sb(x, encoder_hidden_states=es)
+    assert_block_close("fold vs default", ys, ys0.float().cpu(), stores=3)
 
 
 def test_bcast_rows_add_group_inner(cuda):

@@ -97,7 +97,7 @@ def test_transformer_spatio_temporal_model_matches_oracle(cuda, B, T, H, W, C, h
         y = out.sample
         y_tuple = m(x, encoder_hidden_states=(e, e), image_only_indicator=ind, return_dict=False)[0]
     torch.cuda.synchronize()
-    assert ops.LAUNCHES - launches0 >= 2 * 30
+    assert ops.LAUNCHES - launches0 >= 2 * 28
     assert torch.equal(y, y_tuple) and y.shape == x.shape and y.dtype == torch.bfloat16
     ref = spatio_temporal_ref.transformer_spatio_temporal_ref(m, x, e, ind, alpha_dtype=torch.bfloat16)
     assert_block_close(f"spatio-temporal model C={C} T={T}", y, ref, stores=9)  # proj_in, 3 + 4 block stores, blend

@@ -39,6 +39,9 @@ SIGNATURES = {
     "tvi_backward_warp_f32": (_i32, [_ptr, _ptr, _ptr, _ptr, _ptr, _i64, _i32, _i32, _i32, _f32, _f32, _ptr]),
     "tvi_gemm_bf16_tn": (_i32, [_ptr, _ptr, _ptr, _ptr, _i64, _i32, _i32, _i64, _i64, _i64, _ptr]),
     "tvi_geglu_block": (_i32, [_i32]),
+    "tvi_layernorm_stats_supported": (_i32, [_i32]),
+    "tvi_layernorm_stats_f32": (_i32, [_ptr, _ptr, _i64, _i32, _i64, _f32, _ptr]),
+    "tvi_gemm_bf16_tn_ln": (_i32, [_ptr, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr, _i64, _i32, _i32, _i64, _i64, _i64, _i64, _i32, _ptr]),
     "tvi_gemm_bf16_tn_ex": (_i32, [_ptr, _ptr, _ptr, _ptr, _ptr, _i64, _i32, _i32, _i64, _i64, _i64, _i64, _i32, _ptr]),
     "tvi_layernorm_bf16": (_i32, [_ptr, _ptr, _ptr, _ptr, _i64, _i32, _i64, _i64, _f32, _ptr]),
     "tvi_bcast_rows_add_bf16": (_i32, [_ptr, _ptr, _ptr, _i64, _i64, _i64, _i32, _i64, _i64, _i64, _ptr]),

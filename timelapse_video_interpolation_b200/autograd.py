@@ -12,7 +12,7 @@ from __future__ import annotations
 import torch
 from torch.autograd.function import once_differentiable
 
-from . import _lib, caches, ops
+from . import _lib, caches, lnfold, ops
 
 
 def _to_bf16(t):
@@ -31,15 +31,24 @@ def _out_proj(o, w_o, b_o, residual):
     return ops.gemm_bf16_tn_ex(o, w_o, b_o, residual=residual.reshape(o.shape[0], residual.shape[-1]))
 
 
+def _proj(x2, w, ln):
+    """x2 @ w^T, or LayerNorm(x2) @ w^T through the folded GEMM when ln = (owner module, key, norm) (lnfold.py)."""
+    if ln is None:
+        return ops.gemm_bf16_tn(x2, w)
+    owner, key, norm = ln
+    wg, colsum, cb = lnfold.folded(owner, key, w, None, norm)
+    return ops.gemm_bf16_tn_ln(x2, wg, cb, colsum, ops.layernorm_stats(x2, float(norm.eps)))
+
+
 def self_attention(x: torch.Tensor, w_qkv: torch.Tensor, w_o: torch.Tensor, b_o, heads: int, scale: float,
-                   residual=None, frames=None) -> torch.Tensor:
+                   residual=None, frames=None, ln=None) -> torch.Tensor:
     """x [B', S, C] bf16 -> [B', S, C].  Reference: AttnProcessor2_0.__call__ with
     encoder_hidden_states=None (src/models/attention_processor.py:1223-1261).
     `frames` = T: x is [B*T, S, C] in the SPATIAL token order and attention runs over the T tokens of every (b, s)
     — the temporal block's self-attention without the permutes of src/models/attention.py:436-438 / :474-476."""
     Bp, S, C = x.shape
     inner = w_qkv.shape[0] // 3
-    qkv = ops.gemm_bf16_tn(x.view(Bp * S, C), w_qkv)  # [B'*S, 3*inner], heads stay packed along the row
+    qkv = _proj(x.view(Bp * S, C), w_qkv, ln)  # [B'*S, 3*inner], heads stay packed along the row
     q, k, v = qkv[:, :inner], qkv[:, inner:2 * inner], qkv[:, 2 * inner:]
     if frames is not None:
         o = ops.attn_temporal(q, k, v, Bp // frames * S, heads, frames, frames, scale, seq_inner=S)
@@ -50,7 +59,7 @@ def self_attention(x: torch.Tensor, w_qkv: torch.Tensor, w_o: torch.Tensor, b_o,
 
 
 def cross_attention(x: torch.Tensor, e: torch.Tensor, w_q: torch.Tensor, w_kv: torch.Tensor, w_o: torch.Tensor, b_o,
-                    heads: int, scale: float, bias=None, stats=None, residual=None, frames=None) -> torch.Tensor:
+                    heads: int, scale: float, bias=None, stats=None, residual=None, frames=None, ln=None) -> torch.Tensor:
     """x [B', S, C], e [B', L, Ckv] -> [B', S, C].  Reference: same processor with
     encoder_hidden_states given (keys/values from the context, :1225-1231).
     `frames` = T: x is [B*T, S, C] in the spatial token order, e is the temporal block's [B*S, L, Ckv] context; row
@@ -70,7 +79,7 @@ def cross_attention(x: torch.Tensor, e: torch.Tensor, w_q: torch.Tensor, w_kv: t
             return ops.bcast_rows_add(yv, res2, frames, group_inner=S, nrows=Bp * S).view(Bp, S, yv.shape[-1])
         # more keys, the ramp bias or the statistics: the few-keys core reads the T query rows of group (b, s) with a
         # row stride of S (bias / statistics rows are the frame index t)
-        q = ops.gemm_bf16_tn(x.view(Bp * S, C), w_q)
+        q = _proj(x.view(Bp * S, C), w_q, ln)
         o = ops.attn_fewkeys(q, kv[:, :inner], kv[:, inner:], Bp * S, frames, heads, L, scale,
                              Tq=frames if (bias is not None or stats is not None) else 1, bias=bias, stats=stats, group_inner=S)
         y = _out_proj(o, w_o, b_o, residual)
@@ -86,7 +95,7 @@ def cross_attention(x: torch.Tensor, e: torch.Tensor, w_q: torch.Tensor, w_kv: t
             return ops.bcast_rows_add(yv, residual.reshape(Bp * S, residual.shape[-1]), S).view(Bp, S, yv.shape[-1])
         y = ops.attn_fewkeys(None, yv, yv, Bp * S, S, heads, 1, 1.0)  # L == 1: pure row broadcast
         return y.view(Bp, S, y.shape[-1])
-    q = ops.gemm_bf16_tn(x.view(Bp * S, C), w_q)
+    q = _proj(x.view(Bp * S, C), w_q, ln)
     o = ops.attn_fewkeys(q, k, v, Bp * S, S, heads, L, scale, Tq=S if (bias is not None or stats is not None) else 1,
                          bias=bias, stats=stats)
     y = _out_proj(o, w_o, b_o, residual)
@@ -240,18 +249,32 @@ class _AttentionFn(torch.autograd.Function):
         return (dx, de, cast(dwq, dt_wq), cast(dwk, dt_wk), cast(dwv, dt_wv), cast(dwo, dt_wo), cast(dbo, dt_bo), None)
 
 
-def attention_forward(proc, attn, x, e, heads: int, scale: float, wo, bo, bias, stats, residual=None, frames=None) -> torch.Tensor:
+def attention_forward(proc, attn, x, e, heads: int, scale: float, wo, bo, bias, stats, residual=None, frames=None,
+                      pre_norm=None) -> torch.Tensor:
+    """`pre_norm` (an nn.LayerNorm): the call computes attention(pre_norm(x), ...); on the no-grad path the LayerNorm is
+    folded into the query-side projection (lnfold.py), elsewhere it runs as its own kernel first."""
     wq, wk, wv = attn.to_q.weight, attn.to_k.weight, attn.to_v.weight
     needs_grad = torch.is_grad_enabled() and any(
-        t is not None and t.requires_grad for t in (x, e, wq, wk, wv, wo, bo))
+        t is not None and t.requires_grad for t in (x, e, wq, wk, wv, wo, bo) + (
+            tuple(pre_norm.parameters()) if pre_norm is not None else ()))
     caches.note_call(needs_grad)
     w_o = _to_bf16(wo).contiguous()
     b_o = _to_bf16(bo).contiguous() if bo is not None else None
     if not needs_grad and not (residual is not None and torch.is_grad_enabled() and residual.requires_grad):
+        ln = None
+        if pre_norm is not None:
+            if lnfold.supported(pre_norm, x):
+                ln = (attn, "to_q" if e is not None else "qkv", pre_norm)
+            else:
+                from .feedforward import layer_norm
+                x = layer_norm(pre_norm, x)
         if e is None:
-            return self_attention(x, proc._fused(attn, ("to_q", "to_k", "to_v")), w_o, b_o, heads, scale, residual, frames)
+            return self_attention(x, proc._fused(attn, ("to_q", "to_k", "to_v")), w_o, b_o, heads, scale, residual, frames, ln)
         return cross_attention(x, e, proc._fused(attn, ("to_q",)), proc._fused(attn, ("to_k", "to_v")), w_o, b_o, heads,
-                               scale, bias, stats, residual, frames)
+                               scale, bias, stats, residual, frames, ln)
+    if pre_norm is not None:
+        from .feedforward import layer_norm
+        x = layer_norm(pre_norm, x)
     if frames is not None:
         raise NotImplementedError("frames= (temporal attention in the spatial token order) is inference-only: the backward "
                                   "kernels take the [B*S, T, C] layout")

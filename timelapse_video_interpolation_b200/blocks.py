@@ -5,7 +5,10 @@ Drop-in replacements for
   TemporalBasicTransformerBlock.forward  reference src/models/attention.py:423-478
 Every arithmetic step is a libtvi kernel: LayerNorm -> attention (processor path, residual add fused into the
 out-projection epilogue) -> LayerNorm -> cross-attention (+ residual) -> LayerNorm -> FeedForward (GEGLU fused into the
-first GEMM, bias + residual into the second).  The `[B*T, S, C] <-> [B*S, T, C]` re-layout of the temporal block
+first GEMM, bias + residual into the second).  On the no-grad path the LayerNorm in front of a one-key
+cross-attention — whose queries are never read — is skipped; every other LayerNorm is handed to the projection it feeds
+as `pre_norm=`, which either runs it as its own kernel (default) or folds it into the GEMM (lnfold.py, `TVI_LN_FOLD=1`:
+built and parity-tested, measured slower at the SVD shapes, see there).  The `[B*T, S, C] <-> [B*S, T, C]` re-layout of the temporal block
 (:436-438, :474-476) is folded away (row N2): LayerNorm / FeedForward / projections are row-wise, so the block runs on
 the spatial token order in place and only the attention cores address the T tokens of a (b, s) sequence with a
 row stride of S (`tvi_attn_temporal_fwd_interleaved`, `tvi_bcast_rows_add_bf16(group_inner=S)` for one-key contexts,
@@ -25,7 +28,7 @@ from typing import Optional
 import torch
 
 from . import _lib, caches
-from .feedforward import feed_forward, layer_norm
+from .feedforward import feed_forward
 from .processor import TviAttnProcessor
 
 __all__ = ["basic_transformer_block_forward", "temporal_basic_transformer_block_forward", "install_blocks", "uninstall_blocks"]
@@ -52,8 +55,19 @@ def _proc(attn):
     return proc
 
 
-def _attn(attn, x, e, residual, frames=None):
-    return _proc(attn)(attn, x, encoder_hidden_states=e, residual=residual, frames=frames)
+def _attn(attn, x, e, residual, frames=None, pre_norm=None):
+    return _proc(attn)(attn, x, encoder_hidden_states=e, residual=residual, frames=frames, pre_norm=pre_norm)
+
+
+def _cross_attn(block, norm, attn, x, e, frames=None):
+    """norm -> cross-attention -> + x.  With ONE context token the softmax is 1 and the queries are never read
+    (autograd.cross_attention), so on the no-grad path the LayerNorm in front of to_q is dead work: skip it (0.07 ms of
+    HBM traffic per call at L0; SVD's image-embedding context has exactly one token)."""
+    proc = _proc(attn)
+    if (e is not None and e.shape[1] == 1 and proc.stats_sink is None and not proc.ramp_bias
+            and not _training(block, x) and not (torch.is_grad_enabled() and e.requires_grad)):
+        return proc(attn, x, encoder_hidden_states=e, residual=x, frames=frames)   # x only lends its shape
+    return proc(attn, x, encoder_hidden_states=e, residual=x, frames=frames, pre_norm=norm)
 
 
 def _check_basic(block):
@@ -75,15 +89,13 @@ def basic_transformer_block_forward(block, hidden_states: torch.Tensor, attentio
         raise _lib.TviError(_lib.TVI_ERR_UNSUPPORTED, "block forward: unsupported cross_attention_kwargs")
     x = hidden_states.contiguous()
     # 0. self-attention (:270-287): norm1 -> attn1 -> + hidden_states
-    n = layer_norm(block.norm1, x)
-    x = _attn(block.attn1, n, encoder_hidden_states if getattr(block, "only_cross_attention", False) else None, x)
+    x = _attn(block.attn1, x, encoder_hidden_states if getattr(block, "only_cross_attention", False) else None, x,
+              pre_norm=block.norm1)
     # 3. cross-attention (:296-317)
     if getattr(block, "attn2", None) is not None:
-        n = layer_norm(block.norm2, x)
-        x = _attn(block.attn2, n, encoder_hidden_states, x)
+        x = _cross_attn(block, block.norm2, block.attn2, x, encoder_hidden_states)
     # 4. feed-forward (:321-343): norm3 -> ff -> + hidden_states
-    n = layer_norm(block.norm3, x)
-    return feed_forward(block.ff, n, residual=x)
+    return feed_forward(block.ff, x, residual=x, pre_norm=block.norm3)
 
 
 def temporal_basic_transformer_block_forward(block, hidden_states: torch.Tensor, num_frames: int,
@@ -101,26 +113,18 @@ def temporal_basic_transformer_block_forward(block, hidden_states: torch.Tensor,
     if in_place:
         # every op but the attention cores is row-wise: stay in the [B*T, S, C] token order, no permute copies
         x = hidden_states.contiguous()
-        n = layer_norm(block.norm_in, x)
-        x = feed_forward(block.ff_in, n, residual=x if block.is_res else None)   # :441-449
-        n = layer_norm(block.norm1, x)
-        x = _attn(block.attn1, n, None, x, frames=num_frames)                    # :451-453
+        x = feed_forward(block.ff_in, x, residual=x if block.is_res else None, pre_norm=block.norm_in)   # :441-449
+        x = _attn(block.attn1, x, None, x, frames=num_frames, pre_norm=block.norm1)                      # :451-453
         if attn2 is not None:
-            n = layer_norm(block.norm2, x)
-            x = _attn(attn2, n, encoder_hidden_states, x, frames=num_frames)             # :456-460
-        n = layer_norm(block.norm3, x)
-        return feed_forward(block.ff, n, residual=x if block.is_res else None)   # :462-472
+            x = _cross_attn(block, block.norm2, attn2, x, encoder_hidden_states, frames=num_frames)   # :456-460
+        return feed_forward(block.ff, x, residual=x if block.is_res else None, pre_norm=block.norm3)     # :462-472
     # [B*T, S, C] -> [B*S, T, C] (:435-438)
     x = hidden_states.reshape(B, num_frames, S, C).permute(0, 2, 1, 3).reshape(B * S, num_frames, C)
-    n = layer_norm(block.norm_in, x)
-    x = feed_forward(block.ff_in, n, residual=x if block.is_res else None)   # :441-449
-    n = layer_norm(block.norm1, x)
-    x = _attn(block.attn1, n, None, x)                                       # :451-453
+    x = feed_forward(block.ff_in, x, residual=x if block.is_res else None, pre_norm=block.norm_in)   # :441-449
+    x = _attn(block.attn1, x, None, x, pre_norm=block.norm1)                                         # :451-453
     if getattr(block, "attn2", None) is not None:
-        n = layer_norm(block.norm2, x)
-        x = _attn(block.attn2, n, encoder_hidden_states, x)                  # :456-460
-    n = layer_norm(block.norm3, x)
-    x = feed_forward(block.ff, n, residual=x if block.is_res else None)      # :462-472
+        x = _cross_attn(block, block.norm2, block.attn2, x, encoder_hidden_states)   # :456-460
+    x = feed_forward(block.ff, x, residual=x if block.is_res else None, pre_norm=block.norm3)        # :462-472
     # [B*S, T, C] -> [B*T, S, C] (:474-476)
     return x.reshape(B, S, num_frames, x.shape[-1]).permute(0, 2, 1, 3).reshape(B * num_frames, S, x.shape[-1])
 

@@ -42,7 +42,7 @@ constexpr int kABytes = kBM * kBK * 2;             // 16 KB
 constexpr int kStageBufs = 1;
 constexpr int kResStageBufs = 4;                   // with a residual: the buffers also receive the residual chunk two chunks ahead
 // warps x bufs x [32 rows][64 B] + warps x 256 fp32 bias
-constexpr int kBiasBytes = 2 * 256 * 4;            // one fp32 bias strip per accumulator stage, shared by the epilogue warps
+constexpr int kBiasBytes = 4 * 256 * 4;            // one fp32 bias strip (+ one LayerNorm column-sum strip) per accumulator stage, shared by the epilogue warps
 constexpr int staging_bytes(int bufs) { return kEpiWarps * bufs * 2048 + kBiasBytes; }
 constexpr int kMaxStages = 8;
 
@@ -79,6 +79,10 @@ struct GemmParams {
   int stage_bufs;      // staging buffers per epilogue warp (kStageBufs, or kResStageBufs with a residual)
   int res_b;           // the CTA's B slice [BN x K] stays resident in shared memory (grid is a multiple of n_tiles)
   float* partial;      // kSplit: [splits][M_out][ldp] fp32
+  // LayerNorm folded into the GEMM (A = the raw rows x, B = gamma (.) W): y = rstd * (acc - mean * colsum_n) + bias_n with
+  // colsum_n = sum_k B[n, k] and bias_n = W_n . beta + b_n prepared by the host; ln_stats = [M][2] fp32 (mean, rstd)
+  const float2* ln_stats;
+  const float* ln_colsum;
   int64_t M_out;
   int64_t ldp;
 };
@@ -248,6 +252,8 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
     const int nbufs = p.stage_bufs;
     uint8_t* my_staging_ptr = staging_ptr + (warp - 2) * nbufs * 2048;
     float* bias_strips = reinterpret_cast<float*>(staging_ptr + kEpiWarps * nbufs * 2048);
+    float* cs_strips = bias_strips + 2 * 256;
+    const bool has_ln = !kSplit && p.ln_stats != nullptr;
     const int epi_tid = threadIdx.x - 64;
     int buf = 0;
     // Residual (Y = acc + bias + R): a per-chunk global read after the accumulator wait would expose one DRAM latency
@@ -295,6 +301,16 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
       const int nt = (int)(mn - mt * p.n_tiles);
       const int m0 = (int)(mt * kBM), n0 = nt * p.BN;
       const float* my_bias = bias_strips + as * 256;
+      const float* my_cs = cs_strips + as * 256;
+      float ln_r = 1.f, ln_t = 0.f;  // y = ln_r * acc + ln_t * colsum + bias, ln_t = -mean * rstd
+      if (has_ln) {
+        const int64_t row = (int64_t)m0 + quad * 32 + lane;
+        if (row < p.M_out) {
+          const float2 st = __ldg(p.ln_stats + row);
+          ln_r = st.y;
+          ln_t = -st.x * st.y;
+        }
+      }
       if (!kSplit && p.bias != nullptr) {
         // This tile's bias slice as fp32 in the strip of accumulator stage `as` (read back as broadcast LDS.128).  One
         // barrier per tile among the epilogue warps: a warp that passes it knows every warp has finished tile i - 1's
@@ -302,6 +318,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
         if (epi_tid < p.BN)
           bias_strips[as * 256 + epi_tid] =
               (n0 + epi_tid < p.N) ? __bfloat162float(*reinterpret_cast<const __nv_bfloat16*>(p.bias + n0 + epi_tid)) : 0.f;
+        if (has_ln && epi_tid < p.BN) cs_strips[as * 256 + epi_tid] = (n0 + epi_tid < p.N) ? __ldg(p.ln_colsum + n0 + epi_tid) : 0.f;
         named_bar_sync(1, 32 * kEpiWarps);
       }
       mbar_wait(&bar_acc_full[as], aph);
@@ -344,7 +361,17 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
         float f[32];
 #pragma unroll
         for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(r[j]);
-        if (p.bias != nullptr) {
+        if (has_ln) {
+#pragma unroll
+          for (int j = 0; j < 32; j += 4) {
+            const float4 b4 = *reinterpret_cast<const float4*>(my_bias + c * 32 + j);
+            const float4 s4 = *reinterpret_cast<const float4*>(my_cs + c * 32 + j);
+            f[j] = fmaf(ln_r, f[j], fmaf(ln_t, s4.x, b4.x));
+            f[j + 1] = fmaf(ln_r, f[j + 1], fmaf(ln_t, s4.y, b4.y));
+            f[j + 2] = fmaf(ln_r, f[j + 2], fmaf(ln_t, s4.z, b4.z));
+            f[j + 3] = fmaf(ln_r, f[j + 3], fmaf(ln_t, s4.w, b4.w));
+          }
+        } else if (p.bias != nullptr) {
 #pragma unroll
           for (int j = 0; j < 32; j += 4) {
             const float4 b4 = *reinterpret_cast<const float4*>(my_bias + c * 32 + j);
@@ -357,10 +384,15 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
         if (p.geglu) {
           // GEGLU (diffusers GEGLU.forward: hidden * F.gelu(gate), erf form): gate = the partner column
           const float* gate_bias = my_bias + (out_chunks + c) * 32;
+          if (has_ln) {  // the gate pre-activation gets the same affine map of its accumulator
+            const float* gate_cs = my_cs + (out_chunks + c) * 32;
+#pragma unroll
+            for (int j = 0; j < 32; ++j) rg[j] = __float_as_uint(fmaf(ln_r, __uint_as_float(rg[j]), fmaf(ln_t, gate_cs[j], gate_bias[j])));
+          }
 #pragma unroll
           for (int j = 0; j < 32; j += 4) {
             float4 b4 = make_float4(0.f, 0.f, 0.f, 0.f);
-            if (p.bias != nullptr) b4 = *reinterpret_cast<const float4*>(gate_bias + j);
+            if (p.bias != nullptr && !has_ln) b4 = *reinterpret_cast<const float4*>(gate_bias + j);
             f[j] *= gelu_erf(__uint_as_float(rg[j]) + b4.x);
             f[j + 1] *= gelu_erf(__uint_as_float(rg[j + 1]) + b4.y);
             f[j + 2] *= gelu_erf(__uint_as_float(rg[j + 2]) + b4.z);
@@ -491,8 +523,11 @@ int configure_once() {
 template <bool kAMn, bool kBMn, bool kSplit>
 int launch_gemm(const char* name, const tvi_bf16* A, const tvi_bf16* B, const tvi_bf16* bias, tvi_bf16* Y, float* partial,
                 int splits, int64_t Mo, int No, int64_t R, int64_t lda, int64_t ldb, int64_t ldy, cudaStream_t st,
-                int geglu_block = 0, const tvi_bf16* residual = nullptr, int64_t ldr = 0) {
+                int geglu_block = 0, const tvi_bf16* residual = nullptr, int64_t ldr = 0, const float* ln_stats = nullptr,
+                const float* ln_colsum = nullptr) {
   GemmParams p;
+  p.ln_stats = reinterpret_cast<const float2*>(ln_stats);
+  p.ln_colsum = ln_colsum;
   p.BN = pick_bn(No, kBMn ? 64 : 32);
   if (const char* e = getenv("TVI_GEMM_BN")) {
     const int bn = atoi(e);
@@ -608,6 +643,12 @@ extern "C" int tvi_gemm_bf16_tn(const tvi_bf16* X, const tvi_bf16* W, const tvi_
 
 extern "C" int tvi_geglu_block(int inner) {
   // width of the value / gate column blocks the fused GEGLU projection expects in its re-ordered weight
+#ifdef TVI_GEMM_TUNE  // tuning builds only
+  if (const char* e = getenv("TVI_GEGLU_BLOCK")) {
+    const int h = atoi(e);
+    if (h >= 32 && h <= 128 && h % 32 == 0 && inner > 0 && inner % h == 0) return h;
+  }
+#endif
   for (int h = 128; h >= 32; h -= 32)
     if (inner > 0 && inner % h == 0) return h;
   return 0;
@@ -640,6 +681,36 @@ extern "C" int tvi_gemm_bf16_tn_ex(const tvi_bf16* X, const tvi_bf16* W, const t
   TVI_CHECK_ARG(M < ((int64_t)1 << 31) - 256, "tvi_gemm_bf16_tn_ex: M too large for one call");
   return launch_gemm<false, false, false>("tvi_gemm_bf16_tn_ex", X, W, bias, Y, nullptr, 1, M, N, K, ldx, ldw, ldy,
                                           (cudaStream_t)stream, block, residual, ldr);
+}
+
+extern "C" int tvi_gemm_bf16_tn_ln(const tvi_bf16* X, const tvi_bf16* Wg, const tvi_bf16* bias, const float* colsum,
+                                   const float* stats, const tvi_bf16* residual, tvi_bf16* Y, int64_t M, int N, int K, int64_t ldx,
+                                   int64_t ldw, int64_t ldr, int64_t ldy, int epilogue, void* stream) {
+  using namespace tvi;
+  TVI_CHECK_ARG(M >= 0 && N >= 0 && K >= 0, "tvi_gemm_bf16_tn_ln: negative size");
+  if (M == 0 || N == 0) return TVI_OK;
+  TVI_CHECK_ARG(X && Wg && Y && bias && colsum && stats, "tvi_gemm_bf16_tn_ln: null pointer (bias, colsum and stats are required)");
+  TVI_CHECK_ARG(K > 0 && K % 8 == 0 && N % 8 == 0, "tvi_gemm_bf16_tn_ln: N=%d and K=%d must be positive multiples of 8", N, K);
+  TVI_CHECK_ARG(epilogue == TVI_EPILOGUE_NONE || epilogue == TVI_EPILOGUE_GEGLU, "tvi_gemm_bf16_tn_ln: unknown epilogue %d", epilogue);
+  int block = 0;
+  int n_store = N;
+  if (epilogue == TVI_EPILOGUE_GEGLU) {
+    TVI_CHECK_ARG(N % 2 == 0, "tvi_gemm_bf16_tn_ln: GEGLU needs an even number of projection columns");
+    n_store = N / 2;
+    block = tvi_geglu_block(n_store);
+    TVI_CHECK_ARG(block > 0, "tvi_gemm_bf16_tn_ln: GEGLU inner width %d must be a multiple of 32", n_store);
+  }
+  TVI_CHECK_ARG(ldx % 8 == 0 && ldw % 8 == 0 && ldy % 8 == 0 && (residual == nullptr || ldr % 8 == 0),
+                "tvi_gemm_bf16_tn_ln: row strides must be multiples of 8 elements");
+  TVI_CHECK_ARG(ldx >= K && ldw >= K && ldy >= n_store && (residual == nullptr || ldr >= n_store),
+                "tvi_gemm_bf16_tn_ln: row stride smaller than the row");
+  TVI_CHECK_ARG(((uintptr_t)X | (uintptr_t)Wg | (uintptr_t)Y | (uintptr_t)residual) % 16 == 0,
+                "tvi_gemm_bf16_tn_ln: X, Wg, Y, residual must be 16-byte aligned");
+  TVI_CHECK_ARG((uintptr_t)bias % 2 == 0 && (uintptr_t)colsum % 4 == 0 && (uintptr_t)stats % 8 == 0,
+                "tvi_gemm_bf16_tn_ln: bias / colsum / stats are misaligned");
+  TVI_CHECK_ARG(M < ((int64_t)1 << 31) - 256, "tvi_gemm_bf16_tn_ln: M too large for one call");
+  return launch_gemm<false, false, false>("tvi_gemm_bf16_tn_ln", X, Wg, bias, Y, nullptr, 1, M, N, K, ldx, ldw, ldy,
+                                          (cudaStream_t)stream, block, residual, ldr, stats, colsum);
 }
 
 extern "C" int tvi_gemm_bf16_dgrad(const tvi_bf16* dY, const tvi_bf16* W, tvi_bf16* dX, int64_t M, int N, int K,

@@ -110,10 +110,12 @@ layernorm_kernel(const tvi_bf16* __restrict__ x, const tvi_bf16* __restrict__ ga
 // exactly 160 16-byte chunks = 5 per lane, every lane busy in every iteration (the row-per-warp layout above leaves
 // 24 of 64 lane slots idle at C = 320 and was issue-bound at 3.5 TB/s).  Chunk k = lane + 32 i belongs to row k / C8;
 // per-row sums are formed lane-locally (select by row) and butterfly-reduced for all R rows; packed f32x2 arithmetic.
-template <int R>
+// kStats: write (mean, rstd) of every row to `stats` [M][2] fp32 instead of the normalised rows (the LayerNorm is then
+// applied by the epilogue of the GEMM that consumes the rows, tvi_gemm_bf16_tn_ln): a read-only pass, half the traffic.
+template <int R, bool kStats>
 __global__ void __launch_bounds__(kLnWarps * 32)
 layernorm_flat_kernel(const tvi_bf16* __restrict__ x, const tvi_bf16* __restrict__ gamma, const tvi_bf16* __restrict__ beta,
-                      tvi_bf16* __restrict__ y, int64_t M, int64_t ldx, int64_t ldy, float eps) {
+                      tvi_bf16* __restrict__ y, float2* __restrict__ stats, int64_t M, int64_t ldx, int64_t ldy, float eps) {
   constexpr int C8 = 160 / R;
   constexpr int NCH = 5;
   const int lane = threadIdx.x & 31;
@@ -155,6 +157,9 @@ layernorm_flat_kernel(const tvi_bf16* __restrict__ x, const tvi_bf16* __restrict
   }
   constexpr float inv_c = 1.0f / (float)(C8 * 8);
   float negmean[NCH];
+  float mean_r[R];
+#pragma unroll
+  for (int r = 0; r < R; ++r) mean_r[r] = part[r] * inv_c;
 #pragma unroll
   for (int i = 0; i < NCH; ++i) {
     float m = part[0];
@@ -186,6 +191,12 @@ layernorm_flat_kernel(const tvi_bf16* __restrict__ x, const tvi_bf16* __restrict
   }
 #pragma unroll
   for (int r = 0; r < R; ++r) part[r] = rsqrtf(part[r] * inv_c + eps);
+  if (kStats) {
+#pragma unroll
+    for (int r = 0; r < R; ++r)
+      if (lane == r && row0 + r < M) stats[row0 + r] = make_float2(mean_r[r], part[r]);
+    return;
+  }
 #pragma unroll
   for (int i = 0; i < NCH; ++i) {
     float rs = part[0];
@@ -216,8 +227,18 @@ int launch_ln_flat(const tvi_bf16* x, const tvi_bf16* gamma, const tvi_bf16* bet
   const int64_t rows_per_block = (int64_t)kLnWarps * R;
   const int64_t blocks = (M + rows_per_block - 1) / rows_per_block;
   TVI_CHECK_ARG(blocks < ((int64_t)1 << 31), "tvi_layernorm_bf16: too many rows for one call");
-  layernorm_flat_kernel<R><<<(unsigned)blocks, kLnWarps * 32, 0, st>>>(x, gamma, beta, y, M, ldx, ldy, eps);
+  layernorm_flat_kernel<R, false><<<(unsigned)blocks, kLnWarps * 32, 0, st>>>(x, gamma, beta, y, nullptr, M, ldx, ldy, eps);
   TVI_LAUNCH_OK("layernorm_flat_kernel");
+  return TVI_OK;
+}
+
+template <int R>
+int launch_ln_stats(const tvi_bf16* x, float2* stats, int64_t M, int64_t ldx, float eps, cudaStream_t st) {
+  const int64_t rows_per_block = (int64_t)kLnWarps * R;
+  const int64_t blocks = (M + rows_per_block - 1) / rows_per_block;
+  TVI_CHECK_ARG(blocks < ((int64_t)1 << 31), "tvi_layernorm_stats_f32: too many rows for one call");
+  layernorm_flat_kernel<R, true><<<(unsigned)blocks, kLnWarps * 32, 0, st>>>(x, nullptr, nullptr, nullptr, stats, M, ldx, 0, eps);
+  TVI_LAUNCH_OK("layernorm_flat_kernel<stats>");
   return TVI_OK;
 }
 
@@ -257,6 +278,25 @@ extern "C" int tvi_layernorm_bf16(const tvi_bf16* x, const tvi_bf16* gamma, cons
   if (C8 <= 64) return launch_ln<2, 2>(x, gamma, beta, y, M, C8, ldx, ldy, eps, st);
   if (C8 <= 128) return launch_ln<4, 2>(x, gamma, beta, y, M, C8, ldx, ldy, eps, st);
   return launch_ln<8, 1>(x, gamma, beta, y, M, C8, ldx, ldy, eps, st);
+}
+
+extern "C" int tvi_layernorm_stats_supported(int C) { return C == 320 || C == 640 || C == 1280; }
+
+extern "C" int tvi_layernorm_stats_f32(const tvi_bf16* x, float* stats, int64_t M, int C, int64_t ldx, float eps, void* stream) {
+  using namespace tvi;
+  TVI_CHECK_ARG(M >= 0 && C >= 0, "tvi_layernorm_stats_f32: negative size");
+  if (M == 0) return TVI_OK;
+  TVI_CHECK_ARG(x && stats, "tvi_layernorm_stats_f32: null pointer");
+  if (!tvi_layernorm_stats_supported(C))
+    return fail(TVI_ERR_UNSUPPORTED, "tvi_layernorm_stats_f32: C=%d (320, 640 and 1280 — the SVD widths — are built)", C);
+  TVI_CHECK_ARG(ldx % 8 == 0 && ldx >= C, "tvi_layernorm_stats_f32: bad row stride");
+  TVI_CHECK_ARG((uintptr_t)x % 16 == 0 && (uintptr_t)stats % 8 == 0, "tvi_layernorm_stats_f32: x must be 16-byte, stats 8-byte aligned");
+  TVI_CHECK_ARG(eps > 0.f, "tvi_layernorm_stats_f32: eps must be positive");
+  cudaStream_t st = (cudaStream_t)stream;
+  float2* out = reinterpret_cast<float2*>(stats);
+  if (C == 320) return launch_ln_stats<4>(x, out, M, ldx, eps, st);
+  if (C == 640) return launch_ln_stats<2>(x, out, M, ldx, eps, st);
+  return launch_ln_stats<1>(x, out, M, ldx, eps, st);
 }
 
 // ---------------------------------------------------------------------------------------------------------------

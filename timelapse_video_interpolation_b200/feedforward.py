@@ -21,7 +21,7 @@ from typing import Optional
 
 import torch
 
-from . import _lib, caches, ops
+from . import _lib, caches, lnfold, ops
 
 __all__ = ["feed_forward", "layer_norm", "linear", "install_feed_forward", "uninstall_feed_forward"]
 
@@ -165,9 +165,12 @@ class _LayerNormFn(torch.autograd.Function):
             _cast_grad(dbeta, beta) if (need_b and beta is not None) else None, None
 
 
-def feed_forward(ff, hidden_states: torch.Tensor, scale: float = 1.0, residual: Optional[torch.Tensor] = None) -> torch.Tensor:
+def feed_forward(ff, hidden_states: torch.Tensor, scale: float = 1.0, residual: Optional[torch.Tensor] = None,
+                 pre_norm=None) -> torch.Tensor:
     """`ff(hidden_states)` of a FeedForward module with GEGLU activation; `residual` (same shape as the output)
-    is added in the second GEMM's epilogue (the blocks' `ff_output + hidden_states`)."""
+    is added in the second GEMM's epilogue (the blocks' `ff_output + hidden_states`).
+    `pre_norm` (an nn.LayerNorm): computes `ff(pre_norm(hidden_states))`; on the no-grad path the LayerNorm is folded
+    into the first GEMM (lnfold.py) and the normalised rows never reach HBM."""
     if not _is_feed_forward(ff):
         raise _lib.TviError(_lib.TVI_ERR_UNSUPPORTED, "feed_forward: expected a FeedForward module with a GEGLU projection")
     if getattr(ff.net[0].proj, "lora_layer", None) is not None or getattr(ff.net[2], "lora_layer", None) is not None:
@@ -182,14 +185,25 @@ def feed_forward(ff, hidden_states: torch.Tensor, scale: float = 1.0, residual: 
         raise _lib.TviError(_lib.TVI_ERR_UNSUPPORTED, f"feed_forward: hidden_states is {x.dtype}; the libtvi path is bf16")
     on_tape = torch.is_grad_enabled() and (x.requires_grad or any(p.requires_grad for p in ff.parameters()))
     caches.note_call(on_tape)
+    if pre_norm is not None and torch.is_grad_enabled() and any(p.requires_grad for p in pre_norm.parameters()):
+        on_tape = True
     if on_tape:
         # training: the call goes on the autograd tape; the residual add has no fused backward and is added on the tape
+        if pre_norm is not None:
+            x = layer_norm(pre_norm, x)
         proj, out_lin = ff.net[0].proj, ff.net[2]
         y = _FeedForwardFn.apply(x, proj.weight, proj.bias, out_lin.weight, out_lin.bias)
         return y if residual is None else y + residual
     x = x.contiguous()
     wi, bi = _geglu_weights(ff.net[0].proj)
-    h = ops.gemm_bf16_tn_ex(x.view(x.numel() // x.shape[-1], x.shape[-1]), wi, bi, geglu=True)
+    x2 = x.view(x.numel() // x.shape[-1], x.shape[-1])
+    if pre_norm is not None and lnfold.supported(pre_norm, x):
+        wg, colsum, cb = lnfold.folded(ff.net[0].proj, "geglu", wi, bi, pre_norm)
+        h = ops.gemm_bf16_tn_ln(x2, wg, cb, colsum, ops.layernorm_stats(x2, float(pre_norm.eps)), geglu=True)
+    else:
+        if pre_norm is not None:
+            x2 = layer_norm(pre_norm, x2)
+        h = ops.gemm_bf16_tn_ex(x2, wi, bi, geglu=True)
     out_lin = ff.net[2]
     r2 = None
     if residual is not None:

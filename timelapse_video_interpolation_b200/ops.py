@@ -21,9 +21,19 @@ def _stream() -> int:
 
 
 def _need_cuda(*ts):
+    """Every tensor of a call must live on the CURRENT CUDA device: the launch goes to torch's current stream of the
+    current device, so a tensor of another GPU would be read through a stream / context that does not own it."""
+    cur = None
     for t in ts:
-        if t is not None and not t.is_cuda:
+        if t is None:
+            continue
+        if not t.is_cuda:
             raise _lib.TviError(_lib.TVI_ERR_INVALID, "libtvi operates on CUDA tensors only (there is no CPU fallback)")
+        if cur is None:
+            cur = torch.cuda.current_device()
+        if t.device.index != cur:
+            raise _lib.TviError(_lib.TVI_ERR_INVALID, f"tensor on cuda:{t.device.index} while the current device is cuda:{cur}: "
+                                                      "call under torch.cuda.device(tensor.device) (one process per GPU sets it once)")
 
 
 def _rows2d(t: torch.Tensor, what: str):
@@ -108,6 +118,54 @@ def gemm_bf16_tn_ex(x: torch.Tensor, w: torch.Tensor, bias: torch.Tensor | None 
     _hooked("gemm_bf16_tn_ex", 1, _lib.load().tvi_gemm_bf16_tn_ex, x.data_ptr(), w.data_ptr(),
             bias.data_ptr() if bias is not None else None, residual.data_ptr() if residual is not None else None,
             out.data_ptr(), M, N, K, ldx, ldw, ldr, ldy, _lib.EPILOGUE_GEGLU if geglu else _lib.EPILOGUE_NONE, _stream())
+    return out
+
+
+def layernorm_stats_supported(C: int) -> bool:
+    return bool(_lib.load().tvi_layernorm_stats_supported(int(C)))
+
+
+def layernorm_stats(x: torch.Tensor, eps: float) -> torch.Tensor:
+    """(mean, rstd) of every row of x[..., C] as fp32 [M, 2]: the read-only half of a LayerNorm whose affine map runs in
+    the epilogue of gemm_bf16_tn_ln."""
+    _need_cuda(x)
+    x, ldx = _rows2d(x, "x")
+    C = x.shape[-1]
+    M = x.numel() // C if C else 0
+    stats = torch.empty(M, 2, dtype=torch.float32, device=x.device)
+    _hooked("layernorm_stats", 1, _lib.load().tvi_layernorm_stats_f32, x.data_ptr(), stats.data_ptr(), M, C, ldx, float(eps), _stream())
+    return stats
+
+
+def gemm_bf16_tn_ln(x: torch.Tensor, wg: torch.Tensor, bias: torch.Tensor, colsum: torch.Tensor, stats: torch.Tensor,
+                    residual: torch.Tensor | None = None, geglu: bool = False, out: torch.Tensor | None = None) -> torch.Tensor:
+    """y = LayerNorm(x) @ w^T + b computed from the RAW rows x: wg = gamma * w (bf16), colsum = wg.float().sum(1),
+    bias = w @ beta + b, stats = layernorm_stats(x); optional GEGLU / residual as gemm_bf16_tn_ex."""
+    _need_cuda(x, wg, bias, colsum, stats, residual)
+    x, ldx = _rows2d(x, "x")
+    wg, ldw = _rows2d(wg, "wg")
+    K, N = x.shape[-1], wg.shape[0]
+    if wg.shape[1] != K:
+        raise _lib.TviError(_lib.TVI_ERR_INVALID, f"gemm: x has K={K}, wg has K={wg.shape[1]}")
+    n_out = N // 2 if geglu else N
+    M = x.numel() // K if K else 0
+    if out is None:
+        out = torch.empty(*x.shape[:-1], n_out, dtype=torch.bfloat16, device=x.device)
+    out, ldy = _rows2d(out, "out")
+    ldr = 0
+    if residual is not None:
+        residual, ldr = _rows2d(residual, "residual")
+        if residual.shape[-1] != n_out or residual.numel() != M * n_out:
+            raise _lib.TviError(_lib.TVI_ERR_INVALID, "gemm: residual must have the shape of the output")
+    if bias.dtype != torch.bfloat16 or not bias.is_contiguous() or bias.numel() != N:
+        raise _lib.TviError(_lib.TVI_ERR_INVALID, "gemm: bias must be a contiguous bf16 vector of length N")
+    if colsum.dtype != torch.float32 or not colsum.is_contiguous() or colsum.numel() != N:
+        raise _lib.TviError(_lib.TVI_ERR_INVALID, "gemm: colsum must be a contiguous fp32 vector of length N")
+    if stats.dtype != torch.float32 or not stats.is_contiguous() or stats.numel() != 2 * M:
+        raise _lib.TviError(_lib.TVI_ERR_INVALID, "gemm: stats must be a contiguous fp32 [M, 2] tensor")
+    _hooked("gemm_bf16_tn_ln", 1, _lib.load().tvi_gemm_bf16_tn_ln, x.data_ptr(), wg.data_ptr(), bias.data_ptr(), colsum.data_ptr(),
+            stats.data_ptr(), residual.data_ptr() if residual is not None else None, out.data_ptr(), M, N, K, ldx, ldw, ldr, ldy,
+            _lib.EPILOGUE_GEGLU if geglu else _lib.EPILOGUE_NONE, _stream())
     return out
 
 

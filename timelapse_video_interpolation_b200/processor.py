@@ -118,13 +118,15 @@ class TviAttnProcessor:
     def __call__(self, attn, hidden_states: torch.Tensor, encoder_hidden_states: Optional[torch.Tensor] = None,
                  attention_mask: Optional[torch.Tensor] = None, temb: Optional[torch.Tensor] = None,
                  scale: float = 1.0, *args, residual: Optional[torch.Tensor] = None, frames: Optional[int] = None,
-                 **kwargs) -> torch.Tensor:
+                 pre_norm=None, **kwargs) -> torch.Tensor:
         """libtvi extensions used by the block-level forwards of blocks.py:
         `residual` — a tensor of the output's shape added in the out-projection epilogue, i.e. the caller's
         `attn_output + hidden_states`;
         `frames` = T — hidden_states is [B*T, S, C] in the spatial token order and attention runs over the T tokens of
         every (b, s) (encoder_hidden_states: the temporal [B*S, L, Ckv] context): the temporal block without its two
-        permute copies (src/models/attention.py:436-438, :474-476).  Inference only."""
+        permute copies (src/models/attention.py:436-438, :474-476).  Inference only.
+        `pre_norm` — the nn.LayerNorm the block applies in front of this attention: hidden_states is then the
+        UN-normalised input and the LayerNorm is folded into the query-side projection (lnfold.py)."""
         self._check(attn, hidden_states, attention_mask)
         in_dtype = hidden_states.dtype
         if in_dtype != torch.bfloat16:
@@ -161,7 +163,7 @@ class TviAttnProcessor:
             residual = residual.to(torch.bfloat16).contiguous()
         if frames is not None and (frames < 1 or x.shape[0] % frames != 0):
             raise _lib.TviError(_lib.TVI_ERR_INVALID, "frames must divide the batch dimension of hidden_states")
-        y = attention_forward(self, attn, x, e, heads, float(attn.scale), wo, bo, bias, stats, residual, frames)
+        y = attention_forward(self, attn, x, e, heads, float(attn.scale), wo, bo, bias, stats, residual, frames, pre_norm)
 
         if stats is not None:
             self.stats_sink(stats, attn)

@@ -5,6 +5,9 @@ from pathlib import Path
 sys.path.insert(0, str(Path(__file__).resolve().parents[1]))
 import torch
 from timelapse_video_interpolation_b200 import ops, _lib
+import os
+if os.environ.get("PROF_LIB"):  # a tuning build (tools/micro/build_tune.sh)
+    _lib.LIB_PATH = Path(os.environ["PROF_LIB"]).resolve()
 dev = torch.device("cuda:0")
 import os
 M, C = int(os.environ.get("PROF_M", 258048)), int(os.environ.get("PROF_C", 320))
