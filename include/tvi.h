@@ -161,6 +161,25 @@ int tvi_tokens_to_nchw_add_bf16(const tvi_bf16* y, const tvi_bf16* residual, tvi
 int tvi_blend_rows_bf16(const tvi_bf16* x_spatial, const tvi_bf16* x_temporal, const float* alpha, tvi_bf16* out,
                         int64_t nrows, int64_t rows_per_group, int C, int64_t lds, int64_t ldt, int64_t ldo, void* stream);
 
+/* Backward of the three glue kernels above — what autograd derives for F.group_norm + permute
+ * (src/models/transformer_temporal.py:300-304), the permute + residual of :354-357 and AlphaBlender.forward (:349-351)
+ * when src/train.py back-propagates through TransformerSpatioTemporalModel.forward.  All deterministic (fixed-order sums).
+ *   tvi_nchw_to_tokens_bf16        y[n, s, c] = x[n, c, s]: d tokens of tvi_tokens_to_nchw_add_bf16 (d residual = d out).
+ *   tvi_groupnorm_tokens_bwd_bf16  x [N, C, HW] (the forward input), dn [N, HW, C] (lddn) -> dx [N, C, HW] (nullable),
+ *                                  dgamma, dbeta [C] bf16 (nullable).  workspace = ..._bwd_workspace_bytes(N, C, HW, groups).
+ *   tvi_blend_rows_bwd_bf16        dy -> dx_spatial = alpha dy, dx_temporal = (1 - alpha) dy (row stride ld for all);
+ *                                  dalpha_partial (nullable): [frames][tvi_blend_rows_bwd_blocks(rows_per_group, C)] fp32
+ *                                  partial sums of dy (x_spatial - x_temporal); the caller adds each frame's row in order. */
+int tvi_nchw_to_tokens_bf16(const tvi_bf16* x, tvi_bf16* y, int64_t N, int C, int HW, int64_t ldy, void* stream);
+size_t tvi_groupnorm_tokens_bwd_workspace_bytes(int64_t N, int C, int HW, int groups);
+int tvi_groupnorm_tokens_bwd_bf16(const tvi_bf16* x, const tvi_bf16* dn, const tvi_bf16* gamma, tvi_bf16* dx, tvi_bf16* dgamma,
+                                  tvi_bf16* dbeta, void* workspace, int64_t N, int C, int HW, int groups, int64_t lddn, float eps,
+                                  void* stream);
+int tvi_blend_rows_bwd_blocks(int64_t rows_per_group, int C);
+int tvi_blend_rows_bwd_bf16(const tvi_bf16* dy, const tvi_bf16* x_spatial, const tvi_bf16* x_temporal, const float* alpha,
+                            tvi_bf16* dx_spatial, tvi_bf16* dx_temporal, float* dalpha_partial, int64_t frames,
+                            int64_t rows_per_group, int C, int64_t ld, void* stream);
+
 /* Per-denoising-step glue of the pipeline loop (row N4 of SURVEY 8.6), one launch per step:
  *   cfg_euler_step : per-frame classifier-free guidance `uncond + guidance[b, t] * (cond - uncond)`
  *       (src/pipelines/pipeline_stable_video_diffusion_efficient_interp.py:565-566), EulerDiscreteScheduler.step with

@@ -228,8 +228,8 @@ def test_layernorm_folded_into_the_gemm(cuda, M, C, N, geglu, res):
     assert float((stats[:, 1].cpu() * torch.sqrt(xf.var(1, unbiased=False) + norm.eps) - 1).abs().max()) < 1e-4
     wg, colsum, cb = lnfold.folded(lin, "t", w, b, norm)
     y = ops.gemm_bf16_tn_ln(x, wg, cb, colsum, stats, residual=r, geglu=geglu)
-    n_ref = F.layer_norm(xf, (C,), norm.weight.float().cpu(), norm.bias.float().cpu(), norm.eps)
-    ref = F.linear(n_ref, lin.weight.float().cpu(), lin.bias.float().cpu())
+    n_ref = F.layer_norm(xf, (C,), norm.weight.detach().float().cpu(), norm.bias.detach().float().cpu(), norm.eps)
+    ref = F.linear(n_ref, lin.weight.detach().float().cpu(), lin.bias.detach().float().cpu())
     if geglu:
         ref = ref[:, :N // 2] * F.gelu(ref[:, N // 2:])
     if res:

@@ -68,6 +68,46 @@ def test_blend_rows(cuda):
         ops.blend_rows(xs, xt, alpha[:5].contiguous(), S)
 
 
+@pytest.mark.parametrize("N,C,H,W,groups", [(3, 320, 8, 16, 32), (2, 64, 4, 6, 32), (1, 640, 24, 40, 32), (2, 96, 10, 12, 4)])
+def test_groupnorm_tokens_backward(cuda, N, C, H, W, groups):
+    g = torch.Generator().manual_seed(C + W)
+    x = _bf(torch.randn(N, C, H, W, generator=g) * 1.5 + 0.4, cuda)
+    gamma, beta = _bf(1 + 0.3 * torch.randn(C, generator=g), cuda), _bf(0.2 * torch.randn(C, generator=g), cuda)
+    dn = _bf(torch.randn(N, H * W, C, generator=g), cuda)
+    dx, dg, db = ops.groupnorm_tokens_bwd(x, dn, gamma, groups, 1e-6)
+    xr = x.float().cpu().requires_grad_(True)
+    gr, br = gamma.float().cpu().requires_grad_(True), beta.float().cpu().requires_grad_(True)
+    y = F.group_norm(xr, groups, gr, br, 1e-6).permute(0, 2, 3, 1).reshape(N, H * W, C)
+    (y * dn.float().cpu()).sum().backward()
+    for name, got, ref in (("dx", dx, xr.grad), ("dgamma", dg, gr.grad), ("dbeta", db, br.grad)):
+        err, scale = float((got.float().cpu() - ref).abs().max()), float(ref.abs().max())
+        print(f"  {name}: max abs err {err:.3e} / max |ref| {scale:.3e}")
+        assert err <= 2e-2 * scale, name
+    # only what is asked for is produced; identical values
+    dx2, dg2, db2 = ops.groupnorm_tokens_bwd(x, dn, gamma, groups, 1e-6, need_affine=False)
+    assert dg2 is None and db2 is None and torch.equal(dx2, dx)
+    dx3, dg3, _ = ops.groupnorm_tokens_bwd(x, dn, gamma, groups, 1e-6, need_dx=False)
+    assert dx3 is None and torch.equal(dg3, dg)
+    assert torch.equal(ops.nchw_to_tokens(x), x.permute(0, 2, 3, 1).reshape(N, H * W, C))
+
+
+def test_blend_rows_backward(cuda):
+    g = torch.Generator().manual_seed(8)
+    BF, S, C = 5, 70, 320
+    xs, xt, dy = (_bf(torch.randn(BF * S, C, generator=g), cuda) for _ in range(3))
+    alpha = torch.tensor([0.3, 1.0, 0.0, 0.7310, 0.5], device=cuda)
+    dxs, dxt, da = ops.blend_rows_bwd(dy, xs, xt, alpha, S, True)
+    a = alpha.view(BF, 1, 1).cpu()
+    d3 = dy.float().cpu().view(BF, S, C)
+    assert float((dxs.float().cpu().view(BF, S, C) - a * d3).abs().max()) <= 2 ** -7 * 4
+    assert float((dxt.float().cpu().view(BF, S, C) - (1 - a) * d3).abs().max()) <= 2 ** -7 * 4
+    ref = (d3 * (xs.float().cpu() - xt.float().cpu()).view(BF, S, C)).sum(dim=(1, 2))
+    assert float((da.cpu() - ref).abs().max()) <= 1e-3 * float(ref.abs().max())
+    dxs2, dxt2, da2 = ops.blend_rows_bwd(dy, None, None, alpha, S, False)
+    assert da2 is None and torch.equal(dxs2, dxs) and torch.equal(dxt2, dxt)
+    assert torch.equal(dxs[S:2 * S], dy[S:2 * S]) and not dxt[S:2 * S].any()      # image-only frame: all of dy goes to the spatial branch
+
+
 def _model(C, heads, cross, seed, cuda, head_dim=64):
     m = TransformerSpatioTemporalModel(heads, head_dim, in_channels=C, num_layers=1, cross_attention_dim=cross)
     g = torch.Generator().manual_seed(seed)
@@ -190,10 +230,18 @@ def test_model_forward_trains(cuda, ckpt):
     ind = torch.zeros(B, T, device=cuda)
     ind[0, 1] = 1.0
     launches0 = ops.LAUNCHES
-    y = m(x, encoder_hidden_states=e, image_only_indicator=ind, return_dict=False)[0]
-    assert y.requires_grad and y.shape == x.shape
-    (y.float() * wgt.float()).sum().backward()
+    seen = []
+    ops.EVENT_HOOK = lambda name, start: seen.append(name) if start else None
+    try:
+        y = m(x, encoder_hidden_states=e, image_only_indicator=ind, return_dict=False)[0]
+        assert y.requires_grad and y.shape == x.shape
+        (y.float() * wgt.float()).sum().backward()
+    finally:
+        ops.EVENT_HOOK = None
     torch.cuda.synchronize()
+    for name in ("groupnorm_tokens", "groupnorm_tokens_bwd", "tokens_to_nchw_add", "nchw_to_tokens", "blend_rows", "blend_rows_bwd",
+                 "bcast_rows_add", "colsum_bf16"):
+        assert name in seen, name                   # the glue runs on libtvi kernels in both directions
     assert ops.LAUNCHES - launches0 >= 100          # the GEMMs, LayerNorms, attention cores and their backward kernels
     P = {n: p.detach().float().cpu().requires_grad_(True) for n, p in m.named_parameters()}
     xr = x.detach().float().cpu().requires_grad_(True)

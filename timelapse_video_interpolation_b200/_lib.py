@@ -48,6 +48,11 @@ SIGNATURES = {
     "tvi_groupnorm_tokens_workspace_bytes": (_sz, [_i64, _i32, _i32, _i32]),
     "tvi_groupnorm_tokens_bf16": (_i32, [_ptr, _ptr, _ptr, _ptr, _ptr, _i64, _i32, _i32, _i32, _i64, _f32, _ptr]),
     "tvi_tokens_to_nchw_add_bf16": (_i32, [_ptr, _ptr, _ptr, _i64, _i32, _i32, _i64, _ptr]),
+    "tvi_nchw_to_tokens_bf16": (_i32, [_ptr, _ptr, _i64, _i32, _i32, _i64, _ptr]),
+    "tvi_groupnorm_tokens_bwd_workspace_bytes": (_sz, [_i64, _i32, _i32, _i32]),
+    "tvi_groupnorm_tokens_bwd_bf16": (_i32, [_ptr, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr, _i64, _i32, _i32, _i32, _i64, _f32, _ptr]),
+    "tvi_blend_rows_bwd_blocks": (_i32, [_i64, _i32]),
+    "tvi_blend_rows_bwd_bf16": (_i32, [_ptr, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr, _i64, _i64, _i32, _i64, _ptr]),
     "tvi_blend_rows_bf16": (_i32, [_ptr, _ptr, _ptr, _ptr, _i64, _i64, _i32, _i64, _i64, _i64, _ptr]),
     "tvi_cfg_euler_step_f32": (_i32, [_ptr, _ptr, _ptr, _ptr, _i64, _i32, _i32, _i32, _i64, _i64, _f32, _f32, _i32, _ptr]),
     "tvi_model_input_bf16": (_i32, [_ptr, _ptr, _ptr, _i64, _i32, _i32, _i64, _f32, _ptr]),

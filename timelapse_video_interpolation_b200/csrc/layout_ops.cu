@@ -72,7 +72,9 @@ groupnorm_stats_kernel(const tvi_bf16* __restrict__ x, double2* __restrict__ par
   }
 }
 
-// y[n, s, c] = (x[n, c, s] - mean[n, g(c)]) * rstd[n, g(c)] * gamma[c] + beta[c]
+// y[n, s, c] = (x[n, c, s] - mean[n, g(c)]) * rstd[n, g(c)] * gamma[c] + beta[c];  kNorm = false: the bare NCHW -> token-major
+// transpose (backward of tokens_to_nchw_add: d tokens = transpose(d out))
+template <bool kNorm>
 __global__ void __launch_bounds__(256)
 groupnorm_tokens_kernel(const tvi_bf16* __restrict__ x, const double2* __restrict__ partial, const tvi_bf16* __restrict__ gamma,
                         const tvi_bf16* __restrict__ beta, tvi_bf16* __restrict__ y, int C, int HW, int groups, int nsplit,
@@ -84,8 +86,8 @@ groupnorm_tokens_kernel(const tvi_bf16* __restrict__ x, const double2* __restric
   const int cpg = C / groups;
   if (threadIdx.x < kTile) {
     const int c = c0 + threadIdx.x;
-    float sc = 0.f, sh = 0.f;
-    if (c < C) {
+    float sc = kNorm ? 0.f : 1.f, sh = 0.f;
+    if (kNorm && c < C) {
       const int g = c / cpg;
       const double2* pp = partial + ((int64_t)n * groups + g) * nsplit;
       double a = 0.0, b = 0.0;
@@ -194,6 +196,204 @@ blend_rows_kernel(const tvi_bf16* __restrict__ xs, const tvi_bf16* __restrict__ 
   *(reinterpret_cast<uint4*>(out + r * ldo) + c) = make_uint4(o[0], o[1], o[2], o[3]);
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// Backward of the glue (training through the module-level swap, src/train.py back-propagates through
+// transformer_temporal.py:300-304, :349-357).  With xhat = (x - mean) rstd per (image, group) and g = dn * gamma:
+//   dx = rstd * (g - mean_grp(g) - xhat * mean_grp(g xhat)),  dgamma_c = sum_{n,s} dn xhat,  dbeta_c = sum_{n,s} dn.
+// Per (image, channel) A = sum_s dn and B = sum_s dn x give every group mean and both parameter gradients, so the
+// backward is: statistics of x (forward kernel), one tile pass for A / B (fp32 partials per spatial tile, summed in a
+// fixed order: deterministic, no atomics), one tile pass that writes dx = k1_c dn + k2_c x + k3_c in NCHW.
+// ---------------------------------------------------------------------------------------------------------------
+__global__ void gn_stats_finalize_kernel(const double2* __restrict__ partial, float2* __restrict__ mr, int64_t ngroups, int nsplit,
+                                         double cnt, float eps) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= ngroups) return;
+  double a = 0.0, b = 0.0;
+  for (int k = 0; k < nsplit; ++k) {
+    a += partial[i * nsplit + k].x;
+    b += partial[i * nsplit + k].y;
+  }
+  const double mean = a / cnt;
+  double var = b / cnt - mean * mean;
+  if (var < 0.0) var = 0.0;
+  mr[i] = make_float2((float)mean, (float)(1.0 / sqrt(var + (double)eps)));
+}
+
+// partial[((n * s_tiles + st) * C + c)] = (sum_s dn[n, s, c], sum_s dn[n, s, c] x[n, c, s]) over the 64 positions of tile st
+__global__ void __launch_bounds__(256)
+gn_bwd_reduce_kernel(const tvi_bf16* __restrict__ x, const tvi_bf16* __restrict__ dn, float2* __restrict__ partial, int C, int HW,
+                     int64_t lddn) {
+  __shared__ __align__(16) __nv_bfloat16 tile[kTile][kPitch];  // dn as [spatial][channel]
+  const int n = blockIdx.z;
+  const int c0 = blockIdx.y * kTile, s0 = blockIdx.x * kTile;
+  const int chunk = threadIdx.x & 7;
+#pragma unroll
+  for (int j = 0; j < 2; ++j) {
+    const int sl = (threadIdx.x >> 3) + 32 * j;
+    const int sp = s0 + sl, c = c0 + chunk * 8;
+    uint4 u = make_uint4(0, 0, 0, 0);
+    if (sp < HW && c < C) u = __ldg(reinterpret_cast<const uint4*>(dn + ((int64_t)n * HW + sp) * lddn + c));
+    *reinterpret_cast<uint4*>(&tile[sl][chunk * 8]) = u;
+  }
+  __syncthreads();
+#pragma unroll
+  for (int j = 0; j < 2; ++j) {
+    const int cl = (threadIdx.x >> 3) + 32 * j;
+    const int c = c0 + cl, sp = s0 + chunk * 8;
+    float a = 0.f, b = 0.f;
+    if (c < C && sp < HW) {
+      float f[8];
+      unpack8f(__ldg(reinterpret_cast<const uint4*>(x + ((int64_t)n * C + c) * HW + sp)), f);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        const float d = __bfloat162float(tile[chunk * 8 + i][cl]);
+        a += d;
+        b = fmaf(d, f[i], b);
+      }
+    }
+#pragma unroll
+    for (int o = 1; o < 8; o <<= 1) {  // the 8 chunks of a channel are 8 consecutive lanes
+      a += __shfl_xor_sync(0xffffffffu, a, o);
+      b += __shfl_xor_sync(0xffffffffu, b, o);
+    }
+    if (chunk == 0 && c < C) partial[((int64_t)n * gridDim.x + blockIdx.x) * C + c] = make_float2(a, b);
+  }
+}
+
+// ab[n * C + c] = sum over the spatial tiles, in order
+__global__ void gn_bwd_finalize_kernel(const float2* __restrict__ partial, float2* __restrict__ ab, int64_t N, int C, int s_tiles) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= N * C) return;
+  const int64_t n = i / C;
+  const int c = (int)(i - n * C);
+  float a = 0.f, b = 0.f;
+  for (int t = 0; t < s_tiles; ++t) {
+    const float2 v = partial[(n * s_tiles + t) * C + c];
+    a += v.x;
+    b += v.y;
+  }
+  ab[i] = make_float2(a, b);
+}
+
+__global__ void gn_bwd_params_kernel(const float2* __restrict__ ab, const float2* __restrict__ mr, tvi_bf16* __restrict__ dgamma,
+                                     tvi_bf16* __restrict__ dbeta, int64_t N, int C, int groups) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= C) return;
+  const int g = c / (C / groups);
+  float dg = 0.f, db = 0.f;
+  for (int64_t n = 0; n < N; ++n) {
+    const float2 v = ab[n * C + c];
+    const float2 m = mr[n * groups + g];
+    dg += m.y * (v.y - m.x * v.x);
+    db += v.x;
+  }
+  if (dgamma != nullptr) reinterpret_cast<__nv_bfloat16*>(dgamma)[c] = __float2bfloat16_rn(dg);
+  if (dbeta != nullptr) reinterpret_cast<__nv_bfloat16*>(dbeta)[c] = __float2bfloat16_rn(db);
+}
+
+// dx[n, c, s] = k1 dn[n, s, c] + k2 x[n, c, s] + k3 with k1 = rstd gamma_c, k2 = -rstd^2 m2, k3 = -rstd m1 + rstd^2 m2 mean,
+// m1 = mean_grp(gamma A), m2 = mean_grp(gamma rstd (B - mean A))
+__global__ void __launch_bounds__(256)
+gn_bwd_apply_kernel(const tvi_bf16* __restrict__ x, const tvi_bf16* __restrict__ dn, const tvi_bf16* __restrict__ gamma,
+                    const float2* __restrict__ ab, const float2* __restrict__ mr, tvi_bf16* __restrict__ dx, int C, int HW,
+                    int groups, int64_t lddn) {
+  __shared__ __align__(16) __nv_bfloat16 tile[kTile][kPitch];  // dn as [spatial][channel]
+  __shared__ float s_k1[kTile], s_k2[kTile], s_k3[kTile];
+  const int n = blockIdx.z;
+  const int c0 = blockIdx.y * kTile, s0 = blockIdx.x * kTile;
+  const int cpg = C / groups;
+  if (threadIdx.x < kTile) {
+    const int c = c0 + threadIdx.x;
+    float k1 = 0.f, k2 = 0.f, k3 = 0.f;
+    if (c < C) {
+      const int g = c / cpg;
+      const float2 m = mr[(int64_t)n * groups + g];
+      float s1 = 0.f, s2 = 0.f;
+      for (int j = g * cpg; j < (g + 1) * cpg; ++j) {
+        const float ga = gamma ? __bfloat162float(*reinterpret_cast<const __nv_bfloat16*>(gamma + j)) : 1.f;
+        const float2 v = ab[(int64_t)n * C + j];
+        s1 = fmaf(ga, v.x, s1);
+        s2 = fmaf(ga * m.y, v.y - m.x * v.x, s2);
+      }
+      const float inv = 1.f / ((float)cpg * (float)HW);
+      const float m1 = s1 * inv, m2 = s2 * inv;
+      const float ga = gamma ? __bfloat162float(*reinterpret_cast<const __nv_bfloat16*>(gamma + c)) : 1.f;
+      k1 = m.y * ga;
+      k2 = -m.y * m.y * m2;
+      k3 = -m.y * m1 - k2 * m.x;
+    }
+    s_k1[threadIdx.x] = k1;
+    s_k2[threadIdx.x] = k2;
+    s_k3[threadIdx.x] = k3;
+  }
+  const int chunk = threadIdx.x & 7;
+#pragma unroll
+  for (int j = 0; j < 2; ++j) {
+    const int sl = (threadIdx.x >> 3) + 32 * j;
+    const int sp = s0 + sl, c = c0 + chunk * 8;
+    uint4 u = make_uint4(0, 0, 0, 0);
+    if (sp < HW && c < C) u = __ldg(reinterpret_cast<const uint4*>(dn + ((int64_t)n * HW + sp) * lddn + c));
+    *reinterpret_cast<uint4*>(&tile[sl][chunk * 8]) = u;
+  }
+  __syncthreads();
+#pragma unroll
+  for (int j = 0; j < 2; ++j) {
+    const int cl = (threadIdx.x >> 3) + 32 * j;
+    const int c = c0 + cl, sp = s0 + chunk * 8;
+    if (c < C && sp < HW) {
+      const int64_t off = ((int64_t)n * C + c) * HW + sp;
+      float f[8], o[8];
+      unpack8f(__ldg(reinterpret_cast<const uint4*>(x + off)), f);
+      const float k1 = s_k1[cl], k2 = s_k2[cl], k3 = s_k3[cl];
+#pragma unroll
+      for (int i = 0; i < 8; ++i) o[i] = fmaf(k1, __bfloat162float(tile[chunk * 8 + i][cl]), fmaf(k2, f[i], k3));
+      *reinterpret_cast<uint4*>(dx + off) =
+          make_uint4(pack_bf16x2(o[0], o[1]), pack_bf16x2(o[2], o[3]), pack_bf16x2(o[4], o[5]), pack_bf16x2(o[6], o[7]));
+    }
+  }
+}
+
+// AlphaBlender backward: dxs = alpha dy, dxt = (1 - alpha) dy; dalpha[frame] = sum dy (xs - xt) as per-CTA fp32 partials
+// [frames][blocks_per_frame] (summed by the caller in a fixed order) when xs / xt are given
+__global__ void __launch_bounds__(256)
+blend_rows_bwd_kernel(const tvi_bf16* __restrict__ dy, const tvi_bf16* __restrict__ xs, const tvi_bf16* __restrict__ xt,
+                      const float* __restrict__ alpha, tvi_bf16* __restrict__ dxs, tvi_bf16* __restrict__ dxt,
+                      float* __restrict__ dalpha_partial, int64_t rows_per_group, int C8, int64_t ld) {
+  const int64_t frame = blockIdx.y;
+  const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;  // 16-byte chunk inside the frame
+  const bool act = idx < rows_per_group * C8;
+  const float a = __ldg(alpha + frame), b = 1.0f - a;
+  float acc = 0.f;
+  if (act) {
+    const int64_t r = frame * rows_per_group + idx / C8;
+    const int c = (int)(idx % C8);
+    float g[8];
+    unpack8f(__ldg(reinterpret_cast<const uint4*>(dy + r * ld) + c), g);
+    *(reinterpret_cast<uint4*>(dxs + r * ld) + c) = make_uint4(pack_bf16x2(a * g[0], a * g[1]), pack_bf16x2(a * g[2], a * g[3]),
+                                                               pack_bf16x2(a * g[4], a * g[5]), pack_bf16x2(a * g[6], a * g[7]));
+    *(reinterpret_cast<uint4*>(dxt + r * ld) + c) = make_uint4(pack_bf16x2(b * g[0], b * g[1]), pack_bf16x2(b * g[2], b * g[3]),
+                                                               pack_bf16x2(b * g[4], b * g[5]), pack_bf16x2(b * g[6], b * g[7]));
+    if (dalpha_partial != nullptr) {
+      float fs[8], ft[8];
+      unpack8f(__ldg(reinterpret_cast<const uint4*>(xs + r * ld) + c), fs);
+      unpack8f(__ldg(reinterpret_cast<const uint4*>(xt + r * ld) + c), ft);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) acc = fmaf(g[i], fs[i] - ft[i], acc);
+    }
+  }
+  if (dalpha_partial == nullptr) return;
+  __shared__ float red[8];
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = acc;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float t = 0.f;
+    for (int w = 0; w < 8; ++w) t += red[w];
+    dalpha_partial[frame * gridDim.x + blockIdx.x] = t;
+  }
+}
+
 int gn_splits(int64_t span) { return (int)((span + kGnSlice - 1) / kGnSlice); }
 
 }  // namespace
@@ -224,7 +424,7 @@ extern "C" int tvi_groupnorm_tokens_bf16(const tvi_bf16* x, const tvi_bf16* gamm
   groupnorm_stats_kernel<<<(unsigned)(N * groups * nsplit), 256, 0, st>>>(x, (double2*)workspace, span, nsplit);
   TVI_LAUNCH_OK("groupnorm_stats_kernel");
   dim3 grid((HW + kTile - 1) / kTile, (C + kTile - 1) / kTile, (unsigned)N);
-  groupnorm_tokens_kernel<<<grid, 256, 0, st>>>(x, (const double2*)workspace, gamma, beta, y, C, HW, groups, nsplit, ldy, eps);
+  groupnorm_tokens_kernel<true><<<grid, 256, 0, st>>>(x, (const double2*)workspace, gamma, beta, y, C, HW, groups, nsplit, ldy, eps);
   TVI_LAUNCH_OK("groupnorm_tokens_kernel");
   return TVI_OK;
 }
@@ -262,5 +462,118 @@ extern "C" int tvi_blend_rows_bf16(const tvi_bf16* x_spatial, const tvi_bf16* x_
   blend_rows_kernel<<<(unsigned)((total + 255) / 256), 256, 0, (cudaStream_t)stream>>>(x_spatial, x_temporal, alpha, out, nrows,
                                                                                        rows_per_group, C / 8, lds, ldt, ldo);
   TVI_LAUNCH_OK("blend_rows_kernel");
+  return TVI_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// backward entry points of the glue
+// ---------------------------------------------------------------------------------------------------------------
+extern "C" int tvi_nchw_to_tokens_bf16(const tvi_bf16* x, tvi_bf16* y, int64_t N, int C, int HW, int64_t ldy, void* stream) {
+  using namespace tvi;
+  TVI_CHECK_ARG(N >= 0 && C >= 0 && HW >= 0, "tvi_nchw_to_tokens_bf16: negative size");
+  if (N == 0 || C == 0 || HW == 0) return TVI_OK;
+  TVI_CHECK_ARG(x && y, "tvi_nchw_to_tokens_bf16: null pointer");
+  TVI_CHECK_ARG(C % 8 == 0 && HW % 8 == 0, "tvi_nchw_to_tokens_bf16: C=%d and H*W=%d must be multiples of 8", C, HW);
+  TVI_CHECK_ARG(ldy % 8 == 0 && ldy >= C, "tvi_nchw_to_tokens_bf16: bad output row stride");
+  TVI_CHECK_ARG(((uintptr_t)x | (uintptr_t)y) % 16 == 0, "tvi_nchw_to_tokens_bf16: pointers must be 16-byte aligned");
+  TVI_CHECK_ARG(N <= 65535, "tvi_nchw_to_tokens_bf16: more than 65535 images in one call");
+  dim3 grid((HW + kTile - 1) / kTile, (C + kTile - 1) / kTile, (unsigned)N);
+  groupnorm_tokens_kernel<false><<<grid, 256, 0, (cudaStream_t)stream>>>(x, nullptr, nullptr, nullptr, y, C, HW, 1, 0, ldy, 1.f);
+  TVI_LAUNCH_OK("groupnorm_tokens_kernel<transpose>");
+  return TVI_OK;
+}
+
+namespace tvi {
+namespace {
+struct GnBwdLayout {
+  size_t stats, mr, partial, ab, total;
+  int nsplit, s_tiles;
+};
+GnBwdLayout gn_bwd_layout(int64_t N, int C, int HW, int groups) {
+  GnBwdLayout l;
+  l.nsplit = gn_splits((int64_t)(C / groups) * HW);
+  l.s_tiles = (HW + kTile - 1) / kTile;
+  auto up = [](size_t v) { return (v + 255) & ~(size_t)255; };
+  l.stats = 0;
+  l.mr = up(l.stats + (size_t)N * groups * l.nsplit * sizeof(double2));
+  l.partial = up(l.mr + (size_t)N * groups * sizeof(float2));
+  l.ab = up(l.partial + (size_t)N * l.s_tiles * C * sizeof(float2));
+  l.total = up(l.ab + (size_t)N * C * sizeof(float2));
+  return l;
+}
+}  // namespace
+}  // namespace tvi
+
+extern "C" size_t tvi_groupnorm_tokens_bwd_workspace_bytes(int64_t N, int C, int HW, int groups) {
+  if (N <= 0 || C <= 0 || HW <= 0 || groups <= 0 || C % groups != 0) return 0;
+  return tvi::gn_bwd_layout(N, C, HW, groups).total;
+}
+
+extern "C" int tvi_groupnorm_tokens_bwd_bf16(const tvi_bf16* x, const tvi_bf16* dn, const tvi_bf16* gamma, tvi_bf16* dx,
+                                             tvi_bf16* dgamma, tvi_bf16* dbeta, void* workspace, int64_t N, int C, int HW,
+                                             int groups, int64_t lddn, float eps, void* stream) {
+  using namespace tvi;
+  TVI_CHECK_ARG(N >= 0 && C >= 0 && HW >= 0, "tvi_groupnorm_tokens_bwd_bf16: negative size");
+  if (N == 0 || C == 0 || HW == 0) return TVI_OK;
+  TVI_CHECK_ARG(x && dn && workspace, "tvi_groupnorm_tokens_bwd_bf16: null pointer");
+  TVI_CHECK_ARG(dx || dgamma || dbeta, "tvi_groupnorm_tokens_bwd_bf16: no gradient requested");
+  TVI_CHECK_ARG(groups >= 1 && C % groups == 0, "tvi_groupnorm_tokens_bwd_bf16: C=%d is not a multiple of groups=%d", C, groups);
+  TVI_CHECK_ARG(C % 8 == 0 && HW % 8 == 0, "tvi_groupnorm_tokens_bwd_bf16: C=%d and H*W=%d must be multiples of 8", C, HW);
+  TVI_CHECK_ARG(lddn % 8 == 0 && lddn >= C, "tvi_groupnorm_tokens_bwd_bf16: bad row stride of dn");
+  TVI_CHECK_ARG(((uintptr_t)x | (uintptr_t)dn | (uintptr_t)dx | (uintptr_t)workspace) % 16 == 0,
+                "tvi_groupnorm_tokens_bwd_bf16: pointers must be 16-byte aligned");
+  TVI_CHECK_ARG(eps > 0.f, "tvi_groupnorm_tokens_bwd_bf16: eps must be positive");
+  TVI_CHECK_ARG(N <= 65535, "tvi_groupnorm_tokens_bwd_bf16: more than 65535 images in one call");
+  const GnBwdLayout l = gn_bwd_layout(N, C, HW, groups);
+  TVI_CHECK_ARG(N * groups * l.nsplit < ((int64_t)1 << 31), "tvi_groupnorm_tokens_bwd_bf16: grid too large");
+  uint8_t* ws = (uint8_t*)workspace;
+  double2* stats = (double2*)(ws + l.stats);
+  float2* mr = (float2*)(ws + l.mr);
+  float2* partial = (float2*)(ws + l.partial);
+  float2* ab = (float2*)(ws + l.ab);
+  cudaStream_t st = (cudaStream_t)stream;
+  const int64_t span = (int64_t)(C / groups) * HW;
+  groupnorm_stats_kernel<<<(unsigned)(N * groups * l.nsplit), 256, 0, st>>>(x, stats, span, l.nsplit);
+  TVI_LAUNCH_OK("groupnorm_stats_kernel");
+  gn_stats_finalize_kernel<<<(unsigned)((N * groups + 127) / 128), 128, 0, st>>>(stats, mr, N * groups, l.nsplit, (double)span, eps);
+  TVI_LAUNCH_OK("gn_stats_finalize_kernel");
+  dim3 grid((unsigned)l.s_tiles, (C + kTile - 1) / kTile, (unsigned)N);
+  gn_bwd_reduce_kernel<<<grid, 256, 0, st>>>(x, dn, partial, C, HW, lddn);
+  TVI_LAUNCH_OK("gn_bwd_reduce_kernel");
+  gn_bwd_finalize_kernel<<<(unsigned)((N * C + 255) / 256), 256, 0, st>>>(partial, ab, N, C, l.s_tiles);
+  TVI_LAUNCH_OK("gn_bwd_finalize_kernel");
+  if (dgamma != nullptr || dbeta != nullptr) {
+    gn_bwd_params_kernel<<<(C + 127) / 128, 128, 0, st>>>(ab, mr, dgamma, dbeta, N, C, groups);
+    TVI_LAUNCH_OK("gn_bwd_params_kernel");
+  }
+  if (dx != nullptr) {
+    gn_bwd_apply_kernel<<<grid, 256, 0, st>>>(x, dn, gamma, ab, mr, dx, C, HW, groups, lddn);
+    TVI_LAUNCH_OK("gn_bwd_apply_kernel");
+  }
+  return TVI_OK;
+}
+
+extern "C" int tvi_blend_rows_bwd_blocks(int64_t rows_per_group, int C) {
+  if (rows_per_group <= 0 || C <= 0) return 0;
+  return (int)((rows_per_group * (C / 8) + 255) / 256);
+}
+
+extern "C" int tvi_blend_rows_bwd_bf16(const tvi_bf16* dy, const tvi_bf16* x_spatial, const tvi_bf16* x_temporal, const float* alpha,
+                                       tvi_bf16* dx_spatial, tvi_bf16* dx_temporal, float* dalpha_partial, int64_t frames,
+                                       int64_t rows_per_group, int C, int64_t ld, void* stream) {
+  using namespace tvi;
+  TVI_CHECK_ARG(frames >= 0 && rows_per_group >= 0 && C >= 0, "tvi_blend_rows_bwd_bf16: negative size");
+  if (frames == 0 || rows_per_group == 0 || C == 0) return TVI_OK;
+  TVI_CHECK_ARG(dy && alpha && dx_spatial && dx_temporal, "tvi_blend_rows_bwd_bf16: null pointer");
+  TVI_CHECK_ARG(dalpha_partial == nullptr || (x_spatial && x_temporal), "tvi_blend_rows_bwd_bf16: dalpha needs x_spatial and x_temporal");
+  TVI_CHECK_ARG(C % 8 == 0 && ld % 8 == 0 && ld >= C, "tvi_blend_rows_bwd_bf16: C and the row stride must be multiples of 8");
+  TVI_CHECK_ARG(((uintptr_t)dy | (uintptr_t)x_spatial | (uintptr_t)x_temporal | (uintptr_t)dx_spatial | (uintptr_t)dx_temporal) % 16 == 0 &&
+                    ((uintptr_t)alpha | (uintptr_t)dalpha_partial) % 4 == 0,
+                "tvi_blend_rows_bwd_bf16: pointers must be 16-byte aligned");
+  TVI_CHECK_ARG(frames <= 65535, "tvi_blend_rows_bwd_bf16: more than 65535 frames in one call");
+  dim3 grid((unsigned)tvi_blend_rows_bwd_blocks(rows_per_group, C), (unsigned)frames);
+  blend_rows_bwd_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(dy, x_spatial, x_temporal, alpha, dx_spatial, dx_temporal,
+                                                                dalpha_partial, rows_per_group, C / 8, ld);
+  TVI_LAUNCH_OK("blend_rows_bwd_kernel");
   return TVI_OK;
 }

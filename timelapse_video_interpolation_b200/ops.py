@@ -232,6 +232,65 @@ def groupnorm_tokens(x: torch.Tensor, gamma, beta, groups: int, eps: float, out:
     return out
 
 
+def nchw_to_tokens(x: torch.Tensor) -> torch.Tensor:
+    """[N, C, H, W] -> token-major [N, H*W, C] (the backward of tokens_to_nchw_add with respect to the tokens)."""
+    _need_cuda(x)
+    if x.dim() != 4 or x.dtype != torch.bfloat16 or not x.is_contiguous():
+        raise _lib.TviError(_lib.TVI_ERR_INVALID, "nchw_to_tokens: x must be a contiguous bf16 [N, C, H, W] tensor")
+    N, C, H, W = x.shape
+    out = torch.empty(N, H * W, C, dtype=torch.bfloat16, device=x.device)
+    _hooked("nchw_to_tokens", 1, _lib.load().tvi_nchw_to_tokens_bf16, x.data_ptr(), out.data_ptr(), N, C, H * W, C, _stream())
+    return out
+
+
+def groupnorm_tokens_bwd(x: torch.Tensor, dn: torch.Tensor, gamma, groups: int, eps: float, need_dx: bool = True,
+                         need_affine: bool = True):
+    """Backward of groupnorm_tokens: x [N, C, H, W] (the forward input), dn [N, H*W, C] -> (dx [N, C, H, W] or None,
+    dgamma [C] or None, dbeta [C] or None), all bf16."""
+    _need_cuda(x, dn, gamma)
+    if x.dim() != 4 or x.dtype != torch.bfloat16 or not x.is_contiguous():
+        raise _lib.TviError(_lib.TVI_ERR_INVALID, "groupnorm_tokens_bwd: x must be a contiguous bf16 [N, C, H, W] tensor")
+    N, C, H, W = x.shape
+    if dn.shape != (N, H * W, C):
+        raise _lib.TviError(_lib.TVI_ERR_INVALID, "groupnorm_tokens_bwd: dn must be [N, H*W, C]")
+    d2, lddn = _rows2d(dn, "dn")
+    if gamma is not None and (gamma.dtype != torch.bfloat16 or not gamma.is_contiguous() or gamma.numel() != C):
+        raise _lib.TviError(_lib.TVI_ERR_INVALID, "groupnorm_tokens_bwd: gamma must be a contiguous bf16 vector of length C")
+    dx = torch.empty_like(x) if need_dx else None
+    dgamma = torch.empty(C, dtype=torch.bfloat16, device=x.device) if need_affine else None
+    dbeta = torch.empty(C, dtype=torch.bfloat16, device=x.device) if need_affine else None
+    lib = _lib.load()
+    ws = _workspace(lib.tvi_groupnorm_tokens_bwd_workspace_bytes(N, C, H * W, int(groups)), x.device)
+    _hooked("groupnorm_tokens_bwd", 4 + int(need_dx) + int(need_affine), lib.tvi_groupnorm_tokens_bwd_bf16, x.data_ptr(), d2.data_ptr(),
+            gamma.data_ptr() if gamma is not None else None, dx.data_ptr() if dx is not None else None,
+            dgamma.data_ptr() if dgamma is not None else None, dbeta.data_ptr() if dbeta is not None else None,
+            ws.data_ptr(), N, C, H * W, int(groups), lddn, float(eps), _stream())
+    return dx, dgamma, dbeta
+
+
+def blend_rows_bwd(dy: torch.Tensor, xs, xt, alpha: torch.Tensor, rows_per_group: int, need_dalpha: bool):
+    """Backward of blend_rows: (dx_spatial, dx_temporal, dalpha [frames] fp32 or None); dy / xs / xt are [frames*rows, C]
+    contiguous bf16."""
+    _need_cuda(dy, xs, xt, alpha)
+    C = dy.shape[-1]
+    nrows = dy.numel() // C if C else 0
+    frames = nrows // max(1, int(rows_per_group))
+    for t, what in ((dy, "dy"), (xs, "x_spatial"), (xt, "x_temporal")):
+        if t is not None and (t.dtype != torch.bfloat16 or not t.is_contiguous() or t.numel() != nrows * C):
+            raise _lib.TviError(_lib.TVI_ERR_INVALID, f"blend_rows_bwd: {what} must be a contiguous bf16 tensor of dy's shape")
+    if alpha.dtype != torch.float32 or not alpha.is_contiguous() or alpha.numel() != frames or frames * rows_per_group != nrows:
+        raise _lib.TviError(_lib.TVI_ERR_INVALID, "blend_rows_bwd: alpha must be a contiguous fp32 vector with one entry per frame")
+    dxs, dxt = torch.empty_like(dy), torch.empty_like(dy)
+    lib = _lib.load()
+    part = None
+    if need_dalpha:
+        part = torch.empty(frames, lib.tvi_blend_rows_bwd_blocks(int(rows_per_group), C), dtype=torch.float32, device=dy.device)
+    _hooked("blend_rows_bwd", 1, lib.tvi_blend_rows_bwd_bf16, dy.data_ptr(), xs.data_ptr() if need_dalpha else None,
+            xt.data_ptr() if need_dalpha else None, alpha.data_ptr(), dxs.data_ptr(), dxt.data_ptr(),
+            part.data_ptr() if part is not None else None, frames, int(rows_per_group), C, C, _stream())
+    return dxs, dxt, (part.sum(dim=1) if part is not None else None)
+
+
 def tokens_to_nchw_add(y: torch.Tensor, residual: torch.Tensor | None, H: int, W: int, out: torch.Tensor | None = None) -> torch.Tensor:
     """[N, H*W, C] token-major -> NCHW [N, C, H, W] (+ residual of that shape)."""
     _need_cuda(y, residual)

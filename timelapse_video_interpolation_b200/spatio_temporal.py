@@ -15,8 +15,9 @@ Same signature, same results; what changes is where the bytes go:
 Training (src/train.py back-propagates through this forward, the spatial block under `torch.utils.checkpoint(...,
 use_reentrant=False)` at :321-327): when a gradient is needed the call goes on the autograd tape — proj_in / proj_out, the
 blocks' LayerNorms, attention and FeedForward through their libtvi autograd Functions (forward AND backward kernels),
-the thin glue (GroupNorm + NCHW<->token permutes, frame-embedding add, AlphaBlender, module residual) as torch ops:
-their fused kernels above have no backward yet and are the inference fast path.
+the glue (GroupNorm + NCHW<->token transposes, frame-embedding add, AlphaBlender, module residual) through the same
+forward kernels as inference plus their backward kernels (layout_ops.cu: `tvi_groupnorm_tokens_bwd_bf16`,
+`tvi_nchw_to_tokens_bf16`, `tvi_blend_rows_bwd_bf16`, column sums for the embedding).
 """
 from __future__ import annotations
 
@@ -151,37 +152,105 @@ def _forward_fused(model, hidden_states, spatial_ctx, time_context, image_only_i
     return ops.tokens_to_nchw_add(y.view(BF, S, y.shape[-1]), residual, H, W)                      # :354-357
 
 
+def _cast_grad(g, like):
+    return None if (g is None or like is None) else (g if g.dtype == like.dtype else g.to(like.dtype)).view(like.shape)
+
+
+class _GroupNormTokensFn(torch.autograd.Function):
+    """`self.norm(x).permute(0, 2, 3, 1).reshape(BF, H*W, C)` (:300-304) on the tape: groupnorm_tokens forward, the
+    three-pass backward of layout_ops.cu (dx in NCHW, dgamma, dbeta; fixed-order sums)."""
+
+    @staticmethod
+    def forward(ctx, x, gamma, beta, groups, eps):
+        xc = x.detach().contiguous()
+        y = ops.groupnorm_tokens(xc, _bf16_param(gamma), _bf16_param(beta), groups, eps)
+        ctx.save_for_backward(xc, gamma, beta)
+        ctx.groups, ctx.eps = groups, eps
+        return y
+
+    @staticmethod
+    def backward(ctx, dn):
+        xc, gamma, beta = ctx.saved_tensors
+        need_x, need_g, need_b = ctx.needs_input_grad[:3]
+        dx, dg, db = ops.groupnorm_tokens_bwd(xc, dn.contiguous(), _bf16_param(gamma), ctx.groups, ctx.eps, need_dx=need_x,
+                                              need_affine=need_g or need_b)
+        return dx, _cast_grad(dg, gamma) if need_g else None, _cast_grad(db, beta) if need_b else None, None, None
+
+
+class _TokensToNchwAddFn(torch.autograd.Function):
+    """`y.reshape(BF, H, W, C).permute(0, 3, 1, 2).contiguous() + residual` (:354-357): d tokens = transpose(d out)."""
+
+    @staticmethod
+    def forward(ctx, y, residual, H, W):
+        return ops.tokens_to_nchw_add(y.detach().contiguous(), residual.detach().contiguous(), H, W)
+
+    @staticmethod
+    def backward(ctx, dout):
+        dout = dout.contiguous()
+        return (ops.nchw_to_tokens(dout) if ctx.needs_input_grad[0] else None), (dout if ctx.needs_input_grad[1] else None), None, None
+
+
+class _BcastAddFn(torch.autograd.Function):
+    """`hidden_states + emb` (:341-342), emb one row per frame: d emb = the column sums over the frame's H*W rows."""
+
+    @staticmethod
+    def forward(ctx, emb, x, S):
+        ctx.S = S
+        return ops.bcast_rows_add(emb.detach().contiguous(), x.detach().contiguous(), S).view(x.shape)
+
+    @staticmethod
+    def backward(ctx, d):
+        d = d.contiguous()
+        demb = ops.colsum_bf16(d.view(-1, d.shape[-1]), ctx.S) if ctx.needs_input_grad[0] else None
+        return demb, (d if ctx.needs_input_grad[1] else None), None
+
+
+class _BlendFn(torch.autograd.Function):
+    """AlphaBlender.forward (:349-351) with one fp32 alpha per frame; d alpha = sum over the frame of dy (x_s - x_t)."""
+
+    @staticmethod
+    def forward(ctx, xs, xt, alpha, S):
+        xs2, xt2, a = xs.detach().contiguous(), xt.detach().contiguous(), alpha.detach().float().contiguous()
+        ctx.save_for_backward(xs2, xt2, a)
+        ctx.S = S
+        return ops.blend_rows(xs2, xt2, a, S)
+
+    @staticmethod
+    def backward(ctx, dy):
+        xs2, xt2, a = ctx.saved_tensors
+        dxs, dxt, da = ops.blend_rows_bwd(dy.contiguous().view(-1, dy.shape[-1]), xs2.view(-1, xs2.shape[-1]),
+                                          xt2.view(-1, xt2.shape[-1]), a, ctx.S, ctx.needs_input_grad[2])
+        return (dxs.view(xs2.shape) if ctx.needs_input_grad[0] else None), (dxt.view(xt2.shape) if ctx.needs_input_grad[1] else None), da, None
+
+
 def _forward_on_tape(model, hidden_states, spatial_ctx, time_context, image_only_indicator, B, T, H, W):
-    """Training path (see the module docstring): same order of operations as :300-357, glue as torch ops on the tape."""
-    BF, S, C = B * T, H * W, hidden_states.shape[1]
-    residual = hidden_states
+    """Training path (see the module docstring): same order of operations as :300-357, every activation-sized step a
+    libtvi kernel in both directions (the Functions above); torch ops only touch the [B*T, C] embedding and the [B*T]
+    blend weights."""
+    BF, S = B * T, H * W
     norm = model.norm
-    x = torch.nn.functional.group_norm(hidden_states, int(norm.num_groups), _cast_like(norm.weight, hidden_states),
-                                       _cast_like(norm.bias, hidden_states), float(norm.eps))    # :300
-    x = x.permute(0, 2, 3, 1).reshape(BF, S, C)                                                   # :302-304
+    x = _GroupNormTokensFn.apply(hidden_states, norm.weight, norm.bias, int(norm.num_groups), float(norm.eps))   # :300-304
     x = _linear(model.proj_in, x)                                                                 # :306
     idx = torch.arange(T, device=hidden_states.device).repeat(B, 1).reshape(-1)                   # :308-315
     tp = model.time_pos_embed
     t_emb = model.time_proj(idx).to(hidden_states.dtype)
-    emb = tp(t_emb.to(tp.linear_1.weight.dtype)).to(hidden_states.dtype)[:, None, :]
+    emb = tp(t_emb.to(tp.linear_1.weight.dtype)).to(hidden_states.dtype)                          # [BF, C]
     if emb.shape[-1] != x.shape[-1]:
         raise _lib.TviError(_lib.TVI_ERR_UNSUPPORTED, "in_channels != inner_dim: the frame embedding cannot be added (:333)")
-    alpha = _alpha_on_tape(model.time_mixer, image_only_indicator.to(hidden_states.device)).to(hidden_states.dtype)  # [BF, 1, 1]
+    # the reference casts alpha to the activation dtype (`.to(x_spatial.dtype)`): the blend weights are the bf16-rounded ones
+    alpha = _alpha_on_tape(model.time_mixer, image_only_indicator.to(hidden_states.device)).reshape(-1)
+    alpha = alpha.to(hidden_states.dtype).float()                                                 # [BF] fp32
     use_ckpt = bool(getattr(model, "gradient_checkpointing", False)) and model.training
     for block, temporal_block in zip(model.transformer_blocks, model.temporal_transformer_blocks):
         if use_ckpt:  # :321-327
             x = torch.utils.checkpoint.checkpoint(block, x, None, spatial_ctx, None, use_reentrant=False)
         else:
             x = block(x, encoder_hidden_states=spatial_ctx)                                        # :329-333
-        x_mix = x + emb                                                                            # :341-342
+        x_mix = _BcastAddFn.apply(emb, x, S)                                                       # :341-342
         x_mix = temporal_block(x_mix, num_frames=T, encoder_hidden_states=time_context)            # :343-347
-        x = alpha * x + (1.0 - alpha) * x_mix                                                      # :349-351 (AlphaBlender.forward)
+        x = _BlendFn.apply(x, x_mix, alpha, S)                                                     # :349-351 (AlphaBlender.forward)
     y = _linear(model.proj_out, x)                                                                 # :353
-    return y.reshape(BF, H, W, y.shape[-1]).permute(0, 3, 1, 2).contiguous() + residual           # :354-357
-
-
-def _cast_like(p, x):
-    return None if p is None else (p if p.dtype == x.dtype else p.to(x.dtype))
+    return _TokensToNchwAddFn.apply(y.view(BF, S, y.shape[-1]), hidden_states, H, W)               # :354-357
 
 
 def _alpha_on_tape(mixer, image_only_indicator: torch.Tensor) -> torch.Tensor:
