@@ -89,7 +89,11 @@ struct GemmParams {
 
 // kAMn / kBMn: the A / B operand is stored reduction-row-major ("MN-major": the output dimension is the
 // contiguous one).  kSplit: tiles are (split, m, n); fp32 partials instead of the bf16 TMA-store epilogue.
-template <bool kAMn, bool kBMn, bool kSplit>
+// kPair (forward TN GEMM only): two CTAs of a cluster (one TPC) work on ONE 256 x BN tile with `tcgen05.mma.cta_group::2`:
+// each CTA loads its own 128 rows of A and HALF of the B tile, the leader CTA issues the MMAs for both, every CTA runs the
+// epilogue of its own 128 accumulator rows.  Per CTA and k-block the L2 -> SM operand stream is A + B/2 instead of A + B;
+// with the weight slice resident (half of it per CTA: 80 KB at BN = 256, K = 320) only A streams at all.
+template <bool kAMn, bool kBMn, bool kSplit, bool kPair = false>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CUtensorMap tmW,
                  const __grid_constant__ CUtensorMap tmY, const __grid_constant__ CUtensorMap tmR, const GemmParams p) {
@@ -107,7 +111,13 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
   // 1024-byte aligned carve-up (SWIZZLE_128B atoms are 1024 B)
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   uint8_t* base_ptr = smem_raw + (base - smem_u32(smem_raw));
-  const uint32_t b_bytes = (uint32_t)p.BN * kBK * 2;
+  static_assert(!kPair || (!kAMn && !kBMn && !kSplit), "the CTA-pair kernel is the forward (TN) GEMM");
+  const uint32_t cta_rank = kPair ? cluster_ctarank() : 0u;
+  const int64_t worker = kPair ? (int64_t)(blockIdx.x >> 1) : (int64_t)blockIdx.x;      // tile walker: a CTA, or a CTA pair
+  const int64_t nworkers = kPair ? (int64_t)(gridDim.x >> 1) : (int64_t)gridDim.x;
+  constexpr int kMStep = kPair ? 2 * kBM : kBM;                                          // rows of a (pair) tile
+  const int bn_local = kPair ? p.BN / 2 : p.BN;                                          // B rows held by this CTA
+  const uint32_t b_bytes = (uint32_t)bn_local * kBK * 2;
   // Resident-B mode (forward projections at K = 320): with gridDim.x a multiple of n_tiles the walk
   // tile = blockIdx.x + i * gridDim.x keeps nt = blockIdx.x % n_tiles, so the CTA's [BN x K] weight slice is
   // loaded ONCE and only X streams through the ring.  Re-fetching the slice per tile made the L2 -> SM
@@ -134,16 +144,22 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
       for (int b = 0; b < kResStageBufs; ++b) mbar_init(&bar_res[w][b], 1);
     for (int s = 0; s < 2; ++s) {
       mbar_init(&bar_acc_full[s], 1);
-      mbar_init(&bar_acc_empty[s], kEpiWarps);
+      mbar_init(&bar_acc_empty[s], kPair ? 2 * kEpiWarps : kEpiWarps);  // pair: both CTAs' epilogue warps release the leader
     }
     mbar_fence_init();
   }
   if (warp == 1) {
-    tmem_alloc(&s_tmem_base, 512);
-    tmem_relinquish();
+    if (kPair) {
+      tmem_alloc_pair(&s_tmem_base, 512);
+      tmem_relinquish_pair();
+    } else {
+      tmem_alloc(&s_tmem_base, 512);
+      tmem_relinquish();
+    }
   }
   tc_fence_before();
-  __syncthreads();
+  if (kPair) cluster_sync_all();  // the peer's barriers are initialised before any remote arrive / complete_tx
+  else __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = s_tmem_base;
 
@@ -155,23 +171,42 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
     if (lane == 0) {
       int s = 0;
       uint32_t ph = 0;
-      if (res_b && blockIdx.x < n_tiles_total) {
-        const int n0 = (int)(blockIdx.x % p.n_tiles) * p.BN;
-        mbar_arrive_expect_tx(&bar_w, res_bytes);
-        for (int kb = 0; kb < p.k_blocks_total; ++kb) tma_load_2d(wres_ptr + kb * b_bytes, &tmW, &bar_w, kb * kBK, n0);
+      // pair: every load is counted on the LEADER's barrier (which expects both CTAs' bytes); each CTA waits on its own
+      // `empty` barrier, released for both by the leader's multicast commit
+      const uint32_t bar_w_leader = kPair ? mapa_u32(&bar_w, 0) : 0u;
+      if (res_b && worker < n_tiles_total) {
+        const int n0 = (int)(worker % p.n_tiles) * p.BN + (int)cta_rank * bn_local;
+        if (kPair) {
+          if (cta_rank == 0) mbar_arrive_expect_tx(&bar_w, 2 * res_bytes);
+          for (int kb = 0; kb < p.k_blocks_total; ++kb) tma_load_2d_pair(wres_ptr + kb * b_bytes, &tmW, bar_w_leader, kb * kBK, n0);
+        } else {
+          mbar_arrive_expect_tx(&bar_w, res_bytes);
+          for (int kb = 0; kb < p.k_blocks_total; ++kb) tma_load_2d(wres_ptr + kb * b_bytes, &tmW, &bar_w, kb * kBK, n0);
+        }
       }
-      for (int64_t tile = blockIdx.x; tile < n_tiles_total; tile += gridDim.x) {
+      for (int64_t tile = worker; tile < n_tiles_total; tile += nworkers) {
         const int64_t split = kSplit ? tile / mn_tiles : 0;
         const int64_t mn = tile - split * mn_tiles;
         const int64_t mt = mn / p.n_tiles;
         const int nt = (int)(mn - mt * p.n_tiles);
-        const int m0 = (int)(mt * kBM), n0 = nt * p.BN;
+        const int m0 = (int)(mt * kMStep) + (int)cta_rank * kBM, n0 = nt * p.BN + (int)cta_rank * (kPair ? bn_local : 0);
         const int kb_lo = (int)split * p.k_blocks;
         const int kb_hi = min(kb_lo + p.k_blocks, p.k_blocks_total);
         for (int kb = kb_lo; kb < kb_hi; ++kb) {
           mbar_wait(&bar_empty[s], ph ^ 1);
-          mbar_arrive_expect_tx(&bar_full[s], stage_bytes);
           uint8_t* a_dst = base_ptr + s * stage_bytes;
+          if (kPair) {
+            if (cta_rank == 0) mbar_arrive_expect_tx(&bar_full[s], 2 * stage_bytes);
+            const uint32_t full_leader = mapa_u32(&bar_full[s], 0);
+            tma_load_2d_pair(a_dst, &tmX, full_leader, kb * kBK, m0);
+            if (!res_b) tma_load_2d_pair(a_dst + kABytes, &tmW, full_leader, kb * kBK, n0);
+            if (++s == p.stages) {
+              s = 0;
+              ph ^= 1;
+            }
+            continue;
+          }
+          mbar_arrive_expect_tx(&bar_full[s], stage_bytes);
           if (!kAMn) {
             tma_load_2d(a_dst, &tmX, &bar_full[s], kb * kBK, m0);
           } else {
@@ -199,17 +234,17 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
     // The whole warp walks the loop (convergent control flow keeps the descriptors in uniform
     // registers); only the elected lane's tcgen05 instructions are enabled.  Issuing from inside
     // `if (lane == 0)` makes nvcc wrap every MMA in an ELECT / BRA.U.ANY loop (~75 cycles each).
-    const uint32_t leader = elect_one() ? 1u : 0u;
-    const uint32_t idesc = umma_idesc_bf16(kBM, (uint32_t)p.BN, kAMn ? 1 : 0, kBMn ? 1 : 0);
+    const uint32_t leader = (elect_one() && cta_rank == 0) ? 1u : 0u;  // pair: only the leader CTA issues
+    const uint32_t idesc = umma_idesc_bf16(kMStep, (uint32_t)p.BN, kAMn ? 1 : 0, kBMn ? 1 : 0);
     int s = 0;
     uint32_t ph = 0;
     int as = 0;
     uint32_t aph = 0;
-    if (res_b && blockIdx.x < n_tiles_total) {
+    if (res_b && worker < n_tiles_total && cta_rank == 0) {
       mbar_wait(&bar_w, 0);
       tc_fence_after();
     }
-    for (int64_t tile = blockIdx.x; tile < n_tiles_total; tile += gridDim.x) {
+    for (int64_t tile = worker; tile < n_tiles_total && cta_rank == 0; tile += nworkers) {
       mbar_wait(&bar_acc_empty[as], aph ^ 1);
       tc_fence_after();
       const uint32_t d_tmem = tmem_base + as * kAccStride;
@@ -229,15 +264,19 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
                                    : umma_smem_desc(a_addr + kk * 32, 16, 1024, kUmmaLayoutSw128);
           const uint64_t bd = kBMn ? umma_smem_desc(b_addr + kk * 2048, 8192, 1024, kUmmaLayoutSw128)
                                    : umma_smem_desc(b_addr + kk * 32, 16, 1024, kUmmaLayoutSw128);
-          umma_bf16_ss_pred(d_tmem, ad, bd, idesc, (kb | kk) != 0 ? 1u : 0u, leader);
+          if (kPair) umma_bf16_ss_pair_pred(d_tmem, ad, bd, idesc, (kb | kk) != 0 ? 1u : 0u, leader);
+          else umma_bf16_ss_pred(d_tmem, ad, bd, idesc, (kb | kk) != 0 ? 1u : 0u, leader);
         }
-        umma_commit_pred(&bar_empty[s], leader);  // frees the smem stage once these MMAs have read it
+        // frees the smem stage (in both CTAs of a pair) once these MMAs have read it
+        if (kPair) umma_commit_pair_pred(&bar_empty[s], leader);
+        else umma_commit_pred(&bar_empty[s], leader);
         if (++s == p.stages) {
           s = 0;
           ph ^= 1;
         }
       }
-      umma_commit_pred(&bar_acc_full[as], leader);  // accumulator complete -> epilogue
+      if (kPair) umma_commit_pair_pred(&bar_acc_full[as], leader);  // accumulator complete -> both CTAs' epilogues
+      else umma_commit_pred(&bar_acc_full[as], leader);             // accumulator complete -> epilogue
       if (++as == 2) {
         as = 0;
         aph ^= 1;
@@ -262,7 +301,12 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
     // place and the same buffer goes out through the TMA store.
     const bool has_res = !kSplit && p.residual != nullptr;
     uint64_t* my_res_bar = bar_res[warp - 2];
-    int64_t ptile = blockIdx.x;  // prefetch cursor: (tile, chunk) of the next residual chunk to request
+    const uint32_t acc_empty_leader[2] = {kPair ? mapa_u32(&bar_acc_empty[0], 0) : 0u, kPair ? mapa_u32(&bar_acc_empty[1], 0) : 0u};
+    auto release_acc = [&](int stage) {  // lane 0: this warp has read everything it needs of accumulator stage `stage`
+      if (kPair) mbar_arrive_cluster(acc_empty_leader[stage]);
+      else mbar_arrive(&bar_acc_empty[stage]);
+    };
+    int64_t ptile = worker;  // prefetch cursor: (tile, chunk) of the next residual chunk to request
     int pc = chalf;
     uint32_t pq = 0, qn = 0;     // chunks requested / consumed by this warp
     auto valid_chunks = [&](int64_t tile) {  // chunks of this tile that start inside [0, N_store)
@@ -274,7 +318,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
     };
     auto issue_residual = [&]() {  // lane 0
       while (ptile < n_tiles_total && pc >= valid_chunks(ptile)) {
-        ptile += gridDim.x;
+        ptile += nworkers;
         pc = chalf;
       }
       if (ptile >= n_tiles_total) return;
@@ -283,7 +327,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
       const int n0s = p.geglu ? (nt * p.BN) >> 1 : nt * p.BN;
       const uint32_t b = pq % kResStageBufs;
       mbar_arrive_expect_tx(&my_res_bar[b], 2048);
-      tma_load_2d(my_staging_ptr + b * 2048, &tmR, &my_res_bar[b], n0s + pc * 32, (int)(mt * kBM) + quad * 32);
+      tma_load_2d(my_staging_ptr + b * 2048, &tmR, &my_res_bar[b], n0s + pc * 32, (int)(mt * kMStep) + (int)cta_rank * kBM + quad * 32);
       ++pq;
       pc += kChunkStep;
     };
@@ -294,12 +338,12 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
     int as = 0;
     uint32_t aph = 0;
     const int chunks = p.BN / 32;
-    for (int64_t tile = blockIdx.x; tile < n_tiles_total; tile += gridDim.x) {
+    for (int64_t tile = worker; tile < n_tiles_total; tile += nworkers) {
       const int64_t split = kSplit ? tile / mn_tiles : 0;
       const int64_t mn = tile - split * mn_tiles;
       const int64_t mt = mn / p.n_tiles;
       const int nt = (int)(mn - mt * p.n_tiles);
-      const int m0 = (int)(mt * kBM), n0 = nt * p.BN;
+      const int m0 = (int)(mt * kMStep) + (int)cta_rank * kBM, n0 = nt * p.BN;
       const float* my_bias = bias_strips + as * 256;
       const float* my_cs = cs_strips + as * 256;
       float ln_r = 1.f, ln_t = 0.f;  // y = ln_r * acc + ln_t * colsum + bias, ln_t = -mean * rstd
@@ -331,7 +375,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
         // below runs over out_chunks.)
         tc_fence_before();
         __syncwarp();
-        if (lane == 0) mbar_arrive(&bar_acc_empty[as]);
+        if (lane == 0) release_acc(as);
       }
       for (int c = chalf; c < out_chunks; c += kChunkStep) {
         uint32_t r[32], rg[32];
@@ -342,7 +386,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
           // every column this warp needs of the accumulator stage is now in registers
           tc_fence_before();
           __syncwarp();
-          if (lane == 0) mbar_arrive(&bar_acc_empty[as]);
+          if (lane == 0) release_acc(as);
         }
         const int ncol0 = (p.geglu ? (n0 >> 1) : n0) + c * 32;
         if (ncol0 >= p.N_store) continue;  // tile column tail: nothing to store (warp-uniform)
@@ -451,10 +495,12 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
   }
 
   tc_fence_before();
-  __syncthreads();
+  if (kPair) cluster_sync_all();  // neither CTA leaves (or frees tensor memory) while the other may still touch it
+  else __syncthreads();
   if (warp == 1) {
     tc_fence_after();
-    tmem_dealloc(tmem_base, 512);
+    if (kPair) tmem_dealloc_pair(tmem_base, 512);
+    else tmem_dealloc(tmem_base, 512);
   }
 }
 
@@ -505,13 +551,13 @@ int operand_map(CUtensorMap* tm, const tvi_bf16* base, bool mn_major, int64_t ou
   return make_tensor_map(tm, base, 2, 2, dims, strides, box, Swizzle::B128);
 }
 
-template <bool kAMn, bool kBMn, bool kSplit>
+template <bool kAMn, bool kBMn, bool kSplit, bool kPair>
 int configure_once() {
   static bool configured[64] = {false};
   int dev = 0;
   TVI_CUDA_OK(cudaGetDevice(&dev));
   if (dev < 0 || dev >= 64 || !configured[dev]) {
-    TVI_CUDA_OK(cudaFuncSetAttribute(gemm_bf16_kernel<kAMn, kBMn, kSplit>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    TVI_CUDA_OK(cudaFuncSetAttribute(gemm_bf16_kernel<kAMn, kBMn, kSplit, kPair>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                      227 * 1024 - 1024));
     if (dev >= 0 && dev < 64) configured[dev] = true;
   }
@@ -520,7 +566,7 @@ int configure_once() {
 
 // D[Mo, No] = A . B over a reduction of length R.  A is [Mo, R] (K-major) or [R, Mo] (MN-major) with row stride
 // lda; B is [No, R] or [R, No] with row stride ldb.  Output: bf16 Y (ldy) through TMA, or fp32 partials when kSplit.
-template <bool kAMn, bool kBMn, bool kSplit>
+template <bool kAMn, bool kBMn, bool kSplit, bool kPair = false>
 int launch_gemm(const char* name, const tvi_bf16* A, const tvi_bf16* B, const tvi_bf16* bias, tvi_bf16* Y, float* partial,
                 int splits, int64_t Mo, int No, int64_t R, int64_t lda, int64_t ldb, int64_t ldy, cudaStream_t st,
                 int geglu_block = 0, const tvi_bf16* residual = nullptr, int64_t ldr = 0, const float* ln_stats = nullptr,
@@ -539,7 +585,8 @@ int launch_gemm(const char* name, const tvi_bf16* A, const tvi_bf16* B, const tv
   p.residual = residual;
   p.ldr = ldr;
   p.N = No;
-  p.m_tiles = (Mo + kBM - 1) / kBM;
+  constexpr int kMStep = kPair ? 2 * kBM : kBM;  // a CTA pair owns 256 rows
+  p.m_tiles = (Mo + kMStep - 1) / kMStep;
   p.n_tiles = (No + p.BN - 1) / p.BN;
   p.k_blocks_total = (int)((R + kBK - 1) / kBK);
   p.k_blocks = kSplit ? (p.k_blocks_total + splits - 1) / splits : p.k_blocks_total;
@@ -547,12 +594,13 @@ int launch_gemm(const char* name, const tvi_bf16* A, const tvi_bf16* B, const tv
   p.partial = partial;
   p.M_out = Mo;
   p.ldp = No;
-  const int b_bytes = p.BN * kBK * 2;
+  const int b_bytes = (kPair ? p.BN / 2 : p.BN) * kBK * 2;  // per CTA: a pair holds half of the B tile each
   const int res_bytes = p.k_blocks_total * b_bytes;
   const int sms = num_sms();
+  const int workers = kPair ? sms / 2 : sms;               // tile walkers: CTAs, or CTA pairs
   // resident weight slice: plain forward GEMM, slice <= 128 KB, and enough row tiles per CTA to amortise it
-  p.res_b = (!kAMn && !kBMn && !kSplit && res_bytes <= 128 * 1024 && p.n_tiles <= sms &&
-             p.m_tiles * p.n_tiles >= 4 * (int64_t)sms) ? 1 : 0;
+  p.res_b = (!kAMn && !kBMn && !kSplit && res_bytes <= 128 * 1024 && p.n_tiles <= workers &&
+             p.m_tiles * p.n_tiles >= 4 * (int64_t)workers) ? 1 : 0;
   const int stage_bytes = p.res_b ? kABytes : kABytes + b_bytes;
   p.stage_bufs = (!kSplit && residual != nullptr) ? kResStageBufs : kStageBufs;
   const int kStagingBytes = staging_bytes(p.stage_bufs);
@@ -566,7 +614,7 @@ int launch_gemm(const char* name, const tvi_bf16* A, const tvi_bf16* B, const tv
   CUtensorMap tmA, tmB, tmY, tmR;
   int rc = operand_map(&tmA, A, kAMn, Mo, R, lda, kBM);
   if (rc) return rc;
-  rc = operand_map(&tmB, B, kBMn, No, R, ldb, p.BN);
+  rc = operand_map(&tmB, B, kBMn, No, R, ldb, kPair ? p.BN / 2 : p.BN);
   if (rc) return rc;
   if (!kSplit) {
     const uint64_t dims[2] = {(uint64_t)p.N_store, (uint64_t)Mo};
@@ -584,14 +632,42 @@ int launch_gemm(const char* name, const tvi_bf16* A, const tvi_bf16* B, const tv
     tmY = tmA;  // unused by the split epilogue
     tmR = tmA;
   }
-  rc = configure_once<kAMn, kBMn, kSplit>();
+  rc = configure_once<kAMn, kBMn, kSplit, kPair>();
   if (rc) return rc;
   int64_t grid = p.m_tiles * p.n_tiles;
   if (kSplit) grid *= (p.k_blocks_total + p.k_blocks - 1) / p.k_blocks;
-  if (grid > sms) grid = p.res_b ? (sms / p.n_tiles) * p.n_tiles : sms;
-  gemm_bf16_kernel<kAMn, kBMn, kSplit><<<(unsigned)grid, kGemmThreads, smem_bytes, st>>>(tmA, tmB, tmY, tmR, p);
+  if (grid > workers) grid = p.res_b ? (workers / p.n_tiles) * p.n_tiles : workers;
+  if (kPair) {
+    // two CTAs per tile walker, launched as clusters of 2 (the pair shares a TPC)
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)(2 * grid));
+    cfg.blockDim = dim3(kGemmThreads);
+    cfg.dynamicSmemBytes = (size_t)smem_bytes;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = 2;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    TVI_CUDA_OK(cudaLaunchKernelEx(&cfg, gemm_bf16_kernel<kAMn, kBMn, kSplit, kPair>, tmA, tmB, tmY, tmR, p));
+    return TVI_OK;
+  }
+  gemm_bf16_kernel<kAMn, kBMn, kSplit, kPair><<<(unsigned)grid, kGemmThreads, smem_bytes, st>>>(tmA, tmB, tmY, tmR, p);
   TVI_LAUNCH_OK(name);
   return TVI_OK;
+}
+
+// CTA-pair (cta_group::2) forward GEMM.  MEASURED on B200 at the L0 shapes (tools/micro/pair_gemm_check.py,
+// profiles/r2_gemm_pair.txt) and OFF by default: ff_in + GEGLU 0.448 -> 0.537 ms, QKV 0.159 -> 0.220 ms, out-projection
+// 0.109 -> 0.142 ms, ff_out (K = 1 280) 0.223 -> 0.221 ms.  Halving the L2 -> SM operand stream buys nothing: these GEMMs
+// are bound by their epilogue (GEGLU: issue slots) and by the HBM write stream, and the pair adds a cross-CTA handshake
+// per 5-k-block tile.  TVI_GEMM_PAIR=1 selects it wherever the shape allows (parity: tests/test_gpu_gemm_pair.py).
+bool use_pair(int64_t M, int N, int K) {
+  (void)K;
+  const char* e = getenv("TVI_GEMM_PAIR");
+  return e != nullptr && atoi(e) == 1 && M >= 2 * kBM && N >= 32;
 }
 
 int wgrad_splits(int64_t M, int N, int K) {
@@ -637,6 +713,9 @@ extern "C" int tvi_gemm_bf16_tn(const tvi_bf16* X, const tvi_bf16* W, const tvi_
   TVI_CHECK_ARG(((uintptr_t)X | (uintptr_t)W | (uintptr_t)Y) % 16 == 0, "tvi_gemm_bf16_tn: X, W, Y must be 16-byte aligned");
   TVI_CHECK_ARG(bias == nullptr || (uintptr_t)bias % 4 == 0, "tvi_gemm_bf16_tn: bias must be 4-byte aligned");
   TVI_CHECK_ARG(M < ((int64_t)1 << 31) - 256, "tvi_gemm_bf16_tn: M too large for one call");
+  if (use_pair(M, N, K))
+    return launch_gemm<false, false, false, true>("tvi_gemm_bf16_tn", X, W, bias, Y, nullptr, 1, M, N, K, ldx, ldw, ldy,
+                                                  (cudaStream_t)stream);
   return launch_gemm<false, false, false>("tvi_gemm_bf16_tn", X, W, bias, Y, nullptr, 1, M, N, K, ldx, ldw, ldy,
                                           (cudaStream_t)stream);
 }
@@ -679,6 +758,9 @@ extern "C" int tvi_gemm_bf16_tn_ex(const tvi_bf16* X, const tvi_bf16* W, const t
                 "tvi_gemm_bf16_tn_ex: X, W, Y, residual must be 16-byte aligned");
   TVI_CHECK_ARG(bias == nullptr || (uintptr_t)bias % 2 == 0, "tvi_gemm_bf16_tn_ex: bias must be 2-byte aligned");
   TVI_CHECK_ARG(M < ((int64_t)1 << 31) - 256, "tvi_gemm_bf16_tn_ex: M too large for one call");
+  if (use_pair(M, N, K))
+    return launch_gemm<false, false, false, true>("tvi_gemm_bf16_tn_ex", X, W, bias, Y, nullptr, 1, M, N, K, ldx, ldw, ldy,
+                                                  (cudaStream_t)stream, block, residual, ldr);
   return launch_gemm<false, false, false>("tvi_gemm_bf16_tn_ex", X, W, bias, Y, nullptr, 1, M, N, K, ldx, ldw, ldy,
                                           (cudaStream_t)stream, block, residual, ldr);
 }
