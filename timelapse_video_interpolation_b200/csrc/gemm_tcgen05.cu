@@ -51,16 +51,28 @@ constexpr int kMaxStages = 8;
 // (log2(0.5 erfc(u / sqrt 2)) + 1) / u on [0, 6] (|log2 error| <= 7.1e-5); Phi = g < 0 ? E : 1 - E.  No cancellation on
 // the negative side; |gelu error| <= 7.4e-6 absolute and 4.9e-5 relative over the whole line -- 80x below the bf16
 // rounding of the stored product.  6 FMA + 1 MUFU.EX2 instead of erff's two divergent polynomial branches.
-__device__ __forceinline__ float gelu_erf(float g) {
-  const float u = fminf(fabsf(g), 6.0f);
-  float q = 2.3433244e-05f;
-  q = fmaf(q, u, -0.00061973924f);
-  q = fmaf(q, u, 0.007260352f);
-  q = fmaf(q, u, -0.051418606f);
-  q = fmaf(q, u, -0.46086353f);
-  q = fmaf(q, u, -1.1504804f);
-  const float e = fast_exp2(fmaf(q, u, -1.0f));
-  return g * (g < 0.f ? e : 1.0f - e);
+// `geglu_x2` evaluates it on a PAIR of gates with packed fp32 arithmetic (FFMA2 / FADD2 / FMUL2): v * g * Phi(g) for two columns.
+// (the six polynomial FMAs, the bias adds and the products cost one issue slot per pair: 0.448 -> 0.436 ms for ff_in at L0;
+// the epilogue chain is latency-bound, profiles/r2_gemm_ffin.md).
+// Phi = 0.5 + copysign(0.5 - E, g) (E <= 0.5) replaces the compare + select: one LOP3 per element.
+__device__ __forceinline__ uint64_t geglu_x2(uint64_t v2, uint64_t g2) {
+  float g0, g1;
+  f32x2_unpack(g2, g0, g1);
+  const uint64_t u2 = f32x2_pack(fminf(fabsf(g0), 6.0f), fminf(fabsf(g1), 6.0f));
+  uint64_t q = f32x2_fma(f32x2_pack(2.3433244e-05f, 2.3433244e-05f), u2, f32x2_pack(-0.00061973924f, -0.00061973924f));
+  q = f32x2_fma(q, u2, f32x2_pack(0.007260352f, 0.007260352f));
+  q = f32x2_fma(q, u2, f32x2_pack(-0.051418606f, -0.051418606f));
+  q = f32x2_fma(q, u2, f32x2_pack(-0.46086353f, -0.46086353f));
+  q = f32x2_fma(q, u2, f32x2_pack(-1.1504804f, -1.1504804f));
+  float t0, t1;
+  f32x2_unpack(f32x2_fma(q, u2, f32x2_pack(-1.0f, -1.0f)), t0, t1);
+  const uint64_t h2 = f32x2_fma(f32x2_pack(fast_exp2(t0), fast_exp2(t1)), f32x2_pack(-1.0f, -1.0f), f32x2_pack(0.5f, 0.5f));
+  float h0, h1;
+  f32x2_unpack(h2, h0, h1);
+  const float s0 = __uint_as_float(__float_as_uint(h0) | (__float_as_uint(g0) & 0x80000000u));
+  const float s1 = __uint_as_float(__float_as_uint(h1) | (__float_as_uint(g1) & 0x80000000u));
+  const uint64_t phi2 = f32x2_add(f32x2_pack(s0, s1), f32x2_pack(0.5f, 0.5f));
+  return f32x2_mul(f32x2_mul(g2, phi2), v2);
 }
 
 struct GemmParams {
@@ -419,10 +431,8 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
 #pragma unroll
           for (int j = 0; j < 32; j += 4) {
             const float4 b4 = *reinterpret_cast<const float4*>(my_bias + c * 32 + j);
-            f[j] += b4.x;
-            f[j + 1] += b4.y;
-            f[j + 2] += b4.z;
-            f[j + 3] += b4.w;
+            f32x2_unpack(f32x2_add(f32x2_pack(f[j], f[j + 1]), f32x2_pack(b4.x, b4.y)), f[j], f[j + 1]);
+            f32x2_unpack(f32x2_add(f32x2_pack(f[j + 2], f[j + 3]), f32x2_pack(b4.z, b4.w)), f[j + 2], f[j + 3]);
           }
         }
         if (p.geglu) {
@@ -437,10 +447,10 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
           for (int j = 0; j < 32; j += 4) {
             float4 b4 = make_float4(0.f, 0.f, 0.f, 0.f);
             if (p.bias != nullptr && !has_ln) b4 = *reinterpret_cast<const float4*>(gate_bias + j);
-            f[j] *= gelu_erf(__uint_as_float(rg[j]) + b4.x);
-            f[j + 1] *= gelu_erf(__uint_as_float(rg[j + 1]) + b4.y);
-            f[j + 2] *= gelu_erf(__uint_as_float(rg[j + 2]) + b4.z);
-            f[j + 3] *= gelu_erf(__uint_as_float(rg[j + 3]) + b4.w);
+            const uint64_t ga = f32x2_add(f32x2_pack(__uint_as_float(rg[j]), __uint_as_float(rg[j + 1])), f32x2_pack(b4.x, b4.y));
+            const uint64_t gb = f32x2_add(f32x2_pack(__uint_as_float(rg[j + 2]), __uint_as_float(rg[j + 3])), f32x2_pack(b4.z, b4.w));
+            f32x2_unpack(geglu_x2(f32x2_pack(f[j], f[j + 1]), ga), f[j], f[j + 1]);
+            f32x2_unpack(geglu_x2(f32x2_pack(f[j + 2], f[j + 3]), gb), f[j + 2], f[j + 3]);
           }
         }
         uint8_t* row_ptr = my_staging_ptr + buf * 2048 + lane * 64;
