@@ -31,7 +31,10 @@ namespace {
 
 constexpr int kBM = 128;
 constexpr int kBK = 64;
-constexpr int kEpiWarps = 8;                        // two per TMEM lane quadrant, alternating 32-column chunks (12: no further gain)
+#ifndef TVI_GEMM_EPI_WARPS
+#define TVI_GEMM_EPI_WARPS 8
+#endif
+constexpr int kEpiWarps = TVI_GEMM_EPI_WARPS;                        // two per TMEM lane quadrant, alternating 32-column chunks (12 / 16 warps squeeze the chain into 128 / 96 registers and are slower: profiles/r2_gemm_epi_warps.txt)
 constexpr int kGemmThreads = 64 + 32 * kEpiWarps;
 constexpr int kAccStride = 256;                    // TMEM columns per accumulator stage
 constexpr int kABytes = kBM * kBK * 2;             // 16 KB
@@ -40,7 +43,12 @@ constexpr int kABytes = kBM * kBK * 2;             // 16 KB
 // latency is hidden ACROSS warps instead: 8 warps x 1 buffer use the shared memory of 4 warps x 2 buffers and took the
 // N = 2560 / K = 320 GEMM from 0.52 to 0.45 ms, out-projection + residual from 0.175 to 0.105 ms, QKV unchanged (0.158).
 constexpr int kStageBufs = 1;
-constexpr int kResStageBufs = 4;                   // with a residual: the buffers also receive the residual chunk two chunks ahead
+#ifndef TVI_GEMM_RES_BUFS
+#define TVI_GEMM_RES_BUFS 4
+#endif
+constexpr int kResStageBufs = TVI_GEMM_RES_BUFS;
+constexpr int kResAhead = kResStageBufs >= 4 ? 2 : 1;  // residual chunks requested ahead of the one being processed
+//                 // with a residual: the buffers also receive the residual chunk two chunks ahead
 // warps x bufs x [32 rows][64 B] + warps x 256 fp32 bias
 constexpr int kBiasBytes = 4 * 256 * 4;            // one fp32 bias strip (+ one LayerNorm column-sum strip) per accumulator stage, shared by the epilogue warps
 constexpr int staging_bytes(int bufs) { return kEpiWarps * bufs * 2048 + kBiasBytes; }
@@ -344,8 +352,8 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
       pc += kChunkStep;
     };
     if (has_res && lane == 0) {
-      issue_residual();
-      issue_residual();
+#pragma unroll
+      for (int i = 0; i < kResAhead; ++i) issue_residual();
     }
     int as = 0;
     uint32_t aph = 0;
@@ -458,7 +466,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
         if (has_res) {
           // buffer (qn + 2) % 4 was last read by the store of chunk qn - 2: all but the latest store have drained
           if (lane == 0) {
-            tma_store_wait_read<1>();
+            tma_store_wait_read<kResStageBufs - kResAhead - 1>();
             issue_residual();
           }
           mbar_wait(&my_res_bar[buf], (qn / kResStageBufs) & 1);
