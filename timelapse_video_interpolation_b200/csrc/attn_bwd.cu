@@ -602,12 +602,19 @@ __global__ void __launch_bounds__(256) attn_fewkeys_bwd_kernel(const FkParams p)
     // Two keys (L == 2): P = [w, 1 - w], w = sigma(z), z = scale * q . (k0 - k1) + (b0 - b1).  With g = dO . (v0 - v1):
     // dS0 = -dS1 = w (1 - w) g, so dQ = scale dS0 (k0 - k1), dK0 = -dK1 = scale sum dS0 q: two dot products and 24
     // accumulators per row instead of four and 32.
-    float kd[8], vd[8];
+    // Packed fp32 (FFMA2 / FMUL2) throughout: the kernel is bound by its dependent instruction chain per row, not by bytes.
+    uint64_t kd2[4], vd2[4], dk2[4], dv0[4], dv1[4];
 #pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      kd[j] = kf[0][j] - kf[1][j];
-      vd[j] = vf[0][j] - vf[1][j];
+    for (int i = 0; i < 4; ++i) {
+      kd2[i] = f32x2_pack(kf[0][2 * i] - kf[1][2 * i], kf[0][2 * i + 1] - kf[1][2 * i + 1]);
+      vd2[i] = f32x2_pack(vf[0][2 * i] - vf[1][2 * i], vf[0][2 * i + 1] - vf[1][2 * i + 1]);
+      dk2[i] = dv0[i] = dv1[i] = f32x2_pack(0.f, 0.f);
     }
+    auto unpack_pairs = [](const uint4& u, uint64_t* o) {  // bf16 pair -> fp32 pair: low half << 16, high half masked
+      const uint32_t w[4] = {u.x, u.y, u.z, u.w};
+#pragma unroll
+      for (int i = 0; i < 4; ++i) o[i] = f32x2_pack(__uint_as_float(w[i] << 16), __uint_as_float(w[i] & 0xffff0000u));
+    };
     constexpr int kU = 4;  // 4 rows x (Q, dO) = 128 bytes in flight per thread
     for (int it0 = 0; it0 < kFewBwdRowsPerThread; it0 += kU) {
       if (rlo + (int64_t)it0 * RY >= rhi) break;  // block-uniform
@@ -625,15 +632,20 @@ __global__ void __launch_bounds__(256) attn_fewkeys_bwd_kernel(const FkParams p)
         const int64_t rr = rlo + (int64_t)(it0 + u) * RY + ry;
         const bool act = rr < rhi;
         const int64_t r = act ? rr : rlo;
-        float qf[8], gof[8];
-        unpack8b(qv[u], qf);
-        unpack8b(gv[u], gof);
-        float z = 0.f, g = 0.f;
+        uint64_t qp[4], gp[4];
+        unpack_pairs(qv[u], qp);
+        unpack_pairs(gv[u], gp);
+        uint64_t z2 = f32x2_mul(qp[0], kd2[0]), g2 = f32x2_mul(gp[0], vd2[0]);
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {
-          z = fmaf(qf[j], kd[j], z);
-          g = fmaf(gof[j], vd[j], g);
+        for (int i = 1; i < 4; ++i) {
+          z2 = f32x2_fma(qp[i], kd2[i], z2);
+          g2 = f32x2_fma(gp[i], vd2[i], g2);
         }
+        float z, zb, g, gb;
+        f32x2_unpack(z2, z, zb);
+        f32x2_unpack(g2, g, gb);
+        z += zb;
+        g += gb;
 #pragma unroll
         for (int off = LPH / 2; off > 0; off >>= 1) {
           z += __shfl_xor_sync(0xffffffffu, z, off);
@@ -648,21 +660,30 @@ __global__ void __launch_bounds__(256) attn_fewkeys_bwd_kernel(const FkParams p)
         float w1 = 1.f - w;
         if (!act) w = w1 = 0.f;  // inactive rows contribute nothing
         const float ds = w * w1 * g * p.scale;
+        const uint64_t ds2 = f32x2_pack(ds, ds), w2 = f32x2_pack(w, w), w12 = f32x2_pack(w1, w1);
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {
-          dk[0][j] = fmaf(ds, qf[j], dk[0][j]);
-          dv[0][j] = fmaf(w, gof[j], dv[0][j]);
-          dv[1][j] = fmaf(w1, gof[j], dv[1][j]);
+        for (int i = 0; i < 4; ++i) {
+          dk2[i] = f32x2_fma(ds2, qp[i], dk2[i]);
+          dv0[i] = f32x2_fma(w2, gp[i], dv0[i]);
+          dv1[i] = f32x2_fma(w12, gp[i], dv1[i]);
         }
         if (act && p.dq != nullptr) {
-          uint4 o;
-          o.x = pack_bf16x2(ds * kd[0], ds * kd[1]);
-          o.y = pack_bf16x2(ds * kd[2], ds * kd[3]);
-          o.z = pack_bf16x2(ds * kd[4], ds * kd[5]);
-          o.w = pack_bf16x2(ds * kd[6], ds * kd[7]);
-          *reinterpret_cast<uint4*>(p.dq + r * p.lddq + cx * 8) = o;
+          uint32_t o[4];
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            float a, b;
+            f32x2_unpack(f32x2_mul(ds2, kd2[i]), a, b);
+            o[i] = pack_bf16x2(a, b);
+          }
+          *reinterpret_cast<uint4*>(p.dq + r * p.lddq + cx * 8) = make_uint4(o[0], o[1], o[2], o[3]);
         }
       }
+    }
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      f32x2_unpack(dk2[i], dk[0][2 * i], dk[0][2 * i + 1]);
+      f32x2_unpack(dv0[i], dv[0][2 * i], dv[0][2 * i + 1]);
+      f32x2_unpack(dv1[i], dv[1][2 * i], dv[1][2 * i + 1]);
     }
 #pragma unroll
     for (int j = 0; j < 8; ++j) dk[1][j] = -dk[0][j];
