@@ -615,10 +615,11 @@ __global__ void __launch_bounds__(256) attn_fewkeys_bwd_kernel(const FkParams p)
 #pragma unroll
       for (int i = 0; i < 4; ++i) o[i] = f32x2_pack(__uint_as_float(w[i] << 16), __uint_as_float(w[i] & 0xffff0000u));
     };
-    constexpr int kU = 4;  // 4 rows x (Q, dO) = 128 bytes in flight per thread
-    for (int it0 = 0; it0 < kFewBwdRowsPerThread; it0 += kU) {
-      if (rlo + (int64_t)it0 * RY >= rhi) break;  // block-uniform
-      uint4 qv[kU], gv[kU];
+    // Software pipeline over groups of kU rows: the loads of group g + 1 are in flight while group g is computed (the
+    // ncu capture of the un-pipelined loop had 32 % of its stall cycles on the global loads at 3 CTAs / SM).
+    constexpr int kU = 2;
+    constexpr int kGroups = kFewBwdRowsPerThread / kU;
+    auto load_group = [&](int it0, uint4* qv, uint4* gv) {
 #pragma unroll
       for (int u = 0; u < kU; ++u) {
         const int64_t rr = rlo + (int64_t)(it0 + u) * RY + ry;
@@ -626,6 +627,8 @@ __global__ void __launch_bounds__(256) attn_fewkeys_bwd_kernel(const FkParams p)
         qv[u] = __ldg(reinterpret_cast<const uint4*>(p.q + r * p.ldq + cx * 8));
         gv[u] = __ldg(reinterpret_cast<const uint4*>(p.dout + r * p.lddo + cx * 8));
       }
+    };
+    auto compute_group = [&](int it0, const uint4* qv, const uint4* gv) {
 #pragma unroll
       for (int u = 0; u < kU; ++u) {
         if (rlo + (int64_t)(it0 + u) * RY >= rhi) break;  // block-uniform
@@ -678,6 +681,16 @@ __global__ void __launch_bounds__(256) attn_fewkeys_bwd_kernel(const FkParams p)
           *reinterpret_cast<uint4*>(p.dq + r * p.lddq + cx * 8) = make_uint4(o[0], o[1], o[2], o[3]);
         }
       }
+    };
+    uint4 qa[kU], ga[kU], qb[kU], gb2[kU];
+    load_group(0, qa, ga);
+    for (int gi = 0; gi < kGroups; gi += 2) {  // ping-pong buffers: no register copies
+      if (rlo + (int64_t)(gi * kU) * RY >= rhi) break;  // block-uniform
+      load_group((gi + 1) * kU, qb, gb2);
+      compute_group(gi * kU, qa, ga);
+      if (rlo + (int64_t)((gi + 1) * kU) * RY >= rhi) break;
+      if (gi + 2 < kGroups) load_group((gi + 2) * kU, qa, ga);
+      compute_group((gi + 1) * kU, qb, gb2);
     }
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
@@ -780,21 +793,32 @@ __global__ void __launch_bounds__(256) attn_fewkeys_bwd_kernel(const FkParams p)
 
   }  // LT != 2
 
-  // ---- fixed-order reduction over the CTA's row lanes ---------------------------------------------
-  for (int t = 0; t < RY; ++t) {
-    if (ry == t) {
+  // ---- fixed-order reduction over the CTA's row lanes: every lane writes its sums, ONE barrier, lane 0 adds them in
+  // order (a chain of RY barriers cost 14 % of the stall cycles) ------------------------------------------------
+  float* s_part = RY > 1 ? s_red + 2 * LT * C : s_red;  // [RY][2][LT][C]; a single row lane writes the sums directly
 #pragma unroll
-      for (int l = 0; l < LT; ++l) {
+  for (int l = 0; l < LT; ++l) {
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {
-          float* a = &s_red[(0 * LT + l) * C + cx * 8 + j];
-          float* b2 = &s_red[(1 * LT + l) * C + cx * 8 + j];
-          *a = (t == 0 ? 0.f : *a) + dk[l][j];
-          *b2 = (t == 0 ? 0.f : *b2) + dv[l][j];
+    for (int j = 0; j < 8; j += 4) {
+      *reinterpret_cast<float4*>(&s_part[((ry * 2 + 0) * LT + l) * C + cx * 8 + j]) = make_float4(dk[l][j], dk[l][j + 1], dk[l][j + 2], dk[l][j + 3]);
+      *reinterpret_cast<float4*>(&s_part[((ry * 2 + 1) * LT + l) * C + cx * 8 + j]) = make_float4(dv[l][j], dv[l][j + 1], dv[l][j + 2], dv[l][j + 3]);
+    }
+  }
+  __syncthreads();
+  if (ry == 0 && RY > 1) {
+#pragma unroll
+    for (int l = 0; l < LT; ++l) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        float a = 0.f, b2 = 0.f;
+        for (int t = 0; t < RY; ++t) {
+          a += s_part[((t * 2 + 0) * LT + l) * C + cx * 8 + j];
+          b2 += s_part[((t * 2 + 1) * LT + l) * C + cx * 8 + j];
         }
+        s_red[(0 * LT + l) * C + cx * 8 + j] = a;
+        s_red[(1 * LT + l) * C + cx * 8 + j] = b2;
       }
     }
-    __syncthreads();
   }
   if (ry == 0) {
 #pragma unroll
@@ -861,8 +885,8 @@ template <int LT, int LPH>
 int launch_fewkeys_bwd(const FkParams& p, int64_t ngroups, int C8, cudaStream_t st) {
   const int RY = fk_block_rows(C8);
   TVI_CHECK_ARG(C8 * RY <= 256, "tvi_attn_fewkeys_bwd: heads*d = %d is too wide for this kernel", C8 * 8);
-  const size_t sm = (size_t)2 * LT * C8 * 8 * sizeof(float);
-  TVI_CHECK_ARG(sm <= 160 * 1024, "tvi_attn_fewkeys_bwd: L*heads*d too large for the reduction buffer");
+  const size_t sm = (size_t)2 * LT * C8 * 8 * sizeof(float) * (RY > 1 ? 1 + RY : 1);  // the sums + every row lane's partials
+  TVI_CHECK_ARG(sm <= 200 * 1024, "tvi_attn_fewkeys_bwd: L*heads*d too large for the reduction buffer");
   static size_t configured = 0;
   if (sm > 48 * 1024 && sm > configured) {
     TVI_CUDA_OK(cudaFuncSetAttribute(attn_fewkeys_bwd_kernel<LT, LPH>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
