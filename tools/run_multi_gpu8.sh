@@ -5,10 +5,10 @@ OUT=gpurun_out/r2_multi8
 : > ${OUT}_train_ddp.jsonl
 PORT=29611
 for N in 4 8; do
-  for cfg in "576x1024 bf16" "512x320 fp32"; do
+  for cfg in "576x1024 bf16" "512x320 fp32" "576x1024 bf16 --module" "512x320 fp32 --module"; do
     set -- $cfg
     PORT=$((PORT+1))
-    timeout 200 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port $PORT tools/train_ddp_bench.py --res $1 --param-dtype $2 2>> ${OUT}_train_ddp.err | grep '^{' >> ${OUT}_train_ddp.jsonl
+    timeout 200 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port $PORT tools/train_ddp_bench.py --res $1 --param-dtype $2 $3 2>> ${OUT}_train_ddp.err | grep '^{' >> ${OUT}_train_ddp.jsonl
   done
 done
 for N in 4 8; do

@@ -33,6 +33,8 @@ ap.add_argument("--res", default="576x1024")
 ap.add_argument("--param-dtype", default="bf16", choices=["bf16", "fp32"])
 ap.add_argument("--steps", type=int, default=5)
 ap.add_argument("--clips", type=int, default=2)
+ap.add_argument("--module", action="store_true", help="train through the module-level swap (TransformerSpatioTemporalModel.forward, "
+                "NCHW in / out: GroupNorm, proj_in, block pair, AlphaBlender, proj_out) instead of the bare block pair")
 args = ap.parse_args()
 
 rank, world, local = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1)), int(os.environ.get("LOCAL_RANK", 0))
@@ -66,15 +68,46 @@ class Pair(torch.nn.Module):
         return self.temporal(self.spatial(x, encoder_hidden_states=ctx_s), num_frames=T, encoder_hidden_states=ctx_t)
 
 
-pair = Pair().to(dev, pdt)
+class Module(torch.nn.Module):
+    """src/train.py's unit: the whole TransformerSpatioTemporalModel, temporal block + time_mixer trainable."""
+
+    def __init__(self):
+        super().__init__()
+        from timelapse_video_interpolation_b200.modules import TransformerSpatioTemporalModel
+        g = torch.Generator().manual_seed(3)
+        self.m = TransformerSpatioTemporalModel(heads, C // heads, in_channels=C, num_layers=1, cross_attention_dim=1024)
+        with torch.no_grad():
+            for name, p in self.m.named_parameters():
+                if name.endswith("mix_factor"):
+                    p.fill_(0.5)
+                elif "norm" in name:
+                    p.fill_(1.0 if name.endswith("weight") else 0.0)
+                else:
+                    p.copy_((torch.rand(p.shape, generator=g) * 2 - 1) * (p.shape[-1] ** -0.5 if p.dim() > 1 else C ** -0.5))
+                p.requires_grad_("temporal_transformer_blocks" in name or "time_mixer" in name)
+
+    def forward(self, x, ctx_s, ind):
+        return self.m(x, encoder_hidden_states=ctx_s, image_only_indicator=ind, return_dict=False)[0]
+
+
 proc = TviAttnProcessor(cast_inputs=True)
-blocks.install_blocks(pair, processor=proc)
-model = DDP(pair, device_ids=[local], gradient_as_bucket_view=True)
 g = torch.Generator().manual_seed(100 + rank)  # different clips on every rank
-x = torch.randn(B * T, S, C, generator=g).to(torch.bfloat16).to(dev).requires_grad_(True)
-ctx_s = torch.randn(B * T, 2, 1024, generator=g).to(torch.bfloat16).to(dev)
-ctx_t = torch.randn(B * S, 1, 1024, generator=g).to(torch.bfloat16).to(dev)
-dy = (torch.randn(B * T, S, C, generator=g) / 8).to(torch.bfloat16).to(dev)
+if args.module:
+    from timelapse_video_interpolation_b200 import spatio_temporal
+    pair = Module().to(dev, pdt).train()
+    spatio_temporal.install_spatio_temporal(pair, processor=proc)
+    x = torch.randn(B * T, C, h, w, generator=g).to(torch.bfloat16).to(dev).requires_grad_(True)
+    ctx_s = torch.randn(B * T, 1, 1024, generator=g).to(torch.bfloat16).to(dev)
+    ctx_t = torch.zeros(B, T, device=dev)                      # image_only_indicator
+    dy = (torch.randn(B * T, C, h, w, generator=g) / 8).to(torch.bfloat16).to(dev)
+else:
+    pair = Pair().to(dev, pdt)
+    blocks.install_blocks(pair, processor=proc)
+    x = torch.randn(B * T, S, C, generator=g).to(torch.bfloat16).to(dev).requires_grad_(True)
+    ctx_s = torch.randn(B * T, 2, 1024, generator=g).to(torch.bfloat16).to(dev)
+    ctx_t = torch.randn(B * S, 1, 1024, generator=g).to(torch.bfloat16).to(dev)
+    dy = (torch.randn(B * T, S, C, generator=g) / 8).to(torch.bfloat16).to(dev)
+model = DDP(pair, device_ids=[local], gradient_as_bucket_view=True)
 
 
 def step(sync=True):
@@ -122,7 +155,7 @@ dist.all_reduce(same, op=dist.ReduceOp.MIN)
 ddp_extra = ms_ddp - ms_local
 if rank == 0:
     print(json.dumps({
-        "config": "train_ddp_L0_block_pair", "n_gpus": world, "resolution": args.res, "tokens_per_frame": S, "frames": T,
+        "config": "train_ddp_L0_module" if args.module else "train_ddp_L0_block_pair", "n_gpus": world, "resolution": args.res, "tokens_per_frame": S, "frames": T,
         "clips_per_gpu": B, "param_dtype": args.param_dtype, "trainable_params": sum(p.numel() for p in params),
         "gradient_bytes": nbytes, "ms_step_ddp": ms_ddp, "ms_step_no_sync": ms_local, "ms_allreduce_alone": ms_allreduce,
         "ms_ddp_minus_no_sync": ddp_extra,
