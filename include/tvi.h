@@ -324,8 +324,8 @@ int tvi_attn_spatial_fwd_algo(const tvi_bf16* q, const tvi_bf16* k, const tvi_bf
  * column slices of one packed [tokens, 3C] buffer, lddq = lddk = lddv = 3C).
  *
  * spatial : flash-style recomputation from q, k, v and the forward's `lse`; `o` is the forward output.
- *           workspace = tvi_attn_spatial_bwd_workspace_bytes(batch, heads, S) bytes.  d == 64.
- * temporal: T <= 64, needs neither o nor lse.  d == 64.
+ *           workspace = tvi_attn_spatial_bwd_workspace_bytes(batch, heads, S) bytes.  d in {64, 128} (128: mma.sync passes).
+ * temporal: T <= 64, needs neither o nor lse.  d in {64, 128}.
  * fewkeys : dk, dv are [ngroups*L, heads*d] (sum over the rows of each group); `bias` as in the forward
  *           (a constant: no gradient); q == dq == NULL is allowed when L == 1 (softmax == 1).
  *           workspace = tvi_attn_fewkeys_bwd_workspace_bytes(...) bytes (may be 0).

@@ -144,6 +144,43 @@ def test_temporal_bwd_matches_autograd(cuda, nseq, heads, Tq, Tk):
     _grad_close(dv, rv, "temporal dv")
 
 
+@pytest.mark.parametrize("nseq,heads,Tq,Tk", [(300, 10, 14, 14), (97, 3, 25, 25), (12, 2, 64, 64), (19, 1, 14, 9), (11, 2, 33, 50)])
+def test_temporal_bwd_head_dim_128(cuda, nseq, heads, Tq, Tk):
+    # d = 128: the class default num_attention_heads=(5, 10, 10, 20) at C = 1280 (src/models/unet_spatio_temporal_condition.py:94)
+    g = torch.Generator().manual_seed(nseq + Tq + 1)
+    C = heads * 128
+    q, k, v = _packed_qkv(nseq * Tq, nseq * Tk, C, g, cuda)
+    dout = torch.randn(nseq * Tq, C, generator=g).to(torch.bfloat16).to(cuda)
+    scale = 128 ** -0.5
+    dq, dk, dv = ops.attn_temporal_bwd(q, k, v, dout, nseq, heads, Tq, Tk, scale)
+    torch.cuda.synchronize()
+    _, rq, rk, rv = _ref_attention_grads(q, k, v, dout, nseq, heads, Tq, Tk, scale)
+    _grad_close(dq, rq, "temporal dq d=128")
+    _grad_close(dk, rk, "temporal dk d=128")
+    _grad_close(dv, rv, "temporal dv d=128")
+
+
+@pytest.mark.parametrize("batch,heads,S,Skv", [(2, 2, 144, 144), (1, 10, 576, 576), (2, 1, 300, 200), (1, 3, 130, 65), (1, 2, 1111, 1111)])
+def test_spatial_bwd_head_dim_128(cuda, batch, heads, S, Skv):
+    from timelapse_video_interpolation_b200 import _lib
+    g = torch.Generator().manual_seed(S + Skv + 7)
+    C = heads * 128
+    q, k, v = _packed_qkv(batch * S, batch * Skv, C, g, cuda)
+    dout = torch.randn(batch * S, C, generator=g).to(torch.bfloat16).to(cuda)
+    scale = 128 ** -0.5
+    lse = torch.empty(batch * S, heads, dtype=torch.float32, device=cuda)
+    o = ops.attn_spatial(q, k, v, batch, heads, S, Skv, scale, lse=lse)
+    dq, dk, dv = ops.attn_spatial_bwd(q, k, v, o, dout, lse, batch, heads, S, Skv, scale)      # AUTO -> the mma.sync passes
+    torch.cuda.synchronize()
+    ro, rq, rk, rv = _ref_attention_grads(q, k, v, dout, batch, heads, S, Skv, scale)
+    _grad_close(o, ro, "spatial o d=128")
+    _grad_close(dq, rq, "spatial dq d=128")
+    _grad_close(dk, rk, "spatial dk d=128")
+    _grad_close(dv, rv, "spatial dv d=128")
+    with pytest.raises(_lib.TviError):   # the tcgen05 passes are built for 64-wide heads
+        ops.attn_spatial_bwd(q, k, v, o, dout, lse, batch, heads, S, Skv, scale, algo=_lib.SPATIAL_TCGEN05)
+
+
 @pytest.mark.parametrize("algo", ["mma_sync", "tcgen05"])
 @pytest.mark.parametrize("batch,heads,S,Skv", [(2, 5, 144, 144), (2, 5, 576, 576), (1, 2, 1000, 1000), (2, 1, 300, 200),
                                                (1, 3, 130, 65), (1, 5, 2304, 2304), (3, 2, 1111, 1111), (1, 1, 128, 256)])

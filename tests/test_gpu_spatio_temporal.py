@@ -162,6 +162,30 @@ def test_model_with_128_wide_heads_matches_oracle(cuda):
     assert_block_close("spatio-temporal model d=128", y, ref, stores=9)
 
 
+def test_model_with_128_wide_heads_trains(cuda):
+    # forward + backward through a d = 128 module (mma.sync spatial / temporal kernels in both directions): finite gradients that
+    # match fp32 autograd of the same math
+    B, T, H, W, C, heads = 1, 4, 12, 12, 256, 2          # S = 144: the mma.sync spatial kernels; T = 4: the temporal ones
+    m = _model(C, heads, 1024, 19, cuda, head_dim=128).train()
+    spatio_temporal.install_spatio_temporal(m)
+    g = torch.Generator().manual_seed(4)
+    x = _bf(torch.randn(B * T, C, H, W, generator=g), cuda).requires_grad_(True)
+    e = _bf(torch.randn(B * T, 1, 1024, generator=g), cuda)
+    wgt = _bf(torch.randn(B * T, C, H, W, generator=g), cuda)
+    ind = torch.zeros(B, T, device=cuda)
+    y = m(x, encoder_hidden_states=e, image_only_indicator=ind, return_dict=False)[0]
+    (y.float() * wgt.float()).sum().backward()
+    P = {n: p.detach().float().cpu().requires_grad_(True) for n, p in m.named_parameters()}
+    xr = x.detach().float().cpu().requires_grad_(True)
+    yr = _model_ref(P, xr, e.float().cpu(), ind.cpu(), heads, T)
+    (yr * wgt.float().cpu()).sum().backward()
+    ps = dict(m.named_parameters())
+    for name, got, ref in [("dx", x.grad, xr.grad)] + [(n, ps[n].grad, P[n].grad) for n in (
+            "transformer_blocks.0.attn1.to_q.weight", "temporal_transformer_blocks.0.attn1.to_v.weight", "proj_in.weight")]:
+        err, scale = float((got.float().cpu() - ref).abs().max()), max(float(ref.abs().max()), 1e-6)
+        assert err <= 2e-2 * scale, (name, err, scale)
+
+
 def test_model_forward_matches_reference_golden(cuda, golden_dir):
     # the reference's own module output (fp32, CPU) vs the libtvi forward in bf16 on the same weights
     z = np.load(golden_dir / "spatio_temporal.npz")

@@ -27,17 +27,18 @@ constexpr float kLog2e = 1.4426950408889634f;
 // ---------------------------------------------------------------------------------------------
 // D[row, head] = sum_d dO . O
 // ---------------------------------------------------------------------------------------------
+template <int DH>
 __global__ void attn_bwd_dot_kernel(const tvi_bf16* __restrict__ o, const tvi_bf16* __restrict__ dout, float* __restrict__ D,
                                     int64_t nrows, int heads, int64_t ldo, int64_t lddo) {
-  // 8 lanes per (row, head): one 16-byte chunk each
+  // 8 * DH lanes per (row, head): one 16-byte chunk each
   const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  const int64_t item = idx >> 3;
-  const int c = (int)(idx & 7);
+  const int64_t item = idx / (8 * DH);
+  const int c = (int)(idx % (8 * DH));
   const bool in = item < nrows * heads;
   const int64_t row = in ? item / heads : 0;
   const int h = in ? (int)(item - row * heads) : 0;
-  const uint4 a = __ldg(reinterpret_cast<const uint4*>(o + row * ldo + h * 64 + c * 8));
-  const uint4 b = __ldg(reinterpret_cast<const uint4*>(dout + row * lddo + h * 64 + c * 8));
+  const uint4 a = __ldg(reinterpret_cast<const uint4*>(o + row * ldo + h * 64 * DH + c * 8));
+  const uint4 b = __ldg(reinterpret_cast<const uint4*>(dout + row * lddo + h * 64 * DH + c * 8));
   const __nv_bfloat162* ha = reinterpret_cast<const __nv_bfloat162*>(&a);
   const __nv_bfloat162* hb = reinterpret_cast<const __nv_bfloat162*>(&b);
   float s = 0.f;
@@ -50,6 +51,7 @@ __global__ void attn_bwd_dot_kernel(const tvi_bf16* __restrict__ o, const tvi_bf
   s += __shfl_xor_sync(0xffffffffu, s, 1);
   s += __shfl_xor_sync(0xffffffffu, s, 2);
   s += __shfl_xor_sync(0xffffffffu, s, 4);
+  if (DH == 2) s += __shfl_xor_sync(0xffffffffu, s, 8);
   if (in && c == 0) D[item] = s;
 }
 
@@ -60,10 +62,11 @@ constexpr int kFbBr = 128;  // rows per CTA
 constexpr int kFbBc = 64;   // streamed columns per stage
 constexpr int kFbStages = 3;
 constexpr int kFbThreads = 256;
-constexpr int kFbRowBytes = kFbBr * 128;
-constexpr int kFbColBytes = kFbBc * 128;
-constexpr int kFbStageBytes = 2 * kFbColBytes + 2 * kFbBc * 4;  // two tiles + lse[64] + D[64]
-constexpr int kFbSmem = 2 * kFbRowBytes + kFbStages * kFbStageBytes;
+constexpr int kFbRowHalf = kFbBr * 128;  // one 64-column half of a row tile
+constexpr int kFbColHalf = kFbBc * 128;  // one 64-column half of a streamed tile
+// DH = d / 64 swizzled halves per tile (d = 128: the class default heads of unet_spatio_temporal_condition.py:94)
+constexpr int fb_stage_bytes(int DH) { return 2 * DH * kFbColHalf + 2 * kFbBc * 4; }  // two tiles + lse[64] + D[64]
+constexpr int fb_smem(int DH) { return 2 * DH * kFbRowHalf + kFbStages * fb_stage_bytes(DH); }
 
 struct FbParams {
   const tvi_bf16 *r1, *r2;  // row operands      rows = keys: K, V     rows = queries: Q, dO
@@ -76,8 +79,10 @@ struct FbParams {
   float scale;
 };
 
-template <bool kRowsAreKeys>
+template <bool kRowsAreKeys, int DH>
 __global__ void __launch_bounds__(kFbThreads, 1) attn_bwd_flash_kernel(const FbParams p) {
+  constexpr int kFbRowBytes = DH * kFbRowHalf, kFbColBytes = DH * kFbColHalf, kFbStageBytes = fb_stage_bytes(DH);
+  constexpr int ND = 8 * DH;  // 8-column tiles across d
   extern __shared__ __align__(128) uint8_t smem_raw[];
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int g = lane >> 2, qd = lane & 3;
@@ -88,10 +93,10 @@ __global__ void __launch_bounds__(kFbThreads, 1) attn_bwd_flash_kernel(const FbP
   const uint32_t sR1 = smem_u32(smem_raw);
   const uint32_t sR2 = sR1 + kFbRowBytes;
   const uint32_t sSt = sR2 + kFbRowBytes;
-  const tvi_bf16* r1b = p.r1 + ((int64_t)b * p.nrows) * p.ldr1 + h * 64;
-  const tvi_bf16* r2b = p.r2 + ((int64_t)b * p.nrows) * p.ldr2 + h * 64;
-  const tvi_bf16* c1b = p.c1 + ((int64_t)b * p.ncols) * p.ldc1 + h * 64;
-  const tvi_bf16* c2b = p.c2 + ((int64_t)b * p.ncols) * p.ldc2 + h * 64;
+  const tvi_bf16* r1b = p.r1 + ((int64_t)b * p.nrows) * p.ldr1 + h * 64 * DH;
+  const tvi_bf16* r2b = p.r2 + ((int64_t)b * p.nrows) * p.ldr2 + h * 64 * DH;
+  const tvi_bf16* c1b = p.c1 + ((int64_t)b * p.ncols) * p.ldc1 + h * 64 * DH;
+  const tvi_bf16* c2b = p.c2 + ((int64_t)b * p.ncols) * p.ldc2 + h * 64 * DH;
   // lse / D are indexed by the query: a column when rows are keys, a row otherwise
   const int nq = kRowsAreKeys ? p.ncols : p.nrows;
   const float* lse_b = p.lse + ((int64_t)b * nq) * p.heads + h;
@@ -100,11 +105,11 @@ __global__ void __launch_bounds__(kFbThreads, 1) attn_bwd_flash_kernel(const FbP
   auto load_stage = [&](int st, int j0) {
     const uint32_t dst = sSt + st * kFbStageBytes;
 #pragma unroll
-    for (int i = 0; i < (kFbBc * 8) / kFbThreads; ++i) {
+    for (int i = 0; i < (kFbBc * ND) / kFbThreads; ++i) {
       const int idx = tid + i * kFbThreads;
-      const int r = idx >> 3, c = idx & 7;
+      const int r = idx / ND, c = idx % ND;
       const bool in = (j0 + r) < p.ncols;
-      const uint32_t off = tile_off(r, c);
+      const uint32_t off = (c >> 3) * kFbColHalf + tile_off(r, c & 7);
       const int64_t row = in ? (j0 + r) : 0;
       asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst + off), "l"(c1b + row * p.ldc1 + c * 8),
                    "r"(in ? 16 : 0)
@@ -125,15 +130,16 @@ __global__ void __launch_bounds__(kFbThreads, 1) attn_bwd_flash_kernel(const FbP
 
   // ---- prologue: the two row tiles + first two column stages -------------------------------
 #pragma unroll
-  for (int i = 0; i < (kFbBr * 8) / kFbThreads; ++i) {
+  for (int i = 0; i < (kFbBr * ND) / kFbThreads; ++i) {
     const int idx = tid + i * kFbThreads;
-    const int r = idx >> 3, c = idx & 7;
+    const int r = idx / ND, c = idx % ND;
     const bool in = (r0 + r) < p.nrows;
     const int64_t row = in ? (r0 + r) : 0;
-    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(sR1 + tile_off(r, c)), "l"(r1b + row * p.ldr1 + c * 8),
+    const uint32_t roff = (c >> 3) * kFbRowHalf + tile_off(r, c & 7);
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(sR1 + roff), "l"(r1b + row * p.ldr1 + c * 8),
                  "r"(in ? 16 : 0)
                  : "memory");
-    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(sR2 + tile_off(r, c)), "l"(r2b + row * p.ldr2 + c * 8),
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(sR2 + roff), "l"(r2b + row * p.ldr2 + c * 8),
                  "r"(in ? 16 : 0)
                  : "memory");
   }
@@ -158,12 +164,12 @@ __global__ void __launch_bounds__(kFbThreads, 1) attn_bwd_flash_kernel(const FbP
     }
   }
 
-  float acc1[8][4];                         // dS . C1  (dK or dQ)
-  float acc2[kRowsAreKeys ? 8 : 1][4];      // P . C2   (dV)
+  float acc1[ND][4];                         // dS . C1  (dK or dQ)
+  float acc2[kRowsAreKeys ? ND : 1][4];      // P . C2   (dV)
 #pragma unroll
-  for (int nt = 0; nt < 8; ++nt) acc1[nt][0] = acc1[nt][1] = acc1[nt][2] = acc1[nt][3] = 0.f;
+  for (int nt = 0; nt < ND; ++nt) acc1[nt][0] = acc1[nt][1] = acc1[nt][2] = acc1[nt][3] = 0.f;
 #pragma unroll
-  for (int nt = 0; nt < (kRowsAreKeys ? 8 : 1); ++nt) acc2[nt][0] = acc2[nt][1] = acc2[nt][2] = acc2[nt][3] = 0.f;
+  for (int nt = 0; nt < (kRowsAreKeys ? ND : 1); ++nt) acc2[nt][0] = acc2[nt][1] = acc2[nt][2] = acc2[nt][3] = 0.f;
 
   const int arow = warp * 16 + (lane & 7) + ((lane >> 3) & 1) * 8;  // ldmatrix row of this lane in the row tiles
 
@@ -186,14 +192,15 @@ __global__ void __launch_bounds__(kFbThreads, 1) attn_bwd_flash_kernel(const FbP
       dp[nt][0] = dp[nt][1] = dp[nt][2] = dp[nt][3] = 0.f;
     }
 #pragma unroll
-    for (int ks = 0; ks < 4; ++ks) {
+    for (int ks = 0; ks < 4 * DH; ++ks) {
       uint32_t a1[4], a2[4];
-      ldsm_x4(sR1 + tile_off(arow, 2 * ks + (lane >> 4)), a1[0], a1[1], a1[2], a1[3]);
-      ldsm_x4(sR2 + tile_off(arow, 2 * ks + (lane >> 4)), a2[0], a2[1], a2[2], a2[3]);
+      const uint32_t aoff = (ks >> 2) * kFbRowHalf + tile_off(arow, 2 * (ks & 3) + (lane >> 4));
+      ldsm_x4(sR1 + aoff, a1[0], a1[1], a1[2], a1[3]);
+      ldsm_x4(sR2 + aoff, a2[0], a2[1], a2[2], a2[3]);
 #pragma unroll
       for (int np = 0; np < 4; ++np) {
         uint32_t b0, b1, b2, b3;
-        const uint32_t boff = tile_off(np * 16 + (lane & 7) + (lane >> 4) * 8, 2 * ks + ((lane >> 3) & 1));
+        const uint32_t boff = (ks >> 2) * kFbColHalf + tile_off(np * 16 + (lane & 7) + (lane >> 4) * 8, 2 * (ks & 3) + ((lane >> 3) & 1));
         ldsm_x4(sC1 + boff, b0, b1, b2, b3);
         mma_bf16_16816(s[2 * np], a1, b0, b1);
         mma_bf16_16816(s[2 * np + 1], a1, b2, b3);
@@ -237,9 +244,9 @@ __global__ void __launch_bounds__(kFbThreads, 1) attn_bwd_flash_kernel(const FbP
       const uint32_t ad[4] = {dfr[2 * kk][0], dfr[2 * kk][1], dfr[2 * kk + 1][0], dfr[2 * kk + 1][1]};
       const uint32_t ap[4] = {pfr[2 * kk][0], pfr[2 * kk][1], pfr[2 * kk + 1][0], pfr[2 * kk + 1][1]};
 #pragma unroll
-      for (int nc = 0; nc < 8; nc += 2) {
+      for (int nc = 0; nc < ND; nc += 2) {
         uint32_t b0, b1, b2, b3;
-        const uint32_t boff = tile_off(kk * 16 + (lane & 7) + ((lane >> 3) & 1) * 8, nc + (lane >> 4));
+        const uint32_t boff = (nc >> 3) * kFbColHalf + tile_off(kk * 16 + (lane & 7) + ((lane >> 3) & 1) * 8, (nc & 7) + (lane >> 4));
         ldsm_x4_t(sC1 + boff, b0, b1, b2, b3);
         mma_bf16_16816(acc1[nc], ad, b0, b1);
         mma_bf16_16816(acc1[nc + 1], ad, b2, b3);
@@ -259,41 +266,42 @@ __global__ void __launch_bounds__(kFbThreads, 1) attn_bwd_flash_kernel(const FbP
   uint8_t* pR2 = smem_raw + kFbRowBytes;
   const int ra = warp * 16 + g, rb = ra + 8;
 #pragma unroll
-  for (int nt = 0; nt < 8; ++nt) {
-    *reinterpret_cast<uint32_t*>(pR1 + tile_off(ra, nt) + qd * 4) = pack_bf16x2(acc1[nt][0] * p.scale, acc1[nt][1] * p.scale);
-    *reinterpret_cast<uint32_t*>(pR1 + tile_off(rb, nt) + qd * 4) = pack_bf16x2(acc1[nt][2] * p.scale, acc1[nt][3] * p.scale);
+  for (int nt = 0; nt < ND; ++nt) {
+    const int hoff = (nt >> 3) * kFbRowHalf;
+    *reinterpret_cast<uint32_t*>(pR1 + hoff + tile_off(ra, nt & 7) + qd * 4) = pack_bf16x2(acc1[nt][0] * p.scale, acc1[nt][1] * p.scale);
+    *reinterpret_cast<uint32_t*>(pR1 + hoff + tile_off(rb, nt & 7) + qd * 4) = pack_bf16x2(acc1[nt][2] * p.scale, acc1[nt][3] * p.scale);
     if (kRowsAreKeys) {
-      *reinterpret_cast<uint32_t*>(pR2 + tile_off(ra, nt) + qd * 4) = pack_bf16x2(acc2[nt][0], acc2[nt][1]);
-      *reinterpret_cast<uint32_t*>(pR2 + tile_off(rb, nt) + qd * 4) = pack_bf16x2(acc2[nt][2], acc2[nt][3]);
+      *reinterpret_cast<uint32_t*>(pR2 + hoff + tile_off(ra, nt & 7) + qd * 4) = pack_bf16x2(acc2[nt][0], acc2[nt][1]);
+      *reinterpret_cast<uint32_t*>(pR2 + hoff + tile_off(rb, nt & 7) + qd * 4) = pack_bf16x2(acc2[nt][2], acc2[nt][3]);
     }
   }
   __syncwarp();
-  tvi_bf16* o1b = p.out1 + ((int64_t)b * p.nrows) * p.ldo1 + h * 64;
-  tvi_bf16* o2b = kRowsAreKeys ? p.out2 + ((int64_t)b * p.nrows) * p.ldo2 + h * 64 : nullptr;
+  tvi_bf16* o1b = p.out1 + ((int64_t)b * p.nrows) * p.ldo1 + h * 64 * DH;
+  tvi_bf16* o2b = kRowsAreKeys ? p.out2 + ((int64_t)b * p.nrows) * p.ldo2 + h * 64 * DH : nullptr;
 #pragma unroll
-  for (int i = 0; i < 4; ++i) {
-    const int r = warp * 16 + (lane >> 3) + 4 * i;
+  for (int i = 0; i < 4 * DH; ++i) {
+    const int idx = lane + 32 * i;
+    const int r = warp * 16 + idx / ND, c = idx % ND;
     if (r0 + r < p.nrows) {
-      *reinterpret_cast<uint4*>(o1b + (int64_t)(r0 + r) * p.ldo1 + (lane & 7) * 8) =
-          *reinterpret_cast<const uint4*>(pR1 + tile_off(r, lane & 7));
+      const int soff = (c >> 3) * kFbRowHalf + tile_off(r, c & 7);
+      *reinterpret_cast<uint4*>(o1b + (int64_t)(r0 + r) * p.ldo1 + c * 8) = *reinterpret_cast<const uint4*>(pR1 + soff);
       if (kRowsAreKeys)
-        *reinterpret_cast<uint4*>(o2b + (int64_t)(r0 + r) * p.ldo2 + (lane & 7) * 8) =
-            *reinterpret_cast<const uint4*>(pR2 + tile_off(r, lane & 7));
+        *reinterpret_cast<uint4*>(o2b + (int64_t)(r0 + r) * p.ldo2 + c * 8) = *reinterpret_cast<const uint4*>(pR2 + soff);
     }
   }
 }
 
-template <bool kRowsAreKeys>
+template <bool kRowsAreKeys, int DH>
 int launch_flash_bwd(const FbParams& p, int batch, cudaStream_t st) {
   static bool configured[64] = {false};
   int dev = 0;
   TVI_CUDA_OK(cudaGetDevice(&dev));
   if (dev < 0 || dev >= 64 || !configured[dev]) {
-    TVI_CUDA_OK(cudaFuncSetAttribute(attn_bwd_flash_kernel<kRowsAreKeys>, cudaFuncAttributeMaxDynamicSharedMemorySize, kFbSmem));
+    TVI_CUDA_OK(cudaFuncSetAttribute(attn_bwd_flash_kernel<kRowsAreKeys, DH>, cudaFuncAttributeMaxDynamicSharedMemorySize, fb_smem(DH)));
     if (dev >= 0 && dev < 64) configured[dev] = true;
   }
   dim3 grid((unsigned)((p.nrows + kFbBr - 1) / kFbBr), (unsigned)(batch * p.heads));
-  attn_bwd_flash_kernel<kRowsAreKeys><<<grid, kFbThreads, kFbSmem, st>>>(p);
+  attn_bwd_flash_kernel<kRowsAreKeys, DH><<<grid, kFbThreads, fb_smem(DH), st>>>(p);
   TVI_LAUNCH_OK("attn_bwd_flash_kernel");
   return TVI_OK;
 }
@@ -301,12 +309,16 @@ int launch_flash_bwd(const FbParams& p, int batch, cudaStream_t st) {
 // ---------------------------------------------------------------------------------------------
 // temporal (short-sequence) backward
 // ---------------------------------------------------------------------------------------------
-template <int MT>
+// DH = d / 64: the d-wide tiles (Q, K, V, dO, the output staging) are DH swizzled 64-column halves; P and dS are
+// [queries][keys <= 64] and do not depend on d
+template <int MT, int DH>
 struct TemporalBwdCfg {
   static constexpr int kRows = 16 * MT;
-  static constexpr int kTileBytes = kRows * 128;
-  static constexpr int kWarpBytes = 6 * kTileBytes + 16 * 128;  // Q K V dO | P dS | 16-row output staging
-  static constexpr int kWarps = (MT == 1) ? 8 : 4;
+  static constexpr int kHalfBytes = kRows * 128;
+  static constexpr int kTileBytes = DH * kHalfBytes;
+  static constexpr int kStageBytes = DH * 16 * 128;
+  static constexpr int kWarpBytes = 4 * kTileBytes + 2 * kHalfBytes + kStageBytes;  // Q K V dO | P dS | 16-row output staging
+  static constexpr int kWarps = (MT == 1) ? 8 : (MT == 4 && DH == 2) ? 2 : 4;
   static constexpr int kSmemBytes = kWarps * kWarpBytes;
 };
 
@@ -319,10 +331,12 @@ struct TbParams {
   float scale;
 };
 
-template <int MT>
-__global__ void __launch_bounds__(TemporalBwdCfg<MT>::kWarps * 32) attn_temporal_bwd_kernel(const TbParams p) {
-  using Cfg = TemporalBwdCfg<MT>;
+template <int MT, int DH>
+__global__ void __launch_bounds__(TemporalBwdCfg<MT, DH>::kWarps * 32) attn_temporal_bwd_kernel(const TbParams p) {
+  using Cfg = TemporalBwdCfg<MT, DH>;
   constexpr int kRows = Cfg::kRows;
+  constexpr int kHalf = Cfg::kHalfBytes;
+  constexpr int ND = 8 * DH;  // 8-column tiles across d
   constexpr int NT = 2 * MT;
   extern __shared__ __align__(128) uint8_t smem_raw[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -333,45 +347,47 @@ __global__ void __launch_bounds__(TemporalBwdCfg<MT>::kWarps * 32) attn_temporal
   const uint32_t sV = sK + Cfg::kTileBytes;
   const uint32_t sDO = sV + Cfg::kTileBytes;
   const uint32_t sP = sDO + Cfg::kTileBytes;
-  const uint32_t sDS = sP + Cfg::kTileBytes;
+  const uint32_t sDS = sP + kHalf;
   uint8_t* pP = wptr + 4 * Cfg::kTileBytes;
-  uint8_t* pDS = pP + Cfg::kTileBytes;
-  uint8_t* pStage = wptr + 6 * Cfg::kTileBytes;
+  uint8_t* pDS = pP + kHalf;
+  uint8_t* pStage = pDS + kHalf;
   const float sl2 = p.scale * kLog2e;
 
   // 16 staged rows -> coalesced 128-bit stores (rows past `limit` are dropped)
   auto flush_rows = [&](tvi_bf16* dst, int64_t ld, int row0, int limit) {
     __syncwarp();
 #pragma unroll
-    for (int i = 0; i < 4; ++i) {
-      const int r = (lane >> 3) + 4 * i;
+    for (int i = 0; i < 4 * DH; ++i) {
+      const int idx = lane + 32 * i;
+      const int r = idx / ND, c = idx % ND;
       if (row0 + r < limit)
-        *reinterpret_cast<uint4*>(dst + (int64_t)(row0 + r) * ld + (lane & 7) * 8) =
-            *reinterpret_cast<const uint4*>(pStage + tile_off(r, lane & 7));
+        *reinterpret_cast<uint4*>(dst + (int64_t)(row0 + r) * ld + c * 8) =
+            *reinterpret_cast<const uint4*>(pStage + (c >> 3) * 2048 + tile_off(r, c & 7));
     }
     __syncwarp();
   };
   auto stage_acc = [&](const float (*acc)[4], float mul) {
 #pragma unroll
-    for (int nt = 0; nt < 8; ++nt) {
-      *reinterpret_cast<uint32_t*>(pStage + tile_off(g, nt) + qd * 4) = pack_bf16x2(acc[nt][0] * mul, acc[nt][1] * mul);
-      *reinterpret_cast<uint32_t*>(pStage + tile_off(g + 8, nt) + qd * 4) = pack_bf16x2(acc[nt][2] * mul, acc[nt][3] * mul);
+    for (int nt = 0; nt < ND; ++nt) {
+      uint8_t* ph = pStage + (nt >> 3) * 2048;
+      *reinterpret_cast<uint32_t*>(ph + tile_off(g, nt & 7) + qd * 4) = pack_bf16x2(acc[nt][0] * mul, acc[nt][1] * mul);
+      *reinterpret_cast<uint32_t*>(ph + tile_off(g + 8, nt & 7) + qd * 4) = pack_bf16x2(acc[nt][2] * mul, acc[nt][3] * mul);
     }
   };
 
   for (int64_t item = (int64_t)blockIdx.x * Cfg::kWarps + warp; item < p.nitems; item += (int64_t)gridDim.x * Cfg::kWarps) {
     const int64_t seq = item / p.heads;
     const int head = (int)(item - seq * p.heads);
-    const tvi_bf16* qb = p.q + seq * p.Tq * p.ldq + head * 64;
-    const tvi_bf16* kb = p.k + seq * p.Tk * p.ldk + head * 64;
-    const tvi_bf16* vb = p.v + seq * p.Tk * p.ldv + head * 64;
-    const tvi_bf16* dob = p.dout + seq * p.Tq * p.lddo + head * 64;
+    const tvi_bf16* qb = p.q + seq * p.Tq * p.ldq + head * 64 * DH;
+    const tvi_bf16* kb = p.k + seq * p.Tk * p.ldk + head * 64 * DH;
+    const tvi_bf16* vb = p.v + seq * p.Tk * p.ldv + head * 64 * DH;
+    const tvi_bf16* dob = p.dout + seq * p.Tq * p.lddo + head * 64 * DH;
     {
-      const int c = lane & 7;
 #pragma unroll
-      for (int i = 0; i < kRows / 4; ++i) {
-        const int r = (lane >> 3) + 4 * i;
-        const uint32_t off = tile_off(r, c);
+      for (int i = 0; i < kRows * DH / 4; ++i) {
+        const int idx = lane + 32 * i;
+        const int r = idx / ND, c = idx % ND;
+        const uint32_t off = (c >> 3) * kHalf + tile_off(r, c & 7);
         const bool pq = r < p.Tq, pk = r < p.Tk;
         cp_async_16(wptr + off, pq ? qb + r * p.ldq + c * 8 : qb, pq);
         cp_async_16(wptr + Cfg::kTileBytes + off, pk ? kb + r * p.ldk + c * 8 : kb, pk);
@@ -394,15 +410,15 @@ __global__ void __launch_bounds__(TemporalBwdCfg<MT>::kWarps * 32) attn_temporal
         dp[nt][0] = dp[nt][1] = dp[nt][2] = dp[nt][3] = 0.f;
       }
 #pragma unroll
-      for (int ks = 0; ks < 4; ++ks) {
+      for (int ks = 0; ks < 4 * DH; ++ks) {
         uint32_t a1[4], a2[4];
-        const uint32_t aoff = tile_off(mt * 16 + (lane & 7) + ((lane >> 3) & 1) * 8, 2 * ks + (lane >> 4));
+        const uint32_t aoff = (ks >> 2) * kHalf + tile_off(mt * 16 + (lane & 7) + ((lane >> 3) & 1) * 8, 2 * (ks & 3) + (lane >> 4));
         ldsm_x4(sQ + aoff, a1[0], a1[1], a1[2], a1[3]);
         ldsm_x4(sDO + aoff, a2[0], a2[1], a2[2], a2[3]);
 #pragma unroll
         for (int np = 0; np < MT; ++np) {
           uint32_t b0, b1, b2, b3;
-          const uint32_t boff = tile_off(np * 16 + (lane & 7) + (lane >> 4) * 8, 2 * ks + ((lane >> 3) & 1));
+          const uint32_t boff = (ks >> 2) * kHalf + tile_off(np * 16 + (lane & 7) + (lane >> 4) * 8, 2 * (ks & 3) + ((lane >> 3) & 1));
           ldsm_x4(sK + boff, b0, b1, b2, b3);
           mma_bf16_16816(s[2 * np], a1, b0, b1);
           mma_bf16_16816(s[2 * np + 1], a1, b2, b3);
@@ -466,23 +482,23 @@ __global__ void __launch_bounds__(TemporalBwdCfg<MT>::kWarps * 32) attn_temporal
         *reinterpret_cast<uint32_t*>(pDS + tile_off(rb, nt) + qd * 4) = dfr[nt][1];
       }
       // dQ tile = dS K
-      float acc[8][4];
+      float acc[ND][4];
 #pragma unroll
-      for (int nt = 0; nt < 8; ++nt) acc[nt][0] = acc[nt][1] = acc[nt][2] = acc[nt][3] = 0.f;
+      for (int nt = 0; nt < ND; ++nt) acc[nt][0] = acc[nt][1] = acc[nt][2] = acc[nt][3] = 0.f;
 #pragma unroll
       for (int kk = 0; kk < MT; ++kk) {
         if (kk * 16 >= p.Tk) break;
         const uint32_t a[4] = {dfr[2 * kk][0], dfr[2 * kk][1], dfr[2 * kk + 1][0], dfr[2 * kk + 1][1]};
 #pragma unroll
-        for (int nc = 0; nc < 8; nc += 2) {
+        for (int nc = 0; nc < ND; nc += 2) {
           uint32_t b0, b1, b2, b3;
-          ldsm_x4_t(sK + tile_off(kk * 16 + (lane & 7) + ((lane >> 3) & 1) * 8, nc + (lane >> 4)), b0, b1, b2, b3);
+          ldsm_x4_t(sK + (nc >> 3) * kHalf + tile_off(kk * 16 + (lane & 7) + ((lane >> 3) & 1) * 8, (nc & 7) + (lane >> 4)), b0, b1, b2, b3);
           mma_bf16_16816(acc[nc], a, b0, b1);
           mma_bf16_16816(acc[nc + 1], a, b2, b3);
         }
       }
       stage_acc(acc, 1.f);
-      flush_rows(p.dq + seq * p.Tq * p.lddq + head * 64, p.lddq, mt * 16, p.Tq);
+      flush_rows(p.dq + seq * p.Tq * p.lddq + head * 64 * DH, p.lddq, mt * 16, p.Tq);
     }
     __syncwarp();
 
@@ -490,9 +506,9 @@ __global__ void __launch_bounds__(TemporalBwdCfg<MT>::kWarps * 32) attn_temporal
 #pragma unroll
     for (int kt = 0; kt < MT; ++kt) {
       if (kt * 16 >= p.Tk) break;
-      float av[8][4], ak[8][4];
+      float av[ND][4], ak[ND][4];
 #pragma unroll
-      for (int nt = 0; nt < 8; ++nt) {
+      for (int nt = 0; nt < ND; ++nt) {
         av[nt][0] = av[nt][1] = av[nt][2] = av[nt][3] = 0.f;
         ak[nt][0] = ak[nt][1] = ak[nt][2] = ak[nt][3] = 0.f;
       }
@@ -506,9 +522,9 @@ __global__ void __launch_bounds__(TemporalBwdCfg<MT>::kWarps * 32) attn_temporal
         ldsm_x4_t(sP + aoff, ap[0], ap[1], ap[2], ap[3]);
         ldsm_x4_t(sDS + aoff, ad[0], ad[1], ad[2], ad[3]);
 #pragma unroll
-        for (int nc = 0; nc < 8; nc += 2) {
+        for (int nc = 0; nc < ND; nc += 2) {
           uint32_t b0, b1, b2, b3;
-          const uint32_t boff = tile_off(qt * 16 + (lane & 7) + ((lane >> 3) & 1) * 8, nc + (lane >> 4));
+          const uint32_t boff = (nc >> 3) * kHalf + tile_off(qt * 16 + (lane & 7) + ((lane >> 3) & 1) * 8, (nc & 7) + (lane >> 4));
           ldsm_x4_t(sDO + boff, b0, b1, b2, b3);
           mma_bf16_16816(av[nc], ap, b0, b1);
           mma_bf16_16816(av[nc + 1], ap, b2, b3);
@@ -518,27 +534,27 @@ __global__ void __launch_bounds__(TemporalBwdCfg<MT>::kWarps * 32) attn_temporal
         }
       }
       stage_acc(av, 1.f);
-      flush_rows(p.dv + seq * p.Tk * p.lddv + head * 64, p.lddv, kt * 16, p.Tk);
+      flush_rows(p.dv + seq * p.Tk * p.lddv + head * 64 * DH, p.lddv, kt * 16, p.Tk);
       stage_acc(ak, 1.f);
-      flush_rows(p.dk + seq * p.Tk * p.lddk + head * 64, p.lddk, kt * 16, p.Tk);
+      flush_rows(p.dk + seq * p.Tk * p.lddk + head * 64 * DH, p.lddk, kt * 16, p.Tk);
     }
     __syncwarp();  // the tiles are refilled by the next item
   }
 }
 
-template <int MT>
+template <int MT, int DH>
 int launch_temporal_bwd(const TbParams& p, cudaStream_t st) {
-  using Cfg = TemporalBwdCfg<MT>;
+  using Cfg = TemporalBwdCfg<MT, DH>;
   static bool configured = false;
   if (!configured) {
-    TVI_CUDA_OK(cudaFuncSetAttribute(attn_temporal_bwd_kernel<MT>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes));
+    TVI_CUDA_OK(cudaFuncSetAttribute(attn_temporal_bwd_kernel<MT, DH>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes));
     configured = true;
   }
   const int per_sm = (227 * 1024) / (Cfg::kSmemBytes + 1024);
   int64_t grid = (p.nitems + Cfg::kWarps - 1) / Cfg::kWarps;
   const int64_t cap = (int64_t)num_sms() * (per_sm > 0 ? per_sm : 1) * 4;
   if (grid > cap) grid = cap;
-  attn_temporal_bwd_kernel<MT><<<(unsigned)grid, Cfg::kWarps * 32, Cfg::kSmemBytes, st>>>(p);
+  attn_temporal_bwd_kernel<MT, DH><<<(unsigned)grid, Cfg::kWarps * 32, Cfg::kSmemBytes, st>>>(p);
   TVI_LAUNCH_OK("attn_temporal_bwd_kernel");
   return TVI_OK;
 }
@@ -928,9 +944,9 @@ int tvi_attn_spatial_bwd_algo(const tvi_bf16* q, const tvi_bf16* k, const tvi_bf
   if (batch == 0 || heads == 0 || S == 0) return TVI_OK;
   TVI_CHECK_ARG(Skv >= 1, "tvi_attn_spatial_bwd: softmax over zero keys is undefined");
   TVI_CHECK_ARG(q && k && v && o && dout && lse && dq && dk && dv && workspace, "tvi_attn_spatial_bwd: null pointer");
-  if (d != 64) return fail(TVI_ERR_UNSUPPORTED, "tvi_attn_spatial_bwd: head dim %d (only 64 is built)", d);
+  if (d != 64 && d != 128) return fail(TVI_ERR_UNSUPPORTED, "tvi_attn_spatial_bwd: head dim %d (64 and 128 are built)", d);
   TVI_CHECK_ARG((ldq | ldk | ldv | ldo | lddo | lddq | lddk | lddv) % 8 == 0, "tvi_attn_spatial_bwd: row strides must be multiples of 8 elements");
-  const int64_t C = (int64_t)heads * 64;
+  const int64_t C = (int64_t)heads * d;
   TVI_CHECK_ARG(ldq >= C && ldk >= C && ldv >= C && ldo >= C && lddo >= C && lddq >= C && lddk >= C && lddv >= C,
                 "tvi_attn_spatial_bwd: row stride smaller than heads*d");
   TVI_CHECK_ARG(((uintptr_t)q | (uintptr_t)k | (uintptr_t)v | (uintptr_t)o | (uintptr_t)dout | (uintptr_t)dq | (uintptr_t)dk |
@@ -941,16 +957,20 @@ int tvi_attn_spatial_bwd_algo(const tvi_bf16* q, const tvi_bf16* k, const tvi_bf
   if (algo == TVI_SPATIAL_AUTO) {
     // a CTA of the tcgen05 passes owns 128 rows and streams the other side in steps of 128; short sequences (L2 / mid
     // level: 576, 144 tokens) stay on the mma.sync passes, like the forward
-    algo = (S >= 1024 && Skv >= 1024) ? TVI_SPATIAL_TCGEN05 : TVI_SPATIAL_MMA_SYNC;
+    // (and d = 128: the tcgen05 passes are built for 64-wide heads)
+    algo = (S >= 1024 && Skv >= 1024 && d == 64) ? TVI_SPATIAL_TCGEN05 : TVI_SPATIAL_MMA_SYNC;
   }
+  if (algo == TVI_SPATIAL_TCGEN05 && d != 64)
+    return fail(TVI_ERR_UNSUPPORTED, "tvi_attn_spatial_bwd: the tcgen05 passes are built for head dim 64 (got %d)", d);
   if (algo == TVI_SPATIAL_TCGEN05)
     return launch_spatial_bwd_tc(q, k, v, o, dout, lse, dq, dk, dv, workspace, batch, heads, S, Skv, ldq, ldk, ldv, ldo, lddo, lddq, lddk,
                                  lddv, scale, st);
   float* D = (float*)workspace;
   {
     const int64_t nrows = (int64_t)batch * S;
-    const int64_t threads = nrows * heads * 8;
-    attn_bwd_dot_kernel<<<(unsigned)((threads + 255) / 256), 256, 0, st>>>(o, dout, D, nrows, heads, ldo, lddo);
+    const int64_t threads = nrows * heads * (d / 8);
+    if (d == 64) attn_bwd_dot_kernel<1><<<(unsigned)((threads + 255) / 256), 256, 0, st>>>(o, dout, D, nrows, heads, ldo, lddo);
+    else attn_bwd_dot_kernel<2><<<(unsigned)((threads + 255) / 256), 256, 0, st>>>(o, dout, D, nrows, heads, ldo, lddo);
     TVI_LAUNCH_OK("attn_bwd_dot_kernel");
   }
   FbParams p;
@@ -963,14 +983,14 @@ int tvi_attn_spatial_bwd_algo(const tvi_bf16* q, const tvi_bf16* k, const tvi_bf
   p.c1 = q; p.ldc1 = ldq; p.c2 = dout; p.ldc2 = lddo;
   p.out1 = dk; p.ldo1 = lddk; p.out2 = dv; p.ldo2 = lddv;
   p.nrows = Skv; p.ncols = S;
-  int rc = launch_flash_bwd<true>(p, batch, st);
+  int rc = d == 64 ? launch_flash_bwd<true, 1>(p, batch, st) : launch_flash_bwd<true, 2>(p, batch, st);
   if (rc) return rc;
   // pass 2: rows = queries -> dQ
   p.r1 = q; p.ldr1 = ldq; p.r2 = dout; p.ldr2 = lddo;
   p.c1 = k; p.ldc1 = ldk; p.c2 = v; p.ldc2 = ldv;
   p.out1 = dq; p.ldo1 = lddq; p.out2 = nullptr; p.ldo2 = 0;
   p.nrows = S; p.ncols = Skv;
-  return launch_flash_bwd<false>(p, batch, st);
+  return d == 64 ? launch_flash_bwd<false, 1>(p, batch, st) : launch_flash_bwd<false, 2>(p, batch, st);
 }
 
 int tvi_attn_spatial_bwd(const tvi_bf16* q, const tvi_bf16* k, const tvi_bf16* v, const tvi_bf16* o, const tvi_bf16* dout,
@@ -988,10 +1008,10 @@ int tvi_attn_temporal_bwd(const tvi_bf16* q, const tvi_bf16* k, const tvi_bf16* 
   TVI_CHECK_ARG(nseq >= 0 && heads >= 0, "tvi_attn_temporal_bwd: negative size");
   if (nseq == 0 || heads == 0) return TVI_OK;
   TVI_CHECK_ARG(q && k && v && dout && dq && dk && dv, "tvi_attn_temporal_bwd: null pointer");
-  if (d != 64) return fail(TVI_ERR_UNSUPPORTED, "tvi_attn_temporal_bwd: head dim %d (only 64 is built)", d);
+  if (d != 64 && d != 128) return fail(TVI_ERR_UNSUPPORTED, "tvi_attn_temporal_bwd: head dim %d (64 and 128 are built)", d);
   TVI_CHECK_ARG(Tq >= 1 && Tq <= 64 && Tk >= 1 && Tk <= 64, "tvi_attn_temporal_bwd: Tq=%d Tk=%d outside [1,64]", Tq, Tk);
   TVI_CHECK_ARG((ldq | ldk | ldv | lddo | lddq | lddk | lddv) % 8 == 0, "tvi_attn_temporal_bwd: row strides must be multiples of 8 elements");
-  const int64_t C = (int64_t)heads * 64;
+  const int64_t C = (int64_t)heads * d;
   TVI_CHECK_ARG(ldq >= C && ldk >= C && ldv >= C && lddo >= C && lddq >= C && lddk >= C && lddv >= C,
                 "tvi_attn_temporal_bwd: row stride smaller than heads*d");
   TVI_CHECK_ARG(((uintptr_t)q | (uintptr_t)k | (uintptr_t)v | (uintptr_t)dout | (uintptr_t)dq | (uintptr_t)dk | (uintptr_t)dv) % 16 == 0,
@@ -1003,9 +1023,11 @@ int tvi_attn_temporal_bwd(const tvi_bf16* q, const tvi_bf16* k, const tvi_bf16* 
   p.heads = heads; p.Tq = Tq; p.Tk = Tk; p.scale = scale;
   const int T = Tq > Tk ? Tq : Tk;
   cudaStream_t st = (cudaStream_t)stream;
-  if (T <= 16) return launch_temporal_bwd<1>(p, st);
-  if (T <= 32) return launch_temporal_bwd<2>(p, st);
-  return launch_temporal_bwd<4>(p, st);
+#define TVI_TBWD(MT) (d == 64 ? launch_temporal_bwd<MT, 1>(p, st) : launch_temporal_bwd<MT, 2>(p, st))
+  if (T <= 16) return TVI_TBWD(1);
+  if (T <= 32) return TVI_TBWD(2);
+  return TVI_TBWD(4);
+#undef TVI_TBWD
 }
 
 size_t tvi_attn_fewkeys_bwd_workspace_bytes(int64_t nrows, int64_t rows_per_group, int heads, int L, int d) {
