@@ -140,6 +140,12 @@ size_t tvi_layernorm_bwd_workspace_bytes(int64_t M, int C);
 int tvi_layernorm_bwd_bf16(const tvi_bf16* x, const tvi_bf16* dy, const tvi_bf16* gamma, tvi_bf16* dx, tvi_bf16* dgamma,
                            tvi_bf16* dbeta, void* workspace, int64_t M, int C, int64_t ldx, int64_t lddy, int64_t lddx, float eps,
                            void* stream);
+/* The same with the gradient of a residual branch added in the same pass: for `y = x + f(LayerNorm(x))` (every sub-layer
+ * of the two blocks, src/models/attention.py:270-287, :300-317, :321-343) dx = LayerNorm'(dy_norm) + dres, where dres is
+ * the gradient that reached the `+ x` (nullable: then this is tvi_layernorm_bwd_bf16). */
+int tvi_layernorm_bwd_res_bf16(const tvi_bf16* x, const tvi_bf16* dy, const tvi_bf16* gamma, const tvi_bf16* dres, tvi_bf16* dx,
+                               tvi_bf16* dgamma, tvi_bf16* dbeta, void* workspace, int64_t M, int C, int64_t ldx, int64_t lddy,
+                               int64_t lddres, int64_t lddx, float eps, void* stream);
 int tvi_geglu_bwd_bf16(const tvi_bf16* pre, const tvi_bf16* dh, tvi_bf16* h, tvi_bf16* dpre, int64_t M, int inner, int64_t ldpre,
                        int64_t lddh, int64_t ldh, int64_t lddpre, void* stream);
 

@@ -60,6 +60,7 @@ SIGNATURES = {
     "tvi_farneback_clip_f32": (_i32, [_ptr, _ptr, _i64, _i32, _ptr, _ptr, _i32, _i32, _f64, _i32, _i32, _i32, _i32, _f64, _ptr]),
     "tvi_farneback_f32": (_i32, [_ptr, _ptr, _i32, _ptr, _ptr, _i32, _i32, _f64, _i32, _i32, _i32, _i32, _f64, _ptr]),
     "tvi_layernorm_bwd_workspace_bytes": (_sz, [_i64, _i32]),
+    "tvi_layernorm_bwd_res_bf16": (_i32, [_ptr, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr, _i64, _i32, _i64, _i64, _i64, _i64, _f32, _ptr]),
     "tvi_layernorm_bwd_bf16": (_i32, [_ptr, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr, _i64, _i32, _i64, _i64, _i64, _f32, _ptr]),
     "tvi_geglu_bwd_bf16": (_i32, [_ptr, _ptr, _ptr, _ptr, _i64, _i32, _i64, _i64, _i64, _i64, _ptr]),
     "tvi_gemm_bf16_dgrad": (_i32, [_ptr, _ptr, _ptr, _i64, _i32, _i32, _i64, _i64, _i64, _ptr]),

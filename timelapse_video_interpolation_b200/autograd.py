@@ -116,7 +116,10 @@ class _AttentionFn(torch.autograd.Function):
     `.item()`, src/train_decouples.py:460-471, :1027-1029)."""
 
     @staticmethod
-    def forward(ctx, x, e, wq, wk, wv, wo, bo, cfg):
+    def forward(ctx, x, e, wq, wk, wv, wo, bo, cfg, residual=None):
+        # `residual` (shape of the output): added in the out-projection epilogue (the blocks' `attn_output + hidden_states`);
+        # its gradient is dy itself
+        res2 = None if residual is None else residual.detach().contiguous().view(-1, residual.shape[-1])
         heads, scale = cfg["heads"], cfg["scale"]
         w_o, b_o = cfg["w_o"], cfg["b_o"]
         Bp, S, C = x.shape
@@ -131,7 +134,7 @@ class _AttentionFn(torch.autograd.Function):
             q, k, v = qkv[:, :inner], qkv[:, inner:2 * inner], qkv[:, 2 * inner:]
             lse = torch.empty(Bp * S, heads, dtype=torch.float32, device=x.device) if S > 64 else None
             o = _self_core(q, k, v, Bp, S, heads, scale, lse=lse)
-            y = ops.gemm_bf16_tn(o, w_o, b_o)
+            y = _out_proj(o, w_o, b_o, res2)
             ctx.mode = "self"
             ctx.save_for_backward(x2, qkv, o, lse, w_qkv, w_o)
             return y.view(Bp, S, y.shape[-1])
@@ -145,7 +148,10 @@ class _AttentionFn(torch.autograd.Function):
         bias, stats = cfg.get("bias"), cfg.get("stats")
         if L == 1 and stats is None:
             yv = ops.gemm_bf16_tn(v, w_o, b_o)
-            y = ops.attn_fewkeys(None, yv, yv, Bp * S, S, heads, 1, 1.0)
+            if res2 is not None:
+                y = ops.bcast_rows_add(yv, res2, S)
+            else:
+                y = ops.attn_fewkeys(None, yv, yv, Bp * S, S, heads, 1, 1.0)
             ctx.mode = "cross1"
             ctx.save_for_backward(e2, kv, w_kv, w_o)
             return y.view(Bp, S, y.shape[-1])
@@ -153,7 +159,7 @@ class _AttentionFn(torch.autograd.Function):
         q = ops.gemm_bf16_tn(x2, w_q)
         o = ops.attn_fewkeys(q, k, v, Bp * S, S, heads, L, scale, Tq=S if (bias is not None or stats is not None) else 1,
                              bias=bias, stats=stats)
-        y = ops.gemm_bf16_tn(o, w_o, b_o)
+        y = _out_proj(o, w_o, b_o, res2)
         ctx.mode = "cross"
         ctx.save_for_backward(x2, e2, q, kv, o, w_q, w_kv, w_o)
         return y.view(Bp, S, y.shape[-1])
@@ -164,7 +170,8 @@ class _AttentionFn(torch.autograd.Function):
         cfg = ctx.cfg
         heads, scale = cfg["heads"], cfg["scale"]
         Bp, S, C = ctx.shape
-        need_x, need_e, need_wq, need_wk, need_wv, need_wo, need_bo, _ = ctx.needs_input_grad
+        need_x, need_e, need_wq, need_wk, need_wv, need_wo, need_bo = ctx.needs_input_grad[:7]
+        need_res = len(ctx.needs_input_grad) > 8 and ctx.needs_input_grad[8]
         dt_wq, dt_wk, dt_wv, dt_wo, dt_bo = ctx.param_dtypes
         dy2 = dy.contiguous().view(Bp * S, dy.shape[-1])
         if dy2.dtype != torch.bfloat16:
@@ -213,8 +220,10 @@ class _AttentionFn(torch.autograd.Function):
                     de = ops.gemm_bf16_dgrad(dv, w_kv[inner:]).view(Bp, -1, e2.shape[1])
                 if need_wv:
                     dwv = ops.gemm_bf16_wgrad(dv, e2)
-            # softmax over one key is constant: nothing flows to the query path or to the key projection
-            if need_x:
+            # softmax over one key is constant: nothing flows to the query path or to the key projection.  Behind a fused
+            # LayerNorm + residual entry (cfg["dx_none_ok"]) "nothing" is None: that Function still runs (the residual's
+            # gradient reaches it) and passes dres through without touching a zero tensor of the activations' size
+            if need_x and not cfg.get("dx_none_ok"):
                 dx = torch.zeros(Bp, S, C, dtype=torch.bfloat16, device=dy.device)
             if need_wq:
                 dwq = torch.zeros(cfg["w_q"].shape, dtype=torch.bfloat16, device=dy.device)
@@ -246,7 +255,8 @@ class _AttentionFn(torch.autograd.Function):
             else:
                 dwk = ops.gemm_bf16_wgrad(dkv[:, :inner], e2) if need_wk else None
                 dwv = ops.gemm_bf16_wgrad(dkv[:, inner:], e2) if need_wv else None
-        return (dx, de, cast(dwq, dt_wq), cast(dwk, dt_wk), cast(dwv, dt_wv), cast(dwo, dt_wo), cast(dbo, dt_bo), None)
+        return (dx, de, cast(dwq, dt_wq), cast(dwk, dt_wk), cast(dwv, dt_wv), cast(dwo, dt_wo), cast(dbo, dt_bo), None,
+                dy if need_res else None)
 
 
 def attention_forward(proc, attn, x, e, heads: int, scale: float, wo, bo, bias, stats, residual=None, frames=None,
@@ -272,15 +282,21 @@ def attention_forward(proc, attn, x, e, heads: int, scale: float, wo, bo, bias, 
             return self_attention(x, proc._fused(attn, ("to_q", "to_k", "to_v")), w_o, b_o, heads, scale, residual, frames, ln)
         return cross_attention(x, e, proc._fused(attn, ("to_q",)), proc._fused(attn, ("to_k", "to_v")), w_o, b_o, heads,
                                scale, bias, stats, residual, frames, ln)
-    if pre_norm is not None:
-        from .feedforward import layer_norm
-        x = layer_norm(pre_norm, x)
     if frames is not None:
         raise NotImplementedError("frames= (temporal attention in the spatial token order) is inference-only: the backward "
                                   "kernels take the [B*S, T, C] layout")
-    if residual is not None:  # training: the fused residual epilogue has no backward; add it on the tape
-        return attention_forward(proc, attn, x, e, heads, scale, wo, bo, bias, stats) + residual
+    # training: the residual rides in the out-projection epilogue (its gradient is dy itself); when it is the LayerNorm's own
+    # input — the blocks' `x + attn(norm(x))` — the LayerNorm backward kernel adds that gradient to dx in the same pass
     cfg = {"heads": heads, "scale": scale, "w_o": w_o, "b_o": b_o}
+    if pre_norm is not None:
+        from .feedforward import layer_norm, layer_norm_residual
+        if residual is x:
+            x, residual = layer_norm_residual(pre_norm, x)
+            cfg["dx_none_ok"] = True
+        else:
+            x = layer_norm(pre_norm, x)
+    if residual is not None and residual.shape != x.shape[:-1] + (w_o.shape[0],):
+        raise _lib.TviError(_lib.TVI_ERR_INVALID, "residual must have the shape of the output")
     if e is None:
         cfg["w_qkv"] = proc._fused(attn, ("to_q", "to_k", "to_v"))
     else:
@@ -288,4 +304,4 @@ def attention_forward(proc, attn, x, e, heads: int, scale: float, wo, bo, bias, 
         cfg["w_kv"] = proc._fused(attn, ("to_k", "to_v"))
         cfg["bias"] = bias
         cfg["stats"] = stats
-    return _AttentionFn.apply(x, e, wq, wk, wv, wo, bo, cfg)
+    return _AttentionFn.apply(x, e, wq, wk, wv, wo, bo, cfg, residual)

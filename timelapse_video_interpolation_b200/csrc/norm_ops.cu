@@ -315,8 +315,8 @@ constexpr int kLnBwdRowsPerWarp = 8;
 template <int NCH>
 __global__ void __launch_bounds__(kLnBwdWarps * 32)
 layernorm_bwd_kernel(const tvi_bf16* __restrict__ x, const tvi_bf16* __restrict__ dy, const tvi_bf16* __restrict__ gamma,
-                     tvi_bf16* __restrict__ dx, float* __restrict__ partial, int64_t M, int C8, int64_t ldx, int64_t lddy,
-                     int64_t lddx, float eps) {
+                     const tvi_bf16* __restrict__ dres, tvi_bf16* __restrict__ dx, float* __restrict__ partial, int64_t M, int C8,
+                     int64_t ldx, int64_t lddy, int64_t lddres, int64_t lddx, float eps) {
   extern __shared__ float s_acc[];  // [warps][2][C]
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int C = C8 * 8;
@@ -424,6 +424,16 @@ layernorm_bwd_kernel(const tvi_bf16* __restrict__ x, const tvi_bf16* __restrict_
           float o[8];
 #pragma unroll
           for (int q = 0; q < 8; ++q) o[q] = rstd * (gv[i][q] - s1 - xv[i][q] * s2);
+          if (dres != nullptr) {  // the gradient of the residual branch `x + f(LN(x))`: dx = LN'(dy) + dres in one pass
+            const uint4 ur = __ldg(reinterpret_cast<const uint4*>(dres + row * lddres) + c);
+            const __nv_bfloat162* hr = reinterpret_cast<const __nv_bfloat162*>(&ur);
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+              const float2 t = __bfloat1622float2(hr[q]);
+              o[2 * q] += t.x;
+              o[2 * q + 1] += t.y;
+            }
+          }
           *(reinterpret_cast<uint4*>(dx + row * lddx) + c) =
               make_uint4(pack_bf16x2(o[0], o[1]), pack_bf16x2(o[2], o[3]), pack_bf16x2(o[4], o[5]), pack_bf16x2(o[6], o[7]));
         }
@@ -470,16 +480,16 @@ int64_t ln_bwd_blocks(int64_t M) {
 }
 
 template <int NCH>
-int launch_ln_bwd(const tvi_bf16* x, const tvi_bf16* dy, const tvi_bf16* gamma, tvi_bf16* dx, float* partial, int64_t M, int C8,
-                  int64_t ldx, int64_t lddy, int64_t lddx, float eps, cudaStream_t st) {
+int launch_ln_bwd(const tvi_bf16* x, const tvi_bf16* dy, const tvi_bf16* gamma, const tvi_bf16* dres, tvi_bf16* dx, float* partial,
+                  int64_t M, int C8, int64_t ldx, int64_t lddy, int64_t lddres, int64_t lddx, float eps, cudaStream_t st) {
   const size_t smem = (size_t)kLnBwdWarps * 2 * C8 * 8 * sizeof(float);
   static bool configured = false;
   if (!configured) {
     TVI_CUDA_OK(cudaFuncSetAttribute(layernorm_bwd_kernel<NCH>, cudaFuncAttributeMaxDynamicSharedMemorySize, 8 * 2 * 2048 * 4));
     configured = true;
   }
-  layernorm_bwd_kernel<NCH><<<(unsigned)ln_bwd_blocks(M), kLnBwdWarps * 32, smem, st>>>(x, dy, gamma, dx, partial, M, C8, ldx, lddy,
-                                                                                         lddx, eps);
+  layernorm_bwd_kernel<NCH><<<(unsigned)ln_bwd_blocks(M), kLnBwdWarps * 32, smem, st>>>(x, dy, gamma, dres, dx, partial, M, C8, ldx,
+                                                                                         lddy, lddres, lddx, eps);
   TVI_LAUNCH_OK("layernorm_bwd_kernel");
   return TVI_OK;
 }
@@ -497,7 +507,15 @@ extern "C" size_t tvi_layernorm_bwd_workspace_bytes(int64_t M, int C) {
 extern "C" int tvi_layernorm_bwd_bf16(const tvi_bf16* x, const tvi_bf16* dy, const tvi_bf16* gamma, tvi_bf16* dx, tvi_bf16* dgamma,
                                       tvi_bf16* dbeta, void* workspace, int64_t M, int C, int64_t ldx, int64_t lddy, int64_t lddx,
                                       float eps, void* stream) {
+  return tvi_layernorm_bwd_res_bf16(x, dy, gamma, nullptr, dx, dgamma, dbeta, workspace, M, C, ldx, lddy, 0, lddx, eps, stream);
+}
+
+extern "C" int tvi_layernorm_bwd_res_bf16(const tvi_bf16* x, const tvi_bf16* dy, const tvi_bf16* gamma, const tvi_bf16* dres,
+                                          tvi_bf16* dx, tvi_bf16* dgamma, tvi_bf16* dbeta, void* workspace, int64_t M, int C,
+                                          int64_t ldx, int64_t lddy, int64_t lddres, int64_t lddx, float eps, void* stream) {
   using namespace tvi;
+  TVI_CHECK_ARG(dres == nullptr || (dx != nullptr && lddres % 8 == 0 && lddres >= C && (uintptr_t)dres % 16 == 0),
+                "tvi_layernorm_bwd_bf16: dres needs dx, a row stride that is a multiple of 8 and 16-byte alignment");
   TVI_CHECK_ARG(M >= 0 && C >= 0, "tvi_layernorm_bwd_bf16: negative size");
   if (M == 0 || C == 0) return TVI_OK;
   TVI_CHECK_ARG(x && dy && workspace, "tvi_layernorm_bwd_bf16: null pointer");
@@ -512,13 +530,13 @@ extern "C" int tvi_layernorm_bwd_bf16(const tvi_bf16* x, const tvi_bf16* dy, con
   const int C8 = C / 8;
   int rc;
   if (C8 <= 64)
-    rc = launch_ln_bwd<2>(x, dy, gamma, dx, (float*)workspace, M, C8, ldx, lddy, lddx, eps, st);
+    rc = launch_ln_bwd<2>(x, dy, gamma, dres, dx, (float*)workspace, M, C8, ldx, lddy, lddres, lddx, eps, st);
   else if (C8 <= 128)
-    rc = launch_ln_bwd<4>(x, dy, gamma, dx, (float*)workspace, M, C8, ldx, lddy, lddx, eps, st);
+    rc = launch_ln_bwd<4>(x, dy, gamma, dres, dx, (float*)workspace, M, C8, ldx, lddy, lddres, lddx, eps, st);
   else if (C8 <= 160)
-    rc = launch_ln_bwd<5>(x, dy, gamma, dx, (float*)workspace, M, C8, ldx, lddy, lddx, eps, st);
+    rc = launch_ln_bwd<5>(x, dy, gamma, dres, dx, (float*)workspace, M, C8, ldx, lddy, lddres, lddx, eps, st);
   else
-    rc = launch_ln_bwd<8>(x, dy, gamma, dx, (float*)workspace, M, C8, ldx, lddy, lddx, eps, st);
+    rc = launch_ln_bwd<8>(x, dy, gamma, dres, dx, (float*)workspace, M, C8, ldx, lddy, lddres, lddx, eps, st);
   if (rc) return rc;
   if (dgamma != nullptr || dbeta != nullptr) {
     ln_bwd_final_kernel<<<(2 * C + 255) / 256, 256, 0, st>>>((const float*)workspace, dgamma, dbeta, (int)ln_bwd_blocks(M), C);

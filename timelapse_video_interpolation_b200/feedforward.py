@@ -73,7 +73,7 @@ class _FeedForwardFn(torch.autograd.Function):
     gets h and d(pre) from one elementwise kernel, and runs the dgrad / wgrad / column-sum kernels of the projections."""
 
     @staticmethod
-    def forward(ctx, x, w1, b1, w2, b2):
+    def forward(ctx, x, w1, b1, w2, b2, residual=None):
         x2 = x.detach().contiguous().view(x.numel() // max(x.shape[-1], 1), x.shape[-1])
         with torch.no_grad():
             w1b, w2b = _bf16(w1), _bf16(w2)
@@ -87,7 +87,10 @@ class _FeedForwardFn(torch.autograd.Function):
                 bb = _bf16(b1)
                 bi = torch.stack([bb[:inner].view(inner // H, H), bb[inner:].view(inner // H, H)], dim=1).reshape(-1).contiguous()
             h = ops.gemm_bf16_tn_ex(x2, wi.contiguous(), bi, geglu=True)
-            y = ops.gemm_bf16_tn(h, w2b, _bf16(b2))
+            if residual is None:
+                y = ops.gemm_bf16_tn(h, w2b, _bf16(b2))
+            else:  # `ff_output + hidden_states` in the second GEMM's epilogue; its gradient is dy itself
+                y = ops.gemm_bf16_tn_ex(h, w2b, _bf16(b2), residual=residual.detach().contiguous().view(x2.shape[0], -1))
         ctx.save_for_backward(x2, w1, b1, w2, b2)
         ctx.x_shape = x.shape
         return y.view(*x.shape[:-1], y.shape[-1])
@@ -95,7 +98,8 @@ class _FeedForwardFn(torch.autograd.Function):
     @staticmethod
     def backward(ctx, dy):
         x2, w1, b1, w2, b2 = ctx.saved_tensors
-        need_x, need_w1, need_b1, need_w2, need_b2 = ctx.needs_input_grad
+        need_x, need_w1, need_b1, need_w2, need_b2 = ctx.needs_input_grad[:5]
+        need_res = len(ctx.needs_input_grad) > 5 and ctx.needs_input_grad[5]
         dy2 = dy.contiguous().view(-1, dy.shape[-1]).to(torch.bfloat16)
         w1b, w2b = _bf16(w1), _bf16(w2)
         pre = ops.gemm_bf16_tn(x2, w1b, _bf16(b1))                       # [M, 2*inner] = [value | gate]
@@ -107,7 +111,7 @@ class _FeedForwardFn(torch.autograd.Function):
         db1 = ops.colsum_bf16(dpre, dpre.shape[0]).view(-1) if (need_b1 and b1 is not None) else None
         dx = ops.gemm_bf16_dgrad(dpre, w1b).view(ctx.x_shape) if need_x else None
         return dx, _cast_grad(dw1, w1), _cast_grad(db1, b1) if b1 is not None else None, _cast_grad(dw2, w2), \
-            _cast_grad(db2, b2) if b2 is not None else None
+            _cast_grad(db2, b2) if b2 is not None else None, (dy if need_res else None)
 
 
 class _LinearFn(torch.autograd.Function):
@@ -165,6 +169,46 @@ class _LayerNormFn(torch.autograd.Function):
             _cast_grad(dbeta, beta) if (need_b and beta is not None) else None, None
 
 
+class _LayerNormResFn(torch.autograd.Function):
+    """Entry of a residual branch `x + f(LayerNorm(x))` (every sub-layer of the two blocks): returns (LayerNorm(x), x).
+    The second output is what the caller adds back (in the epilogue of f's last GEMM); its gradient arrives here together
+    with the gradient of the normalised rows, and the LayerNorm backward kernel adds it to dx in the same pass
+    (`tvi_layernorm_bwd_res_bf16`) — autograd would otherwise sum the two with one more elementwise kernel per sub-layer."""
+
+    @staticmethod
+    def forward(ctx, x, gamma, beta, eps):
+        xc = x.detach().contiguous()
+        y = ops.layernorm_bf16(xc, _bf16(gamma), _bf16(beta), eps)
+        ctx.save_for_backward(xc, gamma, beta)
+        ctx.eps = eps
+        ctx.set_materialize_grads(False)
+        return y, x.view_as(x)
+
+    @staticmethod
+    def backward(ctx, dn, dres):
+        xc, gamma, beta = ctx.saved_tensors
+        need_x, need_g, need_b, _ = ctx.needs_input_grad
+        need_g, need_b = need_g and gamma is not None, need_b and beta is not None
+        if dres is not None:
+            dres = dres.contiguous().to(torch.bfloat16)
+        if dn is None:  # nothing flowed through f (a one-key cross-attention): the branch passes dres through
+            dg = torch.zeros_like(gamma) if need_g else None
+            db = torch.zeros_like(beta) if need_b else None
+            return (dres if need_x else None), dg, db, None
+        dx, dgamma, dbeta = ops.layernorm_bwd(xc, dn.contiguous().to(torch.bfloat16), _bf16(gamma), ctx.eps, need_dx=need_x,
+                                              need_affine=need_g or need_b, dres=dres if need_x else None)
+        return dx, _cast_grad(dgamma, gamma) if need_g else None, _cast_grad(dbeta, beta) if need_b else None, None
+
+
+def layer_norm_residual(norm, x: torch.Tensor):
+    """(norm(x), x) on the autograd tape for a residual branch (see _LayerNormResFn); training path only."""
+    if tuple(norm.normalized_shape) != (x.shape[-1],):
+        raise _lib.TviError(_lib.TVI_ERR_UNSUPPORTED, "layer_norm: only normalisation over the last dimension is built")
+    if x.dtype != torch.bfloat16 or not x.is_cuda:
+        raise _lib.TviError(_lib.TVI_ERR_UNSUPPORTED, "layer_norm: expected a CUDA bfloat16 tensor")
+    return _LayerNormResFn.apply(x, norm.weight, norm.bias, float(norm.eps))
+
+
 def feed_forward(ff, hidden_states: torch.Tensor, scale: float = 1.0, residual: Optional[torch.Tensor] = None,
                  pre_norm=None) -> torch.Tensor:
     """`ff(hidden_states)` of a FeedForward module with GEGLU activation; `residual` (same shape as the output)
@@ -188,12 +232,17 @@ def feed_forward(ff, hidden_states: torch.Tensor, scale: float = 1.0, residual: 
     if pre_norm is not None and torch.is_grad_enabled() and any(p.requires_grad for p in pre_norm.parameters()):
         on_tape = True
     if on_tape:
-        # training: the call goes on the autograd tape; the residual add has no fused backward and is added on the tape
-        if pre_norm is not None:
-            x = layer_norm(pre_norm, x)
+        # training: the call goes on the autograd tape.  The residual rides in the second GEMM's epilogue (its gradient is
+        # dy itself); when it is the LayerNorm's own input — the blocks' `x + ff(norm(x))` — its gradient is added inside the
+        # LayerNorm backward kernel
         proj, out_lin = ff.net[0].proj, ff.net[2]
-        y = _FeedForwardFn.apply(x, proj.weight, proj.bias, out_lin.weight, out_lin.bias)
-        return y if residual is None else y + residual
+        if pre_norm is not None and residual is x:
+            x, residual = layer_norm_residual(pre_norm, x)
+        elif pre_norm is not None:
+            x = layer_norm(pre_norm, x)
+        if residual is not None and residual.shape[-1] != out_lin.weight.shape[0]:
+            raise _lib.TviError(_lib.TVI_ERR_INVALID, "feed_forward: residual must have the shape of the output")
+        return _FeedForwardFn.apply(x, proj.weight, proj.bias, out_lin.weight, out_lin.bias, residual)
     x = x.contiguous()
     wi, bi = _geglu_weights(ff.net[0].proj)
     x2 = x.view(x.numel() // x.shape[-1], x.shape[-1])

@@ -346,22 +346,29 @@ def farneback(prev: torch.Tensor, nxt: torch.Tensor, pyr_scale: float = 0.5, lev
 
 
 def layernorm_bwd(x: torch.Tensor, dy: torch.Tensor, gamma: torch.Tensor | None, eps: float, need_dx: bool = True,
-                  need_affine: bool = True):
-    """Backward of layernorm_bf16: returns (dx or None, dgamma or None, dbeta or None), all bf16."""
-    _need_cuda(x, dy, gamma)
+                  need_affine: bool = True, dres: torch.Tensor | None = None):
+    """Backward of layernorm_bf16: returns (dx or None, dgamma or None, dbeta or None), all bf16.  `dres` (shape of x): the
+    gradient of a residual branch `x + f(LayerNorm(x))`, added to dx in the same pass."""
+    _need_cuda(x, dy, gamma, dres)
     x, ldx = _rows2d(x, "x")
     dy, lddy = _rows2d(dy, "dy")
     C = x.shape[-1]
     M = x.numel() // C if C else 0
+    lddres = 0
+    if dres is not None:
+        if not need_dx or dres.numel() != x.numel():
+            raise _lib.TviError(_lib.TVI_ERR_INVALID, "layernorm_bwd: dres needs need_dx and the shape of x")
+        dres, lddres = _rows2d(dres.reshape(x.shape), "dres")
     dx = torch.empty(x.shape, dtype=torch.bfloat16, device=x.device) if need_dx else None
     dgamma = torch.empty(C, dtype=torch.bfloat16, device=x.device) if need_affine else None
     dbeta = torch.empty(C, dtype=torch.bfloat16, device=x.device) if need_affine else None
     ws = _workspace(_lib.load().tvi_layernorm_bwd_workspace_bytes(M, C), x.device)
     lddx = _rows2d(dx, "dx")[1] if dx is not None else 0
-    _hooked("layernorm_bwd", 2 if need_affine else 1, _lib.load().tvi_layernorm_bwd_bf16, x.data_ptr(), dy.data_ptr(),
-            gamma.data_ptr() if gamma is not None else None, dx.data_ptr() if dx is not None else None,
-            dgamma.data_ptr() if dgamma is not None else None, dbeta.data_ptr() if dbeta is not None else None,
-            ws.data_ptr() if ws is not None else None, M, C, ldx, lddy, lddx, float(eps), _stream())
+    _hooked("layernorm_bwd", 2 if need_affine else 1, _lib.load().tvi_layernorm_bwd_res_bf16, x.data_ptr(), dy.data_ptr(),
+            gamma.data_ptr() if gamma is not None else None, dres.data_ptr() if dres is not None else None,
+            dx.data_ptr() if dx is not None else None, dgamma.data_ptr() if dgamma is not None else None,
+            dbeta.data_ptr() if dbeta is not None else None, ws.data_ptr() if ws is not None else None, M, C, ldx, lddy, lddres,
+            lddx, float(eps), _stream())
     return dx, dgamma, dbeta
 
 
