@@ -237,6 +237,10 @@ int tvi_gemm_bf16_wgrad(const tvi_bf16* dY, const tvi_bf16* X, tvi_bf16* dW, voi
 size_t tvi_colsum_bf16_workspace_bytes(int64_t nrows, int64_t rows_per_group, int C);
 int tvi_colsum_bf16(const tvi_bf16* x, tvi_bf16* out, void* workspace, int64_t nrows, int64_t rows_per_group, int C,
                     int64_t ldx, int64_t ldo, void* stream);
+/* The same over interleaved groups: logical row i of group (b, s), s < group_inner, is physical row
+ * (b * rows_per_group + i) * group_inner + s (backward of tvi_bcast_rows_add_bf16 with group_inner > 1). */
+int tvi_colsum_bf16_interleaved(const tvi_bf16* x, tvi_bf16* out, void* workspace, int64_t nrows, int64_t rows_per_group,
+                                int64_t group_inner, int C, int64_t ldx, int64_t ldo, void* stream);
 
 /* ---------------------------------------------------------------------------------------------
  * A3c  short-sequence (temporal) attention core: nseq independent sequences, every head,
@@ -356,6 +360,17 @@ int tvi_attn_fewkeys_bwd(const tvi_bf16* q, const tvi_bf16* k, const tvi_bf16* v
                          tvi_bf16* dk, tvi_bf16* dv, void* workspace, int64_t nrows, int64_t rows_per_group, int heads,
                          int L, int d, int64_t ldq, int64_t ldk, int64_t ldv, int64_t lddo, int64_t lddq, int64_t lddk,
                          int64_t lddv, float scale, int Tq, const float* bias, void* stream);
+/* The backward kernels over INTERLEAVED sequences / groups (the `[B*T, S, C]` token order read in place, as the
+ * `_interleaved` forwards): training through the temporal block without the permute copies of
+ * src/models/attention.py:436-438 / :474-476 and without their backward.  seq_inner / group_inner == 1 are the calls above. */
+int tvi_attn_temporal_bwd_interleaved(const tvi_bf16* q, const tvi_bf16* k, const tvi_bf16* v, const tvi_bf16* dout, tvi_bf16* dq,
+                                      tvi_bf16* dk, tvi_bf16* dv, int64_t nseq, int heads, int Tq, int Tk, int d, int64_t seq_inner,
+                                      int64_t ldq, int64_t ldk, int64_t ldv, int64_t lddo, int64_t lddq, int64_t lddk, int64_t lddv,
+                                      float scale, void* stream);
+int tvi_attn_fewkeys_bwd_interleaved(const tvi_bf16* q, const tvi_bf16* k, const tvi_bf16* v, const tvi_bf16* dout, tvi_bf16* dq,
+                                     tvi_bf16* dk, tvi_bf16* dv, void* workspace, int64_t nrows, int64_t rows_per_group, int heads,
+                                     int L, int d, int64_t group_inner, int64_t ldq, int64_t ldk, int64_t ldv, int64_t lddo,
+                                     int64_t lddq, int64_t lddk, int64_t lddv, float scale, int Tq, const float* bias, void* stream);
 
 #ifdef __cplusplus
 }

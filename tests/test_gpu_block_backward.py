@@ -150,6 +150,44 @@ def test_block_backward_matches_fp32_autograd(cuda, temporal):
         _close(n, ps[n].grad, P[n].grad)
 
 
+@pytest.mark.parametrize("L,ramp", [(1, False), (2, False), (2, True)])
+def test_temporal_block_trains_in_the_spatial_token_order(cuda, L, ramp):
+    # N2 in training: the temporal block stays in [B*T, S, C] in BOTH directions (interleaved temporal / few-keys backward cores,
+    # interleaved column sums) — same gradients as the reference's permute -> block -> permute (src/models/attention.py:436-438,
+    # :474-476).  dx is bit-identical (every kernel on its path works row by row); weight gradients sum the tokens in another order.
+    from timelapse_video_interpolation_b200 import TviAttnProcessor
+    B, T, S, C = 2, 14, 40, 320
+    blk = _init_block(TemporalBasicTransformerBlock(C, C, 5, 1024), 23, cuda)
+    if ramp:
+        blk.attn2.processor = TviAttnProcessor(ramp_bias=True)
+    blocks.install_blocks(blk)
+    g = torch.Generator().manual_seed(L)
+    x = torch.randn(B * T, S, C, generator=g).to(torch.bfloat16).to(cuda)
+    e = torch.randn(B * S, L, 1024, generator=g).to(torch.bfloat16).to(cuda)
+    wgt = torch.randn(B * T, S, C, generator=g).to(torch.bfloat16).to(cuda)
+
+    def run(fold):
+        for p in blk.parameters():
+            p.grad = None
+        xi, ei = x.clone().requires_grad_(True), e.clone().requires_grad_(True)
+        seen = []
+        ops.EVENT_HOOK = lambda name, start: seen.append(name) if start else None
+        try:
+            y = blk(xi, num_frames=T, encoder_hidden_states=ei, fold_layout=fold)
+            (y.float() * wgt.float()).sum().backward()
+        finally:
+            ops.EVENT_HOOK = None
+        return y.detach(), xi.grad, ei.grad, {n: p.grad.clone() for n, p in blk.named_parameters()}, seen
+
+    y0, dx0, de0, g0, _ = run(False)
+    y1, dx1, de1, g1, seen = run(True)
+    assert "attn_temporal_bwd" in seen and ("attn_fewkeys_bwd" in seen or L == 1)
+    assert torch.equal(y0, y1) and torch.equal(dx0, dx1)
+    _close("d encoder_hidden_states", de1, de0)
+    for n in g0:
+        _close(n, g1[n], g0[n])
+
+
 def test_frozen_spatial_block_under_no_grad_still_uses_the_fast_path(cuda):
     blk = _init_block(BasicTransformerBlock(320, 5, 1024), 9, cuda)
     blocks.install_blocks(blk)

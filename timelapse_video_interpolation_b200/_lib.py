@@ -68,6 +68,7 @@ SIGNATURES = {
     "tvi_gemm_bf16_wgrad": (_i32, [_ptr, _ptr, _ptr, _ptr, _i64, _i32, _i32, _i64, _i64, _i64, _ptr]),
     "tvi_colsum_bf16_workspace_bytes": (_sz, [_i64, _i64, _i32]),
     "tvi_colsum_bf16": (_i32, [_ptr, _ptr, _ptr, _i64, _i64, _i32, _i64, _i64, _ptr]),
+    "tvi_colsum_bf16_interleaved": (_i32, [_ptr, _ptr, _ptr, _i64, _i64, _i64, _i32, _i64, _i64, _ptr]),
     "tvi_attn_temporal_fwd": (_i32, [_ptr, _ptr, _ptr, _ptr, _ptr, _i64, _i32, _i32, _i32, _i32,
                                      _i64, _i64, _i64, _i64, _f32, _ptr]),
     "tvi_attn_temporal_fwd_interleaved": (_i32, [_ptr, _ptr, _ptr, _ptr, _ptr, _i64, _i32, _i32, _i32, _i32, _i64,
@@ -86,8 +87,10 @@ SIGNATURES = {
     "tvi_attn_spatial_bwd": (_i32, [_ptr] * 10 + [_i32] * 5 + [_i64] * 8 + [_f32, _ptr]),
     "tvi_attn_spatial_bwd_algo": (_i32, [_ptr] * 10 + [_i32] * 5 + [_i64] * 8 + [_f32, _i32, _ptr]),
     "tvi_attn_temporal_bwd": (_i32, [_ptr] * 7 + [_i64, _i32, _i32, _i32, _i32] + [_i64] * 7 + [_f32, _ptr]),
+    "tvi_attn_temporal_bwd_interleaved": (_i32, [_ptr] * 7 + [_i64, _i32, _i32, _i32, _i32] + [_i64] * 8 + [_f32, _ptr]),
     "tvi_attn_fewkeys_bwd_workspace_bytes": (_sz, [_i64, _i64, _i32, _i32, _i32]),
     "tvi_attn_fewkeys_bwd": (_i32, [_ptr] * 8 + [_i64, _i64, _i32, _i32, _i32] + [_i64] * 7 + [_f32, _i32, _ptr, _ptr]),
+    "tvi_attn_fewkeys_bwd_interleaved": (_i32, [_ptr] * 8 + [_i64, _i64, _i32, _i32, _i32] + [_i64] * 8 + [_f32, _i32, _ptr, _ptr]),
 }
 SPATIAL_AUTO, SPATIAL_MMA_SYNC, SPATIAL_TCGEN05 = 0, 1, 2
 EPILOGUE_NONE, EPILOGUE_GEGLU = 0, 1

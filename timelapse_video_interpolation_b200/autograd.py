@@ -123,6 +123,9 @@ class _AttentionFn(torch.autograd.Function):
         heads, scale = cfg["heads"], cfg["scale"]
         w_o, b_o = cfg["w_o"], cfg["b_o"]
         Bp, S, C = x.shape
+        # frames = T: x is [B*T, S, C] in the SPATIAL token order and attention runs over the T tokens of every (b, s) (the
+        # temporal block without its permute copies, forward and backward): the cores address the interleaved sequences
+        frames = cfg.get("frames")
         ctx.cfg = cfg
         ctx.shape = (Bp, S, C)
         ctx.param_dtypes = tuple(None if t is None else t.dtype for t in (wq, wk, wv, wo, bo))
@@ -132,24 +135,34 @@ class _AttentionFn(torch.autograd.Function):
             x2 = x.view(Bp * S, C)
             qkv = ops.gemm_bf16_tn(x2, w_qkv)
             q, k, v = qkv[:, :inner], qkv[:, inner:2 * inner], qkv[:, 2 * inner:]
-            lse = torch.empty(Bp * S, heads, dtype=torch.float32, device=x.device) if S > 64 else None
-            o = _self_core(q, k, v, Bp, S, heads, scale, lse=lse)
+            lse = None
+            if frames is not None:
+                o = ops.attn_temporal(q, k, v, Bp // frames * S, heads, frames, frames, scale, seq_inner=S)
+            else:
+                lse = torch.empty(Bp * S, heads, dtype=torch.float32, device=x.device) if S > 64 else None
+                o = _self_core(q, k, v, Bp, S, heads, scale, lse=lse)
             y = _out_proj(o, w_o, b_o, res2)
             ctx.mode = "self"
             ctx.save_for_backward(x2, qkv, o, lse, w_qkv, w_o)
             return y.view(Bp, S, y.shape[-1])
-        _check_context(x, e)
+        if frames is None:
+            _check_context(x, e)
+        elif e.shape[0] != Bp // frames * S or e.shape[1] > 8:
+            raise _lib.TviError(_lib.TVI_ERR_INVALID, "encoder_hidden_states must be [B*S, L <= 8, C] with frames=")
         L = e.shape[1]
+        ctx.e_shape = tuple(e.shape)
+        # rows per context group and how the groups are laid out: contiguous [group, S] or interleaved [B, T, S]
+        rpg, ginner = (S, 1) if frames is None else (frames, S)
         w_q, w_kv = cfg["w_q"], cfg["w_kv"]
         inner = w_kv.shape[0] // 2
-        e2 = e.view(Bp * L, e.shape[2])
+        e2 = e.reshape(-1, e.shape[2])
         kv = ops.gemm_bf16_tn(e2, w_kv)
         k, v = kv[:, :inner], kv[:, inner:]
         bias, stats = cfg.get("bias"), cfg.get("stats")
         if L == 1 and stats is None:
             yv = ops.gemm_bf16_tn(v, w_o, b_o)
-            if res2 is not None:
-                y = ops.bcast_rows_add(yv, res2, S)
+            if res2 is not None or frames is not None:
+                y = ops.bcast_rows_add(yv, res2, rpg, group_inner=ginner, nrows=Bp * S)
             else:
                 y = ops.attn_fewkeys(None, yv, yv, Bp * S, S, heads, 1, 1.0)
             ctx.mode = "cross1"
@@ -157,8 +170,8 @@ class _AttentionFn(torch.autograd.Function):
             return y.view(Bp, S, y.shape[-1])
         x2 = x.view(Bp * S, C)
         q = ops.gemm_bf16_tn(x2, w_q)
-        o = ops.attn_fewkeys(q, k, v, Bp * S, S, heads, L, scale, Tq=S if (bias is not None or stats is not None) else 1,
-                             bias=bias, stats=stats)
+        o = ops.attn_fewkeys(q, k, v, Bp * S, rpg, heads, L, scale, Tq=rpg if (bias is not None or stats is not None) else 1,
+                             bias=bias, stats=stats, group_inner=ginner)
         y = _out_proj(o, w_o, b_o, res2)
         ctx.mode = "cross"
         ctx.save_for_backward(x2, e2, q, kv, o, w_q, w_kv, w_o)
@@ -192,7 +205,10 @@ class _AttentionFn(torch.autograd.Function):
             q, k, v = qkv[:, :inner], qkv[:, inner:2 * inner], qkv[:, 2 * inner:]
             dqkv = torch.empty_like(qkv)  # dq | dk | dv written in place as column slices
             dq, dk, dv = dqkv[:, :inner], dqkv[:, inner:2 * inner], dqkv[:, 2 * inner:]
-            if S <= 64:
+            frames = cfg.get("frames")
+            if frames is not None:
+                ops.attn_temporal_bwd(q, k, v, do, Bp // frames * S, heads, frames, frames, scale, dq=dq, dk=dk, dv=dv, seq_inner=S)
+            elif S <= 64:
                 ops.attn_temporal_bwd(q, k, v, do, Bp, heads, S, S, scale, dq=dq, dk=dk, dv=dv)
             else:
                 ops.attn_spatial_bwd(q, k, v, o, do, lse, Bp, heads, S, S, scale, dq=dq, dk=dk, dv=dv)
@@ -209,7 +225,9 @@ class _AttentionFn(torch.autograd.Function):
             e2, kv, w_kv, w_o = ctx.saved_tensors
             inner = w_kv.shape[0] // 2
             v = kv[:, inner:]
-            dyv = ops.colsum_bf16(dy2, S)  # [B', C]: every query row of a group received the same row
+            frames = cfg.get("frames")
+            # [groups, C]: every query row of a group received the same row
+            dyv = ops.colsum_bf16(dy2, S) if frames is None else ops.colsum_bf16(dy2, frames, group_inner=S)
             if need_wo:
                 dwo = ops.gemm_bf16_wgrad(dyv, v)
             if need_bo:
@@ -217,7 +235,7 @@ class _AttentionFn(torch.autograd.Function):
             if need_e or need_wv:
                 dv = ops.gemm_bf16_dgrad(dyv, w_o)
                 if need_e:
-                    de = ops.gemm_bf16_dgrad(dv, w_kv[inner:]).view(Bp, -1, e2.shape[1])
+                    de = ops.gemm_bf16_dgrad(dv, w_kv[inner:]).view(ctx.e_shape)
                 if need_wv:
                     dwv = ops.gemm_bf16_wgrad(dv, e2)
             # softmax over one key is constant: nothing flows to the query path or to the key projection.  Behind a fused
@@ -232,7 +250,9 @@ class _AttentionFn(torch.autograd.Function):
         else:
             x2, e2, q, kv, o, w_q, w_kv, w_o = ctx.saved_tensors
             inner = w_kv.shape[0] // 2
-            L = e2.shape[0] // Bp
+            L = ctx.e_shape[1]
+            frames = cfg.get("frames")
+            rpg, ginner = (S, 1) if frames is None else (frames, S)
             k, v = kv[:, :inner], kv[:, inner:]
             if need_wo:
                 dwo = ops.gemm_bf16_wgrad(dy2, o)
@@ -241,14 +261,14 @@ class _AttentionFn(torch.autograd.Function):
             do = ops.gemm_bf16_dgrad(dy2, w_o)
             bias = cfg.get("bias")
             dkv = torch.empty_like(kv)
-            dq, _, _ = ops.attn_fewkeys_bwd(q, k, v, do, Bp * S, S, heads, L, scale, Tq=S if bias is not None else 1, bias=bias,
-                                            dk=dkv[:, :inner], dv=dkv[:, inner:])
+            dq, _, _ = ops.attn_fewkeys_bwd(q, k, v, do, Bp * S, rpg, heads, L, scale, Tq=rpg if bias is not None else 1, bias=bias,
+                                            dk=dkv[:, :inner], dv=dkv[:, inner:], group_inner=ginner)
             if need_x:
                 dx = ops.gemm_bf16_dgrad(dq, w_q).view(Bp, S, C)
             if need_wq:
                 dwq = ops.gemm_bf16_wgrad(dq, x2)
             if need_e:
-                de = ops.gemm_bf16_dgrad(dkv, w_kv).view(Bp, L, e2.shape[1])
+                de = ops.gemm_bf16_dgrad(dkv, w_kv).view(ctx.e_shape)
             if need_wk and need_wv:
                 dw = ops.gemm_bf16_wgrad(dkv, e2)
                 dwk, dwv = dw[:inner], dw[inner:]
@@ -282,12 +302,9 @@ def attention_forward(proc, attn, x, e, heads: int, scale: float, wo, bo, bias, 
             return self_attention(x, proc._fused(attn, ("to_q", "to_k", "to_v")), w_o, b_o, heads, scale, residual, frames, ln)
         return cross_attention(x, e, proc._fused(attn, ("to_q",)), proc._fused(attn, ("to_k", "to_v")), w_o, b_o, heads,
                                scale, bias, stats, residual, frames, ln)
-    if frames is not None:
-        raise NotImplementedError("frames= (temporal attention in the spatial token order) is inference-only: the backward "
-                                  "kernels take the [B*S, T, C] layout")
     # training: the residual rides in the out-projection epilogue (its gradient is dy itself); when it is the LayerNorm's own
     # input — the blocks' `x + attn(norm(x))` — the LayerNorm backward kernel adds that gradient to dx in the same pass
-    cfg = {"heads": heads, "scale": scale, "w_o": w_o, "b_o": b_o}
+    cfg = {"heads": heads, "scale": scale, "w_o": w_o, "b_o": b_o, "frames": frames}
     if pre_norm is not None:
         from .feedforward import layer_norm, layer_norm_residual
         if residual is x:

@@ -17,8 +17,8 @@ row stride of S (`tvi_attn_temporal_fwd_interleaved`, `tvi_bcast_rows_add_bf16(g
 `install_blocks(model)` re-binds `forward` on every module with the block's attribute layout (duck-typed) and installs
 the attention processor on its Attention modules.  Training (config 5) works through the same forwards: when a gradient is
 required LayerNorm, attention and FeedForward go on the autograd tape through their libtvi Functions (forward and backward
-kernels), the residual adds and the temporal re-layout are torch ops on the tape (the fused-residual / folded-layout
-fast paths are inference-only).
+kernels): the residual adds ride in the GEMM epilogues and their gradients in the LayerNorm backward, and the temporal
+block stays in the spatial token order in both directions (interleaved forward AND backward cores).
 """
 from __future__ import annotations
 
@@ -108,7 +108,7 @@ def temporal_basic_transformer_block_forward(block, hidden_states: torch.Tensor,
     BF, S, C = hidden_states.shape
     B = BF // num_frames
     attn2 = getattr(block, "attn2", None)
-    in_place = fold_layout and not _training(block, hidden_states) and num_frames <= 64 and (
+    in_place = fold_layout and num_frames <= 64 and (
         attn2 is None or encoder_hidden_states is None or encoder_hidden_states.shape[1] <= 8)
     if in_place:
         # every op but the attention cores is row-wise: stay in the [B*T, S, C] token order, no permute copies

@@ -329,6 +329,7 @@ struct TbParams {
   int64_t nitems;
   int heads, Tq, Tk;
   float scale;
+  int64_t inner;  // > 1: interleaved sequences — token t of sequence s is row (s / inner) * inner * T + t * inner + s % inner
 };
 
 template <int MT, int DH>
@@ -378,10 +379,14 @@ __global__ void __launch_bounds__(TemporalBwdCfg<MT, DH>::kWarps * 32) attn_temp
   for (int64_t item = (int64_t)blockIdx.x * Cfg::kWarps + warp; item < p.nitems; item += (int64_t)gridDim.x * Cfg::kWarps) {
     const int64_t seq = item / p.heads;
     const int head = (int)(item - seq * p.heads);
-    const tvi_bf16* qb = p.q + seq * p.Tq * p.ldq + head * 64 * DH;
-    const tvi_bf16* kb = p.k + seq * p.Tk * p.ldk + head * 64 * DH;
-    const tvi_bf16* vb = p.v + seq * p.Tk * p.ldv + head * 64 * DH;
-    const tvi_bf16* dob = p.dout + seq * p.Tq * p.lddo + head * 64 * DH;
+    // first row of the sequence and the row stride between its tokens (as the forward kernel, attn_short.cu)
+    const int64_t so = seq / p.inner, si = seq - so * p.inner;
+    const int64_t q0 = so * p.inner * p.Tq + si, k0 = so * p.inner * p.Tk + si;
+    const int64_t ldq = p.ldq * p.inner, ldk = p.ldk * p.inner, ldv = p.ldv * p.inner, lddo = p.lddo * p.inner;
+    const tvi_bf16* qb = p.q + q0 * p.ldq + head * 64 * DH;
+    const tvi_bf16* kb = p.k + k0 * p.ldk + head * 64 * DH;
+    const tvi_bf16* vb = p.v + k0 * p.ldv + head * 64 * DH;
+    const tvi_bf16* dob = p.dout + q0 * p.lddo + head * 64 * DH;
     {
 #pragma unroll
       for (int i = 0; i < kRows * DH / 4; ++i) {
@@ -389,10 +394,10 @@ __global__ void __launch_bounds__(TemporalBwdCfg<MT, DH>::kWarps * 32) attn_temp
         const int r = idx / ND, c = idx % ND;
         const uint32_t off = (c >> 3) * kHalf + tile_off(r, c & 7);
         const bool pq = r < p.Tq, pk = r < p.Tk;
-        cp_async_16(wptr + off, pq ? qb + r * p.ldq + c * 8 : qb, pq);
-        cp_async_16(wptr + Cfg::kTileBytes + off, pk ? kb + r * p.ldk + c * 8 : kb, pk);
-        cp_async_16(wptr + 2 * Cfg::kTileBytes + off, pk ? vb + r * p.ldv + c * 8 : vb, pk);
-        cp_async_16(wptr + 3 * Cfg::kTileBytes + off, pq ? dob + r * p.lddo + c * 8 : dob, pq);
+        cp_async_16(wptr + off, pq ? qb + r * ldq + c * 8 : qb, pq);
+        cp_async_16(wptr + Cfg::kTileBytes + off, pk ? kb + r * ldk + c * 8 : kb, pk);
+        cp_async_16(wptr + 2 * Cfg::kTileBytes + off, pk ? vb + r * ldv + c * 8 : vb, pk);
+        cp_async_16(wptr + 3 * Cfg::kTileBytes + off, pq ? dob + r * lddo + c * 8 : dob, pq);
       }
       cp_async_commit();
       cp_async_wait<0>();
@@ -498,7 +503,7 @@ __global__ void __launch_bounds__(TemporalBwdCfg<MT, DH>::kWarps * 32) attn_temp
         }
       }
       stage_acc(acc, 1.f);
-      flush_rows(p.dq + seq * p.Tq * p.lddq + head * 64 * DH, p.lddq, mt * 16, p.Tq);
+      flush_rows(p.dq + q0 * p.lddq + head * 64 * DH, p.lddq * p.inner, mt * 16, p.Tq);
     }
     __syncwarp();
 
@@ -534,9 +539,9 @@ __global__ void __launch_bounds__(TemporalBwdCfg<MT, DH>::kWarps * 32) attn_temp
         }
       }
       stage_acc(av, 1.f);
-      flush_rows(p.dv + seq * p.Tk * p.lddv + head * 64 * DH, p.lddv, kt * 16, p.Tk);
+      flush_rows(p.dv + k0 * p.lddv + head * 64 * DH, p.lddv * p.inner, kt * 16, p.Tk);
       stage_acc(ak, 1.f);
-      flush_rows(p.dk + seq * p.Tk * p.lddk + head * 64 * DH, p.lddk, kt * 16, p.Tk);
+      flush_rows(p.dk + k0 * p.lddk + head * 64 * DH, p.lddk * p.inner, kt * 16, p.Tk);
     }
     __syncwarp();  // the tiles are refilled by the next item
   }
@@ -583,6 +588,7 @@ struct FkParams {
   int tiles_per_group, L, Tq;
   float scale;
   const float* bias;
+  int64_t inner;  // > 1: interleaved groups (logical row i of group (b, s) is physical row (b * rows_per_group + i) * inner + s)
 };
 
 template <int LT, int LPH>
@@ -599,6 +605,9 @@ __global__ void __launch_bounds__(256) attn_fewkeys_bwd_kernel(const FkParams p)
   const int64_t gend = (group + 1) * p.rows_per_group;
   if (rhi > gend) rhi = gend;
   const int L = p.L;
+  const int64_t gbase = group * p.rows_per_group;
+  const int64_t pbase = (group / p.inner) * p.rows_per_group * p.inner + group % p.inner;
+  auto phys = [&](int64_t r) -> int64_t { return p.inner == 1 ? r : pbase + (r - gbase) * p.inner; };
 
   float kf[LT][8], vf[LT][8], dk[LT][8], dv[LT][8];
 #pragma unroll
@@ -640,8 +649,8 @@ __global__ void __launch_bounds__(256) attn_fewkeys_bwd_kernel(const FkParams p)
       for (int u = 0; u < kU; ++u) {
         const int64_t rr = rlo + (int64_t)(it0 + u) * RY + ry;
         const int64_t r = rr < rhi ? rr : rlo;
-        qv[u] = __ldg(reinterpret_cast<const uint4*>(p.q + r * p.ldq + cx * 8));
-        gv[u] = __ldg(reinterpret_cast<const uint4*>(p.dout + r * p.lddo + cx * 8));
+        qv[u] = __ldg(reinterpret_cast<const uint4*>(p.q + phys(r) * p.ldq + cx * 8));
+        gv[u] = __ldg(reinterpret_cast<const uint4*>(p.dout + phys(r) * p.lddo + cx * 8));
       }
     };
     auto compute_group = [&](int it0, const uint4* qv, const uint4* gv) {
@@ -694,7 +703,7 @@ __global__ void __launch_bounds__(256) attn_fewkeys_bwd_kernel(const FkParams p)
             f32x2_unpack(f32x2_mul(ds2, kd2[i]), a, b);
             o[i] = pack_bf16x2(a, b);
           }
-          *reinterpret_cast<uint4*>(p.dq + r * p.lddq + cx * 8) = make_uint4(o[0], o[1], o[2], o[3]);
+          *reinterpret_cast<uint4*>(p.dq + phys(r) * p.lddq + cx * 8) = make_uint4(o[0], o[1], o[2], o[3]);
         }
       }
     };
@@ -728,8 +737,8 @@ __global__ void __launch_bounds__(256) attn_fewkeys_bwd_kernel(const FkParams p)
     for (int u = 0; u < kUnroll; ++u) {
       const int64_t rr = rlo + (int64_t)(it0 + u) * RY + ry;
       const int64_t r = rr < rhi ? rr : rlo;
-      qv[u] = p.q != nullptr ? __ldg(reinterpret_cast<const uint4*>(p.q + r * p.ldq + cx * 8)) : make_uint4(0, 0, 0, 0);
-      gv[u] = __ldg(reinterpret_cast<const uint4*>(p.dout + r * p.lddo + cx * 8));
+      qv[u] = p.q != nullptr ? __ldg(reinterpret_cast<const uint4*>(p.q + phys(r) * p.ldq + cx * 8)) : make_uint4(0, 0, 0, 0);
+      gv[u] = __ldg(reinterpret_cast<const uint4*>(p.dout + phys(r) * p.lddo + cx * 8));
     }
 #pragma unroll
     for (int u = 0; u < kUnroll; ++u) {
@@ -802,7 +811,7 @@ __global__ void __launch_bounds__(256) attn_fewkeys_bwd_kernel(const FkParams p)
       o.y = pack_bf16x2(dqf[2], dqf[3]);
       o.z = pack_bf16x2(dqf[4], dqf[5]);
       o.w = pack_bf16x2(dqf[6], dqf[7]);
-      *reinterpret_cast<uint4*>(p.dq + r * p.lddq + cx * 8) = o;
+      *reinterpret_cast<uint4*>(p.dq + phys(r) * p.lddq + cx * 8) = o;
     }
     }
   }
@@ -1004,7 +1013,16 @@ int tvi_attn_spatial_bwd(const tvi_bf16* q, const tvi_bf16* k, const tvi_bf16* v
 int tvi_attn_temporal_bwd(const tvi_bf16* q, const tvi_bf16* k, const tvi_bf16* v, const tvi_bf16* dout, tvi_bf16* dq,
                           tvi_bf16* dk, tvi_bf16* dv, int64_t nseq, int heads, int Tq, int Tk, int d, int64_t ldq, int64_t ldk,
                           int64_t ldv, int64_t lddo, int64_t lddq, int64_t lddk, int64_t lddv, float scale, void* stream) {
+  return tvi_attn_temporal_bwd_interleaved(q, k, v, dout, dq, dk, dv, nseq, heads, Tq, Tk, d, 1, ldq, ldk, ldv, lddo, lddq, lddk, lddv,
+                                           scale, stream);
+}
+
+int tvi_attn_temporal_bwd_interleaved(const tvi_bf16* q, const tvi_bf16* k, const tvi_bf16* v, const tvi_bf16* dout, tvi_bf16* dq,
+                                      tvi_bf16* dk, tvi_bf16* dv, int64_t nseq, int heads, int Tq, int Tk, int d, int64_t seq_inner,
+                                      int64_t ldq, int64_t ldk, int64_t ldv, int64_t lddo, int64_t lddq, int64_t lddk, int64_t lddv,
+                                      float scale, void* stream) {
   using namespace tvi;
+  TVI_CHECK_ARG(seq_inner >= 1 && (nseq == 0 || nseq % seq_inner == 0), "tvi_attn_temporal_bwd: nseq must be a multiple of seq_inner");
   TVI_CHECK_ARG(nseq >= 0 && heads >= 0, "tvi_attn_temporal_bwd: negative size");
   if (nseq == 0 || heads == 0) return TVI_OK;
   TVI_CHECK_ARG(q && k && v && dout && dq && dk && dv, "tvi_attn_temporal_bwd: null pointer");
@@ -1021,6 +1039,7 @@ int tvi_attn_temporal_bwd(const tvi_bf16* q, const tvi_bf16* k, const tvi_bf16* 
   p.ldq = ldq; p.ldk = ldk; p.ldv = ldv; p.lddo = lddo; p.lddq = lddq; p.lddk = lddk; p.lddv = lddv;
   p.nitems = nseq * heads;
   p.heads = heads; p.Tq = Tq; p.Tk = Tk; p.scale = scale;
+  p.inner = seq_inner;
   const int T = Tq > Tk ? Tq : Tk;
   cudaStream_t st = (cudaStream_t)stream;
 #define TVI_TBWD(MT) (d == 64 ? launch_temporal_bwd<MT, 1>(p, st) : launch_temporal_bwd<MT, 2>(p, st))
@@ -1042,6 +1061,14 @@ int tvi_attn_fewkeys_bwd(const tvi_bf16* q, const tvi_bf16* k, const tvi_bf16* v
                          tvi_bf16* dk, tvi_bf16* dv, void* workspace, int64_t nrows, int64_t rows_per_group, int heads, int L,
                          int d, int64_t ldq, int64_t ldk, int64_t ldv, int64_t lddo, int64_t lddq, int64_t lddk,
                          int64_t lddv, float scale, int Tq, const float* bias, void* stream) {
+  return tvi_attn_fewkeys_bwd_interleaved(q, k, v, dout, dq, dk, dv, workspace, nrows, rows_per_group, heads, L, d, 1, ldq, ldk, ldv,
+                                          lddo, lddq, lddk, lddv, scale, Tq, bias, stream);
+}
+
+int tvi_attn_fewkeys_bwd_interleaved(const tvi_bf16* q, const tvi_bf16* k, const tvi_bf16* v, const tvi_bf16* dout, tvi_bf16* dq,
+                                     tvi_bf16* dk, tvi_bf16* dv, void* workspace, int64_t nrows, int64_t rows_per_group, int heads,
+                                     int L, int d, int64_t group_inner, int64_t ldq, int64_t ldk, int64_t ldv, int64_t lddo,
+                                     int64_t lddq, int64_t lddk, int64_t lddv, float scale, int Tq, const float* bias, void* stream) {
   using namespace tvi;
   TVI_CHECK_ARG(nrows >= 0 && heads >= 0, "tvi_attn_fewkeys_bwd: negative size");
   if (nrows == 0 || heads == 0) return TVI_OK;
@@ -1058,7 +1085,9 @@ int tvi_attn_fewkeys_bwd(const tvi_bf16* q, const tvi_bf16* k, const tvi_bf16* v
   TVI_CHECK_ARG(((uintptr_t)q | (uintptr_t)k | (uintptr_t)v | (uintptr_t)dout | (uintptr_t)dq | (uintptr_t)dk | (uintptr_t)dv) % 16 == 0,
                 "tvi_attn_fewkeys_bwd: pointers must be 16-byte aligned");
   const int64_t ngroups = nrows / rows_per_group;
+  TVI_CHECK_ARG(group_inner >= 1 && ngroups % group_inner == 0, "tvi_attn_fewkeys_bwd: the group count must be a multiple of group_inner");
   FkParams p;
+  p.inner = group_inner;
   p.q = q; p.k = k; p.v = v; p.dout = dout; p.dq = dq; p.dk = dk; p.dv = dv;
   p.partial = (float*)workspace;
   p.ldq = ldq; p.ldk = ldk; p.ldv = ldv; p.lddo = lddo; p.lddq = lddq; p.lddk = lddk; p.lddv = lddv;

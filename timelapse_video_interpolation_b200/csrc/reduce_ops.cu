@@ -16,7 +16,7 @@ constexpr int kCsTy = 8;
 
 __global__ void __launch_bounds__(32 * kCsTy)
 colsum_kernel(const tvi_bf16* __restrict__ x, tvi_bf16* __restrict__ out, float* __restrict__ partial,
-              int64_t rows_per_group, int tiles_per_group, int C8, int64_t ldx, int64_t ldo) {
+              int64_t rows_per_group, int tiles_per_group, int C8, int64_t ldx, int64_t ldo, int64_t inner) {
   __shared__ float red[kCsTy][32][8];
   const int cx = blockIdx.y * 32 + threadIdx.x;
   const int ty = threadIdx.y;
@@ -29,9 +29,13 @@ colsum_kernel(const tvi_bf16* __restrict__ x, tvi_bf16* __restrict__ out, float*
   float acc[8];
 #pragma unroll
   for (int j = 0; j < 8; ++j) acc[j] = 0.f;
+  // inner > 1: interleaved groups — logical row i of group (b, s) is physical row (b * rows_per_group + i) * inner + s
+  const int64_t gbase = group * rows_per_group;
+  const int64_t pbase = (group / inner) * rows_per_group * inner + group % inner;
   if (cx < C8) {
     for (int64_t r = rlo + ty; r < rhi; r += kCsTy) {
-      const uint4 u = __ldg(reinterpret_cast<const uint4*>(x + r * ldx + cx * 8));
+      const int64_t pr = inner == 1 ? r : pbase + (r - gbase) * inner;
+      const uint4 u = __ldg(reinterpret_cast<const uint4*>(x + pr * ldx + cx * 8));
       const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&u);
 #pragma unroll
       for (int i = 0; i < 4; ++i) {
@@ -127,6 +131,11 @@ extern "C" size_t tvi_colsum_bf16_workspace_bytes(int64_t nrows, int64_t rows_pe
 
 extern "C" int tvi_colsum_bf16(const tvi_bf16* x, tvi_bf16* out, void* workspace, int64_t nrows, int64_t rows_per_group, int C,
                                int64_t ldx, int64_t ldo, void* stream) {
+  return tvi_colsum_bf16_interleaved(x, out, workspace, nrows, rows_per_group, 1, C, ldx, ldo, stream);
+}
+
+extern "C" int tvi_colsum_bf16_interleaved(const tvi_bf16* x, tvi_bf16* out, void* workspace, int64_t nrows, int64_t rows_per_group,
+                                           int64_t group_inner, int C, int64_t ldx, int64_t ldo, void* stream) {
   using namespace tvi;
   TVI_CHECK_ARG(nrows >= 0 && C >= 0, "tvi_colsum_bf16: negative size");
   if (nrows == 0 || C == 0) return TVI_OK;
@@ -135,6 +144,7 @@ extern "C" int tvi_colsum_bf16(const tvi_bf16* x, tvi_bf16* out, void* workspace
   TVI_CHECK_ARG(C % 8 == 0 && ldx % 8 == 0 && ldo % 8 == 0 && ldx >= C && ldo >= C, "tvi_colsum_bf16: C and the row strides must be multiples of 8");
   TVI_CHECK_ARG(((uintptr_t)x | (uintptr_t)out) % 16 == 0, "tvi_colsum_bf16: pointers must be 16-byte aligned");
   const int64_t ngroups = nrows / rows_per_group;
+  TVI_CHECK_ARG(group_inner >= 1 && ngroups % group_inner == 0, "tvi_colsum_bf16: the group count must be a multiple of group_inner");
   const int tiles = cs_tiles(rows_per_group);
   TVI_CHECK_ARG(tiles == 1 || (workspace != nullptr && (uintptr_t)workspace % 16 == 0), "tvi_colsum_bf16: workspace required (16-byte aligned)");
   TVI_CHECK_ARG(ngroups * tiles < ((int64_t)1 << 31), "tvi_colsum_bf16: grid too large");
@@ -142,7 +152,7 @@ extern "C" int tvi_colsum_bf16(const tvi_bf16* x, tvi_bf16* out, void* workspace
   const int C8 = C / 8;
   dim3 grid((unsigned)(ngroups * tiles), (unsigned)((C8 + 31) / 32));
   dim3 block(32, kCsTy);
-  colsum_kernel<<<grid, block, 0, st>>>(x, out, (float*)workspace, rows_per_group, tiles, C8, ldx, ldo);
+  colsum_kernel<<<grid, block, 0, st>>>(x, out, (float*)workspace, rows_per_group, tiles, C8, ldx, ldo, group_inner);
   TVI_LAUNCH_OK("colsum_kernel");
   if (tiles > 1) {
     const int64_t pairs = ngroups * (C / 2);

@@ -443,8 +443,10 @@ def gemm_bf16_wgrad(dy: torch.Tensor, x: torch.Tensor, out: torch.Tensor | None 
     return out
 
 
-def colsum_bf16(x: torch.Tensor, rows_per_group: int | None = None, out: torch.Tensor | None = None) -> torch.Tensor:
-    """out[g, :] = sum of the rows of group g of x[nrows, C] (fp32 accumulation, bf16 result)."""
+def colsum_bf16(x: torch.Tensor, rows_per_group: int | None = None, out: torch.Tensor | None = None,
+                group_inner: int = 1) -> torch.Tensor:
+    """out[g, :] = sum of the rows of group g of x[nrows, C] (fp32 accumulation, bf16 result).  group_inner > 1: interleaved
+    groups (logical row i of group (b, s) is physical row (b * rows_per_group + i) * group_inner + s)."""
     _need_cuda(x)
     x, ldx = _rows2d(x, "x")
     C = x.shape[-1]
@@ -457,8 +459,8 @@ def colsum_bf16(x: torch.Tensor, rows_per_group: int | None = None, out: torch.T
     lib = _lib.load()
     nb = lib.tvi_colsum_bf16_workspace_bytes(nrows, rpg, C)
     ws = _workspace(nb, x.device)
-    _hooked("colsum_bf16", 2 if nb else 1, lib.tvi_colsum_bf16, x.data_ptr(), out.data_ptr(),
-            ws.data_ptr() if ws is not None else None, nrows, rpg, C, ldx, ldo, _stream())
+    _hooked("colsum_bf16", 2 if nb else 1, lib.tvi_colsum_bf16_interleaved, x.data_ptr(), out.data_ptr(),
+            ws.data_ptr() if ws is not None else None, nrows, rpg, int(group_inner), C, ldx, ldo, _stream())
     return out
 
 
@@ -577,8 +579,9 @@ def attn_spatial_bwd(q, k, v, o, dout, lse, batch: int, heads: int, S: int, Skv:
     return dq, dk, dv
 
 
-def attn_temporal_bwd(q, k, v, dout, nseq: int, heads: int, Tq: int, Tk: int, scale: float, dq=None, dk=None, dv=None):
-    """Gradients of the short-sequence core (recomputes the T x T softmax; needs neither o nor lse)."""
+def attn_temporal_bwd(q, k, v, dout, nseq: int, heads: int, Tq: int, Tk: int, scale: float, dq=None, dk=None, dv=None,
+                      seq_inner: int = 1):
+    """Gradients of the short-sequence core (recomputes the T x T softmax; needs neither o nor lse); seq_inner as the forward."""
     _need_cuda(q, k, v, dout)
     q, ldq = _rows2d(q, "q")
     k, ldk = _rows2d(k, "k")
@@ -592,15 +595,15 @@ def attn_temporal_bwd(q, k, v, dout, nseq: int, heads: int, Tq: int, Tk: int, sc
     dq, lddq = _rows2d(dq, "dq")
     dk, lddk = _rows2d(dk, "dk")
     dv, lddv = _rows2d(dv, "dv")
-    _hooked("attn_temporal_bwd", 1, _lib.load().tvi_attn_temporal_bwd, q.data_ptr(), k.data_ptr(), v.data_ptr(),
-            dout.data_ptr(), dq.data_ptr(), dk.data_ptr(), dv.data_ptr(), nseq, heads, Tq, Tk, d, ldq, ldk, ldv, lddo, lddq,
-            lddk, lddv, float(scale), _stream())
+    _hooked("attn_temporal_bwd", 1, _lib.load().tvi_attn_temporal_bwd_interleaved, q.data_ptr(), k.data_ptr(), v.data_ptr(),
+            dout.data_ptr(), dq.data_ptr(), dk.data_ptr(), dv.data_ptr(), nseq, heads, Tq, Tk, d, int(seq_inner), ldq, ldk, ldv,
+            lddo, lddq, lddk, lddv, float(scale), _stream())
     return dq, dk, dv
 
 
 def attn_fewkeys_bwd(q, k, v, dout, nrows: int, rows_per_group: int, heads: int, L: int, scale: float, Tq: int = 1, bias=None,
-                     dq=None, dk=None, dv=None):
-    """Gradients of the few-keys core; returns (dq or None, dk, dv) with dk/dv [ngroups*L, heads*d]."""
+                     dq=None, dk=None, dv=None, group_inner: int = 1):
+    """Gradients of the few-keys core; returns (dq or None, dk, dv) with dk/dv [ngroups*L, heads*d]; group_inner as the forward."""
     _need_cuda(q, k, v, dout, bias)
     k, ldk = _rows2d(k, "k")
     v, ldv = _rows2d(v, "v")
@@ -620,10 +623,10 @@ def attn_fewkeys_bwd(q, k, v, dout, nrows: int, rows_per_group: int, heads: int,
     lib = _lib.load()
     nb = lib.tvi_attn_fewkeys_bwd_workspace_bytes(nrows, rows_per_group, heads, L, d)
     ws = _workspace(nb, k.device)
-    _hooked("attn_fewkeys_bwd", 2 if nb else 1, lib.tvi_attn_fewkeys_bwd, q.data_ptr() if q is not None else None,
+    _hooked("attn_fewkeys_bwd", 2 if nb else 1, lib.tvi_attn_fewkeys_bwd_interleaved, q.data_ptr() if q is not None else None,
             k.data_ptr(), v.data_ptr(), dout.data_ptr(), dq.data_ptr() if q is not None else None, dk.data_ptr(),
-            dv.data_ptr(), ws.data_ptr() if ws is not None else None, nrows, rows_per_group, heads, L, d, ldq, ldk, ldv,
-            lddo, lddq, lddk, lddv, float(scale), Tq, bias.data_ptr() if bias is not None else None, _stream())
+            dv.data_ptr(), ws.data_ptr() if ws is not None else None, nrows, rows_per_group, heads, L, d, int(group_inner), ldq,
+            ldk, ldv, lddo, lddq, lddk, lddv, float(scale), Tq, bias.data_ptr() if bias is not None else None, _stream())
     return (dq if q is not None else None), dk, dv
 
 
