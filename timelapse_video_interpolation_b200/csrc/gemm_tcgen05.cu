@@ -46,9 +46,8 @@ constexpr int kStageBufs = 1;
 #ifndef TVI_GEMM_RES_BUFS
 #define TVI_GEMM_RES_BUFS 4
 #endif
-constexpr int kResStageBufs = TVI_GEMM_RES_BUFS;
+constexpr int kResStageBufs = TVI_GEMM_RES_BUFS;  // with a residual: the buffers also receive the residual chunk ahead of its use
 constexpr int kResAhead = kResStageBufs >= 4 ? 2 : 1;  // residual chunks requested ahead of the one being processed
-//                 // with a residual: the buffers also receive the residual chunk two chunks ahead
 // warps x bufs x [32 rows][64 B] + warps x 256 fp32 bias
 constexpr int kBiasBytes = 4 * 256 * 4;            // one fp32 bias strip (+ one LayerNorm column-sum strip) per accumulator stage, shared by the epilogue warps
 constexpr int staging_bytes(int bufs) { return kEpiWarps * bufs * 2048 + kBiasBytes; }
@@ -553,6 +552,28 @@ int pick_bn(int N, int step = 32) {
 }
 
 
+// Tile width of the MN-major-B kernels (dgrad, wgrad): multiples of the 64-wide swizzle atom.  `pick_bn` (least padding)
+// chose 64 for an output width of 320 — a 128 x 64 tile streams 24 KB of operands per 128 cycles of MMA.  What matters
+// is the operand stream per unit of output, tiles * (A tile + B tile), against the padded MMA work; measured at the L0
+// shapes (profiles/r2_gemm_bn_mn.txt): dgrad to 320 columns 0.690 -> 0.451 ms at 192 (2 560 -> 320), 0.275 -> 0.182 ms
+// (960 -> 320); to 1 280 columns 256 stays best.  wgrad shares its tiles among the token splits and does best with the
+// finer 128 at 320 output columns (0.818 -> 0.645 ms for dW[2560, 320]), 256 at 1 280.
+int pick_bn_mn(int N, bool wgrad) {
+  if (wgrad && N <= 384) return N <= 64 ? 64 : 128;
+  int best = 64;
+  double best_cost = 1e30;
+  for (int bn = 256; bn >= 64; bn -= 64) {
+    const int tiles = (N + bn - 1) / bn;
+    const double waste = (double)(tiles * bn - N) / (double)(tiles * bn);
+    const double cost = (double)tiles * (kABytes + bn * 128.0) * (1.0 + 0.5 * waste);
+    if (cost < best_cost) {
+      best_cost = cost;
+      best = bn;
+    }
+  }
+  return best;
+}
+
 // Operand tensor map.  K-major: dims {reduction, rows}, box {64, rows_box}.  MN-major: dims {out, reduction},
 // box {64, 64}.
 int operand_map(CUtensorMap* tm, const tvi_bf16* base, bool mn_major, int64_t out_extent, int64_t red_extent, int64_t ld,
@@ -592,10 +613,10 @@ int launch_gemm(const char* name, const tvi_bf16* A, const tvi_bf16* B, const tv
   GemmParams p;
   p.ln_stats = reinterpret_cast<const float2*>(ln_stats);
   p.ln_colsum = ln_colsum;
-  p.BN = pick_bn(No, kBMn ? 64 : 32);
+  p.BN = kBMn ? pick_bn_mn(No, kAMn) : pick_bn(No, 32);
   if (const char* e = getenv("TVI_GEMM_BN")) {
     const int bn = atoi(e);
-    if (!kBMn && bn >= 32 && bn <= 256 && bn % 32 == 0) p.BN = bn;
+    if (bn >= 32 && bn <= 256 && bn % (kBMn ? 64 : 32) == 0) p.BN = bn;
   }
   if (geglu_block > 0) p.BN = 2 * geglu_block;  // a tile = geglu_block value columns + their gate columns
   p.geglu = geglu_block > 0 ? 1 : 0;
@@ -689,7 +710,7 @@ bool use_pair(int64_t M, int N, int K) {
 }
 
 int wgrad_splits(int64_t M, int N, int K) {
-  const int64_t tiles = ((N + kBM - 1) / kBM) * (int64_t)((K + pick_bn(K, 64) - 1) / pick_bn(K, 64));
+  const int64_t tiles = ((N + kBM - 1) / kBM) * (int64_t)((K + pick_bn_mn(K, true) - 1) / pick_bn_mn(K, true));
   const int64_t kblocks = (M + kBK - 1) / kBK;
   const int64_t sms = num_sms();
   // The persistent grid works through tiles * splits equal items in rounds of `sms`: pick the split count whose last
