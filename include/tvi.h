@@ -148,6 +148,16 @@ int tvi_layernorm_bwd_res_bf16(const tvi_bf16* x, const tvi_bf16* dy, const tvi_
                                int64_t lddres, int64_t lddx, float eps, void* stream);
 int tvi_geglu_bwd_bf16(const tvi_bf16* pre, const tvi_bf16* dh, tvi_bf16* h, tvi_bf16* dpre, int64_t M, int inner, int64_t ldpre,
                        int64_t lddh, int64_t ldh, int64_t lddpre, void* stream);
+/* The two steps above in one kernel: the backward of `Linear(K -> 2*inner) -> GEGLU` (src/models/attention.py:526-535 under
+ * autograd, the first two modules of FeedForward.net) recomputes the projection on the tensor cores and turns the fp32
+ * accumulator straight into H = value * gelu(gate) [M, inner] (ldh) and dPre = [dH * gelu(gate) | dH * value * gelu'(gate)]
+ * [M, 2*inner] (lddpre, in the un-interleaved [value | gate] column order of the module's weight).  X [M, K] (ldx);
+ * Wi / bias_i are the weight [2*inner, K] (ldw) and bias (nullable) with value / gate rows interleaved in blocks of
+ * tvi_geglu_block(inner), as tvi_gemm_bf16_tn_ex(..., TVI_EPILOGUE_GEGLU) takes them; dH [M, inner] (lddh) is the gradient
+ * that reached H.  The 2*inner-wide pre-activation is never written.  inner % 32 == 0, K % 8 == 0. */
+int tvi_gemm_bf16_geglu_bwd(const tvi_bf16* X, const tvi_bf16* Wi, const tvi_bf16* bias_i, const tvi_bf16* dH, tvi_bf16* H,
+                            tvi_bf16* dPre, int64_t M, int inner, int K, int64_t ldx, int64_t ldw, int64_t lddh, int64_t ldh,
+                            int64_t lddpre, void* stream);
 
 /* Layout glue of TransformerSpatioTemporalModel.forward (rows N1 "AlphaBlender" and N2 of SURVEY 8.6).
  *   groupnorm_tokens : y[n, s, c] = GroupNorm(x)[n, c, s] — `self.norm` (nn.GroupNorm, biased variance, fp32/fp64

@@ -303,3 +303,44 @@ def test_empty_and_ragged_inputs(cuda):
             y = tvi.feed_forward(ff, x, residual=x)
             ref = feedforward_ref.feed_forward_ref(ff, x, residual=x)
             assert_block_close(f"feed_forward rows={rows}", y, ref)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("M,K,inner,bias", [(300, 320, 1280, True), (1000, 640, 2560, True), (257, 320, 96, True), (129, 64, 64, False),
+                                            (4096, 1280, 5120, True), (31, 320, 32, True)])
+def test_gemm_geglu_bwd_matches_fp32_reference(cuda, M, K, inner, bias):
+    """ops.gemm_geglu_bwd (the first FeedForward projection re-run with the GEGLU-backward epilogue) against the fp32
+    arithmetic autograd derives from `hidden, gate = proj(x).chunk(2, -1); hidden * F.gelu(gate)` (reference
+    src/models/attention.py:526-535 via diffusers GEGLU), and against the two-step path it replaces."""
+    import torch.nn.functional as F
+
+    g = torch.Generator().manual_seed(M + inner)
+    x = torch.randn(M, K, generator=g).to(torch.bfloat16).to(cuda)
+    w = (torch.randn(2 * inner, K, generator=g) / K ** 0.5).to(torch.bfloat16).to(cuda)
+    b = (torch.randn(2 * inner, generator=g) * 0.5).to(torch.bfloat16).to(cuda) if bias else None
+    dh = torch.randn(M, inner, generator=g).to(torch.bfloat16).to(cuda)
+    H = ops.geglu_block(inner)
+    wi = torch.stack([w[:inner].view(inner // H, H, K), w[inner:].view(inner // H, H, K)], dim=1).reshape(2 * inner, K).contiguous()
+    bi = torch.stack([b[:inner].view(inner // H, H), b[inner:].view(inner // H, H)], dim=1).reshape(-1).contiguous() if bias else None
+    h, dpre = ops.gemm_geglu_bwd(x, wi, bi, dh)
+    torch.cuda.synchronize()
+
+    pre = x.float() @ w.float().t() + (b.float() if bias else 0.0)
+    pre = pre.detach().requires_grad_(True)
+    val, gate = pre.chunk(2, dim=-1)
+    href = val * F.gelu(gate)
+    href.backward(dh.float())
+    tol_h = 2e-2 * href.abs().max().item()
+    tol_d = 2e-2 * pre.grad.abs().max().item()
+    assert (h.float() - href.detach()).abs().max().item() <= tol_h
+    assert (dpre.float() - pre.grad).abs().max().item() <= tol_d
+    # bf16-level agreement in the mean as well (a wrong column order or a missing bias would pass a loose max test on few rows)
+    assert (h.float() - href.detach()).abs().mean().item() <= 4e-3 * href.abs().mean().item() + 1e-6
+    assert (dpre.float() - pre.grad).abs().mean().item() <= 4e-3 * pre.grad.abs().mean().item() + 1e-6
+    # the forward's fused GEGLU GEMM computes the same h from the same accumulator
+    h_fwd = ops.gemm_bf16_tn_ex(x, wi, bi, geglu=True)
+    assert torch.equal(h_fwd, h)
+    # the path it replaces (bf16-rounded pre-activation, erff): same numbers to bf16 rounding
+    h2, dpre2 = ops.geglu_bwd(ops.gemm_bf16_tn(x, w, b), dh)
+    assert (dpre.float() - dpre2.float()).abs().max().item() <= tol_d
+    assert (h.float() - h2.float()).abs().max().item() <= tol_h

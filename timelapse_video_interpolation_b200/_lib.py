@@ -63,6 +63,7 @@ SIGNATURES = {
     "tvi_layernorm_bwd_res_bf16": (_i32, [_ptr, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr, _i64, _i32, _i64, _i64, _i64, _i64, _f32, _ptr]),
     "tvi_layernorm_bwd_bf16": (_i32, [_ptr, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr, _i64, _i32, _i64, _i64, _i64, _f32, _ptr]),
     "tvi_geglu_bwd_bf16": (_i32, [_ptr, _ptr, _ptr, _ptr, _i64, _i32, _i64, _i64, _i64, _i64, _ptr]),
+    "tvi_gemm_bf16_geglu_bwd": (_i32, [_ptr, _ptr, _ptr, _ptr, _ptr, _ptr, _i64, _i32, _i32, _i64, _i64, _i64, _i64, _i64, _ptr]),
     "tvi_gemm_bf16_dgrad": (_i32, [_ptr, _ptr, _ptr, _i64, _i32, _i32, _i64, _i64, _i64, _ptr]),
     "tvi_gemm_bf16_wgrad_workspace_bytes": (_sz, [_i64, _i32, _i32]),
     "tvi_gemm_bf16_wgrad": (_i32, [_ptr, _ptr, _ptr, _ptr, _i64, _i32, _i32, _i64, _i64, _i64, _ptr]),

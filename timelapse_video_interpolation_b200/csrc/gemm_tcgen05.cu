@@ -82,6 +82,34 @@ __device__ __forceinline__ uint64_t geglu_x2(uint64_t v2, uint64_t g2) {
   return f32x2_mul(f32x2_mul(g2, phi2), v2);
 }
 
+// Backward of the same product on a pair of columns: h = v * gelu(g), d(value) = dh * gelu(g),
+// d(gate) = dh * v * (Phi(g) + g * phi(g)), phi(g) = exp(-g^2 / 2) / sqrt(2 pi).  Phi as above; one more MUFU.EX2 for phi.
+__device__ __forceinline__ void geglu_bwd_x2(uint64_t v2, uint64_t g2, uint64_t d2, uint64_t& h2o, uint64_t& dv2o, uint64_t& dg2o) {
+  float g0, g1;
+  f32x2_unpack(g2, g0, g1);
+  const uint64_t u2 = f32x2_pack(fminf(fabsf(g0), 6.0f), fminf(fabsf(g1), 6.0f));
+  uint64_t q = f32x2_fma(f32x2_pack(2.3433244e-05f, 2.3433244e-05f), u2, f32x2_pack(-0.00061973924f, -0.00061973924f));
+  q = f32x2_fma(q, u2, f32x2_pack(0.007260352f, 0.007260352f));
+  q = f32x2_fma(q, u2, f32x2_pack(-0.051418606f, -0.051418606f));
+  q = f32x2_fma(q, u2, f32x2_pack(-0.46086353f, -0.46086353f));
+  q = f32x2_fma(q, u2, f32x2_pack(-1.1504804f, -1.1504804f));
+  float t0, t1;
+  f32x2_unpack(f32x2_fma(q, u2, f32x2_pack(-1.0f, -1.0f)), t0, t1);
+  const uint64_t hm2 = f32x2_fma(f32x2_pack(fast_exp2(t0), fast_exp2(t1)), f32x2_pack(-1.0f, -1.0f), f32x2_pack(0.5f, 0.5f));
+  float h0, h1;
+  f32x2_unpack(hm2, h0, h1);
+  const float s0 = __uint_as_float(__float_as_uint(h0) | (__float_as_uint(g0) & 0x80000000u));
+  const float s1 = __uint_as_float(__float_as_uint(h1) | (__float_as_uint(g1) & 0x80000000u));
+  const uint64_t phi2 = f32x2_add(f32x2_pack(s0, s1), f32x2_pack(0.5f, 0.5f));
+  float e0, e1;
+  f32x2_unpack(f32x2_mul(f32x2_mul(g2, g2), f32x2_pack(-0.72134752f, -0.72134752f)), e0, e1);  // -g^2 / 2 * log2(e)
+  const uint64_t pdf2 = f32x2_mul(f32x2_pack(fast_exp2(e0), fast_exp2(e1)), f32x2_pack(0.3989422804f, 0.3989422804f));
+  const uint64_t gelu2 = f32x2_mul(g2, phi2);
+  h2o = f32x2_mul(gelu2, v2);
+  dv2o = f32x2_mul(gelu2, d2);
+  dg2o = f32x2_mul(f32x2_mul(d2, v2), f32x2_fma(g2, pdf2, phi2));
+}
+
 struct GemmParams {
   int64_t m_tiles;
   int n_tiles;
@@ -104,6 +132,8 @@ struct GemmParams {
   const float* ln_colsum;
   int64_t M_out;
   int64_t ldp;
+  tvi_bf16* dpre;      // kGbwd: [M, 2 * N_store] = [d(value) | d(gate)], row stride lddpre
+  int64_t lddpre;
 };
 
 // kAMn / kBMn: the A / B operand is stored reduction-row-major ("MN-major": the output dimension is the
@@ -112,7 +142,11 @@ struct GemmParams {
 // each CTA loads its own 128 rows of A and HALF of the B tile, the leader CTA issues the MMAs for both, every CTA runs the
 // epilogue of its own 128 accumulator rows.  Per CTA and k-block the L2 -> SM operand stream is A + B/2 instead of A + B;
 // with the weight slice resident (half of it per CTA: 80 KB at BN = 256, K = 320) only A streams at all.
-template <bool kAMn, bool kBMn, bool kSplit, bool kPair = false>
+// kGbwd (forward TN GEMM with the GEGLU tile layout only): the backward of the fused GEGLU projection.  The accumulator
+// is the recomputed pre-activation [value | gate]; the "residual" stream is dh = d(loss)/d(h); the epilogue writes
+// h = value * gelu(gate) through the staging buffer / TMA store and d(pre) straight from registers (64 contiguous bytes per
+// thread and half, full sectors).  Neither the 2 * inner-wide pre-activation nor a second pass over dh touches HBM.
+template <bool kAMn, bool kBMn, bool kSplit, bool kPair = false, bool kGbwd = false>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CUtensorMap tmW,
                  const __grid_constant__ CUtensorMap tmY, const __grid_constant__ CUtensorMap tmR, const GemmParams p) {
@@ -131,6 +165,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   uint8_t* base_ptr = smem_raw + (base - smem_u32(smem_raw));
   static_assert(!kPair || (!kAMn && !kBMn && !kSplit), "the CTA-pair kernel is the forward (TN) GEMM");
+  static_assert(!kGbwd || (!kAMn && !kBMn && !kSplit && !kPair), "the GEGLU-backward epilogue belongs to the forward (TN) GEMM");
   const uint32_t cta_rank = kPair ? cluster_ctarank() : 0u;
   const int64_t worker = kPair ? (int64_t)(blockIdx.x >> 1) : (int64_t)blockIdx.x;      // tile walker: a CTA, or a CTA pair
   const int64_t nworkers = kPair ? (int64_t)(gridDim.x >> 1) : (int64_t)gridDim.x;
@@ -442,7 +477,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
             f32x2_unpack(f32x2_add(f32x2_pack(f[j + 2], f[j + 3]), f32x2_pack(b4.z, b4.w)), f[j + 2], f[j + 3]);
           }
         }
-        if (p.geglu) {
+        if (!kGbwd && p.geglu) {
           // GEGLU (diffusers GEGLU.forward: hidden * F.gelu(gate), erf form): gate = the partner column
           const float* gate_bias = my_bias + (out_chunks + c) * 32;
           if (has_ln) {  // the gate pre-activation gets the same affine map of its accumulator
@@ -462,7 +497,45 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
         }
         uint8_t* row_ptr = my_staging_ptr + buf * 2048 + lane * 64;
         const int sw = (lane >> 1) & 3;
-        if (has_res) {
+        if constexpr (kGbwd) {
+          // dh chunk (requested kResAhead chunks ago into this chunk's staging buffer) -> h, d(value), d(gate)
+          if (lane == 0) {
+            tma_store_wait_read<kResStageBufs - kResAhead - 1>();
+            issue_residual();
+          }
+          mbar_wait(&my_res_bar[buf], (qn / kResStageBufs) & 1);
+          ++qn;
+          const float* gate_bias = my_bias + (out_chunks + c) * 32;
+          const int64_t row = (int64_t)m0 + quad * 32 + lane;
+          tvi_bf16* dv_dst = p.dpre + row * p.lddpre + ncol0;
+          tvi_bf16* dg_dst = dv_dst + p.N_store;
+#pragma unroll
+          for (int ch = 0; ch < 4; ++ch) {
+            const uint4 u = *reinterpret_cast<const uint4*>(row_ptr + ((ch ^ sw) << 4));
+            const __nv_bfloat162* h2 = reinterpret_cast<const __nv_bfloat162*>(&u);
+            uint32_t ov[4], og[4];
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+              const int j = ch * 8 + 2 * q;
+              const float2 d2 = __bfloat1622float2(h2[q]);
+              float2 gb = make_float2(0.f, 0.f);
+              if (p.bias != nullptr) gb = *reinterpret_cast<const float2*>(gate_bias + j);
+              const uint64_t g2 = f32x2_add(f32x2_pack(__uint_as_float(rg[j]), __uint_as_float(rg[j + 1])), f32x2_pack(gb.x, gb.y));
+              uint64_t hh, dv, dg;
+              geglu_bwd_x2(f32x2_pack(f[j], f[j + 1]), g2, f32x2_pack(d2.x, d2.y), hh, dv, dg);
+              f32x2_unpack(hh, f[j], f[j + 1]);
+              float a, b;
+              f32x2_unpack(dv, a, b);
+              ov[q] = pack_bf16x2(a, b);
+              f32x2_unpack(dg, a, b);
+              og[q] = pack_bf16x2(a, b);
+            }
+            if (row < p.M_out) {
+              *reinterpret_cast<uint4*>(dv_dst + ch * 8) = make_uint4(ov[0], ov[1], ov[2], ov[3]);
+              *reinterpret_cast<uint4*>(dg_dst + ch * 8) = make_uint4(og[0], og[1], og[2], og[3]);
+            }
+          }
+        } else if (has_res) {
           // buffer (qn + 2) % 4 was last read by the store of chunk qn - 2: all but the latest store have drained
           if (lane == 0) {
             tma_store_wait_read<kResStageBufs - kResAhead - 1>();
@@ -590,13 +663,13 @@ int operand_map(CUtensorMap* tm, const tvi_bf16* base, bool mn_major, int64_t ou
   return make_tensor_map(tm, base, 2, 2, dims, strides, box, Swizzle::B128);
 }
 
-template <bool kAMn, bool kBMn, bool kSplit, bool kPair>
+template <bool kAMn, bool kBMn, bool kSplit, bool kPair, bool kGbwd>
 int configure_once() {
   static bool configured[64] = {false};
   int dev = 0;
   TVI_CUDA_OK(cudaGetDevice(&dev));
   if (dev < 0 || dev >= 64 || !configured[dev]) {
-    TVI_CUDA_OK(cudaFuncSetAttribute(gemm_bf16_kernel<kAMn, kBMn, kSplit, kPair>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    TVI_CUDA_OK(cudaFuncSetAttribute(gemm_bf16_kernel<kAMn, kBMn, kSplit, kPair, kGbwd>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                      227 * 1024 - 1024));
     if (dev >= 0 && dev < 64) configured[dev] = true;
   }
@@ -605,19 +678,23 @@ int configure_once() {
 
 // D[Mo, No] = A . B over a reduction of length R.  A is [Mo, R] (K-major) or [R, Mo] (MN-major) with row stride
 // lda; B is [No, R] or [R, No] with row stride ldb.  Output: bf16 Y (ldy) through TMA, or fp32 partials when kSplit.
-template <bool kAMn, bool kBMn, bool kSplit, bool kPair = false>
+template <bool kAMn, bool kBMn, bool kSplit, bool kPair = false, bool kGbwd = false>
 int launch_gemm(const char* name, const tvi_bf16* A, const tvi_bf16* B, const tvi_bf16* bias, tvi_bf16* Y, float* partial,
                 int splits, int64_t Mo, int No, int64_t R, int64_t lda, int64_t ldb, int64_t ldy, cudaStream_t st,
                 int geglu_block = 0, const tvi_bf16* residual = nullptr, int64_t ldr = 0, const float* ln_stats = nullptr,
-                const float* ln_colsum = nullptr) {
+                const float* ln_colsum = nullptr, tvi_bf16* dpre = nullptr, int64_t lddpre = 0) {
   GemmParams p;
+  p.dpre = dpre;
+  p.lddpre = lddpre;
   p.ln_stats = reinterpret_cast<const float2*>(ln_stats);
   p.ln_colsum = ln_colsum;
   p.BN = kBMn ? pick_bn_mn(No, kAMn) : pick_bn(No, 32);
+#ifdef TVI_GEMM_TUNE  // tuning builds only (tools/micro/build_tune.sh): tile-width sweeps
   if (const char* e = getenv("TVI_GEMM_BN")) {
     const int bn = atoi(e);
     if (bn >= 32 && bn <= 256 && bn % (kBMn ? 64 : 32) == 0) p.BN = bn;
   }
+#endif
   if (geglu_block > 0) p.BN = 2 * geglu_block;  // a tile = geglu_block value columns + their gate columns
   p.geglu = geglu_block > 0 ? 1 : 0;
   p.N_store = geglu_block > 0 ? No / 2 : No;
@@ -671,7 +748,7 @@ int launch_gemm(const char* name, const tvi_bf16* A, const tvi_bf16* B, const tv
     tmY = tmA;  // unused by the split epilogue
     tmR = tmA;
   }
-  rc = configure_once<kAMn, kBMn, kSplit, kPair>();
+  rc = configure_once<kAMn, kBMn, kSplit, kPair, kGbwd>();
   if (rc) return rc;
   int64_t grid = p.m_tiles * p.n_tiles;
   if (kSplit) grid *= (p.k_blocks_total + p.k_blocks - 1) / p.k_blocks;
@@ -693,7 +770,7 @@ int launch_gemm(const char* name, const tvi_bf16* A, const tvi_bf16* B, const tv
     TVI_CUDA_OK(cudaLaunchKernelEx(&cfg, gemm_bf16_kernel<kAMn, kBMn, kSplit, kPair>, tmA, tmB, tmY, tmR, p));
     return TVI_OK;
   }
-  gemm_bf16_kernel<kAMn, kBMn, kSplit, kPair><<<(unsigned)grid, kGemmThreads, smem_bytes, st>>>(tmA, tmB, tmY, tmR, p);
+  gemm_bf16_kernel<kAMn, kBMn, kSplit, kPair, kGbwd><<<(unsigned)grid, kGemmThreads, smem_bytes, st>>>(tmA, tmB, tmY, tmR, p);
   TVI_LAUNCH_OK(name);
   return TVI_OK;
 }
@@ -832,6 +909,29 @@ extern "C" int tvi_gemm_bf16_tn_ln(const tvi_bf16* X, const tvi_bf16* Wg, const 
   TVI_CHECK_ARG(M < ((int64_t)1 << 31) - 256, "tvi_gemm_bf16_tn_ln: M too large for one call");
   return launch_gemm<false, false, false>("tvi_gemm_bf16_tn_ln", X, Wg, bias, Y, nullptr, 1, M, N, K, ldx, ldw, ldy,
                                           (cudaStream_t)stream, block, residual, ldr, stats, colsum);
+}
+
+extern "C" int tvi_gemm_bf16_geglu_bwd(const tvi_bf16* X, const tvi_bf16* Wi, const tvi_bf16* bias_i, const tvi_bf16* dH, tvi_bf16* H,
+                                       tvi_bf16* dPre, int64_t M, int inner, int K, int64_t ldx, int64_t ldw, int64_t lddh,
+                                       int64_t ldh, int64_t lddpre, void* stream) {
+  using namespace tvi;
+  TVI_CHECK_ARG(M >= 0 && inner >= 0 && K >= 0, "tvi_gemm_bf16_geglu_bwd: negative size");
+  if (M == 0 || inner == 0) return TVI_OK;
+  TVI_CHECK_ARG(X && Wi && dH && H && dPre, "tvi_gemm_bf16_geglu_bwd: null pointer");
+  TVI_CHECK_ARG(K > 0 && K % 8 == 0, "tvi_gemm_bf16_geglu_bwd: K=%d must be a positive multiple of 8", K);
+  const int block = tvi_geglu_block(inner);
+  TVI_CHECK_ARG(block > 0, "tvi_gemm_bf16_geglu_bwd: GEGLU inner width %d must be a multiple of 32", inner);
+  TVI_CHECK_ARG(ldx % 8 == 0 && ldw % 8 == 0 && lddh % 8 == 0 && ldh % 8 == 0 && lddpre % 8 == 0,
+                "tvi_gemm_bf16_geglu_bwd: row strides must be multiples of 8 elements");
+  TVI_CHECK_ARG(ldx >= K && ldw >= K && lddh >= inner && ldh >= inner && lddpre >= 2 * (int64_t)inner,
+                "tvi_gemm_bf16_geglu_bwd: row stride smaller than the row");
+  TVI_CHECK_ARG(((uintptr_t)X | (uintptr_t)Wi | (uintptr_t)dH | (uintptr_t)H | (uintptr_t)dPre) % 16 == 0,
+                "tvi_gemm_bf16_geglu_bwd: X, Wi, dH, H, dPre must be 16-byte aligned");
+  TVI_CHECK_ARG(bias_i == nullptr || (uintptr_t)bias_i % 2 == 0, "tvi_gemm_bf16_geglu_bwd: bias must be 2-byte aligned");
+  TVI_CHECK_ARG(M < ((int64_t)1 << 31) - 256, "tvi_gemm_bf16_geglu_bwd: M too large for one call");
+  return launch_gemm<false, false, false, false, true>("tvi_gemm_bf16_geglu_bwd", X, Wi, bias_i, H, nullptr, 1, M, 2 * inner, K, ldx,
+                                                       ldw, ldh, (cudaStream_t)stream, block, dH, lddh, nullptr, nullptr, dPre,
+                                                       lddpre);
 }
 
 extern "C" int tvi_gemm_bf16_dgrad(const tvi_bf16* dY, const tvi_bf16* W, tvi_bf16* dX, int64_t M, int N, int K,

@@ -269,7 +269,12 @@ extern "C" int tvi_layernorm_bf16(const tvi_bf16* x, const tvi_bf16* gamma, cons
   TVI_CHECK_ARG(eps > 0.f, "tvi_layernorm_bf16: eps must be positive");
   cudaStream_t st = (cudaStream_t)stream;
   const int C8 = C / 8;
-  if (getenv("TVI_LN_GENERIC") == nullptr) {
+#ifdef TVI_GEMM_TUNE  // tuning builds only: TVI_LN_GENERIC=1 times the generic kernel at the SVD widths
+  const bool flat = getenv("TVI_LN_GENERIC") == nullptr;
+#else
+  const bool flat = true;
+#endif
+  if (flat) {
     if (C8 == 40) return launch_ln_flat<4>(x, gamma, beta, y, M, ldx, ldy, eps, st);
     if (C8 == 80) return launch_ln_flat<2>(x, gamma, beta, y, M, ldx, ldy, eps, st);
     if (C8 == 160) return launch_ln_flat<1>(x, gamma, beta, y, M, ldx, ldy, eps, st);

@@ -69,8 +69,9 @@ def _cast_grad(g, like):
 
 class _FeedForwardFn(torch.autograd.Function):
     """Tape entry of `Linear(C -> 2*inner) -> GEGLU -> Linear(inner -> C_out)` (reference src/models/attention.py:526-535).
-    Saves only x: the backward recomputes the first projection with the plain GEMM (the fused forward never writes it),
-    gets h and d(pre) from one elementwise kernel, and runs the dgrad / wgrad / column-sum kernels of the projections."""
+    Saves only x: the backward re-runs the first projection with the GEGLU-backward epilogue (`ops.gemm_geglu_bwd`: h and
+    d(pre) straight from the fp32 accumulator; the 2*inner-wide projection is never written, forward or backward) and
+    runs the dgrad / wgrad / column-sum kernels of the projections."""
 
     @staticmethod
     def forward(ctx, x, w1, b1, w2, b2, residual=None):
@@ -86,12 +87,14 @@ class _FeedForwardFn(torch.autograd.Function):
             if b1 is not None:
                 bb = _bf16(b1)
                 bi = torch.stack([bb[:inner].view(inner // H, H), bb[inner:].view(inner // H, H)], dim=1).reshape(-1).contiguous()
-            h = ops.gemm_bf16_tn_ex(x2, wi.contiguous(), bi, geglu=True)
+            wi = wi.contiguous()
+            h = ops.gemm_bf16_tn_ex(x2, wi, bi, geglu=True)
             if residual is None:
                 y = ops.gemm_bf16_tn(h, w2b, _bf16(b2))
             else:  # `ff_output + hidden_states` in the second GEMM's epilogue; its gradient is dy itself
                 y = ops.gemm_bf16_tn_ex(h, w2b, _bf16(b2), residual=residual.detach().contiguous().view(x2.shape[0], -1))
         ctx.save_for_backward(x2, w1, b1, w2, b2)
+        ctx.wi, ctx.bi = wi, bi          # the interleaved bf16 copies (1.6 MB at C = 320): the backward re-runs the same GEMM
         ctx.x_shape = x.shape
         return y.view(*x.shape[:-1], y.shape[-1])
 
@@ -102,9 +105,9 @@ class _FeedForwardFn(torch.autograd.Function):
         need_res = len(ctx.needs_input_grad) > 5 and ctx.needs_input_grad[5]
         dy2 = dy.contiguous().view(-1, dy.shape[-1]).to(torch.bfloat16)
         w1b, w2b = _bf16(w1), _bf16(w2)
-        pre = ops.gemm_bf16_tn(x2, w1b, _bf16(b1))                       # [M, 2*inner] = [value | gate]
         dh = ops.gemm_bf16_dgrad(dy2, w2b)                               # [M, inner]
-        h, dpre = ops.geglu_bwd(pre, dh, need_h=need_w2)
+        # the first projection again, its fp32 accumulator turned into h and d(pre) in the epilogue (never written itself)
+        h, dpre = ops.gemm_geglu_bwd(x2, ctx.wi, ctx.bi, dh)
         dw2 = ops.gemm_bf16_wgrad(dy2, h) if need_w2 else None
         db2 = ops.colsum_bf16(dy2, dy2.shape[0]).view(-1) if (need_b2 and b2 is not None) else None
         dw1 = ops.gemm_bf16_wgrad(dpre, x2) if need_w1 else None

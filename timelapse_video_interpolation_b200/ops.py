@@ -388,6 +388,31 @@ def geglu_bwd(pre: torch.Tensor, dh: torch.Tensor, need_h: bool = True):
     return h, dpre
 
 
+def gemm_geglu_bwd(x: torch.Tensor, wi: torch.Tensor, bias_i: torch.Tensor | None, dh: torch.Tensor):
+    """Backward of the fused GEGLU projection in one GEMM: x [M, K], wi [2*inner, K] / bias_i with value / gate rows
+    interleaved in blocks of `geglu_block(inner)` (as `gemm_bf16_tn_ex(..., geglu=True)` takes them), dh [M, inner] ->
+    (h [M, inner], dpre [M, 2*inner] = [d value | d gate])."""
+    _need_cuda(x, wi, dh)
+    x, ldx = _rows2d(x, "x")
+    wi, ldw = _rows2d(wi, "wi")
+    dh, lddh = _rows2d(dh, "dh")
+    inner, K = dh.shape[-1], x.shape[-1]
+    if wi.shape[0] != 2 * inner or wi.shape[-1] != K:
+        raise _lib.TviError(_lib.TVI_ERR_INVALID, "gemm_geglu_bwd: wi must be [2 * inner, K]")
+    if bias_i is not None:
+        _need_cuda(bias_i)
+        bias_i = bias_i.contiguous()
+    M = x.numel() // K if K else 0
+    if dh.numel() != M * inner:
+        raise _lib.TviError(_lib.TVI_ERR_INVALID, "gemm_geglu_bwd: dh must have one row per row of x")
+    h = torch.empty(M, inner, dtype=torch.bfloat16, device=x.device)
+    dpre = torch.empty(M, 2 * inner, dtype=torch.bfloat16, device=x.device)
+    _hooked("gemm_bf16_geglu_bwd", 1, _lib.load().tvi_gemm_bf16_geglu_bwd, x.data_ptr(), wi.data_ptr(),
+            bias_i.data_ptr() if bias_i is not None else None, dh.data_ptr(), h.data_ptr(), dpre.data_ptr(), M, inner, K, ldx, ldw,
+            lddh, inner, 2 * inner, _stream())
+    return h, dpre
+
+
 def farneback_clip(frames: torch.Tensor, pyr_scale: float = 0.5, levels: int = 3, winsize: int = 15, iterations: int = 3,
                    poly_n: int = 5, poly_sigma: float = 1.2, out: torch.Tensor | None = None) -> torch.Tensor:
     """Flows of every consecutive frame pair of a uint8 CUDA clip [N, H, W] / [N, H, W, 3] -> [N - 1, H, W, 2] fp32; every

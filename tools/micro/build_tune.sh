@@ -1,5 +1,5 @@
 #!/bin/bash
-# libtvi with tuning hooks compiled in (-DTVI_GEMM_TUNE: TVI_GEGLU_BLOCK; TVI_GEMM_BN is always read) -> tools/micro/libtvi_tune<suffix>.so
+# libtvi with tuning hooks compiled in (-DTVI_GEMM_TUNE: TVI_GEGLU_BLOCK, TVI_GEMM_BN, TVI_LN_GENERIC) -> tools/micro/libtvi_tune<suffix>.so
 # use: build_tune.sh [suffix] [extra nvcc flags...];  PROF_LIB=tools/micro/libtvi_tune.so TVI_GEGLU_BLOCK=64 python tools/prof_ff.py ffin
 set -e
 cd "$(dirname "$0")"

@@ -45,7 +45,12 @@ ms = timed(lambda: ops.geglu_bwd(pre, dh, need_h=True))
 print(f"geglu_bwd (+h): {ms:.4f} ms  {2.0 * M * (2560 + 1280 + 1280 + 2560) / ms / 1e6:.0f} GB/s")
 ms = timed(lambda: ops.geglu_bwd(pre, dh, need_h=False))
 print(f"geglu_bwd     : {ms:.4f} ms  {2.0 * M * (2560 + 1280 + 2560) / ms / 1e6:.0f} GB/s")
-del pre, dh
+x, wi, bi = rnd(M, 320), rnd(2560, 320) * 0.1, rnd(2560)
+ms0 = timed(lambda: ops.gemm_bf16_tn(x, wi, bi))
+ms = timed(lambda: ops.gemm_geglu_bwd(x, wi, bi, dh))
+print(f"gemm_geglu_bwd (recompute + h + dpre in one kernel): {ms:.4f} ms  {2.0 * M * (320 + 1280 + 1280 + 2560) / ms / 1e6:.0f} GB/s"
+      f"   [replaces plain GEMM {ms0:.4f} ms + geglu_bwd (+h)]")
+del pre, dh, x, wi, bi
 x, dy, g = rnd(M, 320), rnd(M, 320), rnd(320)
 ms = timed(lambda: ops.layernorm_bwd(x, dy, g, 1e-5))
 print(f"layernorm_bwd (dx, dgamma, dbeta): {ms:.4f} ms  {2.0 * M * 320 * 3 / ms / 1e6:.0f} GB/s")
