@@ -41,6 +41,32 @@ def test_layer_norm_backward(cuda, rows, C):
     _close("dbeta", norm.bias.grad, br.grad)
 
 
+@pytest.mark.parametrize("rows,C,with_res,strided", [(40000, 320, True, False), (20001, 640, True, True), (19000, 320, False, True),
+                                                    (5000, 1280, True, False), (7, 320, True, False)])
+def test_layer_norm_backward_many_rows(cuda, rows, C, with_res, strided):
+    """The row ring of the LayerNorm backward (bulk copies `depth` rows ahead of the arithmetic) over several grid strides,
+    with the residual gradient folded in and with row strides wider than the row (column slices of wider buffers)."""
+    g = torch.Generator(device="cuda").manual_seed(rows + C)
+    ld = C + 64 if strided else C
+    xb = (torch.randn(rows, ld, generator=g, device=cuda) * 1.5 + 0.3).to(torch.bfloat16)
+    dyb = torch.randn(rows, ld, generator=g, device=cuda).to(torch.bfloat16)
+    rb = torch.randn(rows, ld, generator=g, device=cuda).to(torch.bfloat16) if with_res else None
+    x, dy, r = xb[:, :C], dyb[:, :C], (rb[:, :C] if with_res else None)
+    gamma = (1 + 0.2 * torch.randn(C, generator=g, device=cuda)).to(torch.bfloat16)
+    dx, dgm, dbt = ops.layernorm_bwd(x, dy, gamma, 1e-5, dres=r)
+    xr = x.float().requires_grad_(True)
+    gr, br = gamma.float().requires_grad_(True), torch.zeros(C, device=cuda, requires_grad=True)
+    (F.layer_norm(xr, (C,), gr, br, 1e-5) * dy.float()).sum().backward()
+    ref_dx = xr.grad + (r.float() if with_res else 0.0)
+    _close("dx", dx, ref_dx)
+    # sums over up to 40 000 rows, rounded to bf16 once at the end
+    _close("dgamma", dgm, gr.grad)
+    _close("dbeta", dbt, br.grad)
+    # two calls give the same bits (fixed summation order, no atomics)
+    dx2, dgm2, dbt2 = ops.layernorm_bwd(x, dy, gamma, 1e-5, dres=r)
+    assert torch.equal(dx, dx2) and torch.equal(dgm, dgm2) and torch.equal(dbt, dbt2)
+
+
 def _ff_ref(x, w1, b1, w2, b2):
     hidden, gate = F.linear(x, w1, b1).chunk(2, dim=-1)
     return F.linear(hidden * F.gelu(gate), w2, b2)

@@ -550,10 +550,12 @@ __global__ void __launch_bounds__(TemporalBwdCfg<MT, DH>::kWarps * 32) attn_temp
 template <int MT, int DH>
 int launch_temporal_bwd(const TbParams& p, cudaStream_t st) {
   using Cfg = TemporalBwdCfg<MT, DH>;
-  static bool configured = false;
-  if (!configured) {
+  static bool configured[64] = {false};  // per device: the attribute belongs to the device's context
+  int dev = 0;
+  TVI_CUDA_OK(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= 64 || !configured[dev]) {
     TVI_CUDA_OK(cudaFuncSetAttribute(attn_temporal_bwd_kernel<MT, DH>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes));
-    configured = true;
+    if (dev >= 0 && dev < 64) configured[dev] = true;
   }
   const int per_sm = (227 * 1024) / (Cfg::kSmemBytes + 1024);
   int64_t grid = (p.nitems + Cfg::kWarps - 1) / Cfg::kWarps;

@@ -223,10 +223,12 @@ int launch_temporal(const tvi_bf16* q, const tvi_bf16* k, const tvi_bf16* v, tvi
                     int heads, int Tq, int Tk, int64_t ldq, int64_t ldk, int64_t ldv, int64_t ldo, float scale,
                     int64_t inner, cudaStream_t st) {
   using Cfg = TemporalCfg<MT, DH>;
-  static bool configured = false;
-  if (!configured) {
+  static bool configured[64] = {false};  // per device: the attribute belongs to the device's context
+  int dev = 0;
+  TVI_CUDA_OK(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= 64 || !configured[dev]) {
     TVI_CUDA_OK(cudaFuncSetAttribute(attn_temporal_kernel<MT, DH>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes));
-    configured = true;
+    if (dev >= 0 && dev < 64) configured[dev] = true;
   }
   const int64_t nitems = nseq * heads;
   const int per_sm = (MT == 1 && DH == 1) ? 2 : 1;

@@ -467,6 +467,146 @@ layernorm_bwd_kernel(const tvi_bf16* __restrict__ x, const tvi_bf16* __restrict_
   }
 }
 
+// The SVD widths (C = 320 / 640 / 1280 = 40 * G columns, G = 8 / 16 / 32): G lanes share a row, 32 / G rows per warp pass,
+// every lane owns the five 16-byte chunks (lane % G) + G * j of its row — all 32 lanes carry data (the kernel above runs
+// its second chunk pass with 8 of 32 lanes at C = 320), a warp-level load covers whole 128-byte lines, the four row
+// reductions are log2(G) shuffles on ONE value per lane instead of five per row, and the arithmetic is packed (f32x2).
+// The kernel above is bound by its instruction stream (~450 per row at C = 320), not by HBM or latency: staging the rows
+// through shared memory (1-D bulk copies, then a per-lane cp.async FIFO) only added instructions, 0.155 -> 0.227 / 0.180 ms.
+template <int G>
+__global__ void __launch_bounds__(kLnBwdWarps * 32, 1)
+layernorm_bwd_flat_kernel(const tvi_bf16* __restrict__ x, const tvi_bf16* __restrict__ dy, const tvi_bf16* __restrict__ gamma,
+                          const tvi_bf16* __restrict__ dres, tvi_bf16* __restrict__ dx, float* __restrict__ partial, int64_t M,
+                          int64_t ldx, int64_t lddy, int64_t lddres, int64_t lddx, float eps) {
+  constexpr int R = 32 / G, C8 = 5 * G, C = C8 * 8;
+  extern __shared__ float s_acc[];  // [warps][R][2][C]
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int rs = lane / G, lg = lane % G;
+  auto unpack2 = [](uint32_t w) { return f32x2_pack(__uint_as_float(w << 16), __uint_as_float(w & 0xffff0000u)); };
+  uint64_t dg[5][4], db[5][4];
+  uint4 ug[5];  // this lane's gamma chunks (bf16), constant over the rows
+#pragma unroll
+  for (int j = 0; j < 5; ++j) {
+#pragma unroll
+    for (int q = 0; q < 4; ++q) dg[j][q] = db[j][q] = f32x2_pack(0.f, 0.f);
+    ug[j] = make_uint4(0x3f803f80u, 0x3f803f80u, 0x3f803f80u, 0x3f803f80u);  // bf16 1.0 pairs
+    if (gamma != nullptr) ug[j] = __ldg(reinterpret_cast<const uint4*>(gamma) + lg + G * j);
+  }
+  constexpr float inv_c = 1.0f / (float)C;
+  for (int64_t row0 = ((int64_t)blockIdx.x * kLnBwdWarps + warp) * R; row0 < M; row0 += (int64_t)gridDim.x * kLnBwdWarps * R) {
+    const int64_t row = row0 + rs;
+    const bool live = row < M;
+    const int64_t rr = live ? row : M - 1;  // tail slots re-read the last row, contribute nothing and store nothing
+    uint4 rx[5], rd[5], rres[5];
+#pragma unroll
+    for (int j = 0; j < 5; ++j) {
+      const int c = lg + G * j;
+      rx[j] = __ldg(reinterpret_cast<const uint4*>(x + rr * ldx) + c);
+      rd[j] = __ldg(reinterpret_cast<const uint4*>(dy + rr * lddy) + c);
+      rres[j] = make_uint4(0u, 0u, 0u, 0u);
+      if (dres != nullptr) rres[j] = __ldg(reinterpret_cast<const uint4*>(dres + rr * lddres) + c);
+      if (!live) rd[j] = make_uint4(0u, 0u, 0u, 0u);
+    }
+    uint64_t xv[5][4];
+    uint64_t acc = f32x2_pack(0.f, 0.f);
+#pragma unroll
+    for (int j = 0; j < 5; ++j) {
+      const uint32_t w[4] = {rx[j].x, rx[j].y, rx[j].z, rx[j].w};
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        xv[j][q] = unpack2(w[q]);
+        acc = f32x2_add(acc, xv[j][q]);
+      }
+    }
+    float a0, a1;
+    f32x2_unpack(acc, a0, a1);
+    float sum = a0 + a1;
+#pragma unroll
+    for (int o = G / 2; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+    const float nmean = -sum * inv_c;
+    const uint64_t nm2 = f32x2_pack(nmean, nmean);
+    acc = f32x2_pack(0.f, 0.f);
+#pragma unroll
+    for (int j = 0; j < 5; ++j)
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        xv[j][q] = f32x2_add(xv[j][q], nm2);
+        acc = f32x2_fma(xv[j][q], xv[j][q], acc);
+      }
+    f32x2_unpack(acc, a0, a1);
+    float sq = a0 + a1;
+#pragma unroll
+    for (int o = G / 2; o > 0; o >>= 1) sq += __shfl_xor_sync(0xffffffffu, sq, o);
+    const float rstd = rsqrtf(sq * inv_c + eps);
+    const uint64_t rs2 = f32x2_pack(rstd, rstd);
+    uint64_t s1v = f32x2_pack(0.f, 0.f), s2v = f32x2_pack(0.f, 0.f);  // sum g, sum g * xhat (g = dy * gamma)
+#pragma unroll
+    for (int j = 0; j < 5; ++j) {
+      const uint32_t wd[4] = {rd[j].x, rd[j].y, rd[j].z, rd[j].w}, wg[4] = {ug[j].x, ug[j].y, ug[j].z, ug[j].w};
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const uint64_t xhat = f32x2_mul(xv[j][q], rs2);
+        const uint64_t d2 = unpack2(wd[q]);
+        dg[j][q] = f32x2_fma(d2, xhat, dg[j][q]);
+        db[j][q] = f32x2_add(db[j][q], d2);
+        const uint64_t g2 = f32x2_mul(d2, unpack2(wg[q]));
+        s1v = f32x2_add(s1v, g2);
+        s2v = f32x2_fma(g2, xhat, s2v);
+        xv[j][q] = xhat;
+      }
+    }
+    f32x2_unpack(s1v, a0, a1);
+    float s1 = a0 + a1;
+    f32x2_unpack(s2v, a0, a1);
+    float s2 = a0 + a1;
+#pragma unroll
+    for (int o = G / 2; o > 0; o >>= 1) {
+      s1 += __shfl_xor_sync(0xffffffffu, s1, o);
+      s2 += __shfl_xor_sync(0xffffffffu, s2, o);
+    }
+    if (dx != nullptr && live) {
+      const uint64_t ns1 = f32x2_pack(-s1 * inv_c, -s1 * inv_c), ns2 = f32x2_pack(-s2 * inv_c, -s2 * inv_c);
+#pragma unroll
+      for (int j = 0; j < 5; ++j) {
+        const uint32_t wd[4] = {rd[j].x, rd[j].y, rd[j].z, rd[j].w}, wg[4] = {ug[j].x, ug[j].y, ug[j].z, ug[j].w};
+        const uint32_t wr[4] = {rres[j].x, rres[j].y, rres[j].z, rres[j].w};
+        uint32_t o[4];
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          // dx = rstd * (g - mean(g) - xhat * mean(g xhat)) (+ the residual branch's gradient)
+          uint64_t t = f32x2_add(f32x2_mul(unpack2(wd[q]), unpack2(wg[q])), ns1);
+          t = f32x2_fma(xv[j][q], ns2, t);
+          t = f32x2_fma(t, rs2, unpack2(wr[q]));
+          float t0, t1;
+          f32x2_unpack(t, t0, t1);
+          o[q] = pack_bf16x2(t0, t1);
+        }
+        *(reinterpret_cast<uint4*>(dx + row * lddx) + lg + G * j) = make_uint4(o[0], o[1], o[2], o[3]);
+      }
+    }
+  }
+  // per-block reduction over (warp, row slot) in a fixed order
+  float* mine = s_acc + ((size_t)warp * R + rs) * 2 * C;
+#pragma unroll
+  for (int j = 0; j < 5; ++j) {
+    const int c = lg + G * j;
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      float v0, v1;
+      f32x2_unpack(dg[j][q], v0, v1);
+      *reinterpret_cast<float2*>(mine + c * 8 + 2 * q) = make_float2(v0, v1);
+      f32x2_unpack(db[j][q], v0, v1);
+      *reinterpret_cast<float2*>(mine + C + c * 8 + 2 * q) = make_float2(v0, v1);
+    }
+  }
+  __syncthreads();
+  for (int j = threadIdx.x; j < 2 * C; j += blockDim.x) {
+    float s = 0.f;
+    for (int w = 0; w < kLnBwdWarps * R; ++w) s += s_acc[(size_t)w * 2 * C + j];
+    partial[(size_t)blockIdx.x * 2 * C + j] = s;
+  }
+}
+
 __global__ void ln_bwd_final_kernel(const float* __restrict__ partial, tvi_bf16* __restrict__ dgamma, tvi_bf16* __restrict__ dbeta,
                                     int nblocks, int C) {
   const int j = blockIdx.x * blockDim.x + threadIdx.x;
@@ -488,14 +628,47 @@ template <int NCH>
 int launch_ln_bwd(const tvi_bf16* x, const tvi_bf16* dy, const tvi_bf16* gamma, const tvi_bf16* dres, tvi_bf16* dx, float* partial,
                   int64_t M, int C8, int64_t ldx, int64_t lddy, int64_t lddres, int64_t lddx, float eps, cudaStream_t st) {
   const size_t smem = (size_t)kLnBwdWarps * 2 * C8 * 8 * sizeof(float);
-  static bool configured = false;
-  if (!configured) {
+  static bool configured[64] = {false};
+  int dev = 0;
+  TVI_CUDA_OK(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= 64 || !configured[dev]) {
     TVI_CUDA_OK(cudaFuncSetAttribute(layernorm_bwd_kernel<NCH>, cudaFuncAttributeMaxDynamicSharedMemorySize, 8 * 2 * 2048 * 4));
-    configured = true;
+    if (dev >= 0 && dev < 64) configured[dev] = true;
   }
   layernorm_bwd_kernel<NCH><<<(unsigned)ln_bwd_blocks(M), kLnBwdWarps * 32, smem, st>>>(x, dy, gamma, dres, dx, partial, M, C8, ldx,
                                                                                          lddy, lddres, lddx, eps);
   TVI_LAUNCH_OK("layernorm_bwd_kernel");
+  return TVI_OK;
+}
+
+// number of fp32 partial rows tvi_layernorm_bwd_workspace_bytes provides (device-independent)
+int64_t ln_bwd_ws_blocks(int64_t M) {
+  const int64_t need = (M + kLnBwdWarps * kLnBwdRowsPerWarp - 1) / (kLnBwdWarps * kLnBwdRowsPerWarp);
+  return need < 4096 ? need : 4096;
+}
+
+template <int G>
+int launch_ln_bwd_flat(const tvi_bf16* x, const tvi_bf16* dy, const tvi_bf16* gamma, const tvi_bf16* dres, tvi_bf16* dx,
+                       float* partial, int64_t M, int64_t ldx, int64_t lddy, int64_t lddres, int64_t lddx, float eps,
+                       cudaStream_t st, int64_t* blocks_out) {
+  constexpr int R = 32 / G, C = 40 * G;
+  constexpr size_t smem = (size_t)kLnBwdWarps * R * 2 * C * sizeof(float);  // 80 KB at every G
+  static bool configured[64] = {false};
+  int dev = 0;
+  TVI_CUDA_OK(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= 64 || !configured[dev]) {
+    TVI_CUDA_OK(cudaFuncSetAttribute(layernorm_bwd_flat_kernel<G>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    if (dev >= 0 && dev < 64) configured[dev] = true;
+  }
+  // persistent: one block per SM (the 80 accumulator registers per lane leave room for one), never more partial rows
+  // than the workspace holds
+  int64_t blocks = (M + kLnBwdWarps * R - 1) / (kLnBwdWarps * R);
+  if (blocks > num_sms()) blocks = num_sms();
+  if (blocks > ln_bwd_ws_blocks(M)) blocks = ln_bwd_ws_blocks(M);
+  layernorm_bwd_flat_kernel<G><<<(unsigned)blocks, kLnBwdWarps * 32, smem, st>>>(x, dy, gamma, dres, dx, partial, M, ldx, lddy,
+                                                                                  lddres, lddx, eps);
+  TVI_LAUNCH_OK("layernorm_bwd_flat_kernel");
+  *blocks_out = blocks;
   return TVI_OK;
 }
 
@@ -505,8 +678,7 @@ int launch_ln_bwd(const tvi_bf16* x, const tvi_bf16* dy, const tvi_bf16* gamma, 
 extern "C" size_t tvi_layernorm_bwd_workspace_bytes(int64_t M, int C) {
   if (M <= 0 || C <= 0) return 0;
   // device-independent upper bound of the partial count (the launch uses min(row groups, 2 x SMs) blocks)
-  const int64_t need = (M + tvi::kLnBwdWarps * tvi::kLnBwdRowsPerWarp - 1) / (tvi::kLnBwdWarps * tvi::kLnBwdRowsPerWarp);
-  return (size_t)(need < 4096 ? need : 4096) * 2 * (size_t)C * sizeof(float);
+  return (size_t)tvi::ln_bwd_ws_blocks(M) * 2 * (size_t)C * sizeof(float);
 }
 
 extern "C" int tvi_layernorm_bwd_bf16(const tvi_bf16* x, const tvi_bf16* dy, const tvi_bf16* gamma, tvi_bf16* dx, tvi_bf16* dgamma,
@@ -534,7 +706,14 @@ extern "C" int tvi_layernorm_bwd_res_bf16(const tvi_bf16* x, const tvi_bf16* dy,
   cudaStream_t st = (cudaStream_t)stream;
   const int C8 = C / 8;
   int rc;
-  if (C8 <= 64)
+  int64_t blocks = ln_bwd_blocks(M);
+  if (C8 == 40)
+    rc = launch_ln_bwd_flat<8>(x, dy, gamma, dres, dx, (float*)workspace, M, ldx, lddy, lddres, lddx, eps, st, &blocks);
+  else if (C8 == 80)
+    rc = launch_ln_bwd_flat<16>(x, dy, gamma, dres, dx, (float*)workspace, M, ldx, lddy, lddres, lddx, eps, st, &blocks);
+  else if (C8 == 160)
+    rc = launch_ln_bwd_flat<32>(x, dy, gamma, dres, dx, (float*)workspace, M, ldx, lddy, lddres, lddx, eps, st, &blocks);
+  else if (C8 <= 64)
     rc = launch_ln_bwd<2>(x, dy, gamma, dres, dx, (float*)workspace, M, C8, ldx, lddy, lddres, lddx, eps, st);
   else if (C8 <= 128)
     rc = launch_ln_bwd<4>(x, dy, gamma, dres, dx, (float*)workspace, M, C8, ldx, lddy, lddres, lddx, eps, st);
@@ -544,7 +723,7 @@ extern "C" int tvi_layernorm_bwd_res_bf16(const tvi_bf16* x, const tvi_bf16* dy,
     rc = launch_ln_bwd<8>(x, dy, gamma, dres, dx, (float*)workspace, M, C8, ldx, lddy, lddres, lddx, eps, st);
   if (rc) return rc;
   if (dgamma != nullptr || dbeta != nullptr) {
-    ln_bwd_final_kernel<<<(2 * C + 255) / 256, 256, 0, st>>>((const float*)workspace, dgamma, dbeta, (int)ln_bwd_blocks(M), C);
+    ln_bwd_final_kernel<<<(2 * C + 255) / 256, 256, 0, st>>>((const float*)workspace, dgamma, dbeta, (int)blocks, C);
     TVI_LAUNCH_OK("ln_bwd_final_kernel");
   }
   return TVI_OK;

@@ -54,5 +54,8 @@ del pre, dh, x, wi, bi
 x, dy, g = rnd(M, 320), rnd(M, 320), rnd(320)
 ms = timed(lambda: ops.layernorm_bwd(x, dy, g, 1e-5))
 print(f"layernorm_bwd (dx, dgamma, dbeta): {ms:.4f} ms  {2.0 * M * 320 * 3 / ms / 1e6:.0f} GB/s")
+dres = rnd(M, 320)
+ms = timed(lambda: ops.layernorm_bwd(x, dy, g, 1e-5, dres=dres))
+print(f"layernorm_bwd (+ dres: dx, dgamma, dbeta): {ms:.4f} ms  {2.0 * M * 320 * 4 / ms / 1e6:.0f} GB/s")
 ms = timed(lambda: ops.layernorm_bwd(x, dy, g, 1e-5, need_affine=False))
 print(f"layernorm_bwd (dx only): {ms:.4f} ms  {2.0 * M * 320 * 3 / ms / 1e6:.0f} GB/s")
