@@ -106,107 +106,74 @@ layernorm_kernel(const tvi_bf16* __restrict__ x, const tvi_bf16* __restrict__ ga
   }
 }
 
-// The three SVD widths (C = 320 / 640 / 1280) as a FLAT chunk array: a warp owns R = 160 / (C / 8) consecutive rows =
-// exactly 160 16-byte chunks = 5 per lane, every lane busy in every iteration (the row-per-warp layout above leaves
-// 24 of 64 lane slots idle at C = 320 and was issue-bound at 3.5 TB/s).  Chunk k = lane + 32 i belongs to row k / C8;
-// per-row sums are formed lane-locally (select by row) and butterfly-reduced for all R rows; packed f32x2 arithmetic.
+// The three SVD widths (C = 320 / 640 / 1280 = 40 G columns, G = 8 / 16 / 32): G lanes share a row, a warp owns R = 32 / G
+// consecutive rows, every lane the five 16-byte chunks (lane % G) + G j of its row — every lane busy in every iteration
+// (the row-per-warp layout above leaves 24 of 64 lane slots idle at C = 320 and was issue-bound at 3.5 TB/s), a warp-level
+// load covers whole 128-byte lines, and the two row reductions are log2(G) shuffles on one value per lane.  (The first
+// version of this kernel dealt chunk lane + 32 i to row (lane + 32 i) / C8: per-row sums then needed a select per chunk
+// and a full butterfly for each of the R rows — 40 shuffles per pass at C = 320 against 6 now.)  Packed f32x2 arithmetic.
 // kStats: write (mean, rstd) of every row to `stats` [M][2] fp32 instead of the normalised rows (the LayerNorm is then
 // applied by the epilogue of the GEMM that consumes the rows, tvi_gemm_bf16_tn_ln): a read-only pass, half the traffic.
 template <int R, bool kStats>
 __global__ void __launch_bounds__(kLnWarps * 32)
 layernorm_flat_kernel(const tvi_bf16* __restrict__ x, const tvi_bf16* __restrict__ gamma, const tvi_bf16* __restrict__ beta,
                       tvi_bf16* __restrict__ y, float2* __restrict__ stats, int64_t M, int64_t ldx, int64_t ldy, float eps) {
-  constexpr int C8 = 160 / R;
+  constexpr int G = 32 / R;
   constexpr int NCH = 5;
   const int lane = threadIdx.x & 31;
+  const int rs = lane / G, lg = lane % G;
   const int64_t row0 = ((int64_t)blockIdx.x * kLnWarps + (threadIdx.x >> 5)) * R;
   if (row0 >= M) return;
+  const int64_t row = row0 + rs;
+  const bool live = row < M;
+  const int64_t rr = live ? row : M - 1;  // tail slots re-read the last row (never stored)
   uint4 raw[NCH];
-  int rw[NCH], col[NCH];
 #pragma unroll
-  for (int i = 0; i < NCH; ++i) {
-    const int k = lane + 32 * i;
-    rw[i] = k / C8;
-    col[i] = k - rw[i] * C8;
-    const int64_t row = row0 + rw[i] < M ? row0 + rw[i] : M - 1;  // tail rows re-read the last row (never stored)
-    raw[i] = __ldg(reinterpret_cast<const uint4*>(x + row * ldx) + col[i]);
-  }
+  for (int i = 0; i < NCH; ++i) raw[i] = __ldg(reinterpret_cast<const uint4*>(x + rr * ldx) + lg + G * i);
   uint64_t v[NCH][4];
-  float part[R];
-#pragma unroll
-  for (int r = 0; r < R; ++r) part[r] = 0.f;
+  uint64_t acc = f32x2_pack(0.f, 0.f);
 #pragma unroll
   for (int i = 0; i < NCH; ++i) {
     const uint32_t w[4] = {raw[i].x, raw[i].y, raw[i].z, raw[i].w};
-    uint64_t acc = f32x2_pack(0.f, 0.f);
 #pragma unroll
     for (int q = 0; q < 4; ++q) {
       v[i][q] = f32x2_pack(__uint_as_float(w[q] << 16), __uint_as_float(w[q] & 0xffff0000u));
       acc = f32x2_add(acc, v[i][q]);
     }
-    float a0, a1;
-    f32x2_unpack(acc, a0, a1);
-    const float s = a0 + a1;
-#pragma unroll
-    for (int r = 0; r < R; ++r) part[r] += (rw[i] == r) ? s : 0.f;
   }
+  float a0, a1;
+  f32x2_unpack(acc, a0, a1);
+  float sum = a0 + a1;
 #pragma unroll
-  for (int o = 16; o > 0; o >>= 1) {
+  for (int o = G / 2; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+  constexpr float inv_c = 1.0f / (float)(40 * G);
+  const float mean = sum * inv_c;
+  const uint64_t nm = f32x2_pack(-mean, -mean);
+  acc = f32x2_pack(0.f, 0.f);
 #pragma unroll
-    for (int r = 0; r < R; ++r) part[r] += __shfl_xor_sync(0xffffffffu, part[r], o);
-  }
-  constexpr float inv_c = 1.0f / (float)(C8 * 8);
-  float negmean[NCH];
-  float mean_r[R];
-#pragma unroll
-  for (int r = 0; r < R; ++r) mean_r[r] = part[r] * inv_c;
-#pragma unroll
-  for (int i = 0; i < NCH; ++i) {
-    float m = part[0];
-#pragma unroll
-    for (int r = 1; r < R; ++r) m = (rw[i] == r) ? part[r] : m;
-    negmean[i] = -m * inv_c;
-  }
-#pragma unroll
-  for (int r = 0; r < R; ++r) part[r] = 0.f;
-#pragma unroll
-  for (int i = 0; i < NCH; ++i) {
-    const uint64_t nm = f32x2_pack(negmean[i], negmean[i]);
-    uint64_t acc = f32x2_pack(0.f, 0.f);
+  for (int i = 0; i < NCH; ++i)
 #pragma unroll
     for (int q = 0; q < 4; ++q) {
       v[i][q] = f32x2_add(v[i][q], nm);  // deviations
       acc = f32x2_fma(v[i][q], v[i][q], acc);
     }
-    float a0, a1;
-    f32x2_unpack(acc, a0, a1);
-    const float s = a0 + a1;
+  f32x2_unpack(acc, a0, a1);
+  float sq = a0 + a1;
 #pragma unroll
-    for (int r = 0; r < R; ++r) part[r] += (rw[i] == r) ? s : 0.f;
-  }
-#pragma unroll
-  for (int o = 16; o > 0; o >>= 1) {
-#pragma unroll
-    for (int r = 0; r < R; ++r) part[r] += __shfl_xor_sync(0xffffffffu, part[r], o);
-  }
-#pragma unroll
-  for (int r = 0; r < R; ++r) part[r] = rsqrtf(part[r] * inv_c + eps);
+  for (int o = G / 2; o > 0; o >>= 1) sq += __shfl_xor_sync(0xffffffffu, sq, o);
+  const float rstd = rsqrtf(sq * inv_c + eps);
   if (kStats) {
-#pragma unroll
-    for (int r = 0; r < R; ++r)
-      if (lane == r && row0 + r < M) stats[row0 + r] = make_float2(mean_r[r], part[r]);
+    if (lg == 0 && live) stats[row] = make_float2(mean, rstd);
     return;
   }
+  const uint64_t rs2 = f32x2_pack(rstd, rstd);
 #pragma unroll
   for (int i = 0; i < NCH; ++i) {
-    float rs = part[0];
-#pragma unroll
-    for (int r = 1; r < R; ++r) rs = (rw[i] == r) ? part[r] : rs;
-    const uint64_t rs2 = f32x2_pack(rs, rs);
+    const int col = lg + G * i;
     uint4 ug = make_uint4(0x3f803f80u, 0x3f803f80u, 0x3f803f80u, 0x3f803f80u);  // bf16 1.0 pairs
     uint4 ub = make_uint4(0u, 0u, 0u, 0u);
-    if (gamma != nullptr) ug = __ldg(reinterpret_cast<const uint4*>(gamma) + col[i]);
-    if (beta != nullptr) ub = __ldg(reinterpret_cast<const uint4*>(beta) + col[i]);
+    if (gamma != nullptr) ug = __ldg(reinterpret_cast<const uint4*>(gamma) + col);
+    if (beta != nullptr) ub = __ldg(reinterpret_cast<const uint4*>(beta) + col);
     const uint32_t wg[4] = {ug.x, ug.y, ug.z, ug.w}, wb[4] = {ub.x, ub.y, ub.z, ub.w};
     uint32_t o[4];
 #pragma unroll
@@ -217,7 +184,7 @@ layernorm_flat_kernel(const tvi_bf16* __restrict__ x, const tvi_bf16* __restrict
       f32x2_unpack(f32x2_fma(f32x2_mul(v[i][q], rs2), g2, b2), lo, hi);
       o[q] = pack_bf16x2(lo, hi);
     }
-    if (row0 + rw[i] < M) *(reinterpret_cast<uint4*>(y + (row0 + rw[i]) * ldy) + col[i]) = make_uint4(o[0], o[1], o[2], o[3]);
+    if (live) *(reinterpret_cast<uint4*>(y + row * ldy) + col) = make_uint4(o[0], o[1], o[2], o[3]);
   }
 }
 
