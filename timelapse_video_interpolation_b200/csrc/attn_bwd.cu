@@ -914,10 +914,12 @@ int launch_fewkeys_bwd(const FkParams& p, int64_t ngroups, int C8, cudaStream_t 
   TVI_CHECK_ARG(C8 * RY <= 256, "tvi_attn_fewkeys_bwd: heads*d = %d is too wide for this kernel", C8 * 8);
   const size_t sm = (size_t)2 * LT * C8 * 8 * sizeof(float) * (RY > 1 ? 1 + RY : 1);  // the sums + every row lane's partials
   TVI_CHECK_ARG(sm <= 200 * 1024, "tvi_attn_fewkeys_bwd: L*heads*d too large for the reduction buffer");
-  static size_t configured = 0;
-  if (sm > 48 * 1024 && sm > configured) {
+  static size_t configured[64] = {0};  // per device: largest dynamic shared memory size opted into so far
+  int dev = 0;
+  TVI_CUDA_OK(cudaGetDevice(&dev));
+  if (sm > 48 * 1024 && (dev < 0 || dev >= 64 || sm > configured[dev])) {
     TVI_CUDA_OK(cudaFuncSetAttribute(attn_fewkeys_bwd_kernel<LT, LPH>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
-    configured = sm;
+    if (dev >= 0 && dev < 64) configured[dev] = sm;
   }
   TVI_CHECK_ARG((int64_t)p.tiles_per_group * ngroups < ((int64_t)1 << 31), "tvi_attn_fewkeys_bwd: grid too large");
   dim3 block((unsigned)C8, (unsigned)RY);

@@ -134,6 +134,9 @@ struct GemmParams {
   int64_t ldp;
   tvi_bf16* dpre;      // kGbwd: [M, 2 * N_store] = [d(value) | d(gate)], row stride lddpre
   int64_t lddpre;
+  tvi_bf16* h_out;     // kGbwd: [M, N_store] = value * gelu(gate), row stride ldh
+  int64_t ldh;
+  int wide_stores;     // kGbwd: all three outputs are 32-byte aligned per row -> 256-bit stores
 };
 
 // kAMn / kBMn: the A / B operand is stored reduction-row-major ("MN-major": the output dimension is the
@@ -144,8 +147,8 @@ struct GemmParams {
 // with the weight slice resident (half of it per CTA: 80 KB at BN = 256, K = 320) only A streams at all.
 // kGbwd (forward TN GEMM with the GEGLU tile layout only): the backward of the fused GEGLU projection.  The accumulator
 // is the recomputed pre-activation [value | gate]; the "residual" stream is dh = d(loss)/d(h); the epilogue writes
-// h = value * gelu(gate) through the staging buffer / TMA store and d(pre) straight from registers (64 contiguous bytes per
-// thread and half, full sectors).  Neither the 2 * inner-wide pre-activation nor a second pass over dh touches HBM.
+// h = value * gelu(gate) and d(pre) = [d value | d gate] straight from registers (64 contiguous bytes per thread and
+// output).  Neither the 2 * inner-wide pre-activation nor a second pass over dh touches HBM.
 template <bool kAMn, bool kBMn, bool kSplit, bool kPair = false, bool kGbwd = false>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CUtensorMap tmW,
@@ -498,43 +501,65 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
         uint8_t* row_ptr = my_staging_ptr + buf * 2048 + lane * 64;
         const int sw = (lane >> 1) & 3;
         if constexpr (kGbwd) {
-          // dh chunk (requested kResAhead chunks ago into this chunk's staging buffer) -> h, d(value), d(gate)
-          if (lane == 0) {
-            tma_store_wait_read<kResStageBufs - kResAhead - 1>();
-            issue_residual();
-          }
+          // dh chunk (requested kResAhead chunks ago into this chunk's staging buffer) -> h, d(value), d(gate), all three
+          // stored straight from registers: 64 contiguous bytes per thread and output (two 32-byte stores when the rows
+          // are 32-byte aligned, else four 16-byte ones).  The staging buffers only ever receive dh, so the epilogue has
+          // no shared-memory stores, no proxy fence and no bulk-store bookkeeping.
+          if (lane == 0) issue_residual();  // into the buffer read two chunks ago (every lane passed a __syncwarp since)
           mbar_wait(&my_res_bar[buf], (qn / kResStageBufs) & 1);
           ++qn;
           const float* gate_bias = my_bias + (out_chunks + c) * 32;
           const int64_t row = (int64_t)m0 + quad * 32 + lane;
+          tvi_bf16* h_dst = p.h_out + row * p.ldh + ncol0;
           tvi_bf16* dv_dst = p.dpre + row * p.lddpre + ncol0;
           tvi_bf16* dg_dst = dv_dst + p.N_store;
+          uint4 oh[4], ov[4], og[4];
 #pragma unroll
           for (int ch = 0; ch < 4; ++ch) {
             const uint4 u = *reinterpret_cast<const uint4*>(row_ptr + ((ch ^ sw) << 4));
-            const __nv_bfloat162* h2 = reinterpret_cast<const __nv_bfloat162*>(&u);
-            uint32_t ov[4], og[4];
+            const uint32_t wd[4] = {u.x, u.y, u.z, u.w};
+            uint32_t th[4], tv[4], tg[4];
 #pragma unroll
             for (int q = 0; q < 4; ++q) {
               const int j = ch * 8 + 2 * q;
-              const float2 d2 = __bfloat1622float2(h2[q]);
+              const uint64_t d2 = f32x2_pack(__uint_as_float(wd[q] << 16), __uint_as_float(wd[q] & 0xffff0000u));
               float2 gb = make_float2(0.f, 0.f);
               if (p.bias != nullptr) gb = *reinterpret_cast<const float2*>(gate_bias + j);
               const uint64_t g2 = f32x2_add(f32x2_pack(__uint_as_float(rg[j]), __uint_as_float(rg[j + 1])), f32x2_pack(gb.x, gb.y));
               uint64_t hh, dv, dg;
-              geglu_bwd_x2(f32x2_pack(f[j], f[j + 1]), g2, f32x2_pack(d2.x, d2.y), hh, dv, dg);
-              f32x2_unpack(hh, f[j], f[j + 1]);
+              geglu_bwd_x2(f32x2_pack(f[j], f[j + 1]), g2, d2, hh, dv, dg);
               float a, b;
+              f32x2_unpack(hh, a, b);
+              th[q] = pack_bf16x2(a, b);
               f32x2_unpack(dv, a, b);
-              ov[q] = pack_bf16x2(a, b);
+              tv[q] = pack_bf16x2(a, b);
               f32x2_unpack(dg, a, b);
-              og[q] = pack_bf16x2(a, b);
+              tg[q] = pack_bf16x2(a, b);
             }
-            if (row < p.M_out) {
-              *reinterpret_cast<uint4*>(dv_dst + ch * 8) = make_uint4(ov[0], ov[1], ov[2], ov[3]);
-              *reinterpret_cast<uint4*>(dg_dst + ch * 8) = make_uint4(og[0], og[1], og[2], og[3]);
+            oh[ch] = make_uint4(th[0], th[1], th[2], th[3]);
+            ov[ch] = make_uint4(tv[0], tv[1], tv[2], tv[3]);
+            og[ch] = make_uint4(tg[0], tg[1], tg[2], tg[3]);
+          }
+          if (row < p.M_out) {
+            if (p.wide_stores) {
+              st_global_256(h_dst, oh[0], oh[1]);
+              st_global_256(h_dst + 16, oh[2], oh[3]);
+              st_global_256(dv_dst, ov[0], ov[1]);
+              st_global_256(dv_dst + 16, ov[2], ov[3]);
+              st_global_256(dg_dst, og[0], og[1]);
+              st_global_256(dg_dst + 16, og[2], og[3]);
+            } else {
+#pragma unroll
+              for (int ch = 0; ch < 4; ++ch) {
+                *reinterpret_cast<uint4*>(h_dst + ch * 8) = oh[ch];
+                *reinterpret_cast<uint4*>(dv_dst + ch * 8) = ov[ch];
+                *reinterpret_cast<uint4*>(dg_dst + ch * 8) = og[ch];
+              }
             }
           }
+          __syncwarp();  // every lane has read its dh row: the buffer may be re-armed (two chunks from now)
+          buf = (buf + 1 == nbufs) ? 0 : buf + 1;
+          continue;
         } else if (has_res) {
           // buffer (qn + 2) % 4 was last read by the store of chunk qn - 2: all but the latest store have drained
           if (lane == 0) {
@@ -558,6 +583,9 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
           // staging buffer `buf` was last read by the TMA store issued kStageBufs chunks ago
           if (lane == 0) tma_store_wait_read<kStageBufs - 1>();
         }
+        // (Storing the 32 columns straight from registers with two 256-bit st.global per thread instead of this staging +
+        // TMA-store path was measured slower on every forward shape: ff_in + GEGLU 0.453 -> 0.491 ms, plain N = 2 560
+        // 0.469 -> 0.505 ms, out-projection 0.070 -> 0.076 ms — a warp-level row-scattered store costs 32 LSU transactions.)
         __syncwarp();
 #pragma unroll
         for (int ch = 0; ch < 4; ++ch) {
@@ -686,6 +714,10 @@ int launch_gemm(const char* name, const tvi_bf16* A, const tvi_bf16* B, const tv
   GemmParams p;
   p.dpre = dpre;
   p.lddpre = lddpre;
+  p.h_out = Y;
+  p.ldh = ldy;
+  p.wide_stores = (kGbwd && ((uintptr_t)Y | (uintptr_t)dpre) % 32 == 0 && ldy % 16 == 0 && lddpre % 16 == 0 && geglu_block > 0 &&
+                   (No / 2) % 16 == 0) ? 1 : 0;
   p.ln_stats = reinterpret_cast<const float2*>(ln_stats);
   p.ln_colsum = ln_colsum;
   p.BN = kBMn ? pick_bn_mn(No, kAMn) : pick_bn(No, 32);

@@ -498,6 +498,12 @@ __device__ __forceinline__ uint64_t exp2_poly_x2(uint64_t x) {
   return f32x2_pack(r0, r1);
 }
 
+// 256-bit global store (STG.E.ENL2.256): one full 32-byte sector per thread; `p` must be 32-byte aligned
+__device__ __forceinline__ void st_global_256(void* p, const uint4& a, const uint4& b) {
+  asm volatile("st.global.v8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"l"(p), "r"(a.x), "r"(a.y), "r"(a.z), "r"(a.w), "r"(b.x),
+               "r"(b.y), "r"(b.z), "r"(b.w)
+               : "memory");
+}
 __device__ __forceinline__ void cp_async_16(void* smem, const void* gmem, bool pred) {
   const int sz = pred ? 16 : 0;
   asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(smem_u32(smem)), "l"(gmem), "r"(sz)
