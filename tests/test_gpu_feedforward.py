@@ -84,6 +84,27 @@ def test_layer_norm_matches_oracle(cuda, rows, C):
     assert err <= 2 ** -7 * max(1.0, float(ref.abs().max()))  # one bf16 rounding of the result
 
 
+@pytest.mark.parametrize("rows,C", [(1003, 320), (3, 320), (1, 320), (4033, 640), (1, 640), (5, 1280)])
+def test_layer_norm_row_tails_and_strided_rows(cuda, rows, C):
+    """The row-group kernels of the SVD widths (32 / G rows per warp): row counts that leave a partly filled warp, and rows
+    that are column slices of wider buffers (ldx, ldy > C); the padding columns of the output stay untouched."""
+    g = torch.Generator(device="cuda").manual_seed(rows * 7 + C)
+    xb = (torch.randn(rows, C + 64, generator=g, device=cuda) * 2 + 1).to(torch.bfloat16)
+    yb = torch.full((rows, C + 32), 7.0, device=cuda, dtype=torch.bfloat16)
+    gamma = (1 + 0.1 * torch.randn(C, generator=g, device=cuda)).to(torch.bfloat16)
+    beta = (0.1 * torch.randn(C, generator=g, device=cuda)).to(torch.bfloat16)
+    x = xb[:, 32:32 + C]
+    ops.layernorm_bf16(x, gamma, beta, 1e-5, out=yb[:, :C])
+    ref = torch.nn.functional.layer_norm(x.float(), (C,), gamma.float(), beta.float(), 1e-5)
+    assert float((yb[:, :C].float() - ref).abs().max()) <= 2 ** -7 * max(1.0, float(ref.abs().max()))
+    assert bool((yb[:, C:] == 7.0).all())
+    stats = ops.layernorm_stats(x, 1e-5)
+    xf = x.float()
+    assert float((stats[:, 0] - xf.mean(-1)).abs().max()) <= 1e-4 * max(1.0, float(xf.abs().max()))
+    rstd = (xf.var(-1, unbiased=False) + 1e-5).rsqrt()
+    assert float(((stats[:, 1] - rstd) / rstd).abs().max()) <= 1e-4
+
+
 def test_gemm_residual_epilogue(cuda):
     g = torch.Generator().manual_seed(11)
     M, N, K = 1000, 320, 1280
