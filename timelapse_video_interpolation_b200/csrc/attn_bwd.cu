@@ -646,22 +646,31 @@ __global__ void __launch_bounds__(256) attn_fewkeys_bwd_kernel(const FkParams p)
     // ncu capture of the un-pipelined loop had 32 % of its stall cycles on the global loads at 3 CTAs / SM).
     constexpr int kU = 2;
     constexpr int kGroups = kFewBwdRowsPerThread / kU;
+    // Row addressing without per-row 64-bit arithmetic (the first version spent ~45 % of its instructions on phys(), the
+    // tail clamp and the bias index): this thread's rows are rlo + ry + it * RY, a constant pointer step apart.
+    const int nrows_tile = (int)(rhi - rlo);                       // <= RY * kFewBwdRowsPerThread
+    const int ry0 = ry < nrows_tile ? ry : 0;                      // a row lane without rows re-reads row 0 (never stored)
+    const int64_t prow0 = phys(rlo + ry0);
+    const int64_t pstep = (int64_t)RY * (p.inner == 1 ? 1 : p.inner);  // physical rows between two rows of this thread
+    const tvi_bf16* q_base = p.q + prow0 * p.ldq + cx * 8;
+    const tvi_bf16* g_base = p.dout + prow0 * p.lddo + cx * 8;
+    tvi_bf16* dq_base = p.dq != nullptr ? p.dq + prow0 * p.lddq + cx * 8 : nullptr;
+    const int64_t q_step = pstep * p.ldq, g_step = pstep * p.lddo, dq_step = pstep * p.lddq;
+    const int tq = p.Tq;
+    const int t_first = p.bias != nullptr ? (int)((rlo + ry0) % tq) : 0, t_step = RY % tq;
     auto load_group = [&](int it0, uint4* qv, uint4* gv) {
 #pragma unroll
       for (int u = 0; u < kU; ++u) {
-        const int64_t rr = rlo + (int64_t)(it0 + u) * RY + ry;
-        const int64_t r = rr < rhi ? rr : rlo;
-        qv[u] = __ldg(reinterpret_cast<const uint4*>(p.q + phys(r) * p.ldq + cx * 8));
-        gv[u] = __ldg(reinterpret_cast<const uint4*>(p.dout + phys(r) * p.lddo + cx * 8));
+        const int it = (it0 + u) * RY + ry < nrows_tile ? it0 + u : 0;  // rows past the tile re-read the thread's first row
+        qv[u] = __ldg(reinterpret_cast<const uint4*>(q_base + it * q_step));
+        gv[u] = __ldg(reinterpret_cast<const uint4*>(g_base + it * g_step));
       }
     };
     auto compute_group = [&](int it0, const uint4* qv, const uint4* gv) {
 #pragma unroll
       for (int u = 0; u < kU; ++u) {
-        if (rlo + (int64_t)(it0 + u) * RY >= rhi) break;  // block-uniform
-        const int64_t rr = rlo + (int64_t)(it0 + u) * RY + ry;
-        const bool act = rr < rhi;
-        const int64_t r = act ? rr : rlo;
+        if ((it0 + u) * RY >= nrows_tile) break;  // block-uniform
+        const bool act = (it0 + u) * RY + ry < nrows_tile;
         uint64_t qp[4], gp[4];
         unpack_pairs(qv[u], qp);
         unpack_pairs(gv[u], gp);
@@ -683,7 +692,7 @@ __global__ void __launch_bounds__(256) attn_fewkeys_bwd_kernel(const FkParams p)
         }
         z *= p.scale;
         if (p.bias != nullptr) {
-          const int t = (int)(r % p.Tq);
+          const int t = (t_first + (it0 + u) * t_step) % tq;  // (rlo + ry + it * RY) mod Tq in 32-bit arithmetic
           z += __ldg(p.bias + t * 2) - __ldg(p.bias + t * 2 + 1);
         }
         float w = __fdividef(1.f, 1.f + __expf(-z));
@@ -697,7 +706,7 @@ __global__ void __launch_bounds__(256) attn_fewkeys_bwd_kernel(const FkParams p)
           dv0[i] = f32x2_fma(w2, gp[i], dv0[i]);
           dv1[i] = f32x2_fma(w12, gp[i], dv1[i]);
         }
-        if (act && p.dq != nullptr) {
+        if (act && dq_base != nullptr) {
           uint32_t o[4];
 #pragma unroll
           for (int i = 0; i < 4; ++i) {
@@ -705,17 +714,17 @@ __global__ void __launch_bounds__(256) attn_fewkeys_bwd_kernel(const FkParams p)
             f32x2_unpack(f32x2_mul(ds2, kd2[i]), a, b);
             o[i] = pack_bf16x2(a, b);
           }
-          *reinterpret_cast<uint4*>(p.dq + phys(r) * p.lddq + cx * 8) = make_uint4(o[0], o[1], o[2], o[3]);
+          *reinterpret_cast<uint4*>(dq_base + (it0 + u) * dq_step) = make_uint4(o[0], o[1], o[2], o[3]);
         }
       }
     };
     uint4 qa[kU], ga[kU], qb[kU], gb2[kU];
     load_group(0, qa, ga);
     for (int gi = 0; gi < kGroups; gi += 2) {  // ping-pong buffers: no register copies
-      if (rlo + (int64_t)(gi * kU) * RY >= rhi) break;  // block-uniform
+      if (gi * kU * RY >= nrows_tile) break;  // block-uniform
       load_group((gi + 1) * kU, qb, gb2);
       compute_group(gi * kU, qa, ga);
-      if (rlo + (int64_t)((gi + 1) * kU) * RY >= rhi) break;
+      if ((gi + 1) * kU * RY >= nrows_tile) break;
       if (gi + 2 < kGroups) load_group((gi + 2) * kU, qa, ga);
       compute_group((gi + 1) * kU, qb, gb2);
     }
