@@ -580,6 +580,7 @@ __device__ __forceinline__ void unpack8b(const uint4& u, float* f) {
 }
 
 constexpr int kFewBwdRowsPerThread = 32;
+constexpr int kFkDepth = 6;  // two-key kernel: rows in flight per thread (16-byte q and dO chunks in a shared-memory FIFO)
 
 struct FkParams {
   const tvi_bf16 *q, *k, *v, *dout;
@@ -642,92 +643,99 @@ __global__ void __launch_bounds__(256) attn_fewkeys_bwd_kernel(const FkParams p)
 #pragma unroll
       for (int i = 0; i < 4; ++i) o[i] = f32x2_pack(__uint_as_float(w[i] << 16), __uint_as_float(w[i] & 0xffff0000u));
     };
-    // Software pipeline over groups of kU rows: the loads of group g + 1 are in flight while group g is computed (the
-    // ncu capture of the un-pipelined loop had 32 % of its stall cycles on the global loads at 3 CTAs / SM).
-    constexpr int kU = 2;
-    constexpr int kGroups = kFewBwdRowsPerThread / kU;
-    // Row addressing without per-row 64-bit arithmetic (the first version spent ~45 % of its instructions on phys(), the
-    // tail clamp and the bias index): this thread's rows are rlo + ry + it * RY, a constant pointer step apart.
+    // Rows stream through a per-thread FIFO in shared memory (cp.async, kFkDepth rows ahead of the arithmetic; a thread
+    // only reads back the 16-byte chunks it copied itself, so no barrier is involved).  The register ping-pong it replaces
+    // kept ONE group of two rows in flight per thread — ~900 cycles of arithmetic against a longer DRAM latency under load:
+    // the ncu capture had a third of all stall samples on the first use of the loaded registers.
+    // Row addressing without per-row 64-bit arithmetic: this thread's rows are rlo + ry + it * RY, a constant pointer
+    // step apart (the first version spent ~45 % of its instructions on phys(), the tail clamp and the bias index).
     const int nrows_tile = (int)(rhi - rlo);                       // <= RY * kFewBwdRowsPerThread
-    const int ry0 = ry < nrows_tile ? ry : 0;                      // a row lane without rows re-reads row 0 (never stored)
+    const int nit = (nrows_tile + RY - 1) / RY;                    // block-uniform
+    const int ry0 = ry < nrows_tile ? ry : 0;
     const int64_t prow0 = phys(rlo + ry0);
     const int64_t pstep = (int64_t)RY * (p.inner == 1 ? 1 : p.inner);  // physical rows between two rows of this thread
-    const tvi_bf16* q_base = p.q + prow0 * p.ldq + cx * 8;
-    const tvi_bf16* g_base = p.dout + prow0 * p.lddo + cx * 8;
-    tvi_bf16* dq_base = p.dq != nullptr ? p.dq + prow0 * p.lddq + cx * 8 : nullptr;
+    const tvi_bf16* q_ptr = p.q + prow0 * p.ldq + cx * 8;          // row of the next FIFO request
+    const tvi_bf16* g_ptr = p.dout + prow0 * p.lddo + cx * 8;
+    tvi_bf16* dq_ptr = p.dq != nullptr ? p.dq + prow0 * p.lddq + cx * 8 : nullptr;  // row being computed
     const int64_t q_step = pstep * p.ldq, g_step = pstep * p.lddo, dq_step = pstep * p.lddq;
     const int tq = p.Tq;
-    const int t_first = p.bias != nullptr ? (int)((rlo + ry0) % tq) : 0, t_step = RY % tq;
-    auto load_group = [&](int it0, uint4* qv, uint4* gv) {
-#pragma unroll
-      for (int u = 0; u < kU; ++u) {
-        const int it = (it0 + u) * RY + ry < nrows_tile ? it0 + u : 0;  // rows past the tile re-read the thread's first row
-        qv[u] = __ldg(reinterpret_cast<const uint4*>(q_base + it * q_step));
-        gv[u] = __ldg(reinterpret_cast<const uint4*>(g_base + it * g_step));
+    int t_row = p.bias != nullptr ? (int)((rlo + ry) % tq) : 0;
+    const int t_step = RY % tq;
+    const int nthreads = blockDim.x * RY, tid = ry * blockDim.x + cx;
+    // [kFkDepth][2][nthreads], in the space the row lanes' partial sums take after the loop
+    uint4* fifo = reinterpret_cast<uint4*>(s_red + (size_t)2 * LT * C) + tid;
+    auto request = [&](int it) {  // always one commit group, so the wait below counts rows
+      if (it * RY + ry < nrows_tile) {
+        uint4* dst = fifo + (size_t)(it % kFkDepth) * 2 * nthreads;
+        cp_async_16(dst, q_ptr, true);
+        cp_async_16(dst + nthreads, g_ptr, true);
+        q_ptr += q_step;
+        g_ptr += g_step;
       }
+      cp_async_commit();
     };
-    auto compute_group = [&](int it0, const uint4* qv, const uint4* gv) {
 #pragma unroll
-      for (int u = 0; u < kU; ++u) {
-        if ((it0 + u) * RY >= nrows_tile) break;  // block-uniform
-        const bool act = (it0 + u) * RY + ry < nrows_tile;
-        uint64_t qp[4], gp[4];
-        unpack_pairs(qv[u], qp);
-        unpack_pairs(gv[u], gp);
-        uint64_t z2 = f32x2_mul(qp[0], kd2[0]), g2 = f32x2_mul(gp[0], vd2[0]);
+    for (int it = 0; it < kFkDepth; ++it) request(it);
+    for (int it = 0; it < nit; ++it) {
+      cp_async_wait<kFkDepth - 1>();
+      const bool act = it * RY + ry < nrows_tile;
+      const uint4* src = fifo + (size_t)(it % kFkDepth) * 2 * nthreads;
+      uint4 qv = make_uint4(0u, 0u, 0u, 0u), gv = qv;  // a row lane past the tile computes on zeros: contributes nothing
+      if (act) {
+        qv = src[0];
+        gv = src[nthreads];
+      }
+      uint64_t qp[4], gp[4];
+      unpack_pairs(qv, qp);
+      unpack_pairs(gv, gp);
+      request(it + kFkDepth);  // the slot's values are in registers
+      uint64_t z2 = f32x2_mul(qp[0], kd2[0]), g2 = f32x2_mul(gp[0], vd2[0]);
 #pragma unroll
-        for (int i = 1; i < 4; ++i) {
-          z2 = f32x2_fma(qp[i], kd2[i], z2);
-          g2 = f32x2_fma(gp[i], vd2[i], g2);
-        }
-        float z, zb, g, gb;
-        f32x2_unpack(z2, z, zb);
-        f32x2_unpack(g2, g, gb);
-        z += zb;
-        g += gb;
+      for (int i = 1; i < 4; ++i) {
+        z2 = f32x2_fma(qp[i], kd2[i], z2);
+        g2 = f32x2_fma(gp[i], vd2[i], g2);
+      }
+      float z, zb, g, gb;
+      f32x2_unpack(z2, z, zb);
+      f32x2_unpack(g2, g, gb);
+      z += zb;
+      g += gb;
 #pragma unroll
-        for (int off = LPH / 2; off > 0; off >>= 1) {
-          z += __shfl_xor_sync(0xffffffffu, z, off);
-          g += __shfl_xor_sync(0xffffffffu, g, off);
-        }
-        z *= p.scale;
-        if (p.bias != nullptr) {
-          const int t = (t_first + (it0 + u) * t_step) % tq;  // (rlo + ry + it * RY) mod Tq in 32-bit arithmetic
-          z += __ldg(p.bias + t * 2) - __ldg(p.bias + t * 2 + 1);
-        }
-        float w = __fdividef(1.f, 1.f + __expf(-z));
-        float w1 = 1.f - w;
-        if (!act) w = w1 = 0.f;  // inactive rows contribute nothing
-        const float ds = w * w1 * g * p.scale;
-        const uint64_t ds2 = f32x2_pack(ds, ds), w2 = f32x2_pack(w, w), w12 = f32x2_pack(w1, w1);
+      for (int off = LPH / 2; off > 0; off >>= 1) {
+        z += __shfl_xor_sync(0xffffffffu, z, off);
+        g += __shfl_xor_sync(0xffffffffu, g, off);
+      }
+      z *= p.scale;
+      if (p.bias != nullptr) {
+        z += __ldg(p.bias + t_row * 2) - __ldg(p.bias + t_row * 2 + 1);
+        t_row += t_step;  // (rlo + ry + it * RY) mod Tq without a division
+        if (t_row >= tq) t_row -= tq;
+      }
+      float w = __fdividef(1.f, 1.f + __expf(-z));
+      float w1 = 1.f - w;
+      if (!act) w = w1 = 0.f;
+      const float ds = w * w1 * g * p.scale;
+      const uint64_t ds2 = f32x2_pack(ds, ds), w2 = f32x2_pack(w, w), w12 = f32x2_pack(w1, w1);
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        dk2[i] = f32x2_fma(ds2, qp[i], dk2[i]);
+        dv0[i] = f32x2_fma(w2, gp[i], dv0[i]);
+        dv1[i] = f32x2_fma(w12, gp[i], dv1[i]);
+      }
+      if (act && dq_ptr != nullptr) {
+        uint32_t o[4];
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
-          dk2[i] = f32x2_fma(ds2, qp[i], dk2[i]);
-          dv0[i] = f32x2_fma(w2, gp[i], dv0[i]);
-          dv1[i] = f32x2_fma(w12, gp[i], dv1[i]);
+          float a, b;
+          f32x2_unpack(f32x2_mul(ds2, kd2[i]), a, b);
+          o[i] = pack_bf16x2(a, b);
         }
-        if (act && dq_base != nullptr) {
-          uint32_t o[4];
-#pragma unroll
-          for (int i = 0; i < 4; ++i) {
-            float a, b;
-            f32x2_unpack(f32x2_mul(ds2, kd2[i]), a, b);
-            o[i] = pack_bf16x2(a, b);
-          }
-          *reinterpret_cast<uint4*>(dq_base + (it0 + u) * dq_step) = make_uint4(o[0], o[1], o[2], o[3]);
-        }
+        *reinterpret_cast<uint4*>(dq_ptr) = make_uint4(o[0], o[1], o[2], o[3]);
+        dq_ptr += dq_step;
       }
-    };
-    uint4 qa[kU], ga[kU], qb[kU], gb2[kU];
-    load_group(0, qa, ga);
-    for (int gi = 0; gi < kGroups; gi += 2) {  // ping-pong buffers: no register copies
-      if (gi * kU * RY >= nrows_tile) break;  // block-uniform
-      load_group((gi + 1) * kU, qb, gb2);
-      compute_group(gi * kU, qa, ga);
-      if ((gi + 1) * kU * RY >= nrows_tile) break;
-      if (gi + 2 < kGroups) load_group((gi + 2) * kU, qa, ga);
-      compute_group((gi + 1) * kU, qb, gb2);
     }
+    cp_async_wait<0>();
+    if (RY > 1) __syncthreads();  // every thread is done with its FIFO slots: the space becomes s_part below
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
       f32x2_unpack(dk2[i], dk[0][2 * i], dk[0][2 * i + 1]);
@@ -921,7 +929,12 @@ template <int LT, int LPH>
 int launch_fewkeys_bwd(const FkParams& p, int64_t ngroups, int C8, cudaStream_t st) {
   const int RY = fk_block_rows(C8);
   TVI_CHECK_ARG(C8 * RY <= 256, "tvi_attn_fewkeys_bwd: heads*d = %d is too wide for this kernel", C8 * 8);
-  const size_t sm = (size_t)2 * LT * C8 * 8 * sizeof(float) * (RY > 1 ? 1 + RY : 1);  // the sums + every row lane's partials
+  const size_t sums = (size_t)2 * LT * C8 * 8 * sizeof(float);
+  size_t sm = sums * (RY > 1 ? 1 + RY : 1);  // the sums + every row lane's partials
+  if (LT == 2) {                              // the two-key kernel's row FIFO shares the partials' space
+    const size_t fifo = (size_t)kFkDepth * 2 * C8 * RY * 16;
+    if (sums + fifo > sm) sm = sums + fifo;
+  }
   TVI_CHECK_ARG(sm <= 200 * 1024, "tvi_attn_fewkeys_bwd: L*heads*d too large for the reduction buffer");
   static size_t configured[64] = {0};  // per device: largest dynamic shared memory size opted into so far
   int dev = 0;
