@@ -42,7 +42,10 @@ constexpr int kABytes = kBM * kBK * 2;             // 16 KB
 // chain (~640 clk per 32-column chunk measured, linear in BN: the epilogue, not the MMAs, set the tile time), so the
 // latency is hidden ACROSS warps instead: 8 warps x 1 buffer use the shared memory of 4 warps x 2 buffers and took the
 // N = 2560 / K = 320 GEMM from 0.52 to 0.45 ms, out-projection + residual from 0.175 to 0.105 ms, QKV unchanged (0.158).
-constexpr int kStageBufs = 1;
+#ifndef TVI_GEMM_STAGE_BUFS
+#define TVI_GEMM_STAGE_BUFS 1
+#endif
+constexpr int kStageBufs = TVI_GEMM_STAGE_BUFS;
 #ifndef TVI_GEMM_RES_BUFS
 #define TVI_GEMM_RES_BUFS 4
 #endif
