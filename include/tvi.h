@@ -154,7 +154,8 @@ int tvi_geglu_bwd_bf16(const tvi_bf16* pre, const tvi_bf16* dh, tvi_bf16* h, tvi
  * [M, 2*inner] (lddpre, in the un-interleaved [value | gate] column order of the module's weight).  X [M, K] (ldx);
  * Wi / bias_i are the weight [2*inner, K] (ldw) and bias (nullable) with value / gate rows interleaved in blocks of
  * tvi_geglu_block(inner), as tvi_gemm_bf16_tn_ex(..., TVI_EPILOGUE_GEGLU) takes them; dH [M, inner] (lddh) is the gradient
- * that reached H.  The 2*inner-wide pre-activation is never written.  inner % 32 == 0, K % 8 == 0. */
+ * that reached H.  H may be NULL (a frozen second projection needs no h).  The 2*inner-wide pre-activation is never
+ * written.  inner % 32 == 0, K % 8 == 0. */
 int tvi_gemm_bf16_geglu_bwd(const tvi_bf16* X, const tvi_bf16* Wi, const tvi_bf16* bias_i, const tvi_bf16* dH, tvi_bf16* H,
                             tvi_bf16* dPre, int64_t M, int inner, int K, int64_t ldx, int64_t ldw, int64_t lddh, int64_t ldh,
                             int64_t lddpre, void* stream);

@@ -361,6 +361,9 @@ def test_gemm_geglu_bwd_matches_fp32_reference(cuda, M, K, inner, bias):
     # the forward's fused GEGLU GEMM computes the same h from the same accumulator
     h_fwd = ops.gemm_bf16_tn_ex(x, wi, bi, geglu=True)
     assert torch.equal(h_fwd, h)
+    # without the h output (a frozen second projection): the same d(pre), nothing else written
+    h3, dpre3 = ops.gemm_geglu_bwd(x, wi, bi, dh, need_h=False)
+    assert h3 is None and torch.equal(dpre3, dpre)
     # the path it replaces (bf16-rounded pre-activation, erff): same numbers to bf16 rounding
     h2, dpre2 = ops.geglu_bwd(ops.gemm_bf16_tn(x, w, b), dh)
     assert (dpre.float() - dpre2.float()).abs().max().item() <= tol_d

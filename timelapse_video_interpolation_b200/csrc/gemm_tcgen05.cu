@@ -545,8 +545,10 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
           }
           if (row < p.M_out) {
             if (p.wide_stores) {
-              st_global_256(h_dst, oh[0], oh[1]);
-              st_global_256(h_dst + 16, oh[2], oh[3]);
+              if (p.h_out != nullptr) {
+                st_global_256(h_dst, oh[0], oh[1]);
+                st_global_256(h_dst + 16, oh[2], oh[3]);
+              }
               st_global_256(dv_dst, ov[0], ov[1]);
               st_global_256(dv_dst + 16, ov[2], ov[3]);
               st_global_256(dg_dst, og[0], og[1]);
@@ -554,7 +556,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
             } else {
 #pragma unroll
               for (int ch = 0; ch < 4; ++ch) {
-                *reinterpret_cast<uint4*>(h_dst + ch * 8) = oh[ch];
+                if (p.h_out != nullptr) *reinterpret_cast<uint4*>(h_dst + ch * 8) = oh[ch];
                 *reinterpret_cast<uint4*>(dv_dst + ch * 8) = ov[ch];
                 *reinterpret_cast<uint4*>(dg_dst + ch * 8) = og[ch];
               }
@@ -719,7 +721,7 @@ int launch_gemm(const char* name, const tvi_bf16* A, const tvi_bf16* B, const tv
   p.lddpre = lddpre;
   p.h_out = Y;
   p.ldh = ldy;
-  p.wide_stores = (kGbwd && ((uintptr_t)Y | (uintptr_t)dpre) % 32 == 0 && ldy % 16 == 0 && lddpre % 16 == 0 && geglu_block > 0 &&
+  p.wide_stores = (kGbwd && ((uintptr_t)Y | (uintptr_t)dpre) % 32 == 0 && (Y == nullptr || ldy % 16 == 0) && lddpre % 16 == 0 && geglu_block > 0 &&
                    (No / 2) % 16 == 0) ? 1 : 0;
   p.ln_stats = reinterpret_cast<const float2*>(ln_stats);
   p.ln_colsum = ln_colsum;
@@ -769,9 +771,11 @@ int launch_gemm(const char* name, const tvi_bf16* A, const tvi_bf16* B, const tv
   if (rc) return rc;
   if (!kSplit) {
     const uint64_t dims[2] = {(uint64_t)p.N_store, (uint64_t)Mo};
-    const uint64_t strides[1] = {(uint64_t)ldy * 2};
+    // kGbwd stores from registers and never uses the output map: without an H output it is built over dH instead
+    const bool no_y = kGbwd && Y == nullptr;
+    const uint64_t strides[1] = {(uint64_t)(no_y ? ldr : ldy) * 2};
     const uint32_t box[2] = {32u, 32u};
-    rc = make_tensor_map(&tmY, Y, 2, 2, dims, strides, box, Swizzle::B64);
+    rc = make_tensor_map(&tmY, no_y ? residual : Y, 2, 2, dims, strides, box, Swizzle::B64);
     if (rc) return rc;
     tmR = tmY;
     if (residual != nullptr) {
@@ -952,13 +956,13 @@ extern "C" int tvi_gemm_bf16_geglu_bwd(const tvi_bf16* X, const tvi_bf16* Wi, co
   using namespace tvi;
   TVI_CHECK_ARG(M >= 0 && inner >= 0 && K >= 0, "tvi_gemm_bf16_geglu_bwd: negative size");
   if (M == 0 || inner == 0) return TVI_OK;
-  TVI_CHECK_ARG(X && Wi && dH && H && dPre, "tvi_gemm_bf16_geglu_bwd: null pointer");
+  TVI_CHECK_ARG(X && Wi && dH && dPre, "tvi_gemm_bf16_geglu_bwd: null pointer");
   TVI_CHECK_ARG(K > 0 && K % 8 == 0, "tvi_gemm_bf16_geglu_bwd: K=%d must be a positive multiple of 8", K);
   const int block = tvi_geglu_block(inner);
   TVI_CHECK_ARG(block > 0, "tvi_gemm_bf16_geglu_bwd: GEGLU inner width %d must be a multiple of 32", inner);
-  TVI_CHECK_ARG(ldx % 8 == 0 && ldw % 8 == 0 && lddh % 8 == 0 && ldh % 8 == 0 && lddpre % 8 == 0,
+  TVI_CHECK_ARG(ldx % 8 == 0 && ldw % 8 == 0 && lddh % 8 == 0 && (H == nullptr || ldh % 8 == 0) && lddpre % 8 == 0,
                 "tvi_gemm_bf16_geglu_bwd: row strides must be multiples of 8 elements");
-  TVI_CHECK_ARG(ldx >= K && ldw >= K && lddh >= inner && ldh >= inner && lddpre >= 2 * (int64_t)inner,
+  TVI_CHECK_ARG(ldx >= K && ldw >= K && lddh >= inner && (H == nullptr || ldh >= inner) && lddpre >= 2 * (int64_t)inner,
                 "tvi_gemm_bf16_geglu_bwd: row stride smaller than the row");
   TVI_CHECK_ARG(((uintptr_t)X | (uintptr_t)Wi | (uintptr_t)dH | (uintptr_t)H | (uintptr_t)dPre) % 16 == 0,
                 "tvi_gemm_bf16_geglu_bwd: X, Wi, dH, H, dPre must be 16-byte aligned");

@@ -107,7 +107,7 @@ class _FeedForwardFn(torch.autograd.Function):
         w1b, w2b = _bf16(w1), _bf16(w2)
         dh = ops.gemm_bf16_dgrad(dy2, w2b)                               # [M, inner]
         # the first projection again, its fp32 accumulator turned into h and d(pre) in the epilogue (never written itself)
-        h, dpre = ops.gemm_geglu_bwd(x2, ctx.wi, ctx.bi, dh)
+        h, dpre = ops.gemm_geglu_bwd(x2, ctx.wi, ctx.bi, dh, need_h=need_w2)
         dw2 = ops.gemm_bf16_wgrad(dy2, h) if need_w2 else None
         db2 = ops.colsum_bf16(dy2, dy2.shape[0]).view(-1) if (need_b2 and b2 is not None) else None
         dw1 = ops.gemm_bf16_wgrad(dpre, x2) if need_w1 else None

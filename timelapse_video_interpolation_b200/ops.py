@@ -388,10 +388,10 @@ def geglu_bwd(pre: torch.Tensor, dh: torch.Tensor, need_h: bool = True):
     return h, dpre
 
 
-def gemm_geglu_bwd(x: torch.Tensor, wi: torch.Tensor, bias_i: torch.Tensor | None, dh: torch.Tensor):
+def gemm_geglu_bwd(x: torch.Tensor, wi: torch.Tensor, bias_i: torch.Tensor | None, dh: torch.Tensor, need_h: bool = True):
     """Backward of the fused GEGLU projection in one GEMM: x [M, K], wi [2*inner, K] / bias_i with value / gate rows
     interleaved in blocks of `geglu_block(inner)` (as `gemm_bf16_tn_ex(..., geglu=True)` takes them), dh [M, inner] ->
-    (h [M, inner], dpre [M, 2*inner] = [d value | d gate])."""
+    (h [M, inner] or None, dpre [M, 2*inner] = [d value | d gate])."""
     _need_cuda(x, wi, dh)
     x, ldx = _rows2d(x, "x")
     wi, ldw = _rows2d(wi, "wi")
@@ -405,11 +405,11 @@ def gemm_geglu_bwd(x: torch.Tensor, wi: torch.Tensor, bias_i: torch.Tensor | Non
     M = x.numel() // K if K else 0
     if dh.numel() != M * inner:
         raise _lib.TviError(_lib.TVI_ERR_INVALID, "gemm_geglu_bwd: dh must have one row per row of x")
-    h = torch.empty(M, inner, dtype=torch.bfloat16, device=x.device)
+    h = torch.empty(M, inner, dtype=torch.bfloat16, device=x.device) if need_h else None
     dpre = torch.empty(M, 2 * inner, dtype=torch.bfloat16, device=x.device)
     _hooked("gemm_bf16_geglu_bwd", 1, _lib.load().tvi_gemm_bf16_geglu_bwd, x.data_ptr(), wi.data_ptr(),
-            bias_i.data_ptr() if bias_i is not None else None, dh.data_ptr(), h.data_ptr(), dpre.data_ptr(), M, inner, K, ldx, ldw,
-            lddh, inner, 2 * inner, _stream())
+            bias_i.data_ptr() if bias_i is not None else None, dh.data_ptr(), h.data_ptr() if h is not None else None,
+            dpre.data_ptr(), M, inner, K, ldx, ldw, lddh, inner, 2 * inner, _stream())
     return h, dpre
 
 
