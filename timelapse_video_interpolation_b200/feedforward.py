@@ -64,7 +64,25 @@ def _bf16(t):
 
 
 def _cast_grad(g, like):
-    return None if g is None else (g if g.dtype == like.dtype else g.to(like.dtype)).view(like.shape)
+    return None if g is None else (g if g.dtype == like.dtype else g.to(like.dtype)).contiguous().view(like.shape)
+
+
+# Bias gradient of the first FeedForward projection without a pass of its own: the LayerNorm in front writes its rows into
+# a buffer _PAD columns wider, with a 1.0 (and zeros) behind every row; `dW1 = d(pre)^T [x | 1 0 ... 0]` then carries
+# db1 = d(pre)^T 1 as column C of the weight-gradient GEMM, whose last column tile was padded to 128 anyway.  Saves the
+# [M, 2*inner] column-sum launch (0.25 ms at L0) per trainable FeedForward.
+_PAD = 16
+_PAD_USED = 8
+_pad_rows = {}
+
+
+def _pad_pattern(device):
+    t = _pad_rows.get(device)
+    if t is None:
+        t = torch.zeros(_PAD, dtype=torch.bfloat16, device=device)
+        t[0] = 1.0
+        _pad_rows[device] = t
+    return t
 
 
 class _FeedForwardFn(torch.autograd.Function):
@@ -74,8 +92,12 @@ class _FeedForwardFn(torch.autograd.Function):
     runs the dgrad / wgrad / column-sum kernels of the projections."""
 
     @staticmethod
-    def forward(ctx, x, w1, b1, w2, b2, residual=None):
-        x2 = x.detach().contiguous().view(x.numel() // max(x.shape[-1], 1), x.shape[-1])
+    def forward(ctx, x, w1, b1, w2, b2, residual=None, x_padded=False):
+        if x_padded:  # rows of a [M, C + _PAD] buffer written by _LayerNormResFn(pad_ones=True): keep the row stride
+            x2 = x.detach().as_strided((x.numel() // x.shape[-1], x.shape[-1]), (x.stride(-2), 1), x.storage_offset())
+        else:
+            x2 = x.detach().contiguous().view(x.numel() // max(x.shape[-1], 1), x.shape[-1])
+        ctx.x_padded = bool(x_padded)
         with torch.no_grad():
             w1b, w2b = _bf16(w1), _bf16(w2)
             inner = w1b.shape[0] // 2
@@ -110,11 +132,18 @@ class _FeedForwardFn(torch.autograd.Function):
         h, dpre = ops.gemm_geglu_bwd(x2, ctx.wi, ctx.bi, dh, need_h=need_w2)
         dw2 = ops.gemm_bf16_wgrad(dy2, h) if need_w2 else None
         db2 = ops.colsum_bf16(dy2, dy2.shape[0]).view(-1) if (need_b2 and b2 is not None) else None
-        dw1 = ops.gemm_bf16_wgrad(dpre, x2) if need_w1 else None
-        db1 = ops.colsum_bf16(dpre, dpre.shape[0]).view(-1) if (need_b1 and b1 is not None) else None
+        need_b1 = need_b1 and b1 is not None
+        if ctx.x_padded and need_w1 and need_b1:
+            C = x2.shape[1]
+            xa = x2.as_strided((x2.shape[0], C + _PAD_USED), (x2.stride(0), 1), x2.storage_offset())  # [x | 1 0 ... 0]
+            dwa = ops.gemm_bf16_wgrad(dpre, xa)
+            dw1, db1 = dwa[:, :C], dwa[:, C]
+        else:
+            dw1 = ops.gemm_bf16_wgrad(dpre, x2) if need_w1 else None
+            db1 = ops.colsum_bf16(dpre, dpre.shape[0]).view(-1) if need_b1 else None
         dx = ops.gemm_bf16_dgrad(dpre, w1b).view(ctx.x_shape) if need_x else None
         return dx, _cast_grad(dw1, w1), _cast_grad(db1, b1) if b1 is not None else None, _cast_grad(dw2, w2), \
-            _cast_grad(db2, b2) if b2 is not None else None, (dy if need_res else None)
+            _cast_grad(db2, b2) if b2 is not None else None, (dy if need_res else None), None
 
 
 class _LinearFn(torch.autograd.Function):
@@ -179,9 +208,16 @@ class _LayerNormResFn(torch.autograd.Function):
     (`tvi_layernorm_bwd_res_bf16`) — autograd would otherwise sum the two with one more elementwise kernel per sub-layer."""
 
     @staticmethod
-    def forward(ctx, x, gamma, beta, eps):
+    def forward(ctx, x, gamma, beta, eps, pad_ones=False):
         xc = x.detach().contiguous()
-        y = ops.layernorm_bf16(xc, _bf16(gamma), _bf16(beta), eps)
+        if pad_ones:  # rows land in a [M, C + _PAD] buffer with [1 0 ... 0] behind each (see _PAD)
+            C = xc.shape[-1]
+            buf = torch.empty(xc.numel() // C, C + _PAD, dtype=torch.bfloat16, device=xc.device)
+            buf[:, C:] = _pad_pattern(xc.device)
+            ops.layernorm_bf16(xc.view(-1, C), _bf16(gamma), _bf16(beta), eps, out=buf[:, :C])
+            y = buf[:, :C].view(*xc.shape)
+        else:
+            y = ops.layernorm_bf16(xc, _bf16(gamma), _bf16(beta), eps)
         ctx.save_for_backward(xc, gamma, beta)
         ctx.eps = eps
         ctx.set_materialize_grads(False)
@@ -190,26 +226,27 @@ class _LayerNormResFn(torch.autograd.Function):
     @staticmethod
     def backward(ctx, dn, dres):
         xc, gamma, beta = ctx.saved_tensors
-        need_x, need_g, need_b, _ = ctx.needs_input_grad
+        need_x, need_g, need_b = ctx.needs_input_grad[:3]
         need_g, need_b = need_g and gamma is not None, need_b and beta is not None
         if dres is not None:
             dres = dres.contiguous().to(torch.bfloat16)
         if dn is None:  # nothing flowed through f (a one-key cross-attention): the branch passes dres through
             dg = torch.zeros_like(gamma) if need_g else None
             db = torch.zeros_like(beta) if need_b else None
-            return (dres if need_x else None), dg, db, None
+            return (dres if need_x else None), dg, db, None, None
         dx, dgamma, dbeta = ops.layernorm_bwd(xc, dn.contiguous().to(torch.bfloat16), _bf16(gamma), ctx.eps, need_dx=need_x,
                                               need_affine=need_g or need_b, dres=dres if need_x else None)
-        return dx, _cast_grad(dgamma, gamma) if need_g else None, _cast_grad(dbeta, beta) if need_b else None, None
+        return dx, _cast_grad(dgamma, gamma) if need_g else None, _cast_grad(dbeta, beta) if need_b else None, None, None
 
 
-def layer_norm_residual(norm, x: torch.Tensor):
-    """(norm(x), x) on the autograd tape for a residual branch (see _LayerNormResFn); training path only."""
+def layer_norm_residual(norm, x: torch.Tensor, pad_ones: bool = False):
+    """(norm(x), x) on the autograd tape for a residual branch (see _LayerNormResFn); training path only.  `pad_ones`: the
+    normalised rows are a strided view into a wider buffer with [1 0 ... 0] behind each row (see _PAD)."""
     if tuple(norm.normalized_shape) != (x.shape[-1],):
         raise _lib.TviError(_lib.TVI_ERR_UNSUPPORTED, "layer_norm: only normalisation over the last dimension is built")
     if x.dtype != torch.bfloat16 or not x.is_cuda:
         raise _lib.TviError(_lib.TVI_ERR_UNSUPPORTED, "layer_norm: expected a CUDA bfloat16 tensor")
-    return _LayerNormResFn.apply(x, norm.weight, norm.bias, float(norm.eps))
+    return _LayerNormResFn.apply(x, norm.weight, norm.bias, float(norm.eps), bool(pad_ones))
 
 
 def feed_forward(ff, hidden_states: torch.Tensor, scale: float = 1.0, residual: Optional[torch.Tensor] = None,
@@ -239,13 +276,17 @@ def feed_forward(ff, hidden_states: torch.Tensor, scale: float = 1.0, residual: 
         # dy itself); when it is the LayerNorm's own input — the blocks' `x + ff(norm(x))` — its gradient is added inside the
         # LayerNorm backward kernel
         proj, out_lin = ff.net[0].proj, ff.net[2]
+        padded = False
         if pre_norm is not None and residual is x:
-            x, residual = layer_norm_residual(pre_norm, x)
+            # the bias gradient of `proj` rides in its weight-gradient GEMM when both are wanted (see _PAD)
+            padded = (proj.bias is not None and proj.bias.requires_grad and proj.weight.requires_grad and x.shape[-1] % 16 == 0
+                      and x.numel() > 0)
+            x, residual = layer_norm_residual(pre_norm, x, pad_ones=padded)
         elif pre_norm is not None:
             x = layer_norm(pre_norm, x)
         if residual is not None and residual.shape[-1] != out_lin.weight.shape[0]:
             raise _lib.TviError(_lib.TVI_ERR_INVALID, "feed_forward: residual must have the shape of the output")
-        return _FeedForwardFn.apply(x, proj.weight, proj.bias, out_lin.weight, out_lin.bias, residual)
+        return _FeedForwardFn.apply(x, proj.weight, proj.bias, out_lin.weight, out_lin.bias, residual, padded)
     x = x.contiguous()
     wi, bi = _geglu_weights(ff.net[0].proj)
     x2 = x.view(x.numel() // x.shape[-1], x.shape[-1])
