@@ -103,6 +103,45 @@ def test_feed_forward_backward(cuda, rows, dim):
     assert torch.equal(x2.grad, x.grad) and all(p.grad is None for p in ff.parameters())
 
 
+@pytest.mark.parametrize("shape,dim,freeze", [((2, 151, 320), 320, ()), ((1000, 640), 640, ()), ((2, 151, 320), 320, ("net.0.proj.bias",)),
+                                              ((333, 320), 320, ("net.2.weight", "net.2.bias"))])
+def test_residual_feed_forward_branch_backward(cuda, shape, dim, freeze):
+    """`x + ff(norm(x))` as the blocks call it (pre_norm=, residual=x): on the tape the first projection's bias gradient
+    comes out of its weight-gradient GEMM (a ones column behind the normalised rows, feedforward._PAD) when both are
+    trainable, from the column-sum kernel otherwise; a frozen second projection drops the h output of the fused backward."""
+    g = torch.Generator().manual_seed(dim + len(freeze))
+    ff, norm = FeedForward(dim), torch.nn.LayerNorm(dim)
+    with torch.no_grad():
+        for p in ff.parameters():
+            p.copy_(torch.randn(p.shape, generator=g) * (p.shape[-1] ** -0.5 if p.dim() > 1 else 0.1))
+        norm.weight.copy_(1 + 0.2 * torch.randn(dim, generator=g))
+        norm.bias.copy_(0.1 * torch.randn(dim, generator=g))
+    ff, norm = ff.to(cuda, torch.bfloat16), norm.to(cuda, torch.bfloat16)
+    for n, p in ff.named_parameters():
+        p.requires_grad_(n not in freeze)
+    x = torch.randn(*shape, generator=g).to(torch.bfloat16).to(cuda).requires_grad_(True)
+    wgt = torch.randn(*shape, generator=g).to(torch.bfloat16).to(cuda)
+    y = tvi.feed_forward(ff, x, residual=x, pre_norm=norm)
+    (y.float() * wgt.float()).sum().backward()
+    names = ["net.0.proj.weight", "net.0.proj.bias", "net.2.weight", "net.2.bias"]
+    ps = dict(ff.named_parameters())
+    ref = [ps[n].detach().float().cpu().requires_grad_(True) for n in names]
+    xr = x.detach().float().cpu().requires_grad_(True)
+    gr, br = norm.weight.detach().float().cpu().requires_grad_(True), norm.bias.detach().float().cpu().requires_grad_(True)
+    yr = xr + _ff_ref(F.layer_norm(xr, (dim,), gr, br, norm.eps), *ref)
+    assert float((y.detach().float().cpu() - yr.detach()).abs().max()) <= 2e-2 * max(1.0, float(yr.detach().abs().max()))
+    (yr * wgt.float().cpu()).sum().backward()
+    _close("dx", x.grad, xr.grad)
+    _close("dgamma", norm.weight.grad, gr.grad)
+    _close("dbeta", norm.bias.grad, br.grad)
+    for n, r in zip(names, ref):
+        if n in freeze:
+            assert ps[n].grad is None
+        else:
+            _close(n, ps[n].grad, r.grad)
+            assert ps[n].grad.is_contiguous() and ps[n].grad.shape == ps[n].shape
+
+
 def _attn_ref(x, e, wq, wk, wv, wo, bo, heads):
     B, S, C = x.shape
     ctx = x if e is None else e
