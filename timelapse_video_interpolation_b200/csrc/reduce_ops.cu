@@ -17,8 +17,9 @@ constexpr int kCsTy = 8;
 __global__ void __launch_bounds__(32 * kCsTy)
 colsum_kernel(const tvi_bf16* __restrict__ x, tvi_bf16* __restrict__ out, float* __restrict__ partial,
               int64_t rows_per_group, int tiles_per_group, int C8, int64_t ldx, int64_t ldo, int64_t inner) {
-  __shared__ float red[kCsTy][32][8];
-  const int cx = blockIdx.y * 32 + threadIdx.x;
+  __shared__ float red[256][8];  // [threadIdx.y][threadIdx.x]: 32 x 8 threads, or 8 x 32 for widths that are not multiples of 256
+  const int bx = blockDim.x, by = blockDim.y;
+  const int cx = blockIdx.y * bx + threadIdx.x;
   const int ty = threadIdx.y;
   const int64_t group = blockIdx.x / tiles_per_group;
   const int tile = (int)(blockIdx.x - group * tiles_per_group);
@@ -33,7 +34,7 @@ colsum_kernel(const tvi_bf16* __restrict__ x, tvi_bf16* __restrict__ out, float*
   const int64_t gbase = group * rows_per_group;
   const int64_t pbase = (group / inner) * rows_per_group * inner + group % inner;
   if (cx < C8) {
-    for (int64_t r = rlo + ty; r < rhi; r += kCsTy) {
+    for (int64_t r = rlo + ty; r < rhi; r += by) {
       const int64_t pr = inner == 1 ? r : pbase + (r - gbase) * inner;
       const uint4 u = __ldg(reinterpret_cast<const uint4*>(x + pr * ldx + cx * 8));
       const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&u);
@@ -46,14 +47,13 @@ colsum_kernel(const tvi_bf16* __restrict__ x, tvi_bf16* __restrict__ out, float*
     }
   }
 #pragma unroll
-  for (int j = 0; j < 8; ++j) red[ty][threadIdx.x][j] = acc[j];
+  for (int j = 0; j < 8; ++j) red[ty * bx + threadIdx.x][j] = acc[j];
   __syncthreads();
   if (ty == 0 && cx < C8) {
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
       float s = 0.f;
-#pragma unroll
-      for (int t = 0; t < kCsTy; ++t) s += red[t][threadIdx.x][j];
+      for (int t = 0; t < by; ++t) s += red[t * bx + threadIdx.x][j];
       acc[j] = s;
     }
     if (tiles_per_group == 1) {
@@ -162,8 +162,11 @@ extern "C" int tvi_colsum_bf16_interleaved(const tvi_bf16* x, tvi_bf16* out, voi
   const int C8 = C / 8;
   // (A variant that deals the 256 threads of a block out as row slots x column chunks, so that C = 320 keeps every lane
   // busy, was measured slower — 0.097 vs 0.067 ms at [258 048, 320]: 252 blocks of one tile each leave the SMs under-filled.)
-  dim3 grid((unsigned)(ngroups * tiles), (unsigned)((C8 + 31) / 32));
-  dim3 block(32, kCsTy);
+  // 32 column chunks x 8 row lanes per block; widths like C = 320 (40 chunks) would leave the second block of a row with
+  // 8 of 32 lanes busy, so they take 8 chunks x 32 row lanes (a warp = four 128-byte row segments)
+  const int bx = (C8 % 32 != 0 && C8 % 8 == 0) ? 8 : 32;
+  dim3 grid((unsigned)(ngroups * tiles), (unsigned)((C8 + bx - 1) / bx));
+  dim3 block((unsigned)bx, (unsigned)(256 / bx));
   colsum_kernel<<<grid, block, 0, st>>>(x, out, (float*)workspace, rows_per_group, tiles, C8, ldx, ldo, group_inner);
   TVI_LAUNCH_OK("colsum_kernel");
   if (tiles > 1) {
