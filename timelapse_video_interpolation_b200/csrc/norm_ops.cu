@@ -574,14 +574,20 @@ layernorm_bwd_flat_kernel(const tvi_bf16* __restrict__ x, const tvi_bf16* __rest
   }
 }
 
-__global__ void ln_bwd_final_kernel(const float* __restrict__ partial, tvi_bf16* __restrict__ dgamma, tvi_bf16* __restrict__ dbeta,
-                                    int nblocks, int C) {
-  const int j = blockIdx.x * blockDim.x + threadIdx.x;
+// one warp per output column: lane l adds blocks l, l + 32, ... in order, then a fixed shuffle tree (deterministic); one
+// thread per column walked all 148+ partials serially
+__global__ void __launch_bounds__(256)
+ln_bwd_final_kernel(const float* __restrict__ partial, tvi_bf16* __restrict__ dgamma, tvi_bf16* __restrict__ dbeta, int nblocks,
+                    int C) {
+  const int j = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
   if (j >= 2 * C) return;
   float s = 0.f;
-  for (int b = 0; b < nblocks; ++b) s += partial[(size_t)b * 2 * C + j];
+  for (int b = lane; b < nblocks; b += 32) s += partial[(size_t)b * 2 * C + j];
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
   tvi_bf16* dst = j < C ? dgamma : dbeta;
-  if (dst != nullptr) reinterpret_cast<__nv_bfloat16*>(dst)[j < C ? j : j - C] = __float2bfloat16_rn(s);
+  if (lane == 0 && dst != nullptr) reinterpret_cast<__nv_bfloat16*>(dst)[j < C ? j : j - C] = __float2bfloat16_rn(s);
 }
 
 int64_t ln_bwd_blocks(int64_t M) {
@@ -690,7 +696,7 @@ extern "C" int tvi_layernorm_bwd_res_bf16(const tvi_bf16* x, const tvi_bf16* dy,
     rc = launch_ln_bwd<8>(x, dy, gamma, dres, dx, (float*)workspace, M, C8, ldx, lddy, lddres, lddx, eps, st);
   if (rc) return rc;
   if (dgamma != nullptr || dbeta != nullptr) {
-    ln_bwd_final_kernel<<<(2 * C + 255) / 256, 256, 0, st>>>((const float*)workspace, dgamma, dbeta, (int)blocks, C);
+    ln_bwd_final_kernel<<<(2 * C + 7) / 8, 256, 0, st>>>((const float*)workspace, dgamma, dbeta, (int)blocks, C);
     TVI_LAUNCH_OK("ln_bwd_final_kernel");
   }
   return TVI_OK;
