@@ -164,7 +164,8 @@ extern "C" int tvi_colsum_bf16_interleaved(const tvi_bf16* x, tvi_bf16* out, voi
   // busy, was measured slower — 0.097 vs 0.067 ms at [258 048, 320]: 252 blocks of one tile each leave the SMs under-filled.)
   // 32 column chunks x 8 row lanes per block; widths like C = 320 (40 chunks) would leave the second block of a row with
   // 8 of 32 lanes busy, so they take 8 chunks x 32 row lanes (a warp = four 128-byte row segments)
-  const int bx = (C8 % 32 != 0 && C8 % 8 == 0) ? 8 : 32;
+  // (only for long groups: 32 row lanes need rows to work on — the one-key dV sums have 14-row groups)
+  const int bx = (C8 % 32 != 0 && C8 % 8 == 0 && rows_per_group >= 256) ? 8 : 32;
   dim3 grid((unsigned)(ngroups * tiles), (unsigned)((C8 + bx - 1) / bx));
   dim3 block((unsigned)bx, (unsigned)(256 / bx));
   colsum_kernel<<<grid, block, 0, st>>>(x, out, (float*)workspace, rows_per_group, tiles, C8, ldx, ldo, group_inner);
