@@ -212,6 +212,16 @@ int tvi_blend_rows_bwd_bf16(const tvi_bf16* dy, const tvi_bf16* x_spatial, const
 int tvi_cfg_euler_step_f32(const tvi_bf16* noise_pred, float* latents, const float* guidance, tvi_bf16* model_input, int64_t B,
                            int T, int C, int Cin, int64_t HW, int64_t guidance_stride_b, float sigma, float sigma_next,
                            int prediction_type, void* stream);
+/* The same step with the arithmetic TYPES of the reference loop (latent_rounding = TVI_LATENT_ROUND_BF16): the CFG combine
+ * runs in the model dtype with every torch op rounded (:565-566), `prev_sample` is cast back to the model dtype as
+ * EulerDiscreteScheduler.step does (`prev_sample.to(model_output.dtype)`), and the next model input is
+ * `sample / ((sigma**2 + 1) ** 0.5)` in the model dtype.  `latents` stays an fp32 array whose values are then
+ * bf16-representable.  TVI_LATENT_ROUND_NONE is tvi_cfg_euler_step_f32 (fp32 master latents, the default). */
+#define TVI_LATENT_ROUND_NONE 0
+#define TVI_LATENT_ROUND_BF16 1
+int tvi_cfg_euler_step_round_f32(const tvi_bf16* noise_pred, float* latents, const float* guidance, tvi_bf16* model_input, int64_t B,
+                                 int T, int C, int Cin, int64_t HW, int64_t guidance_stride_b, float sigma, float sigma_next,
+                                 int prediction_type, int latent_rounding, void* stream);
 int tvi_model_input_bf16(const float* latents, const tvi_bf16* image_latents, tvi_bf16* model_input, int64_t BT, int C, int Cin,
                          int64_t HW, float scale, void* stream);
 

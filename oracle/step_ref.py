@@ -39,3 +39,25 @@ def model_input_ref(latents: torch.Tensor, image_latents: torch.Tensor, sigma: f
     x = torch.cat([latents] * 2)
     x = scale_model_input_ref(x, sigma)
     return torch.cat([x, image_latents.to(x.dtype)], dim=2)
+
+
+def loop_step_model_dtype_ref(noise_pred: torch.Tensor, latents: torch.Tensor, guidance_scale: torch.Tensor, sigma: float,
+                              sigma_next: float, prediction_type: str):
+    """One loop iteration with the arithmetic TYPES of the reference loop (model dtype = that of `noise_pred` / `latents`,
+    e.g. bf16): the CFG lines :563-566 on model-dtype tensors (torch rounds every op), EulerDiscreteScheduler.step's fp32
+    upcast and `prev_sample.to(model_output.dtype)`, then `scale_model_input` in the model dtype for the next UNet call.
+    Returns (latents, scaled latents), both in the model dtype."""
+    dt = noise_pred.dtype
+    uncond, cond = noise_pred.chunk(2)
+    e = uncond + guidance_scale.to(dt) * (cond - uncond)
+    sample = latents.to(torch.float32)
+    mo = e.to(torch.float32)
+    if prediction_type == "epsilon":
+        pred_original = sample - sigma * mo
+    elif prediction_type == "v_prediction":
+        pred_original = mo * (-sigma / (sigma ** 2 + 1) ** 0.5) + (sample / (sigma ** 2 + 1))
+    else:
+        raise ValueError(prediction_type)
+    derivative = (sample - pred_original) / sigma
+    prev = (sample + derivative * (sigma_next - sigma)).to(dt)
+    return prev, scale_model_input_ref(prev, sigma_next)

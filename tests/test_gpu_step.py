@@ -64,3 +64,41 @@ def test_stepper_argument_checks(cuda):
         EulerCfgStepper([1.0], torch.ones(4))
     with pytest.raises(_lib.TviError):
         EulerCfgStepper(sig, torch.ones(4), prediction_type="sample")
+
+
+@pytest.mark.parametrize("B,T,H,W,pred", [(1, 14, 8, 16, "v_prediction"), (2, 5, 6, 10, "epsilon"), (1, 25, 72, 128, "v_prediction")])
+def test_stepper_with_the_reference_loops_rounding(cuda, B, T, H, W, pred):
+    """latent_rounding="bf16": CFG in the model dtype, prev_sample cast back to it every step, model input divided in it —
+    the arithmetic types of the reference loop (pipeline :563-569 + diffusers EulerDiscreteScheduler), against the torch
+    bf16 restatement step by step (each step starts from the kernel's own latents, so one-ulp differences — the kernel's
+    fused multiply-adds against torch's separate ops — cannot compound)."""
+    g = torch.Generator().manual_seed(T + 1)
+    C, Ci, steps = 4, 5, 6
+    sig = _sigmas(steps)
+    guidance = torch.linspace(1.0, 3.0, T)
+    lat = (torch.randn(B, T, C, H, W, generator=g) * float((sig[0] ** 2 + 1) ** 0.5)).to(torch.bfloat16)
+    img = torch.randn(2 * B, T, Ci, H, W, generator=g).to(torch.bfloat16)
+    st = EulerCfgStepper(sig, guidance, prediction_type=pred, latent_rounding="bf16")
+    st.begin(lat.to(cuda), img.to(cuda))
+    assert torch.equal(st.latents.cpu(), lat.float())
+    gs5 = guidance.reshape(-1, T)[..., None, None, None]
+    for i in range(steps):
+        before = st.latents.cpu().to(torch.bfloat16)
+        assert torch.equal(before.float(), st.latents.cpu())            # the fp32 array holds bf16-representable values
+        noise = torch.randn(2 * B, T, C, H, W, generator=g).to(torch.bfloat16)
+        mi = st.step(noise.to(cuda), i)
+        want_lat, want_in = step_ref.loop_step_model_dtype_ref(noise, before, gs5, float(sig[i]), float(sig[i + 1]), pred)
+        got = st.latents.cpu()
+        diff = (got - want_lat.float()).abs()
+        # one bf16 step of the result, plus the fp32 rounding of the operands where the update cancels (x and sigma * e are
+        # O(sigma) while the result may be small)
+        ulp = want_lat.float().abs() * 2 ** -7 + 2e-6 * (float(before.float().abs().max()) + 20.0 * float(sig[i]))
+        assert bool((diff <= ulp).all()), i                              # never more than one bf16 step apart
+        assert float((diff > 0).float().mean()) <= 0.01, i               # and identical for all but a few elements
+        if i < steps - 1:
+            want_in = step_ref.scale_model_input_ref(got.to(torch.bfloat16), float(sig[i + 1]))  # from the kernel's own latents
+            d2 = (mi[:B, :, :C].float().cpu() - want_in.float()).abs()
+            assert bool((d2 <= want_in.float().abs().clamp_min(1e-30) * 2 ** -7).all()), i
+            assert float((d2 > 0).float().mean()) <= 0.02, i
+    with pytest.raises(_lib.TviError):
+        EulerCfgStepper(sig, guidance, latent_rounding="fp16")

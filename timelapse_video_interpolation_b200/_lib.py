@@ -55,6 +55,7 @@ SIGNATURES = {
     "tvi_blend_rows_bwd_bf16": (_i32, [_ptr, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr, _i64, _i64, _i32, _i64, _ptr]),
     "tvi_blend_rows_bf16": (_i32, [_ptr, _ptr, _ptr, _ptr, _i64, _i64, _i32, _i64, _i64, _i64, _ptr]),
     "tvi_cfg_euler_step_f32": (_i32, [_ptr, _ptr, _ptr, _ptr, _i64, _i32, _i32, _i32, _i64, _i64, _f32, _f32, _i32, _ptr]),
+    "tvi_cfg_euler_step_round_f32": (_i32, [_ptr, _ptr, _ptr, _ptr, _i64, _i32, _i32, _i32, _i64, _i64, _f32, _f32, _i32, _i32, _ptr]),
     "tvi_model_input_bf16": (_i32, [_ptr, _ptr, _ptr, _i64, _i32, _i32, _i64, _f32, _ptr]),
     "tvi_farneback_workspace_bytes": (_sz, [_i32, _i32, _f64, _i32]),
     "tvi_farneback_clip_f32": (_i32, [_ptr, _ptr, _i64, _i32, _ptr, _ptr, _i32, _i32, _f64, _i32, _i32, _i32, _i32, _f64, _ptr]),
@@ -97,6 +98,7 @@ SPATIAL_AUTO, SPATIAL_MMA_SYNC, SPATIAL_TCGEN05 = 0, 1, 2
 EPILOGUE_NONE, EPILOGUE_GEGLU = 0, 1
 FEWKEYS_STATIC_MAX_STATS = 4096  # TVI_FEWKEYS_STATIC_MAX_STATS of include/tvi.h
 PRED_EPSILON, PRED_V = 0, 1
+LATENT_ROUND_NONE, LATENT_ROUND_BF16 = 0, 1
 
 _lib = None
 

@@ -18,7 +18,7 @@ namespace {
 __global__ void __launch_bounds__(256)
 cfg_euler_step_kernel(const tvi_bf16* __restrict__ noise_pred, float* __restrict__ latents, const float* __restrict__ guidance,
                       tvi_bf16* __restrict__ model_input, int64_t B, int T, int C, int Cin, int64_t HW4, float sigma,
-                      float sigma_next, int v_prediction, int64_t guidance_stride_b) {
+                      float sigma_next, int v_prediction, int64_t guidance_stride_b, int round_bf16) {
   const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   const int64_t total = B * T * C * HW4;
   if (idx >= total) return;
@@ -39,6 +39,14 @@ cfg_euler_step_kernel(const tvi_bf16* __restrict__ noise_pred, float* __restrict
   const float2 u0 = __bfloat1622float2(hu[0]), u1 = __bfloat1622float2(hu[1]);
   const float2 c0 = __bfloat1622float2(hc[0]), c1 = __bfloat1622float2(hc[1]);
   float e[4] = {u0.x + gs * (c0.x - u0.x), u0.y + gs * (c0.y - u0.y), u1.x + gs * (c1.x - u1.x), u1.y + gs * (c1.y - u1.y)};
+  auto rn = [](float v) { return __bfloat162float(__float2bfloat16_rn(v)); };
+  if (round_bf16) {
+    // the reference loop's arithmetic types: CFG in the model dtype, every torch op rounded (:565-566)
+    const float uu[4] = {u0.x, u0.y, u1.x, u1.y}, cc[4] = {c0.x, c0.y, c1.x, c1.y};
+    const float gr = rn(gs);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) e[i] = rn(uu[i] + rn(gr * rn(cc[i] - uu[i])));
+  }
   float xs[4] = {x.x, x.y, x.z, x.w};
   const float s2p1 = sigma * sigma + 1.0f;
   const float dt = sigma_next - sigma;
@@ -51,11 +59,18 @@ cfg_euler_step_kernel(const tvi_bf16* __restrict__ noise_pred, float* __restrict
     const float x0 = v_prediction ? e[i] * (-sigma / sqrtf(s2p1)) + xs[i] / s2p1 : xs[i] - sigma * e[i];
     const float derivative = (xs[i] - x0) / sigma;
     out[i] = xs[i] + derivative * dt;
+    if (round_bf16) out[i] = rn(out[i]);  // EulerDiscreteScheduler.step: prev_sample.to(model_output.dtype)
   }
   *reinterpret_cast<float4*>(latents + off) = make_float4(out[0], out[1], out[2], out[3]);
   if (model_input != nullptr) {
-    packed[0] = pack_bf16x2(out[0] * in_scale, out[1] * in_scale);
-    packed[1] = pack_bf16x2(out[2] * in_scale, out[3] * in_scale);
+    if (round_bf16) {  // scale_model_input divides (`sample / ((sigma**2 + 1) ** 0.5)`), in the model dtype
+      const float den = sqrtf(sigma_next * sigma_next + 1.0f);
+      packed[0] = pack_bf16x2(out[0] / den, out[1] / den);
+      packed[1] = pack_bf16x2(out[2] / den, out[3] / den);
+    } else {
+      packed[0] = pack_bf16x2(out[0] * in_scale, out[1] * in_scale);
+      packed[1] = pack_bf16x2(out[2] * in_scale, out[3] * in_scale);
+    }
     const int64_t moff = (bt * Cin + c) * HW + s4 * 4;
     *reinterpret_cast<uint2*>(model_input + moff) = make_uint2(packed[0], packed[1]);
     *reinterpret_cast<uint2*>(model_input + B * T * Cin * HW + moff) = make_uint2(packed[0], packed[1]);
@@ -91,7 +106,16 @@ model_input_kernel(const float* __restrict__ latents, const tvi_bf16* __restrict
 extern "C" int tvi_cfg_euler_step_f32(const tvi_bf16* noise_pred, float* latents, const float* guidance, tvi_bf16* model_input,
                                       int64_t B, int T, int C, int Cin, int64_t HW, int64_t guidance_stride_b, float sigma,
                                       float sigma_next, int prediction_type, void* stream) {
+  return tvi_cfg_euler_step_round_f32(noise_pred, latents, guidance, model_input, B, T, C, Cin, HW, guidance_stride_b, sigma, sigma_next,
+                                      prediction_type, TVI_LATENT_ROUND_NONE, stream);
+}
+
+extern "C" int tvi_cfg_euler_step_round_f32(const tvi_bf16* noise_pred, float* latents, const float* guidance, tvi_bf16* model_input,
+                                            int64_t B, int T, int C, int Cin, int64_t HW, int64_t guidance_stride_b, float sigma,
+                                            float sigma_next, int prediction_type, int latent_rounding, void* stream) {
   using namespace tvi;
+  TVI_CHECK_ARG(latent_rounding == TVI_LATENT_ROUND_NONE || latent_rounding == TVI_LATENT_ROUND_BF16,
+                "tvi_cfg_euler_step_f32: unknown latent rounding mode %d", latent_rounding);
   TVI_CHECK_ARG(B >= 0 && T >= 0 && C >= 0 && HW >= 0, "tvi_cfg_euler_step_f32: negative size");
   if (B == 0 || T == 0 || C == 0 || HW == 0) return TVI_OK;
   TVI_CHECK_ARG(noise_pred && latents && guidance, "tvi_cfg_euler_step_f32: null pointer");
@@ -105,7 +129,7 @@ extern "C" int tvi_cfg_euler_step_f32(const tvi_bf16* noise_pred, float* latents
   TVI_CHECK_ARG((total + 255) / 256 < ((int64_t)1 << 31), "tvi_cfg_euler_step_f32: grid too large");
   cfg_euler_step_kernel<<<(unsigned)((total + 255) / 256), 256, 0, (cudaStream_t)stream>>>(
       noise_pred, latents, guidance, model_input, B, T, C, Cin, HW / 4, sigma, sigma_next, prediction_type == TVI_PRED_V ? 1 : 0,
-      guidance_stride_b);
+      guidance_stride_b, latent_rounding == TVI_LATENT_ROUND_BF16 ? 1 : 0);
   TVI_LAUNCH_OK("cfg_euler_step_kernel");
   return TVI_OK;
 }

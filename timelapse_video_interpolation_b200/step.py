@@ -11,6 +11,11 @@ Mirrors src/pipelines/pipeline_stable_video_diffusion_efficient_interp.py:538-56
 
 `sigmas` are the scheduler's (EulerDiscreteScheduler.sigmas, trailing 0 included); `guidance_scale` is the per-frame
 vector built at :523-530 ([T] or [B, T]).  The latents live in fp32 for the whole loop; the UNet sees bf16.
+
+`latent_rounding="bf16"` reproduces the arithmetic TYPES of the reference loop instead: CFG in the model dtype with every
+torch op rounded (:565-566), `prev_sample` cast back to the model dtype after the scheduler's fp32 arithmetic (diffusers
+`EulerDiscreteScheduler.step`), the model input divided in the model dtype (`scale_model_input`); `stepper.latents` is then
+an fp32 tensor of bf16-representable values.  The default (None) keeps the more accurate fp32 master copy.
 """
 from __future__ import annotations
 
@@ -22,13 +27,16 @@ __all__ = ["EulerCfgStepper"]
 
 
 class EulerCfgStepper:
-    def __init__(self, sigmas, guidance_scale: torch.Tensor, prediction_type: str = "v_prediction"):
+    def __init__(self, sigmas, guidance_scale: torch.Tensor, prediction_type: str = "v_prediction", latent_rounding=None):
         self.sigmas = [float(s) for s in (sigmas.tolist() if isinstance(sigmas, torch.Tensor) else sigmas)]
         if len(self.sigmas) < 2 or any(s <= 0 for s in self.sigmas[:-1]) or self.sigmas[-1] < 0:
             raise _lib.TviError(_lib.TVI_ERR_INVALID, "sigmas must be positive with an optional trailing 0")
         if prediction_type not in ("epsilon", "v_prediction"):
             raise _lib.TviError(_lib.TVI_ERR_UNSUPPORTED, f"prediction_type {prediction_type!r}")
         self.pred = _lib.PRED_V if prediction_type == "v_prediction" else _lib.PRED_EPSILON
+        if latent_rounding not in (None, "bf16", torch.bfloat16):
+            raise _lib.TviError(_lib.TVI_ERR_UNSUPPORTED, f"latent_rounding {latent_rounding!r} (None or 'bf16')")
+        self.rounding = _lib.LATENT_ROUND_NONE if latent_rounding is None else _lib.LATENT_ROUND_BF16
         self.guidance = guidance_scale
         self.latents = None
         self.model_input = None
@@ -51,6 +59,8 @@ class EulerCfgStepper:
         self._g = g.contiguous()
         self._g_stride = T if g.shape[0] == B and B > 1 else 0
         self.latents = latents.detach().to(torch.float32).contiguous().clone()
+        if self.rounding == _lib.LATENT_ROUND_BF16:  # the reference's latents are a model-dtype tensor from the start
+            self.latents = self.latents.to(torch.bfloat16).to(torch.float32)
         Ci = image_latents.shape[2]
         self.model_input = torch.empty(2 * B, T, C + Ci, H, W, dtype=torch.bfloat16, device=latents.device)
         self._dims = (B, T, C, C + Ci, H * W)
@@ -69,7 +79,7 @@ class EulerCfgStepper:
         if not 0 <= i < len(self.sigmas) - 1:
             raise _lib.TviError(_lib.TVI_ERR_INVALID, f"step index {i} outside the sigma schedule")
         last = i == len(self.sigmas) - 2
-        ops._hooked("cfg_euler_step", 1, _lib.load().tvi_cfg_euler_step_f32, noise_pred.contiguous().data_ptr(),
+        ops._hooked("cfg_euler_step", 1, _lib.load().tvi_cfg_euler_step_round_f32, noise_pred.contiguous().data_ptr(),
                     self.latents.data_ptr(), self._g.data_ptr(), None if last else self.model_input.data_ptr(), B, T, C, Cin, HW,
-                    self._g_stride, self.sigmas[i], self.sigmas[i + 1], self.pred, ops._stream())
+                    self._g_stride, self.sigmas[i], self.sigmas[i + 1], self.pred, self.rounding, ops._stream())
         return self.model_input
