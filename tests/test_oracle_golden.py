@@ -216,3 +216,24 @@ def test_step_glue_oracle_matches_reference_loop_lines(golden_dir):
         want = torch.from_numpy(z[f"{tag}.guided"])
         assert guided.shape == want.shape
         assert float((guided - want.double()).abs().max()) <= 1e-6 * max(1.0, float(want.abs().max()))
+
+
+def test_step_oracle_with_model_dtype_rounding_tracks_the_fp64_one():
+    """oracle/step_ref.loop_step_model_dtype_ref (the reference loop's arithmetic types, bf16) against the fp64
+    restatement of the same step: they differ by the roundings of the CFG combine and of prev_sample only."""
+    import torch
+    from oracle import step_ref
+    g = torch.Generator().manual_seed(5)
+    B, T, C, H, W = 2, 5, 4, 6, 8
+    for pred in ("epsilon", "v_prediction"):
+        for sigma, sigma_next in ((50.0, 20.0), (1.5, 0.4), (0.4, 0.0)):
+            lat = (torch.randn(B, T, C, H, W, generator=g) * (sigma ** 2 + 1) ** 0.5).to(torch.bfloat16)
+            noise = torch.randn(2 * B, T, C, H, W, generator=g).to(torch.bfloat16)
+            gs = torch.linspace(1.0, 3.0, T).reshape(1, T, 1, 1, 1)
+            prev, scaled = step_ref.loop_step_model_dtype_ref(noise, lat, gs, sigma, sigma_next, pred)
+            assert prev.dtype == torch.bfloat16 and scaled.dtype == torch.bfloat16
+            want = step_ref.euler_step_ref(step_ref.cfg_ref(noise, gs), lat, sigma, sigma_next, pred)
+            # bf16 CFG: three roundings of O(|e|) values, scaled by |sigma_next - sigma| for epsilon and by up to sigma for v
+            tol = 2 ** -7 * (want.abs() + 4.0 * max(sigma, 1.0) * 3.0)
+            assert bool(((prev.double() - want).abs() <= tol).all())
+            assert torch.equal(scaled, step_ref.scale_model_input_ref(prev, sigma_next))
