@@ -33,6 +33,8 @@ ap.add_argument("--res", default="576x1024")
 ap.add_argument("--param-dtype", default="bf16", choices=["bf16", "fp32"])
 ap.add_argument("--steps", type=int, default=5)
 ap.add_argument("--clips", type=int, default=2)
+ap.add_argument("--graph", action="store_true", help="also capture forward + backward of the (un-wrapped) module into ONE CUDA "
+                "graph and time its replay (+ one all-reduce of the flattened gradients when world > 1)")
 ap.add_argument("--module", action="store_true", help="train through the module-level swap (TransformerSpatioTemporalModel.forward, "
                 "NCHW in / out: GroupNorm, proj_in, block pair, AlphaBlender, proj_out) instead of the bare block pair")
 args = ap.parse_args()
@@ -107,17 +109,6 @@ else:
     ctx_s = torch.randn(B * T, 2, 1024, generator=g).to(torch.bfloat16).to(dev)
     ctx_t = torch.randn(B * S, 1, 1024, generator=g).to(torch.bfloat16).to(dev)
     dy = (torch.randn(B * T, S, C, generator=g) / 8).to(torch.bfloat16).to(dev)
-model = DDP(pair, device_ids=[local], gradient_as_bucket_view=True)
-
-
-def step(sync=True):
-    model.zero_grad(set_to_none=True)
-    x.grad = None
-    if sync:
-        model(x, ctx_s, ctx_t).backward(dy)
-    else:
-        with model.no_sync():
-            model(x, ctx_s, ctx_t).backward(dy)
 
 
 def timed(fn, n):
@@ -134,6 +125,59 @@ def timed(fn, n):
     t = torch.tensor([a.elapsed_time(b) / n], device=dev)
     dist.all_reduce(t, op=dist.ReduceOp.MAX)  # time of the slowest rank
     return float(t)
+
+
+# Every libtvi entry is capture-safe (caller's stream, no host sync; torch's allocations come from the graph's pool), so the
+# whole forward + backward records into one CUDA graph: at the reference's 512x320 operating point the eager step is bound by
+# the Python / launch path (~190 launches of a few microseconds each), not by the GPU.  Measured before DDP wraps the module
+# (its reducer hooks expect DDP.forward); data parallelism is then ONE all-reduce of the flattened gradients after the replay.
+graph_ms = graph_same = None
+if args.graph:
+    gparams = [p for p in pair.parameters() if p.requires_grad]
+
+    def eager():
+        pair.zero_grad(set_to_none=True)
+        x.grad = None
+        pair(x, ctx_s, ctx_t).backward(dy)
+
+    side = torch.cuda.Stream()
+    side.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(side):
+        for _ in range(3):
+            eager()
+    torch.cuda.current_stream().wait_stream(side)
+    torch.cuda.synchronize()
+    want = [p.grad.clone() for p in gparams] + [x.grad.clone()]
+    pair.zero_grad(set_to_none=True)
+    x.grad = None
+    cg = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(cg):
+        pair(x, ctx_s, ctx_t).backward(dy)   # .grad tensors are created inside the capture: static across replays
+
+    def gstep():
+        cg.replay()
+        if world > 1:
+            flatg = torch.cat([p.grad.flatten() for p in gparams])
+            dist.all_reduce(flatg)
+
+    graph_ms = timed(gstep, args.steps)
+    cg.replay()
+    torch.cuda.synchronize()
+    graph_same = all(torch.equal(a, b) for a, b in zip(want, [p.grad for p in gparams] + [x.grad]))
+    del cg
+    pair.zero_grad(set_to_none=True)
+    x.grad = None
+model = DDP(pair, device_ids=[local], gradient_as_bucket_view=True)
+
+
+def step(sync=True):
+    model.zero_grad(set_to_none=True)
+    x.grad = None
+    if sync:
+        model(x, ctx_s, ctx_t).backward(dy)
+    else:
+        with model.no_sync():
+            model(x, ctx_s, ctx_t).backward(dy)
 
 
 ms_ddp = timed(lambda: step(True), args.steps)
@@ -159,6 +203,7 @@ if rank == 0:
         "clips_per_gpu": B, "param_dtype": args.param_dtype, "trainable_params": sum(p.numel() for p in params),
         "gradient_bytes": nbytes, "ms_step_ddp": ms_ddp, "ms_step_no_sync": ms_local, "ms_allreduce_alone": ms_allreduce,
         "ms_ddp_minus_no_sync": ddp_extra,
+        "ms_step_cuda_graph": graph_ms, "cuda_graph_gradients_identical_to_eager": graph_same,
         # meaningful only when the exchange itself is long against the run-to-run noise of a step (a few 0.1 ms)
         "overlap_fraction": (max(0.0, min(1.0, 1.0 - max(0.0, ddp_extra) / ms_allreduce)) if world > 1 and ms_allreduce >= 1.0 else None),
         "clip_frames_per_s": world * B * T / (ms_ddp * 1e-3), "gradients_identical_on_all_ranks": bool(int(same)), "finite": finite,
