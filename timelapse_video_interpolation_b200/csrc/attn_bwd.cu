@@ -579,7 +579,9 @@ __device__ __forceinline__ void unpack8b(const uint4& u, float* f) {
   }
 }
 
-constexpr int kFewBwdRowsPerThread = 32;
+constexpr int kFewBwdRowsPerThread = 32;      // default rows per thread and tile (the launcher picks 16 .. 128, see launch_fewkeys_bwd)
+constexpr int kFewBwdMinRowsPerThread = 16;
+constexpr int kFewBwdMaxRowsPerThread = 128;
 constexpr int kFkDepth = 6;  // two-key kernel: rows in flight per thread (16-byte q and dO chunks in a shared-memory FIFO)
 
 struct FkParams {
@@ -589,6 +591,7 @@ struct FkParams {
   int64_t ldq, ldk, ldv, lddo, lddq, lddk, lddv;
   int64_t rows_per_group;
   int tiles_per_group, L, Tq;
+  int rows_per_thread;  // rows of a tile = row lanes (blockDim.y) * rows_per_thread
   float scale;
   const float* bias;
   int64_t inner;  // > 1: interleaved groups (logical row i of group (b, s) is physical row (b * rows_per_group + i) * inner + s)
@@ -602,7 +605,7 @@ __global__ void __launch_bounds__(256) attn_fewkeys_bwd_kernel(const FkParams p)
   const int C = blockDim.x * 8;
   const int64_t group = blockIdx.x / p.tiles_per_group;
   const int tile = blockIdx.x - (int)(group * p.tiles_per_group);
-  const int64_t rows_per_tile = (int64_t)RY * kFewBwdRowsPerThread;
+  const int64_t rows_per_tile = (int64_t)RY * p.rows_per_thread;
   const int64_t rlo = group * p.rows_per_group + (int64_t)tile * rows_per_tile;
   int64_t rhi = rlo + rows_per_tile;
   const int64_t gend = (group + 1) * p.rows_per_group;
@@ -748,8 +751,7 @@ __global__ void __launch_bounds__(256) attn_fewkeys_bwd_kernel(const FkParams p)
   // the Q / dO chunks of kUnroll rows are requested before the first of them is used (memory-level parallelism: the
   // arithmetic of a row is a dependent chain of ~150 instructions)
   constexpr int kUnroll = 2;
-  static_assert(kFewBwdRowsPerThread % kUnroll == 0, "row loop is unrolled in groups");
-  for (int it0 = 0; it0 < kFewBwdRowsPerThread; it0 += kUnroll) {
+  for (int it0 = 0; it0 < p.rows_per_thread; it0 += kUnroll) {  // rows_per_thread is even
     if (rlo + (int64_t)it0 * RY >= rhi) break;  // block-uniform
     uint4 qv[kUnroll], gv[kUnroll];
 #pragma unroll
@@ -920,13 +922,14 @@ int fk_block_rows(int C8) {
   return RY;
 }
 
-int fk_tiles(int64_t rows_per_group, int C8) {
-  const int64_t rows_per_tile = (int64_t)fk_block_rows(C8) * kFewBwdRowsPerThread;
+int fk_tiles(int64_t rows_per_group, int C8, int rows_per_thread) {
+  const int64_t rows_per_tile = (int64_t)fk_block_rows(C8) * rows_per_thread;
   return (int)((rows_per_group + rows_per_tile - 1) / rows_per_tile);
 }
 
 template <int LT, int LPH>
-int launch_fewkeys_bwd(const FkParams& p, int64_t ngroups, int C8, cudaStream_t st) {
+int launch_fewkeys_bwd(const FkParams& p_in, int64_t ngroups, int C8, cudaStream_t st, int* tiles_out) {
+  FkParams p = p_in;
   const int RY = fk_block_rows(C8);
   TVI_CHECK_ARG(C8 * RY <= 256, "tvi_attn_fewkeys_bwd: heads*d = %d is too wide for this kernel", C8 * 8);
   const size_t sums = (size_t)2 * LT * C8 * 8 * sizeof(float);
@@ -943,6 +946,27 @@ int launch_fewkeys_bwd(const FkParams& p, int64_t ngroups, int C8, cudaStream_t 
     TVI_CUDA_OK(cudaFuncSetAttribute(attn_fewkeys_bwd_kernel<LT, LPH>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
     if (dev >= 0 && dev < 64) configured[dev] = sm;
   }
+  // Tile height.  Every tile costs the same and pays a K / V prologue and a partial-sum epilogue, so the grid should be ONE
+  // wave that fills the resident CTA slots, or else waves whose last one is full: among 16 .. 128 rows per thread take the
+  // height with the best fill (near-ties: the taller tile).  L0 spatial cross-attention (28 groups x 9 216 rows, 5 CTAs x
+  // 148 SMs resident): 32 rows per thread = 2 016 tiles = 2.72 waves; 88 rows = 27 x 28 = 756 ... the search decides.
+  int per_sm = 1;
+  TVI_CUDA_OK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, attn_fewkeys_bwd_kernel<LT, LPH>, C8 * RY, sm));
+  const int64_t resident = (int64_t)num_sms() * (per_sm > 0 ? per_sm : 1);
+  int best_rpt = kFewBwdRowsPerThread;
+  double best_eff = -1.0;
+  for (int rpt = kFewBwdMaxRowsPerThread; rpt >= kFewBwdMinRowsPerThread; rpt -= 2) {
+    const int64_t blocks = ngroups * fk_tiles(p.rows_per_group, C8, rpt);
+    const int64_t waves = (blocks + resident - 1) / resident;
+    const double eff = (double)blocks / (double)(waves * resident);
+    if (eff > best_eff + 0.02) {
+      best_eff = eff;
+      best_rpt = rpt;
+    }
+  }
+  p.rows_per_thread = best_rpt;
+  p.tiles_per_group = fk_tiles(p.rows_per_group, C8, best_rpt);
+  *tiles_out = p.tiles_per_group;
   TVI_CHECK_ARG((int64_t)p.tiles_per_group * ngroups < ((int64_t)1 << 31), "tvi_attn_fewkeys_bwd: grid too large");
   dim3 block((unsigned)C8, (unsigned)RY);
   dim3 grid((unsigned)(p.tiles_per_group * ngroups));
@@ -1078,7 +1102,7 @@ int tvi_attn_temporal_bwd_interleaved(const tvi_bf16* q, const tvi_bf16* k, cons
 size_t tvi_attn_fewkeys_bwd_workspace_bytes(int64_t nrows, int64_t rows_per_group, int heads, int L, int d) {
   if (nrows <= 0 || rows_per_group <= 0 || heads <= 0 || L <= 0 || d <= 0) return 0;
   const int C = heads * d;
-  const int tiles = tvi::fk_tiles(rows_per_group, C / 8);
+  const int tiles = tvi::fk_tiles(rows_per_group, C / 8, tvi::kFewBwdMinRowsPerThread);  // the most the launcher may use
   if (tiles == 1) return 0;
   return (size_t)(nrows / rows_per_group) * tiles * 2 * L * (size_t)C * sizeof(float);
 }
@@ -1118,23 +1142,25 @@ int tvi_attn_fewkeys_bwd_interleaved(const tvi_bf16* q, const tvi_bf16* k, const
   p.partial = (float*)workspace;
   p.ldq = ldq; p.ldk = ldk; p.ldv = ldv; p.lddo = lddo; p.lddq = lddq; p.lddk = lddk; p.lddv = lddv;
   p.rows_per_group = rows_per_group;
-  p.tiles_per_group = fk_tiles(rows_per_group, C / 8);
+  p.tiles_per_group = fk_tiles(rows_per_group, C / 8, kFewBwdMinRowsPerThread);  // upper bound; the launcher sets the real one
+  p.rows_per_thread = kFewBwdRowsPerThread;
   p.L = L; p.Tq = Tq; p.scale = scale; p.bias = bias;
   TVI_CHECK_ARG(p.tiles_per_group == 1 || (workspace != nullptr && (uintptr_t)workspace % 16 == 0),
                 "tvi_attn_fewkeys_bwd: workspace required (16-byte aligned)");
   cudaStream_t st = (cudaStream_t)stream;
   int rc;
-#define TVI_FEWB(LT) (d == 64 ? launch_fewkeys_bwd<LT, 8>(p, ngroups, C / 8, st) : launch_fewkeys_bwd<LT, 16>(p, ngroups, C / 8, st))
+  int tiles = 1;
+#define TVI_FEWB(LT) (d == 64 ? launch_fewkeys_bwd<LT, 8>(p, ngroups, C / 8, st, &tiles) : launch_fewkeys_bwd<LT, 16>(p, ngroups, C / 8, st, &tiles))
   if (L == 1) rc = TVI_FEWB(1);
   else if (L == 2) rc = TVI_FEWB(2);
   else if (L <= 4) rc = TVI_FEWB(4);
   else rc = TVI_FEWB(8);
 #undef TVI_FEWB
   if (rc != TVI_OK) return rc;
-  if (p.tiles_per_group > 1) {
+  if (tiles > 1) {
     const int64_t total = ngroups * 2 * L * (C / 2);
-    fewkeys_bwd_final_kernel<<<(unsigned)((total + 255) / 256), 256, 0, st>>>((const float*)workspace, dk, dv, ngroups,
-                                                                              p.tiles_per_group, L, C, lddk, lddv);
+    fewkeys_bwd_final_kernel<<<(unsigned)((total + 255) / 256), 256, 0, st>>>((const float*)workspace, dk, dv, ngroups, tiles, L, C,
+                                                                              lddk, lddv);
     TVI_LAUNCH_OK("fewkeys_bwd_final_kernel");
   }
   return TVI_OK;
