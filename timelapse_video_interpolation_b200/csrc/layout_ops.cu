@@ -79,7 +79,11 @@ __global__ void __launch_bounds__(256)
 groupnorm_tokens_kernel(const tvi_bf16* __restrict__ x, const double2* __restrict__ partial, const tvi_bf16* __restrict__ gamma,
                         const tvi_bf16* __restrict__ beta, tvi_bf16* __restrict__ y, int C, int HW, int groups, int nsplit,
                         int64_t ldy, float eps) {
-  __shared__ __align__(16) __nv_bfloat16 tile[kTile][kPitch];  // [spatial][channel]
+  // [channel][spatial] as it is read, 16-byte chunk k of row r stored at k ^ (r / 8 % 8): the vector stores of a quarter
+  // warp fill one 128-byte row, and the 2-byte gathers of the transposing read (rows 8 apart for the lanes of a warp) land
+  // in eight different 16-byte bank groups.  (The first version transposed with scalar stores into a padded [spatial][channel]
+  // tile whose rows 8 apart shared a bank: 8-way conflicts on every store.)
+  __shared__ __align__(16) uint4 tile[kTile][8];
   __shared__ float s_scale[kTile], s_shift[kTile];
   const int n = blockIdx.z;
   const int c0 = blockIdx.y * kTile, s0 = blockIdx.x * kTile;
@@ -114,21 +118,33 @@ groupnorm_tokens_kernel(const tvi_bf16* __restrict__ x, const double2* __restric
   for (int j = 0; j < 2; ++j) {
     const int cl = (threadIdx.x >> 3) + 32 * j;
     const int c = c0 + cl, s = s0 + chunk * 8;
+    uint4 v = make_uint4(0u, 0u, 0u, 0u);
     if (c < C && s < HW) {  // HW % 8 == 0
       float f[8];
       unpack8f(__ldg(reinterpret_cast<const uint4*>(x + ((int64_t)n * C + c) * HW + s)), f);
       const float sc = s_scale[cl], sh = s_shift[cl];
-#pragma unroll
-      for (int i = 0; i < 8; ++i) tile[chunk * 8 + i][cl] = __float2bfloat16_rn(fmaf(f[i], sc, sh));
+      v = make_uint4(pack_bf16x2(fmaf(f[0], sc, sh), fmaf(f[1], sc, sh)), pack_bf16x2(fmaf(f[2], sc, sh), fmaf(f[3], sc, sh)),
+                     pack_bf16x2(fmaf(f[4], sc, sh), fmaf(f[5], sc, sh)), pack_bf16x2(fmaf(f[6], sc, sh), fmaf(f[7], sc, sh)));
     }
+    tile[cl][chunk ^ ((cl >> 3) & 7)] = v;
   }
   __syncthreads();
+  const uint16_t* t16 = reinterpret_cast<const uint16_t*>(&tile[0][0]);
 #pragma unroll
   for (int j = 0; j < 2; ++j) {
     const int sl = (threadIdx.x >> 3) + 32 * j;
     const int s = s0 + sl, c = c0 + chunk * 8;
-    if (s < HW && c < C)  // C % 8 == 0
-      *reinterpret_cast<uint4*>(y + ((int64_t)n * HW + s) * ldy + c) = *reinterpret_cast<const uint4*>(&tile[sl][chunk * 8]);
+    if (s < HW && c < C) {  // C % 8 == 0
+      // channels chunk * 8 + i of spatial position sl: row r = chunk * 8 + i holds it in chunk (sl / 8) ^ chunk
+      const int off = (((sl >> 3) ^ chunk) << 3) + (sl & 7);
+      uint32_t o[4];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const uint32_t lo = t16[(chunk * 8 + 2 * i) * 64 + off], hi = t16[(chunk * 8 + 2 * i + 1) * 64 + off];
+        o[i] = lo | (hi << 16);
+      }
+      *reinterpret_cast<uint4*>(y + ((int64_t)n * HW + s) * ldy + c) = make_uint4(o[0], o[1], o[2], o[3]);
+    }
   }
 }
 
@@ -136,7 +152,7 @@ groupnorm_tokens_kernel(const tvi_bf16* __restrict__ x, const double2* __restric
 __global__ void __launch_bounds__(256)
 tokens_to_nchw_add_kernel(const tvi_bf16* __restrict__ y, const tvi_bf16* __restrict__ residual, tvi_bf16* __restrict__ out,
                           int C, int HW, int64_t ldy) {
-  __shared__ __align__(16) __nv_bfloat16 tile[kTile][kPitch];  // [channel][spatial]
+  __shared__ __align__(16) uint4 tile[kTile][8];  // [spatial][channel] as read, chunk k of row r at k ^ (r / 8 % 8) (see above)
   const int n = blockIdx.z;
   const int c0 = blockIdx.y * kTile, s0 = blockIdx.x * kTile;
   const int chunk = threadIdx.x & 7;
@@ -144,22 +160,23 @@ tokens_to_nchw_add_kernel(const tvi_bf16* __restrict__ y, const tvi_bf16* __rest
   for (int j = 0; j < 2; ++j) {
     const int sl = (threadIdx.x >> 3) + 32 * j;
     const int s = s0 + sl, c = c0 + chunk * 8;
-    if (s < HW && c < C) {
-      const uint4 u = __ldg(reinterpret_cast<const uint4*>(y + ((int64_t)n * HW + s) * ldy + c));
-      const __nv_bfloat16* h = reinterpret_cast<const __nv_bfloat16*>(&u);
-#pragma unroll
-      for (int i = 0; i < 8; ++i) tile[chunk * 8 + i][sl] = h[i];
-    }
+    uint4 v = make_uint4(0u, 0u, 0u, 0u);
+    if (s < HW && c < C) v = __ldg(reinterpret_cast<const uint4*>(y + ((int64_t)n * HW + s) * ldy + c));
+    tile[sl][chunk ^ ((sl >> 3) & 7)] = v;
   }
   __syncthreads();
+  const uint16_t* t16 = reinterpret_cast<const uint16_t*>(&tile[0][0]);
 #pragma unroll
   for (int j = 0; j < 2; ++j) {
     const int cl = (threadIdx.x >> 3) + 32 * j;
     const int c = c0 + cl, s = s0 + chunk * 8;
     if (c < C && s < HW) {
       const int64_t off = ((int64_t)n * C + c) * HW + s;
+      // spatial positions chunk * 8 + i of channel cl: row r = chunk * 8 + i holds it in chunk (cl / 8) ^ chunk
+      const int so = (((cl >> 3) ^ chunk) << 3) + (cl & 7);
       float a[8], b[8];
-      unpack8f(*reinterpret_cast<const uint4*>(&tile[cl][chunk * 8]), a);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) a[i] = __uint_as_float((uint32_t)t16[(chunk * 8 + i) * 64 + so] << 16);
       if (residual != nullptr) {
         unpack8f(__ldg(reinterpret_cast<const uint4*>(residual + off)), b);
 #pragma unroll
