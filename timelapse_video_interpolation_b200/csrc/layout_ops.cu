@@ -18,7 +18,6 @@ namespace {
 
 constexpr int kGnSlice = 16384;  // elements of one (image, group) span per statistics CTA
 constexpr int kTile = 64;
-constexpr int kPitch = 72;       // bf16 elements per tile row (144 B: 16-byte aligned, 4-bank shift per row)
 
 __device__ __forceinline__ void unpack8f(const uint4& u, float* f) {
   const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&u);
@@ -240,7 +239,7 @@ __global__ void gn_stats_finalize_kernel(const double2* __restrict__ partial, fl
 __global__ void __launch_bounds__(256)
 gn_bwd_reduce_kernel(const tvi_bf16* __restrict__ x, const tvi_bf16* __restrict__ dn, float2* __restrict__ partial, int C, int HW,
                      int64_t lddn) {
-  __shared__ __align__(16) __nv_bfloat16 tile[kTile][kPitch];  // dn as [spatial][channel]
+  __shared__ __align__(16) uint4 tile[kTile][8];  // dn as [spatial][channel], chunk k of row r at k ^ (r / 8 % 8) (see groupnorm_tokens_kernel)
   const int n = blockIdx.z;
   const int c0 = blockIdx.y * kTile, s0 = blockIdx.x * kTile;
   const int chunk = threadIdx.x & 7;
@@ -250,7 +249,7 @@ gn_bwd_reduce_kernel(const tvi_bf16* __restrict__ x, const tvi_bf16* __restrict_
     const int sp = s0 + sl, c = c0 + chunk * 8;
     uint4 u = make_uint4(0, 0, 0, 0);
     if (sp < HW && c < C) u = __ldg(reinterpret_cast<const uint4*>(dn + ((int64_t)n * HW + sp) * lddn + c));
-    *reinterpret_cast<uint4*>(&tile[sl][chunk * 8]) = u;
+    tile[sl][chunk ^ ((sl >> 3) & 7)] = u;
   }
   __syncthreads();
 #pragma unroll
@@ -261,9 +260,11 @@ gn_bwd_reduce_kernel(const tvi_bf16* __restrict__ x, const tvi_bf16* __restrict_
     if (c < C && sp < HW) {
       float f[8];
       unpack8f(__ldg(reinterpret_cast<const uint4*>(x + ((int64_t)n * C + c) * HW + sp)), f);
+      const uint16_t* t16 = reinterpret_cast<const uint16_t*>(&tile[0][0]);
+      const int so = (((cl >> 3) ^ chunk) << 3) + (cl & 7);
 #pragma unroll
       for (int i = 0; i < 8; ++i) {
-        const float d = __bfloat162float(tile[chunk * 8 + i][cl]);
+        const float d = __uint_as_float((uint32_t)t16[(chunk * 8 + i) * 64 + so] << 16);
         a += d;
         b = fmaf(d, f[i], b);
       }
@@ -314,7 +315,7 @@ __global__ void __launch_bounds__(256)
 gn_bwd_apply_kernel(const tvi_bf16* __restrict__ x, const tvi_bf16* __restrict__ dn, const tvi_bf16* __restrict__ gamma,
                     const float2* __restrict__ ab, const float2* __restrict__ mr, tvi_bf16* __restrict__ dx, int C, int HW,
                     int groups, int64_t lddn) {
-  __shared__ __align__(16) __nv_bfloat16 tile[kTile][kPitch];  // dn as [spatial][channel]
+  __shared__ __align__(16) uint4 tile[kTile][8];  // dn as [spatial][channel], chunk k of row r at k ^ (r / 8 % 8) (see groupnorm_tokens_kernel)
   __shared__ float s_k1[kTile], s_k2[kTile], s_k3[kTile];
   const int n = blockIdx.z;
   const int c0 = blockIdx.y * kTile, s0 = blockIdx.x * kTile;
@@ -350,7 +351,7 @@ gn_bwd_apply_kernel(const tvi_bf16* __restrict__ x, const tvi_bf16* __restrict__
     const int sp = s0 + sl, c = c0 + chunk * 8;
     uint4 u = make_uint4(0, 0, 0, 0);
     if (sp < HW && c < C) u = __ldg(reinterpret_cast<const uint4*>(dn + ((int64_t)n * HW + sp) * lddn + c));
-    *reinterpret_cast<uint4*>(&tile[sl][chunk * 8]) = u;
+    tile[sl][chunk ^ ((sl >> 3) & 7)] = u;
   }
   __syncthreads();
 #pragma unroll
@@ -362,8 +363,11 @@ gn_bwd_apply_kernel(const tvi_bf16* __restrict__ x, const tvi_bf16* __restrict__
       float f[8], o[8];
       unpack8f(__ldg(reinterpret_cast<const uint4*>(x + off)), f);
       const float k1 = s_k1[cl], k2 = s_k2[cl], k3 = s_k3[cl];
+      const uint16_t* t16 = reinterpret_cast<const uint16_t*>(&tile[0][0]);
+      const int so = (((cl >> 3) ^ chunk) << 3) + (cl & 7);
 #pragma unroll
-      for (int i = 0; i < 8; ++i) o[i] = fmaf(k1, __bfloat162float(tile[chunk * 8 + i][cl]), fmaf(k2, f[i], k3));
+      for (int i = 0; i < 8; ++i)
+        o[i] = fmaf(k1, __uint_as_float((uint32_t)t16[(chunk * 8 + i) * 64 + so] << 16), fmaf(k2, f[i], k3));
       *reinterpret_cast<uint4*>(dx + off) =
           make_uint4(pack_bf16x2(o[0], o[1]), pack_bf16x2(o[2], o[3]), pack_bf16x2(o[4], o[5]), pack_bf16x2(o[6], o[7]));
     }
