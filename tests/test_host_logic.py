@@ -183,3 +183,25 @@ def test_cache_generation_tracks_data_copy():
     with torch.no_grad():
         attn.to_k.weight.add_(1.0)
     assert proc._fused(attn, ("to_q", "to_k", "to_v")) is not w2
+
+
+def test_stepper_and_feed_forward_reject_bad_arguments_without_a_gpu():
+    """Argument checks that run before any CUDA call: they must raise TviError on a CPU-only machine (no silent fallback)."""
+    import torch
+    from timelapse_video_interpolation_b200 import _lib, feedforward
+    from timelapse_video_interpolation_b200.step import EulerCfgStepper
+    sig = [10.0, 5.0, 1.0, 0.0]
+    with pytest.raises(_lib.TviError):
+        EulerCfgStepper(sig, torch.ones(4), latent_rounding="fp16")            # only None / "bf16" are built
+    with pytest.raises(_lib.TviError):
+        EulerCfgStepper(sig, torch.ones(4), prediction_type="sample")
+    with pytest.raises(_lib.TviError):
+        EulerCfgStepper([1.0], torch.ones(4))                                   # needs at least two sigmas
+    st = EulerCfgStepper(sig, torch.ones(4), latent_rounding="bf16")
+    assert st.rounding == _lib.LATENT_ROUND_BF16 and abs(st.init_noise_sigma - 101.0 ** 0.5) < 1e-6
+    with pytest.raises(_lib.TviError):
+        st.begin(torch.zeros(1, 4, 4, 8, 8), torch.zeros(2, 4, 5, 8, 8, dtype=torch.bfloat16))  # CPU latents
+    with pytest.raises(_lib.TviError):
+        st.step(torch.zeros(2, 4, 4, 8, 8, dtype=torch.bfloat16), 0)           # step before begin
+    with pytest.raises(_lib.TviError):
+        feedforward.layer_norm_residual(torch.nn.LayerNorm(16), torch.zeros(2, 16), pad_ones=True)  # CPU fp32 rows
