@@ -896,9 +896,12 @@ __global__ void __launch_bounds__(256) attn_fewkeys_bwd_kernel(const FkParams p)
   }
 }
 
-__global__ void fewkeys_bwd_final_kernel(const float* __restrict__ partial, tvi_bf16* __restrict__ dk, tvi_bf16* __restrict__ dv,
-                                         int64_t ngroups, int tiles, int L, int C, int64_t lddk, int64_t lddv) {
-  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;  // (group, which, l, column pair)
+// one warp per (group, dK | dV, key, column pair): lane l adds tiles l, l + 32, ... in order, then a fixed shuffle tree
+__global__ void __launch_bounds__(256)
+fewkeys_bwd_final_kernel(const float* __restrict__ partial, tvi_bf16* __restrict__ dk, tvi_bf16* __restrict__ dv, int64_t ngroups,
+                         int tiles, int L, int C, int64_t lddk, int64_t lddv) {
+  const int64_t i = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
   const int half = C / 2;
   const int64_t total = ngroups * 2 * L * half;
   if (i >= total) return;
@@ -907,13 +910,18 @@ __global__ void fewkeys_bwd_final_kernel(const float* __restrict__ partial, tvi_
   const int which = (int)((i / ((int64_t)half * L)) % 2);
   const int64_t g = i / ((int64_t)half * L * 2);
   float a = 0.f, b = 0.f;
-  for (int t = 0; t < tiles; ++t) {
+  for (int t = lane; t < tiles; t += 32) {
     const float2 v = *reinterpret_cast<const float2*>(partial + (((g * tiles + t) * 2 + which) * (int64_t)L + l) * C + cp * 2);
     a += v.x;
     b += v.y;
   }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    a += __shfl_xor_sync(0xffffffffu, a, o);
+    b += __shfl_xor_sync(0xffffffffu, b, o);
+  }
   tvi_bf16* dst = which == 0 ? dk + (g * L + l) * lddk : dv + (g * L + l) * lddv;
-  *reinterpret_cast<uint32_t*>(dst + cp * 2) = pack_bf16x2(a, b);
+  if (lane == 0) *reinterpret_cast<uint32_t*>(dst + cp * 2) = pack_bf16x2(a, b);
 }
 
 int fk_block_rows(int C8) {
@@ -1159,7 +1167,7 @@ int tvi_attn_fewkeys_bwd_interleaved(const tvi_bf16* q, const tvi_bf16* k, const
   if (rc != TVI_OK) return rc;
   if (tiles > 1) {
     const int64_t total = ngroups * 2 * L * (C / 2);
-    fewkeys_bwd_final_kernel<<<(unsigned)((total + 255) / 256), 256, 0, st>>>((const float*)workspace, dk, dv, ngroups, tiles, L, C,
+    fewkeys_bwd_final_kernel<<<(unsigned)((total + 7) / 8), 256, 0, st>>>((const float*)workspace, dk, dv, ngroups, tiles, L, C,
                                                                               lddk, lddv);
     TVI_LAUNCH_OK("fewkeys_bwd_final_kernel");
   }
